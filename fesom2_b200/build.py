@@ -1,0 +1,94 @@
+"""In-tree builds of the native pieces (no JIT cache: the .so files travel with the repo snapshot).
+
+  libfesom_host.so   fesom2_b200/host/*.cpp       g++      host-side mirror of the Fortran setup code
+  libfesom_b200.so   fesom2_b200/csrc/*.cu        nvcc     the product: CUDA kernels + C ABI (sm_100a)
+  liboracle.so       oracle/*.c                   gcc      CPU restatement of the reference (test infrastructure)
+  oracle/_ref/...    /root/reference pARMS + psolve.c  gcc (only when /root/reference exists)
+"""
+import glob
+import os
+import shutil
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "fesom2_b200")
+HOST_SO = os.path.join(PKG, "host", "libfesom_host.so")
+CUDA_SO = os.path.join(PKG, "csrc", "libfesom_b200.so")
+ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libpsolve_ref.so")
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def _run(cmd, cwd=None):
+    r = subprocess.run(cmd, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + r.stdout)
+        raise RuntimeError("build failed: " + " ".join(cmd[:3]))
+    return r.stdout
+
+
+def build_host(force=False):
+    src = sorted(glob.glob(os.path.join(PKG, "host", "*.cpp")))
+    dep = src + glob.glob(os.path.join(PKG, "host", "*.hpp"))
+    if force or _newer(HOST_SO, dep):
+        _run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-o", HOST_SO] + src)
+    return HOST_SO
+
+
+def nvcc_path():
+    for p in (shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if p and os.path.exists(p):
+            return p
+    return None
+
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "--fmad=false", "-Xcompiler", "-fPIC", "-shared"]
+
+
+def build_cuda(force=False, verbose=False):
+    src = sorted(glob.glob(os.path.join(PKG, "csrc", "*.cu")))
+    dep = src + glob.glob(os.path.join(PKG, "csrc", "*.cuh")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
+    if force or _newer(CUDA_SO, dep):
+        nvcc = nvcc_path()
+        if nvcc is None:
+            raise RuntimeError("nvcc not found: cannot build libfesom_b200.so")
+        flags = list(NVCC_FLAGS)
+        if verbose:
+            flags += ["-Xptxas", "-v"]
+        out = _run([nvcc] + flags + ["-I", os.path.join(ROOT, "include"), "-o", CUDA_SO] + src + ["-lnccl"])
+        if verbose:
+            print(out)
+    return CUDA_SO
+
+
+def build_oracle(force=False):
+    src = sorted(glob.glob(os.path.join(ROOT, "oracle", "*.c")))
+    dep = src + glob.glob(os.path.join(ROOT, "oracle", "*.h"))
+    if force or _newer(ORACLE_SO, dep):
+        _run(["gcc", "-O2", "-std=c99", "-fPIC", "-shared", "-ffp-contract=off", "-fopenmp", "-o", ORACLE_SO] + src + ["-lm"])
+    return ORACLE_SO
+
+
+def build_ref(force=False):
+    """Compile the reference's own pARMS + psolve.c from /root/reference (read in place) into oracle/_ref."""
+    mk = os.path.join(ROOT, "oracle", "Makefile.ref")
+    if not os.path.isdir("/root/reference/lib/parms") or not os.path.exists(mk):
+        return REF_SO if os.path.exists(REF_SO) else None
+    if force or not os.path.exists(REF_SO):
+        _run(["make", "-s", "-f", mk, "-j8"], cwd=os.path.join(ROOT, "oracle"))
+    return REF_SO
+
+
+def build_all(force=False):
+    build_host(force)
+    build_oracle(force)
+    build_ref(force)
+    build_cuda(force)

@@ -1,0 +1,149 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY (see oracle/oracle.h).
+
+ctypes binding of liboracle.so (the C restatement of the reference's tracer step and SSH solve) and of
+oracle/_ref/libpsolve_ref.so (the reference's own psolve.c + pARMS, compiled serially from
+/root/reference).  Imported by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs only.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_lib = None
+
+HOR = {"MUSCL": 0, "MFCT": 1, "UPW1": 2}
+VER = {"QR4C": 0, "CDIFF": 1, "PPM": 2, "UPW1": 3}
+LIM = {"FCT": 0, "NONE": 1}
+
+MESH_INT = ["edges", "edge_tri", "elem2D_nodes", "nlevels", "ulevels", "nlevels_nod2D", "ulevels_nod2D",
+            "nlevels_nod2D_min", "ulevels_nod2D_max", "nod_in_elem2D", "nod_in_elem2D_num", "edge_up_dn_tri",
+            "nboundary_lay"]
+MESH_DBL = ["edge_cross_dxdy", "edge_dxdy", "elem_cos", "elem_area", "gradient_sca", "area", "areasvol", "zbar_n_bot"]
+STATE_DBL = ["UV", "Wvel", "Wvel_e", "Wvel_i", "hnode", "hnode_new", "helem", "Z_3d_n", "zbar_3d_n", "Kv", "Ki",
+             "slope_tapered", "heat_flux", "water_flux", "virtual_salt", "relax_salt", "real_salt_flux", "sw_3d"]
+DIMS = ["nl", "myDim_nod2D", "eDim_nod2D", "myDim_elem2D", "eDim_elem2D", "eXDim_elem2D", "myDim_edge2D"]
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        from fesom2_b200 import build
+        L = C.CDLL(build.build_oracle())
+        L.oracle_create.restype = C.c_void_p
+        L.oracle_free.argtypes = [C.c_void_p]
+        L.oracle_set_int.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.oracle_set_dbl.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
+        L.oracle_set_ptr.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
+        L.oracle_get_ptr.argtypes = [C.c_void_p, C.c_char_p]
+        L.oracle_get_ptr.restype = C.c_void_p
+        L.oracle_alloc_work.argtypes = [C.c_void_p]
+        for nm in ("o_phase1", "o_phase2", "o_phase3", "o_phase4", "o_phase5"):
+            getattr(L, nm).argtypes = [C.c_void_p, C.c_int]
+            getattr(L, nm).restype = None
+        L.o_phase_final.argtypes = [C.c_void_p]
+        L.o_phase_final.restype = None
+        L.o_solve_tracers_ale.argtypes = [C.c_void_p]
+        L.o_solve_tracers_ale.restype = None
+        L.o_ssh_solve.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                  C.c_double, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        L.o_spmv.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.o_spmv.restype = None
+        _lib = L
+    return _lib
+
+
+class TracerOracle:
+    """Binds a HostModel's arrays (no copies) into an oracle context.  tr_arr / tr_arr_old are updated in place."""
+
+    def __init__(self, hm, tra_adv_hor="MFCT", tra_adv_ver="QR4C", tra_adv_lim="FCT", tra_adv_ph=1.0, tra_adv_pv=1.0,
+                 w_split=None, i_vert_diff=True, Redi=False, use_sw_pene=False, do_hor_diff=True, clamp_salt=True,
+                 tracer_ids=(0, 1)):
+        self.L = lib()
+        self.hm = hm
+        self.o = C.c_void_p(self.L.oracle_create())
+        self._keep = []
+        si, sd, sp = self.L.oracle_set_int, self.L.oracle_set_dbl, self.L.oracle_set_ptr
+        for d in DIMS:
+            assert si(self.o, d.encode(), hm.ipar(d)) == 0
+        si(self.o, b"nod_in_elem2D_max", hm.ipar("nod_in_elem2D_max"))
+        si(self.o, b"num_tracers", hm.ipar("num_tracers"))
+        for nm in MESH_INT + MESH_DBL + STATE_DBL + ["tr_arr", "tr_arr_old"]:
+            a = hm.arr(nm)
+            self._keep.append(a)
+            assert sp(self.o, nm.encode(), a.ctypes.data) == 0, nm
+        sd(self.o, b"dt", hm.par("dt"))
+        sd(self.o, b"is_nonlinfs", hm.par("is_nonlinfs"))
+        sd(self.o, b"tra_adv_ph", tra_adv_ph)
+        sd(self.o, b"tra_adv_pv", tra_adv_pv)
+        si(self.o, b"tra_adv_hor", HOR[tra_adv_hor])
+        si(self.o, b"tra_adv_ver", VER[tra_adv_ver])
+        si(self.o, b"tra_adv_lim", LIM[tra_adv_lim])
+        si(self.o, b"w_split", hm.ipar("w_split") if w_split is None else int(w_split))
+        si(self.o, b"i_vert_diff", int(i_vert_diff))
+        si(self.o, b"Redi", int(Redi))
+        si(self.o, b"use_sw_pene", int(use_sw_pene))
+        si(self.o, b"do_hor_diff", int(do_hor_diff))
+        si(self.o, b"clamp_salt", int(clamp_salt))
+        for k, tid in enumerate(tracer_ids):
+            si(self.o, ("tracer_id%d" % k).encode(), int(tid))
+        assert self.L.oracle_alloc_work(self.o) == 0
+
+    def __del__(self):
+        try:
+            self.L.oracle_free(self.o)
+        except Exception:
+            pass
+
+    def work(self, name, fshape):
+        """numpy view (reversed Fortran shape) of an oracle-owned work array"""
+        p = self.L.oracle_get_ptr(self.o, name.encode())
+        n = int(np.prod(fshape))
+        buf = (C.c_double * n).from_address(p)
+        return np.frombuffer(buf, dtype=np.float64).reshape(tuple(fshape)[::-1])
+
+    def step(self):
+        self.L.o_solve_tracers_ale(self.o)
+
+    def phase(self, k, tr_num):
+        getattr(self.L, "o_phase%d" % k)(self.o, int(tr_num))
+
+    def final(self):
+        self.L.o_phase_final(self.o)
+
+
+def ssh_solve(rowptr0, colind0, values, rhs, x0, pc_kind=1, block=1, soltol=1e-10, maxits=2000):
+    L = lib()
+    rp = np.ascontiguousarray(rowptr0, dtype=np.int32)
+    ci = np.ascontiguousarray(colind0, dtype=np.int32)
+    v = np.ascontiguousarray(values, dtype=np.float64)
+    b = np.ascontiguousarray(rhs, dtype=np.float64)
+    x = np.array(x0, dtype=np.float64, copy=True)
+    its = C.c_int()
+    res = C.c_double()
+    rc = L.o_ssh_solve(rp.size - 1, rp.ctypes.data, ci.ctypes.data, v.ctypes.data, b.ctypes.data, x.ctypes.data,
+                       int(pc_kind), int(block), float(soltol), int(maxits), C.byref(its), C.byref(res))
+    return x, its.value, res.value, rc
+
+
+# ---------------------------------------------------------------------------------------------------
+_ref = None
+
+
+def ref_lib():
+    """the reference's own psolver_init/psolve (src/psolve.c + lib/parms), or None if it was never built"""
+    global _ref
+    if _ref is None:
+        from fesom2_b200 import build
+        so = build.build_ref()
+        if so is None or not os.path.exists(so):
+            return None
+        R = C.CDLL(so)
+        P = C.POINTER
+        R.psolver_init.argtypes = [P(C.c_int)] * 6 + [P(C.c_double)] + [P(C.c_int)] * 2 + [P(C.c_double)] + \
+                                  [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, P(C.c_int), P(C.c_int)]
+        R.psolver_init.restype = None
+        R.psolve.argtypes = [P(C.c_int), C.c_void_p, C.c_void_p, C.c_void_p, P(C.c_int)]
+        R.psolve.restype = None
+        _ref = R
+    return _ref
