@@ -1,0 +1,195 @@
+"""Caller side of the C ABI (include/fesom_b200.h) for Python: what the reference's Fortran routines
+`solve_tracers_ale` (src/oce_ale_tracer.F90:101) and `solve_ssh_ale` (src/oce_ale.F90:2210) do with the library,
+written with ctypes.  Every call goes through the extern "C" entry points with plain pointers — the same
+calls the Fortran shim in INTEGRATION.md makes.  There is no CPU fallback: loading fails loudly if the CUDA
+library has not been built, and every compute call raises if the library reports an error.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_lib = None
+
+HOR = {"MUSCL": 0, "MFCT": 1, "UPW1": 2}
+VER = {"QR4C": 0, "CDIFF": 1, "PPM": 2, "UPW1": 3}
+LIM = {"FCT": 0, "NONE": 1}
+
+EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
+           "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
+           "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_tracers",
+           "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_debug_fetch",
+           "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
+           "fb200_kernel_launches", "fb200_last_ms"]
+
+
+class FesomB200Error(RuntimeError):
+    pass
+
+
+def lib(rebuild=False):
+    global _lib
+    if _lib is None or rebuild:
+        so = _build.CUDA_SO
+        if rebuild or not os.path.exists(so) or _build.nvcc_path() is not None:
+            so = _build.build_cuda()
+        if not os.path.exists(so):
+            raise FesomB200Error("libfesom_b200.so is missing and nvcc is unavailable: build it with __graft_entry__.build()")
+        L = C.CDLL(so)
+        L.fb200_status.restype = C.c_int
+        L.fb200_status_message.restype = C.c_char_p
+        L.fb200_kernel_launches.restype = C.c_longlong
+        L.fb200_last_ms.restype = C.c_double
+        L.fb200_last_ms.argtypes = [C.c_char_p]
+        L.fb200_debug_fetch.argtypes = [C.c_char_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _check(L):
+    if L.fb200_status() != 0:
+        msg = L.fb200_status_message().decode()
+        code = L.fb200_status()
+        L.fb200_clear_status()
+        raise FesomB200Error("fesom_b200 error %d: %s" % (code, msg))
+
+
+def _i(v):
+    return C.byref(C.c_int(int(v)))
+
+
+def _d(v):
+    return C.byref(C.c_double(float(v)))
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data)
+
+
+class TracerEngine:
+    """Device-side `solve_tracers_ale`.  `hm` is a HostModel (the Fortran driver's state)."""
+
+    def __init__(self, hm, tra_adv_hor="MFCT", tra_adv_ver="QR4C", tra_adv_lim="FCT", tra_adv_ph=1.0, tra_adv_pv=1.0,
+                 w_split=None, i_vert_diff=True, Redi=False, use_sw_pene=False, do_hor_diff=True, clamp_salt=True,
+                 tracer_ids=(0, 1), epsilon=0.1):
+        self.L = lib()
+        self.hm = hm
+        L = self.L
+        L.fb200_clear_status()
+        ntr = hm.ipar("num_tracers")
+        L.fb200_init_dims(_i(hm.ipar("nl")), _i(hm.ipar("myDim_nod2D")), _i(hm.ipar("eDim_nod2D")), _i(hm.ipar("myDim_elem2D")),
+                          _i(hm.ipar("eDim_elem2D")), _i(hm.ipar("eXDim_elem2D")), _i(hm.ipar("myDim_edge2D")), _i(ntr), _i(0))
+        a = hm.arr
+        L.fb200_init_connectivity(_p(a("edges")), _p(a("edge_tri")), _p(a("elem2D_nodes")), _p(a("nod_in_elem2D_num")),
+                                  _p(a("nod_in_elem2D")), _i(hm.ipar("nod_in_elem2D_max")), _p(a("edge_up_dn_tri")))
+        L.fb200_init_levels(_p(a("nlevels")), _p(a("ulevels")), _p(a("nlevels_nod2D")), _p(a("ulevels_nod2D")),
+                            _p(a("nlevels_nod2D_min")), _p(a("ulevels_nod2D_max")), _p(a("nboundary_lay")))
+        L.fb200_init_geometry(_p(a("edge_cross_dxdy")), _p(a("edge_dxdy")), _p(a("elem_cos")), _p(a("elem_area")),
+                              _p(a("gradient_sca")), _p(a("area")), _p(a("areasvol")), _p(a("zbar_n_bot")))
+        ids = (C.c_int * 8)(*([int(t) for t in tracer_ids] + [301] * (8 - len(tracer_ids))))
+        ws = hm.ipar("w_split") if w_split is None else int(w_split)
+        L.fb200_set_options(_i(HOR[tra_adv_hor]), _i(VER[tra_adv_ver]), _i(LIM[tra_adv_lim]), _d(tra_adv_ph), _d(tra_adv_pv),
+                            _i(ws), _i(i_vert_diff), _i(Redi), _i(use_sw_pene), _i(do_hor_diff), _i(clamp_salt),
+                            _d(hm.par("is_nonlinfs")), _d(hm.par("dt")), _d(epsilon), ids)
+        _check(L)
+        L.fb200_init_commit()
+        _check(L)
+
+    def push_step_state(self):
+        a = self.hm.arr
+        self.L.fb200_push_step_state(_p(a("UV")), _p(a("Wvel")), _p(a("Wvel_e")), _p(a("Wvel_i")), _p(a("hnode")), _p(a("hnode_new")),
+                                     _p(a("helem")), _p(a("Z_3d_n")), _p(a("zbar_3d_n")), _p(a("Kv")), _p(a("Ki")),
+                                     _p(a("slope_tapered")), _p(a("heat_flux")), _p(a("water_flux")), _p(a("virtual_salt")),
+                                     _p(a("relax_salt")), _p(a("real_salt_flux")), _p(a("sw_3d")))
+        _check(self.L)
+
+    def push_tracers(self, tr=None, tro=None):
+        tr = self.hm.arr("tr_arr") if tr is None else tr
+        tro = self.hm.arr("tr_arr_old") if tro is None else tro
+        self.L.fb200_push_tracers(_p(tr), _p(tro))
+        _check(self.L)
+
+    def solve(self):
+        self.L.fb200_solve_tracers()
+        _check(self.L)
+
+    def pull_tracers(self, tr=None, tro=None):
+        tr = self.hm.arr("tr_arr") if tr is None else tr
+        tro = self.hm.arr("tr_arr_old") if tro is None else tro
+        self.L.fb200_pull_tracers(_p(tr), _p(tro))
+        _check(self.L)
+
+    def solve_tracers_ale(self, tr=None, tro=None):
+        """push + solve + pull: the drop-in for `call solve_tracers_ale(mesh)` with host-resident tracers"""
+        tr = self.hm.arr("tr_arr") if tr is None else tr
+        tro = self.hm.arr("tr_arr_old") if tro is None else tro
+        self.L.fb200_solve_tracers_ale(_p(tr), _p(tro))
+        _check(self.L)
+
+    def debug(self, name):
+        hm = self.hm
+        nl = hm.ipar("nl")
+        N = hm.ipar("myDim_nod2D") + hm.ipar("eDim_nod2D")
+        if name == "adf_h":
+            shape = (hm.ipar("myDim_edge2D"), nl - 1)
+        elif name in ("tr_xy_x", "tr_xy_y"):
+            shape = (hm.ipar("myDim_elem2D") + hm.ipar("eDim_elem2D") + hm.ipar("eXDim_elem2D"), nl - 1)
+        elif name == "adf_v":
+            shape = (N, nl)
+        else:
+            shape = (N, nl - 1)
+        out = np.zeros(shape)
+        self.L.fb200_debug_fetch(name.encode(), _p(out))
+        _check(self.L)
+        return out
+
+    def last_ms(self):
+        return self.L.fb200_last_ms(b"tracers")
+
+    def close(self):
+        self.L.fb200_finalize()
+
+
+class SSHSolver:
+    """`solve_ssh_ale` (src/oce_ale.F90:2295-2336): psolver_init on first use, psolve per step."""
+    SOLBICGS_RAS, PCRAS, PCILUK = 6, 2, 1        # lib/parms/include/fparms.h:25-32
+
+    def __init__(self, hm, ident=1, block=1, soltol=1e-10, maxiter=2000, reuse=1, library=None):
+        self.L = lib() if library is None else library
+        self.hm = hm
+        self.ident = ident
+        L = self.L
+        if library is None:
+            L.fb200_clear_status()
+            L.fb200_psolver_set_block(_i(block))
+        rp = hm.arr("ssh_rowptr")
+        self._part = (hm.arr("part") - 1).astype(np.int32)                 # part-1
+        self._rp = (rp - rp[0]).astype(np.int32)                            # rowptr(:)-rowptr(1)
+        self._ci = (hm.arr("ssh_colind") - 1).astype(np.int32)             # colind-1
+        vals = hm.arr("ssh_values")
+        fcomm = C.c_int(0)
+        L.psolver_init(_i(ident), _i(self.SOLBICGS_RAS), _i(self.PCRAS), _i(self.PCILUK), _i(2), _i(3), _d(1e-8),
+                       _i(maxiter), _i(15), _d(soltol), _p(self._part), _p(self._rp), _p(self._ci), _p(vals), _i(reuse),
+                       C.byref(fcomm))
+        if library is None:
+            _check(L)
+
+    def solve(self, new_values=1, rhs=None, sol=None):
+        hm = self.hm
+        rhs = hm.arr("ssh_rhs") if rhs is None else rhs
+        sol = hm.arr("d_eta") if sol is None else sol
+        self.L.psolve(_i(self.ident), _p(rhs), _p(hm.arr("ssh_values")), _p(sol), _i(new_values))
+        if hasattr(self.L, "fb200_status"):
+            _check(self.L)
+        return sol
+
+    def info(self):
+        its = C.c_int()
+        res = C.c_double()
+        self.L.fb200_psolve_info(_i(self.ident), C.byref(its), C.byref(res))
+        return its.value, res.value
+
+    def last_ms(self):
+        return self.L.fb200_last_ms(b"psolve")

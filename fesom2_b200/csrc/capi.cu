@@ -1,0 +1,162 @@
+// extern "C" entry points of the tracer path (include/fesom_b200.h).  Plain pointers and sizes only.
+#include "common.cuh"
+#include "fesom_b200.h"
+#include <cstring>
+
+int fb_status_code(); const char* fb_status_msg(); void fb_clear_status();
+const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind);
+double ssh_last_ms();
+
+extern "C" {
+
+int fb200_status(void) { return fb_status_code(); }
+const char* fb200_status_message(void) { return fb_status_msg(); }
+void fb200_clear_status(void) { fb_clear_status(); }
+long long fb200_kernel_launches(void) { return g_launches; }
+double fb200_last_ms(const char* what) {
+    if (what && !strcmp(what, "psolve")) return ssh_last_ms();
+    return (double)tctx().last_ms;
+}
+
+void fb200_init_dims(int* nl, int* myDim_nod2D, int* eDim_nod2D, int* myDim_elem2D, int* eDim_elem2D, int* eXDim_elem2D,
+                     int* myDim_edge2D, int* num_tracers, int* fcomm) {
+    (void)fcomm;
+    TracerCtx& c = tctx();
+    if (c.committed) ctx_release(c);
+    c.nl = *nl; c.myN = *myDim_nod2D; c.N = *myDim_nod2D + *eDim_nod2D;
+    c.myE = *myDim_elem2D; c.E = *myDim_elem2D + *eDim_elem2D; c.Eall = c.E + *eXDim_elem2D;
+    c.myEd = *myDim_edge2D; c.ntr = *num_tracers;
+    if (c.nl < 3 || c.myN < 1 || c.myE < 1 || c.myEd < 1 || c.ntr < 1 || c.ntr > 8) fb_set_error(30, "fb200_init_dims: bad dimensions");
+}
+
+void fb200_init_connectivity(int* edges, int* edge_tri, int* elem2D_nodes, int* nod_in_elem2D_num, int* nod_in_elem2D,
+                             int* nod_in_elem2D_ld, int* edge_up_dn_tri) {
+    TracerCtx& c = tctx();
+    c.h_edges.assign(edges, edges + 2 * (size_t)c.myEd);
+    c.h_edge_tri.assign(edge_tri, edge_tri + 2 * (size_t)c.myEd);
+    c.h_elem_nodes.assign(elem2D_nodes, elem2D_nodes + 3 * (size_t)c.Eall);
+    c.h_nie_num.assign(nod_in_elem2D_num, nod_in_elem2D_num + c.N);
+    c.nie_ld = *nod_in_elem2D_ld;
+    c.h_nie.assign(nod_in_elem2D, nod_in_elem2D + (size_t)c.nie_ld * c.N);
+    c.h_updn.assign(edge_up_dn_tri, edge_up_dn_tri + 2 * (size_t)c.myEd);
+}
+
+void fb200_init_levels(int* nlevels, int* ulevels, int* nlevels_nod2D, int* ulevels_nod2D, int* nlevels_nod2D_min,
+                       int* ulevels_nod2D_max, int* nboundary_lay) {
+    TracerCtx& c = tctx();
+    c.h_nlev.assign(nlevels, nlevels + c.Eall); c.h_ulev.assign(ulevels, ulevels + c.Eall);
+    c.h_nlev_n.assign(nlevels_nod2D, nlevels_nod2D + c.N); c.h_ulev_n.assign(ulevels_nod2D, ulevels_nod2D + c.N);
+    c.h_nlmin.assign(nlevels_nod2D_min, nlevels_nod2D_min + c.N); c.h_ulmax.assign(ulevels_nod2D_max, ulevels_nod2D_max + c.N);
+    c.h_nbl.assign(nboundary_lay, nboundary_lay + c.N);
+    for (int n = 0; n < c.myN; n++)
+        if (c.h_nlev_n[n] - c.h_ulev_n[n] < 3) { fb_set_error(31, "columns with fewer than 3 layers are not supported (QR4C boundary statements would overlap)"); break; }
+}
+
+void fb200_init_geometry(double* edge_cross_dxdy, double* edge_dxdy, double* elem_cos, double* elem_area, double* gradient_sca,
+                         double* area, double* areasvol, double* zbar_n_bot) {
+    TracerCtx& c = tctx();
+    c.h_ecd.assign(edge_cross_dxdy, edge_cross_dxdy + 4 * (size_t)c.myEd);
+    c.h_edxdy.assign(edge_dxdy, edge_dxdy + 2 * (size_t)c.myEd);
+    c.h_ecos.assign(elem_cos, elem_cos + c.Eall); c.h_earea.assign(elem_area, elem_area + c.Eall);
+    c.h_gsca.assign(gradient_sca, gradient_sca + 6 * (size_t)c.myE);
+    c.h_area.assign(area, area + (size_t)c.nl * c.N); c.h_areasvol.assign(areasvol, areasvol + (size_t)c.nl * c.N);
+    c.h_znb.assign(zbar_n_bot, zbar_n_bot + c.N);
+}
+
+void fb200_set_options(int* tra_adv_hor, int* tra_adv_ver, int* tra_adv_lim, double* tra_adv_ph, double* tra_adv_pv, int* w_split,
+                       int* i_vert_diff, int* Redi, int* use_sw_pene, int* do_hor_diff, int* clamp_salt, double* is_nonlinfs,
+                       double* dt, double* epsilon, int* tracer_id) {
+    TracerCtx& c = tctx();
+    Options& o = c.opt;
+    o.tra_adv_hor = *tra_adv_hor; o.tra_adv_ver = *tra_adv_ver; o.tra_adv_lim = *tra_adv_lim; o.ph = *tra_adv_ph; o.pv = *tra_adv_pv;
+    o.w_split = *w_split; o.i_vert_diff = *i_vert_diff; o.Redi = *Redi; o.use_sw_pene = *use_sw_pene; o.do_hor_diff = *do_hor_diff;
+    o.clamp_salt = *clamp_salt; o.is_nonlinfs = *is_nonlinfs; o.dt = *dt; o.epsilon = *epsilon;
+    for (int k = 0; k < c.ntr && k < 8; k++) o.tracer_id[k] = tracer_id[k];
+    if (o.tra_adv_hor < 0 || o.tra_adv_hor > 2 || o.tra_adv_ver < 0 || o.tra_adv_ver > 3) fb_set_error(32, "unknown advection scheme");
+}
+
+void fb200_init_commit(void) { ctx_commit(tctx()); }
+
+void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode, double* hnode_new, double* helem,
+                           double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki, double* slope_tapered, double* heat_flux,
+                           double* water_flux, double* virtual_salt, double* relax_salt, double* real_salt_flux, double* sw_3d) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(33, "fb200_push_step_state before fb200_init_commit"); return; }
+    const int L = c.nl - 1, nl = c.nl, N = c.N;
+    ctx_push_node_field(c, UV, L, c.E, c.U.p, 2, 0);
+    ctx_push_node_field(c, UV, L, c.E, c.V.p, 2, 1);
+    ctx_push_node_field(c, helem, L, c.myE, c.helem.p);
+    ctx_push_node_field(c, Wvel, nl, N, c.W.p);
+    ctx_push_node_field(c, Wvel_e, nl, N, c.We.p);
+    if (c.opt.w_split) ctx_push_node_field(c, Wvel_i, nl, N, c.Wi.p);
+    ctx_push_node_field(c, hnode, L, N, c.hnode.p);
+    ctx_push_node_field(c, hnode_new, L, N, c.hnode_new.p);
+    ctx_push_node_field(c, Z_3d_n, L, N, c.Z3.p);
+    ctx_push_node_field(c, zbar_3d_n, nl, N, c.zbar3.p);
+    ctx_push_node_field(c, Kv, nl, N, c.Kv.p);
+    ctx_push_node_field(c, Ki, L, N, c.Ki.p);
+    if (c.opt.Redi) {
+        ctx_push_node_field(c, slope_tapered, L, N, c.sl1.p, 3, 0);
+        ctx_push_node_field(c, slope_tapered, L, N, c.sl2.p, 3, 1);
+        ctx_push_node_field(c, slope_tapered, L, N, c.sl3.p, 3, 2);
+    }
+    if (c.opt.use_sw_pene) ctx_push_node_field(c, sw_3d, nl, N, c.sw3d.p);
+    const size_t nb = (size_t)N * sizeof(double);
+    CUDA_CHECK(cudaMemcpyAsync(c.heat_flux.p, heat_flux, nb, cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaMemcpyAsync(c.water_flux.p, water_flux, nb, cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaMemcpyAsync(c.virtual_salt.p, virtual_salt, nb, cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaMemcpyAsync(c.relax_salt.p, relax_salt, nb, cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaMemcpyAsync(c.real_salt_flux.p, real_salt_flux, nb, cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+}
+
+void fb200_push_tracers(double* tr_arr, double* tr_arr_old) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(34, "fb200_push_tracers before fb200_init_commit"); return; }
+    const int L = c.nl - 1;
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
+    for (int tr = 0; tr < c.ntr; tr++) {
+        ctx_push_node_field(c, tr_arr + rf * tr, L, c.N, c.T.p + nf * tr);
+        ctx_push_node_field(c, tr_arr_old + rf * tr, L, c.N, c.Told.p + nf * tr);
+    }
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+}
+
+void fb200_solve_tracers(void) { tracer_step_all(tctx()); }
+
+void fb200_pull_tracers(double* tr_arr, double* tr_arr_old) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(35, "fb200_pull_tracers before fb200_init_commit"); return; }
+    const int L = c.nl - 1;
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
+    for (int tr = 0; tr < c.ntr; tr++) {
+        ctx_pull_node_field(c, c.T.p + nf * tr, L, c.N, tr_arr + rf * tr);
+        ctx_pull_node_field(c, c.Told.p + nf * tr, L, c.N, tr_arr_old + rf * tr);
+    }
+}
+
+void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
+    fb200_push_tracers(tr_arr, tr_arr_old);
+    fb200_solve_tracers();
+    fb200_pull_tracers(tr_arr, tr_arr_old);
+}
+
+void fb200_debug_fetch(const char* name, double* out) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(36, "fb200_debug_fetch before fb200_init_commit"); return; }
+    int kind = 0;
+    std::string s(name);
+    const double* f = nullptr;
+    int lev = c.nl - 1, cnt = c.N;
+    if (s == "ttfAB") { f = c.Told.p; }
+    else f = tracer_debug_field(c, name, &kind);
+    if (!f) { fb_set_error(37, "fb200_debug_fetch: unknown field " + s); return; }
+    if (s == "adf_v") lev = c.nl;
+    if (kind == 1) cnt = c.myEd;
+    if (kind == 2) cnt = c.Eall;
+    ctx_pull_node_field(c, f, lev, cnt, out);
+}
+
+void fb200_finalize(void) { ctx_release(tctx()); }
+
+}  // extern "C"

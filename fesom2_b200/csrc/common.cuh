@@ -1,0 +1,102 @@
+// Shared declarations of libfesom_b200.so: device data layout, context, error plumbing.
+//
+// DATA LAYOUT IN HBM ("level-blocked"): every (level, entity) field — entity = node, element or edge — is
+// stored in tiles of TILE = 32 consecutive entities; inside a tile the level index is the slow one and the
+// entity the fast one:   offset(ent, k) = (ent / 32) * (NLP * 32) + k * 32 + (ent % 32),  k = level-1, NLP = nl.
+// A warp that owns 32 consecutive entities therefore reads one fully coalesced 256-byte line per level and
+// walks through ONE contiguous NLP*256-byte region per field, and the reference's (level, entity) column-major
+// block of the same 32 entities is contiguous too, so restaging is a tile-local transpose.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#define TILE 32
+
+struct __align__(16) EdgeRec {      // one record per local edge, read by both endpoint nodes (64 B)
+    int bn1, bn2;                   // tile bases of the two nodes          (see tile_base)
+    int be1, be2;                   // tile bases of the two elements, be2 = -1 on a boundary edge
+    unsigned lev;                   // nu1 | nl1<<8 | nu2<<16 | nl2<<24   (nl* = nlevels-1; nu2 = nl2 = 0 without el2)
+    int pad;
+    double dX1, dY1, dX2, dY2;      // edge_cross_dxdy(1:4)
+    double pad2;
+};
+struct __align__(16) EdgeHo {       // extra per-edge data of the high-order reconstruction (48 B)
+    double dxa, dyr;                // edge_dxdy(1)*a, edge_dxdy(2)*r_earth  (a = r_earth * mean elem_cos)
+    int bup, bdn;                   // tile bases of the up/downwind triangles, -1 if absent
+    unsigned shared;                // nzmin_s | nzmax_s<<8 : levels nzmin_s..nzmax_s-1 use the up/downwind triangles
+    int n1, n2;                     // node ids (for the node-mean gradient fallback)
+    int pad;
+    double pad2;
+};
+
+__host__ __device__ inline int tile_base(int ent, int nlp) { return (ent >> 5) * (nlp * TILE) + (ent & 31); }
+
+struct Options {
+    int tra_adv_hor = 1, tra_adv_ver = 0, tra_adv_lim = 0;
+    double ph = 1.0, pv = 1.0;
+    int w_split = 0, i_vert_diff = 1, Redi = 0, use_sw_pene = 0, do_hor_diff = 1, clamp_salt = 1;
+    double is_nonlinfs = 1.0, dt = 0.0, epsilon = 0.1;
+    int tracer_id[8] = {0, 1, 301, 301, 301, 301, 301, 301};
+};
+
+// error plumbing -------------------------------------------------------------------------------------
+void fb_set_error(int code, const std::string& msg);
+bool fb_ok();
+extern long long g_launches;
+#define CUDA_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fb_set_error(100 + (int)e_, std::string(#x) + ": " + cudaGetErrorString(e_)); } } while (0)
+#define LAUNCH_CHECK() do { g_launches++; cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) fb_set_error(100 + (int)e_, std::string("kernel launch: ") + cudaGetErrorString(e_)); } while (0)
+
+template <class T> struct DevBuf {
+    T* p = nullptr; size_t n = 0;
+    void alloc(size_t count) { release(); n = count; if (count) { CUDA_CHECK(cudaMalloc(&p, count * sizeof(T))); if (p) CUDA_CHECK(cudaMemset(p, 0, count * sizeof(T))); } }
+    void upload(const std::vector<T>& h) { alloc(h.size()); if (p && n) CUDA_CHECK(cudaMemcpy(p, h.data(), n * sizeof(T), cudaMemcpyHostToDevice)); }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+struct TracerCtx {
+    // dimensions
+    int nl = 0, nlp = 0, myN = 0, N = 0, myE = 0, E = 0, Eall = 0, myEd = 0, ntr = 0;
+    int Ntiles = 0, myNtiles = 0, Etiles = 0, Edtiles = 0, maxdeg = 0, maxnie = 0;
+    Options opt;
+    bool committed = false;
+    // host staging of the init_* calls
+    std::vector<int> h_edges, h_edge_tri, h_elem_nodes, h_nie_num, h_nie, h_updn, h_nlev, h_ulev, h_nlev_n, h_ulev_n, h_nlmin, h_ulmax, h_nbl;
+    std::vector<double> h_ecd, h_edxdy, h_ecos, h_earea, h_gsca, h_area, h_areasvol, h_znb;
+    int nie_ld = 0;
+    // static device data
+    DevBuf<EdgeRec> edge; DevBuf<EdgeHo> edgeho;
+    DevBuf<int> ne_slot;            // [Ntile][maxdeg][32]   (edge<<1)|second, -1 = none; ascending reference edge id
+    DevBuf<int> nie_slot;           // [Ntile][maxnie][32]   element id in nod_in_elem2D order, -1 = none
+    DevBuf<int> el_nb;              // [3][Eall] node tile bases of element corners
+    DevBuf<unsigned> el_lev;        // nu | nl<<8 per element (nl = nlevels-1)
+    DevBuf<double> el_g;            // [6][myE] gradient_sca
+    DevBuf<double> el_area;         // [Eall]
+    DevBuf<unsigned> n_lev;         // nu | nlev<<8 | nlmin<<16 | ulmax<<24 per node (nlev = nlevels_nod2D)
+    DevBuf<int> n_nbl;              // nboundary_lay
+    DevBuf<double> n_znb;           // zbar_n_bot
+    DevBuf<double> area, areasvol;  // tiled (nlp levels)
+    // per-step state, tiled
+    DevBuf<double> U, V, helem, W, We, Wi, hnode, hnode_new, Z3, zbar3, Kv, Ki, sl1, sl2, sl3, sw3d;
+    DevBuf<double> heat_flux, water_flux, virtual_salt, relax_salt, real_salt_flux;   // (N)
+    // tracers, tiled: [ntr] fields each
+    DevBuf<double> T, Told;
+    // work fields, tiled
+    DevBuf<double> txy_x, txy_y, trz, LO, adf_h, adf_v, fplus, fminus, tstar;
+    // staging for host<->device transfers (reference layout)
+    DevBuf<double> stage;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+};
+
+// context.cu
+TracerCtx& tctx();
+void ctx_commit(TracerCtx& c);
+void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int count_ent, double* dev_tiled, int ncomp = 1, int comp = 0);
+void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host);
+void ctx_release(TracerCtx& c);
+// tracer_kernels.cu
+void tracer_step_all(TracerCtx& c);

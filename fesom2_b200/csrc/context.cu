@@ -1,0 +1,205 @@
+// Context of the tracer path: error status, building the device-side mesh tables from the Fortran arrays
+// (fb200_init_* -> fb200_init_commit), and restaging between the reference layout and the tiled layout.
+#include "common.cuh"
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+long long g_launches = 0;
+static int g_status = 0;
+static std::string g_status_msg;
+static std::mutex g_mu;
+
+void fb_set_error(int code, const std::string& msg) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    fprintf(stderr, "fesom_b200: ERROR %d: %s\n", code, msg.c_str());
+    if (g_status == 0) { g_status = code; g_status_msg = msg; }
+    const char* ab = getenv("FB200_ABORT_ON_ERROR");
+    if (ab && ab[0] == '1') abort();
+}
+bool fb_ok() { return g_status == 0; }
+int fb_status_code() { return g_status; }
+const char* fb_status_msg() { return g_status_msg.c_str(); }
+void fb_clear_status() { std::lock_guard<std::mutex> lk(g_mu); g_status = 0; g_status_msg.clear(); }
+
+TracerCtx& tctx() { static TracerCtx c; return c; }
+
+// ---------------------------------------------------------------------------------------------------
+// restage kernels.  One block per tile of 32 entities.  src is the reference array (ncomp, lev_ref, ent).
+__global__ void __launch_bounds__(256) k_ref_to_tiled(const double* __restrict__ src, double* __restrict__ dst, int count_ent,
+                                                      int lev_ref, int nlp, int ncomp, int comp) {
+    extern __shared__ double sm[];                 // [nlp][33]
+    const int tile = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int j = warp; j < TILE; j += 8) {
+        const int ent = tile * TILE + j;
+        for (int k = lane; k < nlp; k += 32) {
+            double v = 0.0;
+            if (ent < count_ent && k < lev_ref) v = src[((size_t)ent * lev_ref + k) * ncomp + comp];
+            sm[k * 33 + j] = v;
+        }
+    }
+    __syncthreads();
+    double* out = dst + (size_t)tile * nlp * TILE;
+    for (int idx = threadIdx.x; idx < nlp * TILE; idx += 256) out[idx] = sm[(idx >> 5) * 33 + (idx & 31)];
+}
+__global__ void __launch_bounds__(256) k_tiled_to_ref(const double* __restrict__ src, double* __restrict__ dst, int count_ent,
+                                                      int lev_ref, int nlp) {
+    extern __shared__ double sm[];
+    const int tile = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const double* in = src + (size_t)tile * nlp * TILE;
+    for (int idx = threadIdx.x; idx < nlp * TILE; idx += 256) sm[(idx >> 5) * 33 + (idx & 31)] = in[idx];
+    __syncthreads();
+    for (int j = warp; j < TILE; j += 8) {
+        const int ent = tile * TILE + j;
+        if (ent >= count_ent) continue;
+        for (int k = lane; k < lev_ref; k += 32) dst[(size_t)ent * lev_ref + k] = sm[k * 33 + j];
+    }
+}
+
+static void ensure_stage(TracerCtx& c, size_t count) { if (c.stage.n < count) c.stage.alloc(count); }
+
+// host (reference layout, (ncomp, lev_ref, count_ent)) -> device tiled field of component `comp`
+void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int count_ent, double* dev_tiled, int ncomp, int comp) {
+    if (!fb_ok() || count_ent == 0) return;
+    const size_t cnt = (size_t)ncomp * lev_ref * count_ent;
+    if (comp == 0) {                                   // components of one array are pushed back to back: upload once
+        ensure_stage(c, cnt);
+        CUDA_CHECK(cudaMemcpyAsync(c.stage.p, host, cnt * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    }
+    const int tiles = (count_ent + TILE - 1) / TILE;
+    k_ref_to_tiled<<<tiles, 256, (size_t)c.nlp * 33 * sizeof(double), c.stream>>>(c.stage.p, dev_tiled, count_ent, lev_ref, c.nlp, ncomp, comp);
+    LAUNCH_CHECK();
+}
+void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host) {
+    if (!fb_ok() || count_ent == 0) return;
+    const size_t cnt = (size_t)lev_ref * count_ent;
+    ensure_stage(c, cnt);
+    const int tiles = (count_ent + TILE - 1) / TILE;
+    k_tiled_to_ref<<<tiles, 256, (size_t)c.nlp * 33 * sizeof(double), c.stream>>>(dev_tiled, c.stage.p, count_ent, lev_ref, c.nlp);
+    LAUNCH_CHECK();
+    CUDA_CHECK(cudaMemcpyAsync(host, c.stage.p, cnt * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+}
+
+// ---------------------------------------------------------------------------------------------------
+// fb200_init_commit: turn the Fortran mesh arrays into device tables.
+static inline unsigned pack4(int a, int b, int c, int d) { return (unsigned)a | ((unsigned)b << 8) | ((unsigned)c << 16) | ((unsigned)d << 24); }
+
+void ctx_commit(TracerCtx& c) {
+    if (!fb_ok()) return;
+    if (c.nl <= 2 || c.nl > 255) { fb_set_error(10, "nl must be in 3..255"); return; }
+    if (c.h_edges.empty() || c.h_nlev.empty() || c.h_ecd.empty()) { fb_set_error(11, "fb200_init_commit before connectivity/levels/geometry"); return; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fb_set_error(12, "no CUDA device: libfesom_b200 has no CPU fallback"); return; }
+    if (!c.stream) { CUDA_CHECK(cudaStreamCreate(&c.stream)); CUDA_CHECK(cudaEventCreate(&c.ev0)); CUDA_CHECK(cudaEventCreate(&c.ev1)); }
+    c.nlp = c.nl;
+    const int nlp = c.nlp, N = c.N, myN = c.myN, Eall = c.Eall, myE = c.myE, myEd = c.myEd;
+    c.Ntiles = (N + TILE - 1) / TILE; c.myNtiles = (myN + TILE - 1) / TILE;
+    c.Etiles = (Eall + TILE - 1) / TILE; c.Edtiles = (myEd + TILE - 1) / TILE;
+    if ((long long)std::max(std::max(c.Ntiles, c.Etiles), c.Edtiles) * nlp * TILE >= (1LL << 31)) { fb_set_error(13, "mesh too large for 32-bit tile offsets"); return; }
+    const double r_earth = 6367500.0;
+    // elements
+    std::vector<int> el_nb((size_t)3 * Eall, 0); std::vector<unsigned> el_lev(Eall);
+    for (int e = 0; e < Eall; e++) {
+        for (int k = 0; k < 3; k++) { int n = c.h_elem_nodes[(size_t)e * 3 + k]; el_nb[(size_t)k * Eall + e] = n >= 1 ? tile_base(n - 1, nlp) : -1; }
+        el_lev[e] = pack4(c.h_ulev[e], c.h_nlev[e] - 1, 0, 0);
+    }
+    c.el_nb.upload(el_nb); c.el_lev.upload(el_lev);
+    std::vector<double> g((size_t)6 * myE);
+    for (int e = 0; e < myE; e++) for (int k = 0; k < 6; k++) g[(size_t)k * myE + e] = c.h_gsca[(size_t)e * 6 + k];
+    c.el_g.upload(g); c.el_area.upload(c.h_earea);
+    // nodes
+    std::vector<unsigned> n_lev(N);
+    for (int n = 0; n < N; n++) n_lev[n] = pack4(c.h_ulev_n[n], c.h_nlev_n[n], c.h_nlmin[n], c.h_ulmax[n]);
+    c.n_lev.upload(n_lev); c.n_nbl.upload(c.h_nbl); c.n_znb.upload(c.h_znb);
+    // edges
+    std::vector<EdgeRec> er(myEd); std::vector<EdgeHo> eh(myEd);
+    std::vector<int> deg(N, 0);
+    for (int e = 0; e < myEd; e++) {
+        const int n1 = c.h_edges[2 * (size_t)e], n2 = c.h_edges[2 * (size_t)e + 1];
+        const int t1 = c.h_edge_tri[2 * (size_t)e], t2 = c.h_edge_tri[2 * (size_t)e + 1];
+        if (n1 < 1 || n2 < 1 || n1 > N || n2 > N || t1 < 1 || t1 > Eall || t2 > Eall) { fb_set_error(14, "edge table out of range"); return; }
+        EdgeRec& r = er[e]; memset(&r, 0, sizeof(r));
+        r.bn1 = tile_base(n1 - 1, nlp); r.bn2 = tile_base(n2 - 1, nlp);
+        r.be1 = tile_base(t1 - 1, nlp); r.be2 = t2 > 0 ? tile_base(t2 - 1, nlp) : -1;
+        const int nu1 = c.h_ulev[t1 - 1], nl1 = c.h_nlev[t1 - 1] - 1;
+        const int nu2 = t2 > 0 ? c.h_ulev[t2 - 1] : 0, nl2 = t2 > 0 ? c.h_nlev[t2 - 1] - 1 : 0;
+        r.lev = pack4(nu1, nl1, nu2, nl2);
+        r.dX1 = c.h_ecd[4 * (size_t)e]; r.dY1 = c.h_ecd[4 * (size_t)e + 1]; r.dX2 = c.h_ecd[4 * (size_t)e + 2]; r.dY2 = c.h_ecd[4 * (size_t)e + 3];
+        // the five level ranges of oce_adv_tra_hor.F90:129-209 must not overlap (they never do on a valid mesh);
+        // the kernels evaluate them as a partition
+        {
+            const int nl12 = std::min(nl1, nl2), nu12 = std::max(nu1, nu2);
+            for (int nz = 1; nz <= nlp; nz++) {
+                int m = 0;
+                m += (nz >= nu1 && nz <= nu12 - 1);
+                m += (nu2 > 0 && nz >= nu2 && nz <= nu12 - 1);
+                m += (nz >= nu12 && nz <= nl12);
+                m += (nz >= nl12 + 1 && nz <= nl1);
+                m += (nz >= nl12 + 1 && nz <= nl2);
+                if (m > 1) { fb_set_error(15, "edge with overlapping level ranges (disjoint element columns) is not supported"); return; }
+            }
+        }
+        EdgeHo& h = eh[e]; memset(&h, 0, sizeof(h));
+        double a = r_earth * c.h_ecos[t1 - 1];                       // oce_adv_tra_hor.F90:535,548
+        if (t2 > 0) a = 0.5 * (a + r_earth * c.h_ecos[t2 - 1]);
+        h.dxa = c.h_edxdy[2 * (size_t)e] * a; h.dyr = c.h_edxdy[2 * (size_t)e + 1] * r_earth;
+        const int up = c.h_updn[2 * (size_t)e], dn = c.h_updn[2 * (size_t)e + 1];
+        h.bup = up > 0 ? tile_base(up - 1, nlp) : -1; h.bdn = dn > 0 ? tile_base(dn - 1, nlp) : -1;
+        if (up > 0 && dn > 0) {                                      // oce_muscl_adv.F90:306-308
+            int nzmin = std::max(c.h_ulmax[n1 - 1], c.h_ulmax[n2 - 1]), nzmax = std::min(c.h_nlmin[n1 - 1], c.h_nlmin[n2 - 1]);
+            h.shared = pack4(nzmin, nzmax, 1, 0);
+        } else h.shared = 0;
+        h.n1 = n1 - 1; h.n2 = n2 - 1;
+        deg[n1 - 1]++; deg[n2 - 1]++;
+    }
+    c.edge.upload(er); c.edgeho.upload(eh);
+    c.maxdeg = 0; for (int n = 0; n < N; n++) c.maxdeg = std::max(c.maxdeg, deg[n]);
+    {
+        std::vector<int> slot((size_t)c.Ntiles * c.maxdeg * TILE, -1), fill(N, 0);
+        for (int e = 0; e < myEd; e++)            // ascending edge id == the reference's scatter order
+            for (int s = 0; s < 2; s++) {
+                int n = c.h_edges[2 * (size_t)e + s] - 1;
+                slot[((size_t)(n >> 5) * c.maxdeg + fill[n]) * TILE + (n & 31)] = (e << 1) | s;
+                fill[n]++;
+            }
+        c.ne_slot.upload(slot);
+    }
+    c.maxnie = 0; for (int n = 0; n < N; n++) c.maxnie = std::max(c.maxnie, c.h_nie_num[n]);
+    {
+        std::vector<int> slot((size_t)c.Ntiles * c.maxnie * TILE, -1);
+        for (int n = 0; n < N; n++)
+            for (int k = 0; k < c.h_nie_num[n]; k++) {
+                int e = c.h_nie[(size_t)n * c.nie_ld + k];
+                slot[((size_t)(n >> 5) * c.maxnie + k) * TILE + (n & 31)] = e >= 1 ? e - 1 : -1;
+            }
+        c.nie_slot.upload(slot);
+    }
+    // fields
+    const size_t nf = (size_t)c.Ntiles * nlp * TILE, ef = (size_t)c.Etiles * nlp * TILE, df = (size_t)c.Edtiles * nlp * TILE;
+    for (DevBuf<double>* b : {&c.area, &c.areasvol, &c.W, &c.We, &c.Wi, &c.hnode, &c.hnode_new, &c.Z3, &c.zbar3, &c.Kv, &c.Ki,
+                              &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.fplus, &c.fminus, &c.tstar}) b->alloc(nf);
+    for (DevBuf<double>* b : {&c.U, &c.V, &c.helem, &c.txy_x, &c.txy_y}) b->alloc(ef);
+    c.adf_h.alloc(df);
+    c.T.alloc(nf * c.ntr); c.Told.alloc(nf * c.ntr);
+    for (DevBuf<double>* b : {&c.heat_flux, &c.water_flux, &c.virtual_salt, &c.relax_salt, &c.real_salt_flux}) b->alloc(N);
+    ctx_push_node_field(c, c.h_area.data(), c.nl, N, c.area.p);
+    ctx_push_node_field(c, c.h_areasvol.data(), c.nl, N, c.areasvol.p);
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+    if (fb_ok()) c.committed = true;
+}
+
+void ctx_release(TracerCtx& c) {
+    if (c.stream) { cudaStreamSynchronize(c.stream); }
+    for (DevBuf<double>* b : {&c.area, &c.areasvol, &c.W, &c.We, &c.Wi, &c.hnode, &c.hnode_new, &c.Z3, &c.zbar3, &c.Kv, &c.Ki,
+                              &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.fplus, &c.fminus, &c.tstar, &c.U, &c.V,
+                              &c.helem, &c.txy_x, &c.txy_y, &c.adf_h, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
+                              &c.relax_salt, &c.real_salt_flux, &c.stage, &c.el_g, &c.el_area, &c.n_znb}) b->release();
+    c.edge.release(); c.edgeho.release(); c.ne_slot.release(); c.nie_slot.release(); c.el_nb.release(); c.el_lev.release();
+    c.n_lev.release(); c.n_nbl.release();
+    if (c.ev0) cudaEventDestroy(c.ev0);
+    if (c.ev1) cudaEventDestroy(c.ev1);
+    if (c.stream) cudaStreamDestroy(c.stream);
+    c = TracerCtx();
+}

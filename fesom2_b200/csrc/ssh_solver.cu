@@ -1,0 +1,357 @@
+// SSH elliptic solve: drop-in psolver_init / psolve / psolver_final (src/psolve.c) on the device.
+//
+//   psolve.c:58-65,186-193   row scaling  A <- D^-1 A, y <- D^-1 b,  D_i = sum_j |a_ij|      -> k_scale_rows
+//   bicgstab_ras.c:49-259    right-preconditioned BiCGStab, absolute stop ||r||^2 < tol^2     -> k_* below
+//   parms_pc_ras.c / ILU(k)  replaced by block-Jacobi: dense inverses of bs x bs diagonal blocks, built
+//                            once from the initial matrix and kept when values change (psolve.c:200: the
+//                            reference also keeps its factor unless new==2)
+// Matrix storage: sliced ELL, slice = 32 rows (same tiling as the tracer fields): val[slice][k][32].
+// Dot products: per-block partials reduced by the last finishing block in a fixed order (deterministic,
+// no floating-point atomics); scalars (alpha, sigma, beta, rho, omega) never leave the device; the host
+// polls a "done" flag every few iterations.
+#include "common.cuh"
+#include "fesom_b200.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+
+#define SBS 256                 // threads per block in the solver kernels (8 slices)
+
+struct SolverScal {             // device-resident scalars
+    double alpha, sigma, beta, rho, rho_alt, omega, tol2;
+    double tmp0, tmp1;
+    int done, its, maxits, pad;
+};
+
+struct Solver {
+    int n = 0, nnz = 0, nslice = 0, bs = 1, nblk = 0, reuse = 0, maxits = 2000;
+    double soltol = 1e-10;
+    std::vector<int> rp, ci;                 // host copies (psolve.c:83-99)
+    DevBuf<int> d_rp, d_ci, d_sptr, d_scol;  // CSR + SELL structure
+    DevBuf<double> d_vals, d_sval, d_scale, d_binv;
+    DevBuf<double> x, y, r, p, pt, st, v, t, rhs;
+    DevBuf<double> partial;                  // [2][nblocks]
+    DevBuf<SolverScal> scal;
+    DevBuf<unsigned> counter;
+    int nblocks = 0;
+    int last_its = 0; double last_res = 0.0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+static std::map<int, Solver*> g_solvers;
+static int g_block = 1;
+static float g_ssh_ms = 0.f;
+double ssh_last_ms() { return (double)g_ssh_ms; }
+
+// ---------------------------------------------------------------------------------------------------
+// row scaling + CSR -> SELL fill (psolve.c:186-193)
+__global__ void __launch_bounds__(SBS) k_scale_rows(int n, const int* __restrict__ rp, const double* __restrict__ vals,
+                                                    const int* __restrict__ sptr, double* __restrict__ sval, double* __restrict__ scale) {
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    if (i >= n) return;
+    const int j0 = rp[i], j1 = rp[i + 1];
+    double tmp = 0.;
+    for (int j = j0; j < j1; j++) tmp += fabs(vals[j]);
+    const double s = 1. / tmp;
+    scale[i] = s;
+    const int base = sptr[i >> 5] + (i & 31);
+    const int w = (sptr[(i >> 5) + 1] - sptr[i >> 5]) >> 5;
+    for (int k = 0; k < w; k++) sval[base + (k << 5)] = (k < j1 - j0) ? vals[j0 + k] * s : 0.0;
+}
+
+__device__ __forceinline__ double sell_row(const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                           const double* __restrict__ x, int i) {
+    const int s0 = sptr[i >> 5];
+    const int w = (sptr[(i >> 5) + 1] - s0) >> 5;
+    const int base = s0 + (i & 31);
+    double s = 0.0;
+    for (int k = 0; k < w; k++) s += sval[base + (k << 5)] * x[scol[base + (k << 5)]];
+    return s;
+}
+
+// deterministic two-value reduction: block partials -> last block sums them in order and calls `fin`
+template <class Fin>
+__device__ __forceinline__ void reduce2(double a, double b, double* __restrict__ partial, unsigned* __restrict__ counter, int nblocks, Fin fin) {
+    __shared__ double sa[SBS / 32], sb[SBS / 32];
+    __shared__ bool last;
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_down_sync(0xffffffffu, a, o); b += __shfl_down_sync(0xffffffffu, b, o); }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sa[warp] = a; sb[warp] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double ta = 0.0, tb = 0.0;
+        for (int w = 0; w < SBS / 32; w++) { ta += sa[w]; tb += sb[w]; }
+        partial[blockIdx.x] = ta; partial[nblocks + blockIdx.x] = tb;
+        __threadfence();
+        const unsigned done = atomicAdd(counter, 1u);
+        last = (done == (unsigned)nblocks - 1);
+    }
+    __syncthreads();
+    if (last && threadIdx.x < 32) {
+        __threadfence();
+        double ta = 0.0, tb = 0.0;
+        for (int k = threadIdx.x; k < nblocks; k += 32) { ta += ((volatile double*)partial)[k]; tb += ((volatile double*)partial)[nblocks + k]; }
+        for (int o = 16; o > 0; o >>= 1) { ta += __shfl_down_sync(0xffffffffu, ta, o); tb += __shfl_down_sync(0xffffffffu, tb, o); }
+        if (threadIdx.x == 0) { *counter = 0; fin(ta, tb); }
+    }
+}
+
+// block-Jacobi apply for one row: z_i = sum_c Binv[blk][c][i_loc] * in[b0 + c]   (bs == 1: z = dinv * in)
+__device__ __forceinline__ double bj_row(const double* __restrict__ binv, const double* in, int i, int n, int bs) {
+    if (bs == 1) return binv[i] * in[i];
+    const int blk = i / bs, il = i - blk * bs, b0 = blk * bs;
+    const double* B = binv + (size_t)blk * bs * bs;
+    double s = 0.0;
+    for (int c = 0; c < bs; c++) { const int j = b0 + c; if (j < n) s += B[c * bs + il] * in[j]; }
+    return s;
+}
+
+// setup of one solve: y = rhs*scale (psolve.c:208-209); r = y - A x; omega, rho; p = r  (bicgstab_ras.c:116-143)
+__global__ void __launch_bounds__(SBS) k_init_res(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                                  const double* __restrict__ rhs, const double* __restrict__ scale, const double* __restrict__ x,
+                                                  double* __restrict__ y, double* __restrict__ r, double* __restrict__ p,
+                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc) {
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    double a = 0.0, b = 0.0;
+    if (i < n) {
+        const double yi = rhs[i] * scale[i];
+        const double ri = yi - sell_row(sptr, scol, sval, x, i);
+        y[i] = yi; r[i] = ri; p[i] = ri;
+        a = ri * ri; b = yi * ri;
+    }
+    reduce2(a, b, partial, counter, nblocks, [=](double ta, double tb) {
+        sc->omega = ta; sc->rho = tb; sc->alpha = 0.; sc->sigma = 1.0; sc->rho_alt = 1.0; sc->its = 0;
+        sc->done = (ta > sc->tol2) ? 0 : 1;
+    });
+}
+__global__ void __launch_bounds__(SBS) k_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ in, double* __restrict__ out,
+                                            const SolverScal* sc) {
+    if (sc->done) return;
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    if (i < n) out[i] = bj_row(binv, in, i, n, bs);
+}
+// v = A pt ; alpha = rho / (r0 . v)                                        bicgstab_ras.c:161-164
+__global__ void __launch_bounds__(SBS) k_spmv_alpha(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                                    const double* __restrict__ pt, const double* __restrict__ r0, double* __restrict__ v,
+                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc) {
+    if (sc->done) return;
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    double a = 0.0;
+    if (i < n) { const double vi = sell_row(sptr, scol, sval, pt, i); v[i] = vi; a = r0[i] * vi; }
+    reduce2(a, 0.0, partial, counter, nblocks, [=](double ta, double) { sc->alpha = sc->rho / ta; });
+}
+// r -= alpha v ; st = M r                                                   bicgstab_ras.c:166-175
+__global__ void __launch_bounds__(SBS) k_r_update_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ v,
+                                                     double* __restrict__ r, double* __restrict__ st, const SolverScal* sc) {
+    if (sc->done) return;
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    const double alpha = sc->alpha;
+    if (i < n) r[i] -= alpha * v[i];
+    if (bs == 1) { if (i < n) st[i] = binv[i] * r[i]; return; }
+    __syncthreads();                                     // SBS is a multiple of every supported block size
+    if (i < n) st[i] = bj_row(binv, r, i, n, bs);
+}
+// t = A st ; sigma = (t.r)/(t.t)                                            bicgstab_ras.c:179-197
+__global__ void __launch_bounds__(SBS) k_spmv_sigma(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                                    const double* __restrict__ st, const double* __restrict__ r, double* __restrict__ t,
+                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc) {
+    if (sc->done) return;
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    double a = 0.0, b = 0.0;
+    if (i < n) { const double ti = sell_row(sptr, scol, sval, st, i); t[i] = ti; a = ti * r[i]; b = ti * ti; }
+    reduce2(a, b, partial, counter, nblocks, [=](double ta, double tb) { sc->sigma = ta / tb; });
+}
+// r -= sigma t ; x += alpha pt + sigma st ; omega = r.r ; rho = r0.r ; convergence test ; beta     :200-225
+__global__ void __launch_bounds__(SBS) k_x_update(int n, const double* __restrict__ t, const double* __restrict__ pt, const double* __restrict__ st,
+                                                  const double* __restrict__ r0, double* __restrict__ r, double* __restrict__ x,
+                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc) {
+    if (sc->done) return;
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    const double alpha = sc->alpha, sigma = sc->sigma;
+    double a = 0.0, b = 0.0;
+    if (i < n) {
+        const double ri = r[i] - sigma * t[i];
+        r[i] = ri;
+        x[i] += alpha * pt[i] + sigma * st[i];
+        a = ri * ri; b = r0[i] * ri;
+    }
+    reduce2(a, b, partial, counter, nblocks, [=](double ta, double tb) {
+        sc->omega = ta; sc->its = sc->its + 1;
+        // the last block runs this after every block of the launch has passed its own `done` test, so raising it here is safe
+        if (ta < sc->tol2 || sc->its >= sc->maxits) sc->done = 1;
+        else { sc->rho = tb; sc->beta = (tb * sc->alpha) / (sc->rho_alt * sc->sigma); sc->rho_alt = tb; }
+    });
+}
+// p = r + beta (p - sigma v) ; pt = M p                                     bicgstab_ras.c:227-230, 150-156
+__global__ void __launch_bounds__(SBS) k_p_update_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ r, const double* __restrict__ v,
+                                                     double* __restrict__ p, double* __restrict__ pt, SolverScal* sc) {
+    if (sc->done) return;
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    const double beta = sc->beta, sigma = sc->sigma;
+    if (i < n) p[i] = r[i] + beta * (p[i] - sigma * v[i]);
+    if (bs == 1) { if (i < n) pt[i] = binv[i] * p[i]; return; }
+    __syncthreads();
+    if (i < n) pt[i] = bj_row(binv, p, i, n, bs);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+static void build_binv(Solver& S, const double* vals) {      // dense inverses of the diagonal blocks of D^-1 A
+    const int n = S.n, bs = S.bs;
+    S.nblk = (n + bs - 1) / bs;
+    std::vector<double> binv((size_t)S.nblk * bs * bs, 0.0);
+    std::vector<double> m((size_t)bs * 2 * bs);
+    for (int blk = 0; blk < S.nblk; blk++) {
+        const int b0 = blk * bs, mm = std::min(bs, n - b0);
+        std::fill(m.begin(), m.end(), 0.0);
+        for (int r = 0; r < bs; r++) { m[(size_t)r * 2 * bs + bs + r] = 1.0; if (r >= mm) m[(size_t)r * 2 * bs + r] = 1.0; }
+        for (int r = 0; r < mm; r++) {
+            const int i = b0 + r;
+            double tmp = 0.;
+            for (int j = S.rp[i]; j < S.rp[i + 1]; j++) tmp += fabs(vals[j]);
+            const double sc = 1. / tmp;
+            for (int j = S.rp[i]; j < S.rp[i + 1]; j++) { const int c = S.ci[j] - b0; if (c >= 0 && c < mm) m[(size_t)r * 2 * bs + c] += vals[j] * sc; }
+        }
+        for (int k = 0; k < bs; k++) {                        // Gauss-Jordan, partial pivoting
+            int pv = k; double best = fabs(m[(size_t)k * 2 * bs + k]);
+            for (int r = k + 1; r < bs; r++) if (fabs(m[(size_t)r * 2 * bs + k]) > best) { best = fabs(m[(size_t)r * 2 * bs + k]); pv = r; }
+            if (best == 0.0) { fb_set_error(41, "psolver: singular diagonal block in the block-Jacobi preconditioner"); return; }
+            if (pv != k) for (int c = 0; c < 2 * bs; c++) std::swap(m[(size_t)k * 2 * bs + c], m[(size_t)pv * 2 * bs + c]);
+            const double d = 1.0 / m[(size_t)k * 2 * bs + k];
+            for (int c = 0; c < 2 * bs; c++) m[(size_t)k * 2 * bs + c] *= d;
+            for (int r = 0; r < bs; r++) if (r != k) {
+                const double f = m[(size_t)r * 2 * bs + k];
+                if (f != 0.0) for (int c = 0; c < 2 * bs; c++) m[(size_t)r * 2 * bs + c] -= f * m[(size_t)k * 2 * bs + c];
+            }
+        }
+        double* out = binv.data() + (size_t)blk * bs * bs;     // stored transposed: [c][i_loc] so that rows (threads) read contiguously
+        for (int r = 0; r < bs; r++) for (int c = 0; c < bs; c++) out[(size_t)c * bs + r] = m[(size_t)r * 2 * bs + bs + c];
+    }
+    S.d_binv.upload(binv);
+}
+
+static void upload_values(Solver& S, const double* vals) {
+    CUDA_CHECK(cudaMemcpyAsync(S.d_vals.p, vals, (size_t)S.nnz * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+    k_scale_rows<<<S.nblocks, SBS, 0, S.stream>>>(S.n, S.d_rp.p, S.d_vals.p, S.d_sptr.p, S.d_sval.p, S.d_scale.p);
+    LAUNCH_CHECK();
+}
+
+extern "C" {
+
+void fb200_psolver_set_block(int* block) {
+    const int b = *block;
+    if (b < 1 || b > 32 || (b & (b - 1))) { fb_set_error(40, "block-Jacobi block size must be a power of two in 1..32"); return; }
+    g_block = b;
+}
+
+void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* ilulevel, int* fillin, double* droptol, int* maxits,
+                  int* restart, double* soltol, int* part, int* rptr, int* cols, double* vals, int* reuse, int* fcomm) {
+    (void)stype; (void)pctype; (void)pcilutype; (void)ilulevel; (void)fillin; (void)droptol; (void)restart; (void)fcomm;
+    if (!fb_ok()) return;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fb_set_error(12, "no CUDA device: libfesom_b200 has no CPU fallback"); return; }
+    Solver* S = new Solver();
+    S->n = part[1] - part[0];                                  // one partition per process (psolve.c:38-53, nproc == 1 branch)
+    S->nnz = rptr[S->n]; S->reuse = *reuse; S->maxits = *maxits; S->soltol = *soltol; S->bs = g_block;
+    S->rp.assign(rptr, rptr + S->n + 1);
+    S->ci.resize(S->nnz);
+    for (int j = 0; j < S->nnz; j++) {
+        const int c = cols[j] - part[0];
+        if (c < 0 || c >= S->n) { fb_set_error(42, "psolver_init: column outside the local partition (multi-partition solve needs the halo setup)"); delete S; return; }
+        S->ci[j] = c;
+    }
+    CUDA_CHECK(cudaStreamCreate(&S->stream)); CUDA_CHECK(cudaEventCreate(&S->ev0)); CUDA_CHECK(cudaEventCreate(&S->ev1));
+    const int n = S->n;
+    S->nslice = (n + 31) / 32;
+    S->nblocks = (n + SBS - 1) / SBS;
+    std::vector<int> sptr(S->nslice + 1, 0);
+    for (int s = 0; s < S->nslice; s++) {
+        int w = 0;
+        for (int i = s * 32; i < std::min(n, s * 32 + 32); i++) w = std::max(w, S->rp[i + 1] - S->rp[i]);
+        sptr[s + 1] = sptr[s] + w * 32;
+    }
+    std::vector<int> scol(sptr[S->nslice], 0);
+    for (int i = 0; i < n; i++) {
+        const int base = sptr[i >> 5] + (i & 31), w = (sptr[(i >> 5) + 1] - sptr[i >> 5]) >> 5;
+        for (int k = 0; k < w; k++) scol[base + (k << 5)] = (k < S->rp[i + 1] - S->rp[i]) ? S->ci[S->rp[i] + k] : i;
+    }
+    S->d_rp.upload(S->rp); S->d_ci.upload(S->ci); S->d_sptr.upload(sptr); S->d_scol.upload(scol);
+    S->d_vals.alloc(S->nnz); S->d_sval.alloc(scol.size()); S->d_scale.alloc(n);
+    for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs}) b->alloc(n);
+    S->partial.alloc((size_t)2 * S->nblocks); S->scal.alloc(1); S->counter.alloc(1);
+    upload_values(*S, vals);
+    build_binv(*S, vals);
+    CUDA_CHECK(cudaStreamSynchronize(S->stream));
+    if (!fb_ok()) { delete S; return; }
+    g_solvers[*id] = S;
+}
+
+void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
+    if (!fb_ok()) return;
+    auto it = g_solvers.find(*id);
+    if (it == g_solvers.end()) { fb_set_error(43, "psolve: unknown solver id"); return; }
+    Solver& S = *it->second;
+    cudaStream_t st = S.stream;
+    const int n = S.n, nb = S.nblocks;
+    CUDA_CHECK(cudaEventRecord(S.ev0, st));
+    if (*newvalues) {
+        if (S.reuse) { upload_values(S, vals); if (*newvalues == 2) build_binv(S, vals); }
+        else fprintf(stderr, "ERROR: matrix data is static\n");          // psolve.c:203
+    }
+    CUDA_CHECK(cudaMemcpyAsync(S.rhs.p, rhs, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(S.x.p, sol, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
+    SolverScal h; memset(&h, 0, sizeof(h));
+    h.tol2 = S.soltol * S.soltol; h.maxits = S.maxits;
+    CUDA_CHECK(cudaMemcpyAsync(S.scal.p, &h, sizeof(h), cudaMemcpyHostToDevice, st));
+    k_init_res<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
+                                   S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK();
+    k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK();
+    int done = 0, launched = 0;
+    const int poll = 8;
+    SolverScal* hs = nullptr;
+    CUDA_CHECK(cudaMallocHost(&hs, sizeof(SolverScal)));
+    while (!done && launched < S.maxits && fb_ok()) {
+        for (int k = 0; k < poll && launched < S.maxits; k++, launched++) {
+            k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK();
+            k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK();
+            k_spmv_sigma<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK();
+            k_x_update<<<nb, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK();
+            k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK();
+        }
+        CUDA_CHECK(cudaMemcpyAsync(hs, S.scal.p, sizeof(SolverScal), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        done = hs->done;
+    }
+    if (fb_ok()) {
+        S.last_its = hs->its; S.last_res = sqrt(hs->omega);
+        if (hs->its >= S.maxits && hs->omega > h.tol2) printf("ERROR: no convergence\n");   // bicgstab_ras.c:237-238
+    }
+    cudaFreeHost(hs);
+    CUDA_CHECK(cudaMemcpyAsync(sol, S.x.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaEventRecord(S.ev1, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    if (fb_ok()) CUDA_CHECK(cudaEventElapsedTime(&g_ssh_ms, S.ev0, S.ev1));
+}
+
+void fb200_psolve_info(int* id, int* its, double* resnorm) {
+    auto it = g_solvers.find(*id);
+    if (it == g_solvers.end()) { *its = -1; *resnorm = -1.0; return; }
+    *its = it->second->last_its; *resnorm = it->second->last_res;
+}
+
+void psolver_final(void) {
+    for (auto& kv : g_solvers) {
+        Solver* S = kv.second;
+        if (S->stream) cudaStreamSynchronize(S->stream);
+        for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs, &S->d_vals, &S->d_sval, &S->d_scale, &S->d_binv, &S->partial}) b->release();
+        S->d_rp.release(); S->d_ci.release(); S->d_sptr.release(); S->d_scol.release(); S->scal.release(); S->counter.release();
+        if (S->ev0) cudaEventDestroy(S->ev0);
+        if (S->ev1) cudaEventDestroy(S->ev1);
+        if (S->stream) cudaStreamDestroy(S->stream);
+        delete S;
+    }
+    g_solvers.clear();
+}
+
+}  // extern "C"

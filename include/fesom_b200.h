@@ -1,0 +1,101 @@
+/* fesom_b200.h — C ABI of libfesom_b200.so: FESOM2's per-timestep tracer transport (FCT advection + implicit
+ * vertical diffusion) and SSH elliptic solve as hand-written FP64 CUDA kernels for sm_100a.
+ *
+ * The library is called from FESOM2's own Fortran time loop through ISO_C_BINDING (INTEGRATION.md shows the
+ * interface blocks).  Conventions are the reference's own (src/psolve.c, src/oce_ale.F90:2272-2291):
+ *   - every argument is passed BY REFERENCE (Fortran default), integer(C_INT) / real(C_DOUBLE);
+ *   - arrays are the caller's Fortran arrays as they are: column-major, level index fastest,
+ *     index arrays hold 1-based values (psolver_init receives the 0-based shifted temporaries the
+ *     reference passes, oce_ale.F90:2332-2333);
+ *   - the caller owns all arrays; the library copies what it keeps;
+ *   - no return codes: an error prints "fesom_b200: ERROR ..." to stderr and sets a sticky status that
+ *     fb200_status() reports; with FB200_ABORT_ON_ERROR=1 in the environment it calls abort()
+ *     (the analogue of par_ex(1), src/gen_modules_partitioning.F90:113-157);
+ *   - there is no CPU fallback: without a CUDA device every compute entry point raises that error.
+ */
+#ifndef FESOM_B200_H
+#define FESOM_B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------------------------------------------
+ * SSH solve: symbol-for-symbol replacement of src/psolve.c (psolver_init :16, psolve :152, psolver_final :117).
+ * stype/pctype/pcilutype/ilulevel/fillin/droptol/restart are accepted and ignored: the Krylov method is
+ * right-preconditioned BiCGStab (lib/parms/src/bicgstab_ras.c:49-259) with a block-Jacobi preconditioner.
+ *   part  : npes+1 row offsets of the PE-contiguous numbering (0-based)
+ *   rptr  : N_own+1 CSR row pointers (0-based)         cols : nnz global PE-contiguous column ids (0-based)
+ *   vals  : nnz matrix values                          reuse: 1 = values will be replaced by later psolve calls
+ *   fcomm : Fortran MPI communicator handle (unused by the single-process path; kept for ABI identity)
+ */
+void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* ilulevel, int* fillin, double* droptol,
+                  int* maxits, int* restart, double* soltol, int* part, int* rptr, int* cols, double* vals,
+                  int* reuse, int* fcomm);
+/* rhs: N_own (+halo) right-hand side; sol: in = initial guess (warm start, psolve.c:206), out = solution;
+ * newvalues: 0 keep matrix, 1 replace values (keep preconditioner), 2 replace values and rebuild preconditioner */
+void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues);
+void psolver_final(void);
+/* iteration count and final scaled residual norm of the last psolve(id) (the reference keeps them in the
+ * pARMS solver object, parms_SolverGetIts / bicgstab_ras.c:257) */
+void fb200_psolve_info(int* id, int* its, double* resnorm);
+/* block size of the block-Jacobi preconditioner for solvers created afterwards (1 = point Jacobi) */
+void fb200_psolver_set_block(int* block);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Tracer path.  Replaces the body of solve_tracers_ale (src/oce_ale_tracer.F90:101-199): init_tracers_AB,
+ * adv_tracers_ale -> do_oce_adv_tra (src/oce_adv_tra_driver.F90:41), diff_tracers_ale, salinity clamp.
+ * Call order: fb200_init_dims, fb200_init_connectivity, fb200_init_levels, fb200_init_geometry,
+ * [fb200_init_halo], fb200_set_options, fb200_init_commit — once, after mesh_setup/ocean_setup; then per step
+ * fb200_push_step_state + fb200_solve_tracers_ale (or the push/solve/pull triple to keep tracers resident).
+ */
+void fb200_init_dims(int* nl, int* myDim_nod2D, int* eDim_nod2D, int* myDim_elem2D, int* eDim_elem2D,
+                     int* eXDim_elem2D, int* myDim_edge2D, int* num_tracers, int* fcomm);
+/* t_mesh connectivity (src/MOD_MESH.F90:19-95), local 1-based numbering:
+ * edges(2,myDim_edge2D) edge_tri(2,myDim_edge2D) elem2D_nodes(3,myDim+eDim+eXDim elems)
+ * nod_in_elem2D_num(N) nod_in_elem2D(ld,N)  edge_up_dn_tri(2,myDim_edge2D) (src/oce_muscl_adv.F90:141) */
+void fb200_init_connectivity(int* edges, int* edge_tri, int* elem2D_nodes, int* nod_in_elem2D_num,
+                             int* nod_in_elem2D, int* nod_in_elem2D_ld, int* edge_up_dn_tri);
+/* nlevels/ulevels (all local elems), nlevels_nod2D/ulevels_nod2D/nlevels_nod2D_min/ulevels_nod2D_max (N),
+ * nboundary_lay(N) (src/oce_muscl_adv.F90:74-104) */
+void fb200_init_levels(int* nlevels, int* ulevels, int* nlevels_nod2D, int* ulevels_nod2D, int* nlevels_nod2D_min,
+                       int* ulevels_nod2D_max, int* nboundary_lay);
+/* edge_cross_dxdy(4,E) edge_dxdy(2,E) elem_cos(elems) elem_area(elems) gradient_sca(6,myDim_elem2D)
+ * area(nl,N) areasvol(nl,N) zbar_n_bot(N) */
+void fb200_init_geometry(double* edge_cross_dxdy, double* edge_dxdy, double* elem_cos, double* elem_area,
+                         double* gradient_sca, double* area, double* areasvol, double* zbar_n_bot);
+/* namelist switches the Fortran routines read from modules (src/oce_modules.F90:82-99, config/namelist.oce):
+ * tra_adv_hor 0 MUSCL 1 MFCT 2 UPW1; tra_adv_ver 0 QR4C 1 CDIFF 2 PPM 3 UPW1; tra_adv_lim 0 FCT 1 NONE */
+void fb200_set_options(int* tra_adv_hor, int* tra_adv_ver, int* tra_adv_lim, double* tra_adv_ph, double* tra_adv_pv,
+                       int* w_split, int* i_vert_diff, int* Redi, int* use_sw_pene, int* do_hor_diff, int* clamp_salt,
+                       double* is_nonlinfs, double* dt, double* epsilon, int* tracer_id /* num_tracers */);
+void fb200_init_commit(void);
+/* per-step inputs produced by the host (shapes: src/oce_setup_step.F90:205-323, src/oce_ale.F90:94-104):
+ * UV(2,nl-1,elems) Wvel/Wvel_e/Wvel_i(nl,N) hnode/hnode_new(nl-1,N) helem(nl-1,myDim_elem2D) Z_3d_n(nl-1,N)
+ * zbar_3d_n(nl,N) Kv(nl,N) Ki(nl-1,N) slope_tapered(3,nl-1,N) sw_3d(nl,N); surface fluxes (N) */
+void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode, double* hnode_new,
+                           double* helem, double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki,
+                           double* slope_tapered, double* heat_flux, double* water_flux, double* virtual_salt,
+                           double* relax_salt, double* real_salt_flux, double* sw_3d);
+/* tr_arr / tr_arr_old (nl-1, N, num_tracers) */
+void fb200_push_tracers(double* tr_arr, double* tr_arr_old);
+void fb200_solve_tracers(void);                         /* all tracers, device resident */
+void fb200_pull_tracers(double* tr_arr, double* tr_arr_old);
+void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old);   /* push + solve + pull */
+/* debugging / parity: copy an internal (level, node|edge|elem) work field back in the reference layout.
+ * name: "fct_LO","adf_h","adf_v","fct_plus","fct_minus","tr_xy_x","tr_xy_y","ttfAB","tstar" ; returns via status */
+void fb200_debug_fetch(const char* name, double* out);
+void fb200_finalize(void);
+
+/* 0 = ok; otherwise the code of the first error since the last fb200_clear_status() */
+int fb200_status(void);
+const char* fb200_status_message(void);
+void fb200_clear_status(void);
+/* number of kernels this library has launched since load (bench.py's gpu_launches) */
+long long fb200_kernel_launches(void);
+/* device timing of the last fb200_solve_tracers / psolve in milliseconds (CUDA events on the library's stream) */
+double fb200_last_ms(const char* what);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

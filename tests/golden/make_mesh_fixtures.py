@@ -1,0 +1,17 @@
+"""Pack the reference's own test meshes (test/meshes/pi, test/meshes/soufflet: plain-text files, SURVEY.md §4
+fixtures) into compressed .npz inputs for the tests, because /root/reference does not exist on the GPU box.
+Run in the authoring container:  python tests/golden/make_mesh_fixtures.py
+"""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", ".."))
+from fesom2_b200.host import read_mesh_files  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+for name in ("pi", "soufflet"):
+    m = read_mesh_files(os.path.join("/root/reference/test/meshes", name))
+    np.savez_compressed(os.path.join(HERE, name + "_mesh.npz"), **m)
+    print(name, {k: (v.shape if hasattr(v, "shape") else v) for k, v in m.items()})
