@@ -22,7 +22,7 @@ EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb20
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_tracers",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
-           "fb200_kernel_launches", "fb200_last_ms"]
+           "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report"]
 
 
 class FesomB200Error(RuntimeError):
@@ -44,6 +44,9 @@ def lib(rebuild=False):
         L.fb200_last_ms.restype = C.c_double
         L.fb200_last_ms.argtypes = [C.c_char_p]
         L.fb200_debug_fetch.argtypes = [C.c_char_p, C.c_void_p]
+        L.fb200_set_stream.argtypes = [C.c_void_p]
+        L.fb200_profile_report.argtypes = [C.c_char_p, C.c_void_p]
+        L.fb200_profile_report.restype = C.c_int
         _lib = L
     return _lib
 
@@ -66,6 +69,28 @@ def _d(v):
 
 def _p(a):
     return C.c_void_p(a.ctypes.data)
+
+
+def set_stream(cuda_stream_ptr):
+    """run all later library work on the caller's CUDA stream (an integer cudaStream_t, e.g. torch's .cuda_stream)"""
+    lib().fb200_set_stream(C.c_void_p(int(cuda_stream_ptr) if cuda_stream_ptr else None))
+
+
+def profile(mode):
+    """0 off, 1 on, 2 on + reset"""
+    lib().fb200_profile(_i(mode))
+
+
+def profile_report():
+    """{kernel: (launches, total_ms)} since the last reset"""
+    buf = C.create_string_buffer(1 << 16)
+    n = lib().fb200_profile_report(buf, C.byref(C.c_int(len(buf))))
+    out = {}
+    if n > 0:
+        for line in buf.value.decode().splitlines():
+            nm, cnt, ms = line.split()
+            out[nm] = (int(cnt), float(ms))
+    return out
 
 
 class TracerEngine:

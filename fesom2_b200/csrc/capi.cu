@@ -6,6 +6,7 @@
 int fb_status_code(); const char* fb_status_msg(); void fb_clear_status();
 const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind);
 double ssh_last_ms();
+void prof_reset(); int prof_report(char* buf, int cap);
 
 extern "C" {
 
@@ -17,6 +18,10 @@ double fb200_last_ms(const char* what) {
     if (what && !strcmp(what, "psolve")) return ssh_last_ms();
     return (double)tctx().last_ms;
 }
+
+void fb200_set_stream(void* cuda_stream) { fb_set_stream((cudaStream_t)cuda_stream); }
+void fb200_profile(int* enable) { prof_enable(*enable != 0); if (*enable == 2) prof_reset(); }
+int fb200_profile_report(char* buf, int* cap) { return prof_report(buf, *cap); }
 
 void fb200_init_dims(int* nl, int* myDim_nod2D, int* eDim_nod2D, int* myDim_elem2D, int* eDim_elem2D, int* eXDim_elem2D,
                      int* myDim_edge2D, int* num_tracers, int* fcomm) {
@@ -82,6 +87,7 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
                            double* water_flux, double* virtual_salt, double* relax_salt, double* real_salt_flux, double* sw_3d) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(33, "fb200_push_step_state before fb200_init_commit"); return; }
+    c.stream = fb_stream();
     const int L = c.nl - 1, nl = c.nl, N = c.N;
     ctx_push_node_field(c, UV, L, c.E, c.U.p, 2, 0);
     ctx_push_node_field(c, UV, L, c.E, c.V.p, 2, 1);
@@ -113,6 +119,7 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
 void fb200_push_tracers(double* tr_arr, double* tr_arr_old) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(34, "fb200_push_tracers before fb200_init_commit"); return; }
+    c.stream = fb_stream();
     const int L = c.nl - 1;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
     for (int tr = 0; tr < c.ntr; tr++) {
@@ -127,6 +134,7 @@ void fb200_solve_tracers(void) { tracer_step_all(tctx()); }
 void fb200_pull_tracers(double* tr_arr, double* tr_arr_old) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(35, "fb200_pull_tracers before fb200_init_commit"); return; }
+    c.stream = fb_stream();
     const int L = c.nl - 1;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
     for (int tr = 0; tr < c.ntr; tr++) {
@@ -144,6 +152,7 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
 void fb200_debug_fetch(const char* name, double* out) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(36, "fb200_debug_fetch before fb200_init_commit"); return; }
+    c.stream = fb_stream();
     int kind = 0;
     std::string s(name);
     const double* f = nullptr;

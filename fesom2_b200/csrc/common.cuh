@@ -49,10 +49,23 @@ extern long long g_launches;
 #define CUDA_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fb_set_error(100 + (int)e_, std::string(#x) + ": " + cudaGetErrorString(e_)); } } while (0)
 #define LAUNCH_CHECK() do { g_launches++; cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) fb_set_error(100 + (int)e_, std::string("kernel launch: ") + cudaGetErrorString(e_)); } while (0)
 
+// per-kernel device timing (bench.py's roofline leg): when enabled every ProfScope records a CUDA event pair on the
+// launching stream; prof_collect() (after a stream sync) folds them into per-name totals
+void prof_enable(bool on);
+bool prof_on();
+void prof_push(const char* name, cudaStream_t st);
+void prof_pop(cudaStream_t st);
+void prof_collect();
+struct ProfScope {
+    cudaStream_t st; bool on;
+    ProfScope(const char* name, cudaStream_t s) : st(s), on(prof_on()) { if (on) prof_push(name, st); }
+    ~ProfScope() { if (on) prof_pop(st); }
+};
+
 template <class T> struct DevBuf {
     T* p = nullptr; size_t n = 0;
-    void alloc(size_t count) { release(); n = count; if (count) { CUDA_CHECK(cudaMalloc(&p, count * sizeof(T))); if (p) CUDA_CHECK(cudaMemset(p, 0, count * sizeof(T))); } }
-    void upload(const std::vector<T>& h) { alloc(h.size()); if (p && n) CUDA_CHECK(cudaMemcpy(p, h.data(), n * sizeof(T), cudaMemcpyHostToDevice)); }
+    void alloc(size_t count) { release(); n = count; if (count) { CUDA_CHECK(cudaMalloc(&p, count * sizeof(T))); if (p) { CUDA_CHECK(cudaMemset(p, 0, count * sizeof(T))); CUDA_CHECK(cudaDeviceSynchronize()); } } }
+    void upload(const std::vector<T>& h) { alloc(h.size()); if (p && n) { CUDA_CHECK(cudaMemcpy(p, h.data(), n * sizeof(T), cudaMemcpyHostToDevice)); CUDA_CHECK(cudaDeviceSynchronize()); } }
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
 };
 
@@ -88,9 +101,13 @@ struct TracerCtx {
     // staging for host<->device transfers (reference layout)
     DevBuf<double> stage;
     cudaStream_t stream = nullptr;
+    bool own_stream = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
 };
+// stream every entry point works on: the caller's (fb200_set_stream) or one created by the library
+cudaStream_t fb_stream();
+void fb_set_stream(cudaStream_t s);
 
 // context.cu
 TracerCtx& tctx();

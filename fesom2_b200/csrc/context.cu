@@ -26,6 +26,63 @@ void fb_clear_status() { std::lock_guard<std::mutex> lk(g_mu); g_status = 0; g_s
 TracerCtx& tctx() { static TracerCtx c; return c; }
 
 // ---------------------------------------------------------------------------------------------------
+static cudaStream_t g_stream = nullptr;
+static bool g_stream_owned = false;
+cudaStream_t fb_stream() {
+    if (!g_stream) { CUDA_CHECK(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking)); g_stream_owned = true; }
+    return g_stream;
+}
+void fb_set_stream(cudaStream_t s) {
+    if (g_stream && g_stream_owned) { cudaStreamSynchronize(g_stream); cudaStreamDestroy(g_stream); }
+    g_stream = s; g_stream_owned = false;
+    if (!s) g_stream = nullptr;               // next fb_stream() creates a private one again
+}
+
+// per-kernel timing ----------------------------------------------------------------------------------
+#include <map>
+struct ProfRec { std::string name; cudaEvent_t a, b; };
+static bool g_prof = false;
+static std::vector<ProfRec> g_prof_open, g_prof_done;
+static std::vector<cudaEvent_t> g_prof_pool;
+struct ProfAcc { long long launches = 0; double ms = 0.0; };
+static std::map<std::string, ProfAcc> g_prof_acc;
+void prof_enable(bool on) { g_prof = on; }
+bool prof_on() { return g_prof; }
+static cudaEvent_t prof_event() {
+    if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+void prof_push(const char* name, cudaStream_t st) {
+    ProfRec r; r.name = name; r.a = prof_event(); r.b = prof_event();
+    cudaEventRecord(r.a, st);
+    g_prof_open.push_back(r);
+}
+void prof_pop(cudaStream_t st) {
+    if (g_prof_open.empty()) return;
+    ProfRec r = g_prof_open.back(); g_prof_open.pop_back();
+    cudaEventRecord(r.b, st);
+    g_prof_done.push_back(r);
+}
+void prof_collect() {
+    for (ProfRec& r : g_prof_done) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) { ProfAcc& a = g_prof_acc[r.name]; a.launches++; a.ms += ms; }
+        g_prof_pool.push_back(r.a); g_prof_pool.push_back(r.b);
+    }
+    g_prof_done.clear();
+}
+void prof_reset() { prof_collect(); g_prof_acc.clear(); }
+int prof_report(char* buf, int cap) {          // "name launches ms\n" per kernel
+    prof_collect();
+    std::string s;
+    char line[256];
+    for (auto& kv : g_prof_acc) { snprintf(line, sizeof(line), "%s %lld %.6f\n", kv.first.c_str(), kv.second.launches, kv.second.ms); s += line; }
+    if ((int)s.size() + 1 > cap) return -1;
+    memcpy(buf, s.c_str(), s.size() + 1);
+    return (int)s.size();
+}
+
+// ---------------------------------------------------------------------------------------------------
 // restage kernels.  One block per tile of 32 entities.  src is the reference array (ncomp, lev_ref, ent).
 __global__ void __launch_bounds__(256) k_ref_to_tiled(const double* __restrict__ src, double* __restrict__ dst, int count_ent,
                                                       int lev_ref, int nlp, int ncomp, int comp) {
@@ -92,7 +149,8 @@ void ctx_commit(TracerCtx& c) {
     if (c.h_edges.empty() || c.h_nlev.empty() || c.h_ecd.empty()) { fb_set_error(11, "fb200_init_commit before connectivity/levels/geometry"); return; }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fb_set_error(12, "no CUDA device: libfesom_b200 has no CPU fallback"); return; }
-    if (!c.stream) { CUDA_CHECK(cudaStreamCreate(&c.stream)); CUDA_CHECK(cudaEventCreate(&c.ev0)); CUDA_CHECK(cudaEventCreate(&c.ev1)); }
+    c.stream = fb_stream();
+    if (!c.ev0) { CUDA_CHECK(cudaEventCreate(&c.ev0)); CUDA_CHECK(cudaEventCreate(&c.ev1)); }
     c.nlp = c.nl;
     const int nlp = c.nlp, N = c.N, myN = c.myN, Eall = c.Eall, myE = c.myE, myEd = c.myEd;
     c.Ntiles = (N + TILE - 1) / TILE; c.myNtiles = (myN + TILE - 1) / TILE;
@@ -200,6 +258,5 @@ void ctx_release(TracerCtx& c) {
     c.n_lev.release(); c.n_nbl.release();
     if (c.ev0) cudaEventDestroy(c.ev0);
     if (c.ev1) cudaEventDestroy(c.ev1);
-    if (c.stream) cudaStreamDestroy(c.stream);
     c = TracerCtx();
 }

@@ -233,8 +233,7 @@ static void build_binv(Solver& S, const double* vals) {      // dense inverses o
 
 static void upload_values(Solver& S, const double* vals) {
     CUDA_CHECK(cudaMemcpyAsync(S.d_vals.p, vals, (size_t)S.nnz * sizeof(double), cudaMemcpyHostToDevice, S.stream));
-    k_scale_rows<<<S.nblocks, SBS, 0, S.stream>>>(S.n, S.d_rp.p, S.d_vals.p, S.d_sptr.p, S.d_sval.p, S.d_scale.p);
-    LAUNCH_CHECK();
+    { ProfScope ps_("k_scale_rows", S.stream); k_scale_rows<<<S.nblocks, SBS, 0, S.stream>>>(S.n, S.d_rp.p, S.d_vals.p, S.d_sptr.p, S.d_sval.p, S.d_scale.p); LAUNCH_CHECK(); }
 }
 
 extern "C" {
@@ -261,7 +260,7 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
         if (c < 0 || c >= S->n) { fb_set_error(42, "psolver_init: column outside the local partition (multi-partition solve needs the halo setup)"); delete S; return; }
         S->ci[j] = c;
     }
-    CUDA_CHECK(cudaStreamCreate(&S->stream)); CUDA_CHECK(cudaEventCreate(&S->ev0)); CUDA_CHECK(cudaEventCreate(&S->ev1));
+    S->stream = fb_stream(); CUDA_CHECK(cudaEventCreate(&S->ev0)); CUDA_CHECK(cudaEventCreate(&S->ev1));
     const int n = S->n;
     S->nslice = (n + 31) / 32;
     S->nblocks = (n + SBS - 1) / SBS;
@@ -292,6 +291,7 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     auto it = g_solvers.find(*id);
     if (it == g_solvers.end()) { fb_set_error(43, "psolve: unknown solver id"); return; }
     Solver& S = *it->second;
+    S.stream = fb_stream();
     cudaStream_t st = S.stream;
     const int n = S.n, nb = S.nblocks;
     CUDA_CHECK(cudaEventRecord(S.ev0, st));
@@ -304,20 +304,20 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     SolverScal h; memset(&h, 0, sizeof(h));
     h.tol2 = S.soltol * S.soltol; h.maxits = S.maxits;
     CUDA_CHECK(cudaMemcpyAsync(S.scal.p, &h, sizeof(h), cudaMemcpyHostToDevice, st));
-    k_init_res<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
-                                   S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK();
-    k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK();
+    { ProfScope ps_("k_init_res", st); k_init_res<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
+                                   S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
+    { ProfScope ps_("k_pc", st); k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
     int done = 0, launched = 0;
     const int poll = 8;
     SolverScal* hs = nullptr;
     CUDA_CHECK(cudaMallocHost(&hs, sizeof(SolverScal)));
     while (!done && launched < S.maxits && fb_ok()) {
         for (int k = 0; k < poll && launched < S.maxits; k++, launched++) {
-            k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK();
-            k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK();
-            k_spmv_sigma<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK();
-            k_x_update<<<nb, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK();
-            k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK();
+            { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
+            { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
+            { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
+            { ProfScope ps_("k_x_update", st); k_x_update<<<nb, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
+            { ProfScope ps_("k_p_update_pc", st); k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
         }
         CUDA_CHECK(cudaMemcpyAsync(hs, S.scal.p, sizeof(SolverScal), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
@@ -348,7 +348,6 @@ void psolver_final(void) {
         S->d_rp.release(); S->d_ci.release(); S->d_sptr.release(); S->d_scol.release(); S->scal.release(); S->counter.release();
         if (S->ev0) cudaEventDestroy(S->ev0);
         if (S->ev1) cudaEventDestroy(S->ev1);
-        if (S->stream) cudaStreamDestroy(S->stream);
         delete S;
     }
     g_solvers.clear();

@@ -630,28 +630,34 @@ void tracer_step_all(TracerCtx& c) {
     if (!c.opt.i_vert_diff) { fb_set_error(23, "i_vert_diff=.false. is not implemented on the device path"); return; }
     if (c.opt.dt <= 0.0) { fb_set_error(24, "dt not set (fb200_set_options)"); return; }
     set_smem_attrs();
+    c.stream = fb_stream();
     cudaStream_t st = c.stream;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     const int gN128 = (c.myN + 127) / 128, gN64 = (c.myN + 63) / 64, gE = (c.myE + 127) / 128, gEd = (c.myEd + 127) / 128, gNall = (c.N + 127) / 128;
     const size_t sm1_128 = (size_t)c.nlp * 128 * sizeof(double);
     const size_t sm_64 = (size_t)c.nlp * 64 * sizeof(double);
     CUDA_CHECK(cudaEventRecord(c.ev0, st));
+#define KL(name, ...) do { ProfScope ps_(name, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
     for (int tr = 0; tr < c.ntr; tr++) {
         KP p = make_kp(c, tr);
         const double ca = -(0.5 + c.opt.epsilon), cb = 1.5 + c.opt.epsilon;
-        k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb); LAUNCH_CHECK();
-        k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told); LAUNCH_CHECK();
-        k_lo<<<gN128, 128, sm1_128, st>>>(p); LAUNCH_CHECK();
-        if (c.opt.w_split) { k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi); LAUNCH_CHECK(); }
-        k_ho_edge<<<gEd, 128, 0, st>>>(p); LAUNCH_CHECK();
-        k_fct_bounds<<<gN64, 64, 4 * sm_64, st>>>(p); LAUNCH_CHECK();
-        if (c.opt.do_hor_diff) { k_grad_elem<<<gE, 128, 0, st>>>(p, p.T); LAUNCH_CHECK(); }
-        if (c.opt.do_hor_diff && c.opt.Redi) { k_grad_z<<<gNall, 128, 0, st>>>(p, p.T); LAUNCH_CHECK(); }
-        k_update<<<gN128, 128, sm1_128, st>>>(p); LAUNCH_CHECK();
-        CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));   // tr_arr_old = tr_arr (:274)
-        k_impl_diff<<<gN64, 64, 3 * sm_64, st>>>(p); LAUNCH_CHECK();
+        KL("k_ab2", k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb));
+        KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
+        KL("k_lo", k_lo<<<gN128, 128, sm1_128, st>>>(p));
+        if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
+        KL("k_ho_edge", k_ho_edge<<<gEd, 128, 0, st>>>(p));
+        KL("k_fct_bounds", k_fct_bounds<<<gN64, 64, 4 * sm_64, st>>>(p));
+        if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
+        if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
+        KL("k_update", k_update<<<gN128, 128, sm1_128, st>>>(p));
+        {   // tr_arr_old = tr_arr (:274)
+            ProfScope ps_("copy_told", st);
+            CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
+        }
+        KL("k_impl_diff", k_impl_diff<<<gN64, 64, 3 * sm_64, st>>>(p));
     }
-    if (c.opt.clamp_salt && c.ntr >= 2) { KP p = make_kp(c, 1); k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T); LAUNCH_CHECK(); }
+    if (c.opt.clamp_salt && c.ntr >= 2) { KP p = make_kp(c, 1); KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T)); }
+#undef KL
     CUDA_CHECK(cudaEventRecord(c.ev1, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
     if (fb_ok()) CUDA_CHECK(cudaEventElapsedTime(&c.last_ms, c.ev0, c.ev1));

@@ -90,6 +90,13 @@ void fb200_finalize(void);
 int fb200_status(void);
 const char* fb200_status_message(void);
 void fb200_clear_status(void);
+/* CUDA stream (cudaStream_t passed as void*) every later call works on; NULL = a private stream of the library.
+ * Lets the host driver order library work with its own copies/kernels and time it with its own events. */
+void fb200_set_stream(void* cuda_stream);
+/* per-kernel device timing: *enable = 1 on, 0 off, 2 on + reset totals.  fb200_profile_report writes one line
+ * "kernel launches total_ms" per kernel into buf (capacity *cap) and returns the length, -1 if buf is too small */
+void fb200_profile(int* enable);
+int fb200_profile_report(char* buf, int* cap);
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
 long long fb200_kernel_launches(void);
 /* device timing of the last fb200_solve_tracers / psolve in milliseconds (CUDA events on the library's stream) */

@@ -147,3 +147,35 @@ def ref_lib():
         R.psolve.restype = None
         _ref = R
     return _ref
+
+
+class RefSolver:
+    """The reference's own psolver_init/psolve (oracle/_ref) on one subdomain.  The MPI shim reports two ranks,
+    the second one owning no rows (oracle/mpi_stub/mpi_stub.c), so `part` has three entries."""
+    _next_id = 1
+
+    def __init__(self, rowptr0, colind0, values, soltol=1e-10, maxits=2000, ilulevel=2, fillin=3, droptol=1e-8):
+        R = ref_lib()
+        if R is None:
+            raise RuntimeError("oracle/_ref/libpsolve_ref.so has not been built (needs /root/reference)")
+        self.R = R
+        self.rp = np.ascontiguousarray(rowptr0, dtype=np.int32)
+        self.ci = np.ascontiguousarray(colind0, dtype=np.int32)
+        self.n = self.rp.size - 1
+        self.part = np.array([0, self.n, self.n], dtype=np.int32)
+        self.id = RefSolver._next_id
+        RefSolver._next_id += 1
+        assert self.id < 10, "psolve.c keeps at most NSOL=10 solvers"
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        i = lambda x: C.byref(C.c_int(int(x)))          # noqa: E731
+        d = lambda x: C.byref(C.c_double(float(x)))     # noqa: E731
+        # SOLBICGS_RAS=6, PCRAS=2, PCILUK=1 (lib/parms/include/fparms.h:25-32; oce_ale.F90:2330)
+        R.psolver_init(i(self.id), i(6), i(2), i(1), i(ilulevel), i(fillin), d(droptol), i(maxits), i(15), d(soltol),
+                       self.part.ctypes.data, self.rp.ctypes.data, self.ci.ctypes.data, v.ctypes.data, i(1), i(0))
+
+    def solve(self, rhs, values, x0, new_values=1):
+        x = np.array(x0, dtype=np.float64, copy=True)
+        b = np.ascontiguousarray(rhs, dtype=np.float64)
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        self.R.psolve(C.byref(C.c_int(self.id)), b.ctypes.data, v.ctypes.data, x.ctypes.data, C.byref(C.c_int(int(new_values))))
+        return x
