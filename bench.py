@@ -1,0 +1,415 @@
+#!/usr/bin/env python
+"""bench.py — FESOM2 tracer FCT step + SSH solve on B200 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--nodes M] [--nl L]
+
+One "step" = one pass of the hot path over the synthetic ocean: psolve (SSH elliptic solve, zero initial guess,
+matrix values refreshed) followed by solve_tracers_ale for all tracers (AB2, gradients, FCT advection, horizontal
+diffusion, implicit vertical diffusion, salinity clamp).  Prints ONE JSON line.
+
+  value      tracer node-level updates/s = wet (node, layer) pairs x num_tracers x K / device time of the K tracer
+             steps, state resident in HBM (CUDA events on the launching stream, max over ranks)
+  ssh        SSH solve ms/step (device time of psolve, incl. row scaling), iterations, final scaled residual
+  e2e        the same two calls through the C ABI with HOST (pinned) buffers: fb200_push_step_state +
+             fb200_solve_tracers_ale + psolve, host<->device copies inside the timed region
+  roofline   dominant kernel: algorithmic bytes per launch / measured launch duration vs MEASURED_PEAKS.json
+  cpu_baseline / --impl reference : the oracle (C restatement, tracer step) and the reference's own
+             psolve.c + pARMS (oracle/_ref, SSH solve) on the host cores, on a bounded sample of the workload
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "tracer node-level updates/s (FCT adv+diff)"
+UNIT = "node-level updates/s"
+
+# Algorithmic HBM bytes per wet (node, layer) of ONE launch of each kernel: every array the
+# kernel must read or write counted once (perfect reuse inside the kernel), 2 elements and 3 edges per node.
+ALGO_BYTES = {
+    "k_ab2": 24, "k_grad_elem": 40, "k_lo": 142, "k_ho_edge": 120, "k_fct_bounds": 72, "k_update": 152,
+    "copy_told": 16, "k_impl_diff": 48, "k_clamp_salt": 16, "k_vert_impl": 40, "k_grad_z": 24,
+}
+# SSH kernels: bytes per matrix row per launch (7-wide SELL rows: 7 x (8 B value + 4 B column) + vectors)
+ALGO_BYTES_ROW = {
+    "k_spmv_alpha": 7 * 12 + 8 + 8 + 8, "k_spmv_sigma": 7 * 12 + 8 + 8 + 8, "k_r_update_pc": 8 * 5, "k_x_update": 8 * 8,
+    "k_p_update_pc": 8 * 6, "k_scale_rows": 7 * 8 * 2 + 8 + 8, "k_init_res": 7 * 12 + 8 * 6, "k_pc": 24,
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--nodes", type=int, default=5_000_000, help="target surface nodes per GPU")
+    ap.add_argument("--nl", type=int, default=49, help="number of levels (layers = nl-1)")
+    ap.add_argument("--cpu-nodes", type=int, default=120_000, help="surface nodes of the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--block", type=int, default=1, help="block-Jacobi block size of the SSH preconditioner")
+    return ap.parse_args()
+
+
+def mem_available_gb():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable"):
+                return int(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
+
+
+def band_dims(target_nodes):
+    """nlon x nlat (= nlon/2) lon/lat band whose wet node count is ~target (about 8.5 % becomes land)"""
+    nlon = int(round((2.0 * target_nodes / 0.915) ** 0.5))
+    nlon += nlon % 2
+    return nlon, nlon // 2
+
+
+def build_workload(target_nodes, nl, seed=12345):
+    from tests import util
+    nlon, nlat = band_dims(target_nodes)
+    t0 = time.time()
+    hm = util.build_model("band", nlon=nlon, nlat=nlat, nl=nl, seed=seed, dt=600.0)
+    hm.compute_ssh_rhs()
+    info = dict(nlon=nlon, nlat=nlat, nl=nl, nod2D=hm.ipar("myDim_nod2D"), elem2D=hm.ipar("myDim_elem2D"),
+                edge2D=hm.ipar("myDim_edge2D"), setup_s=round(time.time() - t0, 1))
+    info["wet_node_layers"] = int(util.wet_mask(hm).sum())
+    return hm, info
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons while the timed region runs (B200_PROFILING.md clocks line)"""
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index
+        self.stop_flag = False
+        self.sm, self.reasons, self.max_mhz = [], set(), None
+
+    def query(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=5).stdout.strip()
+            f = [x.strip() for x in out.split(",")]
+            self.sm.append(float(f[0]))
+            self.max_mhz = float(f[1])
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+                if v.lower() == "active":
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def run(self):
+        while not self.stop_flag:
+            self.query()
+            time.sleep(0.05)
+
+    def result(self):
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (copy bandwidth)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
+
+
+def pin(arrays):
+    """page-lock the host arrays the e2e leg copies from/to (cudaHostRegister); returns the registered list"""
+    import torch
+    rt = torch.cuda.cudart()
+    done = []
+    for a in arrays:
+        if a.nbytes == 0:
+            continue
+        try:
+            r = rt.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+            if int(r) == 0:
+                done.append(a)
+        except Exception:
+            pass
+    return done
+
+
+def unpin(arrays):
+    import torch
+    rt = torch.cuda.cudart()
+    for a in arrays:
+        try:
+            rt.cudaHostUnregister(a.ctypes.data)
+        except Exception:
+            pass
+
+
+STATE = ["UV", "Wvel", "Wvel_e", "hnode", "hnode_new", "helem", "Z_3d_n", "zbar_3d_n", "Kv", "Ki",
+         "heat_flux", "water_flux", "virtual_salt", "relax_salt", "real_salt_flux"]
+
+
+def run_b200(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from fesom2_b200 import api
+
+    # ---- workload (host side = what the Fortran driver owns)
+    target = args.nodes
+    need_gb = 19e-6 * target * (args.nl / 49.0) * world            # measured ~18 kB of host state per surface node
+    avail = mem_available_gb()
+    reduced = False
+    if avail and need_gb * 1.25 > avail:
+        target = int(target * avail / (need_gb * 1.25))
+        reduced = True
+    hm, info = build_workload(target, args.nl, seed=12345 + rank)
+    ntr = hm.ipar("num_tracers")
+    n_own = hm.ipar("myDim_nod2D")
+    units_per_step = info["wet_node_layers"] * ntr
+
+    stream = torch.cuda.current_stream()
+    api.set_stream(stream.cuda_stream)
+    eng = api.TracerEngine(hm)
+    solver = api.SSHSolver(hm, block=args.block)
+    eng.push_step_state()
+    eng.push_tracers()
+    L = api.lib()
+    sol = np.zeros_like(hm["d_eta"])
+
+    def one_step(ev=None):
+        sol[:] = 0.0
+        if ev:
+            ev[0].record(stream)
+        solver.solve(new_values=1, sol=sol)
+        if ev:
+            ev[1].record(stream)
+        eng.solve()
+        if ev:
+            ev[2].record(stream)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_step()
+    launches0 = L.fb200_kernel_launches()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    t_wall = time.time()
+    for k in range(args.steps):
+        one_step(evs[k])
+    barrier()
+    t_wall = time.time() - t_wall
+    sampler.stop_flag = True
+    sampler.join()
+    launches = L.fb200_kernel_launches() - launches0
+    ssh_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
+    tra_ms = sum(e[1].elapsed_time(e[2]) for e in evs)
+    tot_ms = evs[0][0].elapsed_time(evs[-1][2])
+    its, res = solver.info()
+
+    # ---- per-kernel timing pass (untimed for the headline; CUDA events around every launch)
+    api.profile(2)
+    for _ in range(2):
+        one_step()
+    torch.cuda.synchronize()
+    api.profile(0)
+    prof = api.profile_report()
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        host_arrays = [hm.arr(nm) for nm in STATE] + [hm.arr("tr_arr"), hm.arr("tr_arr_old"), hm.arr("ssh_values"),
+                                                      hm.arr("ssh_rhs"), sol]
+        pinned = pin(host_arrays)
+        h2d = sum(hm.arr(nm).nbytes for nm in STATE) + hm.arr("tr_arr").nbytes + hm.arr("tr_arr_old").nbytes \
+            + hm.arr("ssh_values").nbytes + 2 * 8 * n_own
+        d2h = hm.arr("tr_arr").nbytes + hm.arr("tr_arr_old").nbytes + 8 * n_own
+        tr_h, tro_h = hm.arr("tr_arr").copy(), hm.arr("tr_arr_old").copy()
+        pinned += pin([tr_h, tro_h])
+
+        def e2e_step():
+            sol[:] = 0.0
+            solver.solve(new_values=1, sol=sol)                    # H2D values, rhs, guess; D2H solution
+            eng.push_step_state()                                   # H2D velocities, thicknesses, mixing, fluxes
+            eng.solve_tracers_ale(tr_h, tro_h)                      # H2D tracers, step, D2H tracers
+
+        e2e_step()
+        ksteps = max(1, min(args.steps, 5))
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(ksteps):
+            e2e_step()
+        b.record(stream)
+        barrier()
+        e2e_ms = a.elapsed_time(b) / ksteps
+        unpin(pinned)
+        e2e = {"ms_per_step": e2e_ms, "steps": ksteps, "h2d": h2d, "d2h": d2h, "pinned_arrays": len(pinned)}
+
+    # ---- max over ranks
+    vals = torch.tensor([tra_ms, ssh_ms, tot_ms, e2e["ms_per_step"] if e2e else 0.0, float(units_per_step)],
+                        dtype=torch.float64, device="cuda")
+    if dist is not None:
+        mx = vals.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = vals.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        tra_ms, ssh_ms, tot_ms, e2e_ms = [float(x) for x in mx[:4]]
+        units_all = float(sm[4])
+    else:
+        e2e_ms = e2e["ms_per_step"] if e2e else 0.0
+        units_all = float(units_per_step)
+    return dict(rank=rank, world=world, hm=hm, info=info, reduced=reduced, units_all=units_all, tra_ms=tra_ms, ssh_ms=ssh_ms,
+                tot_ms=tot_ms, t_wall=t_wall, its=its, res=res, prof=prof, e2e=e2e, e2e_ms=e2e_ms, launches=launches,
+                clocks=sampler.result(), ntr=ntr, dist=dist)
+
+
+def cpu_reference(args, steps, warmup):
+    """The reference's CPU path on the host cores, on a bounded sample of the workload: tracer step = the oracle's C
+    restatement of solve_tracers_ale (serial: the reference parallelises over MPI ranks only, and neither MPI nor a
+    Fortran compiler exists here); SSH solve = the reference's OWN psolve.c + pARMS when oracle/_ref was built,
+    else the oracle's BiCGStab."""
+    from oracle import binding as ob
+    from tests import util
+    hm, info = build_workload(args.cpu_nodes, args.nl)
+    ntr = hm.ipar("num_tracers")
+    units = info["wet_node_layers"] * ntr
+    o = ob.TracerOracle(hm)
+    rp = hm["ssh_rowptr"]
+    n = hm.ipar("myDim_nod2D")
+    rp0, ci0 = (rp - rp[0]).astype(np.int32), (hm["ssh_colind"] - 1).astype(np.int32)
+    vals, rhs = hm["ssh_values"], hm["ssh_rhs"][:n].copy()
+    ref = None
+    kind = "port"                       # the headline metric (tracer step) is timed on the port; ssh_kind says what ran the SSH solve
+    if ob.ref_lib() is not None:
+        ref = ob.RefSolver(rp0, ci0, vals)
+    t_tr, t_ssh = 0.0, 0.0
+    for k in range(warmup + steps):
+        t0 = time.perf_counter()
+        if ref is not None:
+            ref.solve(rhs, vals, np.zeros(n), new_values=1)
+        else:
+            ob.ssh_solve(rp0, ci0, vals, rhs, np.zeros(n), pc_kind=1, block=1)
+        t1 = time.perf_counter()
+        o.step()
+        t2 = time.perf_counter()
+        if k >= warmup:
+            t_ssh += t1 - t0
+            t_tr += t2 - t1
+    sample = "band mesh %dx%d nl=%d: %d surface nodes, %d wet node-layers x %d tracers, %d steps; tracer step = serial C " \
+             "restatement (oracle), SSH = %s" % (info["nlon"], info["nlat"], args.nl, info["nod2D"], info["wet_node_layers"],
+                                                ntr, steps, "reference psolve.c+pARMS (oracle/_ref), 1 subdomain" if ref else "oracle BiCGStab")
+    return dict(value=units * steps / t_tr, unit=UNIT, cores=1, kind=kind, ssh_kind="reference" if ref else "port", sample=sample,
+                tracer_ms_per_step=1e3 * t_tr / steps, ssh_ms_per_step=1e3 * t_ssh / steps, ssh_rows=n,
+                ssh_us_per_row=1e6 * t_ssh / steps / n), info
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    workload = "synthetic lon/lat-band sphere (|lat|<=80, ~8%% land, ragged bathymetry), ~%d surface nodes/GPU x %d layers, " \
+               "2 tracers, MFCT+QR4C+FCT, zstar" % (args.nodes, args.nl - 1)
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cb, info = cpu_reference(args, max(1, args.steps), max(0, min(args.warmup, 1)))
+        line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": cb["tracer_ms_per_step"] + cb["ssh_ms_per_step"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": workload, "sample": cb["sample"]},
+                "ssh": {"ms_per_step": cb["ssh_ms_per_step"], "rows": cb["ssh_rows"], "us_per_row": cb["ssh_us_per_row"]},
+                "cpu_baseline": cb,
+                "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    r = run_b200(args)
+    if r["dist"] is not None:
+        r["dist"].barrier()
+    if rank != 0:
+        if r["dist"] is not None:
+            r["dist"].destroy_process_group()
+        return
+    info = r["info"]
+    K = args.steps
+    value = r["units_all"] * K / (r["tra_ms"] * 1e-3)
+    peak, peak_src = peaks()
+    # dominant kernel of the step
+    prof = r["prof"]
+    wet = info["wet_node_layers"]
+    rows = info["nod2D"]
+    dom = max(prof.items(), key=lambda kv: kv[1][1]) if prof else None
+    roof = None
+    if dom:
+        name, (cnt, ms) = dom
+        per = ALGO_BYTES.get(name)
+        bytes_launch = per * wet if per is not None else ALGO_BYTES_ROW.get(name, 0) * rows
+        avg_ms = ms / cnt
+        ach = bytes_launch / (avg_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
+                "avg_launch_ms": avg_ms, "share_of_step": ms / sum(v[1] for v in prof.values())}
+    kern = {k: {"launches": v[0], "ms": round(v[1], 4),
+                "GBps": round((ALGO_BYTES[k] * wet if k in ALGO_BYTES else ALGO_BYTES_ROW.get(k, 0) * rows) * v[0] / (v[1] * 1e-3) / 1e9, 1) if v[1] > 0 else None}
+            for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
+    step_bytes = 344.0 * wet * r["ntr"]                     # 344 B per (node, layer, tracer)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": r["world"], "steps": K, "warmup": args.warmup,
+            "ms_per_step": r["tot_ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": workload, "mesh": {k: info[k] for k in ("nlon", "nlat", "nl", "nod2D", "elem2D", "edge2D", "wet_node_layers")},
+                       "per_gpu": True, "reduced_for_host_memory": r["reduced"], "l2": "inputs larger than L2 (per-field >> 126 MB)",
+                       "parallelism": "1 domain per GPU" if r["world"] == 1 else "%d independent domains, no halo exchange (round 1)" % r["world"],
+                       "ssh_initial_guess": "zero every step", "setup_s": info["setup_s"]},
+            "tracer_ms_per_step": r["tra_ms"] / K,
+            "ssh": {"ms_per_step": r["ssh_ms"] / K, "iterations": r["its"], "scaled_residual": r["res"], "rows": rows,
+                    "ms_per_iteration": r["ssh_ms"] / K / max(1, r["its"])},
+            "step_roofline": {"algorithmic_GB_per_tracer_step": step_bytes / 1e9, "achieved_GBps": step_bytes / (r["tra_ms"] / K * 1e-3) / 1e9,
+                              "frac": step_bytes / (r["tra_ms"] / K * 1e-3) / 1e9 / peak},
+            "roofline": roof, "kernels": kern, "gpu_launches": int(r["launches"]), "clocks": r["clocks"],
+            "wall_s_timed_region": r["t_wall"]}
+    if r["e2e"]:
+        line["e2e"] = {"value": r["units_all"] / (r["e2e_ms"] * 1e-3), "unit": UNIT, "ms_per_step": r["e2e_ms"],
+                       "h2d_bytes_per_step": int(r["e2e"]["h2d"]), "d2h_bytes_per_step": int(r["e2e"]["d2h"]),
+                       "steps": r["e2e"]["steps"], "pinned_arrays": r["e2e"]["pinned_arrays"]}
+    if r["world"] == 1 and not args.no_cpu_baseline:
+        cb, _ = cpu_reference(args, 2, 0)
+        line["cpu_baseline"] = cb
+    print(json.dumps(line))
+    if r["dist"] is not None:
+        r["dist"].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
