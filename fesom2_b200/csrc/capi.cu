@@ -4,7 +4,7 @@
 #include <cstring>
 
 int fb_status_code(); const char* fb_status_msg(); void fb_clear_status();
-const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind);
+const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind, int* ncomp, int* comp);
 double ssh_last_ms();
 void prof_reset(); int prof_report(char* buf, int cap);
 
@@ -89,8 +89,8 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
     if (!c.committed) { fb_set_error(33, "fb200_push_step_state before fb200_init_commit"); return; }
     c.stream = fb_stream();
     const int L = c.nl - 1, nl = c.nl, N = c.N;
-    ctx_push_node_field(c, UV, L, c.E, c.U.p, 2, 0);
-    ctx_push_node_field(c, UV, L, c.E, c.V.p, 2, 1);
+    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 0, 2, 0);
+    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 1, 2, 1);
     ctx_push_node_field(c, helem, L, c.myE, c.helem.p);
     ctx_push_node_field(c, Wvel, nl, N, c.W.p);
     ctx_push_node_field(c, Wvel_e, nl, N, c.We.p);
@@ -153,17 +153,17 @@ void fb200_debug_fetch(const char* name, double* out) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(36, "fb200_debug_fetch before fb200_init_commit"); return; }
     c.stream = fb_stream();
-    int kind = 0;
+    int kind = 0, ncomp = 1, comp = 0;
     std::string s(name);
     const double* f = nullptr;
     int lev = c.nl - 1, cnt = c.N;
     if (s == "ttfAB") { f = c.Told.p; }
-    else f = tracer_debug_field(c, name, &kind);
+    else f = tracer_debug_field(c, name, &kind, &ncomp, &comp);
     if (!f) { fb_set_error(37, "fb200_debug_fetch: unknown field " + s); return; }
     if (s == "adf_v") lev = c.nl;
     if (kind == 1) cnt = c.myEd;
     if (kind == 2) cnt = c.Eall;
-    ctx_pull_node_field(c, f, lev, cnt, out);
+    ctx_pull_node_field(c, f, lev, cnt, out, ncomp, comp);
 }
 
 void fb200_finalize(void) { ctx_release(tctx()); }

@@ -18,10 +18,8 @@
 struct __align__(16) EdgeRec {      // one record per local edge, read by both endpoint nodes (64 B)
     int bn1, bn2;                   // tile bases of the two nodes          (see tile_base)
     int be1, be2;                   // tile bases of the two elements, be2 = -1 on a boundary edge
-    unsigned lev;                   // nu1 | nl1<<8 | nu2<<16 | nl2<<24   (nl* = nlevels-1; nu2 = nl2 = 0 without el2)
-    int pad;
+    unsigned long long m1, m2;      // level masks: bit nz set where the segment in element 1 / 2 carries a flux at level nz
     double dX1, dY1, dX2, dY2;      // edge_cross_dxdy(1:4)
-    double pad2;
 };
 struct __align__(16) EdgeHo {       // extra per-edge data of the high-order reconstruction (48 B)
     double dxa, dyr;                // edge_dxdy(1)*a, edge_dxdy(2)*r_earth  (a = r_earth * mean elem_cos)
@@ -82,6 +80,11 @@ struct TracerCtx {
     // static device data
     DevBuf<EdgeRec> edge; DevBuf<EdgeHo> edgeho;
     DevBuf<int> ne_slot;            // [Ntile][maxdeg][32]   (edge<<1)|second, -1 = none; ascending reference edge id
+    // per (node, incident-edge slot) copies of the edge data, [Ntile][maxdeg][32]: a warp of 32 consecutive nodes reads
+    // every item fully coalesced (the edge-indexed records would be a scattered 64-byte gather per lane)
+    DevBuf<int> ns_bo, ns_be1, ns_be2, ns_bed;   // tile bases: other node, element 1, element 2 (-1), edge (for adf_h)
+    DevBuf<unsigned long long> ns_m1, ns_m2;     // EdgeRec::m1, m2
+    DevBuf<double2> ns_d1, ns_d2;                // (dX1,dY1), (dX2,dY2)
     DevBuf<int> nie_slot;           // [Ntile][maxnie][32]   element id in nod_in_elem2D order, -1 = none
     DevBuf<int> el_nb;              // [3][Eall] node tile bases of element corners
     DevBuf<unsigned> el_lev;        // nu | nl<<8 per element (nl = nlevels-1)
@@ -92,12 +95,14 @@ struct TracerCtx {
     DevBuf<double> n_znb;           // zbar_n_bot
     DevBuf<double> area, areasvol;  // tiled (nlp levels)
     // per-step state, tiled
-    DevBuf<double> U, V, helem, W, We, Wi, hnode, hnode_new, Z3, zbar3, Kv, Ki, sl1, sl2, sl3, sw3d;
+    DevBuf<double2> UV;             // (u, v) per element-level, tiled
+    DevBuf<double> helem, W, We, Wi, hnode, hnode_new, Z3, zbar3, Kv, Ki, sl1, sl2, sl3, sw3d;
     DevBuf<double> heat_flux, water_flux, virtual_salt, relax_salt, real_salt_flux;   // (N)
     // tracers, tiled: [ntr] fields each
     DevBuf<double> T, Told;
     // work fields, tiled
-    DevBuf<double> txy_x, txy_y, trz, LO, adf_h, adf_v, fplus, fminus, tstar;
+    DevBuf<double2> txy, fpm;       // (tr_xy x, y) per element-level; (fct_plus, fct_minus) per node-level
+    DevBuf<double> trz, LO, adf_h, adf_v, tstar;
     // staging for host<->device transfers (reference layout)
     DevBuf<double> stage;
     cudaStream_t stream = nullptr;
@@ -112,8 +117,9 @@ void fb_set_stream(cudaStream_t s);
 // context.cu
 TracerCtx& tctx();
 void ctx_commit(TracerCtx& c);
-void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int count_ent, double* dev_tiled, int ncomp = 1, int comp = 0);
-void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host);
+// host (ncomp, lev_ref, ent) component comp  ->  tiled field with dncomp interleaved components, component dcomp
+void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int count_ent, double* dev_tiled, int ncomp = 1, int comp = 0, int dncomp = 1, int dcomp = 0);
+void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host, int dncomp = 1, int dcomp = 0);
 void ctx_release(TracerCtx& c);
 // tracer_kernels.cu
 void tracer_step_all(TracerCtx& c);

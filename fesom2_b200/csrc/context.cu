@@ -85,7 +85,7 @@ int prof_report(char* buf, int cap) {          // "name launches ms\n" per kerne
 // ---------------------------------------------------------------------------------------------------
 // restage kernels.  One block per tile of 32 entities.  src is the reference array (ncomp, lev_ref, ent).
 __global__ void __launch_bounds__(256) k_ref_to_tiled(const double* __restrict__ src, double* __restrict__ dst, int count_ent,
-                                                      int lev_ref, int nlp, int ncomp, int comp) {
+                                                      int lev_ref, int nlp, int ncomp, int comp, int dncomp, int dcomp) {
     extern __shared__ double sm[];                 // [nlp][33]
     const int tile = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int j = warp; j < TILE; j += 8) {
@@ -97,15 +97,15 @@ __global__ void __launch_bounds__(256) k_ref_to_tiled(const double* __restrict__
         }
     }
     __syncthreads();
-    double* out = dst + (size_t)tile * nlp * TILE;
-    for (int idx = threadIdx.x; idx < nlp * TILE; idx += 256) out[idx] = sm[(idx >> 5) * 33 + (idx & 31)];
+    double* out = dst + (size_t)tile * nlp * TILE * dncomp + dcomp;
+    for (int idx = threadIdx.x; idx < nlp * TILE; idx += 256) out[(size_t)idx * dncomp] = sm[(idx >> 5) * 33 + (idx & 31)];
 }
 __global__ void __launch_bounds__(256) k_tiled_to_ref(const double* __restrict__ src, double* __restrict__ dst, int count_ent,
-                                                      int lev_ref, int nlp) {
+                                                      int lev_ref, int nlp, int dncomp, int dcomp) {
     extern __shared__ double sm[];
     const int tile = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const double* in = src + (size_t)tile * nlp * TILE;
-    for (int idx = threadIdx.x; idx < nlp * TILE; idx += 256) sm[(idx >> 5) * 33 + (idx & 31)] = in[idx];
+    const double* in = src + (size_t)tile * nlp * TILE * dncomp + dcomp;
+    for (int idx = threadIdx.x; idx < nlp * TILE; idx += 256) sm[(idx >> 5) * 33 + (idx & 31)] = in[(size_t)idx * dncomp];
     __syncthreads();
     for (int j = warp; j < TILE; j += 8) {
         const int ent = tile * TILE + j;
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(256) k_tiled_to_ref(const double* __restrict__
 static void ensure_stage(TracerCtx& c, size_t count) { if (c.stage.n < count) c.stage.alloc(count); }
 
 // host (reference layout, (ncomp, lev_ref, count_ent)) -> device tiled field of component `comp`
-void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int count_ent, double* dev_tiled, int ncomp, int comp) {
+void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int count_ent, double* dev_tiled, int ncomp, int comp, int dncomp, int dcomp) {
     if (!fb_ok() || count_ent == 0) return;
     const size_t cnt = (size_t)ncomp * lev_ref * count_ent;
     if (comp == 0) {                                   // components of one array are pushed back to back: upload once
@@ -125,15 +125,15 @@ void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int coun
         CUDA_CHECK(cudaMemcpyAsync(c.stage.p, host, cnt * sizeof(double), cudaMemcpyHostToDevice, c.stream));
     }
     const int tiles = (count_ent + TILE - 1) / TILE;
-    k_ref_to_tiled<<<tiles, 256, (size_t)c.nlp * 33 * sizeof(double), c.stream>>>(c.stage.p, dev_tiled, count_ent, lev_ref, c.nlp, ncomp, comp);
+    k_ref_to_tiled<<<tiles, 256, (size_t)c.nlp * 33 * sizeof(double), c.stream>>>(c.stage.p, dev_tiled, count_ent, lev_ref, c.nlp, ncomp, comp, dncomp, dcomp);
     LAUNCH_CHECK();
 }
-void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host) {
+void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host, int dncomp, int dcomp) {
     if (!fb_ok() || count_ent == 0) return;
     const size_t cnt = (size_t)lev_ref * count_ent;
     ensure_stage(c, cnt);
     const int tiles = (count_ent + TILE - 1) / TILE;
-    k_tiled_to_ref<<<tiles, 256, (size_t)c.nlp * 33 * sizeof(double), c.stream>>>(dev_tiled, c.stage.p, count_ent, lev_ref, c.nlp);
+    k_tiled_to_ref<<<tiles, 256, (size_t)c.nlp * 33 * sizeof(double), c.stream>>>(dev_tiled, c.stage.p, count_ent, lev_ref, c.nlp, dncomp, dcomp);
     LAUNCH_CHECK();
     CUDA_CHECK(cudaMemcpyAsync(host, c.stage.p, cnt * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
     CUDA_CHECK(cudaStreamSynchronize(c.stream));
@@ -183,20 +183,18 @@ void ctx_commit(TracerCtx& c) {
         r.be1 = tile_base(t1 - 1, nlp); r.be2 = t2 > 0 ? tile_base(t2 - 1, nlp) : -1;
         const int nu1 = c.h_ulev[t1 - 1], nl1 = c.h_nlev[t1 - 1] - 1;
         const int nu2 = t2 > 0 ? c.h_ulev[t2 - 1] : 0, nl2 = t2 > 0 ? c.h_nlev[t2 - 1] - 1 : 0;
-        r.lev = pack4(nu1, nl1, nu2, nl2);
+        if (nlp > 63) { fb_set_error(16, "nl > 63 is not supported (64-bit level masks)"); return; }
         r.dX1 = c.h_ecd[4 * (size_t)e]; r.dY1 = c.h_ecd[4 * (size_t)e + 1]; r.dX2 = c.h_ecd[4 * (size_t)e + 2]; r.dY2 = c.h_ecd[4 * (size_t)e + 3];
         // the five level ranges of oce_adv_tra_hor.F90:129-209 must not overlap (they never do on a valid mesh);
         // the kernels evaluate them as a partition
         {
             const int nl12 = std::min(nl1, nl2), nu12 = std::max(nu1, nu2);
             for (int nz = 1; nz <= nlp; nz++) {
-                int m = 0;
-                m += (nz >= nu1 && nz <= nu12 - 1);
-                m += (nu2 > 0 && nz >= nu2 && nz <= nu12 - 1);
-                m += (nz >= nu12 && nz <= nl12);
-                m += (nz >= nl12 + 1 && nz <= nl1);
-                m += (nz >= nl12 + 1 && nz <= nl2);
-                if (m > 1) { fb_set_error(15, "edge with overlapping level ranges (disjoint element columns) is not supported"); return; }
+                const bool inA = nz >= nu1 && nz <= nu12 - 1, inB = nu2 > 0 && nz >= nu2 && nz <= nu12 - 1;
+                const bool inC = nz >= nu12 && nz <= nl12, inD = nz >= nl12 + 1 && nz <= nl1, inE = nz >= nl12 + 1 && nz <= nl2;
+                if ((int)inA + inB + inC + inD + inE > 1) { fb_set_error(15, "edge with overlapping level ranges (disjoint element columns) is not supported"); return; }
+                if (inA || inC || inD) r.m1 |= 1ull << nz;
+                if (inB || inC || inE) r.m2 |= 1ull << nz;
             }
         }
         EdgeHo& h = eh[e]; memset(&h, 0, sizeof(h));
@@ -223,6 +221,19 @@ void ctx_commit(TracerCtx& c) {
                 fill[n]++;
             }
         c.ne_slot.upload(slot);
+        const size_t ns = slot.size();
+        std::vector<int> bo(ns, 0), be1(ns, 0), be2(ns, -1), bed(ns, 0);
+        std::vector<unsigned long long> m1(ns, 0), m2(ns, 0);
+        std::vector<double2> d1(ns, make_double2(0., 0.)), d2(ns, make_double2(0., 0.));
+        for (size_t k = 0; k < ns; k++) {
+            if (slot[k] < 0) continue;
+            const int e = slot[k] >> 1, second = slot[k] & 1;
+            const EdgeRec& r = er[e];
+            bo[k] = second ? r.bn1 : r.bn2; be1[k] = r.be1; be2[k] = r.be2; bed[k] = tile_base(e, nlp); m1[k] = r.m1; m2[k] = r.m2;
+            d1[k] = make_double2(r.dX1, r.dY1); d2[k] = make_double2(r.dX2, r.dY2);
+        }
+        c.ns_bo.upload(bo); c.ns_be1.upload(be1); c.ns_be2.upload(be2); c.ns_bed.upload(bed); c.ns_m1.upload(m1); c.ns_m2.upload(m2);
+        c.ns_d1.upload(d1); c.ns_d2.upload(d2);
     }
     c.maxnie = 0; for (int n = 0; n < N; n++) c.maxnie = std::max(c.maxnie, c.h_nie_num[n]);
     {
@@ -237,8 +248,9 @@ void ctx_commit(TracerCtx& c) {
     // fields
     const size_t nf = (size_t)c.Ntiles * nlp * TILE, ef = (size_t)c.Etiles * nlp * TILE, df = (size_t)c.Edtiles * nlp * TILE;
     for (DevBuf<double>* b : {&c.area, &c.areasvol, &c.W, &c.We, &c.Wi, &c.hnode, &c.hnode_new, &c.Z3, &c.zbar3, &c.Kv, &c.Ki,
-                              &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.fplus, &c.fminus, &c.tstar}) b->alloc(nf);
-    for (DevBuf<double>* b : {&c.U, &c.V, &c.helem, &c.txy_x, &c.txy_y}) b->alloc(ef);
+                              &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar}) b->alloc(nf);
+    c.fpm.alloc(nf);
+    c.helem.alloc(ef); c.UV.alloc(ef); c.txy.alloc(ef);
     c.adf_h.alloc(df);
     c.T.alloc(nf * c.ntr); c.Told.alloc(nf * c.ntr);
     for (DevBuf<double>* b : {&c.heat_flux, &c.water_flux, &c.virtual_salt, &c.relax_salt, &c.real_salt_flux}) b->alloc(N);
@@ -251,9 +263,11 @@ void ctx_commit(TracerCtx& c) {
 void ctx_release(TracerCtx& c) {
     if (c.stream) { cudaStreamSynchronize(c.stream); }
     for (DevBuf<double>* b : {&c.area, &c.areasvol, &c.W, &c.We, &c.Wi, &c.hnode, &c.hnode_new, &c.Z3, &c.zbar3, &c.Kv, &c.Ki,
-                              &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.fplus, &c.fminus, &c.tstar, &c.U, &c.V,
-                              &c.helem, &c.txy_x, &c.txy_y, &c.adf_h, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
+                              &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar,
+                              &c.helem, &c.adf_h, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
                               &c.relax_salt, &c.real_salt_flux, &c.stage, &c.el_g, &c.el_area, &c.n_znb}) b->release();
+    c.ns_bo.release(); c.ns_be1.release(); c.ns_be2.release(); c.ns_bed.release(); c.ns_m1.release(); c.ns_m2.release(); c.ns_d1.release(); c.ns_d2.release();
+    c.UV.release(); c.txy.release(); c.fpm.release();
     c.edge.release(); c.edgeho.release(); c.ne_slot.release(); c.nie_slot.release(); c.el_nb.release(); c.el_lev.release();
     c.n_lev.release(); c.n_nbl.release();
     if (c.ev0) cudaEventDestroy(c.ev0);

@@ -36,6 +36,7 @@ struct Solver {
     DevBuf<unsigned> counter;
     int nblocks = 0;
     int last_its = 0; double last_res = 0.0;
+    SolverScal* h_scal = nullptr;            // pinned mirror of the device scalars (convergence polling)
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
@@ -60,17 +61,28 @@ __global__ void __launch_bounds__(SBS) k_scale_rows(int n, const int* __restrict
     for (int k = 0; k < w; k++) sval[base + (k << 5)] = (k < j1 - j0) ? vals[j0 + k] * s : 0.0;
 }
 
+// one SELL row times x.  Column indices and values of four entries are fetched before the dependent x gathers are
+// issued, so a thread keeps 8-12 loads in flight instead of one (the sum itself stays in entry order).
 __device__ __forceinline__ double sell_row(const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                            const double* __restrict__ x, int i) {
     const int s0 = sptr[i >> 5];
     const int w = (sptr[(i >> 5) + 1] - s0) >> 5;
     const int base = s0 + (i & 31);
     double s = 0.0;
-    for (int k = 0; k < w; k++) s += sval[base + (k << 5)] * x[scol[base + (k << 5)]];
+    int k = 0;
+    for (; k + 4 <= w; k += 4) {
+        const int o = base + (k << 5);
+        const int c0 = scol[o], c1 = scol[o + 32], c2 = scol[o + 64], c3 = scol[o + 96];
+        const double a0 = sval[o], a1 = sval[o + 32], a2 = sval[o + 64], a3 = sval[o + 96];
+        const double x0 = x[c0], x1 = x[c1], x2 = x[c2], x3 = x[c3];
+        s += a0 * x0; s += a1 * x1; s += a2 * x2; s += a3 * x3;
+    }
+    for (; k < w; k++) s += sval[base + (k << 5)] * x[scol[base + (k << 5)]];
     return s;
 }
 
-// deterministic two-value reduction: block partials -> last block sums them in order and calls `fin`
+// deterministic two-value reduction: block partials -> the last block to finish sums them in a fixed order with all
+// its threads (plain L2 loads after the fence; no floating-point atomics) and calls `fin`
 template <class Fin>
 __device__ __forceinline__ void reduce2(double a, double b, double* __restrict__ partial, unsigned* __restrict__ counter, int nblocks, Fin fin) {
     __shared__ double sa[SBS / 32], sb[SBS / 32];
@@ -88,12 +100,19 @@ __device__ __forceinline__ void reduce2(double a, double b, double* __restrict__
         last = (done == (unsigned)nblocks - 1);
     }
     __syncthreads();
-    if (last && threadIdx.x < 32) {
-        __threadfence();
-        double ta = 0.0, tb = 0.0;
-        for (int k = threadIdx.x; k < nblocks; k += 32) { ta += ((volatile double*)partial)[k]; tb += ((volatile double*)partial)[nblocks + k]; }
-        for (int o = 16; o > 0; o >>= 1) { ta += __shfl_down_sync(0xffffffffu, ta, o); tb += __shfl_down_sync(0xffffffffu, tb, o); }
-        if (threadIdx.x == 0) { *counter = 0; fin(ta, tb); }
+    if (!last) return;
+    __threadfence();
+    double ta = 0.0, tb = 0.0;
+    for (int k = threadIdx.x; k < nblocks; k += SBS) { ta += __ldcg(partial + k); tb += __ldcg(partial + nblocks + k); }
+    for (int o = 16; o > 0; o >>= 1) { ta += __shfl_down_sync(0xffffffffu, ta, o); tb += __shfl_down_sync(0xffffffffu, tb, o); }
+    __syncthreads();
+    if (lane == 0) { sa[warp] = ta; sb[warp] = tb; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ta = 0.0; tb = 0.0;
+        for (int w = 0; w < SBS / 32; w++) { ta += sa[w]; tb += sb[w]; }
+        *counter = 0;
+        fin(ta, tb);
     }
 }
 
@@ -309,8 +328,8 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     { ProfScope ps_("k_pc", st); k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
     int done = 0, launched = 0;
     const int poll = 8;
-    SolverScal* hs = nullptr;
-    CUDA_CHECK(cudaMallocHost(&hs, sizeof(SolverScal)));
+    if (!S.h_scal) CUDA_CHECK(cudaMallocHost(&S.h_scal, sizeof(SolverScal)));
+    SolverScal* hs = S.h_scal;
     while (!done && launched < S.maxits && fb_ok()) {
         for (int k = 0; k < poll && launched < S.maxits; k++, launched++) {
             { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
@@ -327,7 +346,6 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
         S.last_its = hs->its; S.last_res = sqrt(hs->omega);
         if (hs->its >= S.maxits && hs->omega > h.tol2) printf("ERROR: no convergence\n");   // bicgstab_ras.c:237-238
     }
-    cudaFreeHost(hs);
     CUDA_CHECK(cudaMemcpyAsync(sol, S.x.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaEventRecord(S.ev1, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
@@ -348,6 +366,7 @@ void psolver_final(void) {
         S->d_rp.release(); S->d_ci.release(); S->d_sptr.release(); S->d_scol.release(); S->scal.release(); S->counter.release();
         if (S->ev0) cudaEventDestroy(S->ev0);
         if (S->ev1) cudaEventDestroy(S->ev1);
+        if (S->h_scal) cudaFreeHost(S->h_scal);
         delete S;
     }
     g_solvers.clear();

@@ -14,37 +14,30 @@ struct KP {                       // kernel parameter block (by value)
     double dt, ph, pv, eps_ab, is_nonlinfs;
     int hor, ver, w_split, Redi, use_sw_pene, do_hor_diff, tracer_id, tr_num;
     const EdgeRec* edge; const EdgeHo* edgeho; const int* ne_slot; const int* nie_slot; const int* el_nb;
+    const int *ns_bo, *ns_be1, *ns_be2, *ns_bed; const unsigned long long *ns_m1, *ns_m2; const double2 *ns_d1, *ns_d2;
     const unsigned* el_lev; const double* el_g; const double* el_area; const unsigned* n_lev; const int* n_nbl; const double* n_znb;
-    const double *area, *areasvol, *U, *V, *helem, *W, *We, *Wi, *hnode, *hnode_new, *Z3, *zbar3, *Kv, *Ki, *sl1, *sl2, *sl3, *sw3d;
+    const double2* UV;              // (u, v) per element-level
+    const double *area, *areasvol, *helem, *W, *We, *Wi, *hnode, *hnode_new, *Z3, *zbar3, *Kv, *Ki, *sl1, *sl2, *sl3, *sw3d;
     const double *heat_flux, *water_flux, *virtual_salt, *relax_salt, *real_salt_flux;
     double *T, *Told, *T1;        // this tracer's fields; T1 = tracer 1 (bc_surface)
-    double *txy_x, *txy_y, *trz, *LO, *adf_h, *adf_v, *fplus, *fminus, *tstar;
+    double2 *txy, *fpm;            // (tr_xy(1), tr_xy(2)) per element-level; (fct_plus, fct_minus) per node-level
+    double *trz, *LO, *adf_h, *adf_v, *tstar;
 };
 
 __device__ __forceinline__ int tbase(int ent, int nlp) { return (ent >> 5) * (nlp * TILE) + (ent & 31); }
 #define AT(p, base, nz) (p)[(base) + (((nz) - 1) << 5)]          // 1-based level
 
-struct ELv { int nu1, nl1, nu2, nl2, nl12, nu12, lo, hi; };
-__device__ __forceinline__ ELv unpack_edge_levels(unsigned lev) {
-    ELv v; v.nu1 = lev & 255; v.nl1 = (lev >> 8) & 255; v.nu2 = (lev >> 16) & 255; v.nl2 = lev >> 24;
-    v.nl12 = min(v.nl1, v.nl2); v.nu12 = max(v.nu1, v.nu2);
-    v.lo = v.nu2 > 0 ? min(v.nu1, v.nu2) : v.nu1; v.hi = max(v.nl1, v.nl2);
-    return v;
-}
-// which of the ranges (A)-(E) of oce_adv_tra_hor.F90:129-209 holds nz: bit0 = segment of el(1), bit1 = segment of el(2)
-__device__ __forceinline__ int edge_segs(const ELv& v, int nz) {
-    const bool inA = nz >= v.nu1 && nz <= v.nu12 - 1;
-    const bool inB = v.nu2 > 0 && nz >= v.nu2 && nz <= v.nu12 - 1;
-    const bool inC = nz >= v.nu12 && nz <= v.nl12;
-    const bool inD = nz >= v.nl12 + 1 && nz <= v.nl1;
-    const bool inE = nz >= v.nl12 + 1 && nz <= v.nl2;
-    return ((inA | inC | inD) ? 1 : 0) | ((inB | inC | inE) ? 2 : 0);
+// Level masks of an edge: bit nz of m1 (m2) is set where the median-dual segment in element 1 (2) carries a flux at
+// level nz — the five ranges (A)-(E) of oce_adv_tra_hor.F90:129-209 evaluated once on the host (context.cu), so the
+// kernels test two bits instead of re-deriving the ranges for every (edge, level).
+__device__ __forceinline__ int mask_segs(unsigned long long m1, unsigned long long m2, int nz) {
+    return (int)((m1 >> nz) & 1ull) | ((int)((m2 >> nz) & 1ull) << 1);
 }
 // volume flux through the two median-dual segments of an edge, oce_adv_tra_hor.F90:139,157,176
-__device__ __forceinline__ double edge_vflux(const KP& p, const EdgeRec& r, int segs, int nz) {
+__device__ __forceinline__ double seg_vflux(const KP& p, int segs, int be1, int be2, double dX1, double dY1, double dX2, double dY2, int nz) {
     double c1 = 0.0, c2 = 0.0;
-    if (segs & 1) c1 = (-AT(p.V, r.be1, nz) * r.dX1 + AT(p.U, r.be1, nz) * r.dY1) * AT(p.helem, r.be1, nz);
-    if (segs & 2) c2 = (AT(p.V, r.be2, nz) * r.dX2 - AT(p.U, r.be2, nz) * r.dY2) * AT(p.helem, r.be2, nz);
+    if (segs & 1) { const double2 uv = AT(p.UV, be1, nz); c1 = (-uv.y * dX1 + uv.x * dY1) * AT(p.helem, be1, nz); }
+    if (segs & 2) { const double2 uv = AT(p.UV, be2, nz); c2 = (uv.y * dX2 - uv.x * dY2) * AT(p.helem, be2, nz); }
     if (segs == 3) return c1 + c2;
     return (segs & 1) ? c1 : c2;
 }
@@ -72,8 +65,7 @@ __global__ void LB(128) k_grad_elem(KP p, const double* __restrict__ ttf) {
     const int be = tbase(e, p.nlp);
     for (int nz = nu; nz <= nlm; nz++) {
         const double t1 = AT(ttf, b1, nz), t2 = AT(ttf, b2, nz), t3 = AT(ttf, b3, nz);
-        AT(p.txy_x, be, nz) = g1 * t1 + g2 * t2 + g3 * t3;
-        AT(p.txy_y, be, nz) = g4 * t1 + g5 * t2 + g6 * t3;
+        AT(p.txy, be, nz) = make_double2(g1 * t1 + g2 * t2 + g3 * t3, g4 * t1 + g5 * t2 + g6 * t3);
     }
 }
 
@@ -126,55 +118,77 @@ __device__ __forceinline__ double ver_cdiff(const KP& p, const double* __restric
     return -tv * w * ar;
 }
 
-// K3: low-order solution + vertical antidiffusive flux.  One thread per own node.
+// ---------------------------------------------------------------------------------------------------
+// Thread mapping of the node kernels: block = one tile of 32 consecutive nodes (threadIdx.x = lane = node) times
+// blockDim.y level rows; every thread owns LPT levels nz = threadIdx.y + 1 + q * blockDim.y of its node, so a warp
+// reads one coalesced 256-byte line per field and level, all loads of a thread are independent (no serial walk down
+// the column) and sums live in registers.  The per-(node, slot) tables ns_* are read once per thread and reused for
+// its LPT levels.
+#define LPT 3
+struct NodeCol { int n, b, nzmin, nzmax, nlmin; bool valid; };
+__device__ __forceinline__ NodeCol node_col(const KP& p) {
+    NodeCol c;
+    c.n = blockIdx.x * TILE + threadIdx.x;
+    c.valid = c.n < p.myN;
+    c.b = blockIdx.x * (p.nlp * TILE) + threadIdx.x;
+    const unsigned lv = c.valid ? p.n_lev[c.n] : 0u;
+    c.nzmin = lv & 255; c.nzmax = (lv >> 8) & 255; c.nlmin = (lv >> 16) & 255;
+    return c;
+}
+
+// K3: low-order solution + vertical antidiffusive flux.
 //   fct_LO  : oce_adv_tra_driver.F90:83-122 (adv_tra_hor_upw1 + edge scatter + adv_tra_ver_upw1 + column update)
-//   adf_v   : oce_adv_tra_driver.F90:163-179 with init_zero=.false.  (HO(ttfAB, W) - LO(ttf, W))
-// dynamic smem: acc[nlp][blockDim]
-__global__ void LB(128) k_lo(KP p) {
-    extern __shared__ double acc[];
-    const int tid = threadIdx.x, BS = blockDim.x;
-    const int n = blockIdx.x * BS + tid;
-    const bool valid = n < p.myN;
-    for (int k = 0; k < p.nlp; k++) acc[k * BS + tid] = 0.0;
-    if (!valid) return;
-    const int b = tbase(n, p.nlp);
-    const unsigned lv = p.n_lev[n];
-    const int nzmin = lv & 255, nzmax = (lv >> 8) & 255;
+//   adf_v   : oce_adv_tra_driver.F90:163-179 with init_zero=.false.  (HO(ttfAB, W) - LO(ttf, W)); adf_v(nzmax) is
+//             0 - 0 for every scheme and is never written (the buffer is zero-initialised)
+__global__ void LB(512) k_lo(KP p) {
+    const NodeCol c = node_col(p);
+    if (!c.valid) return;
     const double* __restrict__ T = p.T;
-    const int* slot = p.ne_slot + (size_t)(n >> 5) * p.maxdeg * TILE + (n & 31);
+    int nz[LPT]; bool act[LPT]; double acc[LPT], tn[LPT];
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        nz[q] = threadIdx.y + 1 + q * blockDim.y;
+        act[q] = nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
+        acc[q] = 0.0;
+        tn[q] = act[q] ? AT(T, c.b, nz[q]) : 0.0;
+    }
+    if (!(act[0] | act[1] | act[2])) return;
+    const size_t sbase = (size_t)blockIdx.x * p.maxdeg * TILE + threadIdx.x;
     for (int j = 0; j < p.maxdeg; j++) {
-        const int s = slot[j * TILE];
+        const size_t k = sbase + (size_t)j * TILE;
+        const int s = p.ne_slot[k];
         if (s < 0) break;
-        const EdgeRec r = p.edge[s >> 1];
         const bool second = s & 1;
-        const ELv v = unpack_edge_levels(r.lev);
-        for (int nz = v.lo; nz <= v.hi; nz++) {
-            const int segs = edge_segs(v, nz);
+        const int bo = p.ns_bo[k], be1 = p.ns_be1[k], be2 = p.ns_be2[k];
+        const unsigned long long m1 = p.ns_m1[k], m2 = p.ns_m2[k];
+        const double2 d1 = p.ns_d1[k], d2 = p.ns_d2[k];
+#pragma unroll
+        for (int q = 0; q < LPT; q++) {
+            if (!act[q]) continue;
+            const int segs = mask_segs(m1, m2, nz[q]);
             if (!segs) continue;
-            const double vflux = edge_vflux(p, r, segs, nz);
-            const double f = upw1_flux(AT(T, r.bn1, nz), AT(T, r.bn2, nz), vflux);
-            double a = acc[(nz - 1) * BS + tid];
-            a = second ? a - f : a + f;
-            acc[(nz - 1) * BS + tid] = a;
+            const double vflux = seg_vflux(p, segs, be1, be2, d1.x, d1.y, d2.x, d2.y, nz[q]);
+            const double to = AT(T, bo, nz[q]);
+            const double f = second ? upw1_flux(to, tn[q], vflux) : upw1_flux(tn[q], to, vflux);
+            acc[q] = second ? acc[q] - f : acc[q] + f;
         }
     }
     const double* __restrict__ Wlo = p.We;                         // explicit part for the LO solution
     const double* __restrict__ Wad = p.w_split ? p.W : p.We;       // LO part of the antidiffusive flux: full W (:131)
-    double fv = ver_upw1(T, Wlo, p.area, b, nzmin, nzmin, nzmax);
-    for (int nz = nzmin; nz <= nzmax - 1; nz++) {
-        const double fvn = ver_upw1(T, Wlo, p.area, b, nz + 1, nzmin, nzmax);
-        const double lo = (AT(T, b, nz) * AT(p.hnode, b, nz) + (acc[(nz - 1) * BS + tid] + (fv - fvn)) * p.dt / AT(p.areasvol, b, nz)) / AT(p.hnode_new, b, nz);
-        AT(p.LO, b, nz) = lo;
-        fv = fvn;
-    }
     const double* __restrict__ TAB = p.Told;
-    for (int nz = nzmin; nz <= nzmax; nz++) {
-        const double flo = ver_upw1(T, Wad, p.area, b, nz, nzmin, nzmax);
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        if (!act[q]) continue;
+        const int z = nz[q];
+        const double fv = ver_upw1(T, Wlo, p.area, c.b, z, c.nzmin, c.nzmax);
+        const double fvn = ver_upw1(T, Wlo, p.area, c.b, z + 1, c.nzmin, c.nzmax);
+        AT(p.LO, c.b, z) = (tn[q] * AT(p.hnode, c.b, z) + (acc[q] + (fv - fvn)) * p.dt / AT(p.areasvol, c.b, z)) / AT(p.hnode_new, c.b, z);
+        const double flo = ver_upw1(T, Wad, p.area, c.b, z, c.nzmin, c.nzmax);
         double ho;
-        if (p.ver == 0) ho = ver_qr4c(p, TAB, p.W, b, nz, nzmin, nzmax) - flo;
-        else if (p.ver == 1) ho = (nz == nzmax) ? flo : ver_cdiff(p, TAB, p.W, b, nz, nzmin) - flo;
-        else ho = ver_upw1(TAB, p.W, p.area, b, nz, nzmin, nzmax) - flo;
-        AT(p.adf_v, b, nz) = ho;
+        if (p.ver == 0) ho = ver_qr4c(p, TAB, p.W, c.b, z, c.nzmin, c.nzmax) - flo;
+        else if (p.ver == 1) ho = ver_cdiff(p, TAB, p.W, c.b, z, c.nzmin) - flo;
+        else ho = ver_upw1(TAB, p.W, p.area, c.b, z, c.nzmin, c.nzmax) - flo;
+        AT(p.adf_v, c.b, z) = ho;
     }
 }
 
@@ -235,44 +249,52 @@ __global__ void LB(64) k_vert_impl(KP p, double* __restrict__ ttf, const double*
 
 // ---------------------------------------------------------------------------------------------------
 // area-weighted mean of the elemental gradients around a node (fill_up_dn_grad fallback, oce_muscl_adv.F90:313-328)
-__device__ __noinline__ void node_mean_grad(const KP& p, int node, int nz, double& gx, double& gy) {
+__device__ __noinline__ void node_mean_grad(const int* __restrict__ nie_slot, int maxnie, const unsigned* __restrict__ el_lev,
+                                            const double* __restrict__ el_area, const double2* __restrict__ txy,
+                                            int nlp, int node, int nz, double& gx, double& gy) {
     double tvol = 0.0, tx = 0.0, ty = 0.0;
-    const int* slot = p.nie_slot + (size_t)(node >> 5) * p.maxnie * TILE + (node & 31);
-    for (int k = 0; k < p.maxnie; k++) {
+    const int* slot = nie_slot + (size_t)(node >> 5) * maxnie * TILE + (node & 31);
+    for (int k = 0; k < maxnie; k++) {
         const int e = slot[k * TILE];
         if (e < 0) break;
-        const unsigned lv = p.el_lev[e];
+        const unsigned lv = el_lev[e];
         const int nu = lv & 255, nlm = (lv >> 8) & 255;
         if (nlm < nz || nz < nu) continue;
-        const double ar = p.el_area[e];
-        const int be = tbase(e, p.nlp);
+        const double ar = el_area[e];
+        const int be = tbase(e, nlp);
+        const double2 g = AT(txy, be, nz);
         tvol = tvol + ar;
-        tx = tx + AT(p.txy_x, be, nz) * ar;
-        ty = ty + AT(p.txy_y, be, nz) * ar;
+        tx = tx + g.x * ar;
+        ty = ty + g.y * ar;
     }
     gx = tx / tvol; gy = ty / tvol;
 }
 
-// K4: high-order horizontal flux minus low-order flux = antidiffusive flux adf_h.  One thread per own edge.
+// K4: high-order horizontal flux minus low-order flux = antidiffusive flux adf_h.  Block = one tile of 32 edges
+// times blockDim.y level rows, LPT levels per thread (same mapping as the node kernels).
 //   adv_tra_hor_mfct / _muscl / _upw1 with init_zero=.false. (oce_adv_tra_hor.F90:215-733) on ttfAB,
 //   the input flux being adv_tra_hor_upw1(ttf) (oce_adv_tra_driver.F90:83,142-149); the gradients of
-//   fill_up_dn_grad (oce_muscl_adv.F90:285-447) are gathered from txy_x/txy_y instead of being stored.
-__global__ void LB(128) k_ho_edge(KP p) {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+//   fill_up_dn_grad (oce_muscl_adv.F90:285-447) are gathered from txy instead of being stored.
+__global__ void __launch_bounds__(512, 2) k_ho_edge(KP p) {
+    const int e = blockIdx.x * TILE + threadIdx.x;
     if (e >= p.myEd) return;
     const EdgeRec r = p.edge[e];
+    const unsigned long long many = r.m1 | r.m2;
+    if ((many >> (threadIdx.y + 1)) == 0ull) return;                 // no flux-carrying level at or below this thread's first level
     const EdgeHo h = p.edgeho[e];
-    const ELv v = unpack_edge_levels(r.lev);
-    const int be = tbase(e, p.nlp);
+    const int be = blockIdx.x * (p.nlp * TILE) + threadIdx.x;
     const int sh_lo = h.shared & 255, sh_hi = (h.shared >> 8) & 255;
     const bool good = (h.shared >> 16) & 1;
     const int nbl1 = p.n_nbl[h.n1], nbl2 = p.n_nbl[h.n2];
     const double* __restrict__ T = p.T;
     const double* __restrict__ A = p.Told;
-    for (int nz = v.lo; nz <= v.hi; nz++) {
-        const int segs = edge_segs(v, nz);
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        const int nz = threadIdx.y + 1 + q * blockDim.y;
+        if (nz > 63) continue;
+        const int segs = mask_segs(r.m1, r.m2, nz);
         if (!segs) continue;
-        const double vflux = edge_vflux(p, r, segs, nz);
+        const double vflux = seg_vflux(p, segs, r.be1, r.be2, r.dX1, r.dY1, r.dX2, r.dY2, nz);
         const double flo = upw1_flux(AT(T, r.bn1, nz), AT(T, r.bn2, nz), vflux);
         const double a1 = AT(A, r.bn1, nz), a2 = AT(A, r.bn2, nz);
         double fho;
@@ -280,11 +302,11 @@ __global__ void LB(128) k_ho_edge(KP p) {
         else {
             double g1, g2, g3, g4;         // edge_up_dn_grad(1:4): x up, x down, y up, y down
             if (good && nz >= sh_lo && nz <= sh_hi - 1) {
-                g1 = AT(p.txy_x, h.bup, nz); g2 = AT(p.txy_x, h.bdn, nz);
-                g3 = AT(p.txy_y, h.bup, nz); g4 = AT(p.txy_y, h.bdn, nz);
+                const double2 gu = AT(p.txy, h.bup, nz), gd = AT(p.txy, h.bdn, nz);
+                g1 = gu.x; g2 = gd.x; g3 = gu.y; g4 = gd.y;
             } else {
-                node_mean_grad(p, h.n1, nz, g1, g3);
-                node_mean_grad(p, h.n2, nz, g2, g4);
+                node_mean_grad(p.nie_slot, p.maxnie, p.el_lev, p.el_area, p.txy, p.nlp, h.n1, nz, g1, g3);
+                node_mean_grad(p.nie_slot, p.maxnie, p.el_lev, p.el_area, p.txy, p.nlp, h.n2, nz, g2, g4);
             }
             double Tmean2 = a2 - (2.0 * (a2 - a1) + h.dxa * g2 + h.dyr * g4) / 6.0;
             double Tmean1 = a1 + (2.0 * (a2 - a1) + h.dxa * g1 + h.dyr * g3) / 6.0;
@@ -301,67 +323,79 @@ __global__ void LB(128) k_ho_edge(KP p) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K5: Zalesak limiter, parts a1-a3 and b1-b2 of oce_tra_adv_fct (oce_adv_tra_fct.F90:93-276) for one own node
-// per thread.  The element min/max pass (a2) is folded into the node pass: the bound of node n at level nz is
-// the max/min over n and over every edge neighbour m whose edge has a wet adjacent element at nz — the same set
-// of values the reference reaches through UV_rhs(1:2,nz,nod_in_elem2D(:,n)); "-bignumber/+bignumber" enter
-// wherever a surrounding element is already below its bottom (nz >= nlevels_nod2D_min).
-// dynamic smem: pp, pm, mx, mn  [4][nlp][BS]
-__global__ void LB(64) k_fct_bounds(KP p) {
+// K5: Zalesak limiter, parts a1-a3 and b1-b2 of oce_tra_adv_fct (oce_adv_tra_fct.F90:93-276).  Node-kernel
+// mapping (tile x level rows, LPT levels per thread).  The element min/max pass (a2) is folded into the node pass:
+// the bound of node n at level nz is the max/min over n and over every edge neighbour m whose edge has a wet
+// adjacent element at nz — the same set of values the reference reaches through
+// UV_rhs(1:2,nz,nod_in_elem2D(:,n)); "-bignumber/+bignumber" enter wherever a surrounding element is already below
+// its bottom (nz >= nlevels_nod2D_min).  The vertical 3-point max/min (a3, vlimit=1) goes through shared memory.
+// dynamic smem: mx, mn  [2][nlp][32]
+__global__ void LB(512) k_fct_bounds(KP p) {
     extern __shared__ double sm[];
-    const int tid = threadIdx.x, BS = blockDim.x;
-    double* pp = sm; double* pm = sm + (size_t)p.nlp * BS; double* mx = pm + (size_t)p.nlp * BS; double* mn = mx + (size_t)p.nlp * BS;
-    const int n = blockIdx.x * BS + tid;
-    if (n >= p.myN) return;
+    double* smx = sm; double* smn = sm + (size_t)p.nlp * TILE;
+    const NodeCol c = node_col(p);
     const double flux_eps = 1e-16, bignumber = 1e3;
-    const int b = tbase(n, p.nlp);
-    const unsigned lv = p.n_lev[n];
-    const int nzmin = lv & 255, nzmax = (lv >> 8) & 255, nlmin = (lv >> 16) & 255;
     const double* __restrict__ T = p.T;
     const double* __restrict__ LO = p.LO;
-    for (int nz = nzmin; nz <= nzmax - 1; nz++) {
-        const double av = AT(p.adf_v, b, nz), avn = AT(p.adf_v, b, nz + 1);
-        pp[(nz - 1) * BS + tid] = fmax(0.0, av) + fmax(0.0, -avn);          // :235-236
-        pm[(nz - 1) * BS + tid] = fmin(0.0, av) + fmin(0.0, -avn);
-        const double lo = AT(LO, b, nz), t = AT(T, b, nz);
-        double M = fmax(lo, t), m = fmin(lo, t);                             // a1 :99-100
-        if (nz >= nlmin) { M = fmax(M, -bignumber); m = fmin(m, bignumber); }   // a2 :116-121
-        mx[(nz - 1) * BS + tid] = M; mn[(nz - 1) * BS + tid] = m;
+    int nz[LPT]; bool act[LPT]; double pp[LPT], pm[LPT], mx[LPT], mn[LPT], lo[LPT];
+    bool any = false;
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        nz[q] = threadIdx.y + 1 + q * blockDim.y;
+        act[q] = c.valid && nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
+        pp[q] = pm[q] = mx[q] = mn[q] = lo[q] = 0.0;
+        if (!act[q]) continue;
+        any = true;
+        const double av = AT(p.adf_v, c.b, nz[q]), avn = AT(p.adf_v, c.b, nz[q] + 1);
+        pp[q] = fmax(0.0, av) + fmax(0.0, -avn);                              // :235-236
+        pm[q] = fmin(0.0, av) + fmin(0.0, -avn);
+        lo[q] = AT(LO, c.b, nz[q]);
+        const double t = AT(T, c.b, nz[q]);
+        double M = fmax(lo[q], t), m = fmin(lo[q], t);                        // a1 :99-100
+        if (nz[q] >= c.nlmin) { M = fmax(M, -bignumber); m = fmin(m, bignumber); }   // a2 :116-121
+        mx[q] = M; mn[q] = m;
     }
-    const int* slot = p.ne_slot + (size_t)(n >> 5) * p.maxdeg * TILE + (n & 31);
-    for (int j = 0; j < p.maxdeg; j++) {
-        const int s = slot[j * TILE];
-        if (s < 0) break;
-        const int e = s >> 1;
-        const bool second = s & 1;
-        const EdgeRec r = p.edge[e];
-        const ELv v = unpack_edge_levels(r.lev);
-        const int be = tbase(e, p.nlp);
-        const int bo = second ? r.bn1 : r.bn2;
-        for (int nz = v.lo; nz <= v.hi; nz++) {
-            double f = AT(p.adf_h, be, nz);
-            if (second) f = -f;
-            pp[(nz - 1) * BS + tid] = pp[(nz - 1) * BS + tid] + fmax(0.0, f);      // b1 :258-261
-            pm[(nz - 1) * BS + tid] = pm[(nz - 1) * BS + tid] + fmin(0.0, f);
-            if (edge_segs(v, nz)) {
-                const double lo = AT(LO, bo, nz), t = AT(T, bo, nz);
-                mx[(nz - 1) * BS + tid] = fmax(mx[(nz - 1) * BS + tid], fmax(lo, t));
-                mn[(nz - 1) * BS + tid] = fmin(mn[(nz - 1) * BS + tid], fmin(lo, t));
+    if (any) {
+        const size_t sbase = (size_t)blockIdx.x * p.maxdeg * TILE + threadIdx.x;
+        for (int j = 0; j < p.maxdeg; j++) {
+            const size_t k = sbase + (size_t)j * TILE;
+            const int s = p.ne_slot[k];
+            if (s < 0) break;
+            const bool second = s & 1;
+            const int bo = p.ns_bo[k], bed = p.ns_bed[k];
+            const unsigned long long many = p.ns_m1[k] | p.ns_m2[k];
+#pragma unroll
+            for (int q = 0; q < LPT; q++) {
+                if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
+                double f = AT(p.adf_h, bed, nz[q]);
+                if (second) f = -f;
+                pp[q] = pp[q] + fmax(0.0, f);                                  // b1 :258-261
+                pm[q] = pm[q] + fmin(0.0, f);
+                const double lo_o = AT(LO, bo, nz[q]), t_o = AT(T, bo, nz[q]);
+                mx[q] = fmax(mx[q], fmax(lo_o, t_o));
+                mn[q] = fmin(mn[q], fmin(lo_o, t_o));
             }
         }
+#pragma unroll
+        for (int q = 0; q < LPT; q++)
+            if (act[q]) { smx[(nz[q] - 1) * TILE + threadIdx.x] = mx[q]; smn[(nz[q] - 1) * TILE + threadIdx.x] = mn[q]; }
     }
-    for (int nz = nzmin; nz <= nzmax - 1; nz++) {
-        double qmax = mx[(nz - 1) * BS + tid], qmin = mn[(nz - 1) * BS + tid];
-        if (nz > nzmin && nz < nzmax - 1) {                                  // a3, vlimit=1 :153-156
-            qmax = fmax(fmax(mx[(nz - 2) * BS + tid], qmax), mx[nz * BS + tid]);
-            qmin = fmin(fmin(mn[(nz - 2) * BS + tid], qmin), mn[nz * BS + tid]);
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        if (!act[q]) continue;
+        const int z = nz[q];
+        double qmax = mx[q], qmin = mn[q];
+        if (z > c.nzmin && z < c.nzmax - 1) {                                  // a3, vlimit=1 :153-156
+            qmax = fmax(fmax(smx[(z - 2) * TILE + threadIdx.x], qmax), smx[z * TILE + threadIdx.x]);
+            qmin = fmin(fmin(smn[(z - 2) * TILE + threadIdx.x], qmin), smn[z * TILE + threadIdx.x]);
         }
-        const double lo = AT(LO, b, nz), asv = AT(p.areasvol, b, nz);
-        qmax = qmax - lo; qmin = qmin - lo;
-        double flux = pp[(nz - 1) * BS + tid] * p.dt / asv + flux_eps;       // b2 :271-274
-        AT(p.fplus, b, nz) = fmin(1.0, qmax / flux);
-        flux = pm[(nz - 1) * BS + tid] * p.dt / asv - flux_eps;
-        AT(p.fminus, b, nz) = fmin(1.0, qmin / flux);
+        const double asv = AT(p.areasvol, c.b, z);
+        qmax = qmax - lo[q]; qmin = qmin - lo[q];
+        double flux = pp[q] * p.dt / asv + flux_eps;                           // b2 :271-274
+        const double rp = fmin(1.0, qmax / flux);
+        flux = pm[q] * p.dt / asv - flux_eps;
+        AT(p.fpm, c.b, z) = make_double2(rp, fmin(1.0, qmin / flux));
     }
 }
 
@@ -370,197 +404,255 @@ __device__ __forceinline__ double limited_fv(const KP& p, int b, int nz, int nzm
     const double flux = AT(p.adf_v, b, nz);
     if (nz == nzmax) return flux;
     double ae = 1.0;
+    const double2 f0 = AT(p.fpm, b, nz);                   // (fct_plus, fct_minus)
     if (nz == nzmin) {
-        if (flux >= 0.0) ae = fmin(ae, AT(p.fplus, b, nz)); else ae = fmin(ae, AT(p.fminus, b, nz));
+        if (flux >= 0.0) ae = fmin(ae, f0.x); else ae = fmin(ae, f0.y);
     } else {
-        if (flux >= 0.0) { ae = fmin(ae, AT(p.fminus, b, nz - 1)); ae = fmin(ae, AT(p.fplus, b, nz)); }
-        else { ae = fmin(ae, AT(p.fplus, b, nz - 1)); ae = fmin(ae, AT(p.fminus, b, nz)); }
+        const double2 fm1 = AT(p.fpm, b, nz - 1);
+        if (flux >= 0.0) { ae = fmin(ae, fm1.y); ae = fmin(ae, f0.x); }
+        else { ae = fmin(ae, fm1.x); ae = fmin(ae, f0.y); }
     }
     return ae * flux;
 }
 
 // K7a: b3 limiting + oce_tra_adv_flux2dtracer (oce_adv_tra_driver.F90:223-268) + del_ttf assembly
-// (oce_ale_tracer.F90:240) + diff_part_hor_redi (:934-1077) + T* update (:294-305).  One thread per own node.
-// Writes tstar; tr_arr_old = tr_arr is done by the caller for all entries.  dynamic smem: acc[nlp][BS]
-__global__ void LB(128) k_update(KP p) {
-    extern __shared__ double acc[];
-    const int tid = threadIdx.x, BS = blockDim.x;
-    const int n = blockIdx.x * BS + tid;
-    for (int k = 0; k < p.nlp; k++) acc[k * BS + tid] = 0.0;
-    if (n >= p.myN) return;
-    const int b = tbase(n, p.nlp);
-    const unsigned lv = p.n_lev[n];
-    const int nzmin = lv & 255, nzmax = (lv >> 8) & 255;
+// (oce_ale_tracer.F90:240) + diff_part_hor_redi (:934-1077) + T* update (:294-305).  Node-kernel mapping.
+// Writes tstar; tr_arr_old = tr_arr is done by the caller for all entries.
+__global__ void LB(512) k_update(KP p) {
+    const NodeCol c = node_col(p);
+    if (!c.valid) return;
     const double* __restrict__ T = p.T;
-    const int* slot = p.ne_slot + (size_t)(n >> 5) * p.maxdeg * TILE + (n & 31);
+    int nz[LPT]; bool act[LPT]; double acc[LPT], fp[LPT], fm[LPT], asv[LPT];
+    bool any = false;
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        nz[q] = threadIdx.y + 1 + q * blockDim.y;
+        act[q] = nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
+        acc[q] = 0.0; fp[q] = fm[q] = 0.0; asv[q] = 1.0;
+        if (!act[q]) continue;
+        any = true;
+        { const double2 f = AT(p.fpm, c.b, nz[q]); fp[q] = f.x; fm[q] = f.y; }
+        asv[q] = AT(p.areasvol, c.b, nz[q]);
+    }
+    if (!any) return;
+    const size_t sbase = (size_t)blockIdx.x * p.maxdeg * TILE + threadIdx.x;
     for (int j = 0; j < p.maxdeg; j++) {                                     // dttf_h
-        const int s = slot[j * TILE];
+        const size_t k = sbase + (size_t)j * TILE;
+        const int s = p.ne_slot[k];
         if (s < 0) break;
-        const int e = s >> 1;
         const bool second = s & 1;
-        const EdgeRec r = p.edge[e];
-        const ELv v = unpack_edge_levels(r.lev);
-        const int be = tbase(e, p.nlp);
-        for (int nz = v.lo; nz <= v.hi; nz++) {
-            const double flux = AT(p.adf_h, be, nz);
+        const int bo = p.ns_bo[k], bed = p.ns_bed[k];
+        const unsigned long long many = p.ns_m1[k] | p.ns_m2[k];
+#pragma unroll
+        for (int q = 0; q < LPT; q++) {
+            if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
+            const double flux = AT(p.adf_h, bed, nz[q]);
+            const double2 fo = AT(p.fpm, bo, nz[q]);
+            const double fpo = fo.x, fmo = fo.y;
+            const double fp1 = second ? fpo : fp[q], fm1 = second ? fmo : fm[q];     // factors of edge node 1 / node 2
+            const double fp2 = second ? fp[q] : fpo, fm2 = second ? fm[q] : fmo;
             double ae = 1.0;
-            if (flux >= 0.0) { ae = fmin(ae, AT(p.fplus, r.bn1, nz)); ae = fmin(ae, AT(p.fminus, r.bn2, nz)); }
-            else { ae = fmin(ae, AT(p.fminus, r.bn1, nz)); ae = fmin(ae, AT(p.fplus, r.bn2, nz)); }
+            if (flux >= 0.0) { ae = fmin(ae, fp1); ae = fmin(ae, fm2); }
+            else { ae = fmin(ae, fm1); ae = fmin(ae, fp2); }
             const double fl = ae * flux;
-            const double d = fl * p.dt / AT(p.areasvol, b, nz);
-            double a = acc[(nz - 1) * BS + tid];
-            a = second ? a - d : a + d;
-            acc[(nz - 1) * BS + tid] = a;
+            const double d = fl * p.dt / asv[q];
+            acc[q] = second ? acc[q] - d : acc[q] + d;
         }
     }
-    {                                                                         // dttf_v, then del_ttf = dttf_h + dttf_v
-        double fv = limited_fv(p, b, nzmin, nzmin, nzmax);
-        for (int nz = nzmin; nz <= nzmax - 1; nz++) {
-            const double fvn = limited_fv(p, b, nz + 1, nzmin, nzmax);
-            double dv = 0.0 - AT(T, b, nz) * AT(p.hnode, b, nz) + AT(p.LO, b, nz) * AT(p.hnode_new, b, nz);
-            dv = dv + (fv - fvn) * p.dt / AT(p.areasvol, b, nz);
-            acc[(nz - 1) * BS + tid] = acc[(nz - 1) * BS + tid] + dv;
-            fv = fvn;
-        }
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {                                          // dttf_v, then del_ttf = dttf_h + dttf_v
+        if (!act[q]) continue;
+        const int z = nz[q];
+        const double fv = limited_fv(p, c.b, z, c.nzmin, c.nzmax);
+        const double fvn = limited_fv(p, c.b, z + 1, c.nzmin, c.nzmax);
+        double dv = 0.0 - AT(T, c.b, z) * AT(p.hnode, c.b, z) + AT(p.LO, c.b, z) * AT(p.hnode_new, c.b, z);
+        dv = dv + (fv - fvn) * p.dt / asv[q];
+        acc[q] = acc[q] + dv;
     }
     if (p.do_hor_diff) {
         const double isredi = p.Redi ? 1.0 : 0.0;
         for (int j = 0; j < p.maxdeg; j++) {
-            const int s = slot[j * TILE];
+            const size_t k = sbase + (size_t)j * TILE;
+            const int s = p.ne_slot[k];
             if (s < 0) break;
             const bool second = s & 1;
-            const EdgeRec r = p.edge[s >> 1];
-            const ELv v = unpack_edge_levels(r.lev);
-            for (int nz = v.lo; nz <= v.hi; nz++) {
-                const int segs = edge_segs(v, nz);
+            const int bo = p.ns_bo[k], be1 = p.ns_be1[k], be2 = p.ns_be2[k];
+            const int bn1 = second ? bo : c.b, bn2 = second ? c.b : bo;
+            const unsigned long long m1 = p.ns_m1[k], m2 = p.ns_m2[k];
+            const double2 d1 = p.ns_d1[k], d2 = p.ns_d2[k];
+#pragma unroll
+            for (int q = 0; q < LPT; q++) {
+                if (!act[q]) continue;
+                const int z = nz[q];
+                const int segs = mask_segs(m1, m2, z);
                 if (!segs) continue;
-                const double Kh = (AT(p.Ki, r.bn1, nz) + AT(p.Ki, r.bn2, nz)) / 2.0;
+                const double Kh = (AT(p.Ki, bn1, z) + AT(p.Ki, bn2, z)) / 2.0;
                 double SxTz = 0.0, SyTz = 0.0;
                 if (p.Redi) {
-                    const double Tz1 = 0.5 * (AT(p.trz, r.bn1, nz) + AT(p.trz, r.bn1, nz + 1));
-                    const double Tz2 = 0.5 * (AT(p.trz, r.bn2, nz) + AT(p.trz, r.bn2, nz + 1));
-                    SxTz = (Tz1 * AT(p.sl1, r.bn1, nz) + Tz2 * AT(p.sl1, r.bn2, nz)) / 2.0;
-                    SyTz = (Tz1 * AT(p.sl2, r.bn1, nz) + Tz2 * AT(p.sl2, r.bn2, nz)) / 2.0;
+                    const double Tz1 = 0.5 * (AT(p.trz, bn1, z) + AT(p.trz, bn1, z + 1));
+                    const double Tz2 = 0.5 * (AT(p.trz, bn2, z) + AT(p.trz, bn2, z + 1));
+                    SxTz = (Tz1 * AT(p.sl1, bn1, z) + Tz2 * AT(p.sl1, bn2, z)) / 2.0;
+                    SyTz = (Tz1 * AT(p.sl2, bn1, z) + Tz2 * AT(p.sl2, bn2, z)) / 2.0;
                 }
-                double dz, Tx, Ty, c;
+                double dz, Tx, Ty, cc;
                 if (segs == 3) {
-                    dz = (AT(p.helem, r.be1, nz) + AT(p.helem, r.be2, nz)) / 2.0;
-                    Tx = 0.5 * (AT(p.txy_x, r.be1, nz) + AT(p.txy_x, r.be2, nz));
-                    Ty = 0.5 * (AT(p.txy_y, r.be1, nz) + AT(p.txy_y, r.be2, nz));
+                    const double2 ga = AT(p.txy, be1, z), gb = AT(p.txy, be2, z);
+                    dz = (AT(p.helem, be1, z) + AT(p.helem, be2, z)) / 2.0;
+                    Tx = 0.5 * (ga.x + gb.x);
+                    Ty = 0.5 * (ga.y + gb.y);
                     const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
-                    c = ((r.dX2 - r.dX1) * Fy - (r.dY2 - r.dY1) * Fx) * dz;
+                    cc = ((d2.x - d1.x) * Fy - (d2.y - d1.y) * Fx) * dz;
                 } else if (segs == 1) {
-                    dz = AT(p.helem, r.be1, nz); Tx = AT(p.txy_x, r.be1, nz); Ty = AT(p.txy_y, r.be1, nz);
+                    const double2 ga = AT(p.txy, be1, z);
+                    dz = AT(p.helem, be1, z); Tx = ga.x; Ty = ga.y;
                     const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
-                    c = (-r.dX1 * Fy + r.dY1 * Fx) * dz;
+                    cc = (-d1.x * Fy + d1.y * Fx) * dz;
                 } else {
-                    dz = AT(p.helem, r.be2, nz); Tx = AT(p.txy_x, r.be2, nz); Ty = AT(p.txy_y, r.be2, nz);
+                    const double2 gb = AT(p.txy, be2, z);
+                    dz = AT(p.helem, be2, z); Tx = gb.x; Ty = gb.y;
                     const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
-                    c = (r.dX2 * Fy - r.dY2 * Fx) * dz;
+                    cc = (d2.x * Fy - d2.y * Fx) * dz;
                 }
-                const double rhs = second ? 0.0 - c : 0.0 + c;
-                acc[(nz - 1) * BS + tid] = acc[(nz - 1) * BS + tid] + rhs * p.dt / AT(p.areasvol, b, nz);
+                const double rhs = second ? 0.0 - cc : 0.0 + cc;
+                acc[q] = acc[q] + rhs * p.dt / asv[q];
             }
         }
     }
-    for (int nz = nzmin; nz <= nzmax - 1; nz++) {                             // T*  :302-305
-        const double t = AT(T, b, nz);
-        const double del = acc[(nz - 1) * BS + tid] + t * (AT(p.hnode, b, nz) - AT(p.hnode_new, b, nz));
-        AT(p.tstar, b, nz) = t + del / AT(p.hnode_new, b, nz);
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {                                          // T*  :302-305
+        if (!act[q]) continue;
+        const int z = nz[q];
+        const double t = AT(T, c.b, z);
+        const double del = acc[q] + t * (AT(p.hnode, c.b, z) - AT(p.hnode_new, c.b, z));
+        AT(p.tstar, c.b, z) = t + del / AT(p.hnode_new, c.b, z);
     }
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K7b: diff_ver_part_impl_ale (oce_ale_tracer.F90:509-855): per own column rebuild zbar_n/Z_n from hnode_new,
-// assemble a,b,c and the right-hand side from T*, add shortwave penetration and the surface boundary condition
-// (bc_surface :1154-1195), Thomas algorithm, T = T* + dT.  One thread per column; dynamic smem: zb, cp, tp [3][nlp][BS]
-__global__ void LB(64) k_impl_diff(KP p) {
+// K7b: diff_ver_part_impl_ale (oce_ale_tracer.F90:509-855).  Block = one tile of 32 own columns x level rows.
+// The column recurrences are split from the memory-parallel work so that no thread walks down a column issuing
+// dependent global loads:
+//   phase 1 (all threads)   hnode_new -> shared
+//   phase 2 (warp 0)        zbar_n bottom-up scan per column in shared memory                          (:528-536)
+//   phase 3 (all threads)   a, b, c and the right-hand side of every (column, level) from T*, Kv, areas (:560-800),
+//                           shortwave penetration and the surface boundary condition (bc_surface :1154-1195)
+//   phase 4 (warp 0)        Thomas algorithm per column in shared memory                                (:828-844)
+//   phase 5 (all threads)   T = T* + dT, coalesced
+// dynamic smem: H, ZB, A, B, C, R  [6][nlp][32]
+__global__ void LB(512) k_impl_diff(KP p) {
     extern __shared__ double sm[];
-    const int tid = threadIdx.x, BS = blockDim.x;
-    double* zb = sm; double* cp = sm + (size_t)p.nlp * BS; double* tp = cp + (size_t)p.nlp * BS;
-    const int n = blockIdx.x * BS + tid;
-    if (n >= p.myN) return;
-    const int b = tbase(n, p.nlp);
-    const unsigned lv = p.n_lev[n];
-    const int nzmin = lv & 255, nzmax = (lv >> 8) & 255;
+    const int S = p.nlp * TILE, lane = threadIdx.x;
+    double* H = sm; double* ZBs = sm + S; double* sA = sm + 2 * S; double* sB = sm + 3 * S; double* sC = sm + 4 * S; double* sR = sm + 5 * S;
+    const NodeCol c = node_col(p);
     const double* __restrict__ hn = p.hnode_new;
     const double* __restrict__ TS = p.tstar;
     const double dt = p.dt;
     const double isredi = p.Redi ? 1.0 : 0.0;
-    const bool do_wimpl = false;      // FCT limiter on => no implicit w here (:424)
-#define ZB(nz) zb[((nz) - 1) * BS + tid]
-#define ZN(nz) (ZB((nz) + 1) + AT(hn, b, nz) / 2.0)                  /* Z_n(nz) = zbar_n(nz+1) + hnode_new(nz)/2 */
-    ZB(nzmax) = p.n_znb[n];
-    for (int nz = nzmax - 1; nz >= nzmin; nz--) ZB(nz) = ZB(nz + 1) + AT(hn, b, nz);
+    int nz[LPT]; bool act[LPT];
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        nz[q] = threadIdx.y + 1 + q * blockDim.y;
+        act[q] = c.valid && nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
+        if (act[q]) H[(nz[q] - 1) * TILE + lane] = AT(hn, c.b, nz[q]);
+    }
+    __syncthreads();
+#define ZB(z) ZBs[((z) - 1) * TILE + lane]
+#define HN(z) H[((z) - 1) * TILE + lane]
+#define ZN(z) (ZB((z) + 1) + HN(z) / 2.0)                    /* Z_n(nz) = zbar_n(nz+1) + hnode_new(nz)/2 */
+    if (threadIdx.y == 0 && c.valid) {
+        double zb = p.n_znb[c.n];
+        ZB(c.nzmax) = zb;
+        for (int z = c.nzmax - 1; z >= c.nzmin; z--) { zb = zb + HN(z); ZB(z) = zb; }
+    }
+    __syncthreads();
     const double vcpw = 4.2e6;
-    double cpm = 0.0, tpm = 0.0, zinv1 = 0.0;
     const double zinv = 1.0 * dt;
-    for (int nz = nzmin; nz <= nzmax - 1; nz++) {
-        double a, bb, c;
-        const double asv = AT(p.areasvol, b, nz), h = AT(hn, b, nz);
-        if (nz == nzmin) {
-            const double zinv2 = 1.0 / (ZN(nz) - ZN(nz + 1));
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        if (!act[q]) continue;
+        const int z = nz[q];
+        const int nzmin = c.nzmin, nzmax = c.nzmax, b = c.b;
+        double a, bb, cc;
+        const double asv = AT(p.areasvol, b, z), h = HN(z);
+        if (z == nzmin) {
+            const double zinv2 = 1.0 / (ZN(z) - ZN(z + 1));
             double Ty1 = 0.0;
             if (p.Redi) {
-                const double s0 = AT(p.sl3, b, nz), s1 = AT(p.sl3, b, nz + 1);
-                Ty1 = (ZN(nz) - ZB(nz + 1)) * zinv2 * (s0 * s0) * AT(p.Ki, b, nz) + (ZB(nz + 1) - ZN(nz + 1)) * zinv2 * (s1 * s1) * AT(p.Ki, b, nz + 1);
+                const double s0 = AT(p.sl3, b, z), s1 = AT(p.sl3, b, z + 1);
+                Ty1 = (ZN(z) - ZB(z + 1)) * zinv2 * (s0 * s0) * AT(p.Ki, b, z) + (ZB(z + 1) - ZN(z + 1)) * zinv2 * (s1 * s1) * AT(p.Ki, b, z + 1);
             }
             Ty1 = Ty1 * isredi;
             a = 0.0;
-            c = -(AT(p.Kv, b, nz + 1) + Ty1) * zinv2 * zinv * AT(p.area, b, nz + 1) / asv;
-            bb = -c + h;
-            zinv1 = zinv2;
-        } else if (nz <= nzmax - 2) {
-            const double zinv2 = 1.0 / (ZN(nz) - ZN(nz + 1));
+            cc = -(AT(p.Kv, b, z + 1) + Ty1) * zinv2 * zinv * AT(p.area, b, z + 1) / asv;
+            bb = -cc + h;
+        } else if (z <= nzmax - 2) {
+            const double zinv1 = 1.0 / (ZN(z - 1) - ZN(z));
+            const double zinv2 = 1.0 / (ZN(z) - ZN(z + 1));
             double Ty = 0.0, Ty1 = 0.0;
             if (p.Redi) {
-                const double sm1 = AT(p.sl3, b, nz - 1), s0 = AT(p.sl3, b, nz), s1 = AT(p.sl3, b, nz + 1);
-                Ty = (ZN(nz - 1) - ZB(nz)) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, nz - 1) + (ZB(nz) - ZN(nz)) * zinv1 * (s0 * s0) * AT(p.Ki, b, nz);
-                Ty1 = (ZN(nz) - ZB(nz + 1)) * zinv2 * (s0 * s0) * AT(p.Ki, b, nz) + (ZB(nz + 1) - ZN(nz + 1)) * zinv2 * (s1 * s1) * AT(p.Ki, b, nz + 1);
+                const double sm1 = AT(p.sl3, b, z - 1), s0 = AT(p.sl3, b, z), s1 = AT(p.sl3, b, z + 1);
+                Ty = (ZN(z - 1) - ZB(z)) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, z - 1) + (ZB(z) - ZN(z)) * zinv1 * (s0 * s0) * AT(p.Ki, b, z);
+                Ty1 = (ZN(z) - ZB(z + 1)) * zinv2 * (s0 * s0) * AT(p.Ki, b, z) + (ZB(z + 1) - ZN(z + 1)) * zinv2 * (s1 * s1) * AT(p.Ki, b, z + 1);
             }
             Ty = Ty * isredi; Ty1 = Ty1 * isredi;
-            a = -(AT(p.Kv, b, nz) + Ty) * zinv1 * zinv * (AT(p.area, b, nz) / asv);
-            c = -(AT(p.Kv, b, nz + 1) + Ty1) * zinv2 * zinv * AT(p.area, b, nz + 1) / asv;
-            bb = -a - c + h;
-            zinv1 = zinv2;
+            a = -(AT(p.Kv, b, z) + Ty) * zinv1 * zinv * (AT(p.area, b, z) / asv);
+            cc = -(AT(p.Kv, b, z + 1) + Ty1) * zinv2 * zinv * AT(p.area, b, z + 1) / asv;
+            bb = -a - cc + h;
         } else {
+            const double zinv1 = 1.0 / (ZN(z - 1) - ZN(z));
             double Ty = 0.0;
             if (p.Redi) {
-                const double sm1 = AT(p.sl3, b, nz - 1), s0 = AT(p.sl3, b, nz);
-                Ty = (ZN(nz - 1) - ZB(nz)) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, nz - 1) + (ZB(nz) - ZN(nz)) * zinv1 * (s0 * s0) * AT(p.Ki, b, nz);
+                const double sm1 = AT(p.sl3, b, z - 1), s0 = AT(p.sl3, b, z);
+                Ty = (ZN(z - 1) - ZB(z)) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, z - 1) + (ZB(z) - ZN(z)) * zinv1 * (s0 * s0) * AT(p.Ki, b, z);
             }
             Ty = Ty * isredi;
-            a = -(AT(p.Kv, b, nz) + Ty) * zinv1 * zinv * (AT(p.area, b, nz) / asv);
-            c = 0.0;
+            a = -(AT(p.Kv, b, z) + Ty) * zinv1 * zinv * (AT(p.area, b, z) / asv);
+            cc = 0.0;
             bb = -a + h;
         }
-        (void)do_wimpl;
         double tr;
-        if (nz == nzmin) tr = -(bb - h) * AT(TS, b, nz) - c * AT(TS, b, nz + 1);
-        else if (nz <= nzmax - 2) tr = -a * AT(TS, b, nz - 1) - (bb - h) * AT(TS, b, nz) - c * AT(TS, b, nz + 1);
-        else tr = -a * AT(TS, b, nz - 1) - (bb - h) * AT(TS, b, nz);
+        if (z == nzmin) tr = -(bb - h) * AT(TS, b, z) - cc * AT(TS, b, z + 1);
+        else if (z <= nzmax - 2) tr = -a * AT(TS, b, z - 1) - (bb - h) * AT(TS, b, z) - cc * AT(TS, b, z + 1);
+        else tr = -a * AT(TS, b, z - 1) - (bb - h) * AT(TS, b, z);
         if (p.use_sw_pene && p.tr_num == 1)
-            tr = tr + (AT(p.sw3d, b, nz) - AT(p.sw3d, b, nz + 1) * AT(p.area, b, nz + 1) / asv) * zinv;
-        if (nz == nzmin) {
+            tr = tr + (AT(p.sw3d, b, z) - AT(p.sw3d, b, z + 1) * AT(p.area, b, z + 1) / asv) * zinv;
+        if (z == nzmin) {
             double bc = 0.0;
             if (p.tracer_id == 0) {
                 const double tsurf = (p.tr_num == 1) ? AT(TS, b, nzmin) : AT(p.T1, b, nzmin);
-                bc = -dt * (p.heat_flux[n] / vcpw + tsurf * p.water_flux[n] * p.is_nonlinfs);
+                bc = -dt * (p.heat_flux[c.n] / vcpw + tsurf * p.water_flux[c.n] * p.is_nonlinfs);
             } else if (p.tracer_id == 1)
-                bc = dt * (p.virtual_salt[n] + p.relax_salt[n] - p.real_salt_flux[n] * p.is_nonlinfs);
+                bc = dt * (p.virtual_salt[c.n] + p.relax_salt[c.n] - p.real_salt_flux[c.n] * p.is_nonlinfs);
             tr = tr + bc;
         }
-        if (nz == nzmin) { cpm = c / bb; tpm = tr / bb; }
-        else { const double m = bb - cpm * a; cpm = c / m; tpm = (tr - tpm * a) / m; }
-        cp[(nz - 1) * BS + tid] = cpm; tp[(nz - 1) * BS + tid] = tpm;
+        const int o = (z - 1) * TILE + lane;
+        sA[o] = a; sB[o] = bb; sC[o] = cc; sR[o] = tr;
     }
-    double x = tp[(nzmax - 2) * BS + tid];
-    AT(p.T, b, nzmax - 1) = AT(TS, b, nzmax - 1) + x;
-    for (int nz = nzmax - 2; nz >= nzmin; nz--) {
-        x = tp[(nz - 1) * BS + tid] - cp[(nz - 1) * BS + tid] * x;
-        AT(p.T, b, nz) = AT(TS, b, nz) + x;
+    __syncthreads();
+    if (threadIdx.y == 0 && c.valid) {                                        // Thomas :828-844
+        int o = (c.nzmin - 1) * TILE + lane;
+        double cpm = sC[o] / sB[o], tpm = sR[o] / sB[o];
+        sC[o] = cpm; sR[o] = tpm;
+        for (int z = c.nzmin + 1; z <= c.nzmax - 1; z++) {
+            o += TILE;
+            const double a = sA[o];
+            const double m = sB[o] - cpm * a;
+            cpm = sC[o] / m; tpm = (sR[o] - tpm * a) / m;
+            sC[o] = cpm; sR[o] = tpm;
+        }
+        double x = tpm;
+        for (int z = c.nzmax - 2; z >= c.nzmin; z--) {
+            o -= TILE;
+            x = sR[o] - sC[o] * x;
+            sR[o] = x;
+        }
     }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < LPT; q++)
+        if (act[q]) AT(p.T, c.b, nz[q]) = AT(TS, c.b, nz[q]) + sR[(nz[q] - 1) * TILE + lane];
 #undef ZB
+#undef HN
 #undef ZN
 }
 
@@ -597,15 +689,16 @@ static KP make_kp(TracerCtx& c, int tr) {
     p.hor = c.opt.tra_adv_hor; p.ver = c.opt.tra_adv_ver; p.w_split = c.opt.w_split; p.Redi = c.opt.Redi; p.use_sw_pene = c.opt.use_sw_pene;
     p.do_hor_diff = c.opt.do_hor_diff; p.tracer_id = c.opt.tracer_id[tr]; p.tr_num = tr + 1;
     p.edge = c.edge.p; p.edgeho = c.edgeho.p; p.ne_slot = c.ne_slot.p; p.nie_slot = c.nie_slot.p; p.el_nb = c.el_nb.p; p.el_lev = c.el_lev.p;
+    p.ns_bo = c.ns_bo.p; p.ns_be1 = c.ns_be1.p; p.ns_be2 = c.ns_be2.p; p.ns_bed = c.ns_bed.p; p.ns_m1 = c.ns_m1.p; p.ns_m2 = c.ns_m2.p; p.ns_d1 = c.ns_d1.p; p.ns_d2 = c.ns_d2.p;
     p.el_g = c.el_g.p; p.el_area = c.el_area.p; p.n_lev = c.n_lev.p; p.n_nbl = c.n_nbl.p; p.n_znb = c.n_znb.p;
-    p.area = c.area.p; p.areasvol = c.areasvol.p; p.U = c.U.p; p.V = c.V.p; p.helem = c.helem.p; p.W = c.W.p; p.We = c.We.p; p.Wi = c.Wi.p;
+    p.area = c.area.p; p.areasvol = c.areasvol.p; p.UV = c.UV.p; p.helem = c.helem.p; p.W = c.W.p; p.We = c.We.p; p.Wi = c.Wi.p;
     p.hnode = c.hnode.p; p.hnode_new = c.hnode_new.p; p.Z3 = c.Z3.p; p.zbar3 = c.zbar3.p; p.Kv = c.Kv.p; p.Ki = c.Ki.p;
     p.sl1 = c.sl1.p; p.sl2 = c.sl2.p; p.sl3 = c.sl3.p; p.sw3d = c.sw3d.p;
     p.heat_flux = c.heat_flux.p; p.water_flux = c.water_flux.p; p.virtual_salt = c.virtual_salt.p; p.relax_salt = c.relax_salt.p; p.real_salt_flux = c.real_salt_flux.p;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     p.T = c.T.p + nf * tr; p.Told = c.Told.p + nf * tr; p.T1 = c.T.p;
-    p.txy_x = c.txy_x.p; p.txy_y = c.txy_y.p; p.trz = c.trz.p; p.LO = c.LO.p; p.adf_h = c.adf_h.p; p.adf_v = c.adf_v.p;
-    p.fplus = c.fplus.p; p.fminus = c.fminus.p; p.tstar = c.tstar.p;
+    p.txy = c.txy.p; p.fpm = c.fpm.p; p.trz = c.trz.p; p.LO = c.LO.p; p.adf_h = c.adf_h.p; p.adf_v = c.adf_v.p;
+    p.tstar = c.tstar.p;
     return p;
 }
 
@@ -613,10 +706,8 @@ static bool g_attr_done = false;
 static void set_smem_attrs() {
     if (g_attr_done) return;
     const int big = 200 * 1024;
-    CUDA_CHECK(cudaFuncSetAttribute(k_lo, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     CUDA_CHECK(cudaFuncSetAttribute(k_vert_impl, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     CUDA_CHECK(cudaFuncSetAttribute(k_fct_bounds, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    CUDA_CHECK(cudaFuncSetAttribute(k_update, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     CUDA_CHECK(cudaFuncSetAttribute(k_impl_diff, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     g_attr_done = true;
 }
@@ -633,8 +724,11 @@ void tracer_step_all(TracerCtx& c) {
     c.stream = fb_stream();
     cudaStream_t st = c.stream;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
-    const int gN128 = (c.myN + 127) / 128, gN64 = (c.myN + 63) / 64, gE = (c.myE + 127) / 128, gEd = (c.myEd + 127) / 128, gNall = (c.N + 127) / 128;
-    const size_t sm1_128 = (size_t)c.nlp * 128 * sizeof(double);
+    const int gN64 = (c.myN + 63) / 64, gE = (c.myE + 127) / 128, gNall = (c.N + 127) / 128;
+    const int LY = (c.nl - 1 + LPT - 1) / LPT;                  // level rows per block: LPT levels per thread cover nl-1 layers
+    if (LY * TILE > 512) { fb_set_error(25, "nl too large for the level-row thread mapping (nl-1 <= 48)"); return; }
+    const dim3 blk(TILE, LY);
+    const size_t smt = (size_t)c.nlp * TILE * sizeof(double);   // one [nlp][32] shared array
     const size_t sm_64 = (size_t)c.nlp * 64 * sizeof(double);
     CUDA_CHECK(cudaEventRecord(c.ev0, st));
 #define KL(name, ...) do { ProfScope ps_(name, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
@@ -643,18 +737,18 @@ void tracer_step_all(TracerCtx& c) {
         const double ca = -(0.5 + c.opt.epsilon), cb = 1.5 + c.opt.epsilon;
         KL("k_ab2", k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb));
         KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
-        KL("k_lo", k_lo<<<gN128, 128, sm1_128, st>>>(p));
+        KL("k_lo", k_lo<<<c.myNtiles, blk, 0, st>>>(p));
         if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
-        KL("k_ho_edge", k_ho_edge<<<gEd, 128, 0, st>>>(p));
-        KL("k_fct_bounds", k_fct_bounds<<<gN64, 64, 4 * sm_64, st>>>(p));
+        KL("k_ho_edge", k_ho_edge<<<c.Edtiles, blk, 0, st>>>(p));
+        KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
         if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
         if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
-        KL("k_update", k_update<<<gN128, 128, sm1_128, st>>>(p));
+        KL("k_update", k_update<<<c.myNtiles, blk, 0, st>>>(p));
         {   // tr_arr_old = tr_arr (:274)
             ProfScope ps_("copy_told", st);
             CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
         }
-        KL("k_impl_diff", k_impl_diff<<<gN64, 64, 3 * sm_64, st>>>(p));
+        KL("k_impl_diff", k_impl_diff<<<c.myNtiles, blk, 6 * smt, st>>>(p));
     }
     if (c.opt.clamp_salt && c.ntr >= 2) { KP p = make_kp(c, 1); KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T)); }
 #undef KL
@@ -664,16 +758,16 @@ void tracer_step_all(TracerCtx& c) {
 }
 
 // debug access to work fields (tiled) by name
-const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind) {
+const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind, int* ncomp, int* comp) {
     std::string s(name);
-    *kind = 0;                                    // 0 node field, 1 edge field, 2 element field
+    *kind = 0; *ncomp = 1; *comp = 0;             // kind: 0 node field, 1 edge field, 2 element field
     if (s == "fct_LO") return c.LO.p;
     if (s == "adf_v") return c.adf_v.p;
-    if (s == "fct_plus") return c.fplus.p;
-    if (s == "fct_minus") return c.fminus.p;
+    if (s == "fct_plus") { *ncomp = 2; return (const double*)c.fpm.p; }
+    if (s == "fct_minus") { *ncomp = 2; *comp = 1; return (const double*)c.fpm.p; }
     if (s == "tstar") return c.tstar.p;
     if (s == "adf_h") { *kind = 1; return c.adf_h.p; }
-    if (s == "tr_xy_x") { *kind = 2; return c.txy_x.p; }
-    if (s == "tr_xy_y") { *kind = 2; return c.txy_y.p; }
+    if (s == "tr_xy_x") { *kind = 2; *ncomp = 2; return (const double*)c.txy.p; }
+    if (s == "tr_xy_y") { *kind = 2; *ncomp = 2; *comp = 1; return (const double*)c.txy.p; }
     return nullptr;
 }
