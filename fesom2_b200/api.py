@@ -22,7 +22,8 @@ EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb20
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_tracers",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
-           "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report"]
+           "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
+           "fb200_selftest_div"]
 
 
 class FesomB200Error(RuntimeError):
@@ -74,6 +75,14 @@ def _p(a):
 def set_stream(cuda_stream_ptr):
     """run all later library work on the caller's CUDA stream (an integer cudaStream_t, e.g. torch's .cuda_stream)"""
     lib().fb200_set_stream(C.c_void_p(int(cuda_stream_ptr) if cuda_stream_ptr else None))
+
+
+def selftest_div(n=1 << 24):
+    """number of operand pairs on which the kernels' reciprocal-based division differs from IEEE division"""
+    bad = C.c_longlong(-1)
+    lib().fb200_selftest_div(C.byref(C.c_longlong(int(n))), C.byref(bad))
+    _check(lib())
+    return bad.value
 
 
 def profile(mode):

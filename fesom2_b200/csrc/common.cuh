@@ -82,8 +82,9 @@ struct TracerCtx {
     DevBuf<int> ne_slot;            // [Ntile][maxdeg][32]   (edge<<1)|second, -1 = none; ascending reference edge id
     // per (node, incident-edge slot) copies of the edge data, [Ntile][maxdeg][32]: a warp of 32 consecutive nodes reads
     // every item fully coalesced (the edge-indexed records would be a scattered 64-byte gather per lane)
-    DevBuf<int> ns_bo, ns_be1, ns_be2, ns_bed;   // tile bases: other node, element 1, element 2 (-1), edge (for adf_h)
-    DevBuf<unsigned long long> ns_m1, ns_m2;     // EdgeRec::m1, m2
+    DevBuf<int> tile_deg;                        // [Ntile] max degree within the tile
+    DevBuf<int4> ns_i;                           // tile bases: other node, element 1, element 2 (-1), edge (for adf_h)
+    DevBuf<ulonglong2> ns_m;                     // EdgeRec::m1, m2
     DevBuf<double2> ns_d1, ns_d2;                // (dX1,dY1), (dX2,dY2)
     DevBuf<int> nie_slot;           // [Ntile][maxnie][32]   element id in nod_in_elem2D order, -1 = none
     DevBuf<int> el_nb;              // [3][Eall] node tile bases of element corners

@@ -222,17 +222,20 @@ void ctx_commit(TracerCtx& c) {
             }
         c.ne_slot.upload(slot);
         const size_t ns = slot.size();
-        std::vector<int> bo(ns, 0), be1(ns, 0), be2(ns, -1), bed(ns, 0);
-        std::vector<unsigned long long> m1(ns, 0), m2(ns, 0);
+        std::vector<int4> ni(ns, make_int4(0, 0, -1, 0));
+        std::vector<ulonglong2> mk(ns, make_ulonglong2(0ull, 0ull));
         std::vector<double2> d1(ns, make_double2(0., 0.)), d2(ns, make_double2(0., 0.));
         for (size_t k = 0; k < ns; k++) {
             if (slot[k] < 0) continue;
             const int e = slot[k] >> 1, second = slot[k] & 1;
             const EdgeRec& r = er[e];
-            bo[k] = second ? r.bn1 : r.bn2; be1[k] = r.be1; be2[k] = r.be2; bed[k] = tile_base(e, nlp); m1[k] = r.m1; m2[k] = r.m2;
+            ni[k] = make_int4(second ? r.bn1 : r.bn2, r.be1, r.be2, tile_base(e, nlp)); mk[k] = make_ulonglong2(r.m1, r.m2);
             d1[k] = make_double2(r.dX1, r.dY1); d2[k] = make_double2(r.dX2, r.dY2);
         }
-        c.ns_bo.upload(bo); c.ns_be1.upload(be1); c.ns_be2.upload(be2); c.ns_bed.upload(bed); c.ns_m1.upload(m1); c.ns_m2.upload(m2);
+        c.ns_i.upload(ni); c.ns_m.upload(mk);
+        std::vector<int> tdeg(c.Ntiles, 0);
+        for (int n = 0; n < N; n++) tdeg[n >> 5] = std::max(tdeg[n >> 5], deg[n]);
+        c.tile_deg.upload(tdeg);
         c.ns_d1.upload(d1); c.ns_d2.upload(d2);
     }
     c.maxnie = 0; for (int n = 0; n < N; n++) c.maxnie = std::max(c.maxnie, c.h_nie_num[n]);
@@ -266,7 +269,7 @@ void ctx_release(TracerCtx& c) {
                               &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar,
                               &c.helem, &c.adf_h, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
                               &c.relax_salt, &c.real_salt_flux, &c.stage, &c.el_g, &c.el_area, &c.n_znb}) b->release();
-    c.ns_bo.release(); c.ns_be1.release(); c.ns_be2.release(); c.ns_bed.release(); c.ns_m1.release(); c.ns_m2.release(); c.ns_d1.release(); c.ns_d2.release();
+    c.tile_deg.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
     c.UV.release(); c.txy.release(); c.fpm.release();
     c.edge.release(); c.edgeho.release(); c.ne_slot.release(); c.nie_slot.release(); c.el_nb.release(); c.el_lev.release();
     c.n_lev.release(); c.n_nbl.release();

@@ -14,7 +14,10 @@ struct KP {                       // kernel parameter block (by value)
     double dt, ph, pv, eps_ab, is_nonlinfs;
     int hor, ver, w_split, Redi, use_sw_pene, do_hor_diff, tracer_id, tr_num;
     const EdgeRec* edge; const EdgeHo* edgeho; const int* ne_slot; const int* nie_slot; const int* el_nb;
-    const int *ns_bo, *ns_be1, *ns_be2, *ns_bed; const unsigned long long *ns_m1, *ns_m2; const double2 *ns_d1, *ns_d2;
+    const int* tile_deg;           // per node tile: largest number of incident edges among its 32 nodes
+    const int4* ns_i;              // per (node, slot): tile bases (other node, element 1, element 2 or -1, edge)
+    const ulonglong2* ns_m;        // level masks (m1, m2)
+    const double2 *ns_d1, *ns_d2;  // (dX1,dY1), (dX2,dY2)
     const unsigned* el_lev; const double* el_g; const double* el_area; const unsigned* n_lev; const int* n_nbl; const double* n_znb;
     const double2* UV;              // (u, v) per element-level
     const double *area, *areasvol, *helem, *W, *We, *Wi, *hnode, *hnode_new, *Z3, *zbar3, *Kv, *Ki, *sl1, *sl2, *sl3, *sw3d;
@@ -26,6 +29,19 @@ struct KP {                       // kernel parameter block (by value)
 
 __device__ __forceinline__ int tbase(int ent, int nlp) { return (ent >> 5) * (nlp * TILE) + (ent & 31); }
 #define AT(p, base, nz) (p)[(base) + (((nz) - 1) << 5)]          // 1-based level
+
+// min/max of two non-NaN doubles as one compare + select (the values here are never NaN; fmin/fmax spend several
+// more instructions on NaN propagation)
+__device__ __forceinline__ double dmin(double a, double b) { return (b < a) ? b : a; }
+__device__ __forceinline__ double dmax(double a, double b) { return (b > a) ? b : a; }
+// x / b, correctly rounded, given rb = 1.0 / b: quotient estimate plus one exact-residual correction (the last two
+// steps of the IEEE division sequence; the Newton iterations for 1/b are paid once per level instead of per edge).
+// tests/test_gpu_tracer.py::test_div_by_matches_ieee_division checks it against '/' on 2^24 operand pairs.
+__device__ __forceinline__ double div_by(double x, double b, double rb) {
+    const double q = x * rb;
+    const double r = fma(-b, q, x);
+    return fma(r, rb, q);
+}
 
 // Level masks of an edge: bit nz of m1 (m2) is set where the median-dual segment in element 1 (2) carries a flux at
 // level nz — the five ranges (A)-(E) of oce_adv_tra_hor.F90:129-209 evaluated once on the host (context.cu), so the
@@ -145,27 +161,29 @@ __global__ void LB(512) k_lo(KP p) {
     if (!c.valid) return;
     const double* __restrict__ T = p.T;
     int nz[LPT]; bool act[LPT]; double acc[LPT], tn[LPT];
+    bool any = false;
 #pragma unroll
     for (int q = 0; q < LPT; q++) {
-        nz[q] = threadIdx.y + 1 + q * blockDim.y;
+        nz[q] = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
         act[q] = nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
+        any |= act[q];
         acc[q] = 0.0;
         tn[q] = act[q] ? AT(T, c.b, nz[q]) : 0.0;
     }
-    if (!(act[0] | act[1] | act[2])) return;
+    if (!any) return;
     const size_t sbase = (size_t)blockIdx.x * p.maxdeg * TILE + threadIdx.x;
-    for (int j = 0; j < p.maxdeg; j++) {
+    const int ndeg = p.tile_deg[blockIdx.x];
+    for (int j = 0; j < ndeg; j++) {
         const size_t k = sbase + (size_t)j * TILE;
-        const int s = p.ne_slot[k];
-        if (s < 0) break;
-        const bool second = s & 1;
-        const int bo = p.ns_bo[k], be1 = p.ns_be1[k], be2 = p.ns_be2[k];
-        const unsigned long long m1 = p.ns_m1[k], m2 = p.ns_m2[k];
+        const bool second = p.ne_slot[k] & 1;                                  // empty slots have zero masks
+        const int4 ni = p.ns_i[k];
+        const int bo = ni.x, be1 = ni.y, be2 = ni.z;
+        const ulonglong2 mm = p.ns_m[k];
         const double2 d1 = p.ns_d1[k], d2 = p.ns_d2[k];
 #pragma unroll
         for (int q = 0; q < LPT; q++) {
             if (!act[q]) continue;
-            const int segs = mask_segs(m1, m2, nz[q]);
+            const int segs = mask_segs(mm.x, mm.y, nz[q]);
             if (!segs) continue;
             const double vflux = seg_vflux(p, segs, be1, be2, d1.x, d1.y, d2.x, d2.y, nz[q]);
             const double to = AT(T, bo, nz[q]);
@@ -215,19 +233,19 @@ __global__ void LB(64) k_vert_impl(KP p, double* __restrict__ ttf, const double*
             v_adv = zinv * AT(p.area, b, nz) / asv;
             bb = hn + AT(W, b, nz) * v_adv;
             v_adv = zinv * AT(p.area, b, nz + 1) / asv;
-            bb = bb - fmin(0.0, AT(W, b, nz + 1)) * v_adv;
-            c = -fmax(0.0, AT(W, b, nz + 1)) * v_adv;
+            bb = bb - dmin(0.0, AT(W, b, nz + 1)) * v_adv;
+            c = -dmax(0.0, AT(W, b, nz + 1)) * v_adv;
         } else if (nz <= nzmax - 2) {
             v_adv = zinv * AT(p.area, b, nz) / asv;
-            a = fmin(0.0, AT(W, b, nz)) * v_adv;
-            bb = hn + fmax(0.0, AT(W, b, nz)) * v_adv;
+            a = dmin(0.0, AT(W, b, nz)) * v_adv;
+            bb = hn + dmax(0.0, AT(W, b, nz)) * v_adv;
             v_adv = zinv * AT(p.area, b, nz + 1) / asv;
-            bb = bb - fmin(0.0, AT(W, b, nz + 1)) * v_adv;
-            c = -fmax(0.0, AT(W, b, nz + 1)) * v_adv;
+            bb = bb - dmin(0.0, AT(W, b, nz + 1)) * v_adv;
+            c = -dmax(0.0, AT(W, b, nz + 1)) * v_adv;
         } else {
             v_adv = zinv * AT(p.area, b, nz) / asv;
-            a = fmin(0.0, AT(W, b, nz)) * v_adv;
-            bb = hn + fmax(0.0, AT(W, b, nz)) * v_adv;
+            a = dmin(0.0, AT(W, b, nz)) * v_adv;
+            bb = hn + dmax(0.0, AT(W, b, nz)) * v_adv;
             c = 0.0;
         }
         double tr;
@@ -275,12 +293,12 @@ __device__ __noinline__ void node_mean_grad(const int* __restrict__ nie_slot, in
 //   adv_tra_hor_mfct / _muscl / _upw1 with init_zero=.false. (oce_adv_tra_hor.F90:215-733) on ttfAB,
 //   the input flux being adv_tra_hor_upw1(ttf) (oce_adv_tra_driver.F90:83,142-149); the gradients of
 //   fill_up_dn_grad (oce_muscl_adv.F90:285-447) are gathered from txy instead of being stored.
-__global__ void __launch_bounds__(512, 2) k_ho_edge(KP p) {
+__global__ void __launch_bounds__(256, 3) k_ho_edge(KP p) {
     const int e = blockIdx.x * TILE + threadIdx.x;
     if (e >= p.myEd) return;
     const EdgeRec r = p.edge[e];
     const unsigned long long many = r.m1 | r.m2;
-    if ((many >> (threadIdx.y + 1)) == 0ull) return;                 // no flux-carrying level at or below this thread's first level
+    if ((many >> min(63u, blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1)) == 0ull) return;                 // no flux-carrying level at or below this thread's first level
     const EdgeHo h = p.edgeho[e];
     const int be = blockIdx.x * (p.nlp * TILE) + threadIdx.x;
     const int sh_lo = h.shared & 255, sh_hi = (h.shared >> 8) & 255;
@@ -290,7 +308,7 @@ __global__ void __launch_bounds__(512, 2) k_ho_edge(KP p) {
     const double* __restrict__ A = p.Told;
 #pragma unroll
     for (int q = 0; q < LPT; q++) {
-        const int nz = threadIdx.y + 1 + q * blockDim.y;
+        const int nz = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
         if (nz > 63) continue;
         const int segs = mask_segs(r.m1, r.m2, nz);
         if (!segs) continue;
@@ -330,7 +348,7 @@ __global__ void __launch_bounds__(512, 2) k_ho_edge(KP p) {
 // UV_rhs(1:2,nz,nod_in_elem2D(:,n)); "-bignumber/+bignumber" enter wherever a surrounding element is already below
 // its bottom (nz >= nlevels_nod2D_min).  The vertical 3-point max/min (a3, vlimit=1) goes through shared memory.
 // dynamic smem: mx, mn  [2][nlp][32]
-__global__ void LB(512) k_fct_bounds(KP p) {
+__global__ void __launch_bounds__(512, 2) k_fct_bounds(KP p) {
     extern __shared__ double sm[];
     double* smx = sm; double* smn = sm + (size_t)p.nlp * TILE;
     const NodeCol c = node_col(p);
@@ -341,39 +359,40 @@ __global__ void LB(512) k_fct_bounds(KP p) {
     bool any = false;
 #pragma unroll
     for (int q = 0; q < LPT; q++) {
-        nz[q] = threadIdx.y + 1 + q * blockDim.y;
+        nz[q] = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
         act[q] = c.valid && nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
         pp[q] = pm[q] = mx[q] = mn[q] = lo[q] = 0.0;
         if (!act[q]) continue;
         any = true;
         const double av = AT(p.adf_v, c.b, nz[q]), avn = AT(p.adf_v, c.b, nz[q] + 1);
-        pp[q] = fmax(0.0, av) + fmax(0.0, -avn);                              // :235-236
-        pm[q] = fmin(0.0, av) + fmin(0.0, -avn);
+        pp[q] = dmax(0.0, av) + dmax(0.0, -avn);                              // :235-236
+        pm[q] = dmin(0.0, av) + dmin(0.0, -avn);
         lo[q] = AT(LO, c.b, nz[q]);
         const double t = AT(T, c.b, nz[q]);
-        double M = fmax(lo[q], t), m = fmin(lo[q], t);                        // a1 :99-100
-        if (nz[q] >= c.nlmin) { M = fmax(M, -bignumber); m = fmin(m, bignumber); }   // a2 :116-121
+        double M = dmax(lo[q], t), m = dmin(lo[q], t);                        // a1 :99-100
+        if (nz[q] >= c.nlmin) { M = dmax(M, -bignumber); m = dmin(m, bignumber); }   // a2 :116-121
         mx[q] = M; mn[q] = m;
     }
     if (any) {
         const size_t sbase = (size_t)blockIdx.x * p.maxdeg * TILE + threadIdx.x;
-        for (int j = 0; j < p.maxdeg; j++) {
+        const int ndeg = p.tile_deg[blockIdx.x];
+        for (int j = 0; j < ndeg; j++) {
             const size_t k = sbase + (size_t)j * TILE;
-            const int s = p.ne_slot[k];
-            if (s < 0) break;
-            const bool second = s & 1;
-            const int bo = p.ns_bo[k], bed = p.ns_bed[k];
-            const unsigned long long many = p.ns_m1[k] | p.ns_m2[k];
+            const bool second = p.ne_slot[k] & 1;
+            const int4 ni = p.ns_i[k];
+            const int bo = ni.x, bed = ni.w;
+            const ulonglong2 mm = p.ns_m[k];
+            const unsigned long long many = mm.x | mm.y;
 #pragma unroll
             for (int q = 0; q < LPT; q++) {
                 if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
                 double f = AT(p.adf_h, bed, nz[q]);
-                if (second) f = -f;
-                pp[q] = pp[q] + fmax(0.0, f);                                  // b1 :258-261
-                pm[q] = pm[q] + fmin(0.0, f);
                 const double lo_o = AT(LO, bo, nz[q]), t_o = AT(T, bo, nz[q]);
-                mx[q] = fmax(mx[q], fmax(lo_o, t_o));
-                mn[q] = fmin(mn[q], fmin(lo_o, t_o));
+                if (second) f = -f;
+                pp[q] = pp[q] + dmax(0.0, f);                                  // b1 :258-261
+                pm[q] = pm[q] + dmin(0.0, f);
+                mx[q] = dmax(mx[q], dmax(lo_o, t_o));
+                mn[q] = dmin(mn[q], dmin(lo_o, t_o));
             }
         }
 #pragma unroll
@@ -387,15 +406,15 @@ __global__ void LB(512) k_fct_bounds(KP p) {
         const int z = nz[q];
         double qmax = mx[q], qmin = mn[q];
         if (z > c.nzmin && z < c.nzmax - 1) {                                  // a3, vlimit=1 :153-156
-            qmax = fmax(fmax(smx[(z - 2) * TILE + threadIdx.x], qmax), smx[z * TILE + threadIdx.x]);
-            qmin = fmin(fmin(smn[(z - 2) * TILE + threadIdx.x], qmin), smn[z * TILE + threadIdx.x]);
+            qmax = dmax(dmax(smx[(z - 2) * TILE + threadIdx.x], qmax), smx[z * TILE + threadIdx.x]);
+            qmin = dmin(dmin(smn[(z - 2) * TILE + threadIdx.x], qmin), smn[z * TILE + threadIdx.x]);
         }
-        const double asv = AT(p.areasvol, c.b, z);
+        const double asv = AT(p.areasvol, c.b, z), rasv = 1.0 / asv;
         qmax = qmax - lo[q]; qmin = qmin - lo[q];
-        double flux = pp[q] * p.dt / asv + flux_eps;                           // b2 :271-274
-        const double rp = fmin(1.0, qmax / flux);
-        flux = pm[q] * p.dt / asv - flux_eps;
-        AT(p.fpm, c.b, z) = make_double2(rp, fmin(1.0, qmin / flux));
+        double flux = div_by(pp[q] * p.dt, asv, rasv) + flux_eps;              // b2 :271-274
+        const double rp = dmin(1.0, qmax / flux);
+        flux = div_by(pm[q] * p.dt, asv, rasv) - flux_eps;
+        AT(p.fpm, c.b, z) = make_double2(rp, dmin(1.0, qmin / flux));
     }
 }
 
@@ -406,11 +425,11 @@ __device__ __forceinline__ double limited_fv(const KP& p, int b, int nz, int nzm
     double ae = 1.0;
     const double2 f0 = AT(p.fpm, b, nz);                   // (fct_plus, fct_minus)
     if (nz == nzmin) {
-        if (flux >= 0.0) ae = fmin(ae, f0.x); else ae = fmin(ae, f0.y);
+        if (flux >= 0.0) ae = dmin(ae, f0.x); else ae = dmin(ae, f0.y);
     } else {
         const double2 fm1 = AT(p.fpm, b, nz - 1);
-        if (flux >= 0.0) { ae = fmin(ae, fm1.y); ae = fmin(ae, f0.x); }
-        else { ae = fmin(ae, fm1.x); ae = fmin(ae, f0.y); }
+        if (flux >= 0.0) { ae = dmin(ae, fm1.y); ae = dmin(ae, f0.x); }
+        else { ae = dmin(ae, fm1.x); ae = dmin(ae, f0.y); }
     }
     return ae * flux;
 }
@@ -422,40 +441,40 @@ __global__ void LB(512) k_update(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
     const double* __restrict__ T = p.T;
-    int nz[LPT]; bool act[LPT]; double acc[LPT], fp[LPT], fm[LPT], asv[LPT];
+    int nz[LPT]; bool act[LPT]; double acc[LPT], fp[LPT], fm[LPT], asv[LPT], rasv[LPT];
     bool any = false;
 #pragma unroll
     for (int q = 0; q < LPT; q++) {
-        nz[q] = threadIdx.y + 1 + q * blockDim.y;
+        nz[q] = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
         act[q] = nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
-        acc[q] = 0.0; fp[q] = fm[q] = 0.0; asv[q] = 1.0;
+        any |= act[q];
+        acc[q] = 0.0; fp[q] = fm[q] = 0.0; asv[q] = rasv[q] = 1.0;
         if (!act[q]) continue;
-        any = true;
-        { const double2 f = AT(p.fpm, c.b, nz[q]); fp[q] = f.x; fm[q] = f.y; }
-        asv[q] = AT(p.areasvol, c.b, nz[q]);
+        const double2 f = AT(p.fpm, c.b, nz[q]); fp[q] = f.x; fm[q] = f.y;
+        asv[q] = AT(p.areasvol, c.b, nz[q]); rasv[q] = 1.0 / asv[q];
     }
     if (!any) return;
     const size_t sbase = (size_t)blockIdx.x * p.maxdeg * TILE + threadIdx.x;
-    for (int j = 0; j < p.maxdeg; j++) {                                     // dttf_h
+    const int ndeg = p.tile_deg[blockIdx.x];
+    for (int j = 0; j < ndeg; j++) {                                         // dttf_h
         const size_t k = sbase + (size_t)j * TILE;
-        const int s = p.ne_slot[k];
-        if (s < 0) break;
-        const bool second = s & 1;
-        const int bo = p.ns_bo[k], bed = p.ns_bed[k];
-        const unsigned long long many = p.ns_m1[k] | p.ns_m2[k];
+        const bool second = p.ne_slot[k] & 1;
+        const int4 ni = p.ns_i[k];
+        const int bo = ni.x, bed = ni.w;
+        const ulonglong2 mm = p.ns_m[k];
+        const unsigned long long many = mm.x | mm.y;
 #pragma unroll
         for (int q = 0; q < LPT; q++) {
             if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
             const double flux = AT(p.adf_h, bed, nz[q]);
             const double2 fo = AT(p.fpm, bo, nz[q]);
-            const double fpo = fo.x, fmo = fo.y;
-            const double fp1 = second ? fpo : fp[q], fm1 = second ? fmo : fm[q];     // factors of edge node 1 / node 2
-            const double fp2 = second ? fp[q] : fpo, fm2 = second ? fm[q] : fmo;
-            double ae = 1.0;
-            if (flux >= 0.0) { ae = fmin(ae, fp1); ae = fmin(ae, fm2); }
-            else { ae = fmin(ae, fm1); ae = fmin(ae, fp2); }
+            // :313-330  flux >= 0: min(fct_plus(n1), fct_minus(n2)) else min(fct_minus(n1), fct_plus(n2)), n1/n2 the
+            // edge's nodes; this node is n2 when `second`
+            const bool self_plus = (flux >= 0.0) != second;
+            double ae = dmin(1.0, self_plus ? fp[q] : fm[q]);
+            ae = dmin(ae, self_plus ? fo.y : fo.x);
             const double fl = ae * flux;
-            const double d = fl * p.dt / asv[q];
+            const double d = div_by(fl * p.dt, asv[q], rasv[q]);
             acc[q] = second ? acc[q] - d : acc[q] + d;
         }
     }
@@ -466,25 +485,24 @@ __global__ void LB(512) k_update(KP p) {
         const double fv = limited_fv(p, c.b, z, c.nzmin, c.nzmax);
         const double fvn = limited_fv(p, c.b, z + 1, c.nzmin, c.nzmax);
         double dv = 0.0 - AT(T, c.b, z) * AT(p.hnode, c.b, z) + AT(p.LO, c.b, z) * AT(p.hnode_new, c.b, z);
-        dv = dv + (fv - fvn) * p.dt / asv[q];
+        dv = dv + div_by((fv - fvn) * p.dt, asv[q], rasv[q]);
         acc[q] = acc[q] + dv;
     }
     if (p.do_hor_diff) {
         const double isredi = p.Redi ? 1.0 : 0.0;
-        for (int j = 0; j < p.maxdeg; j++) {
+        for (int j = 0; j < ndeg; j++) {
             const size_t k = sbase + (size_t)j * TILE;
-            const int s = p.ne_slot[k];
-            if (s < 0) break;
-            const bool second = s & 1;
-            const int bo = p.ns_bo[k], be1 = p.ns_be1[k], be2 = p.ns_be2[k];
+            const bool second = p.ne_slot[k] & 1;
+            const int4 ni = p.ns_i[k];
+            const int bo = ni.x, be1 = ni.y, be2 = ni.z;
             const int bn1 = second ? bo : c.b, bn2 = second ? c.b : bo;
-            const unsigned long long m1 = p.ns_m1[k], m2 = p.ns_m2[k];
+            const ulonglong2 mm = p.ns_m[k];
             const double2 d1 = p.ns_d1[k], d2 = p.ns_d2[k];
 #pragma unroll
             for (int q = 0; q < LPT; q++) {
                 if (!act[q]) continue;
                 const int z = nz[q];
-                const int segs = mask_segs(m1, m2, z);
+                const int segs = mask_segs(mm.x, mm.y, z);
                 if (!segs) continue;
                 const double Kh = (AT(p.Ki, bn1, z) + AT(p.Ki, bn2, z)) / 2.0;
                 double SxTz = 0.0, SyTz = 0.0;
@@ -494,7 +512,7 @@ __global__ void LB(512) k_update(KP p) {
                     SxTz = (Tz1 * AT(p.sl1, bn1, z) + Tz2 * AT(p.sl1, bn2, z)) / 2.0;
                     SyTz = (Tz1 * AT(p.sl2, bn1, z) + Tz2 * AT(p.sl2, bn2, z)) / 2.0;
                 }
-                double dz, Tx, Ty, cc;
+                double dz, Tx, Ty, cc;                                      // :1020-1062
                 if (segs == 3) {
                     const double2 ga = AT(p.txy, be1, z), gb = AT(p.txy, be2, z);
                     dz = (AT(p.helem, be1, z) + AT(p.helem, be2, z)) / 2.0;
@@ -514,7 +532,7 @@ __global__ void LB(512) k_update(KP p) {
                     cc = (d2.x * Fy - d2.y * Fx) * dz;
                 }
                 const double rhs = second ? 0.0 - cc : 0.0 + cc;
-                acc[q] = acc[q] + rhs * p.dt / asv[q];
+                acc[q] = acc[q] + div_by(rhs * p.dt, asv[q], rasv[q]);
             }
         }
     }
@@ -551,7 +569,7 @@ __global__ void LB(512) k_impl_diff(KP p) {
     int nz[LPT]; bool act[LPT];
 #pragma unroll
     for (int q = 0; q < LPT; q++) {
-        nz[q] = threadIdx.y + 1 + q * blockDim.y;
+        nz[q] = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
         act[q] = c.valid && nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
         if (act[q]) H[(nz[q] - 1) * TILE + lane] = AT(hn, c.b, nz[q]);
     }
@@ -689,7 +707,7 @@ static KP make_kp(TracerCtx& c, int tr) {
     p.hor = c.opt.tra_adv_hor; p.ver = c.opt.tra_adv_ver; p.w_split = c.opt.w_split; p.Redi = c.opt.Redi; p.use_sw_pene = c.opt.use_sw_pene;
     p.do_hor_diff = c.opt.do_hor_diff; p.tracer_id = c.opt.tracer_id[tr]; p.tr_num = tr + 1;
     p.edge = c.edge.p; p.edgeho = c.edgeho.p; p.ne_slot = c.ne_slot.p; p.nie_slot = c.nie_slot.p; p.el_nb = c.el_nb.p; p.el_lev = c.el_lev.p;
-    p.ns_bo = c.ns_bo.p; p.ns_be1 = c.ns_be1.p; p.ns_be2 = c.ns_be2.p; p.ns_bed = c.ns_bed.p; p.ns_m1 = c.ns_m1.p; p.ns_m2 = c.ns_m2.p; p.ns_d1 = c.ns_d1.p; p.ns_d2 = c.ns_d2.p;
+    p.tile_deg = c.tile_deg.p; p.ns_i = c.ns_i.p; p.ns_m = c.ns_m.p; p.ns_d1 = c.ns_d1.p; p.ns_d2 = c.ns_d2.p;
     p.el_g = c.el_g.p; p.el_area = c.el_area.p; p.n_lev = c.n_lev.p; p.n_nbl = c.n_nbl.p; p.n_znb = c.n_znb.p;
     p.area = c.area.p; p.areasvol = c.areasvol.p; p.UV = c.UV.p; p.helem = c.helem.p; p.W = c.W.p; p.We = c.We.p; p.Wi = c.Wi.p;
     p.hnode = c.hnode.p; p.hnode_new = c.hnode_new.p; p.Z3 = c.Z3.p; p.zbar3 = c.zbar3.p; p.Kv = c.Kv.p; p.Ki = c.Ki.p;
@@ -728,6 +746,9 @@ void tracer_step_all(TracerCtx& c) {
     const int LY = (c.nl - 1 + LPT - 1) / LPT;                  // level rows per block: LPT levels per thread cover nl-1 layers
     if (LY * TILE > 512) { fb_set_error(25, "nl too large for the level-row thread mapping (nl-1 <= 48)"); return; }
     const dim3 blk(TILE, LY);
+    // kernels without block-wide exchange run on 8 level rows per block (LPT * 8 = 24 levels) and gridDim.y level chunks
+    const dim3 blk8(TILE, 8);
+    const int nchunk = (c.nl - 1 + LPT * 8 - 1) / (LPT * 8);
     const size_t smt = (size_t)c.nlp * TILE * sizeof(double);   // one [nlp][32] shared array
     const size_t sm_64 = (size_t)c.nlp * 64 * sizeof(double);
     CUDA_CHECK(cudaEventRecord(c.ev0, st));
@@ -739,7 +760,7 @@ void tracer_step_all(TracerCtx& c) {
         KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
         KL("k_lo", k_lo<<<c.myNtiles, blk, 0, st>>>(p));
         if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
-        KL("k_ho_edge", k_ho_edge<<<c.Edtiles, blk, 0, st>>>(p));
+        KL("k_ho_edge", k_ho_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
         KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
         if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
         if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
@@ -770,4 +791,39 @@ const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind, int*
     if (s == "tr_xy_x") { *kind = 2; *ncomp = 2; return (const double*)c.txy.p; }
     if (s == "tr_xy_y") { *kind = 2; *ncomp = 2; *comp = 1; return (const double*)c.txy.p; }
     return nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// self-test of div_by against IEEE division on pseudo-random operand pairs spanning the magnitudes of the tracer
+// path (fluxes 1e-30..1e12, areas 1e4..1e12) plus exact-quotient and tiny/zero numerators
+__global__ void k_selftest_div(long long n, unsigned long long* mismatches) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    unsigned long long bad = 0;
+    for (; i < n; i += stride) {
+        unsigned long long h = (unsigned long long)i * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull;
+        h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+        unsigned long long g = h * 0x94D049BB133111EBull; g ^= g >> 31;
+        const double mx = 1.0 + (double)(h & 0xFFFFFFFFFFFFFull) * 2.220446049250313e-16;      // [1,2)
+        const double mb = 1.0 + (double)(g & 0xFFFFFFFFFFFFFull) * 2.220446049250313e-16;
+        const int ex = (int)((h >> 52) % 140) - 100, eb = (int)((g >> 52) % 28) + 12;
+        double x = ldexp(mx, ex), b = ldexp(mb, eb);
+        if ((i & 15) == 0) x = b * (double)(int)(h >> 58);          // exact quotients
+        if ((i & 1023) == 1) x = 0.0;
+        if (g >> 63) x = -x;
+        const double rb = 1.0 / b;
+        if (div_by(x, b, rb) != x / b) bad++;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+extern "C" void fb200_selftest_div(long long* n, long long* mismatches) {
+    unsigned long long* d = nullptr;
+    *mismatches = -1;
+    if (cudaMalloc(&d, sizeof(unsigned long long)) != cudaSuccess) { fb_set_error(12, "no CUDA device: libfesom_b200 has no CPU fallback"); return; }
+    cudaMemset(d, 0, sizeof(unsigned long long));
+    k_selftest_div<<<148 * 8, 256>>>(*n, d); LAUNCH_CHECK();
+    unsigned long long h = 0;
+    CUDA_CHECK(cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    *mismatches = (long long)h;
 }

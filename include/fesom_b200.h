@@ -86,6 +86,9 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old);   /* push + so
 void fb200_debug_fetch(const char* name, double* out);
 void fb200_finalize(void);
 
+/* self-test: compares the reciprocal-based exact division used inside the kernels with IEEE '/' on *n operand pairs */
+void fb200_selftest_div(long long* n, long long* mismatches);
+
 /* 0 = ok; otherwise the code of the first error since the last fb200_clear_status() */
 int fb200_status(void);
 const char* fb200_status_message(void);

@@ -90,3 +90,10 @@ def test_device_resident_steps_equal_push_pull_steps():
         eng.solve()
     eng.pull_tracers(b_tr, b_tro)
     assert np.array_equal(a_tr, b_tr) and np.array_equal(a_tro, b_tro)
+
+
+def test_div_by_matches_ieee_division():
+    """the kernels divide several fluxes by the same areasvol through one reciprocal + an exact-residual correction;
+    it must round exactly like '/' (bit-exact parity with the reference's divisions depends on it)"""
+    from fesom2_b200 import api
+    assert api.selftest_div(1 << 24) == 0
