@@ -437,7 +437,7 @@ __device__ __forceinline__ double limited_fv(const KP& p, int b, int nz, int nzm
 // K7a: b3 limiting + oce_tra_adv_flux2dtracer (oce_adv_tra_driver.F90:223-268) + del_ttf assembly
 // (oce_ale_tracer.F90:240) + diff_part_hor_redi (:934-1077) + T* update (:294-305).  Node-kernel mapping.
 // Writes tstar; tr_arr_old = tr_arr is done by the caller for all entries.
-__global__ void LB(512) k_update(KP p) {
+__global__ void __launch_bounds__(512, 2) k_update(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
     const double* __restrict__ T = p.T;
