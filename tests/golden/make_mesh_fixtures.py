@@ -15,3 +15,12 @@ for name in ("pi", "soufflet"):
     m = read_mesh_files(os.path.join("/root/reference/test/meshes", name))
     np.savez_compressed(os.path.join(HERE, name + "_mesh.npz"), **m)
     print(name, {k: (v.shape if hasattr(v, "shape") else v) for k, v in m.items()})
+
+# the reference's own 2-way partition of the pi mesh (test/meshes/pi/dist_2: rpart.out, my_listNNNNN.out)
+from fesom2_b200 import partition as P  # noqa: E402
+d = {"part": P.read_rpart("/root/reference/test/meshes/pi/dist_2", 2)}
+for me in range(2):
+    for k, v in P.read_my_list("/root/reference/test/meshes/pi/dist_2", me).items():
+        d["%s_%d" % (k, me)] = v
+np.savez_compressed(os.path.join(HERE, "pi_dist2.npz"), **d)
+print("pi_dist2", {k: (v.shape if hasattr(v, "shape") and v.shape else v) for k, v in d.items()})

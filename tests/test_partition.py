@@ -1,0 +1,95 @@
+"""CPU tests of the multi-partition path (no GPU): partition lists against the reference's own dist_2 files
+(packed into tests/golden/pi_dist2.npz by tests/golden/make_mesh_fixtures.py), and the oracle run partition by
+partition with the reference's halo exchanges between its phases against the oracle on the undivided mesh.
+Because local numbering keeps ascending global order, own-node results must be IDENTICAL (bit for bit)."""
+import os
+
+import numpy as np
+import pytest
+
+from fesom2_b200 import partition as P
+from oracle import binding as ob
+from tests import util
+
+
+def test_lists_match_reference_dist_files():
+    g = np.load(os.path.join(util.GOLD, "pi_dist2.npz"))
+    hm = util.build_model("pi")
+    ranks = P.build_partition(hm, g["part"], 2)
+    for me, r in enumerate(ranks):
+        for k in ("myDim_nod2D", "eDim_nod2D", "myDim_elem2D", "eDim_elem2D", "eXDim_elem2D", "myDim_edge2D"):
+            assert getattr(r, k) == int(g["%s_%d" % (k, me)]), k
+        assert np.array_equal(r.nod[:r.myDim_nod2D], g["myList_nod2D_%d" % me][:r.myDim_nod2D])
+        assert set(r.nod) == set(g["myList_nod2D_%d" % me])
+        assert np.array_equal(r.elem[:r.myDim_elem2D], g["myList_elem2D_%d" % me][:r.myDim_elem2D])
+        assert set(r.elem) == set(g["myList_elem2D_%d" % me])
+        assert np.array_equal(r.edge, g["myList_edge2D_%d" % me][:r.myDim_edge2D])
+
+
+def test_exchange_lists_are_consistent():
+    hm = util.build_model("band")
+    part = P.contiguous_partition(hm, 3)
+    ranks = P.build_partition(hm, part, 3)
+    for kind in ("nod", "elem"):
+        ids = [(r.nod if kind == "nod" else r.elem).astype(np.float64).copy() for r in ranks]
+        for me, r in enumerate(ranks):                       # poison the halo, then exchange global ids
+            ids[me][(r.myDim_nod2D if kind == "nod" else r.myDim_elem2D):] = -1
+        P.exchange_host(ranks, ids, kind)
+        for me, r in enumerate(ranks):
+            assert np.array_equal(ids[me], (r.nod if kind == "nod" else r.elem).astype(np.float64)), (kind, me)
+
+
+def run_partitioned_oracle(hm, part, npes, opts=None, steps=1):
+    opts = opts or {}
+    ranks = P.build_partition(hm, part, npes)
+    lms = [P.local_model(hm, r, part) for r in ranks]
+    ors = [ob.TracerOracle(lm, **opts) for lm in lms]
+    nl = hm.ipar("nl")
+    ntr = hm.ipar("num_tracers")
+    for _ in range(steps):
+        for tr in range(1, ntr + 1):
+            for o in ors:
+                o.phase(1, tr)
+            P.exchange_host(ranks, [o.work("tr_xy", (2, nl - 1, r.elem.size)) for o, r in zip(ors, ranks)], "elem")
+            for o in ors:
+                o.phase(2, tr)
+            for o in ors:
+                o.phase(3, tr)
+            P.exchange_host(ranks, [o.work("fct_LO", (nl - 1, r.nod.size)) for o, r in zip(ors, ranks)], "nod")
+            for o in ors:
+                o.phase(4, tr)
+            for nm in ("fct_plus", "fct_minus"):
+                P.exchange_host(ranks, [o.work(nm, (nl - 1, r.nod.size)) for o, r in zip(ors, ranks)], "nod")
+            for o in ors:
+                o.phase(5, tr)
+            P.exchange_host(ranks, [lm["tr_arr"][tr - 1] for lm in lms], "nod")
+        for o in ors:
+            o.final()
+    return ranks, lms
+
+
+@pytest.mark.parametrize("name,npes,opts", [("pi", 2, {}), ("band", 3, {}), ("soufflet", 2, {"tra_adv_hor": "MUSCL"})])
+def test_partitioned_oracle_equals_undivided_oracle(name, npes, opts):
+    hm = util.build_model(name)
+    part = P.contiguous_partition(hm, npes)
+    ranks, lms = run_partitioned_oracle(hm, part, npes, opts, steps=2)
+    o = ob.TracerOracle(hm, **opts)
+    o.step()
+    o.step()
+    for r, lm in zip(ranks, lms):
+        own = r.nod[:r.myDim_nod2D] - 1
+        alln = r.nod - 1
+        for k in range(hm.ipar("num_tracers")):
+            assert np.array_equal(lm["tr_arr"][k][:r.myDim_nod2D], hm["tr_arr"][k][own])
+            assert np.array_equal(lm["tr_arr"][k], hm["tr_arr"][k][alln])          # halo too, after the last exchange
+            assert np.array_equal(lm["tr_arr_old"][k][:r.myDim_nod2D], hm["tr_arr_old"][k][own])
+
+
+def test_reference_metis_partition_of_pi():
+    g = np.load(os.path.join(util.GOLD, "pi_dist2.npz"))
+    hm = util.build_model("pi")
+    ranks, lms = run_partitioned_oracle(hm, g["part"], 2)
+    ob.TracerOracle(hm).step()
+    for r, lm in zip(ranks, lms):
+        own = r.nod[:r.myDim_nod2D] - 1
+        assert np.array_equal(lm["tr_arr"][:, :r.myDim_nod2D], hm["tr_arr"][:, own])
