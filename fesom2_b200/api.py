@@ -23,7 +23,7 @@ EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb20
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
-           "fb200_selftest_div"]
+           "fb200_selftest_div", "fb200_init_halo", "fb200_comm_unique_id", "fb200_comm_init", "fb200_comm_finalize"]
 
 
 class FesomB200Error(RuntimeError):
@@ -102,6 +102,28 @@ def profile_report():
     return out
 
 
+def comm_init(dist=None, rank=None, world=None):
+    """collective: NCCL communicator of the library (fb200_comm_unique_id on rank 0, broadcast, fb200_comm_init).
+    `dist` is an initialised torch.distributed module (any backend) used only to broadcast the 128-byte id — the
+    Fortran host does the same with MPI_Bcast."""
+    L = lib()
+    rank = dist.get_rank() if rank is None else rank
+    world = dist.get_world_size() if world is None else world
+    buf = C.create_string_buffer(128)
+    if rank == 0:
+        L.fb200_comm_unique_id(buf)
+    obj = [bytes(buf.raw)]
+    if world > 1:
+        dist.broadcast_object_list(obj, src=0)
+    idb = C.create_string_buffer(obj[0], 128)
+    L.fb200_comm_init(_i(world), _i(rank), idb)
+    _check(L)
+
+
+def comm_finalize():
+    lib().fb200_comm_finalize()
+
+
 class TracerEngine:
     """Device-side `solve_tracers_ale`.  `hm` is a HostModel (the Fortran driver's state)."""
 
@@ -128,6 +150,18 @@ class TracerEngine:
                             _i(ws), _i(i_vert_diff), _i(Redi), _i(use_sw_pene), _i(do_hor_diff), _i(clamp_salt),
                             _d(hm.par("is_nonlinfs")), _d(hm.par("dt")), _d(epsilon), ids)
         _check(L)
+        try:
+            npes = hm.ipar("npes")
+        except RuntimeError:
+            npes = 1
+        if npes > 1:                                   # com_nod2D / com_elem2D_full of this partition
+            cn = [a("com_nod2D_" + k) for k in ("rPE", "rptr", "rlist", "sPE", "sptr", "slist")]
+            ce = [a("com_elem2D_full_" + k) for k in ("rPE", "rptr", "rlist", "sPE", "sptr", "slist")]
+            L.fb200_init_halo(_i(hm.ipar("com_nod2D_rPEnum")), _p(cn[0]), _p(cn[1]), _p(cn[2]),
+                              _i(hm.ipar("com_nod2D_sPEnum")), _p(cn[3]), _p(cn[4]), _p(cn[5]),
+                              _i(hm.ipar("com_elem2D_full_rPEnum")), _p(ce[0]), _p(ce[1]), _p(ce[2]),
+                              _i(hm.ipar("com_elem2D_full_sPEnum")), _p(ce[3]), _p(ce[4]), _p(ce[5]))
+            _check(L)
         L.fb200_init_commit()
         _check(L)
 

@@ -53,6 +53,18 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
               "--fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 
 
+def nccl_flags():
+    """NCCL to link against: the copy bundled with PyTorch when there is one (both libraries have the soname
+    libnccl.so.2, and a process that also imports torch must not end up with the older system copy loaded first),
+    else the system library.  A Fortran-only host links the system NCCL."""
+    for sp in sys.path:
+        lib = os.path.join(sp, "nvidia", "nccl", "lib")
+        inc = os.path.join(sp, "nvidia", "nccl", "include")
+        if os.path.exists(os.path.join(lib, "libnccl.so.2")) and os.path.exists(os.path.join(inc, "nccl.h")):
+            return ["-I", inc, "-L", lib, "-l:libnccl.so.2", "-Xlinker", "-rpath", "-Xlinker", lib]
+    return ["-lnccl"]
+
+
 def build_cuda(force=False, verbose=False):
     src = sorted(glob.glob(os.path.join(PKG, "csrc", "*.cu")))
     dep = src + glob.glob(os.path.join(PKG, "csrc", "*.cuh")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
@@ -63,7 +75,7 @@ def build_cuda(force=False, verbose=False):
         flags = list(NVCC_FLAGS)
         if verbose:
             flags += ["-Xptxas", "-v"]
-        out = _run([nvcc] + flags + ["-I", os.path.join(ROOT, "include"), "-o", CUDA_SO] + src + ["-lnccl"])
+        out = _run([nvcc] + flags + ["-I", os.path.join(ROOT, "include"), "-o", CUDA_SO] + src + nccl_flags())
         if verbose:
             print(out)
     return CUDA_SO

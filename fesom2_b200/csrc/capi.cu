@@ -1,5 +1,6 @@
 // extern "C" entry points of the tracer path (include/fesom_b200.h).  Plain pointers and sizes only.
 #include "common.cuh"
+#include "comm.cuh"
 #include "fesom_b200.h"
 #include <cstring>
 
@@ -78,6 +79,17 @@ void fb200_set_options(int* tra_adv_hor, int* tra_adv_ver, int* tra_adv_lim, dou
     o.clamp_salt = *clamp_salt; o.is_nonlinfs = *is_nonlinfs; o.dt = *dt; o.epsilon = *epsilon;
     for (int k = 0; k < c.ntr && k < 8; k++) o.tracer_id[k] = tracer_id[k];
     if (o.tra_adv_hor < 0 || o.tra_adv_hor > 2 || o.tra_adv_ver < 0 || o.tra_adv_ver > 3) fb_set_error(32, "unknown advection scheme");
+}
+
+void fb200_init_halo(int* nod_rPEnum, int* nod_rPE, int* nod_rptr, int* nod_rlist, int* nod_sPEnum, int* nod_sPE, int* nod_sptr, int* nod_slist,
+                     int* elem_rPEnum, int* elem_rPE, int* elem_rptr, int* elem_rlist, int* elem_sPEnum, int* elem_sPE, int* elem_sptr,
+                     int* elem_slist) {
+    TracerCtx& c = tctx();
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fb_set_error(12, "no CUDA device: libfesom_b200 has no CPU fallback"); return; }
+    if (!c.halo_nod) { c.halo_nod = new HaloPlan(); c.halo_elem = new HaloPlan(); }
+    halo_plan_build(*c.halo_nod, *nod_rPEnum, nod_rPE, nod_rptr, nod_rlist, *nod_sPEnum, nod_sPE, nod_sptr, nod_slist);
+    halo_plan_build(*c.halo_elem, *elem_rPEnum, elem_rPE, elem_rptr, elem_rlist, *elem_sPEnum, elem_sPE, elem_sptr, elem_slist);
 }
 
 void fb200_init_commit(void) { ctx_commit(tctx()); }

@@ -67,6 +67,7 @@ template <class T> struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
 };
 
+struct HaloPlan;
 struct TracerCtx {
     // dimensions
     int nl = 0, nlp = 0, myN = 0, N = 0, myE = 0, E = 0, Eall = 0, myEd = 0, ntr = 0;
@@ -106,6 +107,8 @@ struct TracerCtx {
     DevBuf<double> trz, LO, adf_h, adf_v, tstar;
     // staging for host<->device transfers (reference layout)
     DevBuf<double> stage;
+    // halo plans of com_nod2D / com_elem2D_full (fb200_init_halo); null on a single partition
+    HaloPlan* halo_nod = nullptr; HaloPlan* halo_elem = nullptr;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;

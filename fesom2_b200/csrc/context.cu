@@ -1,6 +1,7 @@
 // Context of the tracer path: error status, building the device-side mesh tables from the Fortran arrays
 // (fb200_init_* -> fb200_init_commit), and restaging between the reference layout and the tiled layout.
 #include "common.cuh"
+#include "comm.cuh"
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -273,6 +274,8 @@ void ctx_release(TracerCtx& c) {
     c.UV.release(); c.txy.release(); c.fpm.release();
     c.edge.release(); c.edgeho.release(); c.ne_slot.release(); c.nie_slot.release(); c.el_nb.release(); c.el_lev.release();
     c.n_lev.release(); c.n_nbl.release();
+    if (c.halo_nod) { c.halo_nod->release(); delete c.halo_nod; }
+    if (c.halo_elem) { c.halo_elem->release(); delete c.halo_elem; }
     if (c.ev0) cudaEventDestroy(c.ev0);
     if (c.ev1) cudaEventDestroy(c.ev1);
     c = TracerCtx();

@@ -10,6 +10,7 @@
 // no floating-point atomics); scalars (alpha, sigma, beta, rho, omega) never leave the device; the host
 // polls a "done" flag every few iterations.
 #include "common.cuh"
+#include "comm.cuh"
 #include "fesom_b200.h"
 #include <algorithm>
 #include <cmath>
@@ -25,7 +26,8 @@ struct SolverScal {             // device-resident scalars
 };
 
 struct Solver {
-    int n = 0, nnz = 0, nslice = 0, bs = 1, nblk = 0, reuse = 0, maxits = 2000;
+    int n = 0, nloc = 0, nnz = 0, nslice = 0, bs = 1, nblk = 0, reuse = 0, maxits = 2000;   // nloc = own rows + halo columns
+    HaloPlan halo;                            // interface unknowns needed by the off-diagonal block (parms_comm.c)
     double soltol = 1e-10;
     std::vector<int> rp, ci;                 // host copies (psolve.c:83-99)
     DevBuf<int> d_rp, d_ci, d_sptr, d_scol;  // CSR + SELL structure
@@ -116,6 +118,27 @@ __device__ __forceinline__ void reduce2(double a, double b, double* __restrict__
     }
 }
 
+// scalar recurrences of bicgstab_ras.c once the (global) sums tmp0, tmp1 of a reduction are known.  On one rank the
+// last block of the producing kernel calls it directly; on several ranks the host enqueues an all-reduce of
+// (tmp0, tmp1) and then k_apply_scalars, so that every rank takes identical decisions.
+enum { SC_INIT = 0, SC_ALPHA = 1, SC_SIGMA = 2, SC_XUPD = 3 };
+__device__ __forceinline__ void apply_scalars(SolverScal* sc, int which) {
+    const double ta = sc->tmp0, tb = sc->tmp1;
+    if (which == SC_INIT) {
+        sc->omega = ta; sc->rho = tb; sc->alpha = 0.; sc->sigma = 1.0; sc->rho_alt = 1.0; sc->its = 0;
+        sc->done = (ta > sc->tol2) ? 0 : 1;
+    } else if (which == SC_ALPHA) sc->alpha = sc->rho / ta;
+    else if (which == SC_SIGMA) sc->sigma = ta / tb;
+    else {
+        sc->omega = ta; sc->its = sc->its + 1;
+        // runs after every block of the producing launch has passed its own `done` test, so raising it here is safe
+        if (ta < sc->tol2 || sc->its >= sc->maxits) sc->done = 1;
+        else { sc->rho = tb; sc->beta = (tb * sc->alpha) / (sc->rho_alt * sc->sigma); sc->rho_alt = tb; }
+    }
+}
+__global__ void k_apply_scalars(SolverScal* sc, int which) { if (which == SC_INIT || !sc->done) apply_scalars(sc, which); }
+#define FIN(which) [=](double ta, double tb) { sc->tmp0 = ta; sc->tmp1 = tb; if (!multi) apply_scalars(sc, which); }
+
 // block-Jacobi apply for one row: z_i = sum_c Binv[blk][c][i_loc] * in[b0 + c]   (bs == 1: z = dinv * in)
 __device__ __forceinline__ double bj_row(const double* __restrict__ binv, const double* in, int i, int n, int bs) {
     if (bs == 1) return binv[i] * in[i];
@@ -130,7 +153,7 @@ __device__ __forceinline__ double bj_row(const double* __restrict__ binv, const 
 __global__ void __launch_bounds__(SBS) k_init_res(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                   const double* __restrict__ rhs, const double* __restrict__ scale, const double* __restrict__ x,
                                                   double* __restrict__ y, double* __restrict__ r, double* __restrict__ p,
-                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc) {
+                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
     const int i = blockIdx.x * SBS + threadIdx.x;
     double a = 0.0, b = 0.0;
     if (i < n) {
@@ -139,10 +162,7 @@ __global__ void __launch_bounds__(SBS) k_init_res(int n, const int* __restrict__
         y[i] = yi; r[i] = ri; p[i] = ri;
         a = ri * ri; b = yi * ri;
     }
-    reduce2(a, b, partial, counter, nblocks, [=](double ta, double tb) {
-        sc->omega = ta; sc->rho = tb; sc->alpha = 0.; sc->sigma = 1.0; sc->rho_alt = 1.0; sc->its = 0;
-        sc->done = (ta > sc->tol2) ? 0 : 1;
-    });
+    reduce2(a, b, partial, counter, nblocks, FIN(SC_INIT));
 }
 __global__ void __launch_bounds__(SBS) k_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ in, double* __restrict__ out,
                                             const SolverScal* sc) {
@@ -153,12 +173,12 @@ __global__ void __launch_bounds__(SBS) k_pc(int n, int bs, const double* __restr
 // v = A pt ; alpha = rho / (r0 . v)                                        bicgstab_ras.c:161-164
 __global__ void __launch_bounds__(SBS) k_spmv_alpha(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                     const double* __restrict__ pt, const double* __restrict__ r0, double* __restrict__ v,
-                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc) {
+                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
     if (sc->done) return;
     const int i = blockIdx.x * SBS + threadIdx.x;
     double a = 0.0;
     if (i < n) { const double vi = sell_row(sptr, scol, sval, pt, i); v[i] = vi; a = r0[i] * vi; }
-    reduce2(a, 0.0, partial, counter, nblocks, [=](double ta, double) { sc->alpha = sc->rho / ta; });
+    reduce2(a, 0.0, partial, counter, nblocks, FIN(SC_ALPHA));
 }
 // r -= alpha v ; st = M r                                                   bicgstab_ras.c:166-175
 __global__ void __launch_bounds__(SBS) k_r_update_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ v,
@@ -174,17 +194,17 @@ __global__ void __launch_bounds__(SBS) k_r_update_pc(int n, int bs, const double
 // t = A st ; sigma = (t.r)/(t.t)                                            bicgstab_ras.c:179-197
 __global__ void __launch_bounds__(SBS) k_spmv_sigma(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                     const double* __restrict__ st, const double* __restrict__ r, double* __restrict__ t,
-                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc) {
+                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
     if (sc->done) return;
     const int i = blockIdx.x * SBS + threadIdx.x;
     double a = 0.0, b = 0.0;
     if (i < n) { const double ti = sell_row(sptr, scol, sval, st, i); t[i] = ti; a = ti * r[i]; b = ti * ti; }
-    reduce2(a, b, partial, counter, nblocks, [=](double ta, double tb) { sc->sigma = ta / tb; });
+    reduce2(a, b, partial, counter, nblocks, FIN(SC_SIGMA));
 }
 // r -= sigma t ; x += alpha pt + sigma st ; omega = r.r ; rho = r0.r ; convergence test ; beta     :200-225
 __global__ void __launch_bounds__(SBS) k_x_update(int n, const double* __restrict__ t, const double* __restrict__ pt, const double* __restrict__ st,
                                                   const double* __restrict__ r0, double* __restrict__ r, double* __restrict__ x,
-                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc) {
+                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
     if (sc->done) return;
     const int i = blockIdx.x * SBS + threadIdx.x;
     const double alpha = sc->alpha, sigma = sc->sigma;
@@ -195,12 +215,7 @@ __global__ void __launch_bounds__(SBS) k_x_update(int n, const double* __restric
         x[i] += alpha * pt[i] + sigma * st[i];
         a = ri * ri; b = r0[i] * ri;
     }
-    reduce2(a, b, partial, counter, nblocks, [=](double ta, double tb) {
-        sc->omega = ta; sc->its = sc->its + 1;
-        // the last block runs this after every block of the launch has passed its own `done` test, so raising it here is safe
-        if (ta < sc->tol2 || sc->its >= sc->maxits) sc->done = 1;
-        else { sc->rho = tb; sc->beta = (tb * sc->alpha) / (sc->rho_alt * sc->sigma); sc->rho_alt = tb; }
-    });
+    reduce2(a, b, partial, counter, nblocks, FIN(SC_XUPD));
 }
 // p = r + beta (p - sigma v) ; pt = M p                                     bicgstab_ras.c:227-230, 150-156
 __global__ void __launch_bounds__(SBS) k_p_update_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ r, const double* __restrict__ v,
@@ -263,23 +278,73 @@ void fb200_psolver_set_block(int* block) {
     g_block = b;
 }
 
+// which rows of this rank the other ranks need, and which columns of theirs this rank needs: the interface-variable
+// setup of parms_MatSetup (lib/parms/src/parms_mat_dvcsr.c:93-600).  Requests travel as ints over NCCL.
+static bool setup_halo(Solver& S, const int* part, const std::vector<int>& gcols_sorted /* unique remote global columns */) {
+    const int np = comm_nranks(), me = comm_rank();
+    cudaStream_t st = S.stream;
+    std::vector<int> rPE, rptr{1}, rlist, req_cnt(np, 0);
+    std::vector<std::vector<int>> req(np);
+    int h = 0;
+    for (int g : gcols_sorted) {
+        int pe = int(std::upper_bound(part, part + np + 1, g) - part) - 1;
+        if (pe < 0 || pe >= np || pe == me) { fb_set_error(44, "psolver_init: column outside the global numbering"); return false; }
+        req[pe].push_back(g - part[pe]);                       // row of the owner, 0-based local
+        rlist.push_back(S.n + h + 1); h++;
+    }
+    for (int pe = 0; pe < np; pe++) if (!req[pe].empty()) { rPE.push_back(pe); rptr.push_back(rptr.back() + (int)req[pe].size()); req_cnt[pe] = (int)req[pe].size(); }
+    // all-gather the request counts: cnt[q][p] = how many rows rank q wants from rank p
+    DevBuf<int> d_cnt, d_all;
+    d_cnt.upload(req_cnt); d_all.alloc((size_t)np * np);
+    NCCL_CHECK(ncclAllGather(d_cnt.p, d_all.p, np, ncclInt32, comm_handle(), st));
+    std::vector<int> all((size_t)np * np);
+    CUDA_CHECK(cudaMemcpyAsync(all.data(), d_all.p, all.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    std::vector<int> sPE, sptr{1};
+    for (int q = 0; q < np; q++) if (q != me && all[(size_t)q * np + me] > 0) { sPE.push_back(q); sptr.push_back(sptr.back() + all[(size_t)q * np + me]); }
+    // exchange the requested row lists
+    std::vector<int> flat;
+    for (int pe : rPE) flat.insert(flat.end(), req[pe].begin(), req[pe].end());
+    DevBuf<int> d_req, d_snd;
+    d_req.upload(flat); d_snd.alloc(sptr.back() - 1);
+    NCCL_CHECK(ncclGroupStart());
+    for (size_t k = 0; k < sPE.size(); k++) NCCL_CHECK(ncclRecv(d_snd.p + (sptr[k] - 1), sptr[k + 1] - sptr[k], ncclInt32, sPE[k], comm_handle(), st));
+    for (size_t k = 0; k < rPE.size(); k++) NCCL_CHECK(ncclSend(d_req.p + (rptr[k] - 1), rptr[k + 1] - rptr[k], ncclInt32, rPE[k], comm_handle(), st));
+    NCCL_CHECK(ncclGroupEnd());
+    std::vector<int> slist(sptr.back() - 1);
+    if (!slist.empty()) CUDA_CHECK(cudaMemcpyAsync(slist.data(), d_snd.p, slist.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    for (int& v : slist) { if (v < 0 || v >= S.n) { fb_set_error(45, "psolver_init: a neighbour requested a row this rank does not own"); return false; } v += 1; }
+    halo_plan_build(S.halo, (int)rPE.size(), rPE.data(), rptr.data(), rlist.data(), (int)sPE.size(), sPE.data(), sptr.data(), slist.data());
+    d_cnt.release(); d_all.release(); d_req.release(); d_snd.release();
+    return fb_ok();
+}
+
 void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* ilulevel, int* fillin, double* droptol, int* maxits,
                   int* restart, double* soltol, int* part, int* rptr, int* cols, double* vals, int* reuse, int* fcomm) {
     (void)stype; (void)pctype; (void)pcilutype; (void)ilulevel; (void)fillin; (void)droptol; (void)restart; (void)fcomm;
     if (!fb_ok()) return;
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fb_set_error(12, "no CUDA device: libfesom_b200 has no CPU fallback"); return; }
+    const int np = comm_nranks(), me = comm_rank();
     Solver* S = new Solver();
-    S->n = part[1] - part[0];                                  // one partition per process (psolve.c:38-53, nproc == 1 branch)
+    S->n = part[me + 1] - part[me];                            // rows of this partition (psolve.c:38-43)
     S->nnz = rptr[S->n]; S->reuse = *reuse; S->maxits = *maxits; S->soltol = *soltol; S->bs = g_block;
     S->rp.assign(rptr, rptr + S->n + 1);
     S->ci.resize(S->nnz);
-    for (int j = 0; j < S->nnz; j++) {
-        const int c = cols[j] - part[0];
-        if (c < 0 || c >= S->n) { fb_set_error(42, "psolver_init: column outside the local partition (multi-partition solve needs the halo setup)"); delete S; return; }
-        S->ci[j] = c;
-    }
     S->stream = fb_stream(); CUDA_CHECK(cudaEventCreate(&S->ev0)); CUDA_CHECK(cudaEventCreate(&S->ev1));
+    // local column numbering: own columns first, then the remote ones in ascending global order (= grouped by owner)
+    std::vector<int> remote;
+    for (int j = 0; j < S->nnz; j++) { const int c = cols[j]; if (c < part[me] || c >= part[me + 1]) remote.push_back(c); }
+    std::sort(remote.begin(), remote.end()); remote.erase(std::unique(remote.begin(), remote.end()), remote.end());
+    if (!remote.empty() && np == 1) { fb_set_error(42, "psolver_init: column outside the local partition but only one rank (fb200_comm_init missing?)"); delete S; return; }
+    for (int j = 0; j < S->nnz; j++) {
+        const int c = cols[j];
+        if (c >= part[me] && c < part[me + 1]) S->ci[j] = c - part[me];
+        else S->ci[j] = S->n + int(std::lower_bound(remote.begin(), remote.end(), c) - remote.begin());
+    }
+    S->nloc = S->n + (int)remote.size();
+    if (np > 1 && !setup_halo(*S, part, remote)) { delete S; return; }
     const int n = S->n;
     S->nslice = (n + 31) / 32;
     S->nblocks = (n + SBS - 1) / SBS;
@@ -296,7 +361,7 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
     }
     S->d_rp.upload(S->rp); S->d_ci.upload(S->ci); S->d_sptr.upload(sptr); S->d_scol.upload(scol);
     S->d_vals.alloc(S->nnz); S->d_sval.alloc(scol.size()); S->d_scale.alloc(n);
-    for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs}) b->alloc(n);
+    for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs}) b->alloc(S->nloc);
     S->partial.alloc((size_t)2 * S->nblocks); S->scal.alloc(1); S->counter.alloc(1);
     upload_values(*S, vals);
     build_binv(*S, vals);
@@ -323,8 +388,13 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     SolverScal h; memset(&h, 0, sizeof(h));
     h.tol2 = S.soltol * S.soltol; h.maxits = S.maxits;
     CUDA_CHECK(cudaMemcpyAsync(S.scal.p, &h, sizeof(h), cudaMemcpyHostToDevice, st));
+    const int multi = comm_nranks() > 1 ? 1 : 0;
+    // one global reduction: all-reduce of (tmp0, tmp1) + the scalar recurrences on every rank
+#define REDUCE(which) do { if (multi) { comm_allreduce_sum(&S.scal.p->tmp0, 2, st); k_apply_scalars<<<1, 1, 0, st>>>(S.scal.p, which); LAUNCH_CHECK(); } } while (0)
+    if (multi) halo_exchange_flat(S.halo, S.x.p, st);                            // interface values of the initial guess
     { ProfScope ps_("k_init_res", st); k_init_res<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
-                                   S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
+                                   S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+    REDUCE(SC_INIT);
     { ProfScope ps_("k_pc", st); k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
     int done = 0, launched = 0;
     const int poll = 8;
@@ -332,16 +402,22 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     SolverScal* hs = S.h_scal;
     while (!done && launched < S.maxits && fb_ok()) {
         for (int k = 0; k < poll && launched < S.maxits; k++, launched++) {
-            { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
+            if (multi) halo_exchange_flat(S.halo, S.pt.p, st);                   // parms_MatVec: interface exchange of the SpMV input
+            { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+            REDUCE(SC_ALPHA);
             { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
-            { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
-            { ProfScope ps_("k_x_update", st); k_x_update<<<nb, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nb, S.scal.p); LAUNCH_CHECK(); }
+            if (multi) halo_exchange_flat(S.halo, S.st.p, st);
+            { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+            REDUCE(SC_SIGMA);
+            { ProfScope ps_("k_x_update", st); k_x_update<<<nb, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+            REDUCE(SC_XUPD);
             { ProfScope ps_("k_p_update_pc", st); k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
         }
         CUDA_CHECK(cudaMemcpyAsync(hs, S.scal.p, sizeof(SolverScal), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
         done = hs->done;
     }
+#undef REDUCE
     if (fb_ok()) {
         S.last_its = hs->its; S.last_res = sqrt(hs->omega);
         if (hs->its >= S.maxits && hs->omega > h.tol2) printf("ERROR: no convergence\n");   // bicgstab_ras.c:237-238
@@ -363,6 +439,7 @@ void psolver_final(void) {
         Solver* S = kv.second;
         if (S->stream) cudaStreamSynchronize(S->stream);
         for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs, &S->d_vals, &S->d_sval, &S->d_scale, &S->d_binv, &S->partial}) b->release();
+        S->halo.release();
         S->d_rp.release(); S->d_ci.release(); S->d_sptr.release(); S->d_scol.release(); S->scal.release(); S->counter.release();
         if (S->ev0) cudaEventDestroy(S->ev0);
         if (S->ev1) cudaEventDestroy(S->ev1);

@@ -6,6 +6,7 @@
 // node, so sums are reproduced term by term without atomics.  Arithmetic follows the Fortran expression order
 // (compiled with --fmad=false) — see the file:line notes at each kernel.
 #include "common.cuh"
+#include "comm.cuh"
 
 #define LB(n) __launch_bounds__(n)
 
@@ -752,16 +753,21 @@ void tracer_step_all(TracerCtx& c) {
     const size_t smt = (size_t)c.nlp * TILE * sizeof(double);   // one [nlp][32] shared array
     const size_t sm_64 = (size_t)c.nlp * 64 * sizeof(double);
     CUDA_CHECK(cudaEventRecord(c.ev0, st));
+    const bool multi = comm_nranks() > 1 && c.halo_nod != nullptr;
+    if (comm_nranks() > 1 && !c.halo_nod) { fb_set_error(26, "more than one rank but fb200_init_halo was not called"); return; }
 #define KL(name, ...) do { ProfScope ps_(name, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
     for (int tr = 0; tr < c.ntr; tr++) {
         KP p = make_kp(c, tr);
         const double ca = -(0.5 + c.opt.epsilon), cb = 1.5 + c.opt.epsilon;
         KL("k_ab2", k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb));
         KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
+        if (multi) halo_exchange_tiled(*c.halo_elem, (double*)p.txy, c.nlp, 2, st);       // exchange_elem(tr_xy), oce_tracer_mod.F90:68,72
         KL("k_lo", k_lo<<<c.myNtiles, blk, 0, st>>>(p));
         if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
+        if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);                   // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
         KL("k_ho_edge", k_ho_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
         KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
+        if (multi) halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st);         // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
         if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
         if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
         KL("k_update", k_update<<<c.myNtiles, blk, 0, st>>>(p));
@@ -770,6 +776,7 @@ void tracer_step_all(TracerCtx& c) {
             CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
         }
         KL("k_impl_diff", k_impl_diff<<<c.myNtiles, blk, 6 * smt, st>>>(p));
+        if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
     }
     if (c.opt.clamp_salt && c.ntr >= 2) { KP p = make_kp(c, 1); KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T)); }
 #undef KL

@@ -239,6 +239,10 @@ def local_model(hm, r, part):
     put("ssh_colind", pc[hm["ssh_colind"][gather] - 1].astype(np.int32))
     put("ssh_values", hm["ssh_values"][gather])
     put("part", off)
+    for pre, c in (("com_nod2D", r.com_nod), ("com_elem2D_full", r.com_elem_full)):
+        for k in ("rPE", "rptr", "rlist", "sPE", "sptr", "slist"):
+            put("%s_%s" % (pre, k), np.asarray(c[k], dtype=np.int32) if len(c[k]) else np.zeros(1, dtype=np.int32))
+        lm.set(**{pre + "_rPEnum": len(c["rPE"]), pre + "_sPEnum": len(c["sPE"])})
     lm._ssh_gather = gather                                   # positions of the local nonzeros in the global value array
     return lm
 

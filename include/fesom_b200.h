@@ -68,6 +68,12 @@ void fb200_init_geometry(double* edge_cross_dxdy, double* edge_dxdy, double* ele
 void fb200_set_options(int* tra_adv_hor, int* tra_adv_ver, int* tra_adv_lim, double* tra_adv_ph, double* tra_adv_pv,
                        int* w_split, int* i_vert_diff, int* Redi, int* use_sw_pene, int* do_hor_diff, int* clamp_salt,
                        double* is_nonlinfs, double* dt, double* epsilon, int* tracer_id /* num_tracers */);
+/* halo lists of this partition, the reference's com_nod2D and com_elem2D_full (src/gen_modules_partitioning.F90:17-29,
+ * read from dist_N/com_infoNNNNN.out, src/oce_mesh.F90:568-640): PE ids 0-based, rptr/sptr 1-based offsets, rlist/slist
+ * 1-based local entity numbers.  Only needed on more than one partition; call after fb200_comm_init. */
+void fb200_init_halo(int* nod_rPEnum, int* nod_rPE, int* nod_rptr, int* nod_rlist, int* nod_sPEnum, int* nod_sPE, int* nod_sptr,
+                     int* nod_slist, int* elem_rPEnum, int* elem_rPE, int* elem_rptr, int* elem_rlist, int* elem_sPEnum,
+                     int* elem_sPE, int* elem_sptr, int* elem_slist);
 void fb200_init_commit(void);
 /* per-step inputs produced by the host (shapes: src/oce_setup_step.F90:205-323, src/oce_ale.F90:94-104):
  * UV(2,nl-1,elems) Wvel/Wvel_e/Wvel_i(nl,N) hnode/hnode_new(nl-1,N) helem(nl-1,myDim_elem2D) Z_3d_n(nl-1,N)
@@ -85,6 +91,14 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old);   /* push + so
  * name: "fct_LO","adf_h","adf_v","fct_plus","fct_minus","tr_xy_x","tr_xy_y","ttfAB","tstar" ; returns via status */
 void fb200_debug_fetch(const char* name, double* out);
 void fb200_finalize(void);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Multi-GPU: one process (MPI rank) per GPU, NCCL over NVLink replaces MPI_Isend/Irecv of gen_halo_exchange.F90 and
+ * the solver's MPI_Allreduce.  Rank 0 obtains an id, the host broadcasts its 128 bytes (MPI_Bcast over
+ * MPI_COMM_FESOM), every rank calls fb200_comm_init (collective) after selecting its device (cudaSetDevice). */
+void fb200_comm_unique_id(char* id128);
+void fb200_comm_init(int* nranks, int* rank, char* id128);
+void fb200_comm_finalize(void);
 
 /* self-test: compares the reciprocal-based exact division used inside the kernels with IEEE '/' on *n operand pairs */
 void fb200_selftest_div(long long* n, long long* mismatches);

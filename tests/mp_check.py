@@ -1,0 +1,76 @@
+"""Multi-rank parity check, launched by tests/test_gpu_multi.py (and by hand) as
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/mp_check.py [mesh]
+One rank per GPU.  Every rank builds the same global model, partitions it N ways (src/gen_comm.F90 semantics), keeps its
+own partition, runs the tracer step and the SSH solve through the C ABI with NCCL halo exchange / all-reduce, and
+compares its own nodes with the oracle on the UNDIVIDED mesh: tracers bit for bit, SSH to the solver tolerance."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from fesom2_b200 import api, partition as P
+    from oracle import binding as ob
+    from tests import util
+    name = sys.argv[1] if len(sys.argv) > 1 else "pi"
+    steps = 2
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("gloo")                           # only used to broadcast the NCCL id and gather verdicts
+    hm = util.build_model(name)
+    hm.compute_ssh_rhs()
+    if name == "pi" and world == 2:
+        part = np.load(os.path.join(util.GOLD, "pi_dist2.npz"))["part"]      # the reference's own METIS partition
+    else:
+        part = P.contiguous_partition(hm, world)
+    ranks = P.build_partition(hm, part, world)
+    r = ranks[rank]
+    lm = P.local_model(hm, r, part)
+    api.comm_init(dist)
+    eng = api.TracerEngine(lm)
+    eng.push_step_state()
+    tr, tro = lm["tr_arr"].copy(), lm["tr_arr_old"].copy()
+    eng.push_tracers(tr, tro)
+    for _ in range(steps):
+        eng.solve()
+    eng.pull_tracers(tr, tro)
+    # SSH solve on the partitioned system
+    sol = np.zeros_like(lm["d_eta"])
+    s = api.SSHSolver(lm)
+    s.solve(new_values=1, sol=sol)
+    its, res = s.info()
+    # oracle on the undivided mesh
+    o = ob.TracerOracle(hm)
+    for _ in range(steps):
+        o.step()
+    rp = hm["ssh_rowptr"]
+    n = hm.ipar("myDim_nod2D")
+    x_ref, its_ref, res_ref, _ = ob.ssh_solve(rp - rp[0], hm["ssh_colind"] - 1, hm["ssh_values"], hm["ssh_rhs"][:n], np.zeros(n), 1, 1)
+    own = r.nod[:r.myDim_nod2D] - 1
+    alln = r.nod - 1
+    ok_own = bool(np.array_equal(tr[:, :r.myDim_nod2D], hm["tr_arr"][:, own]) and np.array_equal(tro[:, :r.myDim_nod2D], hm["tr_arr_old"][:, own]))
+    ok_halo = bool(np.array_equal(tr, hm["tr_arr"][:, alln]))
+    err_t = float(np.abs(tr[:, :r.myDim_nod2D] - hm["tr_arr"][:, own]).max())
+    err_s = float(util.rel_err(sol[:r.myDim_nod2D], x_ref[own]))
+    verdict = dict(rank=rank, own_bitexact=ok_own, halo_bitexact=ok_halo, tracer_maxabs=err_t, ssh_rel=err_s, its=its, its_ref=its_ref,
+                   res=res, launches=int(api.lib().fb200_kernel_launches()))
+    allv = [None] * world
+    dist.all_gather_object(allv, verdict)
+    eng.close()
+    api.comm_finalize()
+    if rank == 0:
+        for v in allv:
+            print("MPCHECK", v)
+        good = all(v["own_bitexact"] and v["halo_bitexact"] and v["ssh_rel"] < 1e-6 and v["res"] < 1e-10 for v in allv)
+        print("MPCHECK_RESULT", "PASS" if good else "FAIL")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
