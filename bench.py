@@ -180,15 +180,38 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from fesom2_b200 import api
 
-    # ---- workload (host side = what the Fortran driver owns)
+    # ---- workload (host side = what the Fortran driver owns).  N > 1: the SAME global mesh split into N partitions
+    # (strong scaling, BASELINE.json config 5): rank 0 builds + partitions it and ships every rank its partition.
     target = args.nodes
-    need_gb = 19e-6 * target * (args.nl / 49.0) * world            # measured ~18 kB of host state per surface node
+    need_gb = 19e-6 * target * (args.nl / 49.0)                    # measured ~18 kB of host state per surface node
     avail = mem_available_gb()
     reduced = False
     if avail and need_gb * 1.25 > avail:
         target = int(target * avail / (need_gb * 1.25))
         reduced = True
-    hm, info = build_workload(target, args.nl, seed=12345 + rank)
+    from tests import util
+    if world == 1:
+        hm, info = build_workload(target, args.nl, seed=12345)
+    else:
+        from fesom2_b200 import partition as P
+        gloo = dist.new_group(backend="gloo")
+        t0 = time.time()
+        ghm, info = (build_workload(target, args.nl, seed=12345) if rank == 0 else (None, None))
+        box = [info]
+        dist.broadcast_object_list(box, src=0, group=gloo)
+        info = dict(box[0])
+        part = None
+        if rank == 0:
+            part = P.contiguous_partition(ghm, world)
+        hm = P.scatter_local_models(ghm, part, dist, group=gloo)
+        del ghm
+        own = hm.ipar("myDim_nod2D")
+        info["wet_node_layers"] = int(util.wet_mask(hm)[:own].sum())
+        info["nod2D_global"] = info["nod2D"]
+        info["nod2D"] = own
+        info["halo_nodes"] = hm.ipar("eDim_nod2D")
+        info["setup_s"] = round(time.time() - t0, 1)
+        api.comm_init(dist)
     ntr = hm.ipar("num_tracers")
     n_own = hm.ipar("myDim_nod2D")
     units_per_step = info["wet_node_layers"] * ntr
@@ -339,7 +362,7 @@ def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    workload = "synthetic lon/lat-band sphere (|lat|<=80, ~8%% land, ragged bathymetry), ~%d surface nodes/GPU x %d layers, " \
+    workload = "synthetic lon/lat-band sphere (|lat|<=80, ~8%% land, ragged bathymetry), ~%d surface nodes in total x %d layers, " \
                "2 tracers, MFCT+QR4C+FCT, zstar" % (args.nodes, args.nl - 1)
     if args.impl == "reference":
         if rank != 0:
@@ -386,11 +409,11 @@ def main():
             for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
     step_bytes = 344.0 * wet * r["ntr"]                     # 344 B per (node, layer, tracer)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": r["world"], "steps": K, "warmup": args.warmup,
-            "ms_per_step": r["tot_ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": r["tot_ms"] / K, "higher_is_better": True, "scaling": "strong" if r["world"] > 1 else "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": workload, "mesh": {k: info[k] for k in ("nlon", "nlat", "nl", "nod2D", "elem2D", "edge2D", "wet_node_layers")},
-                       "per_gpu": True, "reduced_for_host_memory": r["reduced"], "l2": "inputs larger than L2 (per-field >> 126 MB)",
-                       "parallelism": "1 domain per GPU" if r["world"] == 1 else "%d independent domains, no halo exchange (round 1)" % r["world"],
+            "config": {"workload": workload, "mesh": {k: info[k] for k in ("nlon", "nlat", "nl", "nod2D", "elem2D", "edge2D", "wet_node_layers", "nod2D_global", "halo_nodes") if k in info},
+                       "mesh_is": "global mesh" if r["world"] == 1 else "partition of rank 0", "reduced_for_host_memory": r["reduced"], "l2": "inputs larger than L2 (per-field >> 126 MB)",
+                       "parallelism": "1 domain per GPU" if r["world"] == 1 else "the same global mesh in %d node partitions (contiguous split of the numbering, gen_comm.F90 halo rules), NCCL halo exchange + all-reduce" % r["world"],
                        "ssh_initial_guess": "zero every step", "setup_s": info["setup_s"]},
             "tracer_ms_per_step": r["tra_ms"] / K,
             "ssh": {"ms_per_step": r["ssh_ms"] / K, "iterations": r["its"], "scaled_residual": r["res"], "rows": rows,

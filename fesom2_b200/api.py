@@ -23,7 +23,7 @@ EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb20
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
-           "fb200_selftest_div", "fb200_init_halo", "fb200_comm_unique_id", "fb200_comm_init", "fb200_comm_finalize"]
+           "fb200_selftest_div", "fb200_init_halo", "fb200_comm_unique_id", "fb200_comm_init", "fb200_comm_finalize", "fb200_psolver_use_graph"]
 
 
 class FesomB200Error(RuntimeError):

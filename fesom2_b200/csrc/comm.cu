@@ -87,6 +87,8 @@ void comm_allreduce_sum(double* dev_inout, int count, cudaStream_t st) {
     NCCL_CHECK(ncclAllReduce(dev_inout, dev_inout, count, ncclDouble, ncclSum, g_comm, st));
 }
 
+extern "C" void ssh_drop_graphs();
+
 extern "C" {
 
 void fb200_comm_unique_id(char* id128) {
@@ -97,6 +99,7 @@ void fb200_comm_unique_id(char* id128) {
 }
 
 void fb200_comm_init(int* nranks, int* rank, char* id128) {
+    if (g_comm) { ssh_drop_graphs(); cudaDeviceSynchronize(); }
     if (g_comm) { ncclCommDestroy(g_comm); g_comm = nullptr; }
     g_nranks = *nranks; g_rank = *rank;
     if (g_nranks <= 1) return;
@@ -108,6 +111,8 @@ void fb200_comm_init(int* nranks, int* rank, char* id128) {
 }
 
 void fb200_comm_finalize(void) {
+    ssh_drop_graphs();
+    cudaDeviceSynchronize();
     if (g_comm) { ncclCommDestroy(g_comm); g_comm = nullptr; }
     g_nranks = 1; g_rank = 0;
 }

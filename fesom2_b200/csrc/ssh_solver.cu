@@ -39,11 +39,14 @@ struct Solver {
     int nblocks = 0;
     int last_its = 0; double last_res = 0.0;
     SolverScal* h_scal = nullptr;            // pinned mirror of the device scalars (convergence polling)
+    cudaGraphExec_t graph = nullptr;         // `poll` BiCGStab iterations captured once (kernels + NCCL), replayed per poll
+    cudaStream_t graph_stream = nullptr; int graph_multi = -1, graph_launches = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 static std::map<int, Solver*> g_solvers;
 static int g_block = 1;
+static bool g_use_graph = true;
 static float g_ssh_ms = 0.f;
 double ssh_last_ms() { return (double)g_ssh_ms; }
 
@@ -272,6 +275,13 @@ static void upload_values(Solver& S, const double* vals) {
 
 extern "C" {
 
+// captured graphs hold references into the NCCL communicator: they must go before ncclCommDestroy
+void ssh_drop_graphs() {
+    for (auto& kv : g_solvers) if (kv.second->graph) { cudaGraphExecDestroy(kv.second->graph); kv.second->graph = nullptr; }
+}
+
+void fb200_psolver_use_graph(int* on) { g_use_graph = *on != 0; }
+
 void fb200_psolver_set_block(int* block) {
     const int b = *block;
     if (b < 1 || b > 32 || (b & (b - 1))) { fb_set_error(40, "block-Jacobi block size must be a power of two in 1..32"); return; }
@@ -316,6 +326,8 @@ static bool setup_halo(Solver& S, const int* part, const std::vector<int>& gcols
     CUDA_CHECK(cudaStreamSynchronize(st));
     for (int& v : slist) { if (v < 0 || v >= S.n) { fb_set_error(45, "psolver_init: a neighbour requested a row this rank does not own"); return false; } v += 1; }
     halo_plan_build(S.halo, (int)rPE.size(), rPE.data(), rptr.data(), rlist.data(), (int)sPE.size(), sPE.data(), sptr.data(), slist.data());
+    if (S.halo.nsend()) S.halo.sbuf.alloc(S.halo.nsend());
+    if (S.halo.nrecv()) S.halo.rbuf.alloc(S.halo.nrecv());      // sized now: no allocation may happen during graph capture
     d_cnt.release(); d_all.release(); d_req.release(); d_snd.release();
     return fb_ok();
 }
@@ -400,19 +412,36 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     const int poll = 8;
     if (!S.h_scal) CUDA_CHECK(cudaMallocHost(&S.h_scal, sizeof(SolverScal)));
     SolverScal* hs = S.h_scal;
+    auto iteration = [&]() {
+        if (multi) halo_exchange_flat(S.halo, S.pt.p, st);                       // parms_MatVec: interface exchange of the SpMV input
+        { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+        REDUCE(SC_ALPHA);
+        { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
+        if (multi) halo_exchange_flat(S.halo, S.st.p, st);
+        { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+        REDUCE(SC_SIGMA);
+        { ProfScope ps_("k_x_update", st); k_x_update<<<nb, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+        REDUCE(SC_XUPD);
+        { ProfScope ps_("k_p_update_pc", st); k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
+    };
+    // The iteration is launch-bound on small partitions (17 launches incl. NCCL per iteration on several ranks), so
+    // `poll` iterations are captured into a CUDA graph once and replayed; converged iterations inside a replay are
+    // no-ops (every kernel returns on sc->done).  Per-kernel profiling uses plain launches.
+    const bool use_graph = !prof_on() && g_use_graph;
+    if (use_graph && S.graph && (S.graph_stream != st || S.graph_multi != multi)) { cudaGraphExecDestroy(S.graph); S.graph = nullptr; }
+    if (use_graph && !S.graph) {
+        cudaGraph_t g = nullptr;
+        CUDA_CHECK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        const long long l0 = g_launches;
+        for (int k = 0; k < poll; k++) iteration();
+        S.graph_launches = (int)(g_launches - l0); g_launches = l0;
+        CUDA_CHECK(cudaStreamEndCapture(st, &g));
+        if (g) { CUDA_CHECK(cudaGraphInstantiate(&S.graph, g, 0)); cudaGraphDestroy(g); }
+        S.graph_stream = st; S.graph_multi = multi;
+    }
     while (!done && launched < S.maxits && fb_ok()) {
-        for (int k = 0; k < poll && launched < S.maxits; k++, launched++) {
-            if (multi) halo_exchange_flat(S.halo, S.pt.p, st);                   // parms_MatVec: interface exchange of the SpMV input
-            { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
-            REDUCE(SC_ALPHA);
-            { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
-            if (multi) halo_exchange_flat(S.halo, S.st.p, st);
-            { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
-            REDUCE(SC_SIGMA);
-            { ProfScope ps_("k_x_update", st); k_x_update<<<nb, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
-            REDUCE(SC_XUPD);
-            { ProfScope ps_("k_p_update_pc", st); k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
-        }
+        if (use_graph && S.graph) { CUDA_CHECK(cudaGraphLaunch(S.graph, st)); g_launches += S.graph_launches; launched += poll; }
+        else for (int k = 0; k < poll && launched < S.maxits; k++, launched++) iteration();
         CUDA_CHECK(cudaMemcpyAsync(hs, S.scal.p, sizeof(SolverScal), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
         done = hs->done;
@@ -444,6 +473,7 @@ void psolver_final(void) {
         if (S->ev0) cudaEventDestroy(S->ev0);
         if (S->ev1) cudaEventDestroy(S->ev1);
         if (S->h_scal) cudaFreeHost(S->h_scal);
+        if (S->graph) cudaGraphExecDestroy(S->graph);
         delete S;
     }
     g_solvers.clear();

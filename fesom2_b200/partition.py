@@ -174,77 +174,115 @@ def pe_contiguous_numbering(part, npes):
     return off, idx
 
 
-def local_model(hm, r, part):
-    """HostModel of partition `r` (a RankMesh): every array of the global model `hm` restricted to the local lists,
-    connectivity renumbered to local 1-based ids (0 = not local), SSH matrix rows of the own nodes with columns in
-    the PE-contiguous global numbering.  This is the state the reference's rank `r.mype` holds after mesh_setup +
-    ocean_setup (src/oce_mesh.F90:108-143, src/oce_setup_step.F90:20)."""
-    lm = HostModel()
-    L = lm._L
+PARAMS = ("nl", "dt", "alpha", "theta", "w_split", "w_max_cfl", "K_hor", "is_nonlinfs", "which_ale", "num_tracers",
+          "cyclic_length", "nod_in_elem2D_max", "use_partial_cell", "cartesian", "force_rotation")
+
+
+def local_arrays(hm, r, part):
+    """(params, arrays) of partition `r` (a RankMesh): every array of the global model `hm` restricted to the local
+    lists, connectivity renumbered to local 1-based ids (0 = not local), SSH matrix rows of the own nodes with columns
+    in the PE-contiguous global numbering.  This is the state the reference's rank `r.mype` holds after mesh_setup +
+    ocean_setup (src/oce_mesh.F90:108-143, src/oce_setup_step.F90:20).  Arrays are numpy, reversed-Fortran shapes."""
     names = set(hm.names())
-    # scalar parameters
-    for k in ("nl", "dt", "alpha", "theta", "w_split", "w_max_cfl", "K_hor", "is_nonlinfs", "which_ale", "num_tracers",
-              "cyclic_length", "nod_in_elem2D_max", "use_partial_cell", "cartesian", "force_rotation"):
+    params = {}
+    for k in PARAMS:
         try:
-            lm.set(**{k: hm.par(k)})
+            params[k] = hm.par(k)
         except RuntimeError:
             pass
     nod, elem, edge = r.nod.astype(np.int64) - 1, r.elem.astype(np.int64) - 1, r.edge.astype(np.int64) - 1
-    lm.set(npes=r.npes, mype=r.mype, myDim_nod2D=r.myDim_nod2D, eDim_nod2D=r.eDim_nod2D, myDim_elem2D=r.myDim_elem2D,
-           eDim_elem2D=r.eDim_elem2D, eXDim_elem2D=r.eXDim_elem2D, myDim_edge2D=r.myDim_edge2D, eDim_edge2D=r.eDim_edge2D,
-           nod2D=hm.ipar("myDim_nod2D"), elem2D=hm.ipar("myDim_elem2D"), edge2D=hm.ipar("myDim_edge2D"))
+    params.update(npes=r.npes, mype=r.mype, myDim_nod2D=r.myDim_nod2D, eDim_nod2D=r.eDim_nod2D, myDim_elem2D=r.myDim_elem2D,
+                  eDim_elem2D=r.eDim_elem2D, eXDim_elem2D=r.eXDim_elem2D, myDim_edge2D=r.myDim_edge2D, eDim_edge2D=r.eDim_edge2D,
+                  nod2D=hm.ipar("myDim_nod2D"), elem2D=hm.ipar("myDim_elem2D"), edge2D=hm.ipar("myDim_edge2D"))
     Ng, Eg = hm.ipar("myDim_nod2D"), hm.ipar("myDim_elem2D")
     g2l_n = np.zeros(Ng + 1, dtype=np.int32)
     g2l_n[nod + 1] = np.arange(1, nod.size + 1)
     g2l_e = np.zeros(Eg + 1, dtype=np.int32)
     g2l_e[elem + 1] = np.arange(1, elem.size + 1)
-
-    def put(name, a):
-        a = np.ascontiguousarray(a)
-        dst = lm.new(name, a.shape[::-1], a.dtype.type if a.dtype == np.int32 else np.float64)
-        dst[...] = a
-
+    A = {}
     for nm in NODE_ARRAYS:
         if nm in names:
-            put(nm, hm[nm][nod])
+            A[nm] = hm[nm][nod]
     for nm in ELEM_ARRAYS:
         if nm in names:
-            put(nm, hm[nm][elem])
+            A[nm] = hm[nm][elem]
     for nm in EDGE_ARRAYS:
         if nm in names:
-            put(nm, hm[nm][edge])
+            A[nm] = hm[nm][edge]
     for nm in GLOBAL_ARRAYS:
         if nm in names:
-            put(nm, hm[nm])
+            A[nm] = hm[nm].copy()
     for nm in ("tr_arr", "tr_arr_old"):
-        put(nm, hm[nm][:, nod])
-    put("myList_nod2D", r.nod)
-    put("myList_elem2D", r.elem)
-    put("myList_edge2D", r.edge)
-    put("edges", g2l_n[hm["edges"][edge]])
-    put("edge_tri", g2l_e[np.maximum(hm["edge_tri"][edge], 0)])
-    put("elem2D_nodes", g2l_n[hm["elem2D_nodes"][elem]])
-    put("edge_up_dn_tri", g2l_e[np.maximum(hm["edge_up_dn_tri"][edge], 0)])
-    put("nod_in_elem2D_num", hm["nod_in_elem2D_num"][nod])
-    put("nod_in_elem2D", g2l_e[np.maximum(hm["nod_in_elem2D"][nod], 0)])
+        A[nm] = hm[nm][:, nod]
+    A["myList_nod2D"], A["myList_elem2D"], A["myList_edge2D"] = r.nod, r.elem, r.edge
+    A["edges"] = g2l_n[hm["edges"][edge]]
+    A["edge_tri"] = g2l_e[np.maximum(hm["edge_tri"][edge], 0)]
+    A["elem2D_nodes"] = g2l_n[hm["elem2D_nodes"][elem]]
+    A["edge_up_dn_tri"] = g2l_e[np.maximum(hm["edge_up_dn_tri"][edge], 0)]
+    A["nod_in_elem2D_num"] = hm["nod_in_elem2D_num"][nod]
+    A["nod_in_elem2D"] = g2l_e[np.maximum(hm["nod_in_elem2D"][nod], 0)]
     # SSH system: own rows, PE-contiguous global columns (init_stiff_mat_ale, oce_ale.F90:1128-1344)
     off, pc = pe_contiguous_numbering(part, r.npes)
     own = nod[:r.myDim_nod2D]
     rp = hm["ssh_rowptr"].astype(np.int64)
     cnt = rp[own + 1] - rp[own]
     lrp = np.concatenate([[0], np.cumsum(cnt)])
-    gather = np.concatenate([np.arange(rp[n] - 1, rp[n + 1] - 1) for n in own]) if own.size < 200000 else \
-        (np.repeat(rp[own] - 1 - lrp[:-1], cnt) + np.arange(lrp[-1]))
-    put("ssh_rowptr", (lrp + int(off[r.mype]) * 0 + 1).astype(np.int32))        # local 1-based row pointers (rowptr_loc)
-    put("ssh_colind", pc[hm["ssh_colind"][gather] - 1].astype(np.int32))
-    put("ssh_values", hm["ssh_values"][gather])
-    put("part", off)
+    gather = np.repeat(rp[own] - 1 - lrp[:-1], cnt) + np.arange(lrp[-1])
+    A["ssh_rowptr"] = (lrp + 1).astype(np.int32)             # local 1-based row pointers (rowptr_loc)
+    A["ssh_colind"] = pc[hm["ssh_colind"][gather] - 1].astype(np.int32)
+    A["ssh_values"] = hm["ssh_values"][gather]
+    A["part"] = off
     for pre, c in (("com_nod2D", r.com_nod), ("com_elem2D_full", r.com_elem_full)):
         for k in ("rPE", "rptr", "rlist", "sPE", "sptr", "slist"):
-            put("%s_%s" % (pre, k), np.asarray(c[k], dtype=np.int32) if len(c[k]) else np.zeros(1, dtype=np.int32))
-        lm.set(**{pre + "_rPEnum": len(c["rPE"]), pre + "_sPEnum": len(c["sPE"])})
-    lm._ssh_gather = gather                                   # positions of the local nonzeros in the global value array
+            A["%s_%s" % (pre, k)] = np.asarray(c[k], dtype=np.int32) if len(c[k]) else np.zeros(1, dtype=np.int32)
+        params[pre + "_rPEnum"] = len(c["rPE"])
+        params[pre + "_sPEnum"] = len(c["sPE"])
+    return params, {k: np.ascontiguousarray(v) for k, v in A.items()}
+
+
+def model_from_arrays(params, arrays):
+    lm = HostModel()
+    lm.set(**params)
+    for name, a in arrays.items():
+        dst = lm.new(name, a.shape[::-1], np.int32 if a.dtype == np.int32 else np.float64)
+        dst[...] = a
     return lm
+
+
+def local_model(hm, r, part):
+    return model_from_arrays(*local_arrays(hm, r, part))
+
+
+def scatter_local_models(hm, part, dist, group=None):
+    """collective over `dist` (a CPU-capable torch.distributed group, e.g. gloo): rank 0 holds the global model `hm`,
+    partitions it and ships every rank its own partition (the reference reaches the same state by every rank reading
+    the mesh files + its dist_N lists, oce_mesh.F90:147-692).  Returns (local HostModel, own wet node-layers)."""
+    import torch
+    rank, world = dist.get_rank(), dist.get_world_size()
+    if rank == 0:
+        ranks = build_partition(hm, part, world)
+        mine = None
+        for dst in range(world):
+            params, arrays = local_arrays(hm, ranks[dst], part)
+            if dst == 0:
+                mine = (params, arrays)
+                continue
+            meta = [(k, a.shape, str(a.dtype)) for k, a in arrays.items()]
+            dist.send_object_list([params, meta], dst=dst, group=group)
+            for k, a in arrays.items():
+                dist.send(torch.from_numpy(a.reshape(-1)), dst=dst, group=group)
+            del arrays
+        params, arrays = mine
+    else:
+        box = [None, None]
+        dist.recv_object_list(box, src=0, group=group)
+        params, meta = box
+        arrays = {}
+        for k, shape, dt in meta:
+            t = torch.empty(int(np.prod(shape)), dtype=torch.int32 if dt == "int32" else torch.float64)
+            dist.recv(t, src=0, group=group)
+            arrays[k] = t.numpy().reshape(shape)
+    return model_from_arrays(params, arrays)
 
 
 def com_arrays(c):
@@ -265,3 +303,26 @@ def exchange_host(ranks, fields, kind="nod"):
             rl = co["rlist"][co["rptr"][j] - 1:co["rptr"][j + 1] - 1] - 1
             assert rl.size == sl.size
             fields[pe][rl] = fields[me][sl]
+
+
+def exchange_dist(lm, field, kind, dist, group=None):
+    """exchange_nod / exchange_elem (gen_halo_exchange.F90:129-164, 317-363, 662-786) of one host array over
+    torch.distributed point-to-point (gloo on CPU): `field`'s first numpy axis is the local entity; com lists from `lm`."""
+    import torch
+    pre = "com_nod2D" if kind == "nod" else "com_elem2D_full"
+    nr, ns = lm.ipar(pre + "_rPEnum"), lm.ipar(pre + "_sPEnum")
+    rPE, rptr, rlist = lm[pre + "_rPE"], lm[pre + "_rptr"], lm[pre + "_rlist"]
+    sPE, sptr, slist = lm[pre + "_sPE"], lm[pre + "_sptr"], lm[pre + "_slist"]
+    reqs, rbufs = [], []
+    for k in range(nr):
+        idx = rlist[rptr[k] - 1:rptr[k + 1] - 1] - 1
+        t = torch.empty((idx.size,) + field.shape[1:], dtype=torch.float64)
+        rbufs.append((idx, t))
+        reqs.append(dist.irecv(t, src=int(rPE[k]), group=group))
+    for k in range(ns):
+        idx = slist[sptr[k] - 1:sptr[k + 1] - 1] - 1
+        reqs.append(dist.isend(torch.from_numpy(np.ascontiguousarray(field[idx])), dst=int(sPE[k]), group=group))
+    for q in reqs:
+        q.wait()
+    for idx, t in rbufs:
+        field[idx] = t.numpy()

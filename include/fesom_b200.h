@@ -40,6 +40,8 @@ void psolver_final(void);
 void fb200_psolve_info(int* id, int* its, double* resnorm);
 /* block size of the block-Jacobi preconditioner for solvers created afterwards (1 = point Jacobi) */
 void fb200_psolver_set_block(int* block);
+/* 1 (default): replay the BiCGStab iterations from a captured CUDA graph; 0: plain launches */
+void fb200_psolver_use_graph(int* on);
 
 /* ---------------------------------------------------------------------------------------------------
  * Tracer path.  Replaces the body of solve_tracers_ale (src/oce_ale_tracer.F90:101-199): init_tracers_AB,

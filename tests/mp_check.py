@@ -63,6 +63,7 @@ def main():
     allv = [None] * world
     dist.all_gather_object(allv, verdict)
     eng.close()
+    api.lib().psolver_final()
     api.comm_finalize()
     if rank == 0:
         for v in allv:

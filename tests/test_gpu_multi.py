@@ -22,5 +22,5 @@ def test_partitioned_gpu_run_matches_undivided_oracle(mesh, nranks):
         pytest.skip("needs %d GPUs" % nranks)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nranks), "--master-addr", "127.0.0.1",
            "--master-port", str(29500 + nranks), os.path.join(ROOT, "tests", "mp_check.py"), mesh]
-    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600, cwd=ROOT).stdout
+    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=180, cwd=ROOT).stdout
     assert "MPCHECK_RESULT PASS" in out, out[-3000:]
