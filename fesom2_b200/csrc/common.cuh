@@ -104,7 +104,7 @@ struct TracerCtx {
     DevBuf<double> T, Told;
     // work fields, tiled
     DevBuf<double2> txy, fpm;       // (tr_xy x, y) per element-level; (fct_plus, fct_minus) per node-level
-    DevBuf<double> trz, LO, adf_h, adf_v, tstar;
+    DevBuf<double> trz, LO, adf_h, adf_v, tstar, eflx;
     // staging for host<->device transfers (reference layout)
     DevBuf<double> stage;
     // halo plans of com_nod2D / com_elem2D_full (fb200_init_halo); null on a single partition

@@ -255,7 +255,7 @@ void ctx_commit(TracerCtx& c) {
                               &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar}) b->alloc(nf);
     c.fpm.alloc(nf);
     c.helem.alloc(ef); c.UV.alloc(ef); c.txy.alloc(ef);
-    c.adf_h.alloc(df);
+    c.adf_h.alloc(df); c.eflx.alloc(df);
     c.T.alloc(nf * c.ntr); c.Told.alloc(nf * c.ntr);
     for (DevBuf<double>* b : {&c.heat_flux, &c.water_flux, &c.virtual_salt, &c.relax_salt, &c.real_salt_flux}) b->alloc(N);
     ctx_push_node_field(c, c.h_area.data(), c.nl, N, c.area.p);
@@ -268,7 +268,7 @@ void ctx_release(TracerCtx& c) {
     if (c.stream) { cudaStreamSynchronize(c.stream); }
     for (DevBuf<double>* b : {&c.area, &c.areasvol, &c.W, &c.We, &c.Wi, &c.hnode, &c.hnode_new, &c.Z3, &c.zbar3, &c.Kv, &c.Ki,
                               &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar,
-                              &c.helem, &c.adf_h, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
+                              &c.helem, &c.adf_h, &c.eflx, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
                               &c.relax_salt, &c.real_salt_flux, &c.stage, &c.el_g, &c.el_area, &c.n_znb}) b->release();
     c.tile_deg.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
     c.UV.release(); c.txy.release(); c.fpm.release();

@@ -26,6 +26,7 @@ struct KP {                       // kernel parameter block (by value)
     double *T, *Told, *T1;        // this tracer's fields; T1 = tracer 1 (bc_surface)
     double2 *txy, *fpm;            // (tr_xy(1), tr_xy(2)) per element-level; (fct_plus, fct_minus) per node-level
     double *trz, *LO, *adf_h, *adf_v, *tstar;
+    double* eflx;                  // per (edge, level) scratch: upwind flux of ttf (k_ho_edge -> k_lo), then the diffusive flux (k_diff_edge -> k_update)
 };
 
 __device__ __forceinline__ int tbase(int ent, int nlp) { return (ent >> 5) * (nlp * TILE) + (ent & 31); }
@@ -177,18 +178,13 @@ __global__ void LB(512) k_lo(KP p) {
     for (int j = 0; j < ndeg; j++) {
         const size_t k = sbase + (size_t)j * TILE;
         const bool second = p.ne_slot[k] & 1;                                  // empty slots have zero masks
-        const int4 ni = p.ns_i[k];
-        const int bo = ni.x, be1 = ni.y, be2 = ni.z;
+        const int bed = p.ns_i[k].w;
         const ulonglong2 mm = p.ns_m[k];
-        const double2 d1 = p.ns_d1[k], d2 = p.ns_d2[k];
+        const unsigned long long many = mm.x | mm.y;
 #pragma unroll
         for (int q = 0; q < LPT; q++) {
-            if (!act[q]) continue;
-            const int segs = mask_segs(mm.x, mm.y, nz[q]);
-            if (!segs) continue;
-            const double vflux = seg_vflux(p, segs, be1, be2, d1.x, d1.y, d2.x, d2.y, nz[q]);
-            const double to = AT(T, bo, nz[q]);
-            const double f = second ? upw1_flux(to, tn[q], vflux) : upw1_flux(tn[q], to, vflux);
+            if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
+            const double f = AT(p.eflx, bed, nz[q]);                           // upwind edge flux, computed once per edge by k_ho_edge
             acc[q] = second ? acc[q] - f : acc[q] + f;
         }
     }
@@ -338,6 +334,7 @@ __global__ void __launch_bounds__(256, 3) k_ho_edge(KP p) {
             fho = -0.5 * (1.0 - p.ph) * cHO - vflux * p.ph * (0.5 * (Tmean1 + Tmean2));
         }
         AT(p.adf_h, be, nz) = fho - flo;
+        AT(p.eflx, be, nz) = flo;                                    // adv_tra_hor_upw1(ttf), gathered by k_lo
     }
 }
 
@@ -435,6 +432,53 @@ __device__ __forceinline__ double limited_fv(const KP& p, int b, int nz, int nzm
     return ae * flux;
 }
 
+// K6: diff_part_hor_redi (oce_ale_tracer.F90:934-1077), the flux through the two median-dual segments of every own
+// edge and level, computed once per edge (edge-kernel mapping) and gathered by k_update.
+__global__ void __launch_bounds__(256, 3) k_diff_edge(KP p) {
+    const int e = blockIdx.x * TILE + threadIdx.x;
+    if (e >= p.myEd) return;
+    const EdgeRec r = p.edge[e];
+    const unsigned long long many = r.m1 | r.m2;
+    if ((many >> min(63u, blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1)) == 0ull) return;
+    const int be = blockIdx.x * (p.nlp * TILE) + threadIdx.x;
+    const double isredi = p.Redi ? 1.0 : 0.0;
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        const int z = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
+        if (z > 63) continue;
+        const int segs = mask_segs(r.m1, r.m2, z);
+        if (!segs) continue;
+        const double Kh = (AT(p.Ki, r.bn1, z) + AT(p.Ki, r.bn2, z)) / 2.0;
+        double SxTz = 0.0, SyTz = 0.0;
+        if (p.Redi) {
+            const double Tz1 = 0.5 * (AT(p.trz, r.bn1, z) + AT(p.trz, r.bn1, z + 1));
+            const double Tz2 = 0.5 * (AT(p.trz, r.bn2, z) + AT(p.trz, r.bn2, z + 1));
+            SxTz = (Tz1 * AT(p.sl1, r.bn1, z) + Tz2 * AT(p.sl1, r.bn2, z)) / 2.0;
+            SyTz = (Tz1 * AT(p.sl2, r.bn1, z) + Tz2 * AT(p.sl2, r.bn2, z)) / 2.0;
+        }
+        double dz, Tx, Ty, cc;                                              // :1020-1062
+        if (segs == 3) {
+            const double2 ga = AT(p.txy, r.be1, z), gb = AT(p.txy, r.be2, z);
+            dz = (AT(p.helem, r.be1, z) + AT(p.helem, r.be2, z)) / 2.0;
+            Tx = 0.5 * (ga.x + gb.x);
+            Ty = 0.5 * (ga.y + gb.y);
+            const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
+            cc = ((r.dX2 - r.dX1) * Fy - (r.dY2 - r.dY1) * Fx) * dz;
+        } else if (segs == 1) {
+            const double2 ga = AT(p.txy, r.be1, z);
+            dz = AT(p.helem, r.be1, z); Tx = ga.x; Ty = ga.y;
+            const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
+            cc = (-r.dX1 * Fy + r.dY1 * Fx) * dz;
+        } else {
+            const double2 gb = AT(p.txy, r.be2, z);
+            dz = AT(p.helem, r.be2, z); Tx = gb.x; Ty = gb.y;
+            const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
+            cc = (r.dX2 * Fy - r.dY2 * Fx) * dz;
+        }
+        AT(p.eflx, be, z) = cc;
+    }
+}
+
 // K7a: b3 limiting + oce_tra_adv_flux2dtracer (oce_adv_tra_driver.F90:223-268) + del_ttf assembly
 // (oce_ale_tracer.F90:240) + diff_part_hor_redi (:934-1077) + T* update (:294-305).  Node-kernel mapping.
 // Writes tstar; tr_arr_old = tr_arr is done by the caller for all entries.
@@ -489,49 +533,17 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
         dv = dv + div_by((fv - fvn) * p.dt, asv[q], rasv[q]);
         acc[q] = acc[q] + dv;
     }
-    if (p.do_hor_diff) {
-        const double isredi = p.Redi ? 1.0 : 0.0;
+    if (p.do_hor_diff) {                                                     // diff_part_hor_redi: fluxes from k_diff_edge
         for (int j = 0; j < ndeg; j++) {
             const size_t k = sbase + (size_t)j * TILE;
             const bool second = p.ne_slot[k] & 1;
-            const int4 ni = p.ns_i[k];
-            const int bo = ni.x, be1 = ni.y, be2 = ni.z;
-            const int bn1 = second ? bo : c.b, bn2 = second ? c.b : bo;
+            const int bed = p.ns_i[k].w;
             const ulonglong2 mm = p.ns_m[k];
-            const double2 d1 = p.ns_d1[k], d2 = p.ns_d2[k];
+            const unsigned long long many = mm.x | mm.y;
 #pragma unroll
             for (int q = 0; q < LPT; q++) {
-                if (!act[q]) continue;
-                const int z = nz[q];
-                const int segs = mask_segs(mm.x, mm.y, z);
-                if (!segs) continue;
-                const double Kh = (AT(p.Ki, bn1, z) + AT(p.Ki, bn2, z)) / 2.0;
-                double SxTz = 0.0, SyTz = 0.0;
-                if (p.Redi) {
-                    const double Tz1 = 0.5 * (AT(p.trz, bn1, z) + AT(p.trz, bn1, z + 1));
-                    const double Tz2 = 0.5 * (AT(p.trz, bn2, z) + AT(p.trz, bn2, z + 1));
-                    SxTz = (Tz1 * AT(p.sl1, bn1, z) + Tz2 * AT(p.sl1, bn2, z)) / 2.0;
-                    SyTz = (Tz1 * AT(p.sl2, bn1, z) + Tz2 * AT(p.sl2, bn2, z)) / 2.0;
-                }
-                double dz, Tx, Ty, cc;                                      // :1020-1062
-                if (segs == 3) {
-                    const double2 ga = AT(p.txy, be1, z), gb = AT(p.txy, be2, z);
-                    dz = (AT(p.helem, be1, z) + AT(p.helem, be2, z)) / 2.0;
-                    Tx = 0.5 * (ga.x + gb.x);
-                    Ty = 0.5 * (ga.y + gb.y);
-                    const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
-                    cc = ((d2.x - d1.x) * Fy - (d2.y - d1.y) * Fx) * dz;
-                } else if (segs == 1) {
-                    const double2 ga = AT(p.txy, be1, z);
-                    dz = AT(p.helem, be1, z); Tx = ga.x; Ty = ga.y;
-                    const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
-                    cc = (-d1.x * Fy + d1.y * Fx) * dz;
-                } else {
-                    const double2 gb = AT(p.txy, be2, z);
-                    dz = AT(p.helem, be2, z); Tx = gb.x; Ty = gb.y;
-                    const double Fx = Kh * (Tx + SxTz * isredi), Fy = Kh * (Ty + SyTz * isredi);
-                    cc = (d2.x * Fy - d2.y * Fx) * dz;
-                }
+                if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
+                const double cc = AT(p.eflx, bed, nz[q]);
                 const double rhs = second ? 0.0 - cc : 0.0 + cc;
                 acc[q] = acc[q] + div_by(rhs * p.dt, asv[q], rasv[q]);
             }
@@ -717,7 +729,7 @@ static KP make_kp(TracerCtx& c, int tr) {
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     p.T = c.T.p + nf * tr; p.Told = c.Told.p + nf * tr; p.T1 = c.T.p;
     p.txy = c.txy.p; p.fpm = c.fpm.p; p.trz = c.trz.p; p.LO = c.LO.p; p.adf_h = c.adf_h.p; p.adf_v = c.adf_v.p;
-    p.tstar = c.tstar.p;
+    p.tstar = c.tstar.p; p.eflx = c.eflx.p;
     return p;
 }
 
@@ -762,14 +774,15 @@ void tracer_step_all(TracerCtx& c) {
         KL("k_ab2", k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb));
         KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
         if (multi) halo_exchange_tiled(*c.halo_elem, (double*)p.txy, c.nlp, 2, st);       // exchange_elem(tr_xy), oce_tracer_mod.F90:68,72
+        KL("k_ho_edge", k_ho_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
         KL("k_lo", k_lo<<<c.myNtiles, blk, 0, st>>>(p));
         if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
         if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);                   // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
-        KL("k_ho_edge", k_ho_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
         KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
         if (multi) halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st);         // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
         if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
         if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
+        if (c.opt.do_hor_diff) KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
         KL("k_update", k_update<<<c.myNtiles, blk, 0, st>>>(p));
         {   // tr_arr_old = tr_arr (:274)
             ProfScope ps_("copy_told", st);
