@@ -136,6 +136,62 @@ __device__ __forceinline__ double ver_cdiff(const KP& p, const double* __restric
     return -tv * w * ar;
 }
 
+// PPM (Colella & Woodward) vertical flux, adv_tra_vert_ppm, oce_adv_tra_ver.F90:361-538.  The reference walks down the
+// column keeping the interface values tv(:) and writes tvert(nz) from the cell the flow leaves; here every interface
+// is evaluated on its own: ppm_iface() is tv(k) with the reference's assignment order deciding which rule wins on short
+// columns, ver_ppm() the flux through interface nz from its upwind cell.
+__device__ __noinline__ double ppm_iface(const double* __restrict__ T, const double* __restrict__ hn, const double* __restrict__ W,
+                                         int b, int k, int nzmin, int nzmax) {
+    if (k == nzmax) return AT(T, b, nzmax - 1);                                                        // :411
+    if (k == nzmax - 1) {                                                                              // :408-409
+        const double s = copysign(1.0, AT(W, b, nzmax - 1));
+        return -AT(T, b, max(nzmax - 2, 1)) * dmin(s, 0.0) + AT(T, b, nzmax - 1) * dmax(s, 0.0);
+    }
+    if (k == nzmin) return AT(T, b, nzmin);                                                            // :401
+    if (k == nzmin + 1) return 0.5 * (AT(T, b, nzmin) + AT(T, b, nzmin + 1));                          // :404
+    const int nz = k - 1;                                                                              // :416-456
+    const double tm1 = AT(T, b, nz - 1), t0 = AT(T, b, nz), tp1 = AT(T, b, nz + 1), tp2 = AT(T, b, nz + 2);
+    const double dzjm1 = AT(hn, b, nz - 1), dzj = AT(hn, b, nz), dzjp1 = AT(hn, b, nz + 1), dzjp2 = AT(hn, b, nz + 2);
+    double deltaj = dzj / (dzjm1 + dzj + dzjp1) *
+                    ((2.0 * dzjm1 + dzj) / (dzjp1 + dzj) * (tp1 - t0) + (dzj + 2.0 * dzjp1) / (dzjm1 + dzj) * (t0 - tm1));
+    double deltajp1 = dzjp1 / (dzj + dzjp1 + dzjp2) *
+                      ((2.0 * dzj + dzjp1) / (dzjp2 + dzjp1) * (tp2 - tp1) + (dzjp1 + 2.0 * dzjp2) / (dzj + dzjp1) * (tp1 - t0));
+    if ((tp1 - t0) * (t0 - tm1) > 0.0)
+        deltaj = copysign(dmin(dmin(fabs(deltaj), 2.0 * fabs(tp1 - t0)), 2.0 * fabs(t0 - tm1)), deltaj);
+    else deltaj = 0.0;
+    if ((tp2 - tp1) * (tp1 - t0) > 0.0)
+        deltajp1 = copysign(dmin(dmin(fabs(deltajp1), 2.0 * fabs(tp2 - tp1)), 2.0 * fabs(tp1 - t0)), deltajp1);
+    else deltajp1 = 0.0;
+    return t0 + dzj / (dzj + dzjp1) * (tp1 - t0) +
+           1.0 / (dzjm1 + dzj + dzjp1 + dzjp2) *
+               ((2.0 * dzjp1 * dzj) / (dzj + dzjp1) * ((dzjm1 + dzj) / (2.0 * dzj + dzjp1) - (dzjp2 + dzjp1) / (2.0 * dzjp1 + dzj)) * (tp1 - t0) -
+                dzj * (dzjm1 + dzj) / (2.0 * dzj + dzjp1) * deltajp1 + dzjp1 * (dzjp1 + dzjp2) / (dzj + 2.0 * dzjp1) * deltaj);
+}
+__device__ __noinline__ double ver_ppm(const KP& p, const double* __restrict__ T, const double* __restrict__ W,
+                                       int b, int nz, int nzmin, int nzmax) {
+    if (nz == nzmax) return 0.0;                                                                       // :527
+    const double w = AT(W, b, nz), ar = AT(p.area, b, nz);
+    if (nz == nzmin) return -ppm_iface(T, p.hnode_new, W, b, nzmin, nzmin, nzmax) * w * ar;            // :525
+    if (w == 0.0) return 0.0;
+    const int j = (w > 0.0) ? nz : nz - 1;                                                             // the cell the flow leaves (:461-519)
+    const double tj = AT(T, b, j);
+    double aL = ppm_iface(T, p.hnode_new, W, b, j, nzmin, nzmax), aR = ppm_iface(T, p.hnode_new, W, b, j + 1, nzmin, nzmax);
+    if ((aR - tj) * (tj - aL) <= 0.0) { aL = tj; aR = tj; }
+    if ((aR - aL) * (tj - 0.5 * (aL + aR)) > (aR - aL) * (aR - aL) / 6.0) aL = 3.0 * tj - 2.0 * aR;
+    if ((aR - aL) * (tj - 0.5 * (aR + aL)) < -((aR - aL) * (aR - aL)) / 6.0) aR = 3.0 * tj - 2.0 * aL;
+    const double dzj = AT(p.hnode, b, j);
+    const double aj = 6.0 * (tj - 0.5 * (aL + aR));
+    double f;
+    if (w > 0.0) {
+        const double x = dmin(w * p.dt / dzj, 1.0);
+        f = (-aL - 0.5 * x * (aR - aL + (1.0 - 2.0 / 3.0 * x) * aj));
+    } else {
+        const double x = dmin(-w * p.dt / dzj, 1.0);
+        f = (-aR + 0.5 * x * (aR - aL - (1.0 - 2.0 / 3.0 * x) * aj));
+    }
+    return f * ar * w;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // Thread mapping of the node kernels: block = one tile of 32 consecutive nodes (threadIdx.x = lane = node) times
 // blockDim.y level rows; every thread owns LPT levels nz = threadIdx.y + 1 + q * blockDim.y of its node, so a warp
@@ -158,6 +214,7 @@ __device__ __forceinline__ NodeCol node_col(const KP& p) {
 //   fct_LO  : oce_adv_tra_driver.F90:83-122 (adv_tra_hor_upw1 + edge scatter + adv_tra_ver_upw1 + column update)
 //   adf_v   : oce_adv_tra_driver.F90:163-179 with init_zero=.false.  (HO(ttfAB, W) - LO(ttf, W)); adf_v(nzmax) is
 //             0 - 0 for every scheme and is never written (the buffer is zero-initialised)
+template <int VER>                          // vertical scheme fixed at compile time: the PPM code stays out of the default kernel
 __global__ void LB(512) k_lo(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
@@ -200,8 +257,9 @@ __global__ void LB(512) k_lo(KP p) {
         AT(p.LO, c.b, z) = (tn[q] * AT(p.hnode, c.b, z) + (acc[q] + (fv - fvn)) * p.dt / AT(p.areasvol, c.b, z)) / AT(p.hnode_new, c.b, z);
         const double flo = ver_upw1(T, Wad, p.area, c.b, z, c.nzmin, c.nzmax);
         double ho;
-        if (p.ver == 0) ho = ver_qr4c(p, TAB, p.W, c.b, z, c.nzmin, c.nzmax) - flo;
-        else if (p.ver == 1) ho = ver_cdiff(p, TAB, p.W, c.b, z, c.nzmin) - flo;
+        if (VER == 0) ho = ver_qr4c(p, TAB, p.W, c.b, z, c.nzmin, c.nzmax) - flo;
+        else if (VER == 1) ho = ver_cdiff(p, TAB, p.W, c.b, z, c.nzmin) - flo;
+        else if (VER == 2) ho = ver_ppm(p, TAB, p.W, c.b, z, c.nzmin, c.nzmax) - flo;
         else ho = ver_upw1(TAB, p.W, p.area, c.b, z, c.nzmin, c.nzmax) - flo;
         AT(p.adf_v, c.b, z) = ho;
     }
@@ -290,7 +348,7 @@ __device__ __noinline__ void node_mean_grad(const int* __restrict__ nie_slot, in
 //   adv_tra_hor_mfct / _muscl / _upw1 with init_zero=.false. (oce_adv_tra_hor.F90:215-733) on ttfAB,
 //   the input flux being adv_tra_hor_upw1(ttf) (oce_adv_tra_driver.F90:83,142-149); the gradients of
 //   fill_up_dn_grad (oce_muscl_adv.F90:285-447) are gathered from txy instead of being stored.
-__global__ void __launch_bounds__(256, 3) k_ho_edge(KP p) {
+__global__ void __launch_bounds__(256, 4) k_ho_edge(KP p) {
     const int e = blockIdx.x * TILE + threadIdx.x;
     if (e >= p.myEd) return;
     const EdgeRec r = p.edge[e];
@@ -300,7 +358,7 @@ __global__ void __launch_bounds__(256, 3) k_ho_edge(KP p) {
     const int be = blockIdx.x * (p.nlp * TILE) + threadIdx.x;
     const int sh_lo = h.shared & 255, sh_hi = (h.shared >> 8) & 255;
     const bool good = (h.shared >> 16) & 1;
-    const int nbl1 = p.n_nbl[h.n1], nbl2 = p.n_nbl[h.n2];
+    const int nbl1 = p.hor == 0 ? p.n_nbl[h.n1] : 0, nbl2 = p.hor == 0 ? p.n_nbl[h.n2] : 0;     // only MUSCL uses nboundary_lay
     const double* __restrict__ T = p.T;
     const double* __restrict__ A = p.Told;
 #pragma unroll
@@ -560,131 +618,131 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K7b: diff_ver_part_impl_ale (oce_ale_tracer.F90:509-855).  Block = one tile of 32 own columns x level rows.
-// The column recurrences are split from the memory-parallel work so that no thread walks down a column issuing
-// dependent global loads:
-//   phase 1 (all threads)   hnode_new -> shared
-//   phase 2 (warp 0)        zbar_n bottom-up scan per column in shared memory                          (:528-536)
-//   phase 3 (all threads)   a, b, c and the right-hand side of every (column, level) from T*, Kv, areas (:560-800),
-//                           shortwave penetration and the surface boundary condition (bc_surface :1154-1195)
-//   phase 4 (warp 0)        Thomas algorithm per column in shared memory                                (:828-844)
-//   phase 5 (all threads)   T = T* + dT, coalesced
-// dynamic smem: H, ZB, A, B, C, R  [6][nlp][32]
-__global__ void LB(512) k_impl_diff(KP p) {
+// K7b: diff_ver_part_impl_ale (oce_ale_tracer.F90:509-855).  One warp = one tile of 32 own columns, one thread per
+// column; warps are independent (no block barrier), so an SM keeps as many column recurrences in flight as shared
+// memory allows (one [nlp][32] array per warp).  Every load address is known up front (level-blocked layout: a warp
+// reads 256 contiguous bytes per level), only the arithmetic of the recurrences is serial:
+//   pass 1 (bottom-up)  zbar_n(nz) = zbar_n(nz+1) + hnode_new(nz)  -> kept in the output slot T(nz) until pass 2 gets there  (:528-536)
+//   pass 2 (top-down)   a, b, c and the right-hand side of level nz (:560-800, shortwave penetration, surface boundary
+//                       condition bc_surface :1154-1195) feed the forward elimination of the Thomas algorithm
+//                       directly (:828-836); c' -> shared memory, d' -> the output field T
+//   pass 3 (bottom-up)  back substitution (:838-844) and T = T* + dT
+// zinv1 of level nz is the same expression as zinv2 of level nz-1 and is carried over.
+// dynamic smem: cp [blockDim.y][nlp][32]
+__global__ void __launch_bounds__(64, 8) k_impl_diff(KP p) {
     extern __shared__ double sm[];
-    const int S = p.nlp * TILE, lane = threadIdx.x;
-    double* H = sm; double* ZBs = sm + S; double* sA = sm + 2 * S; double* sB = sm + 3 * S; double* sC = sm + 4 * S; double* sR = sm + 5 * S;
-    const NodeCol c = node_col(p);
+    const int lane = threadIdx.x;
+    const int tile = blockIdx.x * blockDim.y + threadIdx.y;
+    const int n = tile * TILE + lane;
+    if (n >= p.myN) return;
+    double* __restrict__ cps = sm + (size_t)threadIdx.y * p.nlp * TILE + lane;
+    const int b = tile * (p.nlp * TILE) + lane;
+    const unsigned lv = p.n_lev[n];
+    const int nzmin = lv & 255, nzmax = (lv >> 8) & 255;
     const double* __restrict__ hn = p.hnode_new;
     const double* __restrict__ TS = p.tstar;
+    double* To = p.T;
+    double* ZBg = To;                                     // zbar_n(z) waits in the output slot of level z until d'(z) replaces it
     const double dt = p.dt;
     const double isredi = p.Redi ? 1.0 : 0.0;
-    int nz[LPT]; bool act[LPT];
-#pragma unroll
-    for (int q = 0; q < LPT; q++) {
-        nz[q] = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
-        act[q] = c.valid && nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
-        if (act[q]) H[(nz[q] - 1) * TILE + lane] = AT(hn, c.b, nz[q]);
-    }
-    __syncthreads();
-#define ZB(z) ZBs[((z) - 1) * TILE + lane]
-#define HN(z) H[((z) - 1) * TILE + lane]
-#define ZN(z) (ZB((z) + 1) + HN(z) / 2.0)                    /* Z_n(nz) = zbar_n(nz+1) + hnode_new(nz)/2 */
-    if (threadIdx.y == 0 && c.valid) {
-        double zb = p.n_znb[c.n];
-        ZB(c.nzmax) = zb;
-        for (int z = c.nzmax - 1; z >= c.nzmin; z--) { zb = zb + HN(z); ZB(z) = zb; }
-    }
-    __syncthreads();
     const double vcpw = 4.2e6;
     const double zinv = 1.0 * dt;
-#pragma unroll
-    for (int q = 0; q < LPT; q++) {
-        if (!act[q]) continue;
-        const int z = nz[q];
-        const int nzmin = c.nzmin, nzmax = c.nzmax, b = c.b;
-        double a, bb, cc;
-        const double asv = AT(p.areasvol, b, z), h = HN(z);
+    const double zbot = p.n_znb[n];
+    {
+        double zb = zbot;
+#pragma unroll 4
+        for (int z = nzmax - 1; z >= nzmin; z--) { zb = zb + AT(hn, b, z); AT(ZBg, b, z) = zb; }
+    }
+    __syncwarp();
+#define ZBL(z) ((z) >= nzmax ? zbot : AT(ZBg, b, (z)))
+    // rolling window around level z: zb0..zb2 = zbar_n(z..z+2); h0, hp = hnode_new(z, z+1); znm, zn0 = Z_n(z-1), Z_n(z);
+    // Kv, area, T* at z and z+1.  Everything level z+1 needs is requested at the top of iteration z, before the
+    // divisions of level z, so the loads have a whole iteration to arrive.
+    int z = nzmin;
+    double zb0 = 0.0, zb1 = ZBL(z + 1), zb2 = ZBL(z + 2);
+    double h0 = AT(hn, b, z), hp = AT(hn, b, z + 1);
+    double zn0 = zb1 + h0 / 2.0, znm = 0.0;
+    double kv1 = AT(p.Kv, b, z + 1), ar1 = AT(p.area, b, z + 1), kv0 = 0.0, ar0 = 0.0;
+    double tm = 0.0, t0 = AT(TS, b, z), tp1 = AT(TS, b, z + 1);
+    double asv = AT(p.areasvol, b, z);
+    double zinv1 = 0.0, cpm = 0.0, tpm = 0.0;
+    for (; z <= nzmax - 1; z++) {
+        double n_zb = zbot, n_asv = 0.0, n_hp = 0.0, n_tp = 0.0, n_kv = 0.0, n_ar = 0.0;
+        if (z + 3 < nzmax) n_zb = AT(ZBg, b, z + 3);
+        if (z + 1 <= nzmax - 1) n_asv = AT(p.areasvol, b, z + 1);
+        if (z + 2 <= nzmax - 1) { n_hp = AT(hn, b, z + 2); n_tp = AT(TS, b, z + 2); }
+        if (z + 2 <= nzmax) { n_kv = AT(p.Kv, b, z + 2); n_ar = AT(p.area, b, z + 2); }
+        const double znp = zb2 + hp / 2.0;                                   // Z_n(z+1)
+        const double h = h0;
+        double a, bb, cc, zinv2 = 0.0;
         if (z == nzmin) {
-            const double zinv2 = 1.0 / (ZN(z) - ZN(z + 1));
+            zinv2 = 1.0 / (zn0 - znp);
             double Ty1 = 0.0;
             if (p.Redi) {
                 const double s0 = AT(p.sl3, b, z), s1 = AT(p.sl3, b, z + 1);
-                Ty1 = (ZN(z) - ZB(z + 1)) * zinv2 * (s0 * s0) * AT(p.Ki, b, z) + (ZB(z + 1) - ZN(z + 1)) * zinv2 * (s1 * s1) * AT(p.Ki, b, z + 1);
+                Ty1 = (zn0 - zb1) * zinv2 * (s0 * s0) * AT(p.Ki, b, z) + (zb1 - znp) * zinv2 * (s1 * s1) * AT(p.Ki, b, z + 1);
             }
             Ty1 = Ty1 * isredi;
             a = 0.0;
-            cc = -(AT(p.Kv, b, z + 1) + Ty1) * zinv2 * zinv * AT(p.area, b, z + 1) / asv;
+            cc = -(kv1 + Ty1) * zinv2 * zinv * ar1 / asv;
             bb = -cc + h;
         } else if (z <= nzmax - 2) {
-            const double zinv1 = 1.0 / (ZN(z - 1) - ZN(z));
-            const double zinv2 = 1.0 / (ZN(z) - ZN(z + 1));
+            zinv2 = 1.0 / (zn0 - znp);
             double Ty = 0.0, Ty1 = 0.0;
             if (p.Redi) {
                 const double sm1 = AT(p.sl3, b, z - 1), s0 = AT(p.sl3, b, z), s1 = AT(p.sl3, b, z + 1);
-                Ty = (ZN(z - 1) - ZB(z)) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, z - 1) + (ZB(z) - ZN(z)) * zinv1 * (s0 * s0) * AT(p.Ki, b, z);
-                Ty1 = (ZN(z) - ZB(z + 1)) * zinv2 * (s0 * s0) * AT(p.Ki, b, z) + (ZB(z + 1) - ZN(z + 1)) * zinv2 * (s1 * s1) * AT(p.Ki, b, z + 1);
+                Ty = (znm - zb0) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, z - 1) + (zb0 - zn0) * zinv1 * (s0 * s0) * AT(p.Ki, b, z);
+                Ty1 = (zn0 - zb1) * zinv2 * (s0 * s0) * AT(p.Ki, b, z) + (zb1 - znp) * zinv2 * (s1 * s1) * AT(p.Ki, b, z + 1);
             }
             Ty = Ty * isredi; Ty1 = Ty1 * isredi;
-            a = -(AT(p.Kv, b, z) + Ty) * zinv1 * zinv * (AT(p.area, b, z) / asv);
-            cc = -(AT(p.Kv, b, z + 1) + Ty1) * zinv2 * zinv * AT(p.area, b, z + 1) / asv;
+            a = -(kv0 + Ty) * zinv1 * zinv * (ar0 / asv);
+            cc = -(kv1 + Ty1) * zinv2 * zinv * ar1 / asv;
             bb = -a - cc + h;
         } else {
-            const double zinv1 = 1.0 / (ZN(z - 1) - ZN(z));
             double Ty = 0.0;
             if (p.Redi) {
                 const double sm1 = AT(p.sl3, b, z - 1), s0 = AT(p.sl3, b, z);
-                Ty = (ZN(z - 1) - ZB(z)) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, z - 1) + (ZB(z) - ZN(z)) * zinv1 * (s0 * s0) * AT(p.Ki, b, z);
+                Ty = (znm - zb0) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, z - 1) + (zb0 - zn0) * zinv1 * (s0 * s0) * AT(p.Ki, b, z);
             }
             Ty = Ty * isredi;
-            a = -(AT(p.Kv, b, z) + Ty) * zinv1 * zinv * (AT(p.area, b, z) / asv);
+            a = -(kv0 + Ty) * zinv1 * zinv * (ar0 / asv);
             cc = 0.0;
             bb = -a + h;
         }
         double tr;
-        if (z == nzmin) tr = -(bb - h) * AT(TS, b, z) - cc * AT(TS, b, z + 1);
-        else if (z <= nzmax - 2) tr = -a * AT(TS, b, z - 1) - (bb - h) * AT(TS, b, z) - cc * AT(TS, b, z + 1);
-        else tr = -a * AT(TS, b, z - 1) - (bb - h) * AT(TS, b, z);
+        if (z == nzmin) tr = -(bb - h) * t0 - cc * tp1;
+        else if (z <= nzmax - 2) tr = -a * tm - (bb - h) * t0 - cc * tp1;
+        else tr = -a * tm - (bb - h) * t0;
         if (p.use_sw_pene && p.tr_num == 1)
-            tr = tr + (AT(p.sw3d, b, z) - AT(p.sw3d, b, z + 1) * AT(p.area, b, z + 1) / asv) * zinv;
+            tr = tr + (AT(p.sw3d, b, z) - AT(p.sw3d, b, z + 1) * ar1 / asv) * zinv;
         if (z == nzmin) {
             double bc = 0.0;
             if (p.tracer_id == 0) {
-                const double tsurf = (p.tr_num == 1) ? AT(TS, b, nzmin) : AT(p.T1, b, nzmin);
-                bc = -dt * (p.heat_flux[c.n] / vcpw + tsurf * p.water_flux[c.n] * p.is_nonlinfs);
+                const double tsurf = (p.tr_num == 1) ? t0 : AT(p.T1, b, nzmin);
+                bc = -dt * (p.heat_flux[n] / vcpw + tsurf * p.water_flux[n] * p.is_nonlinfs);
             } else if (p.tracer_id == 1)
-                bc = dt * (p.virtual_salt[c.n] + p.relax_salt[c.n] - p.real_salt_flux[c.n] * p.is_nonlinfs);
+                bc = dt * (p.virtual_salt[n] + p.relax_salt[n] - p.real_salt_flux[n] * p.is_nonlinfs);
             tr = tr + bc;
+            cpm = cc / bb; tpm = tr / bb;                                    // Thomas :828-829
+        } else {
+            const double m = bb - cpm * a;                                   // :831-835
+            cpm = cc / m; tpm = (tr - tpm * a) / m;
         }
-        const int o = (z - 1) * TILE + lane;
-        sA[o] = a; sB[o] = bb; sC[o] = cc; sR[o] = tr;
+        cps[(z - 1) * TILE] = cpm;
+        AT(To, b, z) = tpm;
+        // shift the window to level z+1
+        zb0 = zb1; zb1 = zb2; zb2 = n_zb; znm = zn0; zn0 = znp; h0 = hp; hp = n_hp; zinv1 = zinv2;
+        kv0 = kv1; kv1 = n_kv; ar0 = ar1; ar1 = n_ar; tm = t0; t0 = tp1; tp1 = n_tp; asv = n_asv;
     }
-    __syncthreads();
-    if (threadIdx.y == 0 && c.valid) {                                        // Thomas :828-844
-        int o = (c.nzmin - 1) * TILE + lane;
-        double cpm = sC[o] / sB[o], tpm = sR[o] / sB[o];
-        sC[o] = cpm; sR[o] = tpm;
-        for (int z = c.nzmin + 1; z <= c.nzmax - 1; z++) {
-            o += TILE;
-            const double a = sA[o];
-            const double m = sB[o] - cpm * a;
-            cpm = sC[o] / m; tpm = (sR[o] - tpm * a) / m;
-            sC[o] = cpm; sR[o] = tpm;
-        }
-        double x = tpm;
-        for (int z = c.nzmax - 2; z >= c.nzmin; z--) {
-            o -= TILE;
-            x = sR[o] - sC[o] * x;
-            sR[o] = x;
-        }
+#undef ZBL
+    __syncwarp();
+    double x = tpm;                                                           // :838-844
+    AT(To, b, nzmax - 1) = AT(TS, b, nzmax - 1) + x;
+#pragma unroll 4
+    for (int zz = nzmax - 2; zz >= nzmin; zz--) {
+        x = AT(To, b, zz) - cps[(zz - 1) * TILE] * x;
+        AT(To, b, zz) = AT(TS, b, zz) + x;
     }
-    __syncthreads();
-#pragma unroll
-    for (int q = 0; q < LPT; q++)
-        if (act[q]) AT(p.T, c.b, nz[q]) = AT(TS, c.b, nz[q]) + sR[(nz[q] - 1) * TILE + lane];
-#undef ZB
-#undef HN
-#undef ZN
 }
 
 // explicit vertical diffusion variant is not on the default path (i_vert_diff=.true.); see DESIGN.md
@@ -748,7 +806,6 @@ void tracer_step_all(TracerCtx& c) {
     if (!fb_ok()) return;
     if (!c.committed) { fb_set_error(20, "fb200_solve_tracers before fb200_init_commit"); return; }
     if (c.opt.tra_adv_lim != 0) { fb_set_error(21, "tra_adv_lim='NONE' is not implemented on the device path"); return; }
-    if (c.opt.tra_adv_ver == 2) { fb_set_error(22, "tra_adv_ver='PPM' is not implemented on the device path"); return; }
     if (!c.opt.i_vert_diff) { fb_set_error(23, "i_vert_diff=.false. is not implemented on the device path"); return; }
     if (c.opt.dt <= 0.0) { fb_set_error(24, "dt not set (fb200_set_options)"); return; }
     set_smem_attrs();
@@ -775,7 +832,12 @@ void tracer_step_all(TracerCtx& c) {
         KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
         if (multi) halo_exchange_tiled(*c.halo_elem, (double*)p.txy, c.nlp, 2, st);       // exchange_elem(tr_xy), oce_tracer_mod.F90:68,72
         KL("k_ho_edge", k_ho_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-        KL("k_lo", k_lo<<<c.myNtiles, blk, 0, st>>>(p));
+        switch (c.opt.tra_adv_ver) {
+            case 0: KL("k_lo", k_lo<0><<<c.myNtiles, blk, 0, st>>>(p)); break;
+            case 1: KL("k_lo", k_lo<1><<<c.myNtiles, blk, 0, st>>>(p)); break;
+            case 2: KL("k_lo", k_lo<2><<<c.myNtiles, blk, 0, st>>>(p)); break;
+            default: KL("k_lo", k_lo<3><<<c.myNtiles, blk, 0, st>>>(p)); break;
+        }
         if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
         if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);                   // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
         KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
@@ -788,7 +850,7 @@ void tracer_step_all(TracerCtx& c) {
             ProfScope ps_("copy_told", st);
             CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
         }
-        KL("k_impl_diff", k_impl_diff<<<c.myNtiles, blk, 6 * smt, st>>>(p));
+        KL("k_impl_diff", k_impl_diff<<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
         if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
     }
     if (c.opt.clamp_salt && c.ntr >= 2) { KP p = make_kp(c, 1); KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T)); }

@@ -36,6 +36,9 @@ def run_pair(name, opts=None, model_kw=None, steps=1):
     ("pi", {}, {"tra_adv_hor": "MUSCL"}),
     ("pi", {}, {"tra_adv_hor": "UPW1", "tra_adv_ver": "UPW1"}),
     ("band", {}, {"tra_adv_ver": "CDIFF"}),
+    ("band", {}, {"tra_adv_ver": "PPM"}),
+    ("pi", {}, {"tra_adv_ver": "PPM"}),
+    ("soufflet", {"w_split": True, "w_max_cfl": 0.2}, {"tra_adv_ver": "PPM"}),
     ("band", {"water_flux": 1e-7, "heat_flux": 50.0}, {}),
     ("band", {"num_tracers": 3}, {"tracer_ids": (0, 1, 301)}),
 ])
