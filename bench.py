@@ -55,6 +55,7 @@ def parse():
     ap.add_argument("--nodes", type=int, default=5_000_000, help="target surface nodes per GPU")
     ap.add_argument("--nl", type=int, default=49, help="number of levels (layers = nl-1)")
     ap.add_argument("--cpu-nodes", type=int, default=120_000, help="surface nodes of the CPU-baseline sample")
+    ap.add_argument("--cpu-cores", type=int, default=0, help="processes of the CPU baseline (0 = all host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--block", type=int, default=16, help="block-Jacobi block size of the SSH preconditioner")
@@ -163,7 +164,7 @@ def unpin(arrays):
             pass
 
 
-STATE = ["UV", "Wvel", "Wvel_e", "hnode", "hnode_new", "helem", "Z_3d_n", "zbar_3d_n", "Kv", "Ki",
+STATE = ["UV", "Wvel", "hnode", "hnode_new", "helem", "Z_3d_n", "zbar_3d_n", "Kv", "Ki",
          "heat_flux", "water_flux", "virtual_salt", "relax_salt", "real_salt_flux"]
 
 
@@ -318,44 +319,86 @@ def run_b200(args):
                 clocks=sampler.result(), ntr=ntr, dist=dist)
 
 
+def _cpu_worker(idx, cpu_nodes, nl, steps, warmup, barrier, out):
+    """One host core = one subdomain of the reference's MPI decomposition: build a sample of the workload, then time
+    the oracle's tracer step and the reference's own psolve.c + pARMS (oracle/_ref) on it, all workers stepping at the
+    same time so they share the memory system like the ranks of one node would."""
+    try:
+        from oracle import binding as ob
+        hm, info = build_workload(cpu_nodes, nl)
+        ntr = hm.ipar("num_tracers")
+        o = ob.TracerOracle(hm)
+        rp = hm["ssh_rowptr"]
+        n = hm.ipar("myDim_nod2D")
+        rp0, ci0 = (rp - rp[0]).astype(np.int32), (hm["ssh_colind"] - 1).astype(np.int32)
+        vals, rhs = hm["ssh_values"], hm["ssh_rhs"][:n].copy()
+        ref = ob.RefSolver(rp0, ci0, vals) if ob.ref_lib() is not None else None
+        t_tr, t_ssh = 0.0, 0.0
+        barrier.wait()
+        for k in range(warmup + steps):
+            t0 = time.perf_counter()
+            if ref is not None:
+                ref.solve(rhs, vals, np.zeros(n), new_values=1)
+            else:
+                ob.ssh_solve(rp0, ci0, vals, rhs, np.zeros(n), pc_kind=1, block=1)
+            t1 = time.perf_counter()
+            o.step()
+            t2 = time.perf_counter()
+            if k >= warmup:
+                t_ssh += t1 - t0
+                t_tr += t2 - t1
+        out.put(dict(idx=idx, t_tr=t_tr, t_ssh=t_ssh, units=info["wet_node_layers"] * ntr, rows=n, ntr=ntr, info=info,
+                     ssh_ref=ref is not None))
+    except BaseException as e:          # never leave the parent waiting
+        try:
+            barrier.abort()
+        except Exception:
+            pass
+        out.put(dict(idx=idx, error=repr(e)))
+
+
+def host_cores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_reference(args, steps, warmup):
-    """The reference's CPU path on the host cores, on a bounded sample of the workload: tracer step = the oracle's C
-    restatement of solve_tracers_ale (serial: the reference parallelises over MPI ranks only, and neither MPI nor a
-    Fortran compiler exists here); SSH solve = the reference's OWN psolve.c + pARMS when oracle/_ref was built,
-    else the oracle's BiCGStab."""
-    from oracle import binding as ob
-    from tests import util
-    hm, info = build_workload(args.cpu_nodes, args.nl)
-    ntr = hm.ipar("num_tracers")
-    units = info["wet_node_layers"] * ntr
-    o = ob.TracerOracle(hm)
-    rp = hm["ssh_rowptr"]
-    n = hm.ipar("myDim_nod2D")
-    rp0, ci0 = (rp - rp[0]).astype(np.int32), (hm["ssh_colind"] - 1).astype(np.int32)
-    vals, rhs = hm["ssh_values"], hm["ssh_rhs"][:n].copy()
-    ref = None
-    kind = "port"                       # the headline metric (tracer step) is timed on the port; ssh_kind says what ran the SSH solve
-    if ob.ref_lib() is not None:
-        ref = ob.RefSolver(rp0, ci0, vals)
-    t_tr, t_ssh = 0.0, 0.0
-    for k in range(warmup + steps):
-        t0 = time.perf_counter()
-        if ref is not None:
-            ref.solve(rhs, vals, np.zeros(n), new_values=1)
-        else:
-            ob.ssh_solve(rp0, ci0, vals, rhs, np.zeros(n), pc_kind=1, block=1)
-        t1 = time.perf_counter()
-        o.step()
-        t2 = time.perf_counter()
-        if k >= warmup:
-            t_ssh += t1 - t0
-            t_tr += t2 - t1
-    sample = "band mesh %dx%d nl=%d: %d surface nodes, %d wet node-layers x %d tracers, %d steps; tracer step = serial C " \
-             "restatement (oracle), SSH = %s" % (info["nlon"], info["nlat"], args.nl, info["nod2D"], info["wet_node_layers"],
-                                                ntr, steps, "reference psolve.c+pARMS (oracle/_ref), 1 subdomain" if ref else "oracle BiCGStab")
-    return dict(value=units * steps / t_tr, unit=UNIT, cores=1, kind=kind, ssh_kind="reference" if ref else "port", sample=sample,
-                tracer_ms_per_step=1e3 * t_tr / steps, ssh_ms_per_step=1e3 * t_ssh / steps, ssh_rows=n,
-                ssh_us_per_row=1e6 * t_ssh / steps / n), info
+    """The reference's CPU path on ALL host cores, on a bounded sample of the workload.  FESOM2 parallelises over MPI
+    ranks only (one subdomain per core); neither MPI nor a Fortran compiler exists here, so every core runs one
+    subdomain-sized sample (--cpu-nodes surface nodes) in its own process at the same time, with no halo exchange
+    (which favours the CPU side).  Tracer step = the oracle's C restatement of solve_tracers_ale ("port"); SSH solve =
+    the reference's OWN psolve.c + pARMS when oracle/_ref was built, else the oracle's BiCGStab.  value = sum of the
+    per-core throughputs."""
+    import multiprocessing as mp
+    cores = host_cores() if args.cpu_cores <= 0 else args.cpu_cores
+    per_gb = 3.5 * args.cpu_nodes / 120_000 * args.nl / 49                      # host memory of one sample
+    cores = max(1, min(cores, int(mem_available_gb() * 0.6 / per_gb)))
+    ctx = mp.get_context("spawn")                                                # the parent may hold a CUDA context
+    barrier, out = ctx.Barrier(cores), ctx.Queue()
+    procs = [ctx.Process(target=_cpu_worker, args=(i, args.cpu_nodes, args.nl, steps, warmup, barrier, out)) for i in range(cores)]
+    for p_ in procs:
+        p_.start()
+    res = [out.get() for _ in procs]
+    for p_ in procs:
+        p_.join()
+    bad = [r for r in res if "error" in r]
+    if bad:
+        raise RuntimeError("cpu baseline worker failed: %s" % bad[0]["error"])
+    info, ntr = res[0]["info"], res[0]["ntr"]
+    value = sum(r["units"] * steps / r["t_tr"] for r in res)
+    t_tr = max(r["t_tr"] for r in res)
+    t_ssh = max(r["t_ssh"] for r in res)
+    n = res[0]["rows"]
+    ref = res[0]["ssh_ref"]
+    sample = "%d processes (one per host core), each: band mesh %dx%d nl=%d, %d surface nodes, %d wet node-layers x %d tracers, %d steps; " \
+             "tracer step = C restatement (oracle), SSH = %s; no halo exchange between the samples" % (
+                 cores, info["nlon"], info["nlat"], args.nl, info["nod2D"], info["wet_node_layers"], ntr, steps,
+                 "reference psolve.c+pARMS (oracle/_ref), 1 subdomain per process" if ref else "oracle BiCGStab")
+    return dict(value=value, unit=UNIT, cores=cores, kind="port", ssh_kind="reference" if ref else "port", sample=sample,
+                tracer_ms_per_step=1e3 * t_tr / steps, ssh_ms_per_step=1e3 * t_ssh / steps, ssh_rows=n * cores,
+                ssh_us_per_row=1e6 * t_ssh / steps / (n * cores), per_core_value=value / cores), info
 
 
 def main():

@@ -105,8 +105,10 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
     ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 1, 2, 1);
     ctx_push_node_field(c, helem, L, c.myE, c.helem.p);
     ctx_push_node_field(c, Wvel, nl, N, c.W.p);
-    ctx_push_node_field(c, Wvel_e, nl, N, c.We.p);
-    if (c.opt.w_split) ctx_push_node_field(c, Wvel_i, nl, N, c.Wi.p);
+    if (c.opt.w_split) {                               // without w_split Wvel_e == Wvel and Wvel_i == 0 (oce_ale.F90:2193-2201): not read
+        ctx_push_node_field(c, Wvel_e, nl, N, c.We.p);
+        ctx_push_node_field(c, Wvel_i, nl, N, c.Wi.p);
+    }
     ctx_push_node_field(c, hnode, L, N, c.hnode.p);
     ctx_push_node_field(c, hnode_new, L, N, c.hnode_new.p);
     ctx_push_node_field(c, Z_3d_n, L, N, c.Z3.p);
@@ -155,10 +157,50 @@ void fb200_pull_tracers(double* tr_arr, double* tr_arr_old) {
     }
 }
 
+// solve_tracers_ale with HOST arrays in and out (the call the Fortran shim makes).  The tracers are
+// independent of each other, so the transfers of one overlap the kernels of the other: a copy stream carries
+// push(0), push(1), ..., pull(0), pull(1), ... in that order, the library stream the kernels; events tie kernels(tr) to
+// push(tr) and pull(tr) to kernels(tr).  With pinned host arrays (cudaHostRegister by the caller) the copies are
+// asynchronous; with pageable arrays the same code runs, just without the overlap.
+#define MAX_TR_EVENTS 64
+static cudaStream_t g_copy_stream = nullptr;
+static cudaEvent_t g_ev_push[MAX_TR_EVENTS], g_ev_done[MAX_TR_EVENTS];
+static int g_tr_events = 0;
 void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
-    fb200_push_tracers(tr_arr, tr_arr_old);
-    fb200_solve_tracers();
-    fb200_pull_tracers(tr_arr, tr_arr_old);
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(34, "fb200_solve_tracers_ale before fb200_init_commit"); return; }
+    if (c.ntr > MAX_TR_EVENTS) {                       // no overlap bookkeeping for that many tracers: plain sequence
+        fb200_push_tracers(tr_arr, tr_arr_old); fb200_solve_tracers(); fb200_pull_tracers(tr_arr, tr_arr_old);
+        return;
+    }
+    if (!g_copy_stream) CUDA_CHECK(cudaStreamCreateWithFlags(&g_copy_stream, cudaStreamNonBlocking));
+    for (; g_tr_events < c.ntr; g_tr_events++) {
+        CUDA_CHECK(cudaEventCreateWithFlags(&g_ev_push[g_tr_events], cudaEventDisableTiming));
+        CUDA_CHECK(cudaEventCreateWithFlags(&g_ev_done[g_tr_events], cudaEventDisableTiming));
+    }
+    if (!tracer_step_begin(c)) return;
+    cudaStream_t comp = c.stream, copy = g_copy_stream;
+    const int L = c.nl - 1;
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
+    for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
+        c.stream = copy;
+        ctx_push_node_field(c, tr_arr + rf * tr, L, c.N, c.T.p + nf * tr);
+        ctx_push_node_field(c, tr_arr_old + rf * tr, L, c.N, c.Told.p + nf * tr);
+        CUDA_CHECK(cudaEventRecord(g_ev_push[tr], copy));
+        c.stream = comp;
+        CUDA_CHECK(cudaStreamWaitEvent(comp, g_ev_push[tr], 0));
+        tracer_step_tracer(c, tr);
+        CUDA_CHECK(cudaEventRecord(g_ev_done[tr], comp));
+    }
+    for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
+        c.stream = copy;
+        CUDA_CHECK(cudaStreamWaitEvent(copy, g_ev_done[tr], 0));
+        ctx_pull_node_field(c, c.T.p + nf * tr, L, c.N, tr_arr + rf * tr, 1, 0, false);
+        ctx_pull_node_field(c, c.Told.p + nf * tr, L, c.N, tr_arr_old + rf * tr, 1, 0, false);
+    }
+    c.stream = comp;
+    tracer_step_end(c);
+    CUDA_CHECK(cudaStreamSynchronize(copy));
 }
 
 void fb200_debug_fetch(const char* name, double* out) {

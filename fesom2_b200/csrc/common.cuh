@@ -123,7 +123,10 @@ TracerCtx& tctx();
 void ctx_commit(TracerCtx& c);
 // host (ncomp, lev_ref, ent) component comp  ->  tiled field with dncomp interleaved components, component dcomp
 void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int count_ent, double* dev_tiled, int ncomp = 1, int comp = 0, int dncomp = 1, int dcomp = 0);
-void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host, int dncomp = 1, int dcomp = 0);
+void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host, int dncomp = 1, int dcomp = 0, bool sync = true);
 void ctx_release(TracerCtx& c);
 // tracer_kernels.cu
 void tracer_step_all(TracerCtx& c);
+bool tracer_step_begin(TracerCtx& c);
+void tracer_step_tracer(TracerCtx& c, int tr);
+void tracer_step_end(TracerCtx& c);

@@ -129,7 +129,7 @@ void ctx_push_node_field(TracerCtx& c, const double* host, int lev_ref, int coun
     k_ref_to_tiled<<<tiles, 256, (size_t)c.nlp * 33 * sizeof(double), c.stream>>>(c.stage.p, dev_tiled, count_ent, lev_ref, c.nlp, ncomp, comp, dncomp, dcomp);
     LAUNCH_CHECK();
 }
-void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host, int dncomp, int dcomp) {
+void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int count_ent, double* host, int dncomp, int dcomp, bool sync) {
     if (!fb_ok() || count_ent == 0) return;
     const size_t cnt = (size_t)lev_ref * count_ent;
     ensure_stage(c, cnt);
@@ -137,7 +137,7 @@ void ctx_pull_node_field(TracerCtx& c, const double* dev_tiled, int lev_ref, int
     k_tiled_to_ref<<<tiles, 256, (size_t)c.nlp * 33 * sizeof(double), c.stream>>>(dev_tiled, c.stage.p, count_ent, lev_ref, c.nlp, dncomp, dcomp);
     LAUNCH_CHECK();
     CUDA_CHECK(cudaMemcpyAsync(host, c.stage.p, cnt * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
-    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+    if (sync) CUDA_CHECK(cudaStreamSynchronize(c.stream));
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -780,7 +780,7 @@ static KP make_kp(TracerCtx& c, int tr) {
     p.edge = c.edge.p; p.edgeho = c.edgeho.p; p.ne_slot = c.ne_slot.p; p.nie_slot = c.nie_slot.p; p.el_nb = c.el_nb.p; p.el_lev = c.el_lev.p;
     p.tile_deg = c.tile_deg.p; p.ns_i = c.ns_i.p; p.ns_m = c.ns_m.p; p.ns_d1 = c.ns_d1.p; p.ns_d2 = c.ns_d2.p;
     p.el_g = c.el_g.p; p.el_area = c.el_area.p; p.n_lev = c.n_lev.p; p.n_nbl = c.n_nbl.p; p.n_znb = c.n_znb.p;
-    p.area = c.area.p; p.areasvol = c.areasvol.p; p.UV = c.UV.p; p.helem = c.helem.p; p.W = c.W.p; p.We = c.We.p; p.Wi = c.Wi.p;
+    p.area = c.area.p; p.areasvol = c.areasvol.p; p.UV = c.UV.p; p.helem = c.helem.p; p.W = c.W.p; p.We = c.opt.w_split ? c.We.p : c.W.p; p.Wi = c.Wi.p;
     p.hnode = c.hnode.p; p.hnode_new = c.hnode_new.p; p.Z3 = c.Z3.p; p.zbar3 = c.zbar3.p; p.Kv = c.Kv.p; p.Ki = c.Ki.p;
     p.sl1 = c.sl1.p; p.sl2 = c.sl2.p; p.sl3 = c.sl3.p; p.sw3d = c.sw3d.p;
     p.heat_flux = c.heat_flux.p; p.water_flux = c.water_flux.p; p.virtual_salt = c.virtual_salt.p; p.relax_salt = c.relax_salt.p; p.real_salt_flux = c.real_salt_flux.p;
@@ -801,63 +801,79 @@ static void set_smem_attrs() {
     g_attr_done = true;
 }
 
-// solve_tracers_ale (oce_ale_tracer.F90:101-199) for one partition, everything device resident
-void tracer_step_all(TracerCtx& c) {
-    if (!fb_ok()) return;
-    if (!c.committed) { fb_set_error(20, "fb200_solve_tracers before fb200_init_commit"); return; }
-    if (c.opt.tra_adv_lim != 0) { fb_set_error(21, "tra_adv_lim='NONE' is not implemented on the device path"); return; }
-    if (!c.opt.i_vert_diff) { fb_set_error(23, "i_vert_diff=.false. is not implemented on the device path"); return; }
-    if (c.opt.dt <= 0.0) { fb_set_error(24, "dt not set (fb200_set_options)"); return; }
+// solve_tracers_ale (oce_ale_tracer.F90:101-199) for one partition, everything device resident.
+// tracer_step_begin: option checks + start event; tracer_step_tracer: every kernel of ONE tracer on the library stream
+// (the tracers are independent of each other: fb200_solve_tracers_ale overlaps the host copies of one with the kernels
+// of the other); tracer_step_end: stop event + synchronise.
+bool tracer_step_begin(TracerCtx& c) {
+    if (!fb_ok()) return false;
+    if (!c.committed) { fb_set_error(20, "fb200_solve_tracers before fb200_init_commit"); return false; }
+    if (c.opt.tra_adv_lim != 0) { fb_set_error(21, "tra_adv_lim='NONE' is not implemented on the device path"); return false; }
+    if (!c.opt.i_vert_diff) { fb_set_error(23, "i_vert_diff=.false. is not implemented on the device path"); return false; }
+    if (c.opt.dt <= 0.0) { fb_set_error(24, "dt not set (fb200_set_options)"); return false; }
+    const int LY = (c.nl - 1 + LPT - 1) / LPT;                  // level rows per block: LPT levels per thread cover nl-1 layers
+    if (LY * TILE > 512) { fb_set_error(25, "nl too large for the level-row thread mapping (nl-1 <= 48)"); return false; }
+    if (comm_nranks() > 1 && !c.halo_nod) { fb_set_error(26, "more than one rank but fb200_init_halo was not called"); return false; }
     set_smem_attrs();
     c.stream = fb_stream();
+    CUDA_CHECK(cudaEventRecord(c.ev0, c.stream));
+    return fb_ok();
+}
+
+void tracer_step_tracer(TracerCtx& c, int tr) {
+    if (!fb_ok()) return;
     cudaStream_t st = c.stream;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     const int gN64 = (c.myN + 63) / 64, gE = (c.myE + 127) / 128, gNall = (c.N + 127) / 128;
-    const int LY = (c.nl - 1 + LPT - 1) / LPT;                  // level rows per block: LPT levels per thread cover nl-1 layers
-    if (LY * TILE > 512) { fb_set_error(25, "nl too large for the level-row thread mapping (nl-1 <= 48)"); return; }
+    const int LY = (c.nl - 1 + LPT - 1) / LPT;
     const dim3 blk(TILE, LY);
     // kernels without block-wide exchange run on 8 level rows per block (LPT * 8 = 24 levels) and gridDim.y level chunks
     const dim3 blk8(TILE, 8);
     const int nchunk = (c.nl - 1 + LPT * 8 - 1) / (LPT * 8);
     const size_t smt = (size_t)c.nlp * TILE * sizeof(double);   // one [nlp][32] shared array
     const size_t sm_64 = (size_t)c.nlp * 64 * sizeof(double);
-    CUDA_CHECK(cudaEventRecord(c.ev0, st));
     const bool multi = comm_nranks() > 1 && c.halo_nod != nullptr;
-    if (comm_nranks() > 1 && !c.halo_nod) { fb_set_error(26, "more than one rank but fb200_init_halo was not called"); return; }
 #define KL(name, ...) do { ProfScope ps_(name, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
-    for (int tr = 0; tr < c.ntr; tr++) {
-        KP p = make_kp(c, tr);
-        const double ca = -(0.5 + c.opt.epsilon), cb = 1.5 + c.opt.epsilon;
-        KL("k_ab2", k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb));
-        KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
-        if (multi) halo_exchange_tiled(*c.halo_elem, (double*)p.txy, c.nlp, 2, st);       // exchange_elem(tr_xy), oce_tracer_mod.F90:68,72
-        KL("k_ho_edge", k_ho_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-        switch (c.opt.tra_adv_ver) {
-            case 0: KL("k_lo", k_lo<0><<<c.myNtiles, blk, 0, st>>>(p)); break;
-            case 1: KL("k_lo", k_lo<1><<<c.myNtiles, blk, 0, st>>>(p)); break;
-            case 2: KL("k_lo", k_lo<2><<<c.myNtiles, blk, 0, st>>>(p)); break;
-            default: KL("k_lo", k_lo<3><<<c.myNtiles, blk, 0, st>>>(p)); break;
-        }
-        if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
-        if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);                   // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
-        KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
-        if (multi) halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st);         // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
-        if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
-        if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
-        if (c.opt.do_hor_diff) KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-        KL("k_update", k_update<<<c.myNtiles, blk, 0, st>>>(p));
-        {   // tr_arr_old = tr_arr (:274)
-            ProfScope ps_("copy_told", st);
-            CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
-        }
-        KL("k_impl_diff", k_impl_diff<<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
-        if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
+    KP p = make_kp(c, tr);
+    const double ca = -(0.5 + c.opt.epsilon), cb = 1.5 + c.opt.epsilon;
+    KL("k_ab2", k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb));
+    KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
+    if (multi) halo_exchange_tiled(*c.halo_elem, (double*)p.txy, c.nlp, 2, st);       // exchange_elem(tr_xy), oce_tracer_mod.F90:68,72
+    KL("k_ho_edge", k_ho_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
+    switch (c.opt.tra_adv_ver) {
+        case 0: KL("k_lo", k_lo<0><<<c.myNtiles, blk, 0, st>>>(p)); break;
+        case 1: KL("k_lo", k_lo<1><<<c.myNtiles, blk, 0, st>>>(p)); break;
+        case 2: KL("k_lo", k_lo<2><<<c.myNtiles, blk, 0, st>>>(p)); break;
+        default: KL("k_lo", k_lo<3><<<c.myNtiles, blk, 0, st>>>(p)); break;
     }
-    if (c.opt.clamp_salt && c.ntr >= 2) { KP p = make_kp(c, 1); KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T)); }
+    if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
+    if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);                   // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
+    KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
+    if (multi) halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st);         // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
+    if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
+    if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
+    if (c.opt.do_hor_diff) KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
+    KL("k_update", k_update<<<c.myNtiles, blk, 0, st>>>(p));
+    {   // tr_arr_old = tr_arr (:274)
+        ProfScope ps_("copy_told", st);
+        CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    }
+    KL("k_impl_diff", k_impl_diff<<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
+    if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
+    if (c.opt.clamp_salt && tr == 1) KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T));   // tr_arr(:,:,2) only, :176-198
 #undef KL
-    CUDA_CHECK(cudaEventRecord(c.ev1, st));
-    CUDA_CHECK(cudaStreamSynchronize(st));
+}
+
+void tracer_step_end(TracerCtx& c) {
+    CUDA_CHECK(cudaEventRecord(c.ev1, c.stream));
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));
     if (fb_ok()) CUDA_CHECK(cudaEventElapsedTime(&c.last_ms, c.ev0, c.ev1));
+}
+
+void tracer_step_all(TracerCtx& c) {
+    if (!tracer_step_begin(c)) return;
+    for (int tr = 0; tr < c.ntr; tr++) tracer_step_tracer(c, tr);
+    tracer_step_end(c);
 }
 
 // debug access to work fields (tiled) by name

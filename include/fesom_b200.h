@@ -79,7 +79,9 @@ void fb200_init_halo(int* nod_rPEnum, int* nod_rPE, int* nod_rptr, int* nod_rlis
 void fb200_init_commit(void);
 /* per-step inputs produced by the host (shapes: src/oce_setup_step.F90:205-323, src/oce_ale.F90:94-104):
  * UV(2,nl-1,elems) Wvel/Wvel_e/Wvel_i(nl,N) hnode/hnode_new(nl-1,N) helem(nl-1,myDim_elem2D) Z_3d_n(nl-1,N)
- * zbar_3d_n(nl,N) Kv(nl,N) Ki(nl-1,N) slope_tapered(3,nl-1,N) sw_3d(nl,N); surface fluxes (N) */
+ * zbar_3d_n(nl,N) Kv(nl,N) Ki(nl-1,N) slope_tapered(3,nl-1,N) sw_3d(nl,N); surface fluxes (N).
+ * Only what the selected options read crosses PCIe: Wvel_e/Wvel_i when w_split (otherwise Wvel_e == Wvel and Wvel_i == 0,
+ * src/oce_ale.F90:2193-2201), slope_tapered when Redi, sw_3d when use_sw_pene. */
 void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode, double* hnode_new,
                            double* helem, double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki,
                            double* slope_tapered, double* heat_flux, double* water_flux, double* virtual_salt,
