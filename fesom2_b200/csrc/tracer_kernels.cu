@@ -34,6 +34,8 @@ __device__ __forceinline__ int tbase(int ent, int nlp) { return (ent >> 5) * (nl
 
 // min/max of two non-NaN doubles as one compare + select (the values here are never NaN; fmin/fmax spend several
 // more instructions on NaN propagation)
+__device__ __forceinline__ double omin(double a, double b) { return a < b ? a : b; }     // MIN/MAX as the oracle evaluates them
+__device__ __forceinline__ double omax(double a, double b) { return a > b ? a : b; }
 __device__ __forceinline__ double dmin(double a, double b) { return (b < a) ? b : a; }
 __device__ __forceinline__ double dmax(double a, double b) { return (b > a) ? b : a; }
 // x / b, correctly rounded, given rb = 1.0 / b: quotient estimate plus one exact-residual correction (the last two
@@ -214,7 +216,7 @@ __device__ __forceinline__ NodeCol node_col(const KP& p) {
 //   fct_LO  : oce_adv_tra_driver.F90:83-122 (adv_tra_hor_upw1 + edge scatter + adv_tra_ver_upw1 + column update)
 //   adf_v   : oce_adv_tra_driver.F90:163-179 with init_zero=.false.  (HO(ttfAB, W) - LO(ttf, W)); adf_v(nzmax) is
 //             0 - 0 for every scheme and is never written (the buffer is zero-initialised)
-template <int VER>                          // vertical scheme fixed at compile time: the PPM code stays out of the default kernel
+template <int VER, bool FCT>                // vertical scheme fixed at compile time: the PPM code stays out of the default kernel
 __global__ void LB(512) k_lo(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
@@ -230,6 +232,21 @@ __global__ void LB(512) k_lo(KP p) {
         tn[q] = act[q] ? AT(T, c.b, nz[q]) : 0.0;
     }
     if (!any) return;
+    const double* __restrict__ TAB = p.Told;
+    if (!FCT) {                                                    // tra_adv_lim='NONE': adv_flux_ver = HO(ttfAB, Wvel_e), init_zero=.true. (:163-179)
+#pragma unroll
+        for (int q = 0; q < LPT; q++) {
+            if (!act[q]) continue;
+            const int z = nz[q];
+            double ho;
+            if (VER == 0) ho = ver_qr4c(p, TAB, p.We, c.b, z, c.nzmin, c.nzmax);
+            else if (VER == 1) ho = ver_cdiff(p, TAB, p.We, c.b, z, c.nzmin);
+            else if (VER == 2) ho = ver_ppm(p, TAB, p.We, c.b, z, c.nzmin, c.nzmax);
+            else ho = ver_upw1(TAB, p.We, p.area, c.b, z, c.nzmin, c.nzmax);
+            AT(p.adf_v, c.b, z) = ho - 0.0;
+        }
+        return;
+    }
     const size_t sbase = (size_t)blockIdx.x * p.maxdeg * TILE + threadIdx.x;
     const int ndeg = p.tile_deg[blockIdx.x];
     for (int j = 0; j < ndeg; j++) {
@@ -247,7 +264,6 @@ __global__ void LB(512) k_lo(KP p) {
     }
     const double* __restrict__ Wlo = p.We;                         // explicit part for the LO solution
     const double* __restrict__ Wad = p.w_split ? p.W : p.We;       // LO part of the antidiffusive flux: full W (:131)
-    const double* __restrict__ TAB = p.Told;
 #pragma unroll
     for (int q = 0; q < LPT; q++) {
         if (!act[q]) continue;
@@ -348,6 +364,7 @@ __device__ __noinline__ void node_mean_grad(const int* __restrict__ nie_slot, in
 //   adv_tra_hor_mfct / _muscl / _upw1 with init_zero=.false. (oce_adv_tra_hor.F90:215-733) on ttfAB,
 //   the input flux being adv_tra_hor_upw1(ttf) (oce_adv_tra_driver.F90:83,142-149); the gradients of
 //   fill_up_dn_grad (oce_muscl_adv.F90:285-447) are gathered from txy instead of being stored.
+template <bool FCT>                         // FCT: antidiffusive flux HO - LO and the LO flux; else the HO flux itself (init_zero=.true.)
 __global__ void __launch_bounds__(256, 4) k_ho_edge(KP p) {
     const int e = blockIdx.x * TILE + threadIdx.x;
     if (e >= p.myEd) return;
@@ -368,7 +385,7 @@ __global__ void __launch_bounds__(256, 4) k_ho_edge(KP p) {
         const int segs = mask_segs(r.m1, r.m2, nz);
         if (!segs) continue;
         const double vflux = seg_vflux(p, segs, r.be1, r.be2, r.dX1, r.dY1, r.dX2, r.dY2, nz);
-        const double flo = upw1_flux(AT(T, r.bn1, nz), AT(T, r.bn2, nz), vflux);
+        const double flo = FCT ? upw1_flux(AT(T, r.bn1, nz), AT(T, r.bn2, nz), vflux) : 0.0;
         const double a1 = AT(A, r.bn1, nz), a2 = AT(A, r.bn2, nz);
         double fho;
         if (p.hor == 2) fho = upw1_flux(a1, a2, vflux);
@@ -392,7 +409,7 @@ __global__ void __launch_bounds__(256, 4) k_ho_edge(KP p) {
             fho = -0.5 * (1.0 - p.ph) * cHO - vflux * p.ph * (0.5 * (Tmean1 + Tmean2));
         }
         AT(p.adf_h, be, nz) = fho - flo;
-        AT(p.eflx, be, nz) = flo;                                    // adv_tra_hor_upw1(ttf), gathered by k_lo
+        if (FCT) AT(p.eflx, be, nz) = flo;                           // adv_tra_hor_upw1(ttf), gathered by k_lo
     }
 }
 
@@ -540,6 +557,7 @@ __global__ void __launch_bounds__(256, 3) k_diff_edge(KP p) {
 // K7a: b3 limiting + oce_tra_adv_flux2dtracer (oce_adv_tra_driver.F90:223-268) + del_ttf assembly
 // (oce_ale_tracer.F90:240) + diff_part_hor_redi (:934-1077) + T* update (:294-305).  Node-kernel mapping.
 // Writes tstar; tr_arr_old = tr_arr is done by the caller for all entries.
+template <bool FCT>                         // FCT: limited fluxes (b3) and the LO terms of flux2dtracer; else the raw high-order fluxes
 __global__ void __launch_bounds__(512, 2) k_update(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
@@ -553,7 +571,7 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
         any |= act[q];
         acc[q] = 0.0; fp[q] = fm[q] = 0.0; asv[q] = rasv[q] = 1.0;
         if (!act[q]) continue;
-        const double2 f = AT(p.fpm, c.b, nz[q]); fp[q] = f.x; fm[q] = f.y;
+        if (FCT) { const double2 f = AT(p.fpm, c.b, nz[q]); fp[q] = f.x; fm[q] = f.y; }
         asv[q] = AT(p.areasvol, c.b, nz[q]); rasv[q] = 1.0 / asv[q];
     }
     if (!any) return;
@@ -570,13 +588,16 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
         for (int q = 0; q < LPT; q++) {
             if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
             const double flux = AT(p.adf_h, bed, nz[q]);
-            const double2 fo = AT(p.fpm, bo, nz[q]);
-            // :313-330  flux >= 0: min(fct_plus(n1), fct_minus(n2)) else min(fct_minus(n1), fct_plus(n2)), n1/n2 the
-            // edge's nodes; this node is n2 when `second`
-            const bool self_plus = (flux >= 0.0) != second;
-            double ae = dmin(1.0, self_plus ? fp[q] : fm[q]);
-            ae = dmin(ae, self_plus ? fo.y : fo.x);
-            const double fl = ae * flux;
+            double fl = flux;
+            if (FCT) {
+                const double2 fo = AT(p.fpm, bo, nz[q]);
+                // :313-330  flux >= 0: min(fct_plus(n1), fct_minus(n2)) else min(fct_minus(n1), fct_plus(n2)), n1/n2 the
+                // edge's nodes; this node is n2 when `second`
+                const bool self_plus = (flux >= 0.0) != second;
+                double ae = dmin(1.0, self_plus ? fp[q] : fm[q]);
+                ae = dmin(ae, self_plus ? fo.y : fo.x);
+                fl = ae * flux;
+            }
             const double d = div_by(fl * p.dt, asv[q], rasv[q]);
             acc[q] = second ? acc[q] - d : acc[q] + d;
         }
@@ -585,9 +606,10 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
     for (int q = 0; q < LPT; q++) {                                          // dttf_v, then del_ttf = dttf_h + dttf_v
         if (!act[q]) continue;
         const int z = nz[q];
-        const double fv = limited_fv(p, c.b, z, c.nzmin, c.nzmax);
-        const double fvn = limited_fv(p, c.b, z + 1, c.nzmin, c.nzmax);
-        double dv = 0.0 - AT(T, c.b, z) * AT(p.hnode, c.b, z) + AT(p.LO, c.b, z) * AT(p.hnode_new, c.b, z);
+        const double fv = FCT ? limited_fv(p, c.b, z, c.nzmin, c.nzmax) : AT(p.adf_v, c.b, z);
+        const double fvn = FCT ? limited_fv(p, c.b, z + 1, c.nzmin, c.nzmax) : AT(p.adf_v, c.b, z + 1);
+        double dv = 0.0;
+        if (FCT) dv = 0.0 - AT(T, c.b, z) * AT(p.hnode, c.b, z) + AT(p.LO, c.b, z) * AT(p.hnode_new, c.b, z);
         dv = dv + div_by((fv - fvn) * p.dt, asv[q], rasv[q]);
         acc[q] = acc[q] + dv;
     }
@@ -629,6 +651,7 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
 //   pass 3 (bottom-up)  back substitution (:838-844) and T = T* + dT
 // zinv1 of level nz is the same expression as zinv2 of level nz-1 and is carried over.
 // dynamic smem: cp [blockDim.y][nlp][32]
+template <bool WIMPL>                       // WIMPL = w_split without FCT: implicit upwind advection by Wvel_i enters a, b, c (:604-616, :668-682, :737-744)
 __global__ void __launch_bounds__(64, 8) k_impl_diff(KP p) {
     extern __shared__ double sm[];
     const int lane = threadIdx.x;
@@ -686,6 +709,14 @@ __global__ void __launch_bounds__(64, 8) k_impl_diff(KP p) {
             a = 0.0;
             cc = -(kv1 + Ty1) * zinv2 * zinv * ar1 / asv;
             bb = -cc + h;
+            if (WIMPL) {
+                double v_adv = zinv * (AT(p.area, b, z) / asv);
+                bb = bb + AT(p.Wi, b, z) * v_adv;
+                v_adv = zinv * ar1 / asv;
+                const double wi1 = AT(p.Wi, b, z + 1);
+                bb = bb - omin(0.0, wi1) * v_adv;
+                cc = cc - omax(0.0, wi1) * v_adv;
+            }
         } else if (z <= nzmax - 2) {
             zinv2 = 1.0 / (zn0 - znp);
             double Ty = 0.0, Ty1 = 0.0;
@@ -698,6 +729,15 @@ __global__ void __launch_bounds__(64, 8) k_impl_diff(KP p) {
             a = -(kv0 + Ty) * zinv1 * zinv * (ar0 / asv);
             cc = -(kv1 + Ty1) * zinv2 * zinv * ar1 / asv;
             bb = -a - cc + h;
+            if (WIMPL) {
+                double v_adv = zinv * (ar0 / asv);
+                const double wi0 = AT(p.Wi, b, z), wi1 = AT(p.Wi, b, z + 1);
+                a = a + omin(0.0, wi0) * v_adv;
+                bb = bb + omax(0.0, wi0) * v_adv;
+                v_adv = zinv * ar1 / asv;
+                bb = bb - omin(0.0, wi1) * v_adv;
+                cc = cc - omax(0.0, wi1) * v_adv;
+            }
         } else {
             double Ty = 0.0;
             if (p.Redi) {
@@ -708,6 +748,12 @@ __global__ void __launch_bounds__(64, 8) k_impl_diff(KP p) {
             a = -(kv0 + Ty) * zinv1 * zinv * (ar0 / asv);
             cc = 0.0;
             bb = -a + h;
+            if (WIMPL) {
+                const double v_adv = zinv * (ar0 / asv);
+                const double wi0 = AT(p.Wi, b, z);
+                a = a + omin(0.0, wi0) * v_adv;
+                bb = bb + omax(0.0, wi0) * v_adv;
+            }
         }
         double tr;
         if (z == nzmin) tr = -(bb - h) * t0 - cc * tp1;
@@ -797,7 +843,8 @@ static void set_smem_attrs() {
     const int big = 200 * 1024;
     CUDA_CHECK(cudaFuncSetAttribute(k_vert_impl, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     CUDA_CHECK(cudaFuncSetAttribute(k_fct_bounds, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    CUDA_CHECK(cudaFuncSetAttribute(k_impl_diff, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    CUDA_CHECK(cudaFuncSetAttribute(k_impl_diff<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    CUDA_CHECK(cudaFuncSetAttribute(k_impl_diff<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     g_attr_done = true;
 }
 
@@ -808,7 +855,6 @@ static void set_smem_attrs() {
 bool tracer_step_begin(TracerCtx& c) {
     if (!fb_ok()) return false;
     if (!c.committed) { fb_set_error(20, "fb200_solve_tracers before fb200_init_commit"); return false; }
-    if (c.opt.tra_adv_lim != 0) { fb_set_error(21, "tra_adv_lim='NONE' is not implemented on the device path"); return false; }
     if (!c.opt.i_vert_diff) { fb_set_error(23, "i_vert_diff=.false. is not implemented on the device path"); return false; }
     if (c.opt.dt <= 0.0) { fb_set_error(24, "dt not set (fb200_set_options)"); return false; }
     const int LY = (c.nl - 1 + LPT - 1) / LPT;                  // level rows per block: LPT levels per thread cover nl-1 layers
@@ -839,26 +885,29 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     KL("k_ab2", k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb));
     KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
     if (multi) halo_exchange_tiled(*c.halo_elem, (double*)p.txy, c.nlp, 2, st);       // exchange_elem(tr_xy), oce_tracer_mod.F90:68,72
-    KL("k_ho_edge", k_ho_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-    switch (c.opt.tra_adv_ver) {
-        case 0: KL("k_lo", k_lo<0><<<c.myNtiles, blk, 0, st>>>(p)); break;
-        case 1: KL("k_lo", k_lo<1><<<c.myNtiles, blk, 0, st>>>(p)); break;
-        case 2: KL("k_lo", k_lo<2><<<c.myNtiles, blk, 0, st>>>(p)); break;
-        default: KL("k_lo", k_lo<3><<<c.myNtiles, blk, 0, st>>>(p)); break;
+    const bool fct = c.opt.tra_adv_lim == 0;
+    if (fct) KL("k_ho_edge", k_ho_edge<true><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
+    else KL("k_ho_edge", k_ho_edge<false><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
+#define LO_CASE(V) case V: if (fct) KL("k_lo", k_lo<V, true><<<c.myNtiles, blk, 0, st>>>(p)); else KL("k_lo", k_lo<V, false><<<c.myNtiles, blk, 0, st>>>(p)); break;
+    switch (c.opt.tra_adv_ver) { LO_CASE(0) LO_CASE(1) LO_CASE(2) default: LO_CASE(3) }
+#undef LO_CASE
+    if (fct) {
+        if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
+        if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);               // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
+        KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
+        if (multi) halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st);     // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
     }
-    if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
-    if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);                   // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
-    KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
-    if (multi) halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st);         // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
     if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
     if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
     if (c.opt.do_hor_diff) KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-    KL("k_update", k_update<<<c.myNtiles, blk, 0, st>>>(p));
+    if (fct) KL("k_update", k_update<true><<<c.myNtiles, blk, 0, st>>>(p));
+    else KL("k_update", k_update<false><<<c.myNtiles, blk, 0, st>>>(p));
     {   // tr_arr_old = tr_arr (:274)
         ProfScope ps_("copy_told", st);
         CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
     }
-    KL("k_impl_diff", k_impl_diff<<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
+    if (c.opt.w_split && !fct) KL("k_impl_diff", k_impl_diff<true><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
+    else KL("k_impl_diff", k_impl_diff<false><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
     if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
     if (c.opt.clamp_salt && tr == 1) KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T));   // tr_arr(:,:,2) only, :176-198
 #undef KL

@@ -60,14 +60,15 @@ def test_fct_solution_stays_within_low_order_bounds():
     assert T1[wet].max() <= gmax + 1e-9 and T1[wet].min() >= gmin - 1e-9
 
 
-@pytest.mark.parametrize("hor,ver", [("MFCT", "QR4C"), ("MUSCL", "QR4C"), ("UPW1", "UPW1"), ("MFCT", "CDIFF"), ("MFCT", "PPM")])
-def test_all_scheme_combinations_run_and_conserve(hor, ver):
+@pytest.mark.parametrize("hor,ver,lim", [("MFCT", "QR4C", "FCT"), ("MUSCL", "QR4C", "FCT"), ("UPW1", "UPW1", "FCT"), ("MFCT", "CDIFF", "FCT"),
+                                         ("MFCT", "PPM", "FCT"), ("MUSCL", "QR4C", "NONE"), ("MUSCL", "PPM", "NONE"), ("UPW1", "CDIFF", "NONE")])
+def test_all_scheme_combinations_run_and_conserve(hor, ver, lim):
     hm = util.build_model("band")
     wet = util.wet_mask(hm)
     nl = hm.ipar("nl")
     tr = hm["tr_arr"]
     m0 = (tr[0] * hm["hnode"] * hm["areasvol"][:, :nl - 1])[wet].sum()
-    o = ob.TracerOracle(hm, tra_adv_hor=hor, tra_adv_ver=ver, clamp_salt=False)
+    o = ob.TracerOracle(hm, tra_adv_hor=hor, tra_adv_ver=ver, tra_adv_lim=lim, clamp_salt=False)
     o.step()
     m1 = (tr[0] * hm["hnode_new"] * hm["areasvol"][:, :nl - 1])[wet].sum()
     assert np.isfinite(tr).all()
