@@ -557,7 +557,22 @@ __global__ void __launch_bounds__(256, 3) k_diff_edge(KP p) {
 // K7a: b3 limiting + oce_tra_adv_flux2dtracer (oce_adv_tra_driver.F90:223-268) + del_ttf assembly
 // (oce_ale_tracer.F90:240) + diff_part_hor_redi (:934-1077) + T* update (:294-305).  Node-kernel mapping.
 // Writes tstar; tr_arr_old = tr_arr is done by the caller for all entries.
-template <bool FCT>                         // FCT: limited fluxes (b3) and the LO terms of flux2dtracer; else the raw high-order fluxes
+// diffusive flux through interface z of diff_ver_part_expl_ale (oce_ale_tracer.F90:354-380): surface flux at the top,
+// Kv * dT/dz * area below, zero under the last layer
+__device__ __forceinline__ double expl_vd(const KP& p, const double* __restrict__ T, int n, int b, int z, int ul1, int nl1) {
+    if (z > nl1) return 0.0;
+    if (z == ul1) {
+        if (p.tr_num == 1) return -p.heat_flux[n] / 4.2e6;
+        if (p.tr_num == 2) return p.virtual_salt[n] + p.relax_salt[n] - p.real_salt_flux[n] * p.is_nonlinfs;
+        return 0.0;
+    }
+    const double zinv1 = 1.0 / (AT(p.Z3, b, z - 1) - AT(p.Z3, b, z));
+    return (AT(p.Kv, b, z) + 0.0) * (AT(T, b, z - 1) - AT(T, b, z)) * zinv1 * AT(p.area, b, z);
+}
+
+// FCT: limited fluxes (b3) and the LO terms of flux2dtracer, else the raw high-order fluxes; EXPL: i_vert_diff=.false.,
+// the explicit vertical diffusion joins del_ttf here and no implicit solve follows
+template <bool FCT, bool EXPL>
 __global__ void __launch_bounds__(512, 2) k_update(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
@@ -627,6 +642,19 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
                 const double rhs = second ? 0.0 - cc : 0.0 + cc;
                 acc[q] = acc[q] + div_by(rhs * p.dt, asv[q], rasv[q]);
             }
+        }
+    }
+    if (EXPL) {                                                              // diff_ver_part_expl_ale :381-392
+#pragma unroll
+        for (int q = 0; q < LPT; q++) {
+            if (!act[q]) continue;
+            const int z = nz[q], nl1 = c.nzmax - 1;
+            const double vd = expl_vd(p, T, c.n, c.b, z, c.nzmin, nl1);
+            const double dzb = AT(p.zbar3, c.b, z) - AT(p.zbar3, c.b, z + 1);
+            double term;
+            if (z <= nl1 - 1) term = (vd - expl_vd(p, T, c.n, c.b, z + 1, c.nzmin, nl1)) / dzb * p.dt;
+            else term = (vd / dzb) * p.dt;
+            acc[q] = acc[q] + div_by(term, asv[q], rasv[q]);
         }
     }
 #pragma unroll
@@ -791,8 +819,6 @@ __global__ void __launch_bounds__(64, 8) k_impl_diff(KP p) {
     }
 }
 
-// explicit vertical diffusion variant is not on the default path (i_vert_diff=.true.); see DESIGN.md
-
 // copy own columns of src into dst for levels nzmin..nzmax-1 (used when i_vert_diff is off)
 __global__ void LB(128) k_copy_cols(KP p, double* __restrict__ dst, const double* __restrict__ src) {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
@@ -855,7 +881,6 @@ static void set_smem_attrs() {
 bool tracer_step_begin(TracerCtx& c) {
     if (!fb_ok()) return false;
     if (!c.committed) { fb_set_error(20, "fb200_solve_tracers before fb200_init_commit"); return false; }
-    if (!c.opt.i_vert_diff) { fb_set_error(23, "i_vert_diff=.false. is not implemented on the device path"); return false; }
     if (c.opt.dt <= 0.0) { fb_set_error(24, "dt not set (fb200_set_options)"); return false; }
     const int LY = (c.nl - 1 + LPT - 1) / LPT;                  // level rows per block: LPT levels per thread cover nl-1 layers
     if (LY * TILE > 512) { fb_set_error(25, "nl too large for the level-row thread mapping (nl-1 <= 48)"); return false; }
@@ -900,13 +925,19 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
     if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
     if (c.opt.do_hor_diff) KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-    if (fct) KL("k_update", k_update<true><<<c.myNtiles, blk, 0, st>>>(p));
-    else KL("k_update", k_update<false><<<c.myNtiles, blk, 0, st>>>(p));
+    if (c.opt.i_vert_diff) {
+        if (fct) KL("k_update", k_update<true, false><<<c.myNtiles, blk, 0, st>>>(p));
+        else KL("k_update", k_update<false, false><<<c.myNtiles, blk, 0, st>>>(p));
+    } else {
+        if (fct) KL("k_update", k_update<true, true><<<c.myNtiles, blk, 0, st>>>(p));
+        else KL("k_update", k_update<false, true><<<c.myNtiles, blk, 0, st>>>(p));
+    }
     {   // tr_arr_old = tr_arr (:274)
         ProfScope ps_("copy_told", st);
         CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
     }
-    if (c.opt.w_split && !fct) KL("k_impl_diff", k_impl_diff<true><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
+    if (!c.opt.i_vert_diff) KL("k_copy_cols", k_copy_cols<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, p.tstar));      // T = T*, no implicit solve
+    else if (c.opt.w_split && !fct) KL("k_impl_diff", k_impl_diff<true><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
     else KL("k_impl_diff", k_impl_diff<false><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
     if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
     if (c.opt.clamp_salt && tr == 1) KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T));   // tr_arr(:,:,2) only, :176-198

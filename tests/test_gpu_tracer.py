@@ -39,6 +39,8 @@ def run_pair(name, opts=None, model_kw=None, steps=1):
     ("band", {}, {"tra_adv_ver": "PPM"}),
     ("pi", {}, {"tra_adv_ver": "PPM"}),
     ("soufflet", {"w_split": True, "w_max_cfl": 0.2}, {"tra_adv_ver": "PPM"}),
+    ("pi", {}, {"i_vert_diff": False}),
+    ("band", {"water_flux": 1e-7, "heat_flux": 50.0}, {"i_vert_diff": False, "tra_adv_lim": "NONE", "tra_adv_hor": "MUSCL"}),
     ("pi", {}, {"tra_adv_lim": "NONE", "tra_adv_hor": "MUSCL"}),
     ("band", {}, {"tra_adv_lim": "NONE", "tra_adv_hor": "MUSCL", "tra_adv_ver": "PPM"}),
     ("pi", {"w_split": True, "w_max_cfl": 0.2}, {"tra_adv_lim": "NONE", "tra_adv_hor": "UPW1", "tra_adv_ver": "CDIFF"}),
