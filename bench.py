@@ -39,11 +39,18 @@ ALGO_BYTES = {
     "k_ab2": 24, "k_grad_elem": 40, "k_lo": 118, "k_ho_edge": 144, "k_fct_bounds": 72, "k_update": 120, "k_diff_edge": 88,
     "copy_told": 16, "k_impl_diff": 48, "k_clamp_salt": 16, "k_vert_impl": 40, "k_grad_z": 24,
 }
-# SSH kernels: bytes per matrix row per launch (7-wide SELL rows: 7 x (8 B value + 4 B column) + vectors)
+# SSH kernels: bytes per matrix row per launch (7-wide SELL rows: 7 x (8 B value + 4 B column) + vectors); the
+# block-Jacobi kernels also read their bs x bs inverse once per apply = bs x 8 B per row (added in algo_bytes_row)
 ALGO_BYTES_ROW = {
-    "k_spmv_alpha": 7 * 12 + 8 + 8 + 8, "k_spmv_sigma": 7 * 12 + 8 + 8 + 8, "k_r_update_pc": 8 * 5, "k_x_update": 8 * 8,
-    "k_p_update_pc": 8 * 6, "k_scale_rows": 7 * 8 * 2 + 8 + 8, "k_init_res": 7 * 12 + 8 * 6, "k_pc": 24,
+    "k_spmv_alpha": 7 * 12 + 8 + 8 + 8, "k_spmv_sigma": 7 * 12 + 8 + 8 + 8, "k_r_update_pc": 8 * 4, "k_x_update": 8 * 8,
+    "k_p_update_pc": 8 * 5, "k_scale_rows": 7 * 8 * 2 + 8 + 8, "k_init_res": 7 * 12 + 8 * 6, "k_pc": 16,
 }
+PC_KERNELS = ("k_r_update_pc", "k_p_update_pc", "k_pc")
+
+
+def algo_bytes_row(name, block):
+    b = ALGO_BYTES_ROW.get(name, 0)
+    return b + 8 * block if name in PC_KERNELS else b
 
 
 def parse():
@@ -242,6 +249,8 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # psolve takes HOST arrays by definition (psolve.c:152): page-lock them like the Fortran host would (cudaHostRegister)
+    ssh_pinned = pin([hm.arr("ssh_values"), hm.arr("ssh_rhs"), sol])
     for _ in range(args.warmup):
         one_step()
     launches0 = L.fb200_kernel_launches()
@@ -273,9 +282,8 @@ def run_b200(args):
     # ---- e2e: host buffers through the C ABI, copies inside the timed region
     e2e = None
     if not args.no_e2e:
-        host_arrays = [hm.arr(nm) for nm in STATE] + [hm.arr("tr_arr"), hm.arr("tr_arr_old"), hm.arr("ssh_values"),
-                                                      hm.arr("ssh_rhs"), sol]
-        pinned = pin(host_arrays)
+        host_arrays = [hm.arr(nm) for nm in STATE] + [hm.arr("tr_arr"), hm.arr("tr_arr_old")]
+        pinned = pin(host_arrays) + ssh_pinned
         h2d = sum(hm.arr(nm).nbytes for nm in STATE) + hm.arr("tr_arr").nbytes + hm.arr("tr_arr_old").nbytes \
             + hm.arr("ssh_values").nbytes + 2 * 8 * n_own
         d2h = hm.arr("tr_arr").nbytes + hm.arr("tr_arr_old").nbytes + 8 * n_own
@@ -299,7 +307,9 @@ def run_b200(args):
         barrier()
         e2e_ms = a.elapsed_time(b) / ksteps
         unpin(pinned)
+        ssh_pinned = []
         e2e = {"ms_per_step": e2e_ms, "steps": ksteps, "h2d": h2d, "d2h": d2h, "pinned_arrays": len(pinned)}
+    unpin(ssh_pinned)
 
     # ---- max over ranks
     vals = torch.tensor([tra_ms, ssh_ms, tot_ms, e2e["ms_per_step"] if e2e else 0.0, float(units_per_step)],
@@ -441,14 +451,14 @@ def main():
     if dom:
         name, (cnt, ms) = dom
         per = ALGO_BYTES.get(name)
-        bytes_launch = per * wet if per is not None else ALGO_BYTES_ROW.get(name, 0) * rows
+        bytes_launch = per * wet if per is not None else algo_bytes_row(name, args.block) * rows
         avg_ms = ms / cnt
         ach = bytes_launch / (avg_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                 "avg_launch_ms": avg_ms, "share_of_step": ms / sum(v[1] for v in prof.values())}
     kern = {k: {"launches": v[0], "ms": round(v[1], 4),
-                "GBps": round((ALGO_BYTES[k] * wet if k in ALGO_BYTES else ALGO_BYTES_ROW.get(k, 0) * rows) * v[0] / (v[1] * 1e-3) / 1e9, 1) if v[1] > 0 else None}
+                "GBps": round((ALGO_BYTES[k] * wet if k in ALGO_BYTES else algo_bytes_row(k, args.block) * rows) * v[0] / (v[1] * 1e-3) / 1e9, 1) if v[1] > 0 else None}
             for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
     step_bytes = 344.0 * wet * r["ntr"]                     # 344 B per (node, layer, tracer)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": r["world"], "steps": K, "warmup": args.warmup,

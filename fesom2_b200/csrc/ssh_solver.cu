@@ -14,6 +14,7 @@
 #include "fesom_b200.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 
@@ -36,7 +37,8 @@ struct Solver {
     DevBuf<double> partial;                  // [2][nblocks]
     DevBuf<SolverScal> scal;
     DevBuf<unsigned> counter;
-    int nblocks = 0;
+    int nblocks = 0;                         // one 256-row block per launch block (kernels without a reduction)
+    int nred = 0;                            // persistent grid of the reducing kernels (grid-stride over the rows)
     int last_its = 0; double last_res = 0.0;
     SolverScal* h_scal = nullptr;            // pinned mirror of the device scalars (convergence polling)
     cudaGraphExec_t graph = nullptr;         // `poll` BiCGStab iterations captured once (kernels + NCCL), replayed per poll
@@ -157,13 +159,12 @@ __global__ void __launch_bounds__(SBS) k_init_res(int n, const int* __restrict__
                                                   const double* __restrict__ rhs, const double* __restrict__ scale, const double* __restrict__ x,
                                                   double* __restrict__ y, double* __restrict__ r, double* __restrict__ p,
                                                   double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
-    const int i = blockIdx.x * SBS + threadIdx.x;
     double a = 0.0, b = 0.0;
-    if (i < n) {
+    for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) {
         const double yi = rhs[i] * scale[i];
         const double ri = yi - sell_row(sptr, scol, sval, x, i);
         y[i] = yi; r[i] = ri; p[i] = ri;
-        a = ri * ri; b = yi * ri;
+        a += ri * ri; b += yi * ri;
     }
     reduce2(a, b, partial, counter, nblocks, FIN(SC_INIT));
 }
@@ -178,9 +179,8 @@ __global__ void __launch_bounds__(SBS) k_spmv_alpha(int n, const int* __restrict
                                                     const double* __restrict__ pt, const double* __restrict__ r0, double* __restrict__ v,
                                                     double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
     if (sc->done) return;
-    const int i = blockIdx.x * SBS + threadIdx.x;
     double a = 0.0;
-    if (i < n) { const double vi = sell_row(sptr, scol, sval, pt, i); v[i] = vi; a = r0[i] * vi; }
+    for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) { const double vi = sell_row(sptr, scol, sval, pt, i); v[i] = vi; a += r0[i] * vi; }
     reduce2(a, 0.0, partial, counter, nblocks, FIN(SC_ALPHA));
 }
 // r -= alpha v ; st = M r                                                   bicgstab_ras.c:166-175
@@ -199,9 +199,8 @@ __global__ void __launch_bounds__(SBS) k_spmv_sigma(int n, const int* __restrict
                                                     const double* __restrict__ st, const double* __restrict__ r, double* __restrict__ t,
                                                     double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
     if (sc->done) return;
-    const int i = blockIdx.x * SBS + threadIdx.x;
     double a = 0.0, b = 0.0;
-    if (i < n) { const double ti = sell_row(sptr, scol, sval, st, i); t[i] = ti; a = ti * r[i]; b = ti * ti; }
+    for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) { const double ti = sell_row(sptr, scol, sval, st, i); t[i] = ti; a += ti * r[i]; b += ti * ti; }
     reduce2(a, b, partial, counter, nblocks, FIN(SC_SIGMA));
 }
 // r -= sigma t ; x += alpha pt + sigma st ; omega = r.r ; rho = r0.r ; convergence test ; beta     :200-225
@@ -209,14 +208,13 @@ __global__ void __launch_bounds__(SBS) k_x_update(int n, const double* __restric
                                                   const double* __restrict__ r0, double* __restrict__ r, double* __restrict__ x,
                                                   double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
     if (sc->done) return;
-    const int i = blockIdx.x * SBS + threadIdx.x;
     const double alpha = sc->alpha, sigma = sc->sigma;
     double a = 0.0, b = 0.0;
-    if (i < n) {
+    for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) {
         const double ri = r[i] - sigma * t[i];
         r[i] = ri;
         x[i] += alpha * pt[i] + sigma * st[i];
-        a = ri * ri; b = r0[i] * ri;
+        a += ri * ri; b += r0[i] * ri;
     }
     reduce2(a, b, partial, counter, nblocks, FIN(SC_XUPD));
 }
@@ -360,6 +358,11 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
     const int n = S->n;
     S->nslice = (n + 31) / 32;
     S->nblocks = (n + SBS - 1) / SBS;
+    {   // 8 resident blocks of 256 threads per SM x 148 SMs; FB200_SSH_RED_BLOCKS overrides (tuning)
+        const char* e = getenv("FB200_SSH_RED_BLOCKS");
+        const int cap = e ? std::max(1, atoi(e)) : 148 * 8;
+        S->nred = std::min(S->nblocks, cap);
+    }
     std::vector<int> sptr(S->nslice + 1, 0);
     for (int s = 0; s < S->nslice; s++) {
         int w = 0;
@@ -374,7 +377,7 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
     S->d_rp.upload(S->rp); S->d_ci.upload(S->ci); S->d_sptr.upload(sptr); S->d_scol.upload(scol);
     S->d_vals.alloc(S->nnz); S->d_sval.alloc(scol.size()); S->d_scale.alloc(n);
     for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs}) b->alloc(S->nloc);
-    S->partial.alloc((size_t)2 * S->nblocks); S->scal.alloc(1); S->counter.alloc(1);
+    S->partial.alloc((size_t)2 * S->nred); S->scal.alloc(1); S->counter.alloc(1);
     upload_values(*S, vals);
     build_binv(*S, vals);
     CUDA_CHECK(cudaStreamSynchronize(S->stream));
@@ -389,7 +392,7 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     Solver& S = *it->second;
     S.stream = fb_stream();
     cudaStream_t st = S.stream;
-    const int n = S.n, nb = S.nblocks;
+    const int n = S.n, nb = S.nblocks, nr = S.nred;
     CUDA_CHECK(cudaEventRecord(S.ev0, st));
     if (*newvalues) {
         if (S.reuse) { upload_values(S, vals); if (*newvalues == 2) build_binv(S, vals); }
@@ -404,8 +407,8 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     // one global reduction: all-reduce of (tmp0, tmp1) + the scalar recurrences on every rank
 #define REDUCE(which) do { if (multi) { comm_allreduce_sum(&S.scal.p->tmp0, 2, st); k_apply_scalars<<<1, 1, 0, st>>>(S.scal.p, which); LAUNCH_CHECK(); } } while (0)
     if (multi) halo_exchange_flat(S.halo, S.x.p, st);                            // interface values of the initial guess
-    { ProfScope ps_("k_init_res", st); k_init_res<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
-                                   S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+    { ProfScope ps_("k_init_res", st); k_init_res<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
+                                   S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
     REDUCE(SC_INIT);
     { ProfScope ps_("k_pc", st); k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
     int done = 0, launched = 0;
@@ -414,13 +417,13 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     SolverScal* hs = S.h_scal;
     auto iteration = [&]() {
         if (multi) halo_exchange_flat(S.halo, S.pt.p, st);                       // parms_MatVec: interface exchange of the SpMV input
-        { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+        { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
         REDUCE(SC_ALPHA);
         { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
         if (multi) halo_exchange_flat(S.halo, S.st.p, st);
-        { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nb, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+        { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
         REDUCE(SC_SIGMA);
-        { ProfScope ps_("k_x_update", st); k_x_update<<<nb, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nb, S.scal.p, multi); LAUNCH_CHECK(); }
+        { ProfScope ps_("k_x_update", st); k_x_update<<<nr, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
         REDUCE(SC_XUPD);
         { ProfScope ps_("k_p_update_pc", st); k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
     };
