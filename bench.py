@@ -292,9 +292,10 @@ def run_b200(args):
 
         def e2e_step():
             sol[:] = 0.0
-            solver.solve(new_values=1, sol=sol)                    # H2D values, rhs, guess; D2H solution
-            eng.push_step_state()                                   # H2D velocities, thicknesses, mixing, fluxes
-            eng.solve_tracers_ale(tr_h, tro_h)                      # H2D tracers, step, D2H tracers
+            eng.push_state_early()                                  # H2D old thickness, level depths, mixing, fluxes: enqueued only,
+            solver.solve(new_values=1, sol=sol)                    #   overlaps psolve (H2D values, rhs, guess; D2H solution)
+            eng.push_state_late()                                   # H2D what the SSH solution yields: UV, Wvel, hnode_new, helem
+            eng.solve_tracers_ale(tr_h, tro_h)                      # H2D tracers, step, D2H tracers (copies of one tracer overlap the kernels of the other)
 
         e2e_step()
         ksteps = max(1, min(args.steps, 5))

@@ -19,7 +19,8 @@ LIM = {"FCT": 0, "NONE": 1}
 
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
-           "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_tracers",
+           "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
+           "fb200_push_tracers",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
@@ -171,6 +172,20 @@ class TracerEngine:
                                      _p(a("helem")), _p(a("Z_3d_n")), _p(a("zbar_3d_n")), _p(a("Kv")), _p(a("Ki")),
                                      _p(a("slope_tapered")), _p(a("heat_flux")), _p(a("water_flux")), _p(a("virtual_salt")),
                                      _p(a("relax_salt")), _p(a("real_salt_flux")), _p(a("sw_3d")))
+        _check(self.L)
+
+    def push_state_early(self):
+        """the half of the step state that exists before solve_ssh_ale; returns at once, the copies overlap psolve"""
+        a = self.hm.arr
+        self.L.fb200_push_state_early(_p(a("hnode")), _p(a("Z_3d_n")), _p(a("zbar_3d_n")), _p(a("Kv")), _p(a("Ki")),
+                                      _p(a("slope_tapered")), _p(a("heat_flux")), _p(a("water_flux")), _p(a("virtual_salt")),
+                                      _p(a("relax_salt")), _p(a("real_salt_flux")), _p(a("sw_3d")))
+        _check(self.L)
+
+    def push_state_late(self):
+        """the half the SSH solution produces (UV, Wvel*, hnode_new, helem); returns when all of the state is resident"""
+        a = self.hm.arr
+        self.L.fb200_push_state_late(_p(a("UV")), _p(a("Wvel")), _p(a("Wvel_e")), _p(a("Wvel_i")), _p(a("hnode_new")), _p(a("helem")))
         _check(self.L)
 
     def push_tracers(self, tr=None, tro=None):

@@ -94,23 +94,18 @@ void fb200_init_halo(int* nod_rPEnum, int* nod_rPE, int* nod_rptr, int* nod_rlis
 
 void fb200_init_commit(void) { ctx_commit(tctx()); }
 
-void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode, double* hnode_new, double* helem,
-                           double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki, double* slope_tapered, double* heat_flux,
-                           double* water_flux, double* virtual_salt, double* relax_salt, double* real_salt_flux, double* sw_3d) {
-    TracerCtx& c = tctx();
-    if (!c.committed) { fb_set_error(33, "fb200_push_step_state before fb200_init_commit"); return; }
-    c.stream = fb_stream();
+// ---- per-step state.  Two halves, cut where the reference's time step cuts them (oce_timestep_ale, oce_ale.F90:2521-2790):
+// "early" = what exists before solve_ssh_ale (old thickness and its level depths, mixing coefficients, surface fluxes),
+// "late"  = what the SSH solution produces (update_vel -> UV, compute_hbar_ale/vert_vel_ale -> Wvel*, hnode_new, helem).
+// fb200_push_state_early only ENQUEUES its copies on the library's copy stream and returns, so they overlap psolve;
+// fb200_push_state_late waits for them, pushes the rest and returns when everything is resident.
+static cudaStream_t copy_stream() { return fb_copy_stream(); }
+static void push_early_on(TracerCtx& c, cudaStream_t s, double* hnode, double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki,
+                          double* slope_tapered, double* heat_flux, double* water_flux, double* virtual_salt, double* relax_salt,
+                          double* real_salt_flux, double* sw_3d) {
+    cudaStream_t keep = c.stream; c.stream = s;
     const int L = c.nl - 1, nl = c.nl, N = c.N;
-    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 0, 2, 0);
-    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 1, 2, 1);
-    ctx_push_node_field(c, helem, L, c.myE, c.helem.p);
-    ctx_push_node_field(c, Wvel, nl, N, c.W.p);
-    if (c.opt.w_split) {                               // without w_split Wvel_e == Wvel and Wvel_i == 0 (oce_ale.F90:2193-2201): not read
-        ctx_push_node_field(c, Wvel_e, nl, N, c.We.p);
-        ctx_push_node_field(c, Wvel_i, nl, N, c.Wi.p);
-    }
     ctx_push_node_field(c, hnode, L, N, c.hnode.p);
-    ctx_push_node_field(c, hnode_new, L, N, c.hnode_new.p);
     ctx_push_node_field(c, Z_3d_n, L, N, c.Z3.p);
     ctx_push_node_field(c, zbar_3d_n, nl, N, c.zbar3.p);
     ctx_push_node_field(c, Kv, nl, N, c.Kv.p);
@@ -122,17 +117,58 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
     }
     if (c.opt.use_sw_pene) ctx_push_node_field(c, sw_3d, nl, N, c.sw3d.p);
     const size_t nb = (size_t)N * sizeof(double);
-    CUDA_CHECK(cudaMemcpyAsync(c.heat_flux.p, heat_flux, nb, cudaMemcpyHostToDevice, c.stream));
-    CUDA_CHECK(cudaMemcpyAsync(c.water_flux.p, water_flux, nb, cudaMemcpyHostToDevice, c.stream));
-    CUDA_CHECK(cudaMemcpyAsync(c.virtual_salt.p, virtual_salt, nb, cudaMemcpyHostToDevice, c.stream));
-    CUDA_CHECK(cudaMemcpyAsync(c.relax_salt.p, relax_salt, nb, cudaMemcpyHostToDevice, c.stream));
-    CUDA_CHECK(cudaMemcpyAsync(c.real_salt_flux.p, real_salt_flux, nb, cudaMemcpyHostToDevice, c.stream));
-    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+    CUDA_CHECK(cudaMemcpyAsync(c.heat_flux.p, heat_flux, nb, cudaMemcpyHostToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c.water_flux.p, water_flux, nb, cudaMemcpyHostToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c.virtual_salt.p, virtual_salt, nb, cudaMemcpyHostToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c.relax_salt.p, relax_salt, nb, cudaMemcpyHostToDevice, s));
+    CUDA_CHECK(cudaMemcpyAsync(c.real_salt_flux.p, real_salt_flux, nb, cudaMemcpyHostToDevice, s));
+    c.stream = keep;
+}
+static void push_late_on(TracerCtx& c, cudaStream_t s, double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode_new, double* helem) {
+    cudaStream_t keep = c.stream; c.stream = s;
+    const int L = c.nl - 1, nl = c.nl, N = c.N;
+    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 0, 2, 0);
+    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 1, 2, 1);
+    ctx_push_node_field(c, helem, L, c.myE, c.helem.p);
+    ctx_push_node_field(c, Wvel, nl, N, c.W.p);
+    if (c.opt.w_split) {                               // without w_split Wvel_e == Wvel and Wvel_i == 0 (oce_ale.F90:2193-2201): not read
+        ctx_push_node_field(c, Wvel_e, nl, N, c.We.p);
+        ctx_push_node_field(c, Wvel_i, nl, N, c.Wi.p);
+    }
+    ctx_push_node_field(c, hnode_new, L, N, c.hnode_new.p);
+    c.stream = keep;
+}
+
+void fb200_push_state_early(double* hnode, double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki, double* slope_tapered,
+                            double* heat_flux, double* water_flux, double* virtual_salt, double* relax_salt, double* real_salt_flux,
+                            double* sw_3d) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(33, "fb200_push_state_early before fb200_init_commit"); return; }
+    c.stream = fb_stream();
+    push_early_on(c, copy_stream(), hnode, Z_3d_n, zbar_3d_n, Kv, Ki, slope_tapered, heat_flux, water_flux, virtual_salt, relax_salt,
+                  real_salt_flux, sw_3d);                 // no synchronisation: overlaps whatever the host calls next (psolve)
+}
+
+void fb200_push_state_late(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode_new, double* helem) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(33, "fb200_push_state_late before fb200_init_commit"); return; }
+    c.stream = fb_stream();
+    push_late_on(c, copy_stream(), UV, Wvel, Wvel_e, Wvel_i, hnode_new, helem);    // same stream as the early half: ordered after it
+    CUDA_CHECK(cudaStreamSynchronize(copy_stream()));
+}
+
+void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode, double* hnode_new, double* helem,
+                           double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki, double* slope_tapered, double* heat_flux,
+                           double* water_flux, double* virtual_salt, double* relax_salt, double* real_salt_flux, double* sw_3d) {
+    fb200_push_state_early(hnode, Z_3d_n, zbar_3d_n, Kv, Ki, slope_tapered, heat_flux, water_flux, virtual_salt, relax_salt,
+                           real_salt_flux, sw_3d);
+    if (fb_ok()) fb200_push_state_late(UV, Wvel, Wvel_e, Wvel_i, hnode_new, helem);
 }
 
 void fb200_push_tracers(double* tr_arr, double* tr_arr_old) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(34, "fb200_push_tracers before fb200_init_commit"); return; }
+    fb_copy_sync();
     c.stream = fb_stream();
     const int L = c.nl - 1;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
@@ -148,6 +184,7 @@ void fb200_solve_tracers(void) { tracer_step_all(tctx()); }
 void fb200_pull_tracers(double* tr_arr, double* tr_arr_old) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(35, "fb200_pull_tracers before fb200_init_commit"); return; }
+    fb_copy_sync();
     c.stream = fb_stream();
     const int L = c.nl - 1;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
@@ -163,7 +200,6 @@ void fb200_pull_tracers(double* tr_arr, double* tr_arr_old) {
 // push(tr) and pull(tr) to kernels(tr).  With pinned host arrays (cudaHostRegister by the caller) the copies are
 // asynchronous; with pageable arrays the same code runs, just without the overlap.
 #define MAX_TR_EVENTS 64
-static cudaStream_t g_copy_stream = nullptr;
 static cudaEvent_t g_ev_push[MAX_TR_EVENTS], g_ev_done[MAX_TR_EVENTS];
 static int g_tr_events = 0;
 void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
@@ -173,13 +209,13 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
         fb200_push_tracers(tr_arr, tr_arr_old); fb200_solve_tracers(); fb200_pull_tracers(tr_arr, tr_arr_old);
         return;
     }
-    if (!g_copy_stream) CUDA_CHECK(cudaStreamCreateWithFlags(&g_copy_stream, cudaStreamNonBlocking));
+    copy_stream();
     for (; g_tr_events < c.ntr; g_tr_events++) {
         CUDA_CHECK(cudaEventCreateWithFlags(&g_ev_push[g_tr_events], cudaEventDisableTiming));
         CUDA_CHECK(cudaEventCreateWithFlags(&g_ev_done[g_tr_events], cudaEventDisableTiming));
     }
     if (!tracer_step_begin(c)) return;
-    cudaStream_t comp = c.stream, copy = g_copy_stream;
+    cudaStream_t comp = c.stream, copy = copy_stream();
     const int L = c.nl - 1;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
     for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
@@ -206,6 +242,7 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
 void fb200_debug_fetch(const char* name, double* out) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(36, "fb200_debug_fetch before fb200_init_commit"); return; }
+    fb_copy_sync();
     c.stream = fb_stream();
     int kind = 0, ncomp = 1, comp = 0;
     std::string s(name);
@@ -220,6 +257,6 @@ void fb200_debug_fetch(const char* name, double* out) {
     ctx_pull_node_field(c, f, lev, cnt, out, ncomp, comp);
 }
 
-void fb200_finalize(void) { ctx_release(tctx()); }
+void fb200_finalize(void) { fb_copy_sync(); ctx_release(tctx()); }
 
 }  // extern "C"

@@ -117,6 +117,10 @@ struct TracerCtx {
 // stream every entry point works on: the caller's (fb200_set_stream) or one created by the library
 cudaStream_t fb_stream();
 void fb_set_stream(cudaStream_t s);
+// second stream for host<->device copies that overlap kernels (fb200_push_state_early, fb200_solve_tracers_ale);
+// fb_copy_sync waits for everything enqueued on it (no-op when it was never used)
+cudaStream_t fb_copy_stream();
+void fb_copy_sync();
 
 // context.cu
 TracerCtx& tctx();

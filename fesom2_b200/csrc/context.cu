@@ -83,6 +83,13 @@ int prof_report(char* buf, int cap) {          // "name launches ms\n" per kerne
     return (int)s.size();
 }
 
+static cudaStream_t g_copy_stream = nullptr;
+cudaStream_t fb_copy_stream() {
+    if (!g_copy_stream) CUDA_CHECK(cudaStreamCreateWithFlags(&g_copy_stream, cudaStreamNonBlocking));
+    return g_copy_stream;
+}
+void fb_copy_sync() { if (g_copy_stream) CUDA_CHECK(cudaStreamSynchronize(g_copy_stream)); }
+
 // ---------------------------------------------------------------------------------------------------
 // restage kernels.  One block per tile of 32 entities.  src is the reference array (ncomp, lev_ref, ent).
 __global__ void __launch_bounds__(256) k_ref_to_tiled(const double* __restrict__ src, double* __restrict__ dst, int count_ent,

@@ -886,6 +886,7 @@ bool tracer_step_begin(TracerCtx& c) {
     if (LY * TILE > 512) { fb_set_error(25, "nl too large for the level-row thread mapping (nl-1 <= 48)"); return false; }
     if (comm_nranks() > 1 && !c.halo_nod) { fb_set_error(26, "more than one rank but fb200_init_halo was not called"); return false; }
     set_smem_attrs();
+    fb_copy_sync();                                             // state pushed with fb200_push_state_early must have landed
     c.stream = fb_stream();
     CUDA_CHECK(cudaEventRecord(c.ev0, c.stream));
     return fb_ok();

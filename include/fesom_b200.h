@@ -86,6 +86,15 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
                            double* helem, double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki,
                            double* slope_tapered, double* heat_flux, double* water_flux, double* virtual_salt,
                            double* relax_salt, double* real_salt_flux, double* sw_3d);
+/* The same state in the two halves the reference's time step produces it in (oce_timestep_ale, src/oce_ale.F90:2521-2790):
+ * early = known before solve_ssh_ale (old thickness hnode and its level depths, mixing coefficients from the mixing
+ * step, surface fluxes); late = what the SSH solution yields (update_vel -> UV, compute_hbar_ale / vert_vel_ale ->
+ * Wvel*, hnode_new, helem).  fb200_push_state_early only enqueues its copies and returns, so they overlap psolve; the
+ * host must leave those arrays untouched until fb200_push_state_late has returned (it waits for both halves). */
+void fb200_push_state_early(double* hnode, double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki, double* slope_tapered,
+                            double* heat_flux, double* water_flux, double* virtual_salt, double* relax_salt,
+                            double* real_salt_flux, double* sw_3d);
+void fb200_push_state_late(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode_new, double* helem);
 /* tr_arr / tr_arr_old (nl-1, N, num_tracers) */
 void fb200_push_tracers(double* tr_arr, double* tr_arr_old);
 void fb200_solve_tracers(void);                         /* all tracers, device resident */

@@ -137,6 +137,27 @@ def test_device_resident_steps_equal_push_pull_steps():
     assert np.array_equal(a_tr, b_tr) and np.array_equal(a_tro, b_tro)
 
 
+def test_split_state_push_equals_single_push():
+    """fb200_push_state_early (asynchronous) + psolve + fb200_push_state_late give the same step as fb200_push_step_state"""
+    from fesom2_b200 import api
+    hm = util.build_model("band")
+    hm.compute_ssh_rhs()
+    a_tr, a_tro = hm["tr_arr"].copy(), hm["tr_arr_old"].copy()
+    b_tr, b_tro = a_tr.copy(), a_tro.copy()
+    eng = api.TracerEngine(hm)
+    eng.push_step_state()
+    eng.solve_tracers_ale(a_tr, a_tro)
+    solver = api.SSHSolver(hm)
+    sol = np.zeros_like(hm["d_eta"])
+    eng.push_state_early()
+    solver.solve(new_values=1, sol=sol)
+    eng.push_state_late()
+    eng.solve_tracers_ale(b_tr, b_tro)
+    assert np.array_equal(a_tr, b_tr) and np.array_equal(a_tro, b_tro)
+    assert solver.info()[1] < 1e-10
+    eng.close()
+
+
 def test_div_by_matches_ieee_division():
     """the kernels divide several fluxes by the same areasvol through one reciprocal + an exact-residual correction;
     it must round exactly like '/' (bit-exact parity with the reference's divisions depends on it)"""
