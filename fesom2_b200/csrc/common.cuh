@@ -21,6 +21,10 @@ struct __align__(16) EdgeRec {      // one record per local edge, read by both e
     unsigned long long m1, m2;      // level masks: bit nz set where the segment in element 1 / 2 carries a flux at level nz
     double dX1, dY1, dX2, dY2;      // edge_cross_dxdy(1:4)
 };
+// per (node, slot) record of the node kernels: tile bases of the other node and of the edge, and the level mask
+// m1|m2 of the edge (bit nz set where the edge carries a flux at level nz; levels start at 1) with bit 0 = "this
+// node is the edge's second node" (the flux enters with a minus sign)
+struct __align__(16) SlotRec { int bo, bed; unsigned long long mk; };
 struct __align__(16) EdgeHo {       // extra per-edge data of the high-order reconstruction (48 B)
     double dxa, dyr;                // edge_dxdy(1)*a, edge_dxdy(2)*r_earth  (a = r_earth * mean elem_cos)
     int bup, bdn;                   // tile bases of the up/downwind triangles, -1 if absent
@@ -84,6 +88,7 @@ struct TracerCtx {
     // per (node, incident-edge slot) copies of the edge data, [Ntile][maxdeg][32]: a warp of 32 consecutive nodes reads
     // every item fully coalesced (the edge-indexed records would be a scattered 64-byte gather per lane)
     DevBuf<int> tile_deg;                        // [Ntile] max degree within the tile
+    DevBuf<SlotRec> ns_p;                        // packed (other node, edge, mask|sign), see SlotRec
     DevBuf<int4> ns_i;                           // tile bases: other node, element 1, element 2 (-1), edge (for adf_h)
     DevBuf<ulonglong2> ns_m;                     // EdgeRec::m1, m2
     DevBuf<double2> ns_d1, ns_d2;                // (dX1,dY1), (dX2,dY2)

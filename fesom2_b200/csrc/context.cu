@@ -241,6 +241,14 @@ void ctx_commit(TracerCtx& c) {
             d1[k] = make_double2(r.dX1, r.dY1); d2[k] = make_double2(r.dX2, r.dY2);
         }
         c.ns_i.upload(ni); c.ns_m.upload(mk);
+        {
+            std::vector<SlotRec> sp(ns);
+            for (size_t k = 0; k < ns; k++) {
+                sp[k].bo = ni[k].x; sp[k].bed = ni[k].w;
+                sp[k].mk = slot[k] < 0 ? 0ull : ((mk[k].x | mk[k].y) & ~1ull) | (unsigned long long)(slot[k] & 1);
+            }
+            c.ns_p.upload(sp);
+        }
         std::vector<int> tdeg(c.Ntiles, 0);
         for (int n = 0; n < N; n++) tdeg[n >> 5] = std::max(tdeg[n >> 5], deg[n]);
         c.tile_deg.upload(tdeg);
@@ -277,7 +285,7 @@ void ctx_release(TracerCtx& c) {
                               &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar,
                               &c.helem, &c.adf_h, &c.eflx, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
                               &c.relax_salt, &c.real_salt_flux, &c.stage, &c.el_g, &c.el_area, &c.n_znb}) b->release();
-    c.tile_deg.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
+    c.tile_deg.release(); c.ns_p.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
     c.UV.release(); c.txy.release(); c.fpm.release();
     c.edge.release(); c.edgeho.release(); c.ne_slot.release(); c.nie_slot.release(); c.el_nb.release(); c.el_lev.release();
     c.n_lev.release(); c.n_nbl.release();

@@ -18,6 +18,7 @@ struct KP {                       // kernel parameter block (by value)
     const int* tile_deg;           // per node tile: largest number of incident edges among its 32 nodes
     const int4* ns_i;              // per (node, slot): tile bases (other node, element 1, element 2 or -1, edge)
     const ulonglong2* ns_m;        // level masks (m1, m2)
+    const SlotRec* ns_p;           // packed record the node kernels read: one 16-byte load per (node, slot)
     const double2 *ns_d1, *ns_d2;  // (dX1,dY1), (dX2,dY2)
     const unsigned* el_lev; const double* el_g; const double* el_area; const unsigned* n_lev; const int* n_nbl; const double* n_znb;
     const double2* UV;              // (u, v) per element-level
@@ -217,7 +218,7 @@ __device__ __forceinline__ NodeCol node_col(const KP& p) {
 //   adf_v   : oce_adv_tra_driver.F90:163-179 with init_zero=.false.  (HO(ttfAB, W) - LO(ttf, W)); adf_v(nzmax) is
 //             0 - 0 for every scheme and is never written (the buffer is zero-initialised)
 template <int VER, bool FCT>                // vertical scheme fixed at compile time: the PPM code stays out of the default kernel
-__global__ void LB(512) k_lo(KP p) {
+__global__ void __launch_bounds__(512, 2) k_lo(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
     const double* __restrict__ T = p.T;
@@ -251,10 +252,10 @@ __global__ void LB(512) k_lo(KP p) {
     const int ndeg = p.tile_deg[blockIdx.x];
     for (int j = 0; j < ndeg; j++) {
         const size_t k = sbase + (size_t)j * TILE;
-        const bool second = p.ne_slot[k] & 1;                                  // empty slots have zero masks
-        const int bed = p.ns_i[k].w;
-        const ulonglong2 mm = p.ns_m[k];
-        const unsigned long long many = mm.x | mm.y;
+        const SlotRec sr = p.ns_p[k];                                          // empty slots have zero masks
+        const bool second = sr.mk & 1ull;
+        const int bed = sr.bed;
+        const unsigned long long many = sr.mk;
 #pragma unroll
         for (int q = 0; q < LPT; q++) {
             if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
@@ -451,11 +452,10 @@ __global__ void __launch_bounds__(512, 2) k_fct_bounds(KP p) {
         const int ndeg = p.tile_deg[blockIdx.x];
         for (int j = 0; j < ndeg; j++) {
             const size_t k = sbase + (size_t)j * TILE;
-            const bool second = p.ne_slot[k] & 1;
-            const int4 ni = p.ns_i[k];
-            const int bo = ni.x, bed = ni.w;
-            const ulonglong2 mm = p.ns_m[k];
-            const unsigned long long many = mm.x | mm.y;
+            const SlotRec sr = p.ns_p[k];
+            const bool second = sr.mk & 1ull;
+            const int bo = sr.bo, bed = sr.bed;
+            const unsigned long long many = sr.mk;
 #pragma unroll
             for (int q = 0; q < LPT; q++) {
                 if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
@@ -594,11 +594,10 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
     const int ndeg = p.tile_deg[blockIdx.x];
     for (int j = 0; j < ndeg; j++) {                                         // dttf_h
         const size_t k = sbase + (size_t)j * TILE;
-        const bool second = p.ne_slot[k] & 1;
-        const int4 ni = p.ns_i[k];
-        const int bo = ni.x, bed = ni.w;
-        const ulonglong2 mm = p.ns_m[k];
-        const unsigned long long many = mm.x | mm.y;
+        const SlotRec sr = p.ns_p[k];
+        const bool second = sr.mk & 1ull;
+        const int bo = sr.bo, bed = sr.bed;
+        const unsigned long long many = sr.mk;
 #pragma unroll
         for (int q = 0; q < LPT; q++) {
             if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
@@ -631,10 +630,10 @@ __global__ void __launch_bounds__(512, 2) k_update(KP p) {
     if (p.do_hor_diff) {                                                     // diff_part_hor_redi: fluxes from k_diff_edge
         for (int j = 0; j < ndeg; j++) {
             const size_t k = sbase + (size_t)j * TILE;
-            const bool second = p.ne_slot[k] & 1;
-            const int bed = p.ns_i[k].w;
-            const ulonglong2 mm = p.ns_m[k];
-            const unsigned long long many = mm.x | mm.y;
+            const SlotRec sr = p.ns_p[k];
+            const bool second = sr.mk & 1ull;
+            const int bed = sr.bed;
+            const unsigned long long many = sr.mk;
 #pragma unroll
             for (int q = 0; q < LPT; q++) {
                 if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
@@ -850,7 +849,7 @@ static KP make_kp(TracerCtx& c, int tr) {
     p.hor = c.opt.tra_adv_hor; p.ver = c.opt.tra_adv_ver; p.w_split = c.opt.w_split; p.Redi = c.opt.Redi; p.use_sw_pene = c.opt.use_sw_pene;
     p.do_hor_diff = c.opt.do_hor_diff; p.tracer_id = c.opt.tracer_id[tr]; p.tr_num = tr + 1;
     p.edge = c.edge.p; p.edgeho = c.edgeho.p; p.ne_slot = c.ne_slot.p; p.nie_slot = c.nie_slot.p; p.el_nb = c.el_nb.p; p.el_lev = c.el_lev.p;
-    p.tile_deg = c.tile_deg.p; p.ns_i = c.ns_i.p; p.ns_m = c.ns_m.p; p.ns_d1 = c.ns_d1.p; p.ns_d2 = c.ns_d2.p;
+    p.tile_deg = c.tile_deg.p; p.ns_i = c.ns_i.p; p.ns_m = c.ns_m.p; p.ns_p = c.ns_p.p; p.ns_d1 = c.ns_d1.p; p.ns_d2 = c.ns_d2.p;
     p.el_g = c.el_g.p; p.el_area = c.el_area.p; p.n_lev = c.n_lev.p; p.n_nbl = c.n_nbl.p; p.n_znb = c.n_znb.p;
     p.area = c.area.p; p.areasvol = c.areasvol.p; p.UV = c.UV.p; p.helem = c.helem.p; p.W = c.W.p; p.We = c.opt.w_split ? c.We.p : c.W.p; p.Wi = c.Wi.p;
     p.hnode = c.hnode.p; p.hnode_new = c.hnode_new.p; p.Z3 = c.Z3.p; p.zbar3 = c.zbar3.p; p.Kv = c.Kv.p; p.Ki = c.Ki.p;
