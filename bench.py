@@ -48,6 +48,16 @@ ALGO_BYTES_ROW = {
 PC_KERNELS = ("k_r_update_pc", "k_p_update_pc", "k_pc")
 
 
+def ncu_traffic(name, units):
+    """DRAM bytes per launch of `name` at this run's size, from the committed ncu capture (profiles/r01_ncu_traffic.json:
+    dram__bytes_read.sum + dram__bytes_write.sum per unit at the captured size x this run's units); None if absent"""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))
+        return t[name]["dram_bytes_per_unit"] * units
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def algo_bytes_row(name, block):
     b = ALGO_BYTES_ROW.get(name, 0)
     return b + 8 * block if name in PC_KERNELS else b
@@ -456,7 +466,9 @@ def main():
         avg_ms = ms / cnt
         ach = bytes_launch / (avg_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
+                "traffic": ncu_traffic(name, wet if per is not None else rows),
+                "traffic_source": "profiles/r01_ncu_traffic.json (ncu --set full at 1 M nodes, DRAM bytes per unit x units of this run)",
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                 "avg_launch_ms": avg_ms, "share_of_step": ms / sum(v[1] for v in prof.values())}
     kern = {k: {"launches": v[0], "ms": round(v[1], 4),
                 "GBps": round((ALGO_BYTES[k] * wet if k in ALGO_BYTES else algo_bytes_row(k, args.block) * rows) * v[0] / (v[1] * 1e-3) / 1e9, 1) if v[1] > 0 else None}

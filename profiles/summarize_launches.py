@@ -1,14 +1,14 @@
 #!/usr/bin/env python
 """Per-kernel summary of an `ncu --metrics gpu__time_duration.sum --csv` launch list (profiles/r01_capture.sh).
 usage: python profiles/summarize_launches.py launches.csv[.gz] > summary.txt"""
-import csv, gzip, sys, collections
+import csv, gzip, re, sys, collections
 fn = sys.argv[1]
 f = gzip.open(fn, "rt") if fn.endswith(".gz") else open(fn)
 rows = [r for r in csv.reader(l for l in f if l.startswith('"'))]
 hdr = rows[0]; ki = hdr.index("Kernel Name"); vi = hdr.index("Metric Value"); gi = hdr.index("Grid Size"); bi = hdr.index("Block Size")
 tot = collections.OrderedDict()
 for r in rows[1:]:
-    name = r[ki].split("(")[0]
+    name = re.match(r"(?:void )?([A-Za-z_0-9]+)", r[ki]).group(1)
     t = tot.setdefault(name, [0, 0.0, r[gi], r[bi]])
     t[0] += 1; t[1] += float(r[vi].replace(",", "")) * 1e-6
 alltime = sum(t[1] for t in tot.values())
