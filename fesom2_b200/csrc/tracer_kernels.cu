@@ -218,7 +218,7 @@ __device__ __forceinline__ NodeCol node_col(const KP& p) {
 //   adf_v   : oce_adv_tra_driver.F90:163-179 with init_zero=.false.  (HO(ttfAB, W) - LO(ttf, W)); adf_v(nzmax) is
 //             0 - 0 for every scheme and is never written (the buffer is zero-initialised)
 template <int VER, bool FCT>                // vertical scheme fixed at compile time: the PPM code stays out of the default kernel
-__global__ void __launch_bounds__(512, 2) k_lo(KP p) {
+__global__ void __launch_bounds__(256, 5) k_lo(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
     const double* __restrict__ T = p.T;
@@ -573,7 +573,7 @@ __device__ __forceinline__ double expl_vd(const KP& p, const double* __restrict_
 // FCT: limited fluxes (b3) and the LO terms of flux2dtracer, else the raw high-order fluxes; EXPL: i_vert_diff=.false.,
 // the explicit vertical diffusion joins del_ttf here and no implicit solve follows
 template <bool FCT, bool EXPL>
-__global__ void __launch_bounds__(512, 2) k_update(KP p) {
+__global__ void __launch_bounds__(256, 5) k_update(KP p) {
     const NodeCol c = node_col(p);
     if (!c.valid) return;
     const double* __restrict__ T = p.T;
@@ -913,7 +913,8 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     const bool fct = c.opt.tra_adv_lim == 0;
     if (fct) KL("k_ho_edge", k_ho_edge<true><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
     else KL("k_ho_edge", k_ho_edge<false><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-#define LO_CASE(V) case V: if (fct) KL("k_lo", k_lo<V, true><<<c.myNtiles, blk, 0, st>>>(p)); else KL("k_lo", k_lo<V, false><<<c.myNtiles, blk, 0, st>>>(p)); break;
+    const dim3 gN8(c.myNtiles, nchunk);                         // node kernels without block-wide exchange: 8 level rows per block, like the edge kernels
+#define LO_CASE(V) case V: if (fct) KL("k_lo", k_lo<V, true><<<gN8, blk8, 0, st>>>(p)); else KL("k_lo", k_lo<V, false><<<gN8, blk8, 0, st>>>(p)); break;
     switch (c.opt.tra_adv_ver) { LO_CASE(0) LO_CASE(1) LO_CASE(2) default: LO_CASE(3) }
 #undef LO_CASE
     if (fct) {
@@ -926,11 +927,11 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
     if (c.opt.do_hor_diff) KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
     if (c.opt.i_vert_diff) {
-        if (fct) KL("k_update", k_update<true, false><<<c.myNtiles, blk, 0, st>>>(p));
-        else KL("k_update", k_update<false, false><<<c.myNtiles, blk, 0, st>>>(p));
+        if (fct) KL("k_update", k_update<true, false><<<gN8, blk8, 0, st>>>(p));
+        else KL("k_update", k_update<false, false><<<gN8, blk8, 0, st>>>(p));
     } else {
-        if (fct) KL("k_update", k_update<true, true><<<c.myNtiles, blk, 0, st>>>(p));
-        else KL("k_update", k_update<false, true><<<c.myNtiles, blk, 0, st>>>(p));
+        if (fct) KL("k_update", k_update<true, true><<<gN8, blk8, 0, st>>>(p));
+        else KL("k_update", k_update<false, true><<<gN8, blk8, 0, st>>>(p));
     }
     {   // tr_arr_old = tr_arr (:274)
         ProfScope ps_("copy_told", st);
