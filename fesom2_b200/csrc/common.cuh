@@ -88,6 +88,7 @@ struct TracerCtx {
     // per (node, incident-edge slot) copies of the edge data, [Ntile][maxdeg][32]: a warp of 32 consecutive nodes reads
     // every item fully coalesced (the edge-indexed records would be a scattered 64-byte gather per lane)
     DevBuf<int> tile_deg;                        // [Ntile] max degree within the tile
+    DevBuf<int2> fb_list; int n_fb = 0;          // (edge, level) pairs of k_ho_edge_fb: gradients from the node-mean fallback
     DevBuf<SlotRec> ns_p;                        // packed (other node, edge, mask|sign), see SlotRec
     DevBuf<int4> ns_i;                           // tile bases: other node, element 1, element 2 (-1), edge (for adf_h)
     DevBuf<ulonglong2> ns_m;                     // EdgeRec::m1, m2

@@ -219,6 +219,19 @@ void ctx_commit(TracerCtx& c) {
         deg[n1 - 1]++; deg[n2 - 1]++;
     }
     c.edge.upload(er); c.edgeho.upload(eh);
+    {   // levels of fill_up_dn_grad's fallback branch (oce_muscl_adv.F90:313-328, 372-440): edge without both up/downwind
+        // triangles, or level outside the range they share
+        std::vector<int2> fb;
+        for (int e = 0; e < myEd; e++) {
+            const unsigned long long many = er[e].m1 | er[e].m2;
+            const int lo = eh[e].shared & 255, hi = (eh[e].shared >> 8) & 255;
+            const bool good = (eh[e].shared >> 16) & 1;
+            for (int nz = 1; nz <= nlp && nz < 64; nz++)
+                if (((many >> nz) & 1ull) && !(good && nz >= lo && nz <= hi - 1)) fb.push_back(make_int2(e, nz));
+        }
+        c.n_fb = (int)fb.size();
+        if (c.n_fb) c.fb_list.upload(fb);
+    }
     c.maxdeg = 0; for (int n = 0; n < N; n++) c.maxdeg = std::max(c.maxdeg, deg[n]);
     {
         std::vector<int> slot((size_t)c.Ntiles * c.maxdeg * TILE, -1), fill(N, 0);
@@ -285,7 +298,7 @@ void ctx_release(TracerCtx& c) {
                               &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar,
                               &c.helem, &c.adf_h, &c.eflx, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
                               &c.relax_salt, &c.real_salt_flux, &c.stage, &c.el_g, &c.el_area, &c.n_znb}) b->release();
-    c.tile_deg.release(); c.ns_p.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
+    c.tile_deg.release(); c.fb_list.release(); c.n_fb = 0; c.ns_p.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
     c.UV.release(); c.txy.release(); c.fpm.release();
     c.edge.release(); c.edgeho.release(); c.ne_slot.release(); c.nie_slot.release(); c.el_nb.release(); c.el_lev.release();
     c.n_lev.release(); c.n_nbl.release();

@@ -365,6 +365,40 @@ __device__ __noinline__ void node_mean_grad(const int* __restrict__ nie_slot, in
 //   adv_tra_hor_mfct / _muscl / _upw1 with init_zero=.false. (oce_adv_tra_hor.F90:215-733) on ttfAB,
 //   the input flux being adv_tra_hor_upw1(ttf) (oce_adv_tra_driver.F90:83,142-149); the gradients of
 //   fill_up_dn_grad (oce_muscl_adv.F90:285-447) are gathered from txy instead of being stored.
+// One (edge, level): FB = the gradients come from the node-mean fallback (levels outside the range the up/downwind
+// triangles share, or an edge without them) instead of txy of the two triangles.
+template <bool FCT, bool FB>
+__device__ __forceinline__ void ho_edge_level(const KP& p, const EdgeRec& r, const EdgeHo& h, int be, int nz, int segs, int nbl1, int nbl2) {
+    const double* __restrict__ T = p.T;
+    const double* __restrict__ A = p.Told;
+    const double vflux = seg_vflux(p, segs, r.be1, r.be2, r.dX1, r.dY1, r.dX2, r.dY2, nz);
+    const double flo = FCT ? upw1_flux(AT(T, r.bn1, nz), AT(T, r.bn2, nz), vflux) : 0.0;
+    const double a1 = AT(A, r.bn1, nz), a2 = AT(A, r.bn2, nz);
+    double fho;
+    if (p.hor == 2) fho = upw1_flux(a1, a2, vflux);
+    else {
+        double g1, g2, g3, g4;         // edge_up_dn_grad(1:4): x up, x down, y up, y down
+        if (!FB) {
+            const double2 gu = AT(p.txy, h.bup, nz), gd = AT(p.txy, h.bdn, nz);
+            g1 = gu.x; g2 = gd.x; g3 = gu.y; g4 = gd.y;
+        } else {
+            node_mean_grad(p.nie_slot, p.maxnie, p.el_lev, p.el_area, p.txy, p.nlp, h.n1, nz, g1, g3);
+            node_mean_grad(p.nie_slot, p.maxnie, p.el_lev, p.el_area, p.txy, p.nlp, h.n2, nz, g2, g4);
+        }
+        double Tmean2 = a2 - (2.0 * (a2 - a1) + h.dxa * g2 + h.dyr * g4) / 6.0;
+        double Tmean1 = a1 + (2.0 * (a2 - a1) + h.dxa * g1 + h.dyr * g3) / 6.0;
+        if (p.hor == 0) {              // MUSCL: c_lo, oce_adv_tra_hor.F90:352-353
+            const double c_lo1 = (nbl1 - nz) >= 0 ? 1.0 : 0.0, c_lo2 = (nbl2 - nz) >= 0 ? 1.0 : 0.0;
+            Tmean2 = a2 - (2.0 * (a2 - a1) + h.dxa * g2 + h.dyr * g4) / 6.0 * c_lo2;
+            Tmean1 = a1 + (2.0 * (a2 - a1) + h.dxa * g1 + h.dyr * g3) / 6.0 * c_lo1;
+        }
+        const double cHO = (vflux + fabs(vflux)) * Tmean1 + (vflux - fabs(vflux)) * Tmean2;
+        fho = -0.5 * (1.0 - p.ph) * cHO - vflux * p.ph * (0.5 * (Tmean1 + Tmean2));
+    }
+    AT(p.adf_h, be, nz) = fho - flo;
+    if (FCT) AT(p.eflx, be, nz) = flo;                               // adv_tra_hor_upw1(ttf), gathered by k_lo
+}
+
 template <bool FCT>                         // FCT: antidiffusive flux HO - LO and the LO flux; else the HO flux itself (init_zero=.true.)
 __global__ void __launch_bounds__(256, 4) k_ho_edge(KP p) {
     const int e = blockIdx.x * TILE + threadIdx.x;
@@ -376,42 +410,30 @@ __global__ void __launch_bounds__(256, 4) k_ho_edge(KP p) {
     const int be = blockIdx.x * (p.nlp * TILE) + threadIdx.x;
     const int sh_lo = h.shared & 255, sh_hi = (h.shared >> 8) & 255;
     const bool good = (h.shared >> 16) & 1;
+    const bool grads = p.hor != 2;                                                               // UPW1 needs no gradients: no fallback levels
     const int nbl1 = p.hor == 0 ? p.n_nbl[h.n1] : 0, nbl2 = p.hor == 0 ? p.n_nbl[h.n2] : 0;     // only MUSCL uses nboundary_lay
-    const double* __restrict__ T = p.T;
-    const double* __restrict__ A = p.Told;
 #pragma unroll
     for (int q = 0; q < LPT; q++) {
         const int nz = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
         if (nz > 63) continue;
         const int segs = mask_segs(r.m1, r.m2, nz);
         if (!segs) continue;
-        const double vflux = seg_vflux(p, segs, r.be1, r.be2, r.dX1, r.dY1, r.dX2, r.dY2, nz);
-        const double flo = FCT ? upw1_flux(AT(T, r.bn1, nz), AT(T, r.bn2, nz), vflux) : 0.0;
-        const double a1 = AT(A, r.bn1, nz), a2 = AT(A, r.bn2, nz);
-        double fho;
-        if (p.hor == 2) fho = upw1_flux(a1, a2, vflux);
-        else {
-            double g1, g2, g3, g4;         // edge_up_dn_grad(1:4): x up, x down, y up, y down
-            if (good && nz >= sh_lo && nz <= sh_hi - 1) {
-                const double2 gu = AT(p.txy, h.bup, nz), gd = AT(p.txy, h.bdn, nz);
-                g1 = gu.x; g2 = gd.x; g3 = gu.y; g4 = gd.y;
-            } else {
-                node_mean_grad(p.nie_slot, p.maxnie, p.el_lev, p.el_area, p.txy, p.nlp, h.n1, nz, g1, g3);
-                node_mean_grad(p.nie_slot, p.maxnie, p.el_lev, p.el_area, p.txy, p.nlp, h.n2, nz, g2, g4);
-            }
-            double Tmean2 = a2 - (2.0 * (a2 - a1) + h.dxa * g2 + h.dyr * g4) / 6.0;
-            double Tmean1 = a1 + (2.0 * (a2 - a1) + h.dxa * g1 + h.dyr * g3) / 6.0;
-            if (p.hor == 0) {              // MUSCL: c_lo, oce_adv_tra_hor.F90:352-353
-                const double c_lo1 = (nbl1 - nz) >= 0 ? 1.0 : 0.0, c_lo2 = (nbl2 - nz) >= 0 ? 1.0 : 0.0;
-                Tmean2 = a2 - (2.0 * (a2 - a1) + h.dxa * g2 + h.dyr * g4) / 6.0 * c_lo2;
-                Tmean1 = a1 + (2.0 * (a2 - a1) + h.dxa * g1 + h.dyr * g3) / 6.0 * c_lo1;
-            }
-            const double cHO = (vflux + fabs(vflux)) * Tmean1 + (vflux - fabs(vflux)) * Tmean2;
-            fho = -0.5 * (1.0 - p.ph) * cHO - vflux * p.ph * (0.5 * (Tmean1 + Tmean2));
-        }
-        AT(p.adf_h, be, nz) = fho - flo;
-        if (FCT) AT(p.eflx, be, nz) = flo;                           // adv_tra_hor_upw1(ttf), gathered by k_lo
+        if (grads && !(good && nz >= sh_lo && nz <= sh_hi - 1)) continue;                        // fallback level: k_ho_edge_fb (list built at commit)
+        ho_edge_level<FCT, false>(p, r, h, be, nz, segs, nbl1, nbl2);
     }
+}
+// the (edge, level) pairs whose gradients are node means (about 2 % of them on a ragged-bottom mesh, but spread over
+// 40 % of the edges): one thread per pair from a list built at commit, so no warp of k_ho_edge diverges into the
+// element loops of node_mean_grad
+template <bool FCT>
+__global__ void __launch_bounds__(128) k_ho_edge_fb(KP p, const int2* __restrict__ list, int count) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const int e = list[i].x, nz = list[i].y;
+    const EdgeRec r = p.edge[e];
+    const EdgeHo h = p.edgeho[e];
+    const int nbl1 = p.hor == 0 ? p.n_nbl[h.n1] : 0, nbl2 = p.hor == 0 ? p.n_nbl[h.n2] : 0;
+    ho_edge_level<FCT, true>(p, r, h, tbase(e, p.nlp), nz, mask_segs(r.m1, r.m2, nz), nbl1, nbl2);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -913,6 +935,11 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     const bool fct = c.opt.tra_adv_lim == 0;
     if (fct) KL("k_ho_edge", k_ho_edge<true><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
     else KL("k_ho_edge", k_ho_edge<false><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
+    if (c.opt.tra_adv_hor != 2 && c.n_fb > 0) {
+        const int gfb = (c.n_fb + 127) / 128;
+        if (fct) KL("k_ho_edge_fb", k_ho_edge_fb<true><<<gfb, 128, 0, st>>>(p, c.fb_list.p, c.n_fb));
+        else KL("k_ho_edge_fb", k_ho_edge_fb<false><<<gfb, 128, 0, st>>>(p, c.fb_list.p, c.n_fb));
+    }
     const dim3 gN8(c.myNtiles, nchunk);                         // node kernels without block-wide exchange: 8 level rows per block, like the edge kernels
 #define LO_CASE(V) case V: if (fct) KL("k_lo", k_lo<V, true><<<gN8, blk8, 0, st>>>(p)); else KL("k_lo", k_lo<V, false><<<gN8, blk8, 0, st>>>(p)); break;
     switch (c.opt.tra_adv_ver) { LO_CASE(0) LO_CASE(1) LO_CASE(2) default: LO_CASE(3) }
