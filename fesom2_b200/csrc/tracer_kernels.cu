@@ -531,7 +531,7 @@ __device__ __forceinline__ double limited_fv(const KP& p, int b, int nz, int nzm
 
 // K6: diff_part_hor_redi (oce_ale_tracer.F90:934-1077), the flux through the two median-dual segments of every own
 // edge and level, computed once per edge (edge-kernel mapping) and gathered by k_update.
-__global__ void __launch_bounds__(256, 3) k_diff_edge(KP p) {
+__global__ void __launch_bounds__(256, 5) k_diff_edge(KP p) {
     const int e = blockIdx.x * TILE + threadIdx.x;
     if (e >= p.myEd) return;
     const EdgeRec r = p.edge[e];
