@@ -701,14 +701,13 @@ __global__ void __launch_bounds__(256, 5) k_update(KP p) {
 // zinv1 of level nz is the same expression as zinv2 of level nz-1 and is carried over.
 // dynamic smem: cp [blockDim.y][nlp][32]
 template <bool WIMPL>                       // WIMPL = w_split without FCT: implicit upwind advection by Wvel_i enters a, b, c (:604-616, :668-682, :737-744)
-__global__ void __launch_bounds__(64, 8) k_impl_diff(KP p) {
-    extern __shared__ double sm[];
+__global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
     const int lane = threadIdx.x;
     const int tile = blockIdx.x * blockDim.y + threadIdx.y;
     const int n = tile * TILE + lane;
     if (n >= p.myN) return;
-    double* __restrict__ cps = sm + (size_t)threadIdx.y * p.nlp * TILE + lane;
     const int b = tile * (p.nlp * TILE) + lane;
+    double* __restrict__ cps = p.adf_v + b;                  // c' parked in the vertical-flux scratch (consumed by k_update, rewritten by k_lo)
     const unsigned lv = p.n_lev[n];
     const int nzmin = lv & 255, nzmax = (lv >> 8) & 255;
     const double* __restrict__ hn = p.hnode_new;
@@ -965,8 +964,8 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
         CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
     }
     if (!c.opt.i_vert_diff) KL("k_copy_cols", k_copy_cols<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, p.tstar));      // T = T*, no implicit solve
-    else if (c.opt.w_split && !fct) KL("k_impl_diff", k_impl_diff<true><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
-    else KL("k_impl_diff", k_impl_diff<false><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 2 * smt, st>>>(p));
+    else if (c.opt.w_split && !fct) KL("k_impl_diff", k_impl_diff<true><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 0, st>>>(p));
+    else KL("k_impl_diff", k_impl_diff<false><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 0, st>>>(p));
     if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
     if (c.opt.clamp_salt && tr == 1) KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T));   // tr_arr(:,:,2) only, :176-198
 #undef KL
