@@ -36,7 +36,7 @@ UNIT = "node-level updates/s"
 # Algorithmic HBM bytes per wet (node, layer) of ONE launch of each kernel: every array the
 # kernel must read or write counted once (perfect reuse inside the kernel), 2 elements and 3 edges per node.
 ALGO_BYTES = {
-    "k_ab2": 24, "k_grad_elem": 40, "k_lo": 118, "k_ho_edge": 144, "k_fct_bounds": 72, "k_update": 120, "k_diff_edge": 88,
+    "k_ab2": 24, "k_grad_elem": 40, "k_lo": 118, "k_ho_edge": 144, "k_ho_edge_fb": 3, "k_fct_bounds": 72, "k_update": 120, "k_diff_edge": 88,
     "copy_told": 16, "k_impl_diff": 48, "k_clamp_salt": 16, "k_vert_impl": 40, "k_grad_z": 24,
 }
 # SSH kernels: bytes per matrix row per launch (7-wide SELL rows: 7 x (8 B value + 4 B column) + vectors); the

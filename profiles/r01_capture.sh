@@ -6,6 +6,6 @@ set -x
 B5="python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
 B1="python bench.py --nodes 1000000 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
 $B5 > gpurun_out/plain5.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches_5m.csv $B5 > gpurun_out/ncu5.log 2>&1
-$B1 > gpurun_out/plain1.log 2>&1 && ncu --set full --clock-control none --import-source on -k 'regex:^k_(ab2|ho_edge|update|lo|fct_bounds|impl_diff|diff_edge|grad_elem|clamp_salt)' -c 10 -o gpurun_out/prof_r01_tracer $B1 > gpurun_out/ncu1.log 2>&1
+$B1 > gpurun_out/plain1.log 2>&1 && ncu --set full --clock-control none --import-source on -k 'regex:^k_(ab2|ho_edge|ho_edge_fb|update|lo|fct_bounds|impl_diff|diff_edge|grad_elem|clamp_salt)' -c 11 -o gpurun_out/prof_r01_tracer $B1 > gpurun_out/ncu1.log 2>&1
 $B1 > gpurun_out/plain1b.log 2>&1 && ncu --set full --clock-control none --import-source on -k 'regex:^k_(spmv_alpha|spmv_sigma|p_update_pc|r_update_pc|x_update)' -s 50 -c 5 -o gpurun_out/prof_r01_ssh $B1 > gpurun_out/ncu1b.log 2>&1
 tail -n 2 gpurun_out/ncu5.log gpurun_out/ncu1.log gpurun_out/ncu1b.log
