@@ -63,6 +63,29 @@ def algo_bytes_row(name, block):
     return b + 8 * block if name in PC_KERNELS else b
 
 
+def amg_bytes(levels):
+    """Algorithmic bytes per launch of the multigrid kernels from the hierarchy's sizes [(rows, A, P, R stored SELL entries)]:
+    every stored matrix entry = 8 B value + 4 B column, every vector a kernel reads or writes counted once.  The kernels
+    of the coarse levels share one profile name (k_amg_coarse): its figure is the mean over the coarse launches of a cycle."""
+    if not levels:
+        return {}
+    out = {"k_amg_enter": 60 * levels[0][0]}
+    coarse, ncoarse = 0, 0
+    for l in range(len(levels) - 1):
+        n, a, p, r = levels[l]
+        nc = levels[l + 1][0]
+        per = {"resid": 12 * a + 24 * n, "restrict": 12 * r + 8 * n + 24 * nc, "prolong": 12 * p + 16 * n + 8 * nc, "post": 12 * a + 32 * n}
+        for k, v in per.items():
+            if l == 0:
+                out["k_amg_%s0" % k] = v
+            else:
+                coarse += v
+                ncoarse += 1
+    if ncoarse:
+        out["k_amg_coarse"] = coarse / ncoarse
+    return out
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -75,7 +98,8 @@ def parse():
     ap.add_argument("--cpu-cores", type=int, default=0, help="processes of the CPU baseline (0 = all host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--block", type=int, default=16, help="block-Jacobi block size of the SSH preconditioner")
+    ap.add_argument("--block", type=int, default=16, help="block-Jacobi block size of the SSH preconditioner (--pc bj)")
+    ap.add_argument("--pc", default="amg", choices=["amg", "bj"], help="SSH preconditioner: aggregation multigrid or block-Jacobi")
     return ap.parse_args()
 
 
@@ -237,7 +261,8 @@ def run_b200(args):
     stream = torch.cuda.current_stream()
     api.set_stream(stream.cuda_stream)
     eng = api.TracerEngine(hm)
-    solver = api.SSHSolver(hm, block=args.block)
+    solver = api.SSHSolver(hm, block=args.block, pc=args.pc)
+    amg_levels = solver.amg_levels()
     eng.push_step_state()
     eng.push_tracers()
     L = api.lib()
@@ -337,7 +362,7 @@ def run_b200(args):
         units_all = float(units_per_step)
     return dict(rank=rank, world=world, hm=hm, info=info, reduced=reduced, units_all=units_all, tra_ms=tra_ms, ssh_ms=ssh_ms,
                 tot_ms=tot_ms, t_wall=t_wall, its=its, res=res, prof=prof, e2e=e2e, e2e_ms=e2e_ms, launches=launches,
-                clocks=sampler.result(), ntr=ntr, dist=dist)
+                clocks=sampler.result(), ntr=ntr, dist=dist, amg_levels=amg_levels)
 
 
 def _cpu_worker(idx, cpu_nodes, nl, steps, warmup, barrier, out):
@@ -459,10 +484,19 @@ def main():
     rows = info["nod2D"]
     dom = max(prof.items(), key=lambda kv: kv[1][1]) if prof else None
     roof = None
+    amg_b = amg_bytes(r["amg_levels"])
+
+    def launch_bytes(name):
+        if name in ALGO_BYTES:
+            return ALGO_BYTES[name] * wet
+        if name in amg_b:
+            return amg_b[name]
+        return algo_bytes_row(name, args.block) * rows
+
     if dom:
         name, (cnt, ms) = dom
         per = ALGO_BYTES.get(name)
-        bytes_launch = per * wet if per is not None else algo_bytes_row(name, args.block) * rows
+        bytes_launch = launch_bytes(name)
         avg_ms = ms / cnt
         ach = bytes_launch / (avg_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
@@ -471,7 +505,7 @@ def main():
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                 "avg_launch_ms": avg_ms, "share_of_step": ms / sum(v[1] for v in prof.values())}
     kern = {k: {"launches": v[0], "ms": round(v[1], 4),
-                "GBps": round((ALGO_BYTES[k] * wet if k in ALGO_BYTES else algo_bytes_row(k, args.block) * rows) * v[0] / (v[1] * 1e-3) / 1e9, 1) if v[1] > 0 else None}
+                "GBps": round(launch_bytes(k) * v[0] / (v[1] * 1e-3) / 1e9, 1) if v[1] > 0 else None}
             for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
     step_bytes = 344.0 * wet * r["ntr"]                     # 344 B per (node, layer, tracer)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": r["world"], "steps": K, "warmup": args.warmup,
@@ -480,7 +514,9 @@ def main():
             "config": {"workload": workload, "mesh": {k: info[k] for k in ("nlon", "nlat", "nl", "nod2D", "elem2D", "edge2D", "wet_node_layers", "nod2D_global", "halo_nodes") if k in info},
                        "mesh_is": "global mesh" if r["world"] == 1 else "partition of rank 0", "reduced_for_host_memory": r["reduced"], "l2": "inputs larger than L2 (per-field >> 126 MB)",
                        "parallelism": "1 domain per GPU" if r["world"] == 1 else "the same global mesh in %d node partitions (contiguous split of the numbering, gen_comm.F90 halo rules), NCCL halo exchange + all-reduce" % r["world"],
-                       "ssh_initial_guess": "zero every step", "setup_s": info["setup_s"]},
+                       "ssh_initial_guess": "zero every step", "setup_s": info["setup_s"],
+                       "ssh_preconditioner": ("aggregation multigrid V(1,1), levels (rows, A, P, R entries) = %s" % (r["amg_levels"],)) if args.pc == "amg"
+                       else "block-Jacobi, %d rows per block" % args.block},
             "tracer_ms_per_step": r["tra_ms"] / K,
             "ssh": {"ms_per_step": r["ssh_ms"] / K, "iterations": r["its"], "scaled_residual": r["res"], "rows": rows,
                     "ms_per_iteration": r["ssh_ms"] / K / max(1, r["its"])},

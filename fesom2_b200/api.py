@@ -24,7 +24,9 @@ EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb20
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
-           "fb200_selftest_div", "fb200_init_halo", "fb200_comm_unique_id", "fb200_comm_init", "fb200_comm_finalize", "fb200_psolver_use_graph"]
+           "fb200_selftest_div", "fb200_init_halo", "fb200_comm_unique_id", "fb200_comm_init", "fb200_comm_finalize", "fb200_psolver_use_graph",
+           "fb200_psolver_set_pc", "fb200_psolver_set_amg", "fb200_psolve_amg_info", "fb200_amg_host_build", "fb200_amg_host_levels",
+           "fb200_amg_host_dims", "fb200_amg_host_fetch", "fb200_amg_host_free"]
 
 
 class FesomB200Error(RuntimeError):
@@ -235,11 +237,40 @@ class TracerEngine:
         self.L.fb200_finalize()
 
 
+def amg_host_hierarchy(rp, ci, vals, theta=0.08, max_levels=4, min_rows=200):
+    """The multigrid setup of the SSH preconditioner run on the host (no CUDA call) and read back as scipy CSR matrices:
+    [{"A": .., "P": .., "R": ..}, ...] (P, R absent on the coarsest level).  For the CPU tests of the setup logic."""
+    import scipy.sparse as sp
+    L = lib()
+    rp = np.ascontiguousarray(rp, dtype=np.int32)
+    ci = np.ascontiguousarray(ci, dtype=np.int32)
+    vals = np.ascontiguousarray(vals, dtype=np.float64)
+    h = L.fb200_amg_host_build(_i(len(rp) - 1), _p(rp), _p(ci), _p(vals), _d(theta), _i(max_levels), _i(min_rows))
+    out = []
+    for lev in range(L.fb200_amg_host_levels(_i(h))):
+        d = {}
+        for which, nm in enumerate("APR"):
+            nr, nc, nnz = C.c_int(), C.c_int(), C.c_int()
+            L.fb200_amg_host_dims(_i(h), _i(lev), _i(which), C.byref(nr), C.byref(nc), C.byref(nnz))
+            if nr.value == 0:
+                continue
+            r_, c_, v_ = np.zeros(nr.value + 1, np.int32), np.zeros(nnz.value, np.int32), np.zeros(nnz.value)
+            L.fb200_amg_host_fetch(_i(h), _i(lev), _i(which), _p(r_), _p(c_), _p(v_))
+            d[nm] = sp.csr_matrix((v_, c_, r_), shape=(nr.value, nc.value))
+        out.append(d)
+    L.fb200_amg_host_free(_i(h))
+    return out
+
+
 class SSHSolver:
     """`solve_ssh_ale` (src/oce_ale.F90:2295-2336): psolver_init on first use, psolve per step."""
     SOLBICGS_RAS, PCRAS, PCILUK = 6, 2, 1        # lib/parms/include/fparms.h:25-32
 
-    def __init__(self, hm, ident=1, block=1, soltol=1e-10, maxiter=2000, reuse=1, library=None):
+    PC = {"bj": 0, "amg": 1}
+
+    def __init__(self, hm, ident=1, block=1, soltol=1e-10, maxiter=2000, reuse=1, library=None, pc=None, amg=None):
+        """pc: "bj" (block-Jacobi, `block` rows per block) | "amg" (aggregation multigrid) | None = library default /
+        FB200_SSH_PC; amg = (theta, omega, max_levels, min_rows) overrides the multigrid defaults"""
         self.L = lib() if library is None else library
         self.hm = hm
         self.ident = ident
@@ -247,6 +278,10 @@ class SSHSolver:
         if library is None:
             L.fb200_clear_status()
             L.fb200_psolver_set_block(_i(block))
+            if pc is not None:
+                L.fb200_psolver_set_pc(_i(self.PC[pc]))
+            if amg is not None:
+                L.fb200_psolver_set_amg(_d(amg[0]), _d(amg[1]), _i(amg[2]), _i(amg[3]))
         rp = hm.arr("ssh_rowptr")
         self._part = (hm.arr("part") - 1).astype(np.int32)                 # part-1
         self._rp = (rp - rp[0]).astype(np.int32)                            # rowptr(:)-rowptr(1)
@@ -273,6 +308,17 @@ class SSHSolver:
         res = C.c_double()
         self.L.fb200_psolve_info(_i(self.ident), C.byref(its), C.byref(res))
         return its.value, res.value
+
+    def amg_levels(self):
+        """[(rows, A entries, P entries, R entries)] of the multigrid hierarchy ([] with block-Jacobi)"""
+        out = []
+        for lev in range(8):
+            rows, a, p, r = C.c_int(), C.c_longlong(), C.c_longlong(), C.c_longlong()
+            self.L.fb200_psolve_amg_info(_i(self.ident), _i(lev), C.byref(rows), C.byref(a), C.byref(p), C.byref(r))
+            if rows.value == 0:
+                break
+            out.append((rows.value, a.value, p.value, r.value))
+        return out
 
     def last_ms(self):
         return self.L.fb200_last_ms(b"psolve")

@@ -1,0 +1,287 @@
+// Aggregation multigrid preconditioner of the SSH solve: host setup + device V-cycle.  See ssh_amg.cuh.
+#include "ssh_amg.cuh"
+#include "fesom_b200.h"
+#include <algorithm>
+#include <cmath>
+#include <map>
+
+// ---------------------------------------------------------------------------------------------------
+// host setup (pure C++)
+static void csr_sort_rows(HostCsr& m) {
+    std::vector<std::pair<int, double>> tmp;
+    for (int i = 0; i < m.nrow; i++) {
+        const int a = m.rp[i], b = m.rp[i + 1];
+        tmp.resize(b - a);
+        for (int j = a; j < b; j++) tmp[j - a] = {m.ci[j], m.v[j]};
+        std::sort(tmp.begin(), tmp.end(), [](const std::pair<int, double>& x, const std::pair<int, double>& y) { return x.first < y.first; });
+        for (int j = a; j < b; j++) { m.ci[j] = tmp[j - a].first; m.v[j] = tmp[j - a].second; }
+    }
+}
+
+static HostCsr csr_transpose(const HostCsr& m) {
+    HostCsr t;
+    t.nrow = m.ncol; t.ncol = m.nrow;
+    t.rp.assign(t.nrow + 1, 0);
+    for (int c : m.ci) t.rp[c + 1]++;
+    for (int i = 0; i < t.nrow; i++) t.rp[i + 1] += t.rp[i];
+    t.ci.resize(m.nnz()); t.v.resize(m.nnz());
+    std::vector<int> pos(t.rp.begin(), t.rp.end() - 1);
+    for (int i = 0; i < m.nrow; i++)
+        for (int j = m.rp[i]; j < m.rp[i + 1]; j++) { const int q = pos[m.ci[j]]++; t.ci[q] = i; t.v[q] = m.v[j]; }
+    return t;                        // rows come out with ascending column ids
+}
+
+// C = A * B (Gustavson, dense accumulator); rows of C sorted by column; the sum for one entry runs over A's row order
+static HostCsr csr_matmul(const HostCsr& A, const HostCsr& B) {
+    HostCsr C;
+    C.nrow = A.nrow; C.ncol = B.ncol;
+    C.rp.assign(C.nrow + 1, 0);
+    std::vector<double> acc(B.ncol, 0.0);
+    std::vector<int> mark(B.ncol, -1), cols;
+    for (int i = 0; i < A.nrow; i++) {
+        cols.clear();
+        for (int j = A.rp[i]; j < A.rp[i + 1]; j++) {
+            const int k = A.ci[j];
+            const double a = A.v[j];
+            for (int q = B.rp[k]; q < B.rp[k + 1]; q++) {
+                const int c = B.ci[q];
+                if (mark[c] != i) { mark[c] = i; acc[c] = 0.0; cols.push_back(c); }
+                acc[c] += a * B.v[q];
+            }
+        }
+        std::sort(cols.begin(), cols.end());
+        for (int c : cols) { C.ci.push_back(c); C.v.push_back(acc[c]); }
+        C.rp[i + 1] = (int)C.ci.size();
+    }
+    return C;
+}
+
+static std::vector<double> csr_diag(const HostCsr& A) {
+    std::vector<double> d(A.nrow, 0.0);
+    for (int i = 0; i < A.nrow; i++)
+        for (int j = A.rp[i]; j < A.rp[i + 1]; j++) if (A.ci[j] == i) d[i] += A.v[j];
+    return d;
+}
+
+// greedy aggregation (Vanek, Mandel, Brezina) on the strength graph; returns the number of aggregates
+static int aggregate(const HostCsr& A, const std::vector<char>& strong, std::vector<int>& agg) {
+    const int n = A.nrow;
+    agg.assign(n, -1);
+    int na = 0;
+    for (int i = 0; i < n; i++) {                                  // pass 1: a node whose strong neighbourhood is still free seeds an aggregate
+        if (agg[i] >= 0) continue;
+        bool any = false, free_ = true;
+        for (int j = A.rp[i]; j < A.rp[i + 1]; j++) if (strong[j]) { any = true; if (agg[A.ci[j]] >= 0) { free_ = false; break; } }
+        if (!any || !free_) continue;
+        agg[i] = na;
+        for (int j = A.rp[i]; j < A.rp[i + 1]; j++) if (strong[j]) agg[A.ci[j]] = na;
+        na++;
+    }
+    std::vector<int> join(n, -1);                                  // pass 2: the rest joins a neighbouring pass-1 aggregate
+    for (int i = 0; i < n; i++) {
+        if (agg[i] >= 0) continue;
+        for (int j = A.rp[i]; j < A.rp[i + 1]; j++) if (strong[j] && agg[A.ci[j]] >= 0) { join[i] = agg[A.ci[j]]; break; }
+    }
+    for (int i = 0; i < n; i++) if (agg[i] < 0 && join[i] >= 0) agg[i] = join[i];
+    for (int i = 0; i < n; i++) {                                  // pass 3: leftovers (isolated or surrounded by pass-2 nodes)
+        if (agg[i] >= 0) continue;
+        agg[i] = na;
+        for (int j = A.rp[i]; j < A.rp[i + 1]; j++) if (strong[j] && agg[A.ci[j]] < 0) agg[A.ci[j]] = na;
+        na++;
+    }
+    return na;
+}
+
+void amg_host_setup(const HostCsr& A0, const AmgParams& prm, std::vector<AmgHostLevel>& out) {
+    out.clear();
+    HostCsr A = A0;
+    csr_sort_rows(A);
+    for (int lev = 0; lev < std::max(1, prm.max_levels); lev++) {
+        out.emplace_back();
+        AmgHostLevel& L = out.back();
+        const int n = A.nrow;
+        const std::vector<double> d = csr_diag(A);
+        L.dinv.resize(n);
+        for (int i = 0; i < n; i++) L.dinv[i] = d[i] != 0.0 ? 1.0 / d[i] : 0.0;
+        L.A = std::move(A);
+        if (lev == prm.max_levels - 1 || n < prm.min_rows) break;
+        const HostCsr& Al = L.A;
+        std::vector<char> strong(Al.nnz(), 0);
+        for (int i = 0; i < n; i++)
+            for (int j = Al.rp[i]; j < Al.rp[i + 1]; j++) {
+                const int c = Al.ci[j];
+                if (c != i && std::fabs(Al.v[j]) >= prm.theta * std::sqrt(std::fabs(d[i]) * std::fabs(d[c]))) strong[j] = 1;
+            }
+        std::vector<int> agg;
+        const int na = aggregate(Al, strong, agg);
+        if (na < 1 || na > 0.8 * n) break;                          // coarsening stalled: this level is the coarsest
+        // P = (I - omega_p Df^-1 Af) P_tent,  Af = strong entries + diagonal, weak entries lumped onto the diagonal
+        HostCsr P;
+        P.nrow = n; P.ncol = na; P.rp.assign(n + 1, 0);
+        std::vector<std::pair<int, double>> row;
+        for (int i = 0; i < n; i++) {
+            double df = d[i];
+            for (int j = Al.rp[i]; j < Al.rp[i + 1]; j++) if (Al.ci[j] != i && !strong[j]) df += Al.v[j];
+            if (!(std::fabs(df) > 0.1 * std::fabs(d[i]))) df = d[i];
+            const double w = df != 0.0 ? prm.omega_p / df : 0.0;
+            row.clear();
+            auto add = [&](int c, double val) {
+                for (auto& e : row) if (e.first == c) { e.second += val; return; }
+                row.push_back({c, val});
+            };
+            add(agg[i], 1.0 - w * df);
+            for (int j = Al.rp[i]; j < Al.rp[i + 1]; j++) if (strong[j]) add(agg[Al.ci[j]], -w * Al.v[j]);
+            std::sort(row.begin(), row.end(), [](const std::pair<int, double>& x, const std::pair<int, double>& y) { return x.first < y.first; });
+            for (auto& e : row) { P.ci.push_back(e.first); P.v.push_back(e.second); }
+            P.rp[i + 1] = (int)P.ci.size();
+        }
+        L.R = csr_transpose(P);
+        HostCsr AP = csr_matmul(Al, P);
+        A = csr_matmul(L.R, AP);
+        L.P = std::move(P);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// CPU-test access to the host setup (no CUDA call): build a hierarchy from a CSR matrix and read it back
+static std::map<int, std::vector<AmgHostLevel>*> g_dbg;
+static const HostCsr* dbg_matrix(int handle, int level, int which) {
+    auto it = g_dbg.find(handle);
+    if (it == g_dbg.end() || level < 0 || level >= (int)it->second->size()) return nullptr;
+    const AmgHostLevel& L = (*it->second)[level];
+    return which == 0 ? &L.A : which == 1 ? &L.P : &L.R;
+}
+extern "C" {
+int fb200_amg_host_build(int* n, int* rptr, int* cols, double* vals, double* theta, int* max_levels, int* min_rows) {
+    HostCsr A;
+    A.nrow = A.ncol = *n;
+    A.rp.assign(rptr, rptr + *n + 1);
+    A.ci.assign(cols, cols + rptr[*n]);
+    A.v.assign(vals, vals + rptr[*n]);
+    AmgParams prm;
+    prm.theta = *theta; prm.max_levels = *max_levels; prm.min_rows = *min_rows;
+    auto* h = new std::vector<AmgHostLevel>();
+    amg_host_setup(A, prm, *h);
+    int handle = 1;
+    while (g_dbg.count(handle)) handle++;
+    g_dbg[handle] = h;
+    return handle;
+}
+int fb200_amg_host_levels(int* handle) { auto it = g_dbg.find(*handle); return it == g_dbg.end() ? 0 : (int)it->second->size(); }
+// which: 0 A, 1 P, 2 R
+void fb200_amg_host_dims(int* handle, int* level, int* which, int* nrow, int* ncol, int* nnz) {
+    const HostCsr* m = dbg_matrix(*handle, *level, *which);
+    *nrow = m ? m->nrow : 0; *ncol = m ? m->ncol : 0; *nnz = m ? (int)m->nnz() : 0;
+}
+void fb200_amg_host_fetch(int* handle, int* level, int* which, int* rptr, int* cols, double* vals) {
+    const HostCsr* m = dbg_matrix(*handle, *level, *which);
+    if (!m || m->rp.empty()) return;
+    std::copy(m->rp.begin(), m->rp.end(), rptr);
+    std::copy(m->ci.begin(), m->ci.end(), cols);
+    std::copy(m->v.begin(), m->v.end(), vals);
+}
+void fb200_amg_host_free(int* handle) { auto it = g_dbg.find(*handle); if (it != g_dbg.end()) { delete it->second; g_dbg.erase(it); } }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// device side
+void DevSell::upload(const HostCsr& m) {
+    nrow = m.nrow;
+    nslice = (nrow + 31) / 32;
+    std::vector<int> sp(nslice + 1, 0);
+    for (int s = 0; s < nslice; s++) {
+        int w = 0;
+        for (int i = s * 32; i < std::min(nrow, s * 32 + 32); i++) w = std::max(w, m.rp[i + 1] - m.rp[i]);
+        sp[s + 1] = sp[s] + w * 32;
+    }
+    entries = (size_t)sp[nslice];
+    std::vector<int> col(entries, 0);
+    std::vector<double> val(entries, 0.0);
+    for (int i = 0; i < nrow; i++) {
+        const int base = sp[i >> 5] + (i & 31), w = (sp[(i >> 5) + 1] - sp[i >> 5]) >> 5, len = m.rp[i + 1] - m.rp[i];
+        const int pad = len > 0 ? m.ci[m.rp[i]] : 0;               // padding entries: value 0, a column the row reads anyway
+        for (int k = 0; k < w; k++) {
+            col[base + (k << 5)] = k < len ? m.ci[m.rp[i] + k] : pad;
+            val[base + (k << 5)] = k < len ? m.v[m.rp[i] + k] : 0.0;
+        }
+    }
+    sptr.upload(sp); scol.upload(col); sval.upload(val);
+}
+
+void Amg::upload(const std::vector<AmgHostLevel>& h, double omega_) {
+    release();
+    omega = omega_;
+    L.resize(h.size());
+    for (size_t l = 0; l < h.size(); l++) {
+        AmgDevLevel& D = L[l];
+        D.n = h[l].A.nrow;
+        D.A.upload(h[l].A);
+        if (h[l].P.nrow) { D.P.upload(h[l].P); D.R.upload(h[l].R); }
+        D.dinv.upload(h[l].dinv);
+        D.b.alloc(D.n); D.x.alloc(D.n); D.x2.alloc(D.n); D.r.alloc(D.n);
+    }
+}
+
+void Amg::release() {
+    for (AmgDevLevel& D : L) {
+        D.A.release(); D.P.release(); D.R.release();
+        D.dinv.release(); D.b.release(); D.x.release(); D.x2.release(); D.r.release();
+    }
+    L.clear();
+}
+
+#define ABS 256
+// r = b - A x
+__global__ void __launch_bounds__(ABS) k_amg_resid(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                                   const double* __restrict__ b, const double* __restrict__ x, double* __restrict__ r, const int* done) {
+    if (*done) return;
+    const int i = blockIdx.x * ABS + threadIdx.x;
+    if (i < n) r[i] = b[i] - sell_row(sptr, scol, sval, x, i);
+}
+// b_c = R r ; x_c = omega dinv_c b_c   (pre-smoothing of the coarse level from a zero guess)
+__global__ void __launch_bounds__(ABS) k_amg_restrict(int nc, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                                      const double* __restrict__ r, const double* __restrict__ dinv, double omega,
+                                                      double* __restrict__ bc, double* __restrict__ xc, const int* done) {
+    if (*done) return;
+    const int i = blockIdx.x * ABS + threadIdx.x;
+    if (i >= nc) return;
+    const double v = sell_row(sptr, scol, sval, r, i);
+    bc[i] = v;
+    xc[i] = omega * dinv[i] * v;
+}
+// x += P x_c
+__global__ void __launch_bounds__(ABS) k_amg_prolong(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                                     const double* __restrict__ xc, double* __restrict__ x, const int* done) {
+    if (*done) return;
+    const int i = blockIdx.x * ABS + threadIdx.x;
+    if (i < n) x[i] += sell_row(sptr, scol, sval, xc, i);
+}
+// out = x + omega dinv (b - A x)   (post-smoothing; out != x)
+__global__ void __launch_bounds__(ABS) k_amg_post(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                                  const double* __restrict__ b, const double* __restrict__ x, const double* __restrict__ dinv, double omega,
+                                                  double* __restrict__ out, const int* done) {
+    if (*done) return;
+    const int i = blockIdx.x * ABS + threadIdx.x;
+    if (i < n) out[i] = x[i] + omega * dinv[i] * (b[i] - sell_row(sptr, scol, sval, x, i));
+}
+
+void Amg::cycle(double* out, const int* done, cudaStream_t st) {
+    const int K = (int)L.size();
+    if (K <= 1) return;                                           // single level: the caller's Jacobi step already wrote `out`
+#define AKL(name0, namec, lev, ...) do { ProfScope ps_((lev) == 0 ? name0 : namec, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
+    for (int l = 0; l + 1 < K; l++) {
+        AmgDevLevel& F = L[l];
+        AmgDevLevel& C = L[l + 1];
+        AKL("k_amg_resid0", "k_amg_coarse", l, k_amg_resid<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.r.p, done));
+        AKL("k_amg_restrict0", "k_amg_coarse", l, k_amg_restrict<<<(C.n + ABS - 1) / ABS, ABS, 0, st>>>(C.n, F.R.sptr.p, F.R.scol.p, F.R.sval.p, F.r.p, C.dinv.p, omega, C.b.p, C.x.p, done));
+    }
+    const double* cur = L[K - 1].x.p;
+    for (int l = K - 2; l >= 0; l--) {
+        AmgDevLevel& F = L[l];
+        double* dst = l == 0 ? out : F.x2.p;
+        AKL("k_amg_prolong0", "k_amg_coarse", l, k_amg_prolong<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.P.sptr.p, F.P.scol.p, F.P.sval.p, cur, F.x.p, done));
+        AKL("k_amg_post0", "k_amg_coarse", l, k_amg_post<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.dinv.p, omega, dst, done));
+        cur = dst;
+    }
+#undef AKL
+}

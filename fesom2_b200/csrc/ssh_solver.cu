@@ -2,15 +2,17 @@
 //
 //   psolve.c:58-65,186-193   row scaling  A <- D^-1 A, y <- D^-1 b,  D_i = sum_j |a_ij|      -> k_scale_rows
 //   bicgstab_ras.c:49-259    right-preconditioned BiCGStab, absolute stop ||r||^2 < tol^2     -> k_* below
-//   parms_pc_ras.c / ILU(k)  replaced by block-Jacobi: dense inverses of bs x bs diagonal blocks, built
-//                            once from the initial matrix and kept when values change (psolve.c:200: the
-//                            reference also keeps its factor unless new==2)
+//   parms_pc_ras.c / ILU(k)  replaced by (a) block-Jacobi: dense inverses of bs x bs diagonal blocks, or
+//                            (b) an aggregation-multigrid V-cycle (ssh_amg.cu) on this rank's diagonal block;
+//                            both are built once from the initial matrix and kept when values change
+//                            (psolve.c:200: the reference also keeps its factor unless new==2)
 // Matrix storage: sliced ELL, slice = 32 rows (same tiling as the tracer fields): val[slice][k][32].
 // Dot products: per-block partials reduced by the last finishing block in a fixed order (deterministic,
 // no floating-point atomics); scalars (alpha, sigma, beta, rho, omega) never leave the device; the host
 // polls a "done" flag every few iterations.
 #include "common.cuh"
 #include "comm.cuh"
+#include "ssh_amg.cuh"
 #include "fesom_b200.h"
 #include <algorithm>
 #include <cmath>
@@ -39,6 +41,8 @@ struct Solver {
     DevBuf<unsigned> counter;
     int nblocks = 0;                         // one 256-row block per launch block (kernels without a reduction)
     int nred = 0;                            // persistent grid of the reducing kernels (grid-stride over the rows)
+    int pc = 0;                              // 0 block-Jacobi, 1 aggregation multigrid
+    Amg amg; AmgParams amg_prm;
     int last_its = 0; double last_res = 0.0;
     SolverScal* h_scal = nullptr;            // pinned mirror of the device scalars (convergence polling)
     cudaGraphExec_t graph = nullptr;         // `poll` BiCGStab iterations captured once (kernels + NCCL), replayed per poll
@@ -47,7 +51,10 @@ struct Solver {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 static std::map<int, Solver*> g_solvers;
+#define FB200_DEFAULT_PC 0
 static int g_block = 1;
+static int g_pc = -1;             // -1: FB200_SSH_PC from the environment ("amg" | "bj"), else the default
+static AmgParams g_amg_prm;
 static bool g_use_graph = true;
 static float g_ssh_ms = 0.f;
 double ssh_last_ms() { return (double)g_ssh_ms; }
@@ -68,25 +75,7 @@ __global__ void __launch_bounds__(SBS) k_scale_rows(int n, const int* __restrict
     for (int k = 0; k < w; k++) sval[base + (k << 5)] = (k < j1 - j0) ? vals[j0 + k] * s : 0.0;
 }
 
-// one SELL row times x.  Column indices and values of four entries are fetched before the dependent x gathers are
-// issued, so a thread keeps 8-12 loads in flight instead of one (the sum itself stays in entry order).
-__device__ __forceinline__ double sell_row(const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
-                                           const double* __restrict__ x, int i) {
-    const int s0 = sptr[i >> 5];
-    const int w = (sptr[(i >> 5) + 1] - s0) >> 5;
-    const int base = s0 + (i & 31);
-    double s = 0.0;
-    int k = 0;
-    for (; k + 4 <= w; k += 4) {
-        const int o = base + (k << 5);
-        const int c0 = scol[o], c1 = scol[o + 32], c2 = scol[o + 64], c3 = scol[o + 96];
-        const double a0 = sval[o], a1 = sval[o + 32], a2 = sval[o + 64], a3 = sval[o + 96];
-        const double x0 = x[c0], x1 = x[c1], x2 = x[c2], x3 = x[c3];
-        s += a0 * x0; s += a1 * x1; s += a2 * x2; s += a3 * x3;
-    }
-    for (; k < w; k++) s += sval[base + (k << 5)] * x[scol[base + (k << 5)]];
-    return s;
-}
+// sell_row(): one SELL row times x, see ssh_amg.cuh
 
 // deterministic two-value reduction: block partials -> the last block to finish sums them in a fixed order with all
 // its threads (plain L2 loads after the fence; no floating-point atomics) and calls `fin`
@@ -230,6 +219,28 @@ __global__ void __launch_bounds__(SBS) k_p_update_pc(int n, int bs, const double
     if (i < n) pt[i] = bj_row(binv, p, i, n, bs);
 }
 
+// Multigrid preconditioner, entry of the V-cycle fused with the BiCGStab vector update that produces its input:
+//   MODE 0  in = p                                  (first apply, bicgstab_ras.c:150-156)
+//   MODE 1  r -= alpha v ;           in = r          (:166-175)
+//   MODE 2  p = r + beta (p - sigma v) ; in = p      (:227-230)
+// then b0 = D in (the hierarchy approximates A^-1, the Krylov operator is D^-1 A; D = 1/scale) and the pre-smoothing
+// step from a zero guess x0 = omega dinv0 b0.  With a single level x0 is the preconditioned vector itself.
+template <int MODE>
+__global__ void __launch_bounds__(SBS) k_amg_enter(int n, const double* __restrict__ scale, const double* __restrict__ dinv0, double omega,
+                                                   const double* __restrict__ v, double* __restrict__ r, double* __restrict__ p,
+                                                   double* __restrict__ b0, double* __restrict__ x0, const SolverScal* sc) {
+    if (sc->done) return;
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    if (i >= n) return;
+    double in;
+    if (MODE == 0) in = p[i];
+    else if (MODE == 1) { in = r[i] - sc->alpha * v[i]; r[i] = in; }
+    else { in = r[i] + sc->beta * (p[i] - sc->sigma * v[i]); p[i] = in; }
+    const double b = in / scale[i];
+    b0[i] = b;
+    x0[i] = omega * dinv0[i] * b;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // host side
 static void build_binv(Solver& S, const double* vals) {      // dense inverses of the diagonal blocks of D^-1 A
@@ -266,6 +277,21 @@ static void build_binv(Solver& S, const double* vals) {      // dense inverses o
     S.d_binv.upload(binv);
 }
 
+// hierarchy of this rank's diagonal block (own rows x own columns) of the UNSCALED matrix, which is symmetric
+static void build_amg(Solver& S, const double* vals) {
+    HostCsr A;
+    A.nrow = A.ncol = S.n;
+    A.rp.assign(S.n + 1, 0);
+    A.ci.reserve(S.nnz); A.v.reserve(S.nnz);
+    for (int i = 0; i < S.n; i++) {
+        for (int j = S.rp[i]; j < S.rp[i + 1]; j++) if (S.ci[j] < S.n) { A.ci.push_back(S.ci[j]); A.v.push_back(vals[j]); }
+        A.rp[i + 1] = (int)A.ci.size();
+    }
+    std::vector<AmgHostLevel> h;
+    amg_host_setup(A, S.amg_prm, h);
+    S.amg.upload(h, S.amg_prm.omega);
+}
+
 static void upload_values(Solver& S, const double* vals) {
     CUDA_CHECK(cudaMemcpyAsync(S.d_vals.p, vals, (size_t)S.nnz * sizeof(double), cudaMemcpyHostToDevice, S.stream));
     { ProfScope ps_("k_scale_rows", S.stream); k_scale_rows<<<S.nblocks, SBS, 0, S.stream>>>(S.n, S.d_rp.p, S.d_vals.p, S.d_sptr.p, S.d_sval.p, S.d_scale.p); LAUNCH_CHECK(); }
@@ -284,6 +310,27 @@ void fb200_psolver_set_block(int* block) {
     const int b = *block;
     if (b < 1 || b > 32 || (b & (b - 1))) { fb_set_error(40, "block-Jacobi block size must be a power of two in 1..32"); return; }
     g_block = b;
+}
+
+// preconditioner of solvers created afterwards: 0 block-Jacobi, 1 aggregation multigrid (V(1,1), damped Jacobi)
+void fb200_psolver_set_pc(int* kind) {
+    if (*kind != 0 && *kind != 1) { fb_set_error(46, "fb200_psolver_set_pc: 0 = block-Jacobi, 1 = multigrid"); return; }
+    g_pc = *kind;
+}
+// multigrid parameters (solvers created afterwards): strength threshold, smoother weight, levels, rows below which coarsening stops
+void fb200_psolver_set_amg(double* theta, double* omega, int* max_levels, int* min_rows) {
+    if (*theta < 0.0 || *theta >= 1.0 || *omega <= 0.0 || *omega > 1.0 || *max_levels < 1 || *max_levels > 8 || *min_rows < 1) {
+        fb_set_error(47, "fb200_psolver_set_amg: 0 <= theta < 1, 0 < omega <= 1, 1 <= max_levels <= 8, min_rows >= 1"); return;
+    }
+    g_amg_prm.theta = *theta; g_amg_prm.omega = *omega; g_amg_prm.max_levels = *max_levels; g_amg_prm.min_rows = *min_rows;
+}
+// level sizes of the multigrid hierarchy of solver id: rows and stored SELL entries of A_l, P_l, R_l (0 past the last level)
+void fb200_psolve_amg_info(int* id, int* level, int* rows, long long* a_entries, long long* p_entries, long long* r_entries) {
+    *rows = 0; *a_entries = *p_entries = *r_entries = 0;
+    auto it = g_solvers.find(*id);
+    if (it == g_solvers.end() || *level < 0 || *level >= it->second->amg.levels()) return;
+    const AmgDevLevel& D = it->second->amg.L[*level];
+    *rows = D.n; *a_entries = (long long)D.A.entries; *p_entries = (long long)D.P.entries; *r_entries = (long long)D.R.entries;
 }
 
 // which rows of this rank the other ranks need, and which columns of theirs this rank needs: the interface-variable
@@ -340,6 +387,8 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
     Solver* S = new Solver();
     S->n = part[me + 1] - part[me];                            // rows of this partition (psolve.c:38-43)
     S->nnz = rptr[S->n]; S->reuse = *reuse; S->maxits = *maxits; S->soltol = *soltol; S->bs = g_block;
+    S->pc = g_pc; S->amg_prm = g_amg_prm;
+    if (S->pc < 0) { const char* e = getenv("FB200_SSH_PC"); S->pc = (e && !strcmp(e, "amg")) ? 1 : (e && !strcmp(e, "bj")) ? 0 : FB200_DEFAULT_PC; }
     S->rp.assign(rptr, rptr + S->n + 1);
     S->ci.resize(S->nnz);
     S->stream = fb_stream(); CUDA_CHECK(cudaEventCreate(&S->ev0)); CUDA_CHECK(cudaEventCreate(&S->ev1));
@@ -379,7 +428,7 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
     for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs}) b->alloc(S->nloc);
     S->partial.alloc((size_t)2 * S->nred); S->scal.alloc(1); S->counter.alloc(1);
     upload_values(*S, vals);
-    build_binv(*S, vals);
+    if (S->pc == 1) build_amg(*S, vals); else build_binv(*S, vals);
     CUDA_CHECK(cudaStreamSynchronize(S->stream));
     if (!fb_ok()) { delete S; return; }
     g_solvers[*id] = S;
@@ -395,7 +444,13 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     const int n = S.n, nb = S.nblocks, nr = S.nred;
     CUDA_CHECK(cudaEventRecord(S.ev0, st));
     if (*newvalues) {
-        if (S.reuse) { upload_values(S, vals); if (*newvalues == 2) build_binv(S, vals); }
+        if (S.reuse) {
+            upload_values(S, vals);
+            if (*newvalues == 2) {                                   // the captured graph holds the old preconditioner's buffers
+                if (S.graph) { CUDA_CHECK(cudaStreamSynchronize(st)); cudaGraphExecDestroy(S.graph); S.graph = nullptr; }
+                if (S.pc == 1) build_amg(S, vals); else build_binv(S, vals);
+            }
+        }
         else fprintf(stderr, "ERROR: matrix data is static\n");          // psolve.c:203
     }
     CUDA_CHECK(cudaMemcpyAsync(S.rhs.p, rhs, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
@@ -410,7 +465,16 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     { ProfScope ps_("k_init_res", st); k_init_res<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
                                    S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
     REDUCE(SC_INIT);
-    { ProfScope ps_("k_pc", st); k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
+    const bool amg = S.pc == 1;
+    const int* donep = &S.scal.p->done;
+    // multigrid: entry kernel (vector update + b0, x0) then the V-cycle; a one-level hierarchy is plain Jacobi written straight to `out`
+#define AMG_APPLY(MODE, name, out) do { \
+        AmgDevLevel& L0 = S.amg.L[0]; \
+        { ProfScope ps_(name, st); k_amg_enter<MODE><<<nb, SBS, 0, st>>>(n, S.d_scale.p, L0.dinv.p, S.amg.omega, S.v.p, S.r.p, S.p.p, L0.b.p, \
+                                                   S.amg.levels() > 1 ? L0.x.p : (out), S.scal.p); LAUNCH_CHECK(); } \
+        S.amg.cycle(out, donep, st); } while (0)
+    if (amg) AMG_APPLY(0, "k_amg_enter", S.pt.p);
+    else { ProfScope ps_("k_pc", st); k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
     int done = 0, launched = 0;
     const int poll = 8;
     if (!S.h_scal) CUDA_CHECK(cudaMallocHost(&S.h_scal, sizeof(SolverScal)));
@@ -419,13 +483,15 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
         if (multi) halo_exchange_flat(S.halo, S.pt.p, st);                       // parms_MatVec: interface exchange of the SpMV input
         { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
         REDUCE(SC_ALPHA);
-        { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
+        if (amg) AMG_APPLY(1, "k_amg_enter", S.st.p);
+        else { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
         if (multi) halo_exchange_flat(S.halo, S.st.p, st);
         { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
         REDUCE(SC_SIGMA);
         { ProfScope ps_("k_x_update", st); k_x_update<<<nr, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
         REDUCE(SC_XUPD);
-        { ProfScope ps_("k_p_update_pc", st); k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
+        if (amg) AMG_APPLY(2, "k_amg_enter", S.pt.p);
+        else { ProfScope ps_("k_p_update_pc", st); k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
     };
     // The iteration is launch-bound on small partitions (17 launches incl. NCCL per iteration on several ranks), so
     // `poll` iterations are captured into a CUDA graph once and replayed; converged iterations inside a replay are
@@ -450,6 +516,7 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
         done = hs->done;
     }
 #undef REDUCE
+#undef AMG_APPLY
     if (fb_ok()) {
         S.last_its = hs->its; S.last_res = sqrt(hs->omega);
         if (hs->its >= S.maxits && hs->omega > h.tol2) printf("ERROR: no convergence\n");   // bicgstab_ras.c:237-238
@@ -472,6 +539,7 @@ void psolver_final(void) {
         if (S->stream) cudaStreamSynchronize(S->stream);
         for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs, &S->d_vals, &S->d_sval, &S->d_scale, &S->d_binv, &S->partial}) b->release();
         S->halo.release();
+        S->amg.release();
         S->d_rp.release(); S->d_ci.release(); S->d_sptr.release(); S->d_scol.release(); S->scal.release(); S->counter.release();
         if (S->ev0) cudaEventDestroy(S->ev0);
         if (S->ev1) cudaEventDestroy(S->ev1);

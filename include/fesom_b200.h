@@ -22,7 +22,9 @@ extern "C" {
 /* ---------------------------------------------------------------------------------------------------
  * SSH solve: symbol-for-symbol replacement of src/psolve.c (psolver_init :16, psolve :152, psolver_final :117).
  * stype/pctype/pcilutype/ilulevel/fillin/droptol/restart are accepted and ignored: the Krylov method is
- * right-preconditioned BiCGStab (lib/parms/src/bicgstab_ras.c:49-259) with a block-Jacobi preconditioner.
+ * right-preconditioned BiCGStab (lib/parms/src/bicgstab_ras.c:49-259); the preconditioner (RAS + ILU(k) in the
+ * reference, lib/parms/src/parms_pc_ras.c:56-120) is block-Jacobi or an aggregation-multigrid V-cycle, see
+ * fb200_psolver_set_pc.
  *   part  : npes+1 row offsets of the PE-contiguous numbering (0-based)
  *   rptr  : N_own+1 CSR row pointers (0-based)         cols : nnz global PE-contiguous column ids (0-based)
  *   vals  : nnz matrix values                          reuse: 1 = values will be replaced by later psolve calls
@@ -40,6 +42,23 @@ void psolver_final(void);
 void fb200_psolve_info(int* id, int* its, double* resnorm);
 /* block size of the block-Jacobi preconditioner for solvers created afterwards (1 = point Jacobi) */
 void fb200_psolver_set_block(int* block);
+/* preconditioner of solvers created afterwards: 0 = block-Jacobi, 1 = aggregation multigrid (one V(1,1) cycle with
+ * damped-Jacobi smoothing on this rank's diagonal block; hierarchy built once at psolver_init like the reference's ILU
+ * factor, rebuilt by psolve(newvalues=2)).  Without a call the environment variable FB200_SSH_PC ("amg" | "bj") decides,
+ * else the library default. */
+void fb200_psolver_set_pc(int* kind);
+/* multigrid parameters: strength-of-connection threshold, smoother weight, number of levels, rows below which
+ * coarsening stops (defaults 0.08, 0.8, 4, 200) */
+void fb200_psolver_set_amg(double* theta, double* omega, int* max_levels, int* min_rows);
+/* rows and stored sliced-ELL entries of A_l, P_l, R_l of the hierarchy of solver id (rows = 0 past the last level) */
+void fb200_psolve_amg_info(int* id, int* level, int* rows, long long* a_entries, long long* p_entries, long long* r_entries);
+/* host-only access to the multigrid setup for CPU tests (no CUDA call): build a hierarchy from a 0-based CSR matrix,
+ * read level `level`'s matrix `which` (0 A, 1 P, 2 R) back as CSR, free it */
+int fb200_amg_host_build(int* n, int* rptr, int* cols, double* vals, double* theta, int* max_levels, int* min_rows);
+int fb200_amg_host_levels(int* handle);
+void fb200_amg_host_dims(int* handle, int* level, int* which, int* nrow, int* ncol, int* nnz);
+void fb200_amg_host_fetch(int* handle, int* level, int* which, int* rptr, int* cols, double* vals);
+void fb200_amg_host_free(int* handle);
 /* 1 (default): replay the BiCGStab iterations from a captured CUDA graph; 0: plain launches */
 void fb200_psolver_use_graph(int* on);
 

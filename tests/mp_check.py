@@ -45,6 +45,11 @@ def main():
     s = api.SSHSolver(lm)
     s.solve(new_values=1, sol=sol)
     its, res = s.info()
+    # the same solve with the multigrid preconditioner (each rank: V-cycle on its own diagonal block)
+    sol_mg = np.zeros_like(lm["d_eta"])
+    s2 = api.SSHSolver(lm, ident=2, pc="amg", amg=(0.08, 0.8, 4, 50))
+    s2.solve(new_values=1, sol=sol_mg)
+    its_mg, res_mg = s2.info()
     # oracle on the undivided mesh
     o = ob.TracerOracle(hm)
     for _ in range(steps):
@@ -58,8 +63,9 @@ def main():
     ok_halo = bool(np.array_equal(tr, hm["tr_arr"][:, alln]))
     err_t = float(np.abs(tr[:, :r.myDim_nod2D] - hm["tr_arr"][:, own]).max())
     err_s = float(util.rel_err(sol[:r.myDim_nod2D], x_ref[own]))
+    err_mg = float(util.rel_err(sol_mg[:r.myDim_nod2D], x_ref[own]))
     verdict = dict(rank=rank, own_bitexact=ok_own, halo_bitexact=ok_halo, tracer_maxabs=err_t, ssh_rel=err_s, its=its, its_ref=its_ref,
-                   res=res, launches=int(api.lib().fb200_kernel_launches()))
+                   res=res, ssh_rel_mg=err_mg, its_mg=its_mg, res_mg=res_mg, launches=int(api.lib().fb200_kernel_launches()))
     allv = [None] * world
     dist.all_gather_object(allv, verdict)
     eng.close()
@@ -68,7 +74,8 @@ def main():
     if rank == 0:
         for v in allv:
             print("MPCHECK", v)
-        good = all(v["own_bitexact"] and v["halo_bitexact"] and v["ssh_rel"] < 1e-6 and v["res"] < 1e-10 for v in allv)
+        good = all(v["own_bitexact"] and v["halo_bitexact"] and v["ssh_rel"] < 1e-6 and v["res"] < 1e-10
+                   and v["ssh_rel_mg"] < 1e-6 and v["res_mg"] < 1e-10 for v in allv)
         print("MPCHECK_RESULT", "PASS" if good else "FAIL")
     dist.destroy_process_group()
 

@@ -63,3 +63,51 @@ def test_value_refresh_and_warm_start():
     x2, _, _, _ = ob.ssh_solve(rp, ci, vals2, b, np.zeros_like(b), pc_kind=1, block=1)
     assert scaled_residual(rp, ci, vals2, sol[:b.size], b) < 2e-10
     assert util.rel_err(sol[:b.size], x2) < 1e-6
+
+
+@pytest.mark.parametrize("name", ["pi", "soufflet", "band"])
+def test_psolve_multigrid_matches_reference_and_oracle(name):
+    """pc='amg': same Krylov loop, the preconditioner is one multigrid V-cycle (ssh_amg.cu).  The solution must meet the
+    reference's stopping test and agree with the oracle / golden pARMS solution to the solver tolerance; the iteration
+    count must be that of the numpy restatement of the cycle (tests/test_amg_host.py) up to summation-order effects."""
+    from fesom2_b200 import api
+    from oracle import binding as ob
+    from tests.test_amg_host import solve_with_hierarchy
+    hm, rp, ci, vals, b = system(name)
+    min_rows = 50                                              # small meshes: still exercise two or more levels
+    H, A, x_np, its_np, _ = solve_with_hierarchy(rp, ci, vals, b, min_rows=min_rows)
+    s = api.SSHSolver(hm, ident=11, pc="amg", amg=(0.08, 0.8, 4, min_rows))
+    lev = s.amg_levels()
+    assert [l[0] for l in lev] == [h["A"].shape[0] for h in H] and len(lev) >= 2
+    sol = np.zeros_like(hm["d_eta"])
+    s.solve(new_values=0, sol=sol)
+    its, res = s.info()
+    n = b.size
+    assert res < 1e-10 and scaled_residual(rp, ci, vals, sol[:n], b) < 2e-10
+    x_ref, its_bj, _, _ = ob.ssh_solve(rp, ci, vals, b, np.zeros_like(b), pc_kind=1, block=1)
+    assert util.rel_err(sol[:n], x_ref) < 1e-6 and util.rel_err(sol[:n], x_np) < 1e-6
+    assert abs(its - its_np) <= 2 and its < its_bj
+    if name != "band":
+        g = np.load(os.path.join(util.GOLD, "ssh_%s.npz" % name))
+        assert util.rel_err(sol[:n], g["x_ref"]) < 1e-6
+    # value refresh keeps the hierarchy (psolve.c:200); new=2 rebuilds it; warm start converges at once
+    hm["dhe"][:] = 0.05 * np.sin(np.arange(hm["dhe"].size))
+    hm.stiff_mat_update()
+    vals2 = hm["ssh_values"].copy()
+    for new in (1, 2):
+        sol[:] = 0.0
+        s.solve(new_values=new, sol=sol)
+        assert scaled_residual(rp, ci, vals2, sol[:n], b) < 2e-10
+    s.solve(new_values=0, sol=sol)
+    assert s.info()[0] <= 1
+
+
+def test_psolve_multigrid_single_level_is_jacobi():
+    """a hierarchy that cannot coarsen (max_levels=1) degenerates to damped point Jacobi: same iterates as block=1 up to the damping"""
+    from fesom2_b200 import api
+    hm, rp, ci, vals, b = system("pi")
+    s = api.SSHSolver(hm, ident=12, pc="amg", amg=(0.08, 0.8, 1, 50))
+    assert len(s.amg_levels()) == 1
+    sol = np.zeros_like(hm["d_eta"])
+    s.solve(new_values=0, sol=sol)
+    assert s.info()[1] < 1e-10 and scaled_residual(rp, ci, vals, sol[:b.size], b) < 2e-10
