@@ -10,8 +10,8 @@ diffusion, implicit vertical diffusion, salinity clamp).  Prints ONE JSON line (
   value      tracer node-level updates/s = wet (node, layer) pairs x num_tracers x K / device time of the K tracer
              steps, state resident in HBM (CUDA events on the launching stream, max over ranks)
   ssh        SSH solve ms/step (device time of psolve, incl. row scaling), iterations, final scaled residual
-  e2e        the same two calls through the C ABI with HOST (pinned) buffers: fb200_push_step_state +
-             fb200_solve_tracers_ale + psolve, host<->device copies inside the timed region
+  e2e        the same two calls through the C ABI with HOST (pinned) buffers: fb200_push_state_early/_late +
+             psolve + fb200_solve_tracers_ale_resident, host<->device copies inside the timed region
   roofline   dominant kernel: algorithmic bytes per launch / measured launch duration vs MEASURED_PEAKS.json
   cpu_baseline / --impl reference : the oracle (C restatement, tracer step) and the reference's own
              psolve.c + pARMS (oracle/_ref, SSH solve) on the host cores, on a bounded sample of the workload
@@ -319,18 +319,21 @@ def run_b200(args):
     if not args.no_e2e:
         host_arrays = [hm.arr(nm) for nm in STATE] + [hm.arr("tr_arr"), hm.arr("tr_arr_old")]
         pinned = pin(host_arrays) + ssh_pinned
-        h2d = sum(hm.arr(nm).nbytes for nm in STATE) + hm.arr("tr_arr").nbytes + hm.arr("tr_arr_old").nbytes \
-            + hm.arr("ssh_values").nbytes + 2 * 8 * n_own
-        d2h = hm.arr("tr_arr").nbytes + hm.arr("tr_arr_old").nbytes + 8 * n_own
-        tr_h, tro_h = hm.arr("tr_arr").copy(), hm.arr("tr_arr_old").copy()
-        pinned += pin([tr_h, tro_h])
+        # what crosses PCIe every step: the state the host produces (all of STATE but the old thickness hnode, which is the
+        # resident hnode_new of the previous step, and Ki, static without Fer_GM/Redi), the SSH system and guess; back: the
+        # new tr_arr and the SSH solution.  The tracers are time-stepped on the device (fb200_solve_tracers_ale_resident).
+        h2d = sum(hm.arr(nm).nbytes for nm in STATE if nm not in ("hnode", "Ki")) + hm.arr("ssh_values").nbytes + 2 * 8 * n_own
+        d2h = hm.arr("tr_arr").nbytes + 8 * n_own
+        tr_h = hm.arr("tr_arr").copy()
+        pinned += pin([tr_h])
+        eng.push_tracers()                                          # once: initial condition
 
         def e2e_step():
             sol[:] = 0.0
-            eng.push_state_early()                                  # H2D old thickness, level depths, mixing, fluxes: enqueued only,
+            eng.push_state_early(hnode_resident=True, ki_resident=True)   # H2D level depths, mixing, fluxes: enqueued only,
             solver.solve(new_values=1, sol=sol)                    #   overlaps psolve (H2D values, rhs, guess; D2H solution)
             eng.push_state_late()                                   # H2D what the SSH solution yields: UV, Wvel, hnode_new, helem
-            eng.solve_tracers_ale(tr_h, tro_h)                      # H2D tracers, step, D2H tracers (copies of one tracer overlap the kernels of the other)
+            eng.solve_tracers_ale_resident(tr_h)                    # step on the resident tracers, D2H tr_arr (copy of one tracer overlaps the kernels of the next)
 
         e2e_step()
         ksteps = max(1, min(args.steps, 5))

@@ -21,7 +21,7 @@ EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb20
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
            "fb200_push_tracers",
-           "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_debug_fetch",
+           "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
            "fb200_selftest_div", "fb200_init_halo", "fb200_comm_unique_id", "fb200_comm_init", "fb200_comm_finalize", "fb200_psolver_use_graph",
@@ -176,10 +176,14 @@ class TracerEngine:
                                      _p(a("relax_salt")), _p(a("real_salt_flux")), _p(a("sw_3d")))
         _check(self.L)
 
-    def push_state_early(self):
-        """the half of the step state that exists before solve_ssh_ale; returns at once, the copies overlap psolve"""
+    def push_state_early(self, hnode_resident=False, ki_resident=False):
+        """the half of the step state that exists before solve_ssh_ale; returns at once, the copies overlap psolve.
+        hnode_resident: pass NULL for hnode (the library's hnode_new of the previous step is the old thickness);
+        ki_resident: pass NULL for Ki (unchanged since the last push)"""
         a = self.hm.arr
-        self.L.fb200_push_state_early(_p(a("hnode")), _p(a("Z_3d_n")), _p(a("zbar_3d_n")), _p(a("Kv")), _p(a("Ki")),
+        null = C.c_void_p(None)
+        self.L.fb200_push_state_early(null if hnode_resident else _p(a("hnode")), _p(a("Z_3d_n")), _p(a("zbar_3d_n")), _p(a("Kv")),
+                                      null if ki_resident else _p(a("Ki")),
                                       _p(a("slope_tapered")), _p(a("heat_flux")), _p(a("water_flux")), _p(a("virtual_salt")),
                                       _p(a("relax_salt")), _p(a("real_salt_flux")), _p(a("sw_3d")))
         _check(self.L)
@@ -211,6 +215,12 @@ class TracerEngine:
         tr = self.hm.arr("tr_arr") if tr is None else tr
         tro = self.hm.arr("tr_arr_old") if tro is None else tro
         self.L.fb200_solve_tracers_ale(_p(tr), _p(tro))
+        _check(self.L)
+
+    def solve_tracers_ale_resident(self, tr_out=None):
+        """one step on the device-resident tracers; only tr_arr comes back to the host"""
+        tr_out = self.hm.arr("tr_arr") if tr_out is None else tr_out
+        self.L.fb200_solve_tracers_ale_resident(_p(tr_out))
         _check(self.L)
 
     def debug(self, name):

@@ -105,11 +105,15 @@ static void push_early_on(TracerCtx& c, cudaStream_t s, double* hnode, double* Z
                           double* real_salt_flux, double* sw_3d) {
     cudaStream_t keep = c.stream; c.stream = s;
     const int L = c.nl - 1, nl = c.nl, N = c.N;
-    ctx_push_node_field(c, hnode, L, N, c.hnode.p);
+    // NULL = "unchanged on the host side since the library last saw it": hnode then becomes the resident hnode_new of the
+    // previous step (update_thickness_ale assigns exactly that, oce_ale.F90:924,936,967), Ki keeps its resident copy (it is
+    // set once in oce_setup_step.F90:330 and only rewritten per step under Fer_GM / Redi, oce_fer_gm.F90:243-333)
+    if (hnode) ctx_push_node_field(c, hnode, L, N, c.hnode.p);
+    else CUDA_CHECK(cudaMemcpyAsync(c.hnode.p, c.hnode_new.p, c.hnode.n * sizeof(double), cudaMemcpyDeviceToDevice, s));
     ctx_push_node_field(c, Z_3d_n, L, N, c.Z3.p);
     ctx_push_node_field(c, zbar_3d_n, nl, N, c.zbar3.p);
     ctx_push_node_field(c, Kv, nl, N, c.Kv.p);
-    ctx_push_node_field(c, Ki, L, N, c.Ki.p);
+    if (Ki) ctx_push_node_field(c, Ki, L, N, c.Ki.p);
     if (c.opt.Redi) {
         ctx_push_node_field(c, slope_tapered, L, N, c.sl1.p, 3, 0);
         ctx_push_node_field(c, slope_tapered, L, N, c.sl2.p, 3, 1);
@@ -235,6 +239,34 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
         ctx_pull_node_field(c, c.Told.p + nf * tr, L, c.N, tr_arr_old + rf * tr, 1, 0, false);
     }
     c.stream = comp;
+    tracer_step_end(c);
+    CUDA_CHECK(cudaStreamSynchronize(copy));
+}
+
+// Time stepping with device-resident tracers: the step consumes the tracers the previous step left in HBM (first step:
+// fb200_push_tracers) and the host receives tr_arr only — tr_arr_old is read by nothing but init_tracers_AB
+// (oce_tracer_mod.F90:64), i.e. by this library.  The copy of tracer k overlaps the kernels of tracer k+1.
+void fb200_solve_tracers_ale_resident(double* tr_arr_out) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(34, "fb200_solve_tracers_ale_resident before fb200_init_commit"); return; }
+    if (c.ntr > MAX_TR_EVENTS) { fb_set_error(38, "fb200_solve_tracers_ale_resident: too many tracers"); return; }
+    copy_stream();
+    for (; g_tr_events < c.ntr; g_tr_events++) {
+        CUDA_CHECK(cudaEventCreateWithFlags(&g_ev_push[g_tr_events], cudaEventDisableTiming));
+        CUDA_CHECK(cudaEventCreateWithFlags(&g_ev_done[g_tr_events], cudaEventDisableTiming));
+    }
+    if (!tracer_step_begin(c)) return;
+    cudaStream_t comp = c.stream, copy = copy_stream();
+    const int L = c.nl - 1;
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
+    for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
+        tracer_step_tracer(c, tr);
+        CUDA_CHECK(cudaEventRecord(g_ev_done[tr], comp));
+        c.stream = copy;
+        CUDA_CHECK(cudaStreamWaitEvent(copy, g_ev_done[tr], 0));
+        ctx_pull_node_field(c, c.T.p + nf * tr, L, c.N, tr_arr_out + rf * tr, 1, 0, false);
+        c.stream = comp;
+    }
     tracer_step_end(c);
     CUDA_CHECK(cudaStreamSynchronize(copy));
 }

@@ -110,6 +110,10 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
  * step, surface fluxes); late = what the SSH solution yields (update_vel -> UV, compute_hbar_ale / vert_vel_ale ->
  * Wvel*, hnode_new, helem).  fb200_push_state_early only enqueues its copies and returns, so they overlap psolve; the
  * host must leave those arrays untouched until fb200_push_state_late has returned (it waits for both halves). */
+/* Two of the early arrays may be passed as NULL (Fortran: c_null_ptr through a type(c_ptr), value dummy) = "the host has
+ * not changed it since the library last saw it": hnode = NULL makes the resident hnode_new of the previous step the old
+ * thickness (what update_thickness_ale assigns, src/oce_ale.F90:924,936,967); Ki = NULL keeps the resident copy (Ki is set
+ * once in src/oce_setup_step.F90:330 and rewritten per step only under Fer_GM/Redi, src/oce_fer_gm.F90:243-333). */
 void fb200_push_state_early(double* hnode, double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki, double* slope_tapered,
                             double* heat_flux, double* water_flux, double* virtual_salt, double* relax_salt,
                             double* real_salt_flux, double* sw_3d);
@@ -119,6 +123,10 @@ void fb200_push_tracers(double* tr_arr, double* tr_arr_old);
 void fb200_solve_tracers(void);                         /* all tracers, device resident */
 void fb200_pull_tracers(double* tr_arr, double* tr_arr_old);
 void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old);   /* push + solve + pull */
+/* time stepping with device-resident tracers: the step starts from the tracers the previous step left in HBM (first step:
+ * fb200_push_tracers) and returns tr_arr to the host; tr_arr_old stays on the device (its only reader is
+ * init_tracers_AB, src/oce_tracer_mod.F90:64).  The copy of tracer k overlaps the kernels of tracer k+1. */
+void fb200_solve_tracers_ale_resident(double* tr_arr_out);
 /* debugging / parity: copy an internal (level, node|edge|elem) work field back in the reference layout.
  * name: "fct_LO","adf_h","adf_v","fct_plus","fct_minus","tr_xy_x","tr_xy_y","ttfAB","tstar" ; returns via status */
 void fb200_debug_fetch(const char* name, double* out);

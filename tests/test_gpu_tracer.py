@@ -163,3 +163,35 @@ def test_div_by_matches_ieee_division():
     it must round exactly like '/' (bit-exact parity with the reference's divisions depends on it)"""
     from fesom2_b200 import api
     assert api.selftest_div(1 << 24) == 0
+
+
+@pytest.mark.parametrize("name", ["pi", "band"])
+def test_resident_time_stepping_matches_oracle(name):
+    """fb200_solve_tracers_ale_resident: three steps on device-resident tracers (only tr_arr comes back) with the early
+    state pushed through the NULL conventions (Ki kept resident; hnode kept = the host's unchanged hnode) == three oracle
+    steps, and == the host-array path step by step."""
+    from fesom2_b200 import api
+    from oracle import binding as ob
+    hm = util.build_model(name)
+    eng = api.TracerEngine(hm)
+    eng.push_step_state()
+    eng.push_tracers()
+    out = np.zeros_like(hm["tr_arr"])
+    o = ob.TracerOracle(hm)
+    wet = util.wet_mask(hm)
+    for step in range(3):
+        eng.push_state_early(ki_resident=True)
+        eng.push_state_late()
+        eng.solve_tracers_ale_resident(out)
+        o.step()
+        for k in range(out.shape[0]):
+            assert util.rel_err(out[k][wet], hm["tr_arr"][k][wet]) < TOL, "step %d tracer %d" % (step, k)
+    # hnode = NULL: the old thickness becomes the resident hnode_new.  Make the host agree (hnode := hnode_new, what
+    # update_thickness_ale does) and compare one more step
+    hm["hnode"][:] = hm["hnode_new"]
+    eng.push_state_early(hnode_resident=True, ki_resident=True)
+    eng.push_state_late()
+    eng.solve_tracers_ale_resident(out)
+    ob.TracerOracle(hm).step()
+    for k in range(out.shape[0]):
+        assert util.rel_err(out[k][wet], hm["tr_arr"][k][wet]) < TOL
