@@ -288,10 +288,9 @@ class SSHSolver:
         if library is None:
             L.fb200_clear_status()
             L.fb200_psolver_set_block(_i(block))
-            if pc is not None:
-                L.fb200_psolver_set_pc(_i(self.PC[pc]))
-            if amg is not None:
-                L.fb200_psolver_set_amg(_d(amg[0]), _d(amg[1]), _i(amg[2]), _i(amg[3]))
+            L.fb200_psolver_set_pc(_i(-1 if pc is None else self.PC[pc]))       # the setters are sticky: always state both
+            amg = (0.08, 0.8, 4, 200) if amg is None else amg
+            L.fb200_psolver_set_amg(_d(amg[0]), _d(amg[1]), _i(amg[2]), _i(amg[3]))
         rp = hm.arr("ssh_rowptr")
         self._part = (hm.arr("part") - 1).astype(np.int32)                 # part-1
         self._rp = (rp - rp[0]).astype(np.int32)                            # rowptr(:)-rowptr(1)

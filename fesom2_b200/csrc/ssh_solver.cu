@@ -51,7 +51,7 @@ struct Solver {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 static std::map<int, Solver*> g_solvers;
-#define FB200_DEFAULT_PC 0
+#define FB200_DEFAULT_PC 1      // multigrid; block-Jacobi through fb200_psolver_set_pc(0) or FB200_SSH_PC=bj
 static int g_block = 1;
 static int g_pc = -1;             // -1: FB200_SSH_PC from the environment ("amg" | "bj"), else the default
 static AmgParams g_amg_prm;
@@ -312,9 +312,9 @@ void fb200_psolver_set_block(int* block) {
     g_block = b;
 }
 
-// preconditioner of solvers created afterwards: 0 block-Jacobi, 1 aggregation multigrid (V(1,1), damped Jacobi)
+// preconditioner of solvers created afterwards: 0 block-Jacobi, 1 aggregation multigrid (V(1,1), damped Jacobi), -1 = back to FB200_SSH_PC / the default
 void fb200_psolver_set_pc(int* kind) {
-    if (*kind != 0 && *kind != 1) { fb_set_error(46, "fb200_psolver_set_pc: 0 = block-Jacobi, 1 = multigrid"); return; }
+    if (*kind < -1 || *kind > 1) { fb_set_error(46, "fb200_psolver_set_pc: 0 = block-Jacobi, 1 = multigrid, -1 = FB200_SSH_PC / library default"); return; }
     g_pc = *kind;
 }
 // multigrid parameters (solvers created afterwards): strength threshold, smoother weight, levels, rows below which coarsening stops

@@ -42,10 +42,10 @@ void psolver_final(void);
 void fb200_psolve_info(int* id, int* its, double* resnorm);
 /* block size of the block-Jacobi preconditioner for solvers created afterwards (1 = point Jacobi) */
 void fb200_psolver_set_block(int* block);
-/* preconditioner of solvers created afterwards: 0 = block-Jacobi, 1 = aggregation multigrid (one V(1,1) cycle with
+/* preconditioner of solvers created afterwards: -1 = default, 0 = block-Jacobi, 1 = aggregation multigrid (one V(1,1) cycle with
  * damped-Jacobi smoothing on this rank's diagonal block; hierarchy built once at psolver_init like the reference's ILU
  * factor, rebuilt by psolve(newvalues=2)).  Without a call the environment variable FB200_SSH_PC ("amg" | "bj") decides,
- * else the library default. */
+ * else the library default (multigrid). */
 void fb200_psolver_set_pc(int* kind);
 /* multigrid parameters: strength-of-connection threshold, smoother weight, number of levels, rows below which
  * coarsening stops (defaults 0.08, 0.8, 4, 200) */

@@ -42,7 +42,7 @@ def main():
     eng.pull_tracers(tr, tro)
     # SSH solve on the partitioned system
     sol = np.zeros_like(lm["d_eta"])
-    s = api.SSHSolver(lm)
+    s = api.SSHSolver(lm, pc="bj")
     s.solve(new_values=1, sol=sol)
     its, res = s.info()
     # the same solve with the multigrid preconditioner (each rank: V-cycle on its own diagonal block)

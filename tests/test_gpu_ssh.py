@@ -22,7 +22,7 @@ def test_psolve_matches_oracle(name, block):
     from oracle import binding as ob
     hm, rp, ci, vals, b = system(name)
     x_ref, its_ref, res_ref, rc = ob.ssh_solve(rp, ci, vals, b, np.zeros_like(b), pc_kind=1, block=block)
-    s = api.SSHSolver(hm, ident=block, block=block)
+    s = api.SSHSolver(hm, ident=block, block=block, pc="bj")
     sol = np.zeros_like(hm["d_eta"])
     s.solve(new_values=0, sol=sol)
     its, res = s.info()
