@@ -26,6 +26,8 @@ def main():
     per = collections.OrderedDict()
     for r in rows[2:]:
         name = re.match(r"(?:void )?([A-Za-z_0-9]+)", r[ki]).group(1)      # template arguments dropped: k_lo<0, 1> -> k_lo
+        if name.startswith("k_amg_") and "Grid Size" in hdr:               # one kernel per multigrid level: keep the levels apart
+            name += "[grid %s]" % r[hdr.index("Grid Size")].replace(" ", "")
         d = per.setdefault(name, collections.defaultdict(list))
         for m, _ in METRICS:
             if m in hdr:
