@@ -9,6 +9,8 @@ hdr = rows[0]; ki = hdr.index("Kernel Name"); vi = hdr.index("Metric Value"); gi
 tot = collections.OrderedDict()
 for r in rows[1:]:
     name = re.match(r"(?:void )?([A-Za-z_0-9]+)", r[ki]).group(1)
+    if name.startswith("k_amg_") and not name.startswith("k_amg_enter"):      # one launch per multigrid level: keep the levels apart by grid size
+        name += "[%s]" % r[gi].split(",")[0].strip("( ")
     t = tot.setdefault(name, [0, 0.0, r[gi], r[bi]])
     t[0] += 1; t[1] += float(r[vi].replace(",", "")) * 1e-6
 alltime = sum(t[1] for t in tot.values())

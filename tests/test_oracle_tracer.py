@@ -89,3 +89,25 @@ def test_explicit_vertical_diffusion_runs():
     m1 = (tr[0] * hm["hnode_new"] * hm["areasvol"][:, :nl - 1])[wet].sum()
     assert np.isfinite(tr).all()
     assert abs(m0 - m1) / abs(m0) < 1e-6
+
+
+@pytest.mark.parametrize("name", ["pi", "band"])
+def test_100_coupled_steps_conserve_mass_and_keep_extrema(name):
+    """BASELINE.json north_star: 'stated bounds on global tracer mass and extrema after 100 steps'.  100 steps of the
+    time loop (compute_hbar_ale -> vert_vel_ale -> solve_tracers_ale -> update_thickness_ale, zstar, prescribed
+    velocities, no surface flux): tracer mass sum(T h areasvol) is conserved to 1e-13 relative, and FCT advection +
+    diffusion create no new extrema (every value stays inside the initial [min, max])."""
+    hm = util.build_model(name, which_ale="zstar", umax=0.02)
+    wet = util.wet_mask(hm)
+    tr = hm["tr_arr"]
+    m0 = [util.tracer_mass(hm, k) for k in range(2)]
+    ext0 = [(tr[k][wet].min(), tr[k][wet].max()) for k in range(2)]
+    o = ob.TracerOracle(hm, clamp_salt=False)
+    for s in range(100):
+        util.advance_ale_state(hm, first=(s == 0))
+        o.step()
+        hm.update_thickness()
+    assert hm["hnode"][wet].min() > 0.0
+    for k in range(2):
+        assert abs(util.tracer_mass(hm, k) - m0[k]) <= 1e-13 * abs(m0[k])
+        assert tr[k][wet].min() >= ext0[k][0] - 1e-12 and tr[k][wet].max() <= ext0[k][1] + 1e-12

@@ -62,3 +62,20 @@ def rel_err(a, b):
     d = np.abs(np.asarray(a) - np.asarray(b)).max()
     s = np.abs(np.asarray(b)).max()
     return d / s if s > 0 else d
+
+
+def advance_ale_state(hm, first):
+    """the host side of one time step around solve_tracers_ale with a prescribed velocity field (oce_timestep_ale,
+    src/oce_ale.F90:2694-2760): compute_ssh_rhs_ale -> compute_hbar_ale -> vert_vel_ale before the tracer step (skipped
+    on the first step: fill_state has already run them), update_thickness_ale after it (the caller runs hm.update_thickness())"""
+    if not first:
+        hm.compute_ssh_rhs()
+        hm.compute_hbar()
+        hm.vert_vel()
+
+
+def tracer_mass(hm, k):
+    """sum_n sum_nz T h areasvol over wet cells with the current thickness (integrate_nod_3D, gen_support.F90:288-311)"""
+    nl = hm.ipar("nl")
+    wet = wet_mask(hm)
+    return float((hm["tr_arr"][k] * hm["hnode"] * hm["areasvol"][:, :nl - 1])[wet].sum())
