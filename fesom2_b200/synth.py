@@ -81,12 +81,20 @@ def fill_state(hm, seed=12345, umax=0.5, hbar_amp=0.3, noise=0.1, water_flux=0.0
 
 # ---------------------------------------------------------------------------------------------------
 def lonlat_band_mesh(nlon, nlat, lat_max=80.0, nl=24, depth_max=5000.0, seed=20261104, land_frac=0.12,
-                     shuffle=False):
+                     shuffle=False, refine_north=0.0):
     """Triangulated lon/lat band (cyclic in longitude) with elliptical land patches and ragged bathymetry.
-    Returns the raw arrays `HostModel.set_global_mesh` takes.  Structured-like but stored fully unstructured."""
+    Returns the raw arrays `HostModel.set_global_mesh` takes.  Structured-like but stored fully unstructured.
+    refine_north = r > 1: multi-resolution variant (the stand-in for the Arctic-refined farc mesh of BASELINE.json
+    config 4, which is not in the repository): the meridional spacing shrinks by the factor r between 50 N and 65 N
+    and stays there up to lat_max.  shuffle: random node and element numbering (no locality at all)."""
     rng = np.random.default_rng(seed)
     lons = np.linspace(0.0, 360.0, nlon, endpoint=False)
     lats = np.linspace(-lat_max, lat_max, nlat)
+    if refine_north and refine_north > 1.0:
+        fine = np.linspace(-lat_max, lat_max, 20 * nlat)
+        dens = 1.0 + (refine_north - 1.0) * np.clip((fine - 50.0) / 15.0, 0.0, 1.0)      # rows per degree, relative
+        cdf = np.concatenate([[0.0], np.cumsum(0.5 * (dens[1:] + dens[:-1]) * np.diff(fine))])
+        lats = np.interp(np.linspace(0.0, cdf[-1], nlat), cdf, fine)
     LON, LAT = np.meshgrid(lons, lats, indexing="xy")          # (nlat, nlon)
     # land mask from a few ellipses
     land = np.zeros_like(LON, dtype=bool)

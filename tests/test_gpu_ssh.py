@@ -65,7 +65,7 @@ def test_value_refresh_and_warm_start():
     assert util.rel_err(sol[:b.size], x2) < 1e-6
 
 
-@pytest.mark.parametrize("name", ["pi", "soufflet", "band"])
+@pytest.mark.parametrize("name", ["pi", "soufflet", "band", "farclike", "core2like"])
 def test_psolve_multigrid_matches_reference_and_oracle(name):
     """pc='amg': same Krylov loop, the preconditioner is one multigrid V-cycle (ssh_amg.cu).  The solution must meet the
     reference's stopping test and agree with the oracle / golden pARMS solution to the solver tolerance; the iteration
@@ -87,7 +87,7 @@ def test_psolve_multigrid_matches_reference_and_oracle(name):
     x_ref, its_bj, _, _ = ob.ssh_solve(rp, ci, vals, b, np.zeros_like(b), pc_kind=1, block=1)
     assert util.rel_err(sol[:n], x_ref) < 1e-6 and util.rel_err(sol[:n], x_np) < 1e-6
     assert abs(its - its_np) <= 2 and its < its_bj
-    if name != "band":
+    if name in ("pi", "soufflet"):
         g = np.load(os.path.join(util.GOLD, "ssh_%s.npz" % name))
         assert util.rel_err(sol[:n], g["x_ref"]) < 1e-6
     # value refresh keeps the hierarchy (psolve.c:200); new=2 rebuilds it; warm start converges at once

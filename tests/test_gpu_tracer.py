@@ -47,6 +47,9 @@ def run_pair(name, opts=None, model_kw=None, steps=1):
     ("soufflet", {"w_split": True, "w_max_cfl": 0.2}, {"tra_adv_lim": "NONE", "tra_adv_hor": "MUSCL"}),
     ("band", {"water_flux": 1e-7, "heat_flux": 50.0}, {}),
     ("band", {"num_tracers": 3}, {"tracer_ids": (0, 1, 301)}),
+    ("farclike", {}, {}),                         # BASELINE.json config 4 stand-in: multi-resolution mesh
+    ("farclike", {"shuffle": True}, {}),          # the same mesh with a random node/element numbering (no locality)
+    ("core2like", {}, {}),                        # BASELINE.json config 3 stand-in: 127 k surface nodes x 47 layers
 ])
 def test_tracer_step_matches_oracle(name, model_kw, opts):
     hm, eng, o, g_tr, g_tro = run_pair(name, opts, model_kw)

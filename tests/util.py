@@ -17,8 +17,9 @@ def mesh_fixture(name):
 
 def build_model(name="pi", dt=None, which_ale=None, w_split=False, w_max_cfl=1.0, num_tracers=2, seed=12345,
                 water_flux=0.0, heat_flux=0.0, umax=0.5, **mesh_kw):
-    """name: 'pi' (test_pi: rotated global mesh, zstar), 'soufflet' (test_souf: cyclic channel, linfs), or
-    'band' (synthetic lon/lat band with land and ragged bathymetry)"""
+    """name: 'pi' (test_pi: rotated global mesh, zstar), 'soufflet' (test_souf: cyclic channel, linfs),
+    'band' (synthetic lon/lat band with land and ragged bathymetry), 'farclike' (band refined 3x towards the north: the
+    stand-in for BASELINE.json's farc mesh) or 'core2like' (band of CORE2's size: ~127 k surface nodes x 47 layers)"""
     hm = HostModel()
     if name == "pi":
         m = mesh_fixture("pi")
@@ -34,8 +35,12 @@ def build_model(name="pi", dt=None, which_ale=None, w_split=False, w_max_cfl=1.0
         dt = 1200.0 if dt is None else dt               # setups/test_souf: step_per_day 72
         which_ale = which_ale or "linfs"
         pc = False
-    elif name == "band":
+    elif name in ("band", "farclike", "core2like"):
         kw = dict(nlon=72, nlat=40, nl=24)
+        if name == "farclike":           # BASELINE.json config 4 stand-in: multi-resolution (3x finer north of 65 N)
+            kw = dict(nlon=120, nlat=90, nl=24, refine_north=3.0)
+        if name == "core2like":          # BASELINE.json config 3 stand-in: ~127 k surface nodes, 47 layers
+            kw = dict(nlon=528, nlat=264, nl=48)
         kw.update(mesh_kw)
         m = synth.lonlat_band_mesh(**kw)
         hm.set_global_mesh(m["lon"], m["lat"], m["tri"], m["zbar"], m["depth"], force_rotation=False, cyclic_deg=360.0)
