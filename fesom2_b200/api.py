@@ -20,7 +20,7 @@ LIM = {"FCT": 0, "NONE": 1}
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
-           "fb200_push_tracers",
+           "fb200_push_tracers", "fb200_set_clim", "fb200_tracer_extrema",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
@@ -193,6 +193,19 @@ class TracerEngine:
         a = self.hm.arr
         self.L.fb200_push_state_late(_p(a("UV")), _p(a("Wvel")), _p(a("Wvel_e")), _p(a("Wvel_i")), _p(a("hnode_new")), _p(a("helem")))
         _check(self.L)
+
+    def set_clim(self, clim_relax, relax2clim, Tclim, Sclim):
+        """relax_to_clim inside the step: relax2clim (N), Tclim/Sclim (N, nl-1) numpy arrays, pushed once"""
+        self._clim = (np.ascontiguousarray(relax2clim), np.ascontiguousarray(Tclim), np.ascontiguousarray(Sclim))
+        self.L.fb200_set_clim(_d(clim_relax), _p(self._clim[0]), _p(self._clim[1]), _p(self._clim[2]))
+        _check(self.L)
+
+    def extrema(self, tr_num):
+        """(min, max) of the resident tracer tr_num (1-based) over own wet cells"""
+        lo, hi = C.c_double(), C.c_double()
+        self.L.fb200_tracer_extrema(_i(tr_num), C.byref(lo), C.byref(hi))
+        _check(self.L)
+        return lo.value, hi.value
 
     def push_tracers(self, tr=None, tro=None):
         tr = self.hm.arr("tr_arr") if tr is None else tr

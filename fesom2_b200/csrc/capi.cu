@@ -169,6 +169,23 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
     if (fb_ok()) fb200_push_state_late(UV, Wvel, Wvel_e, Wvel_i, hnode_new, helem);
 }
 
+// relax_to_clim (oce_tracer_mod.F90:87-119): the climatology is static (set with the initial conditions), so it is pushed
+// once; *clim_relax <= 1e-8 switches the relaxation off like the reference's test does
+void fb200_set_clim(double* clim_relax, double* relax2clim, double* Tclim, double* Sclim) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(33, "fb200_set_clim before fb200_init_commit"); return; }
+    c.opt.clim_relax = *clim_relax;
+    if (!(c.opt.clim_relax > 1.0e-8)) return;
+    fb_copy_sync();
+    c.stream = fb_stream();
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
+    if (!c.relax2clim.p) { c.relax2clim.alloc(c.N); c.Tclim.alloc(nf); c.Sclim.alloc(nf); }
+    CUDA_CHECK(cudaMemcpyAsync(c.relax2clim.p, relax2clim, (size_t)c.N * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    ctx_push_node_field(c, Tclim, c.nl - 1, c.N, c.Tclim.p);
+    ctx_push_node_field(c, Sclim, c.nl - 1, c.N, c.Sclim.p);
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+}
+
 void fb200_push_tracers(double* tr_arr, double* tr_arr_old) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(34, "fb200_push_tracers before fb200_init_commit"); return; }
@@ -270,6 +287,10 @@ void fb200_solve_tracers_ale_resident(double* tr_arr_out) {
     tracer_step_end(c);
     CUDA_CHECK(cudaStreamSynchronize(copy));
 }
+
+// extrema of the resident tracer *tr_num (1-based) over this partition's own wet cells (the host combines the ranks with
+// its own MPI_Allreduce, as write_step_info.F90 does)
+void fb200_tracer_extrema(int* tr_num, double* tmin, double* tmax) { tracer_extrema(tctx(), *tr_num - 1, tmin, tmax); }
 
 void fb200_debug_fetch(const char* name, double* out) {
     TracerCtx& c = tctx();

@@ -7,6 +7,7 @@
 // (compiled with --fmad=false) — see the file:line notes at each kernel.
 #include "common.cuh"
 #include "comm.cuh"
+#include <algorithm>
 
 #define LB(n) __launch_bounds__(n)
 
@@ -848,6 +849,38 @@ __global__ void LB(128) k_copy_cols(KP p, double* __restrict__ dst, const double
     for (int nz = (lv & 255); nz <= (int)((lv >> 8) & 255) - 1; nz++) AT(dst, b, nz) = AT(src, b, nz);
 }
 
+// relax_to_clim, oce_tracer_mod.F90:87-119 — own nodes, wet levels: T += relax2clim(n) * dt * (clim - T)
+__global__ void LB(128) k_relax_clim(KP p, double* __restrict__ T, const double* __restrict__ clim, const double* __restrict__ relax2clim) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.myN) return;
+    const int b = tbase(n, p.nlp);
+    const unsigned lv = p.n_lev[n];
+    const double r = relax2clim[n];
+    for (int nz = (lv & 255); nz <= (int)((lv >> 8) & 255) - 1; nz++) {
+        const double t = AT(T, b, nz);
+        AT(T, b, nz) = t + r * p.dt * (AT(clim, b, nz) - t);
+    }
+}
+
+// global extrema of one tracer over own wet cells: the quantity check_blowup (write_step_info.F90:220-504) and the
+// min/max lines of write_step_info test on the host; with device-resident tracers only two scalars cross PCIe.
+// One partial (min, max) per block; the host combines the <= 1184 partials (min/max are order-independent).
+__global__ void LB(256) k_extrema(KP p, const double* __restrict__ T, double2* __restrict__ partial) {
+    double lo = 1.0e300, hi = -1.0e300;
+    for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < p.myN; n += gridDim.x * blockDim.x) {
+        const int b = tbase(n, p.nlp);
+        const unsigned lv = p.n_lev[n];
+        for (int nz = (lv & 255); nz <= (int)((lv >> 8) & 255) - 1; nz++) { const double t = AT(T, b, nz); lo = dmin(lo, t); hi = dmax(hi, t); }
+    }
+    __shared__ double slo[8], shi[8];
+    for (int o = 16; o > 0; o >>= 1) { lo = dmin(lo, __shfl_down_sync(0xffffffffu, lo, o)); hi = dmax(hi, __shfl_down_sync(0xffffffffu, hi, o)); }
+    if ((threadIdx.x & 31) == 0) { slo[threadIdx.x >> 5] = lo; shi[threadIdx.x >> 5] = hi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; w++) { lo = dmin(lo, slo[w]); hi = dmax(hi, shi[w]); }
+        partial[blockIdx.x] = make_double2(lo, hi);
+    }
+}
 // salinity clamp, oce_ale_tracer.F90:176-198 — all local nodes
 __global__ void LB(128) k_clamp_salt(KP p, double* __restrict__ S) {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
@@ -881,6 +914,25 @@ static KP make_kp(TracerCtx& c, int tr) {
     p.txy = c.txy.p; p.fpm = c.fpm.p; p.trz = c.trz.p; p.LO = c.LO.p; p.adf_h = c.adf_h.p; p.adf_v = c.adf_v.p;
     p.tstar = c.tstar.p; p.eflx = c.eflx.p;
     return p;
+}
+
+void tracer_extrema(TracerCtx& c, int tr, double* tmin, double* tmax) {
+    *tmin = 0.0; *tmax = 0.0;
+    if (!fb_ok()) return;
+    if (!c.committed || tr < 0 || tr >= c.ntr) { fb_set_error(27, "fb200_tracer_extrema: not committed or no such tracer"); return; }
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    const int nb = std::min(148 * 8, (c.myN + 255) / 256);
+    DevBuf<double2> part; part.alloc(nb);
+    KP p = make_kp(c, tr);
+    { ProfScope ps_("k_extrema", st); k_extrema<<<nb, 256, 0, st>>>(p, p.T, part.p); LAUNCH_CHECK(); }
+    std::vector<double2> h(nb);
+    CUDA_CHECK(cudaMemcpyAsync(h.data(), part.p, nb * sizeof(double2), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    part.release();
+    double lo = 1.0e300, hi = -1.0e300;
+    for (const double2& v : h) { lo = v.x < lo ? v.x : lo; hi = v.y > hi ? v.y : hi; }
+    *tmin = lo; *tmax = hi;
 }
 
 static bool g_attr_done = false;
@@ -966,6 +1018,8 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     if (!c.opt.i_vert_diff) KL("k_copy_cols", k_copy_cols<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, p.tstar));      // T = T*, no implicit solve
     else if (c.opt.w_split && !fct) KL("k_impl_diff", k_impl_diff<true><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 0, st>>>(p));
     else KL("k_impl_diff", k_impl_diff<false><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 0, st>>>(p));
+    if (c.opt.clim_relax > 1.0e-8 && tr < 2 && c.relax2clim.p)                          // relax_to_clim(tr_num), oce_ale_tracer.F90:150-154
+        KL("k_relax_clim", k_relax_clim<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, tr == 0 ? c.Tclim.p : c.Sclim.p, c.relax2clim.p));
     if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
     if (c.opt.clamp_salt && tr == 1) KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T));   // tr_arr(:,:,2) only, :176-198
 #undef KL

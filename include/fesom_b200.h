@@ -118,6 +118,11 @@ void fb200_push_state_early(double* hnode, double* Z_3d_n, double* zbar_3d_n, do
                             double* heat_flux, double* water_flux, double* virtual_salt, double* relax_salt,
                             double* real_salt_flux, double* sw_3d);
 void fb200_push_state_late(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode_new, double* helem);
+/* climatology relaxation inside the step, relax_to_clim (src/oce_tracer_mod.F90:87-119, called at
+ * src/oce_ale_tracer.F90:150-154 between diff_tracers_ale and exchange_nod(tr_arr)): clim_relax (namelist oce_tra),
+ * relax2clim(N), Tclim/Sclim(nl-1,N).  Static data: call once after fb200_init_commit; *clim_relax <= 1e-8 = off.
+ * (relax_zonal_temp of the soufflet toy, src/toy_channel_soufflet.F90:78-103, is not provided.) */
+void fb200_set_clim(double* clim_relax, double* relax2clim, double* Tclim, double* Sclim);
 /* tr_arr / tr_arr_old (nl-1, N, num_tracers) */
 void fb200_push_tracers(double* tr_arr, double* tr_arr_old);
 void fb200_solve_tracers(void);                         /* all tracers, device resident */
@@ -127,6 +132,10 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old);   /* push + so
  * fb200_push_tracers) and returns tr_arr to the host; tr_arr_old stays on the device (its only reader is
  * init_tracers_AB, src/oce_tracer_mod.F90:64).  The copy of tracer k overlaps the kernels of tracer k+1. */
 void fb200_solve_tracers_ale_resident(double* tr_arr_out);
+/* min and max of the device-resident tracer *tr_num (1-based) over this partition's own wet cells: what check_blowup and
+ * the extrema lines of write_step_info (src/write_step_info.F90:220-504) test; lets a host that keeps the tracers resident
+ * monitor them without pulling the fields (combine the ranks with MPI_Allreduce as the reference does) */
+void fb200_tracer_extrema(int* tr_num, double* tmin, double* tmax);
 /* debugging / parity: copy an internal (level, node|edge|elem) work field back in the reference layout.
  * name: "fct_LO","adf_h","adf_v","fct_plus","fct_minus","tr_xy_x","tr_xy_y","ttfAB","tstar" ; returns via status */
 void fb200_debug_fetch(const char* name, double* out);

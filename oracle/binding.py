@@ -95,6 +95,13 @@ class TracerOracle:
         except Exception:
             pass
 
+    def set_clim(self, clim_relax, relax2clim, Tclim, Sclim):
+        """climatology relaxation (relax_to_clim, oce_tracer_mod.F90:87-119); arrays are bound, not copied"""
+        self._keep += [relax2clim, Tclim, Sclim]
+        self.L.oracle_set_dbl(self.o, b"clim_relax", float(clim_relax))
+        for nm, a in (("relax2clim", relax2clim), ("Tclim", Tclim), ("Sclim", Sclim)):
+            assert self.L.oracle_set_ptr(self.o, nm.encode(), a.ctypes.data) == 0
+
     def work(self, name, fshape):
         """numpy view (reversed Fortran shape) of an oracle-owned work array"""
         p = self.L.oracle_get_ptr(self.o, name.encode())

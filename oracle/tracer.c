@@ -730,6 +730,18 @@ void o_phase5(oracle_t* o, int tr_num) {
     }
     if (o->i_vert_diff) o_diff_ver_part_impl_ale(o, tr_num);
 }
+/* relax_to_clim, oce_tracer_mod.F90:87-119: own nodes, wet levels, tracers 1 (Tclim) and 2 (Sclim) */
+void o_relax_to_clim(oracle_t* o, int tr_num) {
+    if (!(o->clim_relax > 1.0e-8) || tr_num > 2 || !o->relax2clim) return;
+    const double* clim = tr_num == 1 ? o->Tclim : o->Sclim;
+    if (!clim) return;
+    double* ttf = TR(o, tr_num);
+    for (int n = 1; n <= o->myDim_nod2D; n++) {
+        int nzmin = o->ulevels_nod2D[n - 1], nzmax = o->nlevels_nod2D[n - 1];
+        for (int nz = nzmin; nz <= nzmax - 1; nz++)
+            T2(ttf, nz, n) = T2(ttf, nz, n) + o->relax2clim[n - 1] * o->dt * (T2(clim, nz, n) - T2(ttf, nz, n));
+    }
+}
 void o_phase_final(oracle_t* o) {                   /* oce_ale_tracer.F90:176-198 */
     if (!o->clamp_salt || o->num_tracers < 2) return;
     int N = o->myDim_nod2D + o->eDim_nod2D;
@@ -743,6 +755,7 @@ void o_phase_final(oracle_t* o) {                   /* oce_ale_tracer.F90:176-19
 void o_solve_tracers_ale(oracle_t* o) {
     for (int tr = 1; tr <= o->num_tracers; tr++) {
         o_phase1(o, tr); o_phase2(o, tr); o_phase3(o, tr); o_phase4(o, tr); o_phase5(o, tr);
+        o_relax_to_clim(o, tr);                         /* oce_ale_tracer.F90:150-154 (relax_zonal_temp of the soufflet toy is not restated) */
     }
     o_phase_final(o);
 }

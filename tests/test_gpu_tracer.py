@@ -235,3 +235,43 @@ def test_100_coupled_steps_match_oracle_mass_and_extrema(name):
         assert abs(a.min() - b.min()) <= 1e-12 * abs(b.min()) and abs(a.max() - b.max()) <= 1e-12 * abs(b.max())
         assert a.min() >= ext0[k][0] - 1e-12 and a.max() <= ext0[k][1] + 1e-12
     eng.close()
+
+
+@pytest.mark.parametrize("name", ["pi", "band"])
+def test_relax_to_clim_and_extrema_match_oracle(name):
+    """relax_to_clim inside the step (oce_tracer_mod.F90:87-119, between diff_tracers_ale and exchange_nod(tr_arr)) and
+    the device-side extrema scan of the resident tracers (what check_blowup / write_step_info test on the host)"""
+    from fesom2_b200 import api
+    from oracle import binding as ob
+    hm = util.build_model(name)
+    N, L = hm["tr_arr"].shape[1], hm["tr_arr"].shape[2]
+    rng = np.random.default_rng(3)
+    lat = hm["coord_nod2D"][:, 1]
+    relax2clim = np.where(np.abs(lat) > 1.0, 1.0 / (10.0 * 86400.0), 0.0) * rng.uniform(0.5, 1.0, N)      # ~10-day restoring poleward of 57 deg
+    Tclim = hm["tr_arr"][0] + 0.5 * rng.uniform(-1, 1, (N, L))
+    Sclim = hm["tr_arr"][1] + 0.1 * rng.uniform(-1, 1, (N, L))
+    eng = api.TracerEngine(hm)
+    eng.set_clim(1.0 / (10.0 * 86400.0), relax2clim, Tclim, Sclim)
+    eng.push_step_state()
+    eng.push_tracers()
+    o = ob.TracerOracle(hm)
+    o.set_clim(1.0 / (10.0 * 86400.0), relax2clim, Tclim, Sclim)
+    ref_norelax = None
+    out = np.zeros_like(hm["tr_arr"])
+    wet = util.wet_mask(hm)
+    for _ in range(2):
+        eng.solve_tracers_ale_resident(out)
+        o.step()
+    for k in range(2):
+        assert util.rel_err(out[k][wet], hm["tr_arr"][k][wet]) < TOL
+        lo, hi = eng.extrema(k + 1)
+        own = wet[:hm.ipar("myDim_nod2D")]
+        vals = hm["tr_arr"][k][:hm.ipar("myDim_nod2D")][own]
+        assert abs(lo - vals.min()) <= 1e-12 * abs(vals.min()) and abs(hi - vals.max()) <= 1e-12 * abs(vals.max())
+    # the relaxation really acted: switching it off gives a different field
+    hm2 = util.build_model(name)
+    o2 = ob.TracerOracle(hm2)
+    for _ in range(2):
+        o2.step()
+    assert util.rel_err(hm2["tr_arr"][0][wet], hm["tr_arr"][0][wet]) > 1e-8
+    eng.close()

@@ -111,3 +111,25 @@ def test_100_coupled_steps_conserve_mass_and_keep_extrema(name):
     for k in range(2):
         assert abs(util.tracer_mass(hm, k) - m0[k]) <= 1e-13 * abs(m0[k])
         assert tr[k][wet].min() >= ext0[k][0] - 1e-12 and tr[k][wet].max() <= ext0[k][1] + 1e-12
+
+
+def test_relax_to_clim_pulls_towards_climatology():
+    """relax_to_clim (oce_tracer_mod.F90:87-119): T_new = T + relax2clim*dt*(Tclim - T) on own wet cells after the
+    diffusion step; with relax2clim*dt = 1 the tracer lands exactly on the climatology, with 0 nothing changes"""
+    hm = util.build_model("band")
+    wet = util.wet_mask(hm)
+    N, L = hm["tr_arr"].shape[1], hm["tr_arr"].shape[2]
+    dt = hm.par("dt")
+    half = np.arange(N) % 2 == 0
+    relax2clim = np.where(half, 1.0 / dt, 0.0)
+    Tclim = np.full((N, L), 5.0)
+    Sclim = np.full((N, L), 35.0)
+    ref = util.build_model("band")
+    ob.TracerOracle(ref).step()
+    o = ob.TracerOracle(hm)
+    o.set_clim(1.0, relax2clim, Tclim, Sclim)
+    o.step()
+    on = wet & half[:, None]
+    off = wet & ~half[:, None]
+    assert np.abs(hm["tr_arr"][0][on] - 5.0).max() < 1e-12 and np.abs(hm["tr_arr"][1][on] - 35.0).max() < 1e-12
+    assert np.array_equal(hm["tr_arr"][0][off], ref["tr_arr"][0][off])
