@@ -20,7 +20,7 @@ LIM = {"FCT": 0, "NONE": 1}
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
-           "fb200_push_tracers", "fb200_set_clim", "fb200_tracer_extrema",
+           "fb200_push_tracers", "fb200_set_clim", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
@@ -198,6 +198,11 @@ class TracerEngine:
         """relax_to_clim inside the step: relax2clim (N), Tclim/Sclim (N, nl-1) numpy arrays, pushed once"""
         self._clim = (np.ascontiguousarray(relax2clim), np.ascontiguousarray(Tclim), np.ascontiguousarray(Sclim))
         self.L.fb200_set_clim(_d(clim_relax), _p(self._clim[0]), _p(self._clim[1]), _p(self._clim[2]))
+        _check(self.L)
+
+    def push_kpp_nonlocal(self, gT, gS, b2, b3, ref_sss=34.7, ref_sss_local=False, enable=True):
+        """KPP non-local transport arrays of this step, (N, nl) each (see fb200_push_kpp_nonlocal)"""
+        self.L.fb200_push_kpp_nonlocal(_i(int(enable)), _p(gT), _p(gS), _p(b2), _p(b3), _d(ref_sss), _i(int(ref_sss_local)))
         _check(self.L)
 
     def extrema(self, tr_num):

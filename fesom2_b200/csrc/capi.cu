@@ -186,6 +186,26 @@ void fb200_set_clim(double* clim_relax, double* relax2clim, double* Tclim, doubl
     CUDA_CHECK(cudaStreamSynchronize(c.stream));
 }
 
+// KPP non-local transport (use_kpp_nonlclflx, oce_ale_tracer.F90:688-781): per-step arrays of the mixing scheme.
+// fesom KPP (mix_scheme_nmb 1, 17): gT = gS = ghats, b2/b3 = blmc(:,:,2)/blmc(:,:,3); cvmix KPP (3, 37): gT/gS =
+// kpp_nonlcltranspT/S, b2/b3 = kpp_oblmixc(:,:,2)/(:,:,3).  *enable = 0 switches the term off.
+void fb200_push_kpp_nonlocal(int* enable, double* gT, double* gS, double* b2, double* b3, double* ref_sss, int* ref_sss_local) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(33, "fb200_push_kpp_nonlocal before fb200_init_commit"); return; }
+    c.opt.use_kpp_nonlclflx = *enable != 0;
+    if (!c.opt.use_kpp_nonlclflx) return;
+    c.opt.ref_sss = *ref_sss; c.opt.ref_sss_local = *ref_sss_local != 0;
+    fb_copy_sync();
+    c.stream = fb_stream();
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
+    if (!c.kgT.p) { c.kgT.alloc(nf); c.kgS.alloc(nf); c.kb2.alloc(nf); c.kb3.alloc(nf); }
+    ctx_push_node_field(c, gT, c.nl, c.N, c.kgT.p);
+    ctx_push_node_field(c, gS, c.nl, c.N, c.kgS.p);
+    ctx_push_node_field(c, b2, c.nl, c.N, c.kb2.p);
+    ctx_push_node_field(c, b3, c.nl, c.N, c.kb3.p);
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+}
+
 void fb200_push_tracers(double* tr_arr, double* tr_arr_old) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(34, "fb200_push_tracers before fb200_init_commit"); return; }

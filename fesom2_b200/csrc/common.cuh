@@ -41,6 +41,7 @@ struct Options {
     double ph = 1.0, pv = 1.0;
     int w_split = 0, i_vert_diff = 1, Redi = 0, use_sw_pene = 0, do_hor_diff = 1, clamp_salt = 1;
     double is_nonlinfs = 1.0, dt = 0.0, epsilon = 0.1;
+    int use_kpp_nonlclflx = 0, ref_sss_local = 0; double ref_sss = 34.7;   // fb200_push_kpp_nonlocal (oce_modules.F90:51-52)
     double clim_relax = 0.0;        // > 1e-8: relax_to_clim is applied to tracers 1 and 2 (fb200_set_clim)
     int tracer_id[8] = {0, 1, 301, 301, 301, 301, 301, 301};
 };
@@ -107,6 +108,7 @@ struct TracerCtx {
     DevBuf<double2> UV;             // (u, v) per element-level, tiled
     DevBuf<double> helem, W, We, Wi, hnode, hnode_new, Z3, zbar3, Kv, Ki, sl1, sl2, sl3, sw3d;
     DevBuf<double> heat_flux, water_flux, virtual_salt, relax_salt, real_salt_flux;   // (N)
+    DevBuf<double> kgT, kgS, kb2, kb3;          // KPP non-local transport: ghats / kpp_nonlcltransp{T,S}, blmc(:,:,2:3) (nl, N) tiled
     DevBuf<double> relax2clim, Tclim, Sclim;   // climatology relaxation: (N), tiled, tiled (fb200_set_clim)
     // tracers, tiled: [ntr] fields each
     DevBuf<double> T, Told;

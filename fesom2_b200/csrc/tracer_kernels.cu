@@ -25,6 +25,7 @@ struct KP {                       // kernel parameter block (by value)
     const double2* UV;              // (u, v) per element-level
     const double *area, *areasvol, *helem, *W, *We, *Wi, *hnode, *hnode_new, *Z3, *zbar3, *Kv, *Ki, *sl1, *sl2, *sl3, *sw3d;
     const double *heat_flux, *water_flux, *virtual_salt, *relax_salt, *real_salt_flux;
+    const double *kgT, *kgS, *kb2, *kb3; double ref_sss; int ref_sss_local;      // KPP non-local transport (fb200_push_kpp_nonlocal)
     double *T, *Told, *T1;        // this tracer's fields; T1 = tracer 1 (bc_surface)
     double2 *txy, *fpm;            // (tr_xy(1), tr_xy(2)) per element-level; (fct_plus, fct_minus) per node-level
     double *trz, *LO, *adf_h, *adf_v, *tstar;
@@ -701,7 +702,8 @@ __global__ void __launch_bounds__(256, 5) k_update(KP p) {
 //   pass 3 (bottom-up)  back substitution (:838-844) and T = T* + dT
 // zinv1 of level nz is the same expression as zinv2 of level nz-1 and is carried over.
 // dynamic smem: cp [blockDim.y][nlp][32]
-template <bool WIMPL>                       // WIMPL = w_split without FCT: implicit upwind advection by Wvel_i enters a, b, c (:604-616, :668-682, :737-744)
+// KPP = use_kpp_nonlclflx: the non-local transport of the boundary-layer scheme joins the right-hand side (:688-781)
+template <bool WIMPL, bool KPP>             // WIMPL = w_split without FCT: implicit upwind advection by Wvel_i enters a, b, c (:604-616, :668-682, :737-744)
 __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
     const int lane = threadIdx.x;
     const int tile = blockIdx.x * blockDim.y + threadIdx.y;
@@ -808,6 +810,21 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
         if (z == nzmin) tr = -(bb - h) * t0 - cc * tp1;
         else if (z <= nzmax - 2) tr = -a * tm - (bb - h) * t0 - cc * tp1;
         else tr = -a * tm - (bb - h) * t0;
+        if (KPP && p.tr_num <= 2) {                                          // :688-781, fesom KPP and cvmix KPP share the formula
+            const double* __restrict__ G = p.tr_num == 1 ? p.kgT : p.kgS;
+            const double* __restrict__ B = p.tr_num == 1 ? p.kb2 : p.kb3;
+            const double m0 = z > nzmin ? omin(AT(G, b, z) * AT(B, b, z), 1.0) : 0.0;
+            const double m1 = z <= nzmax - 2 ? omin(AT(G, b, z + 1) * AT(B, b, z + 1), 1.0) : 0.0;
+            double x;
+            if (z == nzmin) x = -m1 * (ar1 / asv);
+            else if (z <= nzmax - 2) x = m0 * (ar0 / asv) - m1 * (ar1 / asv);
+            else x = m0 * (ar0 / asv);
+            if (p.tr_num == 1) tr = tr + x * p.heat_flux[n] / vcpw * dt;
+            else {
+                const double rsss = p.ref_sss_local ? AT(TS, b, 1) : p.ref_sss;     // tr_arr(1,n,2), :691
+                tr = tr - x * rsss * p.water_flux[n] * dt;
+            }
+        }
         if (p.use_sw_pene && p.tr_num == 1)
             tr = tr + (AT(p.sw3d, b, z) - AT(p.sw3d, b, z + 1) * ar1 / asv) * zinv;
         if (z == nzmin) {
@@ -908,6 +925,7 @@ static KP make_kp(TracerCtx& c, int tr) {
     p.area = c.area.p; p.areasvol = c.areasvol.p; p.UV = c.UV.p; p.helem = c.helem.p; p.W = c.W.p; p.We = c.opt.w_split ? c.We.p : c.W.p; p.Wi = c.Wi.p;
     p.hnode = c.hnode.p; p.hnode_new = c.hnode_new.p; p.Z3 = c.Z3.p; p.zbar3 = c.zbar3.p; p.Kv = c.Kv.p; p.Ki = c.Ki.p;
     p.sl1 = c.sl1.p; p.sl2 = c.sl2.p; p.sl3 = c.sl3.p; p.sw3d = c.sw3d.p;
+    p.kgT = c.kgT.p; p.kgS = c.kgS.p; p.kb2 = c.kb2.p; p.kb3 = c.kb3.p; p.ref_sss = c.opt.ref_sss; p.ref_sss_local = c.opt.ref_sss_local;
     p.heat_flux = c.heat_flux.p; p.water_flux = c.water_flux.p; p.virtual_salt = c.virtual_salt.p; p.relax_salt = c.relax_salt.p; p.real_salt_flux = c.real_salt_flux.p;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     p.T = c.T.p + nf * tr; p.Told = c.Told.p + nf * tr; p.T1 = c.T.p;
@@ -941,8 +959,6 @@ static void set_smem_attrs() {
     const int big = 200 * 1024;
     CUDA_CHECK(cudaFuncSetAttribute(k_vert_impl, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     CUDA_CHECK(cudaFuncSetAttribute(k_fct_bounds, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    CUDA_CHECK(cudaFuncSetAttribute(k_impl_diff<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    CUDA_CHECK(cudaFuncSetAttribute(k_impl_diff<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     g_attr_done = true;
 }
 
@@ -1016,8 +1032,14 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
         CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
     }
     if (!c.opt.i_vert_diff) KL("k_copy_cols", k_copy_cols<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, p.tstar));      // T = T*, no implicit solve
-    else if (c.opt.w_split && !fct) KL("k_impl_diff", k_impl_diff<true><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 0, st>>>(p));
-    else KL("k_impl_diff", k_impl_diff<false><<<(c.myNtiles + 1) / 2, dim3(TILE, 2), 0, st>>>(p));
+    else {
+        const bool wimpl = c.opt.w_split && !fct, kpp = c.opt.use_kpp_nonlclflx && c.kgT.p;
+        const dim3 gI((c.myNtiles + 1) / 2), bI(TILE, 2);
+        if (wimpl && kpp) KL("k_impl_diff", k_impl_diff<true, true><<<gI, bI, 0, st>>>(p));
+        else if (wimpl) KL("k_impl_diff", k_impl_diff<true, false><<<gI, bI, 0, st>>>(p));
+        else if (kpp) KL("k_impl_diff", k_impl_diff<false, true><<<gI, bI, 0, st>>>(p));
+        else KL("k_impl_diff", k_impl_diff<false, false><<<gI, bI, 0, st>>>(p));
+    }
     if (c.opt.clim_relax > 1.0e-8 && tr < 2 && c.relax2clim.p)                          // relax_to_clim(tr_num), oce_ale_tracer.F90:150-154
         KL("k_relax_clim", k_relax_clim<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, tr == 0 ? c.Tclim.p : c.Sclim.p, c.relax2clim.p));
     if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155

@@ -118,6 +118,11 @@ void fb200_push_state_early(double* hnode, double* Z_3d_n, double* zbar_3d_n, do
                             double* heat_flux, double* water_flux, double* virtual_salt, double* relax_salt,
                             double* real_salt_flux, double* sw_3d);
 void fb200_push_state_late(double* UV, double* Wvel, double* Wvel_e, double* Wvel_i, double* hnode_new, double* helem);
+/* KPP non-local transport in the implicit vertical diffusion (use_kpp_nonlclflx, src/oce_ale_tracer.F90:688-781), per step
+ * when the mixing scheme has run: (nl,N) arrays gT/gS = ghats (fesom KPP, mix_scheme_nmb 1/17) or kpp_nonlcltranspT/S
+ * (cvmix KPP, 3/37), b2/b3 = blmc(:,:,2:3) or kpp_oblmixc(:,:,2:3); ref_sss, ref_sss_local (src/oce_modules.F90:51-52).
+ * *enable = 0 switches the term off (the arrays are then not read). */
+void fb200_push_kpp_nonlocal(int* enable, double* gT, double* gS, double* b2, double* b3, double* ref_sss, int* ref_sss_local);
 /* climatology relaxation inside the step, relax_to_clim (src/oce_tracer_mod.F90:87-119, called at
  * src/oce_ale_tracer.F90:150-154 between diff_tracers_ale and exchange_nod(tr_arr)): clim_relax (namelist oce_tra),
  * relax2clim(N), Tclim/Sclim(nl-1,N).  Static data: call once after fb200_init_commit; *clim_relax <= 1e-8 = off.

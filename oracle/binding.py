@@ -102,6 +102,15 @@ class TracerOracle:
         for nm, a in (("relax2clim", relax2clim), ("Tclim", Tclim), ("Sclim", Sclim)):
             assert self.L.oracle_set_ptr(self.o, nm.encode(), a.ctypes.data) == 0
 
+    def set_kpp_nonlocal(self, gT, gS, b2, b3, ref_sss=34.7, ref_sss_local=False):
+        """KPP non-local transport in diff_ver_part_impl_ale (oce_ale_tracer.F90:688-781); (N, nl) arrays, bound not copied"""
+        self._keep += [gT, gS, b2, b3]
+        self.L.oracle_set_int(self.o, b"use_kpp_nonlclflx", 1)
+        self.L.oracle_set_int(self.o, b"ref_sss_local", int(ref_sss_local))
+        self.L.oracle_set_dbl(self.o, b"ref_sss", float(ref_sss))
+        for nm, a in (("kpp_gT", gT), ("kpp_gS", gS), ("kpp_b2", b2), ("kpp_b3", b3)):
+            assert self.L.oracle_set_ptr(self.o, nm.encode(), a.ctypes.data) == 0
+
     def work(self, name, fshape):
         """numpy view (reversed Fortran shape) of an oracle-owned work array"""
         p = self.L.oracle_get_ptr(self.o, name.encode())

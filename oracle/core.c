@@ -6,13 +6,13 @@
 
 #define INT_FIELDS(X) X(nl) X(myDim_nod2D) X(eDim_nod2D) X(myDim_elem2D) X(eDim_elem2D) X(eXDim_elem2D) X(myDim_edge2D) \
     X(nod_in_elem2D_max) X(num_tracers) X(tra_adv_hor) X(tra_adv_ver) X(tra_adv_lim) X(w_split) X(i_vert_diff) X(Redi)    \
-    X(use_sw_pene) X(do_hor_diff) X(clamp_salt)
-#define DBL_FIELDS(X) X(dt) X(epsilon) X(tra_adv_ph) X(tra_adv_pv) X(is_nonlinfs) X(clim_relax)
+    X(use_sw_pene) X(do_hor_diff) X(clamp_salt) X(use_kpp_nonlclflx) X(ref_sss_local)
+#define DBL_FIELDS(X) X(dt) X(epsilon) X(tra_adv_ph) X(tra_adv_pv) X(is_nonlinfs) X(clim_relax) X(ref_sss)
 #define CIPTR_FIELDS(X) X(edges) X(edge_tri) X(elem2D_nodes) X(nlevels) X(ulevels) X(nlevels_nod2D) X(ulevels_nod2D) \
     X(nlevels_nod2D_min) X(ulevels_nod2D_max) X(nod_in_elem2D) X(nod_in_elem2D_num) X(edge_up_dn_tri) X(nboundary_lay)
 #define CDPTR_FIELDS(X) X(edge_cross_dxdy) X(edge_dxdy) X(elem_cos) X(elem_area) X(gradient_sca) X(area) X(areasvol) \
     X(zbar_n_bot) X(UV) X(Wvel) X(Wvel_e) X(Wvel_i) X(hnode) X(hnode_new) X(helem) X(Z_3d_n) X(zbar_3d_n) X(Kv) X(Ki)  \
-    X(slope_tapered) X(heat_flux) X(water_flux) X(virtual_salt) X(relax_salt) X(real_salt_flux) X(sw_3d) X(relax2clim) X(Tclim) X(Sclim)
+    X(slope_tapered) X(heat_flux) X(water_flux) X(virtual_salt) X(relax_salt) X(real_salt_flux) X(sw_3d) X(relax2clim) X(Tclim) X(Sclim) X(kpp_gT) X(kpp_gS) X(kpp_b2) X(kpp_b3)
 #define DPTR_FIELDS(X) X(tr_arr) X(tr_arr_old)
 #define WORK_FIELDS(X) X(del_ttf) X(del_ttf_advhoriz) X(del_ttf_advvert) X(tr_xy) X(tr_z) X(edge_up_dn_grad) X(fct_LO) \
     X(adv_flux_hor) X(adv_flux_ver) X(fct_ttf_max) X(fct_ttf_min) X(fct_plus) X(fct_minus) X(aux_minmax)
@@ -24,6 +24,7 @@ oracle_t* oracle_create(void) {
     o->tra_adv_hor = O_HOR_MFCT; o->tra_adv_ver = O_VER_QR4C; o->tra_adv_lim = O_LIM_FCT;   /* config/namelist.oce:74-78 */
     o->i_vert_diff = 1; o->do_hor_diff = 1; o->clamp_salt = 1; o->is_nonlinfs = 1.0;
     o->num_tracers = 2; o->tracer_id[0] = 0; o->tracer_id[1] = 1;
+    o->ref_sss = 34.7;          /* oce_modules.F90:52 */
     return o;
 }
 void oracle_free(oracle_t* o) {

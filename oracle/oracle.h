@@ -36,14 +36,17 @@ typedef struct oracle {
                  *slope_tapered, *heat_flux, *water_flux, *virtual_salt, *relax_salt, *real_salt_flux, *sw_3d;
     /* climatology relaxation (o_ARRAYS: relax2clim(N), Tclim/Sclim(nl-1,N); namelist oce_tra: clim_relax) */
     const double *relax2clim, *Tclim, *Sclim;
+    /* KPP non-local transport (use_kpp_nonlclflx): ghats (fesom KPP) or kpp_nonlcltranspT/S (cvmix) as kpp_gT/kpp_gS (nl,N),
+     * blmc(:,:,2:3) or kpp_oblmixc(:,:,2:3) as kpp_b2/kpp_b3 (nl,N); ref_sss, ref_sss_local (oce_modules.F90:51-52) */
+    const double *kpp_gT, *kpp_gS, *kpp_b2, *kpp_b3;
     /* tracers, (nl-1, N, num_tracers) */
     double *tr_arr, *tr_arr_old;
     /* work arrays owned by the oracle (o_ARRAYS / o_MESH work arrays) */
     double *del_ttf, *del_ttf_advhoriz, *del_ttf_advvert, *tr_xy, *tr_z, *edge_up_dn_grad, *fct_LO,
            *adv_flux_hor, *adv_flux_ver, *fct_ttf_max, *fct_ttf_min, *fct_plus, *fct_minus, *aux_minmax;
     /* parameters (namelists oce_tra / oce_dyn, g_config) */
-    double dt, epsilon, tra_adv_ph, tra_adv_pv, is_nonlinfs, clim_relax;
-    int tra_adv_hor, tra_adv_ver, tra_adv_lim, w_split, i_vert_diff, Redi, use_sw_pene, do_hor_diff, clamp_salt;
+    double dt, epsilon, tra_adv_ph, tra_adv_pv, is_nonlinfs, clim_relax, ref_sss;
+    int tra_adv_hor, tra_adv_ver, tra_adv_lim, w_split, i_vert_diff, Redi, use_sw_pene, do_hor_diff, clamp_salt, use_kpp_nonlclflx, ref_sss_local;
     int tracer_id[8];
 } oracle_t;
 

@@ -554,7 +554,7 @@ static double bc_surface(oracle_t* o, int n, int id) {
     return 0.0;   /* ids 301..303 */
 }
 
-/* oce_ale_tracer.F90:398-856 (KPP non-local transport is outside the path: use_kpp_nonlclflx = .false.) */
+/* oce_ale_tracer.F90:398-856 */
 void o_diff_ver_part_impl_ale(oracle_t* o, int tr_num) {
     const double dt = o->dt;
     int N = o->myDim_nod2D + o->eDim_nod2D;
@@ -633,6 +633,22 @@ void o_diff_ver_part_impl_ale(oracle_t* o, int tr_num) {
         nz = nzmax - 1;
         dz = T2(hn, nz, n);
         tr[nz] = -a[nz] * T2(trc, nz - 1, n) - (b[nz] - dz) * T2(trc, nz, n);
+        if (o->use_kpp_nonlclflx && tr_num <= 2) {            /* KPP non-local fluxes, oce_ale_tracer.F90:688-781 (both KPP variants: same formula) */
+            const double* g = tr_num == 1 ? o->kpp_gT : o->kpp_gS;
+            const double* bl = tr_num == 1 ? o->kpp_b2 : o->kpp_b3;
+            double rsss = o->ref_sss;
+            if (tr_num == 2 && o->ref_sss_local) rsss = T2(trc, 1, n);                     /* tr_arr(1,n,2) */
+#define KM(z) dmin(W2(g, z, n) * W2(bl, z, n), 1.0)
+            for (nz = nzmin; nz <= nzmax - 1; nz++) {
+                double x;
+                if (nz == nzmin) x = (-KM(nz + 1) * (W2(area, nz + 1, n) / W2(asv, nz, n)));
+                else if (nz <= nzmax - 2) x = (KM(nz) * (W2(area, nz, n) / W2(asv, nz, n)) - KM(nz + 1) * (W2(area, nz + 1, n) / W2(asv, nz, n)));
+                else x = (KM(nz) * (W2(area, nz, n) / W2(asv, nz, n)));
+                if (tr_num == 1) tr[nz] = tr[nz] + x * o->heat_flux[n - 1] / vcpw * dt;
+                else tr[nz] = tr[nz] - x * rsss * o->water_flux[n - 1] * dt;
+            }
+#undef KM
+        }
         if (o->use_sw_pene && tr_num == 1)
             for (nz = nzmin; nz <= nzmax - 1; nz++) {
                 zinv = 1.0 * dt;

@@ -275,3 +275,39 @@ def test_relax_to_clim_and_extrema_match_oracle(name):
         o2.step()
     assert util.rel_err(hm2["tr_arr"][0][wet], hm["tr_arr"][0][wet]) > 1e-8
     eng.close()
+
+
+@pytest.mark.parametrize("name,local,opts,model_kw", [
+    ("band", True, {}, {}),
+    ("pi", False, {}, {}),
+    ("soufflet", True, {"tra_adv_lim": "NONE", "tra_adv_hor": "MUSCL"}, {"w_split": True, "w_max_cfl": 0.2}),     # with the implicit Wvel_i terms
+])
+def test_kpp_nonlocal_transport_matches_oracle(name, local, opts, model_kw):
+    """use_kpp_nonlclflx (oce_ale_tracer.F90:688-781) in the implicit vertical diffusion: ghats*blmc products above and
+    below 1 (the MIN acts), non-zero heat and freshwater fluxes, ref_sss and ref_sss_local"""
+    from fesom2_b200 import api
+    from oracle import binding as ob
+    from tests.test_oracle_tracer import _kpp_arrays
+    hm = util.build_model(name, water_flux=2e-7, heat_flux=80.0, **model_kw)
+    arrs = _kpp_arrays(hm)
+    eng = api.TracerEngine(hm, **opts)
+    eng.push_step_state()
+    eng.push_kpp_nonlocal(*arrs, ref_sss=34.2, ref_sss_local=local)
+    g_tr, g_tro = hm["tr_arr"].copy(), hm["tr_arr_old"].copy()
+    for _ in range(2):
+        eng.solve_tracers_ale(g_tr, g_tro)
+    o = ob.TracerOracle(hm, **opts)
+    o.set_kpp_nonlocal(*arrs, ref_sss=34.2, ref_sss_local=local)
+    for _ in range(2):
+        o.step()
+    wet = util.wet_mask(hm)
+    for k in range(2):
+        assert util.rel_err(g_tr[k][wet], hm["tr_arr"][k][wet]) < TOL
+    # switching it off again restores the plain step
+    eng.push_kpp_nonlocal(*arrs, enable=False)
+    h2 = util.build_model(name, water_flux=2e-7, heat_flux=80.0, **model_kw)
+    a_tr, a_tro = h2["tr_arr"].copy(), h2["tr_arr_old"].copy()
+    eng.solve_tracers_ale(a_tr, a_tro)
+    ob.TracerOracle(h2, **opts).step()
+    assert util.rel_err(a_tr[0][wet], h2["tr_arr"][0][wet]) < TOL
+    eng.close()

@@ -133,3 +133,33 @@ def test_relax_to_clim_pulls_towards_climatology():
     off = wet & ~half[:, None]
     assert np.abs(hm["tr_arr"][0][on] - 5.0).max() < 1e-12 and np.abs(hm["tr_arr"][1][on] - 35.0).max() < 1e-12
     assert np.array_equal(hm["tr_arr"][0][off], ref["tr_arr"][0][off])
+
+
+def _kpp_arrays(hm, seed=11):
+    rng = np.random.default_rng(seed)
+    N, nl = hm["Kv"].shape
+    z = np.arange(nl)[None, :]
+    g = 2.0 * np.exp(-z / 6.0) * rng.uniform(0.2, 1.0, (N, nl))          # "ghats": decays below the boundary layer
+    gS = 1.5 * np.exp(-z / 5.0) * rng.uniform(0.2, 1.0, (N, nl))
+    b2 = rng.uniform(0.0, 1.2, (N, nl))                                    # ghats*blmc exceeds 1 in places: the MIN(.., 1) acts
+    b3 = rng.uniform(0.0, 1.2, (N, nl))
+    return [np.ascontiguousarray(a) for a in (g, gS, b2, b3)]
+
+
+def test_kpp_nonlocal_transport_redistributes_without_changing_the_column_content():
+    """use_kpp_nonlclflx (oce_ale_tracer.F90:688-781): the non-local flux is a telescoping sum over the column (no flux
+    through the surface or the bottom), so it changes the profile but not sum_z T h area — the step with it conserves
+    exactly what the step without it conserves"""
+    kw = dict(water_flux=2e-7, heat_flux=80.0)
+    ha, hb = util.build_model("band", **kw), util.build_model("band", **kw)
+    wet = util.wet_mask(ha)
+    nl = ha.ipar("nl")
+    oa, obb = ob.TracerOracle(ha, clamp_salt=False), ob.TracerOracle(hb, clamp_salt=False)
+    oa.set_kpp_nonlocal(*_kpp_arrays(ha), ref_sss=34.7, ref_sss_local=True)
+    oa.step()
+    obb.step()
+    for k in range(2):
+        ca = (ha["tr_arr"][k] * ha["hnode_new"] * ha["areasvol"][:, :nl - 1] * wet).sum(axis=1)
+        cb = (hb["tr_arr"][k] * hb["hnode_new"] * hb["areasvol"][:, :nl - 1] * wet).sum(axis=1)
+        assert np.abs(ca - cb).max() <= 1e-11 * np.abs(cb).max()
+        assert util.rel_err(ha["tr_arr"][k][wet], hb["tr_arr"][k][wet]) > 1e-9            # but the profile did change
