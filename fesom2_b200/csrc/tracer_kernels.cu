@@ -446,6 +446,7 @@ __global__ void __launch_bounds__(128) k_ho_edge_fb(KP p, const int2* __restrict
 // UV_rhs(1:2,nz,nod_in_elem2D(:,n)); "-bignumber/+bignumber" enter wherever a surrounding element is already below
 // its bottom (nz >= nlevels_nod2D_min).  The vertical 3-point max/min (a3, vlimit=1) goes through shared memory.
 // dynamic smem: mx, mn  [2][nlp][32]
+template <int LP>                           // levels per thread: 3 up to 48 layers (16 level rows), 4 up to 62 (the block holds the whole column)
 __global__ void __launch_bounds__(512, 2) k_fct_bounds(KP p) {
     extern __shared__ double sm[];
     double* smx = sm; double* smn = sm + (size_t)p.nlp * TILE;
@@ -453,11 +454,11 @@ __global__ void __launch_bounds__(512, 2) k_fct_bounds(KP p) {
     const double flux_eps = 1e-16, bignumber = 1e3;
     const double* __restrict__ T = p.T;
     const double* __restrict__ LO = p.LO;
-    int nz[LPT]; bool act[LPT]; double pp[LPT], pm[LPT], mx[LPT], mn[LPT], lo[LPT];
+    int nz[LP]; bool act[LP]; double pp[LP], pm[LP], mx[LP], mn[LP], lo[LP];
     bool any = false;
 #pragma unroll
-    for (int q = 0; q < LPT; q++) {
-        nz[q] = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
+    for (int q = 0; q < LP; q++) {
+        nz[q] = blockIdx.y * (LP * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
         act[q] = c.valid && nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
         pp[q] = pm[q] = mx[q] = mn[q] = lo[q] = 0.0;
         if (!act[q]) continue;
@@ -481,7 +482,7 @@ __global__ void __launch_bounds__(512, 2) k_fct_bounds(KP p) {
             const int bo = sr.bo, bed = sr.bed;
             const unsigned long long many = sr.mk;
 #pragma unroll
-            for (int q = 0; q < LPT; q++) {
+            for (int q = 0; q < LP; q++) {
                 if (!act[q] || !((many >> nz[q]) & 1ull)) continue;
                 double f = AT(p.adf_h, bed, nz[q]);
                 const double lo_o = AT(LO, bo, nz[q]), t_o = AT(T, bo, nz[q]);
@@ -493,12 +494,12 @@ __global__ void __launch_bounds__(512, 2) k_fct_bounds(KP p) {
             }
         }
 #pragma unroll
-        for (int q = 0; q < LPT; q++)
+        for (int q = 0; q < LP; q++)
             if (act[q]) { smx[(nz[q] - 1) * TILE + threadIdx.x] = mx[q]; smn[(nz[q] - 1) * TILE + threadIdx.x] = mn[q]; }
     }
     __syncthreads();
 #pragma unroll
-    for (int q = 0; q < LPT; q++) {
+    for (int q = 0; q < LP; q++) {
         if (!act[q]) continue;
         const int z = nz[q];
         double qmax = mx[q], qmin = mn[q];
@@ -958,7 +959,8 @@ static void set_smem_attrs() {
     if (g_attr_done) return;
     const int big = 200 * 1024;
     CUDA_CHECK(cudaFuncSetAttribute(k_vert_impl, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-    CUDA_CHECK(cudaFuncSetAttribute(k_fct_bounds, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    CUDA_CHECK(cudaFuncSetAttribute(k_fct_bounds<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    CUDA_CHECK(cudaFuncSetAttribute(k_fct_bounds<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     g_attr_done = true;
 }
 
@@ -970,8 +972,7 @@ bool tracer_step_begin(TracerCtx& c) {
     if (!fb_ok()) return false;
     if (!c.committed) { fb_set_error(20, "fb200_solve_tracers before fb200_init_commit"); return false; }
     if (c.opt.dt <= 0.0) { fb_set_error(24, "dt not set (fb200_set_options)"); return false; }
-    const int LY = (c.nl - 1 + LPT - 1) / LPT;                  // level rows per block: LPT levels per thread cover nl-1 layers
-    if (LY * TILE > 512) { fb_set_error(25, "nl too large for the level-row thread mapping (nl-1 <= 48)"); return false; }
+    if (c.nl - 1 > 64) { fb_set_error(25, "nl too large for the level-row thread mapping of k_fct_bounds (nl-1 <= 64)"); return false; }
     if (comm_nranks() > 1 && !c.halo_nod) { fb_set_error(26, "more than one rank but fb200_init_halo was not called"); return false; }
     set_smem_attrs();
     fb_copy_sync();                                             // state pushed with fb200_push_state_early must have landed
@@ -985,8 +986,8 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     cudaStream_t st = c.stream;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     const int gN64 = (c.myN + 63) / 64, gE = (c.myE + 127) / 128, gNall = (c.N + 127) / 128;
-    const int LY = (c.nl - 1 + LPT - 1) / LPT;
-    const dim3 blk(TILE, LY);
+    const int LPB = c.nl - 1 <= 48 ? 3 : 4;                     // k_fct_bounds: one block = one tile x the whole column, <= 16 level rows
+    const dim3 blk(TILE, (c.nl - 1 + LPB - 1) / LPB);
     // kernels without block-wide exchange run on 8 level rows per block (LPT * 8 = 24 levels) and gridDim.y level chunks
     const dim3 blk8(TILE, 8);
     const int nchunk = (c.nl - 1 + LPT * 8 - 1) / (LPT * 8);
@@ -1014,7 +1015,8 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     if (fct) {
         if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
         if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);               // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
-        KL("k_fct_bounds", k_fct_bounds<<<c.myNtiles, blk, 2 * smt, st>>>(p));
+        if (LPB == 3) KL("k_fct_bounds", k_fct_bounds<3><<<c.myNtiles, blk, 2 * smt, st>>>(p));
+        else KL("k_fct_bounds", k_fct_bounds<4><<<c.myNtiles, blk, 2 * smt, st>>>(p));
         if (multi) halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st);     // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
     }
     if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));

@@ -50,6 +50,8 @@ def run_pair(name, opts=None, model_kw=None, steps=1):
     ("farclike", {}, {}),                         # BASELINE.json config 4 stand-in: multi-resolution mesh
     ("farclike", {"shuffle": True}, {}),          # the same mesh with a random node/element numbering (no locality)
     ("core2like", {}, {}),                        # BASELINE.json config 3 stand-in: 127 k surface nodes x 47 layers
+    ("band", {"nlon": 60, "nlat": 36, "nl": 63}, {}),                                   # up to 59 wet layers: k_fct_bounds<4>, three level chunks
+    ("band", {"nlon": 60, "nlat": 36, "nl": 56, "w_split": True, "w_max_cfl": 0.2}, {"tra_adv_ver": "PPM"}),
 ])
 def test_tracer_step_matches_oracle(name, model_kw, opts):
     hm, eng, o, g_tr, g_tro = run_pair(name, opts, model_kw)
