@@ -199,7 +199,10 @@ void ctx_commit(TracerCtx& c) {
             const int nl12 = std::min(nl1, nl2), nu12 = std::max(nu1, nu2);
             for (int nz = 1; nz <= nlp; nz++) {
                 const bool inA = nz >= nu1 && nz <= nu12 - 1, inB = nu2 > 0 && nz >= nu2 && nz <= nu12 - 1;
-                const bool inC = nz >= nu12 && nz <= nl12, inD = nz >= nl12 + 1 && nz <= nl1, inE = nz >= nl12 + 1 && nz <= nl2;
+                // (D)/(E) also require the element to be wet at nz: on a boundary edge (nl12 = 0) the reference's loop (D) starts at
+                // level 1 even when the element begins below an ice-shelf cavity; UV and helem are zero up there, so those
+                // fluxes are exact zeros — dropping them changes no sum and keeps "mask bit = a wet element joins the two nodes"
+                const bool inC = nz >= nu12 && nz <= nl12, inD = nz >= nl12 + 1 && nz <= nl1 && nz >= nu1, inE = nz >= nl12 + 1 && nz <= nl2 && nz >= nu2;
                 if ((int)inA + inB + inC + inD + inE > 1) { fb_set_error(15, "edge with overlapping level ranges (disjoint element columns) is not supported"); return; }
                 if (inA || inC || inD) r.m1 |= 1ull << nz;
                 if (inB || inC || inE) r.m2 |= 1ull << nz;

@@ -359,6 +359,10 @@ __device__ __noinline__ void node_mean_grad(const int* __restrict__ nie_slot, in
         tx = tx + g.x * ar;
         ty = ty + g.y * ar;
     }
+    // tvol == 0: nz lies outside this node's own level range (above its cavity top or below its bottom).  The reference
+    // does not compute edge_up_dn_grad there (oce_muscl_adv.F90:313,337: the loops start at ulevels_nod2D(node)) and the
+    // entry only ever meets a zero volume flux (no element of the node is wet at nz); 0/0 would turn that 0 into NaN
+    if (tvol == 0.0) { gx = 0.0; gy = 0.0; return; }
     gx = tx / tvol; gy = ty / tvol;
 }
 

@@ -6,7 +6,7 @@
 
 #define INT_FIELDS(X) X(nl) X(myDim_nod2D) X(eDim_nod2D) X(myDim_elem2D) X(eDim_elem2D) X(eXDim_elem2D) X(myDim_edge2D) \
     X(nod_in_elem2D_max) X(num_tracers) X(tra_adv_hor) X(tra_adv_ver) X(tra_adv_lim) X(w_split) X(i_vert_diff) X(Redi)    \
-    X(use_sw_pene) X(do_hor_diff) X(clamp_salt) X(use_kpp_nonlclflx) X(ref_sss_local)
+    X(use_sw_pene) X(do_hor_diff) X(clamp_salt) X(use_kpp_nonlclflx) X(ref_sss_local) X(fct_cavity_neutral)
 #define DBL_FIELDS(X) X(dt) X(epsilon) X(tra_adv_ph) X(tra_adv_pv) X(is_nonlinfs) X(clim_relax) X(ref_sss)
 #define CIPTR_FIELDS(X) X(edges) X(edge_tri) X(elem2D_nodes) X(nlevels) X(ulevels) X(nlevels_nod2D) X(ulevels_nod2D) \
     X(nlevels_nod2D_min) X(ulevels_nod2D_max) X(nod_in_elem2D) X(nod_in_elem2D_num) X(edge_up_dn_tri) X(nboundary_lay)

@@ -47,6 +47,11 @@ typedef struct oracle {
     /* parameters (namelists oce_tra / oce_dyn, g_config) */
     double dt, epsilon, tra_adv_ph, tra_adv_pv, is_nonlinfs, clim_relax, ref_sss;
     int tra_adv_hor, tra_adv_ver, tra_adv_lim, w_split, i_vert_diff, Redi, use_sw_pene, do_hor_diff, clamp_salt, use_kpp_nonlclflx, ref_sss_local;
+    /* oce_tra_adv_fct a2/a3 under cavities: a3 (oce_adv_tra_fct.F90:139-140) reads UV_rhs(1:2,nz,elem) of elements whose
+     * cavity top lies below nz, entries a2 (:108-121) never wrote — in the reference they hold whatever the momentum step
+     * left in UV_rhs.  0: the scratch as allocated (zeros, then the previous call's values); 1: those entries are neutral
+     * (-bignumber / +bignumber, the rule a2 applies below the bottom), which is what the CUDA path computes. */
+    int fct_cavity_neutral;
     int tracer_id[8];
 } oracle_t;
 

@@ -346,6 +346,8 @@ void o_oce_tra_adv_fct_a(oracle_t* o, const double* ttf, const double* LO, doubl
     for (int elem = 1; elem <= o->myDim_elem2D; elem++) {                                      /* a2 */
         const int* en = &I2(o->elem2D_nodes, 3, 1, elem);
         int nu1 = o->ulevels[elem - 1], nl1 = o->nlevels[elem - 1];
+        if (o->fct_cavity_neutral)                                                             /* see oracle.h */
+            for (int nz = 1; nz <= nu1 - 1; nz++) { V3(aux, 1, nz, elem) = -bignumber; V3(aux, 2, nz, elem) = bignumber; }
         for (int nz = nu1; nz <= nl1 - 1; nz++) {
             V3(aux, 1, nz, elem) = dmax(dmax(T2(fmax, nz, en[0]), T2(fmax, nz, en[1])), T2(fmax, nz, en[2]));
             V3(aux, 2, nz, elem) = dmin(dmin(T2(fmin, nz, en[0]), T2(fmin, nz, en[1])), T2(fmin, nz, en[2]));

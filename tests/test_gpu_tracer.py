@@ -313,3 +313,38 @@ def test_kpp_nonlocal_transport_matches_oracle(name, local, opts, model_kw):
     ob.TracerOracle(h2, **opts).step()
     assert util.rel_err(a_tr[0][wet], h2["tr_arr"][0][wet]) < TOL
     eng.close()
+
+
+def cavity_ring(hm):
+    """nodes whose elements start at different levels (the edge of an ice-shelf cavity) and their edge neighbours"""
+    C = hm["ulevels_nod2D"] < hm["ulevels_nod2D_max"]
+    ed = hm["edges"].reshape(-1, 2) - 1
+    ring = C.copy()
+    ring[ed[C[ed[:, 1]], 0]] = True
+    ring[ed[C[ed[:, 0]], 1]] = True
+    return ring
+
+
+@pytest.mark.parametrize("opts", [{}, {"tra_adv_hor": "MUSCL", "tra_adv_ver": "PPM"}, {"tra_adv_lim": "NONE", "tra_adv_hor": "MUSCL"}])
+def test_cavity_patch_matches_oracle(opts):
+    """ice-shelf cavity (ulevels 3/4 inside a box; boundary edges of cavity elements, all five level ranges of
+    oce_adv_tra_hor.F90:129-209).  Under a cavity edge the reference's limiter reads scratch entries it never wrote
+    (oracle.h: fct_cavity_neutral); the CUDA path treats them as neutral, so it is bit-compared with the oracle in that
+    mode (tests/test_oracle_tracer.py shows that the oracle's two modes differ only in the ring around the cavity edge)."""
+    from fesom2_b200 import api
+    from oracle import binding as ob
+    hm = util.build_model("cavity")
+    eng = api.TracerEngine(hm, **opts)
+    eng.push_step_state()
+    g_tr, g_tro = hm["tr_arr"].copy(), hm["tr_arr_old"].copy()
+    for _ in range(2):
+        eng.solve_tracers_ale(g_tr, g_tro)
+    eng.close()
+    assert np.isfinite(g_tr).all()
+    o1 = ob.TracerOracle(hm, fct_cavity_neutral=True, **opts)
+    for _ in range(2):
+        o1.step()
+    wet = util.wet_mask(hm)
+    for k in range(2):
+        assert util.rel_err(g_tr[k][wet], hm["tr_arr"][k][wet]) < TOL
+        assert util.rel_err(g_tro[k], hm["tr_arr_old"][k]) < TOL

@@ -7,7 +7,8 @@ from oracle import binding as ob
 from tests import util
 
 
-@pytest.mark.parametrize("name,kw", [("pi", {}), ("soufflet", {}), ("band", {}), ("pi", {"w_split": True, "w_max_cfl": 0.2})])
+@pytest.mark.parametrize("name,kw", [("pi", {}), ("soufflet", {}), ("band", {}), ("pi", {"w_split": True, "w_max_cfl": 0.2}),
+                                     ("cavity", {})])
 def test_constant_tracer_is_preserved(name, kw):
     hm = util.build_model(name, **kw)
     wet = util.wet_mask(hm)
@@ -163,3 +164,24 @@ def test_kpp_nonlocal_transport_redistributes_without_changing_the_column_conten
         cb = (hb["tr_arr"][k] * hb["hnode_new"] * hb["areasvol"][:, :nl - 1] * wet).sum(axis=1)
         assert np.abs(ca - cb).max() <= 1e-11 * np.abs(cb).max()
         assert util.rel_err(ha["tr_arr"][k][wet], hb["tr_arr"][k][wet]) > 1e-9            # but the profile did change
+
+
+def test_cavity_limiter_scratch_only_matters_at_the_cavity_edge():
+    """oce_tra_adv_fct a3 reads element scratch above an element's cavity top that a2 never wrote (oracle.h:
+    fct_cavity_neutral).  The two readings of that (zeros as allocated / neutral entries) may only differ at nodes whose
+    elements start at different levels and at their edge neighbours; both keep a constant tracer constant."""
+    from tests.test_gpu_tracer import cavity_ring
+    ha, hb = util.build_model("cavity"), util.build_model("cavity")
+    ob.TracerOracle(ha).step()
+    ob.TracerOracle(hb, fct_cavity_neutral=True).step()
+    wet = util.wet_mask(ha)
+    ring = cavity_ring(ha)
+    assert ring.sum() > 0 and (~ring).sum() > 0
+    for k in range(2):
+        far = wet & ~ring[:, None]
+        assert np.array_equal(ha["tr_arr"][k][far], hb["tr_arr"][k][far])
+    hc = util.build_model("cavity")
+    hc["tr_arr"][0] = np.where(wet, 7.0, 0.0)
+    hc["tr_arr_old"][0] = hc["tr_arr"][0]
+    ob.TracerOracle(hc, fct_cavity_neutral=True).step()
+    assert np.abs(hc["tr_arr"][0][wet] - 7.0).max() < 5e-14

@@ -47,6 +47,27 @@ def build_model(name="pi", dt=None, which_ale=None, w_split=False, w_max_cfl=1.0
         dt = 1800.0 if dt is None else dt
         which_ale = which_ale or "zstar"
         pc = True
+    elif name == "cavity":
+        # band mesh with an ice-shelf cavity patch ("a second run with a cavity patch"): elements
+        # inside a box get ulevels = 3 or 4 (neighbouring elements differ, so all five level ranges of
+        # oce_adv_tra_hor.F90:129-209 occur), nodes the minimum over their elements (find_levels_cavity).  linfs: under
+        # zstar the reference treats cavity nodes as linfs, which the host-side mirror of the ALE setup does not restate.
+        kw = dict(nlon=72, nlat=40, nl=24)
+        kw.update(mesh_kw)
+        m = synth.lonlat_band_mesh(**kw)
+        hm.set_global_mesh(m["lon"], m["lat"], m["tri"], m["zbar"], m["depth"], force_rotation=False, cyclic_deg=360.0)
+        tri = m["tri"] - 1
+        inb = (m["lat"] < -55) & (m["lon"] > 100) & (m["lon"] < 220)
+        ule, uln, nle = hm["ulevels"], hm["ulevels_nod2D"], hm["nlevels"]
+        cav = np.flatnonzero(inb[tri].all(axis=1) & (nle - 4 >= 4))
+        ule[cav] = np.where(np.arange(cav.size) % 2 == 0, 4, 3)
+        un = np.full(m["lon"].size, 10 ** 6)
+        for k in range(3):
+            np.minimum.at(un, tri[:, k], ule)
+        uln[:] = un
+        dt = 1800.0 if dt is None else dt
+        which_ale = which_ale or "linfs"
+        pc = True
     else:
         raise ValueError(name)
     hm.derive()
