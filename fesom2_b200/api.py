@@ -20,7 +20,7 @@ LIM = {"FCT": 0, "NONE": 1}
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
-           "fb200_push_tracers", "fb200_set_clim", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema",
+           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_push_tracers", "fb200_set_clim", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
@@ -205,6 +205,22 @@ class TracerEngine:
         self.L.fb200_push_kpp_nonlocal(_i(int(enable)), _p(gT), _p(gS), _p(b2), _p(b3), _d(ref_sss), _i(int(ref_sss_local)))
         _check(self.L)
 
+    def ale_init(self):
+        """device-side compute_hbar_ale / vert_vel_ale / update_thickness_ale: hand over the current surface elevation"""
+        hm = self.hm
+        self.L.fb200_ale_init(_i(hm.ipar("which_ale")), _d(hm.par("w_max_cfl")), _p(hm.arr("hbar")))
+        _check(self.L)
+
+    def ale_step_begin(self):
+        """H2D UV + water_flux; hbar, ssh_rhs_old, dhe land in the host model's arrays"""
+        a = self.hm.arr
+        self.L.fb200_ale_step_begin(_p(a("UV")), _p(a("water_flux")), _p(a("hbar")), _p(a("ssh_rhs_old")), _p(a("dhe")))
+        _check(self.L)
+
+    def ale_step_end(self):
+        self.L.fb200_ale_step_end()
+        _check(self.L)
+
     def extrema(self, tr_num):
         """(min, max) of the resident tracer tr_num (1-based) over own wet cells"""
         lo, hi = C.c_double(), C.c_double()
@@ -249,7 +265,9 @@ class TracerEngine:
             shape = (hm.ipar("myDim_edge2D"), nl - 1)
         elif name in ("tr_xy_x", "tr_xy_y"):
             shape = (hm.ipar("myDim_elem2D") + hm.ipar("eDim_elem2D") + hm.ipar("eXDim_elem2D"), nl - 1)
-        elif name == "adf_v":
+        elif name == "helem":
+            shape = (hm.ipar("myDim_elem2D") + hm.ipar("eDim_elem2D") + hm.ipar("eXDim_elem2D"), nl - 1)
+        elif name in ("adf_v", "Wvel", "Wvel_e", "Wvel_i", "zbar_3d_n"):
             shape = (N, nl)
         else:
             shape = (N, nl - 1)

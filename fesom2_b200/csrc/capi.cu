@@ -324,7 +324,7 @@ void fb200_debug_fetch(const char* name, double* out) {
     if (s == "ttfAB") { f = c.Told.p; }
     else f = tracer_debug_field(c, name, &kind, &ncomp, &comp);
     if (!f) { fb_set_error(37, "fb200_debug_fetch: unknown field " + s); return; }
-    if (s == "adf_v") lev = c.nl;
+    if (s == "adf_v" || kind == 3) lev = c.nl;
     if (kind == 1) cnt = c.myEd;
     if (kind == 2) cnt = c.Eall;
     ctx_pull_node_field(c, f, lev, cnt, out, ncomp, comp);

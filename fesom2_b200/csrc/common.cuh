@@ -108,6 +108,9 @@ struct TracerCtx {
     DevBuf<double2> UV;             // (u, v) per element-level, tiled
     DevBuf<double> helem, W, We, Wi, hnode, hnode_new, Z3, zbar3, Kv, Ki, sl1, sl2, sl3, sw3d;
     DevBuf<double> heat_flux, water_flux, virtual_salt, relax_salt, real_salt_flux;   // (N)
+    // device-side ALE producers (fb200_ale_*): surface elevation, its right-hand side, element thickness change, edge sums
+    DevBuf<double> hbar, hbar_old, ssh_rhs_old, dhe, esum, CFL;
+    int which_ale = -1; double w_max_cfl = 1.0;
     DevBuf<double> kgT, kgS, kb2, kb3;          // KPP non-local transport: ghats / kpp_nonlcltransp{T,S}, blmc(:,:,2:3) (nl, N) tiled
     DevBuf<double> relax2clim, Tclim, Sclim;   // climatology relaxation: (N), tiled, tiled (fb200_set_clim)
     // tracers, tiled: [ntr] fields each

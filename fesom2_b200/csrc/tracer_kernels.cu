@@ -1077,6 +1077,14 @@ const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind, int*
     if (s == "adf_h") { *kind = 1; return c.adf_h.p; }
     if (s == "tr_xy_x") { *kind = 2; *ncomp = 2; return (const double*)c.txy.p; }
     if (s == "tr_xy_y") { *kind = 2; *ncomp = 2; *comp = 1; return (const double*)c.txy.p; }
+    if (s == "helem") { *kind = 2; return c.helem.p; }
+    if (s == "hnode") return c.hnode.p;
+    if (s == "hnode_new") return c.hnode_new.p;
+    if (s == "Z_3d_n") return c.Z3.p;
+    if (s == "Wvel") { *kind = 3; return c.W.p; }                  // kind 3: node field with nl levels
+    if (s == "Wvel_e") { *kind = 3; return c.We.p; }
+    if (s == "Wvel_i") { *kind = 3; return c.Wi.p; }
+    if (s == "zbar_3d_n") { *kind = 3; return c.zbar3.p; }
     return nullptr;
 }
 
@@ -1114,3 +1122,257 @@ extern "C" void fb200_selftest_div(long long* n, long long* mismatches) {
     cudaFree(d);
     *mismatches = (long long)h;
 }
+
+// ===================================================================================================
+// Device-side producers of the tracer step's inputs: compute_hbar_ale (oce_ale.F90:1585-1676),
+// vert_vel_ale (:1692-2204, linfs / plain zlevel / zstar) and update_thickness_ale (:800-993), restated after the
+// host-side mirror fesom2_b200/host/ale.cpp, which the GPU tests compare them with bit for bit.  With them resident the
+// host sends UV (after update_vel) and the surface fluxes only; Wvel*, hnode_new, helem, hnode, zbar_3d_n and Z_3d_n never
+// cross PCIe.  Edge loops become gathers in ascending edge id per node (ne_slot order), like the tracer kernels.
+// Single partition only for now (the reference exchanges ssh_rhs_old, hbar, Wvel, hnode_new between the steps).
+__device__ __forceinline__ int node_of_base(int base, int nlp) { return (base / (nlp * TILE)) * TILE + base % (nlp * TILE); }
+
+// per edge: c1 + c2 of compute_hbar_ale (:1612-1640), the transport through the edge's two segments summed over the column
+__global__ void LB(128) k_ale_edge_sum(KP p, double* __restrict__ esum) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= p.myEd) return;
+    const EdgeRec r = p.edge[e];
+    double c1 = 0.0, c2 = 0.0;
+    for (int nz = 1; nz <= p.nl - 1; nz++)
+        if ((r.m1 >> nz) & 1ull) { const double2 uv = AT(p.UV, r.be1, nz); c1 = c1 + (uv.y * r.dX1 - uv.x * r.dY1) * AT(p.helem, r.be1, nz); }
+    if (r.be2 >= 0)
+        for (int nz = 1; nz <= p.nl - 1; nz++)
+            if ((r.m2 >> nz) & 1ull) { const double2 uv = AT(p.UV, r.be2, nz); c2 = c2 - (uv.y * r.dX2 - uv.x * r.dY2) * AT(p.helem, r.be2, nz); }
+    esum[e] = c1 + c2;
+}
+// ssh_rhs_old, hbar_old = hbar, hbar += ssh_rhs_old * dt / areasvol(ulevel)   (:1641-1663)
+__global__ void LB(128) k_ale_hbar(KP p, const double* __restrict__ esum, double* __restrict__ sro, double* __restrict__ hbar,
+                                   double* __restrict__ hbar_old, int ale) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.N) return;
+    const double hb = hbar[n];
+    hbar_old[n] = hb;
+    if (n >= p.myN) { sro[n] = 0.0; return; }
+    double s = 0.0;
+    const int* slot = p.ne_slot + (size_t)(n >> 5) * p.maxdeg * TILE + (n & 31);
+    for (int j = 0; j < p.maxdeg; j++) {
+        const int v = slot[j * TILE];
+        if (v < 0) break;
+        const double cc = esum[v >> 1];
+        s = (v & 1) ? s - cc : s + cc;
+    }
+    const int nzmin = p.n_lev[n] & 255;
+    const double asv = AT(p.areasvol, tbase(n, p.nlp), nzmin);
+    if (ale != 0) s = s - p.water_flux[n] * asv;
+    sro[n] = s;
+    hbar[n] = hb + s * p.dt / asv;
+}
+// dhe (:1665-1675)
+__global__ void LB(128) k_ale_dhe(KP p, const double* __restrict__ hbar, const double* __restrict__ hbar_old, double* __restrict__ dhe) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= p.myE) return;
+    if ((p.el_lev[e] & 255) > 1) { dhe[e] = 0.0; return; }
+    const int n1 = node_of_base(p.el_nb[e], p.nlp), n2 = node_of_base(p.el_nb[p.Eall + e], p.nlp), n3 = node_of_base(p.el_nb[2 * p.Eall + e], p.nlp);
+    dhe[e] = ((hbar[n1] - hbar_old[n1]) + (hbar[n2] - hbar_old[n2]) + (hbar[n3] - hbar_old[n3])) / 3.0;
+}
+// horizontal divergence per (node, level): the edge loop of vert_vel_ale (:1745-1790) as a gather; node-kernel mapping
+__global__ void __launch_bounds__(256, 4) k_ale_wdiv(KP p, double* __restrict__ W) {
+    const NodeCol c = node_col(p);
+    if (!c.valid) return;
+    int nz[LPT]; bool act[LPT]; double acc[LPT];
+    bool any = false;
+#pragma unroll
+    for (int q = 0; q < LPT; q++) {
+        nz[q] = blockIdx.y * (LPT * blockDim.y) + threadIdx.y + 1 + q * blockDim.y;
+        act[q] = nz[q] >= c.nzmin && nz[q] <= c.nzmax - 1;
+        any |= act[q];
+        acc[q] = 0.0;
+    }
+    if (!any) return;
+    const size_t sbase = (size_t)blockIdx.x * p.maxdeg * TILE + threadIdx.x;
+    const int ndeg = p.tile_deg[blockIdx.x];
+    for (int j = 0; j < ndeg; j++) {
+        const size_t k = sbase + (size_t)j * TILE;
+        const ulonglong2 m = p.ns_m[k];
+        if ((m.x | m.y) == 0ull) continue;
+        const int4 ni = p.ns_i[k];
+        const bool second = p.ns_p[k].mk & 1ull;
+        const double2 d1 = p.ns_d1[k], d2 = p.ns_d2[k];
+#pragma unroll
+        for (int q = 0; q < LPT; q++) {
+            if (!act[q]) continue;
+            if ((m.x >> nz[q]) & 1ull) {
+                const double2 uv = AT(p.UV, ni.y, nz[q]);
+                const double c1 = (uv.y * d1.x - uv.x * d1.y) * AT(p.helem, ni.y, nz[q]);
+                acc[q] = second ? acc[q] - c1 : acc[q] + c1;
+            }
+            if ((m.y >> nz[q]) & 1ull) {
+                const double2 uv = AT(p.UV, ni.z, nz[q]);
+                const double c2 = -(uv.y * d2.x - uv.x * d2.y) * AT(p.helem, ni.z, nz[q]);
+                acc[q] = second ? acc[q] - c2 : acc[q] + c2;
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < LPT; q++) if (act[q]) AT(W, c.b, nz[q]) = acc[q];
+}
+// column part of vert_vel_ale: bottom-up sum, division by the area, surface terms of zlevel / zstar with hnode_new, Courant
+// number and the explicit/implicit split (:1795-2204).  One thread per own column.
+__global__ void LB(128) k_ale_wcol(KP p, double* __restrict__ W, double* __restrict__ We, double* __restrict__ Wi, double* __restrict__ hnode_new,
+                                   double* __restrict__ CFL, const double* __restrict__ hbar, const double* __restrict__ hbar_old,
+                                   int ale, int w_split, double w_max_cfl) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.myN) return;
+    const int b = tbase(n, p.nlp);
+    const unsigned lv = p.n_lev[n];
+    const int nzmin = lv & 255, nln = (lv >> 8) & 255, nlmin = (lv >> 16) & 255;
+    for (int nz = nln - 1; nz >= nzmin; nz--) AT(W, b, nz) = AT(W, b, nz) + AT(W, b, nz + 1);
+    for (int nz = nzmin; nz <= nln - 1; nz++) AT(W, b, nz) = AT(W, b, nz) / AT(p.area, b, nz);
+    if (ale == 1) {
+        if (nzmin == 1) {
+            const double dh = hbar[n] - hbar_old[n];
+            AT(W, b, nzmin) = AT(W, b, nzmin) - dh / p.dt;
+            AT(hnode_new, b, nzmin) = AT(p.hnode, b, nzmin) + dh;
+        }
+        AT(W, b, nzmin) = AT(W, b, nzmin) - p.water_flux[n];
+    } else if (ale == 2) {
+        const int nzmax = nlmin - 1;
+        if (nzmin == 1) {
+            const double dd1 = AT(p.zbar3, b, nzmax);
+            double dd = AT(p.zbar3, b, nzmin) - dd1;
+            dd = (hbar[n] - hbar_old[n]) / dd;
+            const double dddt = dd / p.dt;
+            for (int nz = nzmin; nz <= nzmax - 1; nz++) {
+                AT(W, b, nz) = AT(W, b, nz) - (AT(p.zbar3, b, nz) - dd1) * dddt;
+                AT(hnode_new, b, nz) = AT(p.hnode, b, nz) + (AT(p.zbar3, b, nz) - AT(p.zbar3, b, nz + 1)) * dd;
+            }
+        }
+        AT(W, b, nzmin) = AT(W, b, nzmin) - p.water_flux[n];
+    }
+    if (!w_split) return;                              // We == W and Wi == 0 are not read without w_split
+    AT(CFL, b, 1) = 0.0;
+    for (int nz = nzmin; nz <= nln - 1; nz++) {
+        const double c1 = fabs(AT(W, b, nz) * p.dt / AT(hnode_new, b, nz));
+        const double c2 = fabs(AT(W, b, nz + 1) * p.dt / AT(hnode_new, b, nz));
+        AT(CFL, b, nz) = AT(CFL, b, nz) + c1;
+        AT(CFL, b, nz + 1) = c2;
+    }
+    for (int nz = nzmin; nz <= nln; nz++) {
+        double c1 = 1.0, c2 = 0.0;
+        const double cfl = AT(CFL, b, nz);
+        if (cfl > w_max_cfl) {
+            const double dd = omax(cfl - w_max_cfl, 0.0) / omax(w_max_cfl, 1.e-12);
+            c1 = 1.0 / (1.0 + dd); c2 = dd / (1.0 + dd);
+        }
+        AT(We, b, nz) = c1 * AT(W, b, nz);
+        AT(Wi, b, nz) = c2 * AT(W, b, nz);
+    }
+}
+// update_thickness_ale, node part (:905-970): hnode = hnode_new, zbar_3d_n and Z_3d_n rebuilt from below
+__global__ void LB(128) k_ale_thick(KP p, double* __restrict__ hnode, double* __restrict__ zbar3, double* __restrict__ Z3, int ale) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.N) return;
+    const int b = tbase(n, p.nlp);
+    const unsigned lv = p.n_lev[n];
+    const int uln = lv & 255, nlmin = (lv >> 16) & 255, ulmax = (lv >> 24) & 255;
+    if (ale == 1) {
+        const int nz = ulmax;
+        if (nz > 1) return;
+        const double hn = AT(p.hnode_new, b, nz);
+        AT(hnode, b, nz) = hn;
+        AT(zbar3, b, nz) = AT(zbar3, b, nz + 1) + hn;
+        AT(Z3, b, nz) = AT(zbar3, b, nz + 1) + hn / 2.0;
+    } else if (ale == 2) {
+        if (uln > 1) return;
+        for (int nz = nlmin - 2; nz >= uln; nz--) {
+            const double hn = AT(p.hnode_new, b, nz);
+            AT(hnode, b, nz) = hn;
+            AT(zbar3, b, nz) = AT(zbar3, b, nz + 1) + hn;
+            AT(Z3, b, nz) = AT(zbar3, b, nz + 1) + hn / 2.0;
+        }
+    }
+}
+// update_thickness_ale, element part (:972-990)
+__global__ void LB(128) k_ale_helem(KP p, double* __restrict__ helem, int ale) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= p.myE) return;
+    const unsigned lv = p.el_lev[e];
+    const int nu = lv & 255, nlm = (lv >> 8) & 255;
+    if (nu > 1) return;
+    const int b1 = p.el_nb[e], b2 = p.el_nb[p.Eall + e], b3 = p.el_nb[2 * p.Eall + e], be = tbase(e, p.nlp);
+    if (ale == 1) AT(helem, be, nu) = (AT(p.hnode_new, b1, nu) + AT(p.hnode_new, b2, nu) + AT(p.hnode_new, b3, nu)) / 3.0;
+    else if (ale == 2)
+        for (int nz = nu; nz <= nlm - 1; nz++) AT(helem, be, nz) = (AT(p.hnode, b1, nz) + AT(p.hnode, b2, nz) + AT(p.hnode, b3, nz)) / 3.0;
+}
+
+static bool ale_ready(TracerCtx& c, const char* who) {
+    if (!fb_ok()) return false;
+    if (!c.committed || c.which_ale < 0) { fb_set_error(28, std::string(who) + ": fb200_init_commit / fb200_ale_init missing"); return false; }
+    if (comm_nranks() > 1) { fb_set_error(29, std::string(who) + ": the device-side ALE producers run on a single partition only"); return false; }
+    return true;
+}
+
+extern "C" {
+
+// which_ale: 0 linfs, 1 zlevel, 2 zstar (oce_ale.F90:82-795 sets the thicknesses up on the host; push them once with
+// fb200_push_step_state).  hbar(N) = the current surface elevation.
+void fb200_ale_init(int* which_ale, double* w_max_cfl, double* hbar) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(28, "fb200_ale_init before fb200_init_commit"); return; }
+    if (*which_ale < 0 || *which_ale > 2) { fb_set_error(28, "fb200_ale_init: which_ale must be 0 (linfs), 1 (zlevel) or 2 (zstar)"); return; }
+    fb_copy_sync();
+    c.stream = fb_stream();
+    c.which_ale = *which_ale; c.w_max_cfl = *w_max_cfl;
+    if (!c.hbar.p) {
+        c.hbar.alloc(c.N); c.hbar_old.alloc(c.N); c.ssh_rhs_old.alloc(c.N); c.dhe.alloc(c.myE); c.esum.alloc(c.myEd);
+        if (c.opt.w_split) c.CFL.alloc((size_t)c.Ntiles * c.nlp * TILE);
+    }
+    CUDA_CHECK(cudaMemcpyAsync(c.hbar.p, hbar, (size_t)c.N * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaMemcpyAsync(c.hbar_old.p, hbar, (size_t)c.N * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));
+}
+
+// compute_hbar_ale + vert_vel_ale on the device from the velocity the host has just updated (update_vel) and the
+// freshwater flux: H2D UV(2,nl-1,elems) and water_flux(N); resident afterwards: Wvel, Wvel_e, Wvel_i, hnode_new; back to the
+// host (it needs them for the next SSH right-hand side and stiffness update): hbar(N), ssh_rhs_old(N), dhe(myDim_elem2D).
+void fb200_ale_step_begin(double* UV, double* water_flux, double* hbar_out, double* ssh_rhs_old_out, double* dhe_out) {
+    TracerCtx& c = tctx();
+    if (!ale_ready(c, "fb200_ale_step_begin")) return;
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    const int L = c.nl - 1;
+    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 0, 2, 0);
+    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 1, 2, 1);
+    CUDA_CHECK(cudaMemcpyAsync(c.water_flux.p, water_flux, (size_t)c.N * sizeof(double), cudaMemcpyHostToDevice, st));
+    KP p = make_kp(c, 0);
+    const int ale = c.which_ale;
+#define KL(name, ...) do { ProfScope ps_(name, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
+    KL("k_ale_edge_sum", k_ale_edge_sum<<<(c.myEd + 127) / 128, 128, 0, st>>>(p, c.esum.p));
+    KL("k_ale_hbar", k_ale_hbar<<<(c.N + 127) / 128, 128, 0, st>>>(p, c.esum.p, c.ssh_rhs_old.p, c.hbar.p, c.hbar_old.p, ale));
+    KL("k_ale_dhe", k_ale_dhe<<<(c.myE + 127) / 128, 128, 0, st>>>(p, c.hbar.p, c.hbar_old.p, c.dhe.p));
+    CUDA_CHECK(cudaMemsetAsync(c.W.p, 0, c.W.n * sizeof(double), st));
+    const int nchunk = (c.nl - 1 + LPT * 8 - 1) / (LPT * 8);
+    KL("k_ale_wdiv", k_ale_wdiv<<<dim3(c.myNtiles, nchunk), dim3(TILE, 8), 0, st>>>(p, c.W.p));
+    KL("k_ale_wcol", k_ale_wcol<<<(c.myN + 127) / 128, 128, 0, st>>>(p, c.W.p, c.We.p, c.Wi.p, c.hnode_new.p, c.CFL.p, c.hbar.p, c.hbar_old.p,
+                                                                   ale, c.opt.w_split, c.w_max_cfl));
+    CUDA_CHECK(cudaMemcpyAsync(hbar_out, c.hbar.p, (size_t)c.N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(ssh_rhs_old_out, c.ssh_rhs_old.p, (size_t)c.N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(dhe_out, c.dhe.p, (size_t)c.myE * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+}
+
+// update_thickness_ale on the device, after the tracer step: hnode, zbar_3d_n, Z_3d_n, helem for the next step
+void fb200_ale_step_end(void) {
+    TracerCtx& c = tctx();
+    if (!ale_ready(c, "fb200_ale_step_end")) return;
+    cudaStream_t st = c.stream = fb_stream();
+    KP p = make_kp(c, 0);
+    const int ale = c.which_ale;
+    if (ale == 0) return;                              // linfs: the thicknesses never change
+    KL("k_ale_thick", k_ale_thick<<<(c.N + 127) / 128, 128, 0, st>>>(p, c.hnode.p, c.zbar3.p, c.Z3.p, ale));
+    KL("k_ale_helem", k_ale_helem<<<(c.myE + 127) / 128, 128, 0, st>>>(p, c.helem.p, ale));
+#undef KL
+    CUDA_CHECK(cudaStreamSynchronize(st));
+}
+
+}  // extern "C"

@@ -137,6 +137,15 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old);   /* push + so
  * fb200_push_tracers) and returns tr_arr to the host; tr_arr_old stays on the device (its only reader is
  * init_tracers_AB, src/oce_tracer_mod.F90:64).  The copy of tracer k overlaps the kernels of tracer k+1. */
 void fb200_solve_tracers_ale_resident(double* tr_arr_out);
+/* Device-side producers of the tracer step's inputs (single partition): compute_hbar_ale (src/oce_ale.F90:1585-1676),
+ * vert_vel_ale (:1692-2204; linfs, plain zlevel, zstar) and update_thickness_ale (:800-993).  With them the thicknesses,
+ * level depths and vertical velocities stay resident; per step the host sends UV (after update_vel) and water_flux and
+ * receives hbar(N), ssh_rhs_old(N), dhe(myDim_elem2D).  Call order per step: fb200_ale_step_begin, [fb200_push_state_early
+ * for Kv and the surface fluxes], fb200_solve_tracers_ale_resident, fb200_ale_step_end.  Once: fb200_push_step_state with
+ * the initial thicknesses, then fb200_ale_init(which_ale 0 linfs | 1 zlevel | 2 zstar, w_max_cfl, hbar). */
+void fb200_ale_init(int* which_ale, double* w_max_cfl, double* hbar);
+void fb200_ale_step_begin(double* UV, double* water_flux, double* hbar_out, double* ssh_rhs_old_out, double* dhe_out);
+void fb200_ale_step_end(void);
 /* min and max of the device-resident tracer *tr_num (1-based) over this partition's own wet cells: what check_blowup and
  * the extrema lines of write_step_info (src/write_step_info.F90:220-504) test; lets a host that keeps the tracers resident
  * monitor them without pulling the fields (combine the ranks with MPI_Allreduce as the reference does) */
