@@ -99,6 +99,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--block", type=int, default=16, help="block-Jacobi block size of the SSH preconditioner (--pc bj)")
+    ap.add_argument("--e2e-ale", action="store_true", help="also time the end-to-end step with the device-side ALE producers "
+                    "(fb200_ale_step_begin/_end: only UV, Kv and the surface fluxes cross PCIe); single GPU")
     ap.add_argument("--pc", default="amg", choices=["amg", "bj"], help="SSH preconditioner: aggregation multigrid or block-Jacobi")
     return ap.parse_args()
 
@@ -345,9 +347,38 @@ def run_b200(args):
         b.record(stream)
         barrier()
         e2e_ms = a.elapsed_time(b) / ksteps
+        e2e_ale = None
+        if args.e2e_ale and world == 1:
+            # the same step with compute_hbar_ale / vert_vel_ale / update_thickness_ale on the device: per step the host
+            # sends UV (after update_vel), Kv and the surface fluxes and receives tr_arr, hbar, ssh_rhs_old, dhe, d_eta
+            pinned += pin([hm.arr("hbar"), hm.arr("ssh_rhs_old"), hm.arr("dhe")])
+            eng.push_step_state()
+            eng.push_tracers()
+            eng.ale_init()
+
+            def e2e_ale_step():
+                sol[:] = 0.0
+                eng.push_state_early(hnode_resident=True, ki_resident=True, depths_resident=True)    # Kv + surface fluxes, overlaps psolve
+                solver.solve(new_values=1, sol=sol)
+                eng.ale_step_begin()                                # H2D UV, water_flux; hbar/Wvel/hnode_new on the device; D2H hbar, ssh_rhs_old, dhe
+                eng.solve_tracers_ale_resident(tr_h)
+                eng.ale_step_end()                                  # hnode, zbar_3d_n, Z_3d_n, helem for the next step
+
+            e2e_ale_step()
+            barrier()
+            a2, b2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a2.record(stream)
+            for _ in range(ksteps):
+                e2e_ale_step()
+            b2.record(stream)
+            barrier()
+            small = sum(hm.arr(nm).nbytes for nm in ("heat_flux", "water_flux", "virtual_salt", "relax_salt", "real_salt_flux"))
+            e2e_ale = {"ms_per_step": a2.elapsed_time(b2) / ksteps, "steps": ksteps,
+                       "h2d": hm.arr("UV").nbytes + hm.arr("water_flux").nbytes + hm.arr("Kv").nbytes + small + hm.arr("ssh_values").nbytes + 2 * 8 * n_own,
+                       "d2h": hm.arr("tr_arr").nbytes + hm.arr("hbar").nbytes + hm.arr("ssh_rhs_old").nbytes + hm.arr("dhe").nbytes + 8 * n_own}
         unpin(pinned)
         ssh_pinned = []
-        e2e = {"ms_per_step": e2e_ms, "steps": ksteps, "h2d": h2d, "d2h": d2h, "pinned_arrays": len(pinned)}
+        e2e = {"ms_per_step": e2e_ms, "steps": ksteps, "h2d": h2d, "d2h": d2h, "pinned_arrays": len(pinned), "ale": e2e_ale}
     unpin(ssh_pinned)
 
     # ---- max over ranks
@@ -531,6 +562,11 @@ def main():
         line["e2e"] = {"value": r["units_all"] / (r["e2e_ms"] * 1e-3), "unit": UNIT, "ms_per_step": r["e2e_ms"],
                        "h2d_bytes_per_step": int(r["e2e"]["h2d"]), "d2h_bytes_per_step": int(r["e2e"]["d2h"]),
                        "steps": r["e2e"]["steps"], "pinned_arrays": r["e2e"]["pinned_arrays"]}
+        if r["e2e"].get("ale"):
+            ea = r["e2e"]["ale"]
+            line["e2e_device_producers"] = {"value": r["units_all"] / (ea["ms_per_step"] * 1e-3), "unit": UNIT, "ms_per_step": ea["ms_per_step"],
+                                            "h2d_bytes_per_step": int(ea["h2d"]), "d2h_bytes_per_step": int(ea["d2h"]), "steps": ea["steps"],
+                                            "what": "compute_hbar_ale, vert_vel_ale, update_thickness_ale on the device (fb200_ale_*): UV, Kv and the surface fluxes in; tr_arr, hbar, ssh_rhs_old, dhe, d_eta out"}
     if r["world"] == 1 and not args.no_cpu_baseline:
         cb, _ = cpu_reference(args, 2, 0)
         line["cpu_baseline"] = cb

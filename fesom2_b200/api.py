@@ -176,13 +176,14 @@ class TracerEngine:
                                      _p(a("relax_salt")), _p(a("real_salt_flux")), _p(a("sw_3d")))
         _check(self.L)
 
-    def push_state_early(self, hnode_resident=False, ki_resident=False):
+    def push_state_early(self, hnode_resident=False, ki_resident=False, depths_resident=False):
         """the half of the step state that exists before solve_ssh_ale; returns at once, the copies overlap psolve.
         hnode_resident: pass NULL for hnode (the library's hnode_new of the previous step is the old thickness);
         ki_resident: pass NULL for Ki (unchanged since the last push)"""
         a = self.hm.arr
         null = C.c_void_p(None)
-        self.L.fb200_push_state_early(null if hnode_resident else _p(a("hnode")), _p(a("Z_3d_n")), _p(a("zbar_3d_n")), _p(a("Kv")),
+        self.L.fb200_push_state_early(null if hnode_resident else _p(a("hnode")), null if depths_resident else _p(a("Z_3d_n")),
+                                      null if depths_resident else _p(a("zbar_3d_n")), _p(a("Kv")),
                                       null if ki_resident else _p(a("Ki")),
                                       _p(a("slope_tapered")), _p(a("heat_flux")), _p(a("water_flux")), _p(a("virtual_salt")),
                                       _p(a("relax_salt")), _p(a("real_salt_flux")), _p(a("sw_3d")))

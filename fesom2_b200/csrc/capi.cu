@@ -109,9 +109,10 @@ static void push_early_on(TracerCtx& c, cudaStream_t s, double* hnode, double* Z
     // previous step (update_thickness_ale assigns exactly that, oce_ale.F90:924,936,967), Ki keeps its resident copy (it is
     // set once in oce_setup_step.F90:330 and only rewritten per step under Fer_GM / Redi, oce_fer_gm.F90:243-333)
     if (hnode) ctx_push_node_field(c, hnode, L, N, c.hnode.p);
-    else CUDA_CHECK(cudaMemcpyAsync(c.hnode.p, c.hnode_new.p, c.hnode.n * sizeof(double), cudaMemcpyDeviceToDevice, s));
-    ctx_push_node_field(c, Z_3d_n, L, N, c.Z3.p);
-    ctx_push_node_field(c, zbar_3d_n, nl, N, c.zbar3.p);
+    else if (c.which_ale < 0) CUDA_CHECK(cudaMemcpyAsync(c.hnode.p, c.hnode_new.p, c.hnode.n * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    // (with the device-side ALE producers, fb200_ale_step_end has already updated hnode)
+    if (Z_3d_n) ctx_push_node_field(c, Z_3d_n, L, N, c.Z3.p);          // NULL: resident (kept current by fb200_ale_step_end)
+    if (zbar_3d_n) ctx_push_node_field(c, zbar_3d_n, nl, N, c.zbar3.p);
     ctx_push_node_field(c, Kv, nl, N, c.Kv.p);
     if (Ki) ctx_push_node_field(c, Ki, L, N, c.Ki.p);
     if (c.opt.Redi) {

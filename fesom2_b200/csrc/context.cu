@@ -297,6 +297,7 @@ void ctx_commit(TracerCtx& c) {
 
 void ctx_release(TracerCtx& c) {
     if (c.stream) { cudaStreamSynchronize(c.stream); }
+    c.which_ale = -1;                                   // the device-side ALE producers need a new fb200_ale_init
     for (DevBuf<double>* b : {&c.area, &c.areasvol, &c.W, &c.We, &c.Wi, &c.hnode, &c.hnode_new, &c.Z3, &c.zbar3, &c.Kv, &c.Ki,
                               &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar,
                               &c.helem, &c.adf_h, &c.eflx, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,

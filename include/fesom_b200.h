@@ -113,7 +113,9 @@ void fb200_push_step_state(double* UV, double* Wvel, double* Wvel_e, double* Wve
 /* Two of the early arrays may be passed as NULL (Fortran: c_null_ptr through a type(c_ptr), value dummy) = "the host has
  * not changed it since the library last saw it": hnode = NULL makes the resident hnode_new of the previous step the old
  * thickness (what update_thickness_ale assigns, src/oce_ale.F90:924,936,967); Ki = NULL keeps the resident copy (Ki is set
- * once in src/oce_setup_step.F90:330 and rewritten per step only under Fer_GM/Redi, src/oce_fer_gm.F90:243-333). */
+ * once in src/oce_setup_step.F90:330 and rewritten per step only under Fer_GM/Redi, src/oce_fer_gm.F90:243-333).
+ * Z_3d_n / zbar_3d_n = NULL keep the resident copies, which fb200_ale_step_end maintains (with fb200_ale_init, hnode = NULL
+ * likewise means the copy fb200_ale_step_end has just updated). */
 void fb200_push_state_early(double* hnode, double* Z_3d_n, double* zbar_3d_n, double* Kv, double* Ki, double* slope_tapered,
                             double* heat_flux, double* water_flux, double* virtual_salt, double* relax_salt,
                             double* real_salt_flux, double* sw_3d);
