@@ -189,10 +189,13 @@ void DevSell::upload(const HostCsr& m) {
     nrow = m.nrow;
     nslice = (nrow + 31) / 32;
     std::vector<int> sp(nslice + 1, 0);
+    long long total = 0;
     for (int s = 0; s < nslice; s++) {
         int w = 0;
         for (int i = s * 32; i < std::min(nrow, s * 32 + 32); i++) w = std::max(w, m.rp[i + 1] - m.rp[i]);
-        sp[s + 1] = sp[s] + w * 32;
+        total += (long long)w * 32;
+        if (total >= (1LL << 31)) { fb_set_error(48, "multigrid level too large for 32-bit sliced-ELL offsets"); return; }
+        sp[s + 1] = (int)total;
     }
     entries = (size_t)sp[nslice];
     std::vector<int> col(entries, 0);
