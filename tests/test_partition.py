@@ -68,7 +68,7 @@ def run_partitioned_oracle(hm, part, npes, opts=None, steps=1):
     return ranks, lms
 
 
-@pytest.mark.parametrize("name,npes,opts", [("pi", 2, {}), ("band", 3, {}), ("soufflet", 2, {"tra_adv_hor": "MUSCL"}), ("farclike", 4, {})])
+@pytest.mark.parametrize("name,npes,opts", [("pi", 2, {}), ("band", 3, {}), ("soufflet", 2, {"tra_adv_hor": "MUSCL"}), ("farclike", 4, {}), ("cavity", 3, {})])
 def test_partitioned_oracle_equals_undivided_oracle(name, npes, opts):
     hm = util.build_model(name)
     part = P.contiguous_partition(hm, npes)
