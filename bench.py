@@ -348,7 +348,7 @@ def run_b200(args):
         barrier()
         e2e_ms = a.elapsed_time(b) / ksteps
         e2e_ale = None
-        if args.e2e_ale and world == 1:
+        if args.e2e_ale:
             # the same step with compute_hbar_ale / vert_vel_ale / update_thickness_ale on the device: per step the host
             # sends UV (after update_vel), Kv and the surface fluxes and receives tr_arr, hbar, ssh_rhs_old, dhe, d_eta
             pinned += pin([hm.arr("hbar"), hm.arr("ssh_rhs_old"), hm.arr("dhe")])
@@ -373,7 +373,12 @@ def run_b200(args):
             b2.record(stream)
             barrier()
             small = sum(hm.arr(nm).nbytes for nm in ("heat_flux", "water_flux", "virtual_salt", "relax_salt", "real_salt_flux"))
-            e2e_ale = {"ms_per_step": a2.elapsed_time(b2) / ksteps, "steps": ksteps,
+            ale_ms = a2.elapsed_time(b2) / ksteps
+            if dist is not None:                                    # max over ranks (the byte counts are rank 0's, like e2e's)
+                t_ = torch.tensor([ale_ms], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+                ale_ms = float(t_[0])
+            e2e_ale = {"ms_per_step": ale_ms, "steps": ksteps,
                        "h2d": hm.arr("UV").nbytes + hm.arr("water_flux").nbytes + hm.arr("Kv").nbytes + small + hm.arr("ssh_values").nbytes + 2 * 8 * n_own,
                        "d2h": hm.arr("tr_arr").nbytes + hm.arr("hbar").nbytes + hm.arr("ssh_rhs_old").nbytes + hm.arr("dhe").nbytes + 8 * n_own}
         unpin(pinned)

@@ -1129,7 +1129,10 @@ extern "C" void fb200_selftest_div(long long* n, long long* mismatches) {
 // host-side mirror fesom2_b200/host/ale.cpp, which the GPU tests compare them with bit for bit.  With them resident the
 // host sends UV (after update_vel) and the surface fluxes only; Wvel*, hnode_new, helem, hnode, zbar_3d_n and Z_3d_n never
 // cross PCIe.  Edge loops become gathers in ascending edge id per node (ne_slot order), like the tracer kernels.
-// Single partition only for now (the reference exchanges ssh_rhs_old, hbar, Wvel, hnode_new between the steps).
+// With several partitions the reference's four exchanges (ssh_rhs_old :1654, hbar :1663, Wvel and hnode_new :2135-2136) run
+// over NCCL between the kernels; Wvel_e / Wvel_i of the halo nodes, which the reference recomputes from the exchanged
+// Wvel and hnode_new (:2140-2203, same arithmetic on the same numbers), are exchanged as well.  Under linfs the reference
+// leaves partial edge sums in the halo entries of ssh_rhs_old (never read); here they are zero.
 __device__ __forceinline__ int node_of_base(int base, int nlp) { return (base / (nlp * TILE)) * TILE + base % (nlp * TILE); }
 
 // per edge: c1 + c2 of compute_hbar_ale (:1612-1640), the transport through the edge's two segments summed over the column
@@ -1308,7 +1311,7 @@ __global__ void LB(128) k_ale_helem(KP p, double* __restrict__ helem, int ale) {
 static bool ale_ready(TracerCtx& c, const char* who) {
     if (!fb_ok()) return false;
     if (!c.committed || c.which_ale < 0) { fb_set_error(28, std::string(who) + ": fb200_init_commit / fb200_ale_init missing"); return false; }
-    if (comm_nranks() > 1) { fb_set_error(29, std::string(who) + ": the device-side ALE producers run on a single partition only"); return false; }
+    if (comm_nranks() > 1 && !c.halo_nod) { fb_set_error(26, std::string(who) + ": more than one rank but fb200_init_halo was not called"); return false; }
     return true;
 }
 
@@ -1349,12 +1352,22 @@ void fb200_ale_step_begin(double* UV, double* water_flux, double* hbar_out, doub
 #define KL(name, ...) do { ProfScope ps_(name, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
     KL("k_ale_edge_sum", k_ale_edge_sum<<<(c.myEd + 127) / 128, 128, 0, st>>>(p, c.esum.p));
     KL("k_ale_hbar", k_ale_hbar<<<(c.N + 127) / 128, 128, 0, st>>>(p, c.esum.p, c.ssh_rhs_old.p, c.hbar.p, c.hbar_old.p, ale));
+    const bool multi = comm_nranks() > 1;
+    if (multi) {
+        if (ale != 0) halo_exchange_flat(*c.halo_nod, c.ssh_rhs_old.p, st);           // exchange_nod(ssh_rhs_old), :1654
+        halo_exchange_flat(*c.halo_nod, c.hbar.p, st);                                // exchange_nod(hbar), :1663
+    }
     KL("k_ale_dhe", k_ale_dhe<<<(c.myE + 127) / 128, 128, 0, st>>>(p, c.hbar.p, c.hbar_old.p, c.dhe.p));
     CUDA_CHECK(cudaMemsetAsync(c.W.p, 0, c.W.n * sizeof(double), st));
     const int nchunk = (c.nl - 1 + LPT * 8 - 1) / (LPT * 8);
     KL("k_ale_wdiv", k_ale_wdiv<<<dim3(c.myNtiles, nchunk), dim3(TILE, 8), 0, st>>>(p, c.W.p));
     KL("k_ale_wcol", k_ale_wcol<<<(c.myN + 127) / 128, 128, 0, st>>>(p, c.W.p, c.We.p, c.Wi.p, c.hnode_new.p, c.CFL.p, c.hbar.p, c.hbar_old.p,
                                                                    ale, c.opt.w_split, c.w_max_cfl));
+    if (multi) {
+        halo_exchange_tiled(*c.halo_nod, c.W.p, c.nlp, 1, st);                        // exchange_nod(Wvel), :2135
+        if (ale != 0) halo_exchange_tiled(*c.halo_nod, c.hnode_new.p, c.nlp, 1, st);  // exchange_nod(hnode_new), :2136
+        if (c.opt.w_split) { halo_exchange_tiled(*c.halo_nod, c.We.p, c.nlp, 1, st); halo_exchange_tiled(*c.halo_nod, c.Wi.p, c.nlp, 1, st); }
+    }
     CUDA_CHECK(cudaMemcpyAsync(hbar_out, c.hbar.p, (size_t)c.N * sizeof(double), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(ssh_rhs_old_out, c.ssh_rhs_old.p, (size_t)c.N * sizeof(double), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(dhe_out, c.dhe.p, (size_t)c.myE * sizeof(double), cudaMemcpyDeviceToHost, st));

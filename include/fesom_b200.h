@@ -139,7 +139,8 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old);   /* push + so
  * fb200_push_tracers) and returns tr_arr to the host; tr_arr_old stays on the device (its only reader is
  * init_tracers_AB, src/oce_tracer_mod.F90:64).  The copy of tracer k overlaps the kernels of tracer k+1. */
 void fb200_solve_tracers_ale_resident(double* tr_arr_out);
-/* Device-side producers of the tracer step's inputs (single partition): compute_hbar_ale (src/oce_ale.F90:1585-1676),
+/* Device-side producers of the tracer step's inputs (any number of partitions: with more than one the four exchanges
+ * of oce_ale.F90:1654,1663,2135-2136 run over NCCL, fb200_init_halo required): compute_hbar_ale (src/oce_ale.F90:1585-1676),
  * vert_vel_ale (:1692-2204; linfs, plain zlevel, zstar) and update_thickness_ale (:800-993).  With them the thicknesses,
  * level depths and vertical velocities stay resident; per step the host sends UV (after update_vel) and water_flux and
  * receives hbar(N), ssh_rhs_old(N), dhe(myDim_elem2D).  Call order per step: fb200_ale_step_begin, [fb200_push_state_early

@@ -12,6 +12,51 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def check_device_ale(name, rank, world, part_in):
+    """the device-side ALE producers (fb200_ale_step_begin / _end) on this rank's partition, with the reference's four
+    exchanges over NCCL, against the host-side mirror on the UNDIVIDED mesh: three coupled steps, own and halo entries bit
+    for bit; the tracers stepped on the device-produced state against the oracle on the undivided mesh."""
+    from fesom2_b200 import api, partition as P
+    from oracle import binding as ob
+    from tests import util
+    kw = dict(umax=0.05, water_flux=0.0 if name == "soufflet" else 2e-7)
+    A = util.build_model(name, **kw)                          # undivided: host mirror + oracle
+    G = util.build_model(name, **kw)                          # the same state, partitioned
+    part = part_in if part_in is not None else P.contiguous_partition(G, world)
+    r = P.build_partition(G, part, world)[rank]
+    lm = P.local_model(G, r, part)
+    nod, el = r.nod - 1, r.elem[:r.myDim_elem2D] - 1
+    myN = r.myDim_nod2D
+    o = ob.TracerOracle(A)
+    eng = api.TracerEngine(lm)
+    eng.push_step_state()
+    eng.push_tracers()
+    eng.ale_init()
+    out = np.zeros_like(lm["tr_arr"])
+    linfs = A.ipar("which_ale") == 0
+    bad = []
+    for s in range(3):
+        if s > 0:
+            util.advance_ale_state(A, first=False)
+            eng.ale_step_begin()
+            if not np.array_equal(lm["hbar"], A["hbar"][nod]): bad.append((s, "hbar"))
+            sro_n = slice(0, myN) if linfs else slice(None)   # linfs: the reference leaves partial sums in the halo entries
+            if not np.array_equal(lm["ssh_rhs_old"][sro_n], A["ssh_rhs_old"][nod][sro_n]): bad.append((s, "ssh_rhs_old"))
+            if not np.array_equal(lm["dhe"][:r.myDim_elem2D], A["dhe"][el]): bad.append((s, "dhe"))
+            for nm in ("Wvel", "hnode_new"):
+                if not np.array_equal(eng.debug(nm), A[nm][nod]): bad.append((s, nm))
+        o.step()
+        eng.solve_tracers_ale_resident(out)
+        if not np.array_equal(out, A["tr_arr"][:, nod]): bad.append((s, "tr_arr"))
+        A.update_thickness()
+        eng.ale_step_end()
+        for nm in ("hnode", "Z_3d_n", "zbar_3d_n"):
+            if not np.array_equal(eng.debug(nm), A[nm][nod]): bad.append((s, nm))
+        if not np.array_equal(eng.debug("helem")[:r.myDim_elem2D], A["helem"][el]): bad.append((s, "helem"))
+    eng.close()
+    return "ok" if not bad else repr(bad)
+
+
 def main():
     import torch
     import torch.distributed as dist
@@ -27,8 +72,10 @@ def main():
     hm.compute_ssh_rhs()
     if name == "pi" and world == 2:
         part = np.load(os.path.join(util.GOLD, "pi_dist2.npz"))["part"]      # the reference's own METIS partition
+        part_fixed = part
     else:
         part = P.contiguous_partition(hm, world)
+        part_fixed = None
     ranks = P.build_partition(hm, part, world)
     r = ranks[rank]
     lm = P.local_model(hm, r, part)
@@ -40,6 +87,8 @@ def main():
     for _ in range(steps):
         eng.solve()
     eng.pull_tracers(tr, tro)
+    eng.close()
+    ale = check_device_ale(name, rank, world, part_fixed)
     # SSH solve on the partitioned system
     sol = np.zeros_like(lm["d_eta"])
     s = api.SSHSolver(lm, pc="bj")
@@ -65,17 +114,16 @@ def main():
     err_s = float(util.rel_err(sol[:r.myDim_nod2D], x_ref[own]))
     err_mg = float(util.rel_err(sol_mg[:r.myDim_nod2D], x_ref[own]))
     verdict = dict(rank=rank, own_bitexact=ok_own, halo_bitexact=ok_halo, tracer_maxabs=err_t, ssh_rel=err_s, its=its, its_ref=its_ref,
-                   res=res, ssh_rel_mg=err_mg, its_mg=its_mg, res_mg=res_mg, launches=int(api.lib().fb200_kernel_launches()))
+                   res=res, ssh_rel_mg=err_mg, its_mg=its_mg, res_mg=res_mg, ale=ale, launches=int(api.lib().fb200_kernel_launches()))
     allv = [None] * world
     dist.all_gather_object(allv, verdict)
-    eng.close()
     api.lib().psolver_final()
     api.comm_finalize()
     if rank == 0:
         for v in allv:
             print("MPCHECK", v)
         good = all(v["own_bitexact"] and v["halo_bitexact"] and v["ssh_rel"] < 1e-6 and v["res"] < 1e-10
-                   and v["ssh_rel_mg"] < 1e-6 and v["res_mg"] < 1e-10 for v in allv)
+                   and v["ssh_rel_mg"] < 1e-6 and v["res_mg"] < 1e-10 and v["ale"] == "ok" for v in allv)
         print("MPCHECK_RESULT", "PASS" if good else "FAIL")
     dist.destroy_process_group()
 

@@ -93,3 +93,46 @@ def test_reference_metis_partition_of_pi():
     for r, lm in zip(ranks, lms):
         own = r.nod[:r.myDim_nod2D] - 1
         assert np.array_equal(lm["tr_arr"][:, :r.myDim_nod2D], hm["tr_arr"][:, own])
+
+
+@pytest.mark.parametrize("name,npes,kw", [("pi", 2, {}), ("band", 3, {"water_flux": 2e-7}), ("band", 2, {"which_ale": "zlevel", "water_flux": 2e-7}),
+                                          ("soufflet", 2, {}), ("pi", 3, {"w_split": True, "w_max_cfl": 0.2, "umax": 0.5})])
+def test_partitioned_ale_producers_need_exactly_the_four_exchanges(name, npes, kw):
+    """compute_hbar_ale / vert_vel_ale / update_thickness_ale partition by partition with the exchanges the device path
+    issues (fb200_ale_step_begin: ssh_rhs_old, hbar, then Wvel, hnode_new and the split velocities) reproduce the
+    undivided run bit for bit on own AND halo entries over three coupled steps (oce_ale.F90:1654,1663,2135-2136)."""
+    kw = dict({"umax": 0.05}, **kw)
+    A, G = util.build_model(name, **kw), util.build_model(name, **kw)
+    part = P.contiguous_partition(G, npes)
+    ranks = P.build_partition(G, part, npes)
+    lms = [P.local_model(G, r, part) for r in ranks]
+    linfs = A.ipar("which_ale") == 0
+    for s in range(3):
+        A.compute_hbar()
+        A.vert_vel()
+        for lm in lms:
+            lm.compute_hbar()
+        if not linfs:
+            P.exchange_host(ranks, [lm["ssh_rhs_old"] for lm in lms], "nod")
+        P.exchange_host(ranks, [lm["hbar"] for lm in lms], "nod")
+        for lm, r in zip(lms, ranks):                       # dhe after the exchange, as compute_hbar_ale orders it (:1665-1675)
+            en = lm["elem2D_nodes"][:r.myDim_elem2D] - 1
+            d = lm["hbar"] - lm["hbar_old"]
+            lm["dhe"][:r.myDim_elem2D] = np.where(lm["ulevels"][:r.myDim_elem2D] > 1, 0.0, ((d[en[:, 0]] + d[en[:, 1]]) + d[en[:, 2]]) / 3.0)
+            lm.vert_vel()
+        for nm in ("Wvel", "hnode_new", "Wvel_e", "Wvel_i"):
+            P.exchange_host(ranks, [lm[nm] for lm in lms], "nod")
+        for lm, r in zip(lms, ranks):
+            nod, el = r.nod - 1, r.elem[:r.myDim_elem2D] - 1
+            sl = slice(0, r.myDim_nod2D) if linfs else slice(None)
+            assert np.array_equal(lm["ssh_rhs_old"][sl], A["ssh_rhs_old"][nod][sl]), s
+            assert np.array_equal(lm["dhe"][:r.myDim_elem2D], A["dhe"][el]), s
+            for nm in ("hbar", "hbar_old", "Wvel", "Wvel_e", "Wvel_i", "hnode_new"):
+                assert np.array_equal(lm[nm], A[nm][nod]), (s, nm)
+        A.update_thickness()
+        for lm, r in zip(lms, ranks):
+            lm.update_thickness()
+            nod, el = r.nod - 1, r.elem[:r.myDim_elem2D] - 1
+            for nm in ("hnode", "Z_3d_n", "zbar_3d_n"):
+                assert np.array_equal(lm[nm], A[nm][nod]), (s, nm)
+            assert np.array_equal(lm["helem"][:r.myDim_elem2D], A["helem"][el]), s
