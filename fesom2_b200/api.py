@@ -20,7 +20,7 @@ LIM = {"FCT": 0, "NONE": 1}
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
-           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_push_tracers", "fb200_set_clim", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema",
+           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_push_tracers", "fb200_set_clim", "fb200_set_zonal_relax", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
@@ -204,6 +204,14 @@ class TracerEngine:
     def push_kpp_nonlocal(self, gT, gS, b2, b3, ref_sss=34.7, ref_sss_local=False, enable=True):
         """KPP non-local transport arrays of this step, (N, nl) each (see fb200_push_kpp_nonlocal)"""
         self.L.fb200_push_kpp_nonlocal(_i(int(enable)), _p(gT), _p(gS), _p(b2), _p(b3), _d(ref_sss), _i(int(ref_sss_local)))
+        _check(self.L)
+
+    def set_zonal_relax(self, ztem, Tclim, lat0, dy, tau_inv, enable=True):
+        """relax_zonal_temp of the soufflet channel instead of relax_to_clim: ztem (nybins, nl-1), Tclim (N, nl-1)"""
+        self._zonal = (np.ascontiguousarray(ztem, dtype=np.float64), np.ascontiguousarray(Tclim, dtype=np.float64),
+                       np.ascontiguousarray(self.hm.arr("coord_nod2D"), dtype=np.float64))
+        self.L.fb200_set_zonal_relax(_i(int(enable)), _i(self._zonal[0].shape[0]), _d(lat0), _d(dy), _d(tau_inv), _p(self._zonal[2]),
+                                     _p(self._zonal[0]), _p(self._zonal[1]))
         _check(self.L)
 
     def ale_init(self):

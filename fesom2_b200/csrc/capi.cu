@@ -1,5 +1,6 @@
 // extern "C" entry points of the tracer path (include/fesom_b200.h).  Plain pointers and sizes only.
 #include "common.cuh"
+#include <cmath>
 #include "comm.cuh"
 #include "fesom_b200.h"
 #include <cstring>
@@ -187,6 +188,48 @@ void fb200_set_clim(double* clim_relax, double* relax2clim, double* Tclim, doubl
     CUDA_CHECK(cudaStreamSynchronize(c.stream));
 }
 
+// relax_zonal_temp of the soufflet channel (toy_channel_soufflet.F90:78-103), which solve_tracers_ale calls INSTEAD of
+// relax_to_clim when toy_ocean and which_toy == "soufflet" (oce_ale_tracer.F90:150-151).  ztem(nl-1, nybins) is the zonal-mean
+// temperature of compute_zonal_mean (:143-200; call again whenever the host refreshes it), coord_nod2D(2, N) the node
+// coordinates in radians, lat0 / dy / tau_inv the module's parameters (:19-24, :207), Tclim(nl-1, N) the restoring target.
+// The bin of a node and its interpolation weight (:86-96) are evaluated here on the host, once per call.
+void fb200_set_zonal_relax(int* enable, int* nybins, double* lat0, double* dy, double* tau_inv, double* coord_nod2D, double* ztem, double* Tclim) {
+    TracerCtx& c = tctx();
+    if (!c.committed) { fb_set_error(33, "fb200_set_zonal_relax before fb200_init_commit"); return; }
+    c.opt.relax_zonal = *enable != 0;
+    if (!c.opt.relax_zonal) return;
+    if (*nybins < 1 || !(*dy > 0.0)) { fb_set_error(33, "fb200_set_zonal_relax: nybins >= 1 and dy > 0 required"); c.opt.relax_zonal = 0; return; }
+    fb_copy_sync();
+    c.stream = fb_stream();
+    const int L = c.nl - 1;
+    std::vector<int2> bins(c.N);
+    std::vector<double> wgt(c.N);
+    for (int n = 0; n < c.N; n++) {
+        const double yy = coord_nod2D[2 * (size_t)n + 1] - *lat0;
+        double a = 0;
+        int nn = 1, nn1 = 1;
+        if (!(yy < *dy / 2)) {
+            nn = (int)floor(yy / *dy - 0.5) + 1;
+            nn1 = nn + 1;
+            if (nn1 > 100) nn1 = nn;                       // the reference's literal 100, not nybins
+            a = yy / *dy + 0.5 - nn;
+        }
+        if (nn < 1 || nn1 > *nybins) { fb_set_error(33, "fb200_set_zonal_relax: a node lies outside the nybins latitude bins"); c.opt.relax_zonal = 0; return; }
+        bins[n] = make_int2(nn, nn1);
+        wgt[n] = a;
+    }
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
+    if (!c.zon_nn.p) { c.zon_nn.alloc(c.N); c.zon_a.alloc(c.N); }
+    if (c.zon_ztem.n < (size_t)L * *nybins) c.zon_ztem.alloc((size_t)L * *nybins);
+    if (!c.Tclim.p) c.Tclim.alloc(nf);
+    CUDA_CHECK(cudaMemcpyAsync(c.zon_nn.p, bins.data(), (size_t)c.N * sizeof(int2), cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaMemcpyAsync(c.zon_a.p, wgt.data(), (size_t)c.N * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    CUDA_CHECK(cudaMemcpyAsync(c.zon_ztem.p, ztem, (size_t)L * *nybins * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+    ctx_push_node_field(c, Tclim, L, c.N, c.Tclim.p);
+    c.zon_fac = *tau_inv;
+    CUDA_CHECK(cudaStreamSynchronize(c.stream));            // bins / wgt are locals
+}
+
 // KPP non-local transport (use_kpp_nonlclflx, oce_ale_tracer.F90:688-781): per-step arrays of the mixing scheme.
 // fesom KPP (mix_scheme_nmb 1, 17): gT = gS = ghats, b2/b3 = blmc(:,:,2)/blmc(:,:,3); cvmix KPP (3, 37): gT/gS =
 // kpp_nonlcltranspT/S, b2/b3 = kpp_oblmixc(:,:,2)/(:,:,3).  *enable = 0 switches the term off.
@@ -270,9 +313,10 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
         tracer_step_tracer(c, tr);
         CUDA_CHECK(cudaEventRecord(g_ev_done[tr], comp));
     }
+    const bool late = c.opt.relax_zonal != 0;             // relax_zonal_temp touches tracer 1 on every later pass
     for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
         c.stream = copy;
-        CUDA_CHECK(cudaStreamWaitEvent(copy, g_ev_done[tr], 0));
+        CUDA_CHECK(cudaStreamWaitEvent(copy, g_ev_done[late ? c.ntr - 1 : tr], 0));
         ctx_pull_node_field(c, c.T.p + nf * tr, L, c.N, tr_arr + rf * tr, 1, 0, false);
         ctx_pull_node_field(c, c.Told.p + nf * tr, L, c.N, tr_arr_old + rf * tr, 1, 0, false);
     }
@@ -297,12 +341,14 @@ void fb200_solve_tracers_ale_resident(double* tr_arr_out) {
     cudaStream_t comp = c.stream, copy = copy_stream();
     const int L = c.nl - 1;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
+    const bool late = c.opt.relax_zonal != 0;             // relax_zonal_temp touches tracer 1 on every later pass: copy after the loop
     for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
         tracer_step_tracer(c, tr);
         CUDA_CHECK(cudaEventRecord(g_ev_done[tr], comp));
+        if (late && tr + 1 < c.ntr) continue;
         c.stream = copy;
         CUDA_CHECK(cudaStreamWaitEvent(copy, g_ev_done[tr], 0));
-        ctx_pull_node_field(c, c.T.p + nf * tr, L, c.N, tr_arr_out + rf * tr, 1, 0, false);
+        for (int k = late ? 0 : tr; k <= tr; k++) ctx_pull_node_field(c, c.T.p + nf * k, L, c.N, tr_arr_out + rf * k, 1, 0, false);
         c.stream = comp;
     }
     tracer_step_end(c);

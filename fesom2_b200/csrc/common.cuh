@@ -43,6 +43,7 @@ struct Options {
     double is_nonlinfs = 1.0, dt = 0.0, epsilon = 0.1;
     int use_kpp_nonlclflx = 0, ref_sss_local = 0; double ref_sss = 34.7;   // fb200_push_kpp_nonlocal (oce_modules.F90:51-52)
     double clim_relax = 0.0;        // > 1e-8: relax_to_clim is applied to tracers 1 and 2 (fb200_set_clim)
+    int relax_zonal = 0;            // relax_zonal_temp of the soufflet channel instead of relax_to_clim (fb200_set_zonal_relax)
     int tracer_id[8] = {0, 1, 301, 301, 301, 301, 301, 301};
 };
 
@@ -113,6 +114,8 @@ struct TracerCtx {
     int which_ale = -1; double w_max_cfl = 1.0;
     DevBuf<double> kgT, kgS, kb2, kb3;          // KPP non-local transport: ghats / kpp_nonlcltransp{T,S}, blmc(:,:,2:3) (nl, N) tiled
     DevBuf<double> relax2clim, Tclim, Sclim;   // climatology relaxation: (N), tiled, tiled (fb200_set_clim)
+    // relax_zonal_temp (fb200_set_zonal_relax): zonal-mean temperature (nl-1, nybins), per node the two bins and the weight
+    DevBuf<double> zon_ztem, zon_a; DevBuf<int2> zon_nn; double zon_fac = 0.0;   // zon_fac = tau_inv
     // tracers, tiled: [ntr] fields each
     DevBuf<double> T, Told;
     // work fields, tiled

@@ -884,6 +884,24 @@ __global__ void LB(128) k_relax_clim(KP p, double* __restrict__ T, const double*
     }
 }
 
+// relax_zonal_temp, toy_channel_soufflet.F90:78-103 — own + halo nodes, levels 1..nlevels_nod2D-1, always tracer 1:
+// T += dt*tau_inv * (Tclim - ((1-a) ztem(nz,nn) + a ztem(nz,nn1))); nn, nn1, a per node come from fb200_set_zonal_relax
+__global__ void LB(128) k_relax_zonal(KP p, double* __restrict__ T, const double* __restrict__ clim, const double* __restrict__ ztem,
+                                      const int2* __restrict__ bins, const double* __restrict__ wgt, double fac) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.N) return;
+    const int b = tbase(n, p.nlp), L = p.nl - 1;
+    const int nln = (p.n_lev[n] >> 8) & 255;
+    const int2 nn = bins[n];
+    const double a = wgt[n];
+    const double* z0 = ztem + (size_t)(nn.x - 1) * L - 1;
+    const double* z1 = ztem + (size_t)(nn.y - 1) * L - 1;
+    for (int nz = 1; nz <= nln - 1; nz++) {
+        const double tzon = (1.0 - a) * z0[nz] + a * z1[nz];
+        AT(T, b, nz) = AT(T, b, nz) + fac * (AT(clim, b, nz) - tzon);
+    }
+}
+
 // global extrema of one tracer over own wet cells: the quantity check_blowup (write_step_info.F90:220-504) and the
 // min/max lines of write_step_info test on the host; with device-resident tracers only two scalars cross PCIe.
 // One partial (min, max) per block; the host combines the <= 1184 partials (min/max are order-independent).
@@ -1046,7 +1064,9 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
         else if (kpp) KL("k_impl_diff", k_impl_diff<false, true><<<gI, bI, 0, st>>>(p));
         else KL("k_impl_diff", k_impl_diff<false, false><<<gI, bI, 0, st>>>(p));
     }
-    if (c.opt.clim_relax > 1.0e-8 && tr < 2 && c.relax2clim.p)                          // relax_to_clim(tr_num), oce_ale_tracer.F90:150-154
+    if (c.opt.relax_zonal)                                                              // relax_zonal_temp: tracer 1 on every pass, oce_ale_tracer.F90:150-151
+        KL("k_relax_zonal", k_relax_zonal<<<gNall, 128, 0, st>>>(p, c.T.p, c.Tclim.p, c.zon_ztem.p, c.zon_nn.p, c.zon_a.p, c.opt.dt * c.zon_fac));
+    else if (c.opt.clim_relax > 1.0e-8 && tr < 2 && c.relax2clim.p)                     // relax_to_clim(tr_num), :152-154
         KL("k_relax_clim", k_relax_clim<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, tr == 0 ? c.Tclim.p : c.Sclim.p, c.relax2clim.p));
     if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
     if (c.opt.clamp_salt && tr == 1) KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T));   // tr_arr(:,:,2) only, :176-198

@@ -127,9 +127,15 @@ void fb200_push_state_late(double* UV, double* Wvel, double* Wvel_e, double* Wve
 void fb200_push_kpp_nonlocal(int* enable, double* gT, double* gS, double* b2, double* b3, double* ref_sss, int* ref_sss_local);
 /* climatology relaxation inside the step, relax_to_clim (src/oce_tracer_mod.F90:87-119, called at
  * src/oce_ale_tracer.F90:150-154 between diff_tracers_ale and exchange_nod(tr_arr)): clim_relax (namelist oce_tra),
- * relax2clim(N), Tclim/Sclim(nl-1,N).  Static data: call once after fb200_init_commit; *clim_relax <= 1e-8 = off.
- * (relax_zonal_temp of the soufflet toy, src/toy_channel_soufflet.F90:78-103, is not provided.) */
+ * relax2clim(N), Tclim/Sclim(nl-1,N).  Static data: call once after fb200_init_commit; *clim_relax <= 1e-8 = off. */
 void fb200_set_clim(double* clim_relax, double* relax2clim, double* Tclim, double* Sclim);
+/* relax_zonal_temp of the soufflet channel (src/toy_channel_soufflet.F90:78-103), which solve_tracers_ale calls instead of
+ * relax_to_clim when toy_ocean and which_toy == "soufflet" (src/oce_ale_tracer.F90:150-151) — once per pass of the tracer
+ * loop and always on tracer 1, as the reference does.  nybins, lat0, dy, tau_inv: the module's parameters (:19-24, :207);
+ * coord_nod2D(2,N) in radians; ztem(nl-1,nybins) from compute_zonal_mean (:143-200) — call again whenever the host
+ * refreshes it; Tclim(nl-1,N).  *enable = 0 switches back to fb200_set_clim's relaxation. */
+void fb200_set_zonal_relax(int* enable, int* nybins, double* lat0, double* dy, double* tau_inv, double* coord_nod2D, double* ztem,
+                           double* Tclim);
 /* tr_arr / tr_arr_old (nl-1, N, num_tracers) */
 void fb200_push_tracers(double* tr_arr, double* tr_arr_old);
 void fb200_solve_tracers(void);                         /* all tracers, device resident */

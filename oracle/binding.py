@@ -103,6 +103,17 @@ class TracerOracle:
         for nm, a in (("relax2clim", relax2clim), ("Tclim", Tclim), ("Sclim", Sclim)):
             assert self.L.oracle_set_ptr(self.o, nm.encode(), a.ctypes.data) == 0
 
+    def set_zonal_relax(self, ztem, coord_nod2D, Tclim, lat0, dy, tau_inv):
+        """relax_zonal_temp of the soufflet channel (toy_channel_soufflet.F90:78-103) instead of relax_to_clim:
+        ztem (nybins, nl-1), coord_nod2D (N, 2) [rad], Tclim (N, nl-1); arrays are bound, not copied"""
+        self._keep += [ztem, coord_nod2D, Tclim]
+        self.L.oracle_set_int(self.o, b"relax_zonal", 1)
+        for nm, v in (("zonal_lat0", lat0), ("zonal_dy", dy), ("zonal_tau_inv", tau_inv)):
+            assert self.L.oracle_set_dbl(self.o, nm.encode(), float(v)) == 0
+        for nm, a in (("zonal_ztem", ztem), ("coord_nod2D", coord_nod2D), ("Tclim", Tclim)):
+            assert a.flags.c_contiguous and a.dtype == np.float64
+            assert self.L.oracle_set_ptr(self.o, nm.encode(), a.ctypes.data) == 0
+
     def set_kpp_nonlocal(self, gT, gS, b2, b3, ref_sss=34.7, ref_sss_local=False):
         """KPP non-local transport in diff_ver_part_impl_ale (oce_ale_tracer.F90:688-781); (N, nl) arrays, bound not copied"""
         self._keep += [gT, gS, b2, b3]

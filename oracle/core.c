@@ -6,13 +6,13 @@
 
 #define INT_FIELDS(X) X(nl) X(myDim_nod2D) X(eDim_nod2D) X(myDim_elem2D) X(eDim_elem2D) X(eXDim_elem2D) X(myDim_edge2D) \
     X(nod_in_elem2D_max) X(num_tracers) X(tra_adv_hor) X(tra_adv_ver) X(tra_adv_lim) X(w_split) X(i_vert_diff) X(Redi)    \
-    X(use_sw_pene) X(do_hor_diff) X(clamp_salt) X(use_kpp_nonlclflx) X(ref_sss_local) X(fct_cavity_neutral)
-#define DBL_FIELDS(X) X(dt) X(epsilon) X(tra_adv_ph) X(tra_adv_pv) X(is_nonlinfs) X(clim_relax) X(ref_sss)
+    X(use_sw_pene) X(do_hor_diff) X(clamp_salt) X(use_kpp_nonlclflx) X(ref_sss_local) X(fct_cavity_neutral) X(relax_zonal)
+#define DBL_FIELDS(X) X(dt) X(epsilon) X(tra_adv_ph) X(tra_adv_pv) X(is_nonlinfs) X(clim_relax) X(ref_sss) X(zonal_lat0) X(zonal_dy) X(zonal_tau_inv)
 #define CIPTR_FIELDS(X) X(edges) X(edge_tri) X(elem2D_nodes) X(nlevels) X(ulevels) X(nlevels_nod2D) X(ulevels_nod2D) \
     X(nlevels_nod2D_min) X(ulevels_nod2D_max) X(nod_in_elem2D) X(nod_in_elem2D_num) X(edge_up_dn_tri) X(nboundary_lay)
 #define CDPTR_FIELDS(X) X(edge_cross_dxdy) X(edge_dxdy) X(elem_cos) X(elem_area) X(gradient_sca) X(area) X(areasvol) \
     X(zbar_n_bot) X(UV) X(Wvel) X(Wvel_e) X(Wvel_i) X(hnode) X(hnode_new) X(helem) X(Z_3d_n) X(zbar_3d_n) X(Kv) X(Ki)  \
-    X(slope_tapered) X(heat_flux) X(water_flux) X(virtual_salt) X(relax_salt) X(real_salt_flux) X(sw_3d) X(relax2clim) X(Tclim) X(Sclim) X(kpp_gT) X(kpp_gS) X(kpp_b2) X(kpp_b3)
+    X(slope_tapered) X(heat_flux) X(water_flux) X(virtual_salt) X(relax_salt) X(real_salt_flux) X(sw_3d) X(relax2clim) X(Tclim) X(Sclim) X(kpp_gT) X(kpp_gS) X(kpp_b2) X(kpp_b3) X(zonal_ztem) X(coord_nod2D)
 #define DPTR_FIELDS(X) X(tr_arr) X(tr_arr_old)
 #define WORK_FIELDS(X) X(del_ttf) X(del_ttf_advhoriz) X(del_ttf_advvert) X(tr_xy) X(tr_z) X(edge_up_dn_grad) X(fct_LO) \
     X(adv_flux_hor) X(adv_flux_ver) X(fct_ttf_max) X(fct_ttf_min) X(fct_plus) X(fct_minus) X(aux_minmax)

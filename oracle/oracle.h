@@ -36,6 +36,12 @@ typedef struct oracle {
                  *slope_tapered, *heat_flux, *water_flux, *virtual_salt, *relax_salt, *real_salt_flux, *sw_3d;
     /* climatology relaxation (o_ARRAYS: relax2clim(N), Tclim/Sclim(nl-1,N); namelist oce_tra: clim_relax) */
     const double *relax2clim, *Tclim, *Sclim;
+    /* relax_zonal_temp of the soufflet channel (toy_channel_soufflet.F90:78-103), taken instead of relax_to_clim when
+     * relax_zonal != 0: zonal-mean temperature zonal_ztem(nl-1, nybins) from compute_zonal_mean (:143-200), node latitudes
+     * coord_nod2D(2,N) [rad], module parameters lat0, dy = ysize/nybins/r_earth, tau_inv (:19-24, :207) */
+    const double *zonal_ztem, *coord_nod2D;
+    double zonal_lat0, zonal_dy, zonal_tau_inv;
+    int relax_zonal;
     /* KPP non-local transport (use_kpp_nonlclflx): ghats (fesom KPP) or kpp_nonlcltranspT/S (cvmix) as kpp_gT/kpp_gS (nl,N),
      * blmc(:,:,2:3) or kpp_oblmixc(:,:,2:3) as kpp_b2/kpp_b3 (nl,N); ref_sss, ref_sss_local (oce_modules.F90:51-52) */
     const double *kpp_gT, *kpp_gS, *kpp_b2, *kpp_b3;
@@ -81,6 +87,8 @@ void o_oce_tra_adv_flux2dtracer(oracle_t* o, double* dttf_h, double* dttf_v, dou
 void o_diff_part_hor_redi(oracle_t* o);
 void o_diff_ver_part_expl_ale(oracle_t* o, int tr_num);
 void o_diff_ver_part_impl_ale(oracle_t* o, int tr_num);
+void o_relax_to_clim(oracle_t* o, int tr_num);
+void o_relax_zonal_temp(oracle_t* o);
 
 /* phases of solve_tracers_ale between halo exchanges (see tracer.c) */
 void o_phase1(oracle_t* o, int tr_num);   /* AB2 + tracer_gradient_elements(AB)            -> exchange_elem(tr_xy)            */

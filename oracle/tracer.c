@@ -760,6 +760,30 @@ void o_relax_to_clim(oracle_t* o, int tr_num) {
             T2(ttf, nz, n) = T2(ttf, nz, n) + o->relax2clim[n - 1] * o->dt * (T2(clim, nz, n) - T2(ttf, nz, n));
     }
 }
+/* relax_zonal_temp, toy_channel_soufflet.F90:78-103: own + halo nodes, levels 1..nlevels_nod2D-1, ALWAYS tracer 1 (the
+ * caller's tracer loop reaches it once per tracer, oce_ale_tracer.F90:150-151, so temperature is relaxed num_tracers times
+ * per step); the bin index limit is the literal 100 of the reference, not nybins */
+void o_relax_zonal_temp(oracle_t* o) {
+    const int N = o->myDim_nod2D + o->eDim_nod2D, L = o->nl - 1;
+    const double dy = o->zonal_dy;
+    double* ttf = TR(o, 1);
+    for (int n = 1; n <= N; n++) {
+        double yy = o->coord_nod2D[2 * (n - 1) + 1] - o->zonal_lat0;
+        double a = 0;
+        int nn, nn1;
+        if (yy < dy / 2) { nn = 1; nn1 = 1; }
+        else {
+            nn = (int)floor(yy / dy - 0.5) + 1;
+            nn1 = nn + 1;
+            if (nn1 > 100) nn1 = nn;
+            a = yy / dy + 0.5 - nn;
+        }
+        for (int nz = 1; nz <= o->nlevels_nod2D[n - 1] - 1; nz++) {
+            double Tzon = (1.0 - a) * o->zonal_ztem[(size_t)(nn - 1) * L + nz - 1] + a * o->zonal_ztem[(size_t)(nn1 - 1) * L + nz - 1];
+            T2(ttf, nz, n) = T2(ttf, nz, n) + o->dt * o->zonal_tau_inv * (T2(o->Tclim, nz, n) - Tzon);
+        }
+    }
+}
 void o_phase_final(oracle_t* o) {                   /* oce_ale_tracer.F90:176-198 */
     if (!o->clamp_salt || o->num_tracers < 2) return;
     int N = o->myDim_nod2D + o->eDim_nod2D;
@@ -773,7 +797,8 @@ void o_phase_final(oracle_t* o) {                   /* oce_ale_tracer.F90:176-19
 void o_solve_tracers_ale(oracle_t* o) {
     for (int tr = 1; tr <= o->num_tracers; tr++) {
         o_phase1(o, tr); o_phase2(o, tr); o_phase3(o, tr); o_phase4(o, tr); o_phase5(o, tr);
-        o_relax_to_clim(o, tr);                         /* oce_ale_tracer.F90:150-154 (relax_zonal_temp of the soufflet toy is not restated) */
+        if (o->relax_zonal) o_relax_zonal_temp(o);      /* oce_ale_tracer.F90:150-154 */
+        else o_relax_to_clim(o, tr);
     }
     o_phase_final(o);
 }

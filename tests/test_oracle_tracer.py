@@ -185,3 +185,28 @@ def test_cavity_limiter_scratch_only_matters_at_the_cavity_edge():
     hc["tr_arr_old"][0] = hc["tr_arr"][0]
     ob.TracerOracle(hc, fct_cavity_neutral=True).step()
     assert np.abs(hc["tr_arr"][0][wet] - 7.0).max() < 5e-14
+
+
+def test_relax_zonal_temp_adds_the_zonal_restoring_once_per_tracer_pass():
+    """relax_zonal_temp (toy_channel_soufflet.F90:78-103) replaces relax_to_clim on the soufflet channel: the increment
+    dt*tau_inv*(Tclim - Tzon) does not depend on the current temperature and the tracer loop reaches the routine once per
+    tracer (oce_ale_tracer.F90:150-151), so after one step T = (T_without + inc) + inc exactly and S is untouched."""
+    A, B = util.build_model("soufflet"), util.build_model("soufflet")
+    ztem, Tclim, lat0, dy, tau_inv = util.soufflet_zonal_setup(B)
+    Tclim = Tclim + 0.3                                   # make the restoring term non-trivial
+    ob.TracerOracle(A).step()
+    o = ob.TracerOracle(B)
+    o.set_zonal_relax(ztem, np.ascontiguousarray(B["coord_nod2D"]), Tclim, lat0, dy, tau_inv)
+    o.step()
+    nl, dt = B.ipar("nl"), B.par("dt")
+    yy = B["coord_nod2D"][:, 1] - lat0
+    nn = np.where(yy < dy / 2, 1, np.floor(yy / dy - 0.5).astype(np.int64) + 1)
+    nn1 = np.where(yy < dy / 2, 1, np.where(nn + 1 > 100, nn, nn + 1))
+    a = np.where(yy < dy / 2, 0.0, yy / dy + 0.5 - nn)
+    Tzon = (1.0 - a)[:, None] * ztem[nn - 1] + a[:, None] * ztem[nn1 - 1]
+    inc = dt * tau_inv * (Tclim - Tzon)
+    lev = np.arange(1, nl)[None, :] <= (B["nlevels_nod2D"] - 1)[:, None]
+    want = np.where(lev, (A["tr_arr"][0] + inc) + inc, A["tr_arr"][0])
+    assert np.abs(inc[lev]).max() > 1e-4
+    assert np.array_equal(B["tr_arr"][0], want)
+    assert np.array_equal(B["tr_arr"][1], A["tr_arr"][1])

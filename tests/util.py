@@ -105,3 +105,28 @@ def tracer_mass(hm, k):
     nl = hm.ipar("nl")
     wet = wet_mask(hm)
     return float((hm["tr_arr"][k] * hm["hnode"] * hm["areasvol"][:, :nl - 1])[wet].sum())
+
+
+def soufflet_zonal_setup(hm, nybins=100, ysize=2000000.0, lat0=0.0):
+    """the soufflet channel's zonal restoring inputs: (ztem, Tclim, lat0, dy, tau_inv).  ztem (nybins, nl-1) follows
+    compute_zonal_mean_ini / compute_zonal_mean (toy_channel_soufflet.F90:110-200) on one partition; Tclim is the initial
+    temperature (initial_state_soufflet sets Tclim = tr_arr(:,:,1)); tau_inv = 1/50 days (:19)"""
+    r_earth = 6367500.0
+    dy = ysize / nybins / r_earth
+    nl = hm.ipar("nl")
+    myE = hm.ipar("myDim_elem2D")
+    en = hm["elem2D_nodes"][:myE] - 1
+    lat = hm["coord_nod2D"][:, 1]
+    ymean = ((lat[en[:, 0]] + lat[en[:, 1]]) + lat[en[:, 2]]) / 3.0
+    bpos = np.floor((ymean - lat0) / dy).astype(np.int64) + 1
+    assert bpos.min() >= 1 and bpos.max() <= nybins
+    T = hm["tr_arr"][0]
+    ztem = np.zeros((nybins, nl - 1))
+    znum = np.zeros((nybins, nl - 1))
+    nle = hm["nlevels"]
+    for e in range(myE):
+        znum[bpos[e] - 1, :] += 1.0
+        k = nle[e] - 1
+        ztem[bpos[e] - 1, :k] += ((T[en[e, 0], :k] + T[en[e, 1], :k]) + T[en[e, 2], :k]) / 3.0
+    ztem = np.ascontiguousarray(ztem / (znum + 0.001))
+    return ztem, np.ascontiguousarray(T.copy()), lat0, dy, 1.0 / 50.0 / 24.0 / 3600.0
