@@ -20,7 +20,7 @@ LIM = {"FCT": 0, "NONE": 1}
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
-           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_push_tracers", "fb200_set_clim", "fb200_set_zonal_relax", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema",
+           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_push_tracers", "fb200_set_clim", "fb200_set_zonal_relax", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema", "fb200_mean_accumulate", "fb200_mean_fetch",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
@@ -236,6 +236,19 @@ class TracerEngine:
         self.L.fb200_tracer_extrema(_i(tr_num), C.byref(lo), C.byref(hi))
         _check(self.L)
         return lo.value, hi.value
+
+    def mean_accumulate(self, tr_num, accuracy=8):
+        """update_means for the output stream of tracer tr_num (1-based), accuracy 8 (real64) or 4 (real32)"""
+        self.L.fb200_mean_accumulate(_i(tr_num), _i(accuracy))
+        _check(self.L)
+
+    def mean_fetch(self, tr_num, accuracy=8):
+        """(myDim_nod2D, nl-1) mean over the accumulated steps in the stream's precision; clears the accumulator"""
+        hm = self.hm
+        out = np.zeros((hm.ipar("myDim_nod2D"), hm.ipar("nl") - 1), dtype=np.float64 if accuracy == 8 else np.float32)
+        self.L.fb200_mean_fetch(_i(tr_num), _p(out))
+        _check(self.L)
+        return out
 
     def push_tracers(self, tr=None, tro=None):
         tr = self.hm.arr("tr_arr") if tr is None else tr

@@ -359,6 +359,11 @@ void fb200_solve_tracers_ale_resident(double* tr_arr_out) {
 // its own MPI_Allreduce, as write_step_info.F90 does)
 void fb200_tracer_extrema(int* tr_num, double* tmin, double* tmax) { tracer_extrema(tctx(), *tr_num - 1, tmin, tmax); }
 
+// output means of the resident tracer *tr_num (1-based): fb200_mean_accumulate = update_means for that stream
+// (io_meandata.F90:768-794; *accuracy 8 = real64, 4 = real32), fb200_mean_fetch = compute_means + clean_meanarrays (:894-900)
+void fb200_mean_accumulate(int* tr_num, int* accuracy) { tracer_mean_accumulate(tctx(), *tr_num - 1, *accuracy); }
+void fb200_mean_fetch(int* tr_num, void* mean_out) { tracer_mean_fetch(tctx(), *tr_num - 1, mean_out); }
+
 void fb200_debug_fetch(const char* name, double* out) {
     TracerCtx& c = tctx();
     if (!c.committed) { fb_set_error(36, "fb200_debug_fetch before fb200_init_commit"); return; }

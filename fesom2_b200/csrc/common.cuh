@@ -116,6 +116,9 @@ struct TracerCtx {
     DevBuf<double> relax2clim, Tclim, Sclim;   // climatology relaxation: (N), tiled, tiled (fb200_set_clim)
     // relax_zonal_temp (fb200_set_zonal_relax): zonal-mean temperature (nl-1, nybins), per node the two bins and the weight
     DevBuf<double> zon_ztem, zon_a; DevBuf<int2> zon_nn; double zon_fac = 0.0;   // zon_fac = tau_inv
+    // output means of the resident tracers (fb200_mean_*; io_meandata.F90 update_means): one accumulator per tracer in the
+    // stream's precision, allocated on first use
+    DevBuf<double> mean8[8]; DevBuf<float> mean4[8]; int mean_count[8] = {0, 0, 0, 0, 0, 0, 0, 0}, mean_prec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     // tracers, tiled: [ntr] fields each
     DevBuf<double> T, Told;
     // work fields, tiled
@@ -151,3 +154,5 @@ bool tracer_step_begin(TracerCtx& c);
 void tracer_step_tracer(TracerCtx& c, int tr);
 void tracer_step_end(TracerCtx& c);
 void tracer_extrema(TracerCtx& c, int tr, double* tmin, double* tmax);
+void tracer_mean_accumulate(TracerCtx& c, int tr, int accuracy);
+void tracer_mean_fetch(TracerCtx& c, int tr, void* mean_out);

@@ -976,6 +976,62 @@ void tracer_extrema(TracerCtx& c, int tr, double* tmin, double* tmax) {
     *tmin = lo; *tmax = hi;
 }
 
+// Output means of the resident tracers: update_means (io_meandata.F90:768-794) adds the stream's field to local_values in
+// the stream's precision (real64, or real32 with the field rounded to real32 first) and counts; output (:894-900) divides
+// by real(addcounter) in that precision and clears.  The whole tiled field is accumulated (dry levels, halo and padding
+// included: the reference adds ptr3(1:nl-1, 1:myDim_nod2D) including the entries below the bottom).
+template <class A>
+__global__ void LB(256) k_mean_acc(A* __restrict__ acc, const double* __restrict__ T, size_t count) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) acc[i] = acc[i] + (A)T[i];
+}
+template <class A>
+__global__ void LB(256) k_mean_out(A* __restrict__ acc, double* __restrict__ out, size_t count, int addcounter) {
+    const A d = (A)addcounter;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) {
+        out[i] = (double)(acc[i] / d);
+        acc[i] = (A)0;
+    }
+}
+void tracer_mean_accumulate(TracerCtx& c, int tr, int accuracy) {
+    if (!fb_ok()) return;
+    if (!c.committed || tr < 0 || tr >= c.ntr || tr >= 8) { fb_set_error(27, "fb200_mean_accumulate: not committed or no such tracer"); return; }
+    if (accuracy != 4 && accuracy != 8) { fb_set_error(27, "fb200_mean_accumulate: accuracy must be 4 (real32) or 8 (real64)"); return; }
+    if (c.mean_count[tr] > 0 && c.mean_prec[tr] != accuracy) { fb_set_error(27, "fb200_mean_accumulate: precision changed inside an averaging interval"); return; }
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
+    c.mean_prec[tr] = accuracy;
+    if (accuracy == 8) {
+        if (!c.mean8[tr].p) c.mean8[tr].alloc(nf);             // alloc clears
+        ProfScope ps_("k_mean_acc", st); k_mean_acc<double><<<148 * 8, 256, 0, st>>>(c.mean8[tr].p, c.T.p + nf * tr, nf); LAUNCH_CHECK();
+    } else {
+        if (!c.mean4[tr].p) c.mean4[tr].alloc(nf);
+        ProfScope ps_("k_mean_acc", st); k_mean_acc<float><<<148 * 8, 256, 0, st>>>(c.mean4[tr].p, c.T.p + nf * tr, nf); LAUNCH_CHECK();
+    }
+    c.mean_count[tr]++;
+}
+// mean_out: (nl-1, myDim_nod2D) real64 or real32, whichever the interval was accumulated in
+void tracer_mean_fetch(TracerCtx& c, int tr, void* mean_out) {
+    if (!fb_ok()) return;
+    if (!c.committed || tr < 0 || tr >= c.ntr || tr >= 8 || c.mean_count[tr] == 0) { fb_set_error(27, "fb200_mean_fetch: nothing accumulated for this tracer"); return; }
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
+    const int L = c.nl - 1;
+    double* scratch = c.tstar.p;                                // work field of the step, free between steps
+    if (c.mean_prec[tr] == 8) {
+        { ProfScope ps_("k_mean_out", st); k_mean_out<double><<<148 * 8, 256, 0, st>>>(c.mean8[tr].p, scratch, nf, c.mean_count[tr]); LAUNCH_CHECK(); }
+        ctx_pull_node_field(c, scratch, L, c.myN, (double*)mean_out, 1, 0, true);
+    } else {
+        { ProfScope ps_("k_mean_out", st); k_mean_out<float><<<148 * 8, 256, 0, st>>>(c.mean4[tr].p, scratch, nf, c.mean_count[tr]); LAUNCH_CHECK(); }
+        std::vector<double> h((size_t)L * c.myN);
+        ctx_pull_node_field(c, scratch, L, c.myN, h.data(), 1, 0, true);
+        float* o = (float*)mean_out;
+        for (size_t i = 0; i < h.size(); i++) o[i] = (float)h[i];      // exact: the values are real32 numbers
+    }
+    c.mean_count[tr] = 0;
+}
+
 static bool g_attr_done = false;
 static void set_smem_attrs() {
     if (g_attr_done) return;

@@ -159,6 +159,13 @@ void fb200_ale_step_end(void);
  * the extrema lines of write_step_info (src/write_step_info.F90:220-504) test; lets a host that keeps the tracers resident
  * monitor them without pulling the fields (combine the ranks with MPI_Allreduce as the reference does) */
 void fb200_tracer_extrema(int* tr_num, double* tmin, double* tmax);
+/* Output means of the device-resident tracers (src/io_meandata.F90): fb200_mean_accumulate is update_means (:768-794) for
+ * the stream of tracer *tr_num (1-based) — local_values += tr_arr(:,:,tr_num) in the stream's precision, *accuracy = 8
+ * (real64) or 4 (real32: the field is rounded to real32 before it is added, as the reference does), addcounter += 1;
+ * fb200_mean_fetch is compute_means + clean_meanarrays at output time (:894-900): mean_out(nl-1, myDim_nod2D) =
+ * local_values / real(addcounter) in that precision (real64 or real32 array), accumulator and counter cleared. */
+void fb200_mean_accumulate(int* tr_num, int* accuracy);
+void fb200_mean_fetch(int* tr_num, void* mean_out);
 /* debugging / parity: copy an internal (level, node|edge|elem) work field back in the reference layout.
  * name: "fct_LO","adf_h","adf_v","fct_plus","fct_minus","tr_xy_x","tr_xy_y","ttfAB","tstar" ; returns via status */
 void fb200_debug_fetch(const char* name, double* out);

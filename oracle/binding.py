@@ -140,6 +140,28 @@ class TracerOracle:
         self.L.o_phase_final(self.o)
 
 
+class MeanStream:
+    """one output stream of io_meandata.F90 (update_means :768-794, compute_means/clean_meanarrays :894-900) over a
+    (n, nl-1) field in real64 (accuracy 8) or real32 (accuracy 4)"""
+
+    def __init__(self, shape, accuracy=8):
+        self.accuracy = int(accuracy)
+        self.acc = np.zeros(shape, dtype=np.float64 if accuracy == 8 else np.float32)
+        self.count = 0
+
+    def update(self, field):
+        f = np.ascontiguousarray(field, dtype=np.float64)
+        assert f.shape == self.acc.shape
+        lib().o_update_means(self.accuracy, C.c_void_p(self.acc.ctypes.data), C.c_void_p(f.ctypes.data), C.c_longlong(f.size))
+        self.count += 1
+
+    def output(self):
+        out = np.zeros_like(self.acc)
+        lib().o_compute_means(self.accuracy, C.c_void_p(self.acc.ctypes.data), C.c_void_p(out.ctypes.data), C.c_longlong(out.size), self.count)
+        self.count = 0
+        return out
+
+
 def ssh_solve(rowptr0, colind0, values, rhs, x0, pc_kind=1, block=1, soltol=1e-10, maxits=2000):
     L = lib()
     rp = np.ascontiguousarray(rowptr0, dtype=np.int32)

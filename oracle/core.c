@@ -77,3 +77,15 @@ int oracle_alloc_work(oracle_t* o) {     /* array_setup + oce_adv_tra_fct_init +
 #undef AL
     return 0;
 }
+
+/* Output means, io_meandata.F90: update_means (:768-794) adds the stream's field to local_values in the stream's precision
+ * (accuracy 8 = real64; 4 = real32 with the field rounded to real32 first) — the caller counts addcounter; compute_means +
+ * clean_meanarrays (:894-900) divide by real(addcounter) in that precision and clear. */
+void o_update_means(int accuracy, void* local_values, const double* ptr3, long long n) {
+    if (accuracy == 8) { double* a = (double*)local_values; for (long long i = 0; i < n; i++) a[i] = a[i] + ptr3[i]; }
+    else { float* a = (float*)local_values; for (long long i = 0; i < n; i++) a[i] = a[i] + (float)ptr3[i]; }
+}
+void o_compute_means(int accuracy, void* local_values, void* copy, long long n, int addcounter) {
+    if (accuracy == 8) { double* a = (double*)local_values; double* c = (double*)copy; const double d = (double)addcounter; for (long long i = 0; i < n; i++) { c[i] = a[i] / d; a[i] = 0.0; } }
+    else { float* a = (float*)local_values; float* c = (float*)copy; const float d = (float)addcounter; for (long long i = 0; i < n; i++) { c[i] = a[i] / d; a[i] = 0.0f; } }
+}

@@ -89,6 +89,8 @@ void o_diff_ver_part_expl_ale(oracle_t* o, int tr_num);
 void o_diff_ver_part_impl_ale(oracle_t* o, int tr_num);
 void o_relax_to_clim(oracle_t* o, int tr_num);
 void o_relax_zonal_temp(oracle_t* o);
+void o_update_means(int accuracy, void* local_values, const double* ptr3, long long n);
+void o_compute_means(int accuracy, void* local_values, void* copy, long long n, int addcounter);
 
 /* phases of solve_tracers_ale between halo exchanges (see tracer.c) */
 void o_phase1(oracle_t* o, int tr_num);   /* AB2 + tracer_gradient_elements(AB)            -> exchange_elem(tr_xy)            */

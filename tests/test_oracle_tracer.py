@@ -210,3 +210,19 @@ def test_relax_zonal_temp_adds_the_zonal_restoring_once_per_tracer_pass():
     assert np.abs(inc[lev]).max() > 1e-4
     assert np.array_equal(B["tr_arr"][0], want)
     assert np.array_equal(B["tr_arr"][1], A["tr_arr"][1])
+
+
+@pytest.mark.parametrize("accuracy", [8, 4])
+def test_output_mean_stream_restatement(accuracy):
+    """update_means / compute_means (io_meandata.F90:768-794, 894-900) in the stream's precision: against numpy in that precision"""
+    rng = np.random.default_rng(3)
+    fields = [15.0 + rng.standard_normal((50, 7)) for _ in range(5)]
+    ms = ob.MeanStream((50, 7), accuracy)
+    dt = np.float64 if accuracy == 8 else np.float32
+    acc = np.zeros((50, 7), dtype=dt)
+    for f in fields:
+        ms.update(f)
+        acc = acc + f.astype(dt)
+    got = ms.output()
+    assert got.dtype == dt and np.array_equal(got, acc / dt(5))
+    assert ms.count == 0 and not ms.acc.any()
