@@ -20,7 +20,7 @@ LIM = {"FCT": 0, "NONE": 1}
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
            "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
-           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_push_tracers", "fb200_set_clim", "fb200_set_zonal_relax", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema", "fb200_mean_accumulate", "fb200_mean_fetch",
+           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_ssh_assembly_init", "fb200_update_stiff_mat", "fb200_compute_ssh_rhs", "fb200_update_vel", "fb200_push_tracers", "fb200_set_clim", "fb200_set_zonal_relax", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema", "fb200_mean_accumulate", "fb200_mean_fetch",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
@@ -220,10 +220,33 @@ class TracerEngine:
         self.L.fb200_ale_init(_i(hm.ipar("which_ale")), _d(hm.par("w_max_cfl")), _p(hm.arr("hbar")))
         _check(self.L)
 
-    def ale_step_begin(self):
-        """H2D UV + water_flux; hbar, ssh_rhs_old, dhe land in the host model's arrays"""
+    def ale_step_begin(self, uv_resident=False):
+        """H2D UV (unless fb200_update_vel has just produced it on the device) + water_flux; hbar, ssh_rhs_old, dhe land in
+        the host model's arrays"""
         a = self.hm.arr
-        self.L.fb200_ale_step_begin(_p(a("UV")), _p(a("water_flux")), _p(a("hbar")), _p(a("ssh_rhs_old")), _p(a("dhe")))
+        self.L.fb200_ale_step_begin(None if uv_resident else _p(a("UV")), _p(a("water_flux")), _p(a("hbar")), _p(a("ssh_rhs_old")), _p(a("dhe")))
+        _check(self.L)
+
+    def ssh_assembly_init(self, g=9.81):
+        """device-side compute_ssh_rhs_ale / update_stiff_mat_ale / update_vel: hand over ssh_stiff and g, alpha, theta"""
+        hm = self.hm
+        self.L.fb200_ssh_assembly_init(_p(hm.arr("ssh_rowptr")), _p(hm.arr("ssh_colind_loc")), _p(hm.arr("ssh_values")), _d(g),
+                                       _d(hm.par("alpha")), _d(hm.par("theta")))
+        _check(self.L)
+
+    def update_stiff_mat(self):
+        """update_stiff_mat_ale from the resident dhe; the host model's ssh_values receive the result"""
+        self.L.fb200_update_stiff_mat(_p(self.hm.arr("ssh_values")))
+        _check(self.L)
+
+    def compute_ssh_rhs(self):
+        """H2D UV_rhs; compute_ssh_rhs_ale on the device; the host model's ssh_rhs receives the result"""
+        self.L.fb200_compute_ssh_rhs(_p(self.hm.arr("UV_rhs")), _p(self.hm.arr("ssh_rhs")))
+        _check(self.L)
+
+    def update_vel(self):
+        """update_vel with the host model's d_eta; the host model's UV receives the new velocity"""
+        self.L.fb200_update_vel(_p(self.hm.arr("d_eta")), _p(self.hm.arr("UV")))
         _check(self.L)
 
     def ale_step_end(self):

@@ -112,6 +112,9 @@ struct TracerCtx {
     // device-side ALE producers (fb200_ale_*): surface elevation, its right-hand side, element thickness change, edge sums
     DevBuf<double> hbar, hbar_old, ssh_rhs_old, dhe, esum, CFL;
     int which_ale = -1; double w_max_cfl = 1.0;
+    // SSH assembly on the device (fb200_ssh_assembly_init, ..._update_stiff_mat, ..._compute_ssh_rhs, ..._update_vel)
+    DevBuf<int> sa_rowptr, sa_colind; DevBuf<double> sa_values, sa_rhs, sa_eta; DevBuf<double2> UVr;
+    double sa_g = 9.81, sa_alpha = 1.0, sa_theta = 1.0;
     DevBuf<double> kgT, kgS, kb2, kb3;          // KPP non-local transport: ghats / kpp_nonlcltransp{T,S}, blmc(:,:,2:3) (nl, N) tiled
     DevBuf<double> relax2clim, Tclim, Sclim;   // climatology relaxation: (N), tiled, tiled (fb200_set_clim)
     // relax_zonal_temp (fb200_set_zonal_relax): zonal-mean temperature (nl-1, nybins), per node the two bins and the weight

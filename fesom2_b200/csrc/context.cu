@@ -305,6 +305,7 @@ void ctx_release(TracerCtx& c) {
     c.tile_deg.release(); c.fb_list.release(); c.n_fb = 0; c.ns_p.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
     c.UV.release(); c.txy.release(); c.fpm.release(); c.zon_nn.release();
     for (int k = 0; k < 8; k++) { c.mean8[k].release(); c.mean4[k].release(); }
+    c.sa_rowptr.release(); c.sa_colind.release(); c.sa_values.release(); c.sa_rhs.release(); c.sa_eta.release(); c.UVr.release();
     c.edge.release(); c.edgeho.release(); c.ne_slot.release(); c.nie_slot.release(); c.el_nb.release(); c.el_lev.release();
     c.n_lev.release(); c.n_nbl.release();
     if (c.halo_nod) { c.halo_nod->release(); delete c.halo_nod; }

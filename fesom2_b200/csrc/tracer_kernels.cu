@@ -1420,8 +1420,10 @@ void fb200_ale_step_begin(double* UV, double* water_flux, double* hbar_out, doub
     fb_copy_sync();
     cudaStream_t st = c.stream = fb_stream();
     const int L = c.nl - 1;
-    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 0, 2, 0);
-    ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 1, 2, 1);
+    if (UV) {                                          // NULL: the resident velocity (fb200_update_vel has just produced it)
+        ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 0, 2, 0);
+        ctx_push_node_field(c, UV, L, c.E, (double*)c.UV.p, 2, 1, 2, 1);
+    }
     CUDA_CHECK(cudaMemcpyAsync(c.water_flux.p, water_flux, (size_t)c.N * sizeof(double), cudaMemcpyHostToDevice, st));
     KP p = make_kp(c, 0);
     const int ale = c.which_ale;
@@ -1461,6 +1463,190 @@ void fb200_ale_step_end(void) {
     KL("k_ale_thick", k_ale_thick<<<(c.N + 127) / 128, 128, 0, st>>>(p, c.hnode.p, c.zbar3.p, c.Z3.p, ale));
     KL("k_ale_helem", k_ale_helem<<<(c.myE + 127) / 128, 128, 0, st>>>(p, c.helem.p, ale));
 #undef KL
+    CUDA_CHECK(cudaStreamSynchronize(st));
+}
+
+}  // extern "C"
+
+// ===================================================================================================
+// SSH assembly on the device: compute_ssh_rhs_ale (oce_ale.F90:1478-1572), update_stiff_mat_ale
+// (:1371-1470) and update_vel (oce_dyn.F90:101-127), restated after the host-side mirror fesom2_b200/host/setup.cpp.  They
+// work on the state the device-side ALE producers keep resident (UV, helem, water_flux, ssh_rhs_old, dhe), so
+// fb200_ale_init must have been called.  What still crosses PCIe is the momentum step's UV_rhs (the momentum step itself
+// is outside the path); the stiffness values, the right-hand side and — after update_vel — UV are returned so that the
+// host's psolve call and momentum step see them.
+// per edge: c1 + c2 of compute_ssh_rhs_ale (:1518-1547)
+__global__ void LB(128) k_sshrhs_edge_sum(KP p, const double2* __restrict__ UVr, double alpha, double* __restrict__ esum) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= p.myEd) return;
+    const EdgeRec r = p.edge[e];
+    double c1 = 0.0, c2 = 0.0;
+    for (int nz = 1; nz <= p.nl - 1; nz++)
+        if ((r.m1 >> nz) & 1ull) {
+            const double2 uv = AT(p.UV, r.be1, nz), ur = AT(UVr, r.be1, nz);
+            c1 = c1 + alpha * ((uv.y + ur.y) * r.dX1 - (uv.x + ur.x) * r.dY1) * AT(p.helem, r.be1, nz);
+        }
+    if (r.be2 >= 0)
+        for (int nz = 1; nz <= p.nl - 1; nz++)
+            if ((r.m2 >> nz) & 1ull) {
+                const double2 uv = AT(p.UV, r.be2, nz), ur = AT(UVr, r.be2, nz);
+                c2 = c2 - alpha * ((uv.y + ur.y) * r.dX2 - (uv.x + ur.x) * r.dY2) * AT(p.helem, r.be2, nz);
+            }
+    esum[e] = c1 + c2;
+}
+// per own node: signed sum over the incident edges in ascending edge id, water flux and the (1 - alpha) part (:1549-1568)
+__global__ void LB(128) k_sshrhs_node(KP p, const double* __restrict__ esum, const double* __restrict__ sro, double* __restrict__ rhs,
+                                      double alpha, int ale) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.N) return;
+    if (n >= p.myN) { rhs[n] = 0.0; return; }
+    double s = 0.0;
+    const int* slot = p.ne_slot + (size_t)(n >> 5) * p.maxdeg * TILE + (n & 31);
+    for (int j = 0; j < p.maxdeg; j++) {
+        const int v = slot[j * TILE];
+        if (v < 0) break;
+        const double cc = esum[v >> 1];
+        s = (v & 1) ? s - cc : s + cc;
+    }
+    const int nzmin = p.n_lev[n] & 255;
+    if (ale != 0) {
+        const double asv = AT(p.areasvol, tbase(n, p.nlp), nzmin);
+        if (nzmin > 1) s = s - alpha * p.water_flux[n] * asv;
+        else s = s - alpha * p.water_flux[n] * asv + (1.0 - alpha) * sro[n];
+    } else if (nzmin <= 1) s = s + (1.0 - alpha) * sro[n];
+    rhs[n] = s;
+}
+// update_stiff_mat_ale (:1398-1468) as a row gather: one thread per own row walks its edges in ascending edge id and, per
+// edge, the two elements and their three corners — the order in which the reference's edge loop reaches the entries of
+// that row — so every entry receives its contributions in the reference's order without atomics.
+__global__ void LB(128) k_stiff_update(KP p, const int* __restrict__ rowptr, const int* __restrict__ colind, const double* __restrict__ dhe,
+                                       double factor, double* __restrict__ values) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.myN) return;
+    const int q0 = rowptr[n] - rowptr[0], q1 = rowptr[n + 1] - rowptr[0];
+    const int* slot = p.ne_slot + (size_t)(n >> 5) * p.maxdeg * TILE + (n & 31);
+    for (int j = 0; j < p.maxdeg; j++) {
+        const int v = slot[j * TILE];
+        if (v < 0) break;
+        const EdgeRec r = p.edge[v >> 1];
+        const bool second = v & 1;
+        for (int i = 0; i < 2; i++) {
+            const int be = i == 0 ? r.be1 : r.be2;
+            if (be < 0) continue;
+            const int elem = node_of_base(be, p.nlp);
+            const double dX = i == 0 ? r.dX1 : r.dX2, dY = i == 0 ? r.dY1 : r.dY2;
+            const double dh = dhe[elem];
+            for (int k = 0; k < 3; k++) {
+                double fy = -dh * (p.el_g[k * p.myE + elem] * dY - p.el_g[(k + 3) * p.myE + elem] * dX);
+                if (i == 1) fy = -fy;
+                if (second) fy = -fy;
+                const int col = node_of_base(p.el_nb[k * p.Eall + elem], p.nlp) + 1;
+                for (int q = q0; q < q1; q++)
+                    if (colind[q] == col) { values[q] = values[q] + fy * factor; break; }
+            }
+        }
+    }
+}
+// update_vel (oce_dyn.F90:101-124): UV += UV_rhs - g theta dt grad(d_eta) on own elements
+__global__ void LB(128) k_update_vel(KP p, const double2* __restrict__ UVr, const double* __restrict__ d_eta, double g, double theta,
+                                     double2* __restrict__ UV) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= p.myE) return;
+    const int n1 = node_of_base(p.el_nb[e], p.nlp), n2 = node_of_base(p.el_nb[p.Eall + e], p.nlp), n3 = node_of_base(p.el_nb[2 * p.Eall + e], p.nlp);
+    const double e1 = -(g * theta * p.dt * d_eta[n1]), e2 = -(g * theta * p.dt * d_eta[n2]), e3 = -(g * theta * p.dt * d_eta[n3]);
+    const double Fx = p.el_g[e] * e1 + p.el_g[p.myE + e] * e2 + p.el_g[2 * p.myE + e] * e3;
+    const double Fy = p.el_g[3 * p.myE + e] * e1 + p.el_g[4 * p.myE + e] * e2 + p.el_g[5 * p.myE + e] * e3;
+    const unsigned lv = p.el_lev[e];
+    const int nu = lv & 255, nlm = (lv >> 8) & 255, be = tbase(e, p.nlp);
+    for (int nz = nu; nz <= nlm; nz++) {
+        const double2 uv = AT(UV, be, nz), ur = AT(UVr, be, nz);
+        AT(UV, be, nz) = make_double2(uv.x + ur.x + Fx, uv.y + ur.y + Fy);
+    }
+}
+// UV in the reference layout (2, nl-1, elems) for the trip back to the host
+__global__ void LB(256) k_uv_to_ref(const double2* __restrict__ UV, double2* __restrict__ out, int E, int L, int nlp) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)E * L) return;
+    const int e = (int)(i / L), nz = (int)(i - (size_t)e * L) + 1;
+    out[i] = AT(UV, tbase(e, nlp), nz);
+}
+
+static void push_uv_rhs(TracerCtx& c, double* UV_rhs) {
+    const size_t ne = (size_t)c.Etiles * c.nlp * TILE;
+    if (c.UVr.n < ne) c.UVr.alloc(ne);
+    const int L = c.nl - 1;
+    ctx_push_node_field(c, UV_rhs, L, c.E, (double*)c.UVr.p, 2, 0, 2, 0);
+    ctx_push_node_field(c, UV_rhs, L, c.E, (double*)c.UVr.p, 2, 1, 2, 1);
+}
+
+extern "C" {
+
+// once, after fb200_ale_init: the CSR structure of ssh_stiff as init_stiff_mat_ale leaves it (rowptr(myDim_nod2D+1) 1-based,
+// colind_loc(nnz) LOCAL 1-based node numbers, values(nnz)), g and the namelist's alpha, theta (oce_ale.F90:1088-1354)
+void fb200_ssh_assembly_init(int* rowptr, int* colind_loc, double* values, double* g, double* alpha, double* theta) {
+    TracerCtx& c = tctx();
+    if (!ale_ready(c, "fb200_ssh_assembly_init")) return;
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    const int nnz = rowptr[c.myN] - rowptr[0];
+    c.sa_rowptr.alloc(c.myN + 1); c.sa_colind.alloc(nnz); c.sa_values.alloc(nnz); c.sa_rhs.alloc(c.N);
+    CUDA_CHECK(cudaMemcpyAsync(c.sa_rowptr.p, rowptr, (size_t)(c.myN + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(c.sa_colind.p, colind_loc, (size_t)nnz * sizeof(int), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(c.sa_values.p, values, (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice, st));
+    c.sa_g = *g; c.sa_alpha = *alpha; c.sa_theta = *theta;
+    CUDA_CHECK(cudaStreamSynchronize(st));
+}
+
+// update_stiff_mat_ale from the resident dhe of the last fb200_ale_step_begin; values_out(nnz) receives the updated matrix
+// (what the host hands to psolve); not called under linfs, as in the reference (oce_ale.F90:2686)
+void fb200_update_stiff_mat(double* values_out) {
+    TracerCtx& c = tctx();
+    if (!ale_ready(c, "fb200_update_stiff_mat")) return;
+    if (!c.sa_values.p) { fb_set_error(28, "fb200_update_stiff_mat before fb200_ssh_assembly_init"); return; }
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    KP p = make_kp(c, 0);
+    const double factor = c.sa_g * c.opt.dt * c.sa_alpha * c.sa_theta;
+    { ProfScope ps_("k_stiff_update", st); k_stiff_update<<<(c.myN + 127) / 128, 128, 0, st>>>(p, c.sa_rowptr.p, c.sa_colind.p, c.dhe.p, factor, c.sa_values.p); LAUNCH_CHECK(); }
+    CUDA_CHECK(cudaMemcpyAsync(values_out, c.sa_values.p, c.sa_values.n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+}
+
+// compute_ssh_rhs_ale: H2D UV_rhs(2, nl-1, elems) of the momentum step; ssh_rhs_out(N) (own entries, halo exchanged)
+void fb200_compute_ssh_rhs(double* UV_rhs, double* ssh_rhs_out) {
+    TracerCtx& c = tctx();
+    if (!ale_ready(c, "fb200_compute_ssh_rhs")) return;
+    if (!c.sa_rhs.p) { fb_set_error(28, "fb200_compute_ssh_rhs before fb200_ssh_assembly_init"); return; }
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    push_uv_rhs(c, UV_rhs);
+    KP p = make_kp(c, 0);
+    { ProfScope ps_("k_sshrhs_edge_sum", st); k_sshrhs_edge_sum<<<(c.myEd + 127) / 128, 128, 0, st>>>(p, c.UVr.p, c.sa_alpha, c.esum.p); LAUNCH_CHECK(); }
+    { ProfScope ps_("k_sshrhs_node", st); k_sshrhs_node<<<(c.N + 127) / 128, 128, 0, st>>>(p, c.esum.p, c.ssh_rhs_old.p, c.sa_rhs.p, c.sa_alpha, c.which_ale); LAUNCH_CHECK(); }
+    if (comm_nranks() > 1) halo_exchange_flat(*c.halo_nod, c.sa_rhs.p, st);          // exchange_nod(ssh_rhs), :1570
+    CUDA_CHECK(cudaMemcpyAsync(ssh_rhs_out, c.sa_rhs.p, (size_t)c.N * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+}
+
+// update_vel with the UV_rhs of the last fb200_compute_ssh_rhs and the SSH solution d_eta(N): the resident UV becomes the
+// velocity of the new step (pass UV = NULL to the following fb200_ale_step_begin) and UV_out(2, nl-1, elems) returns it to
+// the host's momentum code.  eta_n += d_eta stays on the host (one line of oce_dyn.F90:125).
+void fb200_update_vel(double* d_eta, double* UV_out) {
+    TracerCtx& c = tctx();
+    if (!ale_ready(c, "fb200_update_vel")) return;
+    if (!c.UVr.p) { fb_set_error(28, "fb200_update_vel before fb200_compute_ssh_rhs"); return; }
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    if (c.sa_eta.n < (size_t)c.N) c.sa_eta.alloc(c.N);
+    CUDA_CHECK(cudaMemcpyAsync(c.sa_eta.p, d_eta, (size_t)c.N * sizeof(double), cudaMemcpyHostToDevice, st));
+    KP p = make_kp(c, 0);
+    { ProfScope ps_("k_update_vel", st); k_update_vel<<<(c.myE + 127) / 128, 128, 0, st>>>(p, c.UVr.p, c.sa_eta.p, c.sa_g, c.sa_theta, c.UV.p); LAUNCH_CHECK(); }
+    if (comm_nranks() > 1) halo_exchange_tiled(*c.halo_elem, (double*)c.UV.p, c.nlp, 2, st);      // exchange_elem(UV), oce_dyn.F90:126
+    const int L = c.nl - 1;
+    const size_t cnt = (size_t)c.E * L;
+    if (c.stage.n < 2 * cnt) c.stage.alloc(2 * cnt);
+    { ProfScope ps_("k_uv_to_ref", st); k_uv_to_ref<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(c.UV.p, (double2*)c.stage.p, c.E, L, c.nlp); LAUNCH_CHECK(); }
+    CUDA_CHECK(cudaMemcpyAsync(UV_out, c.stage.p, 2 * cnt * sizeof(double), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
 }
 

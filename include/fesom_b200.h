@@ -148,13 +148,26 @@ void fb200_solve_tracers_ale_resident(double* tr_arr_out);
 /* Device-side producers of the tracer step's inputs (any number of partitions: with more than one the four exchanges
  * of oce_ale.F90:1654,1663,2135-2136 run over NCCL, fb200_init_halo required): compute_hbar_ale (src/oce_ale.F90:1585-1676),
  * vert_vel_ale (:1692-2204; linfs, plain zlevel, zstar) and update_thickness_ale (:800-993).  With them the thicknesses,
- * level depths and vertical velocities stay resident; per step the host sends UV (after update_vel) and water_flux and
+ * level depths and vertical velocities stay resident; per step the host sends UV (after update_vel; NULL = the resident velocity fb200_update_vel produced) and water_flux and
  * receives hbar(N), ssh_rhs_old(N), dhe(myDim_elem2D).  Call order per step: fb200_ale_step_begin, [fb200_push_state_early
  * for Kv and the surface fluxes], fb200_solve_tracers_ale_resident, fb200_ale_step_end.  Once: fb200_push_step_state with
  * the initial thicknesses, then fb200_ale_init(which_ale 0 linfs | 1 zlevel | 2 zstar, w_max_cfl, hbar). */
 void fb200_ale_init(int* which_ale, double* w_max_cfl, double* hbar);
 void fb200_ale_step_begin(double* UV, double* water_flux, double* hbar_out, double* ssh_rhs_old_out, double* dhe_out);
 void fb200_ale_step_end(void);
+/* SSH assembly on the device, for hosts that run the ALE producers above (fb200_ale_init required):
+ *   fb200_ssh_assembly_init  once: ssh_stiff as init_stiff_mat_ale leaves it (src/oce_ale.F90:1088-1354) — rowptr(myDim_nod2D+1)
+ *                            1-based, colind_loc(nnz) LOCAL 1-based node numbers, values(nnz) — and g, alpha, theta;
+ *   fb200_update_stiff_mat   update_stiff_mat_ale (:1371-1470) from the resident dhe; values_out(nnz) = updated matrix for psolve;
+ *   fb200_compute_ssh_rhs    compute_ssh_rhs_ale (:1478-1572): H2D UV_rhs(2,nl-1,elems) of the momentum step, resident UV, helem,
+ *                            water_flux, ssh_rhs_old; ssh_rhs_out(N), halo entries exchanged (:1570);
+ *   fb200_update_vel         update_vel (src/oce_dyn.F90:101-127) with that UV_rhs and the solution d_eta(N): the resident UV
+ *                            becomes the new velocity (then pass UV = NULL to fb200_ale_step_begin), UV_out(2,nl-1,elems)
+ *                            returns it to the host's momentum code; eta_n += d_eta stays on the host. */
+void fb200_ssh_assembly_init(int* rowptr, int* colind_loc, double* values, double* g, double* alpha, double* theta);
+void fb200_update_stiff_mat(double* values_out);
+void fb200_compute_ssh_rhs(double* UV_rhs, double* ssh_rhs_out);
+void fb200_update_vel(double* d_eta, double* UV_out);
 /* min and max of the device-resident tracer *tr_num (1-based) over this partition's own wet cells: what check_blowup and
  * the extrema lines of write_step_info (src/write_step_info.F90:220-504) test; lets a host that keeps the tracers resident
  * monitor them without pulling the fields (combine the ranks with MPI_Allreduce as the reference does) */

@@ -130,3 +130,20 @@ def soufflet_zonal_setup(hm, nybins=100, ysize=2000000.0, lat0=0.0):
         ztem[bpos[e] - 1, :k] += ((T[en[e, 0], :k] + T[en[e, 1], :k]) + T[en[e, 2], :k]) / 3.0
     ztem = np.ascontiguousarray(ztem / (znum + 0.001))
     return ztem, np.ascontiguousarray(T.copy()), lat0, dy, 1.0 / 50.0 / 24.0 / 3600.0
+
+
+def update_vel_host(hm, g=9.81):
+    """update_vel (oce_dyn.F90:101-127) on the host model, own elements: UV += UV_rhs - g theta dt grad(d_eta); eta_n += d_eta"""
+    myE, theta, dt = hm.ipar("myDim_elem2D"), hm.par("theta"), hm.par("dt")
+    en = hm["elem2D_nodes"][:myE] - 1
+    eta = -(g * theta * dt * hm["d_eta"][en])                          # (myE, 3)
+    gs = hm["gradient_sca"][:myE]                                      # (myE, 6)
+    Fx = (gs[:, 0] * eta[:, 0] + gs[:, 1] * eta[:, 1]) + gs[:, 2] * eta[:, 2]
+    Fy = (gs[:, 3] * eta[:, 0] + gs[:, 4] * eta[:, 1]) + gs[:, 5] * eta[:, 2]
+    nl = hm.ipar("nl")
+    lev = np.arange(1, nl)[None, :]
+    act = (lev >= hm["ulevels"][:myE, None]) & (lev <= (hm["nlevels"][:myE] - 1)[:, None])
+    UV, UVr = hm["UV"], hm["UV_rhs"]
+    UV[:myE, :, 0] = np.where(act, (UV[:myE, :, 0] + UVr[:myE, :, 0]) + Fx[:, None], UV[:myE, :, 0])
+    UV[:myE, :, 1] = np.where(act, (UV[:myE, :, 1] + UVr[:myE, :, 1]) + Fy[:, None], UV[:myE, :, 1])
+    hm["eta_n"][:] = hm["eta_n"] + hm["d_eta"]
