@@ -230,8 +230,8 @@ class TracerEngine:
     def ssh_assembly_init(self, g=9.81):
         """device-side compute_ssh_rhs_ale / update_stiff_mat_ale / update_vel: hand over ssh_stiff and g, alpha, theta"""
         hm = self.hm
-        self.L.fb200_ssh_assembly_init(_p(hm.arr("ssh_rowptr")), _p(hm.arr("ssh_colind_loc")), _p(hm.arr("ssh_values")), _d(g),
-                                       _d(hm.par("alpha")), _d(hm.par("theta")))
+        self.L.fb200_ssh_assembly_init(_p(hm.arr("ssh_rowptr")), _p(hm.arr("ssh_colind_loc")), _p(hm.arr("ssh_values")), _p(hm.arr("dhe")),
+                                       _p(hm.arr("ssh_rhs_old")), _d(g), _d(hm.par("alpha")), _d(hm.par("theta")))
         _check(self.L)
 
     def update_stiff_mat(self):

@@ -1582,8 +1582,11 @@ static void push_uv_rhs(TracerCtx& c, double* UV_rhs) {
 extern "C" {
 
 // once, after fb200_ale_init: the CSR structure of ssh_stiff as init_stiff_mat_ale leaves it (rowptr(myDim_nod2D+1) 1-based,
-// colind_loc(nnz) LOCAL 1-based node numbers, values(nnz)), g and the namelist's alpha, theta (oce_ale.F90:1088-1354)
-void fb200_ssh_assembly_init(int* rowptr, int* colind_loc, double* values, double* g, double* alpha, double* theta) {
+// colind_loc(nnz) LOCAL 1-based node numbers, values(nnz)), the host's current dhe(myDim_elem2D) and ssh_rhs_old(N) (what its
+// last compute_hbar_ale left; from then on fb200_ale_step_begin produces them), g and the namelist's alpha, theta
+// (oce_ale.F90:1088-1354)
+void fb200_ssh_assembly_init(int* rowptr, int* colind_loc, double* values, double* dhe, double* ssh_rhs_old, double* g, double* alpha,
+                             double* theta) {
     TracerCtx& c = tctx();
     if (!ale_ready(c, "fb200_ssh_assembly_init")) return;
     fb_copy_sync();
@@ -1593,6 +1596,8 @@ void fb200_ssh_assembly_init(int* rowptr, int* colind_loc, double* values, doubl
     CUDA_CHECK(cudaMemcpyAsync(c.sa_rowptr.p, rowptr, (size_t)(c.myN + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
     CUDA_CHECK(cudaMemcpyAsync(c.sa_colind.p, colind_loc, (size_t)nnz * sizeof(int), cudaMemcpyHostToDevice, st));
     CUDA_CHECK(cudaMemcpyAsync(c.sa_values.p, values, (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(c.dhe.p, dhe, (size_t)c.myE * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(c.ssh_rhs_old.p, ssh_rhs_old, (size_t)c.N * sizeof(double), cudaMemcpyHostToDevice, st));
     c.sa_g = *g; c.sa_alpha = *alpha; c.sa_theta = *theta;
     CUDA_CHECK(cudaStreamSynchronize(st));
 }

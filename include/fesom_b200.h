@@ -157,14 +157,16 @@ void fb200_ale_step_begin(double* UV, double* water_flux, double* hbar_out, doub
 void fb200_ale_step_end(void);
 /* SSH assembly on the device, for hosts that run the ALE producers above (fb200_ale_init required):
  *   fb200_ssh_assembly_init  once: ssh_stiff as init_stiff_mat_ale leaves it (src/oce_ale.F90:1088-1354) — rowptr(myDim_nod2D+1)
- *                            1-based, colind_loc(nnz) LOCAL 1-based node numbers, values(nnz) — and g, alpha, theta;
+ *                            1-based, colind_loc(nnz) LOCAL 1-based node numbers, values(nnz) —, the host's current
+ *                            dhe(myDim_elem2D) and ssh_rhs_old(N) of its last compute_hbar_ale, and g, alpha, theta;
  *   fb200_update_stiff_mat   update_stiff_mat_ale (:1371-1470) from the resident dhe; values_out(nnz) = updated matrix for psolve;
  *   fb200_compute_ssh_rhs    compute_ssh_rhs_ale (:1478-1572): H2D UV_rhs(2,nl-1,elems) of the momentum step, resident UV, helem,
  *                            water_flux, ssh_rhs_old; ssh_rhs_out(N), halo entries exchanged (:1570);
  *   fb200_update_vel         update_vel (src/oce_dyn.F90:101-127) with that UV_rhs and the solution d_eta(N): the resident UV
  *                            becomes the new velocity (then pass UV = NULL to fb200_ale_step_begin), UV_out(2,nl-1,elems)
  *                            returns it to the host's momentum code; eta_n += d_eta stays on the host. */
-void fb200_ssh_assembly_init(int* rowptr, int* colind_loc, double* values, double* g, double* alpha, double* theta);
+void fb200_ssh_assembly_init(int* rowptr, int* colind_loc, double* values, double* dhe, double* ssh_rhs_old, double* g, double* alpha,
+                             double* theta);
 void fb200_update_stiff_mat(double* values_out);
 void fb200_compute_ssh_rhs(double* UV_rhs, double* ssh_rhs_out);
 void fb200_update_vel(double* d_eta, double* UV_out);
