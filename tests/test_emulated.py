@@ -1,0 +1,57 @@
+"""CPU execution of the CUDA kernels' SOURCE through the CUDA-on-CPU emulation of tests/emu (test infrastructure, see
+tests/emu/cuda_emu.h): fesom2_b200/csrc/{tracer_kernels,context,capi}.cu are rewritten into plain C++ (launches -> fiber
+scheduler) and compiled with g++ -ffp-contract=off, then the SAME parity tests the GPU suite runs are called against that
+library.  It checks the kernels' logic and arithmetic order before GPU time is spent; it says nothing about races,
+occupancy or speed, and it is not a fallback: the product library never loads it (tests/test_abi.py checks that the
+product fails without a device)."""
+import pytest
+
+
+@pytest.fixture()
+def emulated(monkeypatch):
+    from fesom2_b200 import api
+    from tests import emu
+    monkeypatch.setattr(api, "_lib", emu.load())
+    yield
+    
+
+def test_emulated_tracer_step_is_bit_identical_to_oracle(emulated):
+    import numpy as np
+    from fesom2_b200 import api
+    from oracle import binding as ob
+    from tests import util
+    A, B = util.build_model("pi"), util.build_model("pi")
+    o = ob.TracerOracle(A)
+    eng = api.TracerEngine(B)
+    eng.push_step_state()
+    g_tr, g_tro = B["tr_arr"].copy(), B["tr_arr_old"].copy()
+    for s in range(2):
+        o.step()
+        eng.solve_tracers_ale(g_tr, g_tro)
+        assert np.array_equal(g_tr, A["tr_arr"]) and np.array_equal(g_tro, A["tr_arr_old"]), s
+    eng.close()
+
+
+@pytest.mark.parametrize("resident", [False, True])
+def test_emulated_relax_zonal_temp(emulated, resident):
+    from tests import test_gpu_zz_zonal as t
+    t.test_relax_zonal_temp_matches_oracle(resident)
+
+
+@pytest.mark.parametrize("accuracy", [8, 4])
+def test_emulated_output_means(emulated, accuracy):
+    from tests import test_gpu_zz_means as t
+    t.test_device_means_match_stream_restatement(accuracy)
+
+
+@pytest.mark.parametrize("name,kw", [("pi", {"which_ale": "zstar"}), ("band", {"which_ale": "zlevel", "water_flux": 2e-7}), ("soufflet", {})])
+def test_emulated_ssh_assembly(emulated, name, kw):
+    from tests import test_gpu_zz_ssh_assembly as t
+    t.test_device_ssh_assembly_matches_host_mirror(name, kw)
+
+
+@pytest.mark.parametrize("name,kw", [("band", {"which_ale": "zstar", "water_flux": 2e-7}),
+                                     ("pi", {"which_ale": "zstar", "w_split": True, "w_max_cfl": 0.2, "umax": 0.5})])
+def test_emulated_ale_producers(emulated, name, kw):
+    from tests import test_gpu_tracer as t
+    t.test_device_ale_producers_match_host_mirror(name, kw)
