@@ -1,9 +1,8 @@
 """TEST INFRASTRUCTURE — CUDA-on-CPU emulation of the tracer library (see cuda_emu.h).
 
-build() rewrites fesom2_b200/csrc/{tracer_kernels,context,capi,comm}.cu into plain C++ (kernel launches become calls of
+build() rewrites fesom2_b200/csrc/*.cu into plain C++ (kernel launches become calls of
 emu_launch, dynamic shared memory a per-launch buffer), compiles them with g++ -ffp-contract=off (the counterpart of
-nvcc --fmad=false) together with the fiber scheduler, an NCCL-over-files stand-in (nccl.h, nccl_emu.cpp) and stubs for
-the SSH solver's symbols into tests/emu/_build/libfesom_b200_emu.so.
+nvcc --fmad=false) together with the fiber scheduler, an NCCL-over-files stand-in (nccl.h, nccl_emu.cpp) into tests/emu/_build/libfesom_b200_emu.so.
 load() returns it as a ctypes library set up like fesom2_b200.api.lib().  Only tests/test_emulated.py uses it."""
 import ctypes as C
 import os
@@ -15,7 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "fesom2_b200", "csrc")
 OUT = os.path.join(HERE, "_build")
 SO = os.path.join(OUT, "libfesom_b200_emu.so")
-SOURCES = ["tracer_kernels.cu", "context.cu", "capi.cu", "comm.cu"]
+SOURCES = ["tracer_kernels.cu", "context.cu", "capi.cu", "comm.cu", "ssh_solver.cu", "ssh_amg.cu"]
 
 
 def _match_paren(s, i):
@@ -80,7 +79,7 @@ def build(force=False):
         with open(dst, "w") as fh:
             fh.write(t)
         cpp.append(dst)
-    cpp += [os.path.join(HERE, "cuda_emu.cpp"), os.path.join(HERE, "stubs_emu.cpp"), os.path.join(HERE, "nccl_emu.cpp")]
+    cpp += [os.path.join(HERE, "cuda_emu.cpp"), os.path.join(HERE, "nccl_emu.cpp")]
     cmd = ["g++", "-std=c++17", "-O1", "-g", "-ffp-contract=off", "-fPIC", "-shared", "-include", os.path.join(HERE, "cuda_emu.h"),
            "-I", HERE, "-I", CSRC, "-I", os.path.join(ROOT, "include"), "-o", SO] + cpp
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
@@ -98,4 +97,5 @@ def load():
     L.fb200_last_ms.argtypes = [C.c_char_p]
     L.fb200_debug_fetch.argtypes = [C.c_char_p, C.c_void_p]
     L.fb200_set_stream.argtypes = [C.c_void_p]
+    L.fb200_psolver_use_graph(C.byref(C.c_int(0)))      # CUDA graphs are not emulated: plain launches (the same kernels)
     return L

@@ -66,6 +66,19 @@ static inline const char* cudaGetErrorString(cudaError_t) { return "emulated"; }
 static inline cudaError_t cudaHostRegister(void*, size_t, unsigned) { return 0; }
 static inline cudaError_t cudaHostUnregister(void*) { return 0; }
 template <class F> static inline cudaError_t cudaFuncSetAttribute(F, int, int) { return 0; }
+template <class T> static inline cudaError_t cudaMallocHost(T** p, size_t n) { *p = (T*)malloc(n ? n : 1); return *p ? 0 : 2; }
+static inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }
+// CUDA graphs are not emulated (tests/emu/__init__.py switches them off with fb200_psolver_use_graph(0)): capture reports an error
+typedef struct emu_graph_* cudaGraph_t;
+typedef struct emu_graph_exec_* cudaGraphExec_t;
+enum { cudaStreamCaptureModeThreadLocal = 1 };
+static inline cudaError_t cudaStreamBeginCapture(cudaStream_t, int) { return 900; }
+static inline cudaError_t cudaStreamEndCapture(cudaStream_t, cudaGraph_t* g) { *g = nullptr; return 900; }
+static inline cudaError_t cudaGraphInstantiate(cudaGraphExec_t*, cudaGraph_t, unsigned long long) { return 900; }
+static inline cudaError_t cudaGraphDestroy(cudaGraph_t) { return 0; }
+static inline cudaError_t cudaGraphExecDestroy(cudaGraphExec_t) { return 0; }
+static inline cudaError_t cudaGraphLaunch(cudaGraphExec_t, cudaStream_t) { return 900; }
+static inline void __threadfence() {}
 
 // ---- execution model
 struct emu_cfg {
@@ -96,6 +109,7 @@ template <class T> static inline T __shfl_sync(unsigned, T v, int src) {
 }
 template <class T> static inline T atomicAdd(T* p, T v) { T o = *p; *p = o + v; return o; }
 template <class T> static inline T __ldg(const T* p) { return *p; }
+template <class T> static inline T __ldcg(const T* p) { return *p; }
 using std::fma; using std::fabs; using std::floor; using std::sqrt;
 static inline int max(int a, int b) { return a > b ? a : b; }
 static inline int min(int a, int b) { return a < b ? a : b; }

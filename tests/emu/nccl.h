@@ -7,7 +7,7 @@
 typedef struct emu_nccl_comm* ncclComm_t;
 typedef int ncclResult_t;
 enum { ncclSuccess = 0 };
-enum ncclDataType_t { ncclDouble = 8 };
+enum ncclDataType_t { ncclInt32 = 4, ncclDouble = 8 };            // value = bytes per element
 enum ncclRedOp_t { ncclSum = 0 };
 struct ncclUniqueId { char internal[128]; };
 const char* ncclGetErrorString(ncclResult_t);
@@ -18,4 +18,5 @@ ncclResult_t ncclGroupStart();
 ncclResult_t ncclGroupEnd();
 ncclResult_t ncclSend(const void* buf, size_t count, ncclDataType_t, int peer, ncclComm_t comm, void* stream);
 ncclResult_t ncclRecv(void* buf, size_t count, ncclDataType_t, int peer, ncclComm_t comm, void* stream);
+ncclResult_t ncclAllGather(const void* send, void* recv, size_t sendcount, ncclDataType_t, ncclComm_t comm, void* stream);
 ncclResult_t ncclAllReduce(const void* send, void* recv, size_t count, ncclDataType_t, ncclRedOp_t, ncclComm_t comm, void* stream);

@@ -77,15 +77,24 @@ ncclResult_t ncclGroupEnd() {
     pending.clear();
     return r;
 }
-ncclResult_t ncclSend(const void* buf, size_t count, ncclDataType_t, int peer, ncclComm_t comm, void*) {
+ncclResult_t ncclSend(const void* buf, size_t count, ncclDataType_t dt, int peer, ncclComm_t comm, void*) {
     emu_nccl_comm& c = *comm;
     const std::string path = c.dir + "/p2p_s" + std::to_string(c.rank) + "_d" + std::to_string(peer) + "_" + std::to_string(c.sseq[peer]++) + ".bin";
-    return write_file(path, buf, count * sizeof(double)) ? 0 : 1;
+    return write_file(path, buf, count * (size_t)dt) ? 0 : 1;
 }
-ncclResult_t ncclRecv(void* buf, size_t count, ncclDataType_t, int peer, ncclComm_t comm, void*) {
-    Pending p{buf, count * sizeof(double), peer, comm};
+ncclResult_t ncclRecv(void* buf, size_t count, ncclDataType_t dt, int peer, ncclComm_t comm, void*) {
+    Pending p{buf, count * (size_t)dt, peer, comm};
     if (group_depth > 0) { pending.push_back(p); return 0; }
     return do_recv(p);
+}
+ncclResult_t ncclAllGather(const void* send, void* recv, size_t sendcount, ncclDataType_t dt, ncclComm_t comm, void*) {
+    emu_nccl_comm& c = *comm;
+    const long s = c.arseq++;
+    const size_t bytes = sendcount * (size_t)dt;
+    if (!write_file(c.dir + "/ar" + std::to_string(s) + "_r" + std::to_string(c.rank) + ".bin", send, bytes)) return 1;
+    for (int r = 0; r < c.n; r++)
+        if (!read_file(c.dir + "/ar" + std::to_string(s) + "_r" + std::to_string(r) + ".bin", (char*)recv + (size_t)r * bytes, bytes, false)) return 1;
+    return 0;
 }
 ncclResult_t ncclAllReduce(const void* send, void* recv, size_t count, ncclDataType_t, ncclRedOp_t, ncclComm_t comm, void*) {
     emu_nccl_comm& c = *comm;

@@ -68,7 +68,7 @@ def main():
     name = names[0] if names else "pi"
     steps = 2
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-    emulate = "--emulate" in sys.argv                         # CPU: the kernels' source through tests/emu, NCCL over files, no SSH solve
+    emulate = "--emulate" in sys.argv                         # CPU: the kernels' source through tests/emu, NCCL over files
     if emulate:
         from tests import emu
         api._lib = emu.load()
@@ -102,35 +102,29 @@ def main():
         o.step()
     own = r.nod[:r.myDim_nod2D] - 1
     alln = r.nod - 1
-    if emulate:
-        sol = sol_mg = x_ref = np.ones(hm.ipar("myDim_nod2D"))
-        its = its_mg = its_ref = 0
-        res = res_mg = 0.0
-    else:
-        # SSH solve on the partitioned system
-        sol = np.zeros_like(lm["d_eta"])
-        s = api.SSHSolver(lm, pc="bj")
-        s.solve(new_values=1, sol=sol)
-        its, res = s.info()
-        # the same solve with the multigrid preconditioner (each rank: V-cycle on its own diagonal block)
-        sol_mg = np.zeros_like(lm["d_eta"])
-        s2 = api.SSHSolver(lm, ident=2, pc="amg", amg=(0.08, 0.8, 4, 50))
-        s2.solve(new_values=1, sol=sol_mg)
-        its_mg, res_mg = s2.info()
-        rp = hm["ssh_rowptr"]
-        n = hm.ipar("myDim_nod2D")
-        x_ref, its_ref, res_ref, _ = ob.ssh_solve(rp - rp[0], hm["ssh_colind"] - 1, hm["ssh_values"], hm["ssh_rhs"][:n], np.zeros(n), 1, 1)
+    # SSH solve on the partitioned system
+    sol = np.zeros_like(lm["d_eta"])
+    s = api.SSHSolver(lm, pc="bj")
+    s.solve(new_values=1, sol=sol)
+    its, res = s.info()
+    # the same solve with the multigrid preconditioner (each rank: V-cycle on its own diagonal block)
+    sol_mg = np.zeros_like(lm["d_eta"])
+    s2 = api.SSHSolver(lm, ident=2, pc="amg", amg=(0.08, 0.8, 4, 50))
+    s2.solve(new_values=1, sol=sol_mg)
+    its_mg, res_mg = s2.info()
+    rp = hm["ssh_rowptr"]
+    n = hm.ipar("myDim_nod2D")
+    x_ref, its_ref, res_ref, _ = ob.ssh_solve(rp - rp[0], hm["ssh_colind"] - 1, hm["ssh_values"], hm["ssh_rhs"][:n], np.zeros(n), 1, 1)
     ok_own = bool(np.array_equal(tr[:, :r.myDim_nod2D], hm["tr_arr"][:, own]) and np.array_equal(tro[:, :r.myDim_nod2D], hm["tr_arr_old"][:, own]))
     ok_halo = bool(np.array_equal(tr, hm["tr_arr"][:, alln]))
     err_t = float(np.abs(tr[:, :r.myDim_nod2D] - hm["tr_arr"][:, own]).max())
-    err_s = 0.0 if emulate else float(util.rel_err(sol[:r.myDim_nod2D], x_ref[own]))
-    err_mg = 0.0 if emulate else float(util.rel_err(sol_mg[:r.myDim_nod2D], x_ref[own]))
+    err_s = float(util.rel_err(sol[:r.myDim_nod2D], x_ref[own]))
+    err_mg = float(util.rel_err(sol_mg[:r.myDim_nod2D], x_ref[own]))
     verdict = dict(rank=rank, own_bitexact=ok_own, halo_bitexact=ok_halo, tracer_maxabs=err_t, ssh_rel=err_s, its=its, its_ref=its_ref,
                    res=res, ssh_rel_mg=err_mg, its_mg=its_mg, res_mg=res_mg, ale=ale, launches=int(api.lib().fb200_kernel_launches()))
     allv = [None] * world
     dist.all_gather_object(allv, verdict)
-    if not emulate:
-        api.lib().psolver_final()
+    api.lib().psolver_final()
     api.comm_finalize()
     if rank == 0:
         for v in allv:

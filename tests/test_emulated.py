@@ -1,5 +1,5 @@
 """CPU execution of the CUDA kernels' SOURCE through the CUDA-on-CPU emulation of tests/emu (test infrastructure, see
-tests/emu/cuda_emu.h): fesom2_b200/csrc/{tracer_kernels,context,capi}.cu are rewritten into plain C++ (launches -> fiber
+tests/emu/cuda_emu.h): fesom2_b200/csrc/*.cu are rewritten into plain C++ (launches -> fiber
 scheduler) and compiled with g++ -ffp-contract=off, then the SAME parity tests the GPU suite runs are called against that
 library.  It checks the kernels' logic and arithmetic order before GPU time is spent; it says nothing about races,
 occupancy or speed, and it is not a fallback: the product library never loads it (tests/test_abi.py checks that the
@@ -55,3 +55,19 @@ def test_emulated_ssh_assembly(emulated, name, kw):
 def test_emulated_ale_producers(emulated, name, kw):
     from tests import test_gpu_tracer as t
     t.test_device_ale_producers_match_host_mirror(name, kw)
+
+
+@pytest.mark.parametrize("name", ["pi", "soufflet"])
+def test_emulated_psolve(emulated, name):
+    """the SSH solver's kernels (persistent reducing SpMV, block-Jacobi and multigrid V-cycle) under the emulation, CUDA
+    graphs off: the same checks against the oracle and the reference's golden solution as on the GPU"""
+    from tests import test_gpu_ssh as t
+    t.test_psolve_matches_oracle(name, 4)
+    t.test_psolve_matches_reference_golden(name)
+    t.test_psolve_multigrid_matches_reference_and_oracle(name)
+
+
+def test_emulated_psolve_value_refresh(emulated):
+    from tests import test_gpu_ssh as t
+    t.test_value_refresh_and_warm_start()
+    t.test_psolve_multigrid_single_level_is_jacobi()
