@@ -80,7 +80,7 @@ def build(force=False):
             fh.write(t)
         cpp.append(dst)
     cpp += [os.path.join(HERE, "cuda_emu.cpp"), os.path.join(HERE, "nccl_emu.cpp")]
-    cmd = ["g++", "-std=c++17", "-O1", "-g", "-ffp-contract=off", "-fPIC", "-shared", "-include", os.path.join(HERE, "cuda_emu.h"),
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-include", os.path.join(HERE, "cuda_emu.h"),
            "-I", HERE, "-I", CSRC, "-I", os.path.join(ROOT, "include"), "-o", SO] + cpp
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:

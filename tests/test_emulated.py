@@ -57,7 +57,7 @@ def test_emulated_ale_producers(emulated, name, kw):
     t.test_device_ale_producers_match_host_mirror(name, kw)
 
 
-@pytest.mark.parametrize("name", ["pi", "soufflet"])
+@pytest.mark.parametrize("name", ["pi"])
 def test_emulated_psolve(emulated, name):
     """the SSH solver's kernels (persistent reducing SpMV, block-Jacobi and multigrid V-cycle) under the emulation, CUDA
     graphs off: the same checks against the oracle and the reference's golden solution as on the GPU"""
