@@ -306,7 +306,9 @@ class TracerEngine:
         hm = self.hm
         nl = hm.ipar("nl")
         N = hm.ipar("myDim_nod2D") + hm.ipar("eDim_nod2D")
-        if name == "adf_h":
+        if name == "edge_perm":
+            shape = (hm.ipar("myDim_edge2D"),)
+        elif name == "adf_h":
             shape = (hm.ipar("myDim_edge2D"), nl - 1)
         elif name in ("tr_xy_x", "tr_xy_y"):
             shape = (hm.ipar("myDim_elem2D") + hm.ipar("eDim_elem2D") + hm.ipar("eXDim_elem2D"), nl - 1)

@@ -373,12 +373,20 @@ void fb200_debug_fetch(const char* name, double* out) {
     std::string s(name);
     const double* f = nullptr;
     int lev = c.nl - 1, cnt = c.N;
+    if (s == "edge_perm") { for (int e = 0; e < c.myEd; e++) out[e] = (double)c.edge_perm[e]; return; }   // internal id of reference edge e
     if (s == "ttfAB") { f = c.Told.p; }
     else f = tracer_debug_field(c, name, &kind, &ncomp, &comp);
     if (!f) { fb_set_error(37, "fb200_debug_fetch: unknown field " + s); return; }
     if (s == "adf_v" || kind == 3) lev = c.nl;
     if (kind == 1) cnt = c.myEd;
     if (kind == 2) cnt = c.Eall;
+    if (kind == 1) {                                   // edge field: stored in the internal edge order, returned in the reference's
+        std::vector<double> tmp((size_t)lev * cnt);
+        ctx_pull_node_field(c, f, lev, cnt, tmp.data(), ncomp, comp);
+        if (!fb_ok()) return;
+        for (int e = 0; e < cnt; e++) memcpy(out + (size_t)e * lev, tmp.data() + (size_t)c.edge_perm[e] * lev, (size_t)lev * sizeof(double));
+        return;
+    }
     ctx_pull_node_field(c, f, lev, cnt, out, ncomp, comp);
 }
 

@@ -87,7 +87,8 @@ struct TracerCtx {
     int nie_ld = 0;
     // static device data
     DevBuf<EdgeRec> edge; DevBuf<EdgeHo> edgeho;
-    DevBuf<int> ne_slot;            // [Ntile][maxdeg][32]   (edge<<1)|second, -1 = none; ascending reference edge id
+    std::vector<int> edge_perm;     // internal edge id of reference edge e (identity unless FB200_EDGE_ORDER=tile, see ctx_commit)
+    DevBuf<int> ne_slot;            // [Ntile][maxdeg][32]   (internal edge<<1)|second, -1 = none; in ascending REFERENCE edge id
     // per (node, incident-edge slot) copies of the edge data, [Ntile][maxdeg][32]: a warp of 32 consecutive nodes reads
     // every item fully coalesced (the edge-indexed records would be a scattered 64-byte gather per lane)
     DevBuf<int> tile_deg;                        // [Ntile] max degree within the tile

@@ -179,14 +179,36 @@ void ctx_commit(TracerCtx& c) {
     std::vector<unsigned> n_lev(N);
     for (int n = 0; n < N; n++) n_lev[n] = pack4(c.h_ulev_n[n], c.h_nlev_n[n], c.h_nlmin[n], c.h_ulmax[n]);
     c.n_lev.upload(n_lev); c.n_nbl.upload(c.h_nbl); c.n_znb.upload(c.h_znb);
-    // edges
+    // edges.  Internal numbering: the reference's (identity), or with FB200_EDGE_ORDER=tile an experimental one in which the
+    // edges that share a FIRST node's rank k (k-th edge of that node in reference order) are consecutive over the 32 nodes of
+    // a node tile — sorted by (tile of n1, k, lane of n1) — so that slot j of 32 consecutive nodes gathers (nearly)
+    // consecutive edge-field entries instead of entries 3 apart (profiles/r01_gather_coalescing.txt).  Only the storage
+    // order of the edge-indexed tables and fields changes: every per-node sum still runs in ascending REFERENCE edge id, so
+    // results are bit-identical (tests/test_emulated.py runs both orders).
+    std::vector<int>& perm = c.edge_perm;
+    perm.resize(myEd);
+    for (int e = 0; e < myEd; e++) perm[e] = e;
+    {
+        const char* eo = getenv("FB200_EDGE_ORDER");
+        if (eo && !strcmp(eo, "tile")) {
+            std::vector<int> rank(myEd), cnt(N, 0), order(myEd);
+            for (int e = 0; e < myEd; e++) { const int n1 = c.h_edges[2 * (size_t)e] - 1; rank[e] = (n1 >= 0 && n1 < N) ? cnt[n1]++ : 0; order[e] = e; }
+            std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+                const int na = c.h_edges[2 * (size_t)a] - 1, nb = c.h_edges[2 * (size_t)b] - 1;
+                if ((na >> 5) != (nb >> 5)) return (na >> 5) < (nb >> 5);
+                if (rank[a] != rank[b]) return rank[a] < rank[b];
+                return (na & 31) < (nb & 31);
+            });
+            for (int k = 0; k < myEd; k++) perm[order[k]] = k;
+        }
+    }
     std::vector<EdgeRec> er(myEd); std::vector<EdgeHo> eh(myEd);
     std::vector<int> deg(N, 0);
     for (int e = 0; e < myEd; e++) {
         const int n1 = c.h_edges[2 * (size_t)e], n2 = c.h_edges[2 * (size_t)e + 1];
         const int t1 = c.h_edge_tri[2 * (size_t)e], t2 = c.h_edge_tri[2 * (size_t)e + 1];
         if (n1 < 1 || n2 < 1 || n1 > N || n2 > N || t1 < 1 || t1 > Eall || t2 > Eall) { fb_set_error(14, "edge table out of range"); return; }
-        EdgeRec& r = er[e]; memset(&r, 0, sizeof(r));
+        EdgeRec& r = er[perm[e]]; memset(&r, 0, sizeof(r));
         r.bn1 = tile_base(n1 - 1, nlp); r.bn2 = tile_base(n2 - 1, nlp);
         r.be1 = tile_base(t1 - 1, nlp); r.be2 = t2 > 0 ? tile_base(t2 - 1, nlp) : -1;
         const int nu1 = c.h_ulev[t1 - 1], nl1 = c.h_nlev[t1 - 1] - 1;
@@ -208,7 +230,7 @@ void ctx_commit(TracerCtx& c) {
                 if (inB || inC || inE) r.m2 |= 1ull << nz;
             }
         }
-        EdgeHo& h = eh[e]; memset(&h, 0, sizeof(h));
+        EdgeHo& h = eh[perm[e]]; memset(&h, 0, sizeof(h));
         double a = r_earth * c.h_ecos[t1 - 1];                       // oce_adv_tra_hor.F90:535,548
         if (t2 > 0) a = 0.5 * (a + r_earth * c.h_ecos[t2 - 1]);
         h.dxa = c.h_edxdy[2 * (size_t)e] * a; h.dyr = c.h_edxdy[2 * (size_t)e + 1] * r_earth;
@@ -241,7 +263,7 @@ void ctx_commit(TracerCtx& c) {
         for (int e = 0; e < myEd; e++)            // ascending edge id == the reference's scatter order
             for (int s = 0; s < 2; s++) {
                 int n = c.h_edges[2 * (size_t)e + s] - 1;
-                slot[((size_t)(n >> 5) * c.maxdeg + fill[n]) * TILE + (n & 31)] = (e << 1) | s;
+                slot[((size_t)(n >> 5) * c.maxdeg + fill[n]) * TILE + (n & 31)] = (perm[e] << 1) | s;
                 fill[n]++;
             }
         c.ne_slot.upload(slot);

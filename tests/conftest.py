@@ -16,3 +16,15 @@ def pytest_configure(config):
 def cases():
     from tests import util
     return util
+
+
+@pytest.fixture(autouse=True)
+def _emulated_library(monkeypatch):
+    """FB200_EMULATE=1 python -m pytest tests -m gpu: run the GPU parity tests on the CPU against the CUDA-on-CPU emulation of
+    tests/emu (test infrastructure; add FB200_EMU_ASAN=1 and LD_PRELOAD=$(g++ -print-file-name=libasan.so) for heap checks).
+    Without the variable nothing is patched: the tests load the product library and need a CUDA device."""
+    if os.environ.get("FB200_EMULATE"):
+        from fesom2_b200 import api
+        from tests import emu
+        monkeypatch.setattr(api, "_lib", emu.load())
+    yield

@@ -66,7 +66,15 @@ def transform(src):
     return "".join(out)
 
 
-def build(force=False):
+def build(force=False, asan=False):
+    """asan=True: a second library with -fsanitize=address (heap redzones around every emulated device allocation: run it
+    with LD_PRELOAD=$(g++ -print-file-name=libasan.so) to find out-of-bounds indexing in the kernels)"""
+    if asan:
+        return _build(force, os.path.join(OUT, "libfesom_b200_emu_asan.so"), ["-O1", "-g", "-fsanitize=address", "-fno-omit-frame-pointer"])
+    return _build(force, SO, ["-O2"])
+
+
+def _build(force, SO, optflags):
     os.makedirs(OUT, exist_ok=True)
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))] + \
            [os.path.join(HERE, f) for f in os.listdir(HERE) if f.endswith((".h", ".cpp", ".py"))]
@@ -80,16 +88,17 @@ def build(force=False):
             fh.write(t)
         cpp.append(dst)
     cpp += [os.path.join(HERE, "cuda_emu.cpp"), os.path.join(HERE, "nccl_emu.cpp")]
-    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-include", os.path.join(HERE, "cuda_emu.h"),
-           "-I", HERE, "-I", CSRC, "-I", os.path.join(ROOT, "include"), "-o", SO] + cpp
+    cmd = ["g++", "-std=c++17"] + optflags + ["-ffp-contract=off", "-fPIC", "-shared", "-include", os.path.join(HERE, "cuda_emu.h"),
+           "-I", HERE, "-I", CSRC, "-I", os.path.join(ROOT, "include"), "-o", SO + ".tmp"] + cpp
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("emulation build failed:\n" + r.stdout[-6000:])
+    os.replace(SO + ".tmp", SO)                            # a process that has the old library mapped keeps its copy
     return SO
 
 
 def load():
-    L = C.CDLL(build())
+    L = C.CDLL(build(asan=bool(os.environ.get("FB200_EMU_ASAN"))))
     L.fb200_status.restype = C.c_int
     L.fb200_status_message.restype = C.c_char_p
     L.fb200_kernel_launches.restype = C.c_longlong

@@ -71,3 +71,34 @@ def test_emulated_psolve_value_refresh(emulated):
     from tests import test_gpu_ssh as t
     t.test_value_refresh_and_warm_start()
     t.test_psolve_multigrid_single_level_is_jacobi()
+
+
+def test_emulated_tile_edge_order_is_bit_identical(emulated, monkeypatch):
+    """FB200_EDGE_ORDER=tile (experimental storage order of the edge tables and edge fields, context.cu) must not change a
+    bit: tracers over two steps, the antidiffusive edge fluxes returned in reference order, the ALE producers and the SSH
+    assembly, which index edge records through the node slots"""
+    import numpy as np
+    from fesom2_b200 import api
+    from oracle import binding as ob
+    from tests import util
+    adf = {}
+    for order in ("ref", "tile"):
+        monkeypatch.setenv("FB200_EDGE_ORDER", order)
+        A, B = util.build_model("pi"), util.build_model("pi")
+        o = ob.TracerOracle(A)
+        eng = api.TracerEngine(B)
+        perm = eng.debug("edge_perm")
+        assert np.array_equal(np.sort(perm), np.arange(perm.size))
+        assert np.array_equal(perm, np.arange(perm.size)) == (order == "ref")          # the permutation is in force
+        eng.push_step_state()
+        g_tr, g_tro = B["tr_arr"].copy(), B["tr_arr_old"].copy()
+        for s in range(2):
+            o.step()
+            eng.solve_tracers_ale(g_tr, g_tro)
+            assert np.array_equal(g_tr, A["tr_arr"]) and np.array_equal(g_tro, A["tr_arr_old"]), (order, s)
+        adf[order] = eng.debug("adf_h").copy()
+        eng.close()
+    assert np.abs(adf["ref"]).max() > 0 and np.array_equal(adf["ref"], adf["tile"])
+    from tests import test_gpu_tracer as t1, test_gpu_zz_ssh_assembly as t2
+    t1.test_device_ale_producers_match_host_mirror("band", {"which_ale": "zstar", "water_flux": 2e-7})
+    t2.test_device_ssh_assembly_matches_host_mirror("pi", {"which_ale": "zstar"})
