@@ -37,3 +37,22 @@ def test_no_cpu_fallback_without_gpu():
         api.TracerEngine(hm)
     with pytest.raises(api.FesomB200Error, match="no CUDA device"):
         api.SSHSolver(hm)
+
+
+def test_product_never_refers_to_the_test_emulation_or_the_oracle():
+    """tests/emu (CUDA-on-CPU emulation) and oracle/ are test infrastructure: no product source may import, load or name them
+    as something to run (bench.py's cpu_baseline / --impl reference legs and __graft_entry__.smoke() are the stated exceptions
+    for the oracle)."""
+    pkg = os.path.join(ROOT, "fesom2_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if not f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp")):
+                continue
+            src = open(os.path.join(dp, f)).read()
+            assert "FB200_EMULATE" not in src and "libfesom_b200_emu" not in src and "tests.emu" not in src and "from tests" not in src, f
+            if f == "build.py":                            # compiles liboracle.so / oracle/_ref: building the checker is not using it
+                continue
+            assert "import oracle" not in src and "from oracle" not in src and "liboracle" not in src, f
+    for f in ("bench.py", "__graft_entry__.py"):
+        src = open(os.path.join(ROOT, f)).read()
+        assert "FB200_EMULATE" not in src and "tests.emu" not in src and "libfesom_b200_emu" not in src, f
