@@ -48,7 +48,13 @@ void emu_launch(const emu_cfg& cfg, const std::function<void()>& body) {
     shfl_slots.assign((size_t)((nt + 31) / 32) * 32 * 16, 0);
     blockDim = cfg.block; gridDim = cfg.grid;
     cur_body = &body;
-    for (unsigned bz = 0; bz < cfg.grid.z; bz++) for (unsigned by = 0; by < cfg.grid.y; by++) for (unsigned bx = 0; bx < cfg.grid.x; bx++) {
+    // FB200_EMU_ORDER=reverse: blocks and the threads of a block are scheduled back to front.  A kernel without atomics whose
+    // result depends on the execution order has a race; running the parity tests in both orders is a cheap detector.
+    static const bool reverse = getenv("FB200_EMU_ORDER") && !strcmp(getenv("FB200_EMU_ORDER"), "reverse");
+    const unsigned long long nblocks = (unsigned long long)cfg.grid.x * cfg.grid.y * cfg.grid.z;
+    for (unsigned long long bi = 0; bi < nblocks; bi++) {
+        const unsigned long long b = reverse ? nblocks - 1 - bi : bi;
+        const unsigned bx = (unsigned)(b % cfg.grid.x), by = (unsigned)((b / cfg.grid.x) % cfg.grid.y), bz = (unsigned)(b / ((unsigned long long)cfg.grid.x * cfg.grid.y));
         blockIdx.x = bx; blockIdx.y = by; blockIdx.z = bz;
         int lin = 0;
         for (unsigned tz = 0; tz < cfg.block.z; tz++) for (unsigned ty = 0; ty < cfg.block.y; ty++) for (unsigned tx = 0; tx < cfg.block.x; tx++, lin++) {
@@ -61,7 +67,8 @@ void emu_launch(const emu_cfg& cfg, const std::function<void()>& body) {
         int done = 0;
         while (done < nt) {
             bool progressed = false;
-            for (int i = 0; i < nt; i++) {
+            for (int ii = 0; ii < nt; ii++) {
+                const int i = reverse ? nt - 1 - ii : ii;
                 if (fibers[i].state != 0) continue;
                 cur = i; threadIdx = fibers[i].tid;
                 swapcontext(&sched_ctx, &fibers[i].ctx);
