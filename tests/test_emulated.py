@@ -38,20 +38,19 @@ def test_emulated_relax_zonal_temp(emulated, resident):
     t.test_relax_zonal_temp_matches_oracle(resident)
 
 
-@pytest.mark.parametrize("accuracy", [8, 4])
+@pytest.mark.parametrize("accuracy", [4])
 def test_emulated_output_means(emulated, accuracy):
     from tests import test_gpu_zz_means as t
     t.test_device_means_match_stream_restatement(accuracy)
 
 
-@pytest.mark.parametrize("name,kw", [("pi", {"which_ale": "zstar"}), ("band", {"which_ale": "zlevel", "water_flux": 2e-7}), ("soufflet", {})])
+@pytest.mark.parametrize("name,kw", [("band", {"which_ale": "zlevel", "water_flux": 2e-7}), ("soufflet", {})])
 def test_emulated_ssh_assembly(emulated, name, kw):
     from tests import test_gpu_zz_ssh_assembly as t
     t.test_device_ssh_assembly_matches_host_mirror(name, kw)
 
 
-@pytest.mark.parametrize("name,kw", [("band", {"which_ale": "zstar", "water_flux": 2e-7}),
-                                     ("pi", {"which_ale": "zstar", "w_split": True, "w_max_cfl": 0.2, "umax": 0.5})])
+@pytest.mark.parametrize("name,kw", [("pi", {"which_ale": "zstar", "w_split": True, "w_max_cfl": 0.2, "umax": 0.5})])
 def test_emulated_ale_producers(emulated, name, kw):
     from tests import test_gpu_tracer as t
     t.test_device_ale_producers_match_host_mirror(name, kw)
