@@ -1648,9 +1648,9 @@ void fb200_update_vel(double* d_eta, double* UV_out) {
     { ProfScope ps_("k_update_vel", st); k_update_vel<<<(c.myE + 127) / 128, 128, 0, st>>>(p, c.UVr.p, c.sa_eta.p, c.sa_g, c.sa_theta, c.UV.p); LAUNCH_CHECK(); }
     if (comm_nranks() > 1) halo_exchange_tiled(*c.halo_elem, (double*)c.UV.p, c.nlp, 2, st);      // exchange_elem(UV), oce_dyn.F90:126
     const int L = c.nl - 1;
-    const size_t cnt = (size_t)c.E * L;
+    const size_t cnt = (size_t)c.Eall * L;              // UV(2, nl-1, myDim+eDim+eXDim): exchange_elem fills every halo element
     if (c.stage.n < 2 * cnt) c.stage.alloc(2 * cnt);
-    { ProfScope ps_("k_uv_to_ref", st); k_uv_to_ref<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(c.UV.p, (double2*)c.stage.p, c.E, L, c.nlp); LAUNCH_CHECK(); }
+    { ProfScope ps_("k_uv_to_ref", st); k_uv_to_ref<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(c.UV.p, (double2*)c.stage.p, c.Eall, L, c.nlp); LAUNCH_CHECK(); }
     CUDA_CHECK(cudaMemcpyAsync(UV_out, c.stage.p, 2 * cnt * sizeof(double), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
 }

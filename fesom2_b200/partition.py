@@ -231,6 +231,7 @@ def local_arrays(hm, r, part):
     A["ssh_rowptr"] = (lrp + 1).astype(np.int32)             # local 1-based row pointers (rowptr_loc)
     A["ssh_colind"] = pc[hm["ssh_colind"][gather] - 1].astype(np.int32)
     A["ssh_values"] = hm["ssh_values"][gather]
+    A["ssh_colind_loc"] = g2l_n[hm["ssh_colind_loc"][gather]]    # local 1-based column numbers (colind_loc, MOD_MESH.F90:15)
     A["part"] = off
     for pre, c in (("com_nod2D", r.com_nod), ("com_elem2D_full", r.com_elem_full)):
         for k in ("rPE", "rptr", "rlist", "sPE", "sptr", "slist"):

@@ -163,7 +163,7 @@ void fb200_ale_step_end(void);
  *   fb200_compute_ssh_rhs    compute_ssh_rhs_ale (:1478-1572): H2D UV_rhs(2,nl-1,elems) of the momentum step, resident UV, helem,
  *                            water_flux, ssh_rhs_old; ssh_rhs_out(N), halo entries exchanged (:1570);
  *   fb200_update_vel         update_vel (src/oce_dyn.F90:101-127) with that UV_rhs and the solution d_eta(N): the resident UV
- *                            becomes the new velocity (then pass UV = NULL to fb200_ale_step_begin), UV_out(2,nl-1,elems)
+ *                            becomes the new velocity (then pass UV = NULL to fb200_ale_step_begin), UV_out(2,nl-1,myDim+eDim+eXDim elements)
  *                            returns it to the host's momentum code; eta_n += d_eta stays on the host. */
 void fb200_ssh_assembly_init(int* rowptr, int* colind_loc, double* values, double* dhe, double* ssh_rhs_old, double* g, double* alpha,
                              double* theta);

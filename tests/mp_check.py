@@ -36,10 +36,38 @@ def check_device_ale(name, rank, world, part_in):
     out = np.zeros_like(lm["tr_arr"])
     linfs = A.ipar("which_ale") == 0
     bad = []
+    eng.ssh_assembly_init()
+    rng = np.random.default_rng(11)
+    lon = A["geo_coord_nod2D"][:, 0]
+    elem_all = r.elem - 1
+    rpA, rpL = A["ssh_rowptr"] - 1, lm["ssh_rowptr"] - 1
     for s in range(3):
         if s > 0:
-            util.advance_ale_state(A, first=False)
-            eng.ale_step_begin()
+            # the SSH assembly on the device (update_stiff_mat_ale, compute_ssh_rhs_ale, update_vel) with its exchanges of
+            # ssh_rhs and UV, against the undivided host mirror; UV_rhs and d_eta stand in for the momentum step and the solve
+            if not linfs:
+                A.stiff_mat_update()
+                eng.update_stiff_mat()
+                for i in range(myN):                       # row i of this partition = row nod[i] of the undivided matrix
+                    if not np.array_equal(lm["ssh_values"][rpL[i]:rpL[i + 1]], A["ssh_values"][rpA[nod[i]]:rpA[nod[i] + 1]]):
+                        bad.append((s, "ssh_values")); break
+            uvr = 1e-3 * rng.standard_normal(A["UV_rhs"].shape)
+            A["UV_rhs"][:] = uvr
+            lm["UV_rhs"][:] = uvr[elem_all]
+            A.compute_ssh_rhs()
+            eng.compute_ssh_rhs()
+            if not np.array_equal(lm["ssh_rhs"], A["ssh_rhs"][nod]): bad.append((s, "ssh_rhs"))
+            d = 1e-2 * np.sin(3 * lon + s)
+            A["d_eta"][:] = d
+            lm["d_eta"][:] = d[nod]
+            util.update_vel_host(A)
+            eng.update_vel()
+            if not np.array_equal(lm["UV"], A["UV"][elem_all]):
+                w = np.flatnonzero((lm["UV"] != A["UV"][elem_all]).any(axis=(1, 2)))
+                bad.append((s, "UV", int(w.min()), int(w.max()), int(w.size), r.myDim_elem2D, r.eDim_elem2D, r.eXDim_elem2D))
+            A.compute_hbar()
+            A.vert_vel()
+            eng.ale_step_begin(uv_resident=True)
             if not np.array_equal(lm["hbar"], A["hbar"][nod]): bad.append((s, "hbar"))
             sro_n = slice(0, myN) if linfs else slice(None)   # linfs: the reference leaves partial sums in the halo entries
             if not np.array_equal(lm["ssh_rhs_old"][sro_n], A["ssh_rhs_old"][nod][sro_n]): bad.append((s, "ssh_rhs_old"))
