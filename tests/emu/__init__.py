@@ -1,9 +1,11 @@
-"""TEST INFRASTRUCTURE — CUDA-on-CPU emulation of the tracer library (see cuda_emu.h).
+"""TEST INFRASTRUCTURE — CUDA-on-CPU emulation of libfesom_b200 (see cuda_emu.h).
 
-build() rewrites fesom2_b200/csrc/*.cu into plain C++ (kernel launches become calls of
-emu_launch, dynamic shared memory a per-launch buffer), compiles them with g++ -ffp-contract=off (the counterpart of
-nvcc --fmad=false) together with the fiber scheduler, an NCCL-over-files stand-in (nccl.h, nccl_emu.cpp) into tests/emu/_build/libfesom_b200_emu.so.
-load() returns it as a ctypes library set up like fesom2_b200.api.lib().  Only tests/test_emulated.py uses it."""
+build() rewrites fesom2_b200/csrc/*.cu into plain C++ (kernel launches become calls of emu_launch, dynamic shared memory a
+per-launch buffer) and compiles them with g++ -ffp-contract=off (the counterpart of nvcc --fmad=false) together with the
+fiber scheduler (cuda_emu.cpp) and an NCCL-over-files stand-in (nccl.h, nccl_emu.cpp) into
+tests/emu/_build/libfesom_b200_emu.so.  load() returns it as a ctypes library set up like fesom2_b200.api.lib().
+Used by tests/test_emulated*.py, by tests/mp_check.py --emulate and, with FB200_EMULATE=1, by tests/conftest.py; never by
+the product."""
 import ctypes as C
 import os
 import re
