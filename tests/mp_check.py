@@ -21,6 +21,9 @@ def check_device_ale(name, rank, world, part_in):
     from oracle import binding as ob
     from tests import util
     kw = dict(umax=0.05, water_flux=0.0 if name == "soufflet" else 2e-7)
+    wsplit = "--wsplit" in sys.argv                           # Courant numbers above w_max_cfl: Wvel_i != 0, Wvel_e / Wvel_i exchanged too
+    if wsplit:
+        kw.update(w_split=True, w_max_cfl=0.2, umax=0.5)
     A = util.build_model(name, **kw)                          # undivided: host mirror + oracle
     G = util.build_model(name, **kw)                          # the same state, partitioned
     part = part_in if part_in is not None else P.contiguous_partition(G, world)
@@ -72,8 +75,9 @@ def check_device_ale(name, rank, world, part_in):
             sro_n = slice(0, myN) if linfs else slice(None)   # linfs: the reference leaves partial sums in the halo entries
             if not np.array_equal(lm["ssh_rhs_old"][sro_n], A["ssh_rhs_old"][nod][sro_n]): bad.append((s, "ssh_rhs_old"))
             if not np.array_equal(lm["dhe"][:r.myDim_elem2D], A["dhe"][el]): bad.append((s, "dhe"))
-            for nm in ("Wvel", "hnode_new"):
+            for nm in ("Wvel", "hnode_new") + (("Wvel_e", "Wvel_i") if wsplit else ()):
                 if not np.array_equal(eng.debug(nm), A[nm][nod]): bad.append((s, nm))
+            if wsplit and not np.abs(A["Wvel_i"]).max() > 0: bad.append((s, "Wvel_i is zero: the split is not exercised"))
         o.step()
         eng.solve_tracers_ale_resident(out)
         if not np.array_equal(out, A["tr_arr"][:, nod]): bad.append((s, "tr_arr"))

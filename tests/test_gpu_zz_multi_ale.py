@@ -12,12 +12,12 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("mesh,nranks", [("pi", 2), ("band", 2), ("soufflet", 2), ("band", 4)])
-def test_partitioned_device_ale_matches_undivided_host_mirror(mesh, nranks):
+@pytest.mark.parametrize("mesh,nranks,extra", [("pi", 2, []), ("pi", 2, ["--wsplit"]), ("band", 2, []), ("soufflet", 2, []), ("band", 4, [])])
+def test_partitioned_device_ale_matches_undivided_host_mirror(mesh, nranks, extra):
     import torch
     if (torch.cuda.device_count() if torch.cuda.is_available() else 0) < nranks:
         pytest.skip("needs %d GPUs" % nranks)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nranks), "--master-addr", "127.0.0.1",
-           "--master-port", str(29540 + nranks), os.path.join(ROOT, "tests", "mp_check.py"), mesh, "--ale"]
+           "--master-port", str(29540 + nranks), os.path.join(ROOT, "tests", "mp_check.py"), mesh, "--ale"] + extra
     out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=240, cwd=ROOT).stdout
     assert "MPCHECK_RESULT PASS" in out, out[-3000:]
