@@ -19,7 +19,7 @@ LIM = {"FCT": 0, "NONE": 1}
 
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
-           "fb200_set_options", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
+           "fb200_set_options", "fb200_set_bh_filter", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
            "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_ssh_assembly_init", "fb200_update_stiff_mat", "fb200_compute_ssh_rhs", "fb200_update_vel", "fb200_push_tracers", "fb200_set_clim", "fb200_set_zonal_relax", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema", "fb200_mean_accumulate", "fb200_mean_fetch",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
@@ -132,7 +132,7 @@ class TracerEngine:
 
     def __init__(self, hm, tra_adv_hor="MFCT", tra_adv_ver="QR4C", tra_adv_lim="FCT", tra_adv_ph=1.0, tra_adv_pv=1.0,
                  w_split=None, i_vert_diff=True, Redi=False, use_sw_pene=False, do_hor_diff=True, clamp_salt=True,
-                 tracer_ids=(0, 1), epsilon=0.1):
+                 tracer_ids=(0, 1), epsilon=0.1, smooth_bh_tra=False, gamma_tra=(0.0005, 0.0125, 0.0)):
         self.L = lib()
         self.hm = hm
         L = self.L
@@ -152,6 +152,7 @@ class TracerEngine:
         L.fb200_set_options(_i(HOR[tra_adv_hor]), _i(VER[tra_adv_ver]), _i(LIM[tra_adv_lim]), _d(tra_adv_ph), _d(tra_adv_pv),
                             _i(ws), _i(i_vert_diff), _i(Redi), _i(use_sw_pene), _i(do_hor_diff), _i(clamp_salt),
                             _d(hm.par("is_nonlinfs")), _d(hm.par("dt")), _d(epsilon), ids)
+        L.fb200_set_bh_filter(_i(int(smooth_bh_tra)), _d(gamma_tra[0]), _d(gamma_tra[1]), _d(gamma_tra[2]))
         _check(L)
         try:
             npes = hm.ipar("npes")

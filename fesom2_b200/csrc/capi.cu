@@ -79,7 +79,17 @@ void fb200_set_options(int* tra_adv_hor, int* tra_adv_ver, int* tra_adv_lim, dou
     o.w_split = *w_split; o.i_vert_diff = *i_vert_diff; o.Redi = *Redi; o.use_sw_pene = *use_sw_pene; o.do_hor_diff = *do_hor_diff;
     o.clamp_salt = *clamp_salt; o.is_nonlinfs = *is_nonlinfs; o.dt = *dt; o.epsilon = *epsilon;
     for (int k = 0; k < c.ntr && k < 8; k++) o.tracer_id[k] = tracer_id[k];
-    if (o.tra_adv_hor < 0 || o.tra_adv_hor > 2 || o.tra_adv_ver < 0 || o.tra_adv_ver > 3) fb_set_error(32, "unknown advection scheme");
+    if (o.tra_adv_hor < 0 || o.tra_adv_hor > 2 || o.tra_adv_ver < 0 || o.tra_adv_ver > 3 || o.tra_adv_lim < 0 || o.tra_adv_lim > 1) fb_set_error(32, "unknown advection scheme");
+    for (int k = 0; k < c.ntr && k < 8; k++) {             // bc_surface, oce_ale_tracer.F90:1169-1193: any other id stops the reference too
+        const int id = o.tracer_id[k];
+        if (id == 101) fb_set_error(32, "tracer_id 101 (bc_surface: prec_rain) is not supported: the ABI carries no prec_rain array");
+        else if (!(id == 0 || id == 1 || id == 301 || id == 302 || id == 303)) fb_set_error(32, "invalid tracer_id (bc_surface knows 0, 1, 101, 301, 302, 303)");
+    }
+}
+
+void fb200_set_bh_filter(int* smooth_bh_tra, double* gamma0_tra, double* gamma1_tra, double* gamma2_tra) {
+    Options& o = tctx().opt;
+    o.smooth_bh_tra = *smooth_bh_tra != 0; o.gamma0_tra = *gamma0_tra; o.gamma1_tra = *gamma1_tra; o.gamma2_tra = *gamma2_tra;
 }
 
 void fb200_init_halo(int* nod_rPEnum, int* nod_rPE, int* nod_rptr, int* nod_rlist, int* nod_sPEnum, int* nod_sPE, int* nod_sptr, int* nod_slist,

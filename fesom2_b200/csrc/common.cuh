@@ -43,6 +43,7 @@ struct Options {
     double is_nonlinfs = 1.0, dt = 0.0, epsilon = 0.1;
     int use_kpp_nonlclflx = 0, ref_sss_local = 0; double ref_sss = 34.7;   // fb200_push_kpp_nonlocal (oce_modules.F90:51-52)
     double clim_relax = 0.0;        // > 1e-8: relax_to_clim is applied to tracers 1 and 2 (fb200_set_clim)
+    int smooth_bh_tra = 0; double gamma0_tra = 0.0005, gamma1_tra = 0.0125, gamma2_tra = 0.0;   // diff_part_bh (fb200_set_bh_filter; oce_modules.F90:138-141)
     int relax_zonal = 0;            // relax_zonal_temp of the soufflet channel instead of relax_to_clim (fb200_set_zonal_relax)
     int tracer_id[8] = {0, 1, 301, 301, 301, 301, 301, 301};
 };
@@ -128,6 +129,7 @@ struct TracerCtx {
     // work fields, tiled
     DevBuf<double2> txy, fpm;       // (tr_xy x, y) per element-level; (fct_plus, fct_minus) per node-level
     DevBuf<double> trz, LO, adf_h, adf_v, tstar, eflx;
+    DevBuf<double> redi_v, bh_tmp;   // diff_ver_part_redi_expl's del_ttf term (Redi), temporary_ttf of diff_part_bh; allocated on first use
     // staging for host<->device transfers (reference layout)
     DevBuf<double> stage;
     // halo plans of com_nod2D / com_elem2D_full (fb200_init_halo); null on a single partition

@@ -323,7 +323,7 @@ void ctx_release(TracerCtx& c) {
     for (DevBuf<double>* b : {&c.area, &c.areasvol, &c.W, &c.We, &c.Wi, &c.hnode, &c.hnode_new, &c.Z3, &c.zbar3, &c.Kv, &c.Ki,
                               &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar,
                               &c.helem, &c.adf_h, &c.eflx, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
-                              &c.relax_salt, &c.real_salt_flux, &c.relax2clim, &c.Tclim, &c.Sclim, &c.zon_ztem, &c.zon_a, &c.kgT, &c.kgS, &c.kb2, &c.kb3, &c.hbar, &c.hbar_old, &c.ssh_rhs_old, &c.dhe, &c.esum, &c.CFL, &c.stage, &c.el_g, &c.el_area, &c.n_znb}) b->release();
+                              &c.relax_salt, &c.real_salt_flux, &c.relax2clim, &c.Tclim, &c.Sclim, &c.zon_ztem, &c.zon_a, &c.kgT, &c.kgS, &c.kb2, &c.kb3, &c.hbar, &c.hbar_old, &c.ssh_rhs_old, &c.dhe, &c.esum, &c.CFL, &c.stage, &c.el_g, &c.el_area, &c.n_znb, &c.redi_v, &c.bh_tmp}) b->release();
     c.tile_deg.release(); c.fb_list.release(); c.n_fb = 0; c.ns_p.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
     c.UV.release(); c.txy.release(); c.fpm.release(); c.zon_nn.release();
     for (int k = 0; k < 8; k++) { c.mean8[k].release(); c.mean4[k].release(); }

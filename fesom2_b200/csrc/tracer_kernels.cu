@@ -29,11 +29,13 @@ struct KP {                       // kernel parameter block (by value)
     double *T, *Told, *T1;        // this tracer's fields; T1 = tracer 1 (bc_surface)
     double2 *txy, *fpm;            // (tr_xy(1), tr_xy(2)) per element-level; (fct_plus, fct_minus) per node-level
     double *trz, *LO, *adf_h, *adf_v, *tstar;
+    const double* redi_v;          // diff_ver_part_redi_expl's contribution to del_ttf per (node, level), from k_redi_expl (Redi only)
     double* eflx;                  // per (edge, level) scratch: upwind flux of ttf (k_ho_edge -> k_lo), then the diffusive flux (k_diff_edge -> k_update)
 };
 
 __device__ __forceinline__ int tbase(int ent, int nlp) { return (ent >> 5) * (nlp * TILE) + (ent & 31); }
 #define AT(p, base, nz) (p)[(base) + (((nz) - 1) << 5)]          // 1-based level
+__device__ __forceinline__ int node_of_base_d(int base, int nlp) { return (base / (nlp * TILE)) * TILE + base % (nlp * TILE); }   // entity id of a tile base
 
 // min/max of two non-NaN doubles as one compare + select (the values here are never NaN; fmin/fmax spend several
 // more instructions on NaN propagation)
@@ -685,6 +687,10 @@ __global__ void __launch_bounds__(256, 5) k_update(KP p) {
             acc[q] = acc[q] + div_by(term, asv[q], rasv[q]);
         }
     }
+    if (p.Redi) {                                                            // diff_ver_part_redi_expl :288, term from k_redi_expl
+#pragma unroll
+        for (int q = 0; q < LPT; q++) if (act[q]) acc[q] = acc[q] + AT(p.redi_v, c.b, nz[q]);
+    }
 #pragma unroll
     for (int q = 0; q < LPT; q++) {                                          // T*  :302-305
         if (!act[q]) continue;
@@ -692,6 +698,106 @@ __global__ void __launch_bounds__(256, 5) k_update(KP p) {
         const double t = AT(T, c.b, z);
         const double del = acc[q] + t * (AT(p.hnode, c.b, z) - AT(p.hnode_new, c.b, z));
         AT(p.tstar, c.b, z) = t + del / AT(p.hnode_new, c.b, z);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// diff_ver_part_redi_expl (oce_ale_tracer.F90:860-930): the projection of the horizontal Redi diffusivity onto the
+// vertical.  Thread per own column.  Pass 1 (bottom-up) leaves zbar_n(z) in the scratch column zs (:904-914); pass 2
+// (top-down) forms tr_xynodes(1:2,z) — the area-weighted sum of tr_xy over nod_in_elem2D in the reference's order, divided
+// by 3 and by areasvol (:876-893) —, the product P(z) = slope_tapered(1)*tr_xynodes(1) + slope_tapered(2)*tr_xynodes(2) that
+// both lines of vd_flux share (:918-921), vd_flux(z), and writes the del_ttf contribution of level z-1 (:925-927) to out.
+// p.txy must hold the gradients of tr_arr (the second tracer_gradient_elements call of init_tracers_AB).
+__global__ void LB(128) k_redi_expl(KP p, double* __restrict__ zs, double* __restrict__ out) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.myN) return;
+    const int b = tbase(n, p.nlp);
+    const unsigned lv = p.n_lev[n];
+    const int ul1 = lv & 255, nl1 = (int)((lv >> 8) & 255) - 1;
+    const double* __restrict__ hn = p.hnode_new;
+    const double zbot = p.n_znb[n];
+    {
+        double zb = zbot;
+        for (int z = nl1; z >= ul1; z--) { zb = zb + AT(hn, b, z); AT(zs, b, z) = zb; }
+    }
+    const int* slot = p.nie_slot + (size_t)(n >> 5) * p.maxnie * TILE + (n & 31);
+    double vd_prev = 0.0, P_prev = 0.0, Ki_prev = 0.0, Z_prev = 0.0;            // vd_flux(ul1) = 0
+    for (int z = ul1; z <= nl1; z++) {
+        double Tx = 0.0, Ty = 0.0;
+        for (int k = 0; k < p.maxnie; k++) {
+            const int e = slot[k * TILE];
+            if (e < 0) break;
+            const unsigned le = p.el_lev[e];
+            if (z <= (int)((le >> 8) & 255) && z >= (int)(le & 255)) {
+                const double ar = p.el_area[e];
+                const double2 g = AT(p.txy, tbase(e, p.nlp), z);
+                Tx = Tx + g.x * ar;
+                Ty = Ty + g.y * ar;
+            }
+        }
+        const double asv = AT(p.areasvol, b, z);
+        const double x1 = Tx / 3.0 / asv, x2 = Ty / 3.0 / asv;
+        const double P = AT(p.sl1, b, z) * x1 + AT(p.sl2, b, z) * x2;
+        const double Ki = AT(p.Ki, b, z);
+        const double zb = AT(zs, b, z);                                         // zbar_n(z)
+        const double zbn = z + 1 <= nl1 ? AT(zs, b, z + 1) : zbot;              // zbar_n(z+1)
+        const double Z = zbn + AT(hn, b, z) / 2.0;                              // Z_n(z)
+        double vd = 0.0;
+        if (z > ul1) {
+            vd = (Z_prev - zb) * P_prev * Ki_prev;
+            vd = vd + (zb - Z) * P * Ki;
+            vd = vd / (Z_prev - Z) * AT(p.area, b, z);
+            AT(out, b, z - 1) = (vd_prev - vd) * p.dt / AT(p.areasvol, b, z - 1);
+        }
+        vd_prev = vd; P_prev = P; Ki_prev = Ki; Z_prev = Z;
+    }
+    AT(out, b, nl1) = (vd_prev - 0.0) * p.dt / AT(p.areasvol, b, nl1);          // vd_flux(nl1+1) = 0
+}
+
+// diff_part_bh (oce_ale_tracer.F90:1081-1148): biharmonic diffusion as a two-round filter over the edges with two
+// triangles.  Thread per own column, per level the incident edges in ascending reference edge id (the order in which
+// the reference's edge loop reaches this node).  ROUND 1: dst = temporary_ttf (own nodes; the caller exchanges the halo),
+// src = ttf.  ROUND 2: src = temporary_ttf, dst = ttf, updated in place (a thread writes its own column only).
+template <int ROUND>
+__global__ void LB(128) k_bh(KP p, const double* __restrict__ src, double* __restrict__ dst, double g0, double g1, double g2) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= p.myN) return;
+    const int b = tbase(n, p.nlp);
+    const unsigned lv = p.n_lev[n];
+    const int nlmin_s = (lv >> 16) & 255, ulmax_s = (lv >> 24) & 255;
+    const size_t sbase = (size_t)(n >> 5) * p.maxdeg * TILE + (n & 31);
+    for (int z = 1; z <= p.nl - 1; z++) {
+        double acc = ROUND == 1 ? 0.0 : AT(dst, b, z);
+        bool touched = false;
+        for (int j = 0; j < p.maxdeg; j++) {
+            const size_t k = sbase + (size_t)j * TILE;
+            const int es = p.ne_slot[k];
+            if (es < 0) break;
+            const int4 ni = p.ns_i[k];                                          // other node, element 1, element 2, edge
+            if (ni.z < 0) continue;                                             // boundary edge: myList_edge2D(ed) > edge2D_in
+            const int no = node_of_base_d(ni.x, p.nlp);
+            const unsigned lo = p.n_lev[no];
+            const int ul1 = min(ulmax_s, (int)((lo >> 24) & 255)), nl1 = max(nlmin_s, (int)((lo >> 16) & 255)) - 1;
+            if (z < ul1 || z > nl1) continue;
+            const bool second = es & 1;
+            const double len = sqrt(p.el_area[node_of_base_d(ni.y, p.nlp)] + p.el_area[node_of_base_d(ni.z, p.nlp)]);
+            const double2 ua = AT(p.UV, ni.y, z), ub = AT(p.UV, ni.z, z);
+            const double u1 = ua.x - ub.x, v1 = ua.y - ub.y;
+            double vi = u1 * u1 + v1 * v1;
+            vi = sqrt(omax(g0, omax(g1 * sqrt(vi), g2 * vi)) * len);
+            const double s_self = AT(src, b, z), s_oth = AT(src, ni.x, z);
+            double tt = second ? s_oth - s_self : s_self - s_oth;               // value(en(1)) - value(en(2))
+            if (ROUND == 1) {
+                tt = tt * vi;
+                acc = second ? acc + tt : acc - tt;
+            } else {
+                tt = -tt * vi * p.dt;
+                const double q = tt / AT(p.area, b, z);
+                acc = second ? acc + q : acc - q;
+            }
+            touched = true;
+        }
+        if (ROUND == 1 || touched) AT(dst, b, z) = acc;
     }
 }
 
@@ -953,7 +1059,7 @@ static KP make_kp(TracerCtx& c, int tr) {
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     p.T = c.T.p + nf * tr; p.Told = c.Told.p + nf * tr; p.T1 = c.T.p;
     p.txy = c.txy.p; p.fpm = c.fpm.p; p.trz = c.trz.p; p.LO = c.LO.p; p.adf_h = c.adf_h.p; p.adf_v = c.adf_v.p;
-    p.tstar = c.tstar.p; p.eflx = c.eflx.p;
+    p.tstar = c.tstar.p; p.eflx = c.eflx.p; p.redi_v = c.redi_v.p;
     return p;
 }
 
@@ -1100,6 +1206,11 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
     if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
     if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
     if (c.opt.do_hor_diff) KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
+    if (c.opt.Redi) {                                                                   // diff_ver_part_redi_expl, oce_ale_tracer.F90:288
+        if (!c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
+        if (!c.redi_v.p) { c.redi_v.alloc(nf); p.redi_v = c.redi_v.p; }
+        KL("k_redi_expl", k_redi_expl<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.tstar, c.redi_v.p));
+    }
     if (c.opt.i_vert_diff) {
         if (fct) KL("k_update", k_update<true, false><<<gN8, blk8, 0, st>>>(p));
         else KL("k_update", k_update<false, false><<<gN8, blk8, 0, st>>>(p));
@@ -1119,6 +1230,13 @@ void tracer_step_tracer(TracerCtx& c, int tr) {
         else if (wimpl) KL("k_impl_diff", k_impl_diff<true, false><<<gI, bI, 0, st>>>(p));
         else if (kpp) KL("k_impl_diff", k_impl_diff<false, true><<<gI, bI, 0, st>>>(p));
         else KL("k_impl_diff", k_impl_diff<false, false><<<gI, bI, 0, st>>>(p));
+    }
+    if (c.opt.smooth_bh_tra) {                                                          // diff_part_bh, oce_ale_tracer.F90:321-323
+        if (!c.bh_tmp.p) c.bh_tmp.alloc(nf);
+        const int gB = (c.myN + 127) / 128;
+        KL("k_bh", k_bh<1><<<gB, 128, 0, st>>>(p, p.T, c.bh_tmp.p, c.opt.gamma0_tra, c.opt.gamma1_tra, c.opt.gamma2_tra));
+        if (multi) halo_exchange_tiled(*c.halo_nod, c.bh_tmp.p, c.nlp, 1, st);          // exchange_nod(temporary_ttf), :1121
+        KL("k_bh", k_bh<2><<<gB, 128, 0, st>>>(p, c.bh_tmp.p, p.T, c.opt.gamma0_tra, c.opt.gamma1_tra, c.opt.gamma2_tra));
     }
     if (c.opt.relax_zonal)                                                              // relax_zonal_temp: tracer 1 on every pass, oce_ale_tracer.F90:150-151
         KL("k_relax_zonal", k_relax_zonal<<<gNall, 128, 0, st>>>(p, c.T.p, c.Tclim.p, c.zon_ztem.p, c.zon_nn.p, c.zon_a.p, c.opt.dt * c.zon_fac));

@@ -89,6 +89,17 @@ void fb200_init_geometry(double* edge_cross_dxdy, double* edge_dxdy, double* ele
 void fb200_set_options(int* tra_adv_hor, int* tra_adv_ver, int* tra_adv_lim, double* tra_adv_ph, double* tra_adv_pv,
                        int* w_split, int* i_vert_diff, int* Redi, int* use_sw_pene, int* do_hor_diff, int* clamp_salt,
                        double* is_nonlinfs, double* dt, double* epsilon, int* tracer_id /* num_tracers */);
+/* Limits the reference does not have (each raises an error instead of computing something else): nl <= 63 (64-bit level
+ * masks per edge); every own column has at least 3 layers (QR4C's boundary statements would overlap); the two triangles
+ * of an edge must share at least one level (error 15); num_tracers <= 8; tracer_id in {0, 1, 301, 302, 303} — id 101
+ * (bc_surface's prec_rain case, src/oce_ale_tracer.F90:1178) needs an array this ABI does not carry and is refused.
+ * Redi = 1 runs diff_part_hor_redi with the slope terms (:934-1077), diff_ver_part_redi_expl (:860-930, call site :288)
+ * and the Ki*slope^2 terms of diff_ver_part_impl_ale; it needs slope_tapered in fb200_push_step_state. */
+/* biharmonic tracer filter diff_part_bh (src/oce_ale_tracer.F90:1081-1148, call site :321-323): namelist oce_tra
+ * smooth_bh_tra, gamma0_tra, gamma1_tra, gamma2_tra (src/oce_modules.F90:138-141).  Off unless called with
+ * *smooth_bh_tra != 0.  Applied to every tracer after the vertical diffusion, with the reference's
+ * exchange_nod(temporary_ttf) between its two rounds on more than one partition. */
+void fb200_set_bh_filter(int* smooth_bh_tra, double* gamma0_tra, double* gamma1_tra, double* gamma2_tra);
 /* halo lists of this partition, the reference's com_nod2D and com_elem2D_full (src/gen_modules_partitioning.F90:17-29,
  * read from dist_N/com_infoNNNNN.out, src/oce_mesh.F90:568-640): PE ids 0-based, rptr/sptr 1-based offsets, rlist/slist
  * 1-based local entity numbers.  Only needed on more than one partition; call after fb200_comm_init. */

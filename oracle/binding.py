@@ -58,7 +58,7 @@ class TracerOracle:
 
     def __init__(self, hm, tra_adv_hor="MFCT", tra_adv_ver="QR4C", tra_adv_lim="FCT", tra_adv_ph=1.0, tra_adv_pv=1.0,
                  w_split=None, i_vert_diff=True, Redi=False, use_sw_pene=False, do_hor_diff=True, clamp_salt=True,
-                 tracer_ids=(0, 1), fct_cavity_neutral=False):
+                 tracer_ids=(0, 1), fct_cavity_neutral=False, smooth_bh_tra=False, gamma_tra=(0.0005, 0.0125, 0.0), bh_split=False):
         self.L = lib()
         self.hm = hm
         self.o = C.c_void_p(self.L.oracle_create())
@@ -86,6 +86,10 @@ class TracerOracle:
         si(self.o, b"do_hor_diff", int(do_hor_diff))
         si(self.o, b"clamp_salt", int(clamp_salt))
         si(self.o, b"fct_cavity_neutral", int(fct_cavity_neutral))
+        si(self.o, b"smooth_bh_tra", int(smooth_bh_tra))
+        si(self.o, b"bh_split", int(bh_split))
+        for k in range(3):
+            sd(self.o, ("gamma%d_tra" % k).encode(), float(gamma_tra[k]))
         for k, tid in enumerate(tracer_ids):
             si(self.o, ("tracer_id%d" % k).encode(), int(tid))
         assert self.L.oracle_alloc_work(self.o) == 0

@@ -6,8 +6,8 @@
 
 #define INT_FIELDS(X) X(nl) X(myDim_nod2D) X(eDim_nod2D) X(myDim_elem2D) X(eDim_elem2D) X(eXDim_elem2D) X(myDim_edge2D) \
     X(nod_in_elem2D_max) X(num_tracers) X(tra_adv_hor) X(tra_adv_ver) X(tra_adv_lim) X(w_split) X(i_vert_diff) X(Redi)    \
-    X(use_sw_pene) X(do_hor_diff) X(clamp_salt) X(use_kpp_nonlclflx) X(ref_sss_local) X(fct_cavity_neutral) X(relax_zonal)
-#define DBL_FIELDS(X) X(dt) X(epsilon) X(tra_adv_ph) X(tra_adv_pv) X(is_nonlinfs) X(clim_relax) X(ref_sss) X(zonal_lat0) X(zonal_dy) X(zonal_tau_inv)
+    X(use_sw_pene) X(do_hor_diff) X(clamp_salt) X(use_kpp_nonlclflx) X(ref_sss_local) X(fct_cavity_neutral) X(relax_zonal) X(smooth_bh_tra) X(bh_split) X(skip_redi_expl)
+#define DBL_FIELDS(X) X(dt) X(epsilon) X(tra_adv_ph) X(tra_adv_pv) X(is_nonlinfs) X(clim_relax) X(ref_sss) X(zonal_lat0) X(zonal_dy) X(zonal_tau_inv) X(gamma0_tra) X(gamma1_tra) X(gamma2_tra)
 #define CIPTR_FIELDS(X) X(edges) X(edge_tri) X(elem2D_nodes) X(nlevels) X(ulevels) X(nlevels_nod2D) X(ulevels_nod2D) \
     X(nlevels_nod2D_min) X(ulevels_nod2D_max) X(nod_in_elem2D) X(nod_in_elem2D_num) X(edge_up_dn_tri) X(nboundary_lay)
 #define CDPTR_FIELDS(X) X(edge_cross_dxdy) X(edge_dxdy) X(elem_cos) X(elem_area) X(gradient_sca) X(area) X(areasvol) \
@@ -15,7 +15,7 @@
     X(slope_tapered) X(heat_flux) X(water_flux) X(virtual_salt) X(relax_salt) X(real_salt_flux) X(sw_3d) X(relax2clim) X(Tclim) X(Sclim) X(kpp_gT) X(kpp_gS) X(kpp_b2) X(kpp_b3) X(zonal_ztem) X(coord_nod2D)
 #define DPTR_FIELDS(X) X(tr_arr) X(tr_arr_old)
 #define WORK_FIELDS(X) X(del_ttf) X(del_ttf_advhoriz) X(del_ttf_advvert) X(tr_xy) X(tr_z) X(edge_up_dn_grad) X(fct_LO) \
-    X(adv_flux_hor) X(adv_flux_ver) X(fct_ttf_max) X(fct_ttf_min) X(fct_plus) X(fct_minus) X(aux_minmax)
+    X(adv_flux_hor) X(adv_flux_ver) X(fct_ttf_max) X(fct_ttf_min) X(fct_plus) X(fct_minus) X(aux_minmax) X(bh_tmp)
 
 oracle_t* oracle_create(void) {
     oracle_t* o = (oracle_t*)calloc(1, sizeof(oracle_t));
@@ -25,6 +25,7 @@ oracle_t* oracle_create(void) {
     o->i_vert_diff = 1; o->do_hor_diff = 1; o->clamp_salt = 1; o->is_nonlinfs = 1.0;
     o->num_tracers = 2; o->tracer_id[0] = 0; o->tracer_id[1] = 1;
     o->ref_sss = 34.7;          /* oce_modules.F90:52 */
+    o->gamma0_tra = 0.0005; o->gamma1_tra = 0.0125; o->gamma2_tra = 0.0;   /* oce_modules.F90:139-141 */
     return o;
 }
 void oracle_free(oracle_t* o) {
@@ -74,6 +75,7 @@ int oracle_alloc_work(oracle_t* o) {     /* array_setup + oce_adv_tra_fct_init +
     AL(fct_LO, L * N); AL(adv_flux_hor, L * Ed); AL(adv_flux_ver, nl * (size_t)o->myDim_nod2D);
     AL(fct_ttf_max, L * N); AL(fct_ttf_min, L * N); AL(fct_plus, L * N); AL(fct_minus, L * N);
     AL(aux_minmax, 2 * L * (size_t)(o->myDim_elem2D + o->eDim_elem2D));
+    AL(bh_tmp, L * N);
 #undef AL
     return 0;
 }

@@ -49,7 +49,7 @@ typedef struct oracle {
     double *tr_arr, *tr_arr_old;
     /* work arrays owned by the oracle (o_ARRAYS / o_MESH work arrays) */
     double *del_ttf, *del_ttf_advhoriz, *del_ttf_advvert, *tr_xy, *tr_z, *edge_up_dn_grad, *fct_LO,
-           *adv_flux_hor, *adv_flux_ver, *fct_ttf_max, *fct_ttf_min, *fct_plus, *fct_minus, *aux_minmax;
+           *adv_flux_hor, *adv_flux_ver, *fct_ttf_max, *fct_ttf_min, *fct_plus, *fct_minus, *aux_minmax, *bh_tmp;
     /* parameters (namelists oce_tra / oce_dyn, g_config) */
     double dt, epsilon, tra_adv_ph, tra_adv_pv, is_nonlinfs, clim_relax, ref_sss;
     int tra_adv_hor, tra_adv_ver, tra_adv_lim, w_split, i_vert_diff, Redi, use_sw_pene, do_hor_diff, clamp_salt, use_kpp_nonlclflx, ref_sss_local;
@@ -58,6 +58,11 @@ typedef struct oracle {
      * left in UV_rhs.  0: the scratch as allocated (zeros, then the previous call's values); 1: those entries are neutral
      * (-bignumber / +bignumber, the rule a2 applies below the bottom), which is what the CUDA path computes. */
     int fct_cavity_neutral;
+    /* diff_part_bh (oce_ale_tracer.F90:1081-1148): smooth_bh_tra, gamma0_tra..gamma2_tra (namelist oce_tra, oce_modules.F90:138-141);
+     * bh_split: the caller runs the two rounds itself with the reference's exchange_nod(temporary_ttf) in between */
+    int smooth_bh_tra, bh_split;
+    int skip_redi_expl;   /* tests only: leave the term out to show that it matters */
+    double gamma0_tra, gamma1_tra, gamma2_tra;
     int tracer_id[8];
 } oracle_t;
 
@@ -86,6 +91,10 @@ void o_oce_tra_adv_flux2dtracer(oracle_t* o, double* dttf_h, double* dttf_v, dou
                                 int use_lo, const double* ttf, const double* lo);
 void o_diff_part_hor_redi(oracle_t* o);
 void o_diff_ver_part_expl_ale(oracle_t* o, int tr_num);
+void o_diff_ver_part_redi_expl(oracle_t* o);
+void o_diff_part_bh(oracle_t* o, double* ttf);
+void o_diff_part_bh_round1(oracle_t* o, const double* ttf, double* temporary_ttf);
+void o_diff_part_bh_round2(oracle_t* o, double* ttf, const double* temporary_ttf);
 void o_diff_ver_part_impl_ale(oracle_t* o, int tr_num);
 void o_relax_to_clim(oracle_t* o, int tr_num);
 void o_relax_zonal_temp(oracle_t* o);

@@ -521,6 +521,113 @@ void o_diff_part_hor_redi(oracle_t* o) {
     free(rhs1); free(rhs2);
 }
 
+/* diff_ver_part_redi_expl, oce_ale_tracer.F90:860-930 — "a projection of horizontal Redi diffusivity onto vertical"
+ * (call site :288, under `if (Redi)`, after diff_ver_part_expl_ale and before the T* update).  tr_xy holds the gradients of
+ * tr_arr (the second tracer_gradient_elements call of init_tracers_AB, oce_tracer_mod.F90:79).  tr_xynodes is a local of
+ * the reference (own nodes only: "the halo is not needed", :895); zbar_n, Z_n are the module's column scratch. */
+void o_diff_ver_part_redi_expl(oracle_t* o) {
+    const double dt = o->dt;
+    const int myN = o->myDim_nod2D;
+    const double *Ki = o->Ki, *sl = o->slope_tapered, *hn = o->hnode_new, *tr_xy = o->tr_xy;
+    double* tr_xynodes = (double*)calloc((size_t)2 * (size_t)LM * (size_t)myN + 1, sizeof(double));
+    size_t sz = (size_t)NL + 2;
+    double* buf = (double*)calloc(3 * sz, sizeof(double));
+    double *vd_flux = buf, *zbar_n = buf + sz, *Z_n = buf + 2 * sz;
+#define XN(c, nz, n) tr_xynodes[((size_t)((n) - 1) * (size_t)LM + (size_t)((nz) - 1)) * 2 + ((c) - 1)]
+    for (int n = 1; n <= myN; n++) {                                                     /* :876-893 */
+        int nl1 = o->nlevels_nod2D[n - 1] - 1, ul1 = o->ulevels_nod2D[n - 1];
+        for (int nz = ul1; nz <= nl1; nz++) {
+            double Tx = 0.0, Ty = 0.0;
+            for (int k = 1; k <= o->nod_in_elem2D_num[n - 1]; k++) {
+                int elem = I2(o->nod_in_elem2D, o->nod_in_elem2D_max, k, n);
+                if (nz <= o->nlevels[elem - 1] - 1 && nz >= o->ulevels[elem - 1]) {
+                    Tx = Tx + V3(tr_xy, 1, nz, elem) * o->elem_area[elem - 1];
+                    Ty = Ty + V3(tr_xy, 2, nz, elem) * o->elem_area[elem - 1];
+                }
+            }
+            XN(1, nz, n) = Tx / 3.0 / W2(o->areasvol, nz, n);
+            XN(2, nz, n) = Ty / 3.0 / W2(o->areasvol, nz, n);
+        }
+    }
+    for (int n = 1; n <= myN; n++) {                                                     /* :897-929 */
+        int nl1 = o->nlevels_nod2D[n - 1] - 1, ul1 = o->ulevels_nod2D[n - 1];
+        memset(buf, 0, 3 * sz * sizeof(double));
+        zbar_n[nl1 + 1] = o->zbar_n_bot[n - 1];
+        Z_n[nl1] = zbar_n[nl1 + 1] + T2(hn, nl1, n) / 2.0;
+        for (int nz = nl1; nz >= ul1 + 1; nz--) {
+            zbar_n[nz] = zbar_n[nz + 1] + T2(hn, nz, n);
+            Z_n[nz - 1] = zbar_n[nz] + T2(hn, nz - 1, n) / 2.0;
+        }
+        zbar_n[ul1] = zbar_n[ul1 + 1] + T2(hn, ul1, n);
+        for (int nz = ul1 + 1; nz <= nl1; nz++) {
+            vd_flux[nz] = (Z_n[nz - 1] - zbar_n[nz]) * (S3(sl, 1, nz - 1, n) * XN(1, nz - 1, n) + S3(sl, 2, nz - 1, n) * XN(2, nz - 1, n)) * T2(Ki, nz - 1, n);
+            vd_flux[nz] = vd_flux[nz] + (zbar_n[nz] - Z_n[nz]) * (S3(sl, 1, nz, n) * XN(1, nz, n) + S3(sl, 2, nz, n) * XN(2, nz, n)) * T2(Ki, nz, n);
+            vd_flux[nz] = vd_flux[nz] / (Z_n[nz - 1] - Z_n[nz]) * W2(o->area, nz, n);
+        }
+        for (int nz = ul1; nz <= nl1; nz++)
+            T2(o->del_ttf, nz, n) = T2(o->del_ttf, nz, n) + (vd_flux[nz] - vd_flux[nz + 1]) * dt / W2(o->areasvol, nz, n);
+    }
+#undef XN
+    free(buf); free(tr_xynodes);
+}
+
+/* diff_part_bh, oce_ale_tracer.F90:1081-1148 — biharmonic diffusion of tracer ttf implemented as a filter (call site
+ * :321-323, `if (smooth_bh_tra)`, after the implicit vertical diffusion).  Two rounds over the edges with two triangles
+ * (myList_edge2D(ed) <= edge2D_in, passed here as edge_tri(2,ed) > 0: an edge past edge2D_in has no second triangle,
+ * oce_mesh.F90:1456-1499); between them the reference exchanges temporary_ttf — the caller of a partitioned run does that
+ * between o_diff_part_bh_round1 and _round2.  The reference's loop also covers eDim_edge2D edges: both nodes of those are
+ * halo nodes, whose temporary_ttf the exchange overwrites and whose ttf the following exchange_nod(tr_arr) (:155)
+ * overwrites, so own entries never see them.  gamma0/1/2 are gamma0_tra, gamma1_tra, gamma2_tra (oce_modules.F90:139-141). */
+static void bh_edge_coef(oracle_t* o, int ed, int nz, int el1, int el2, double len, double* vi_out) {
+    (void)ed;
+    double u1 = V3(o->UV, 1, nz, el1) - V3(o->UV, 1, nz, el2);
+    double v1 = V3(o->UV, 2, nz, el1) - V3(o->UV, 2, nz, el2);
+    double vi = u1 * u1 + v1 * v1;
+    vi = sqrt(dmax(o->gamma0_tra, dmax(o->gamma1_tra * sqrt(vi), o->gamma2_tra * vi)) * len);
+    *vi_out = vi;
+}
+void o_diff_part_bh_round1(oracle_t* o, const double* ttf, double* temporary_ttf) {
+    size_t cnt = (size_t)LM * (size_t)(o->myDim_nod2D + o->eDim_nod2D);
+    memset(temporary_ttf, 0, cnt * sizeof(double));
+    for (int ed = 1; ed <= o->myDim_edge2D; ed++) {
+        int el1 = I2(o->edge_tri, 2, 1, ed), el2 = I2(o->edge_tri, 2, 2, ed);
+        if (el2 <= 0) continue;
+        int en1 = I2(o->edges, 2, 1, ed), en2 = I2(o->edges, 2, 2, ed);
+        double len = sqrt(o->elem_area[el1 - 1] + o->elem_area[el2 - 1]);
+        int ul1 = imin(o->ulevels_nod2D_max[en1 - 1], o->ulevels_nod2D_max[en2 - 1]);
+        int nl1 = imax(o->nlevels_nod2D_min[en1 - 1], o->nlevels_nod2D_min[en2 - 1]) - 1;
+        for (int nz = ul1; nz <= nl1; nz++) {
+            double vi, tt = T2(ttf, nz, en1) - T2(ttf, nz, en2);
+            bh_edge_coef(o, ed, nz, el1, el2, len, &vi);
+            tt = tt * vi;
+            T2(temporary_ttf, nz, en1) = T2(temporary_ttf, nz, en1) - tt;
+            T2(temporary_ttf, nz, en2) = T2(temporary_ttf, nz, en2) + tt;
+        }
+    }
+}
+void o_diff_part_bh_round2(oracle_t* o, double* ttf, const double* temporary_ttf) {
+    const double dt = o->dt;
+    for (int ed = 1; ed <= o->myDim_edge2D; ed++) {
+        int el1 = I2(o->edge_tri, 2, 1, ed), el2 = I2(o->edge_tri, 2, 2, ed);
+        if (el2 <= 0) continue;
+        int en1 = I2(o->edges, 2, 1, ed), en2 = I2(o->edges, 2, 2, ed);
+        double len = sqrt(o->elem_area[el1 - 1] + o->elem_area[el2 - 1]);
+        int ul1 = imin(o->ulevels_nod2D_max[en1 - 1], o->ulevels_nod2D_max[en2 - 1]);
+        int nl1 = imax(o->nlevels_nod2D_min[en1 - 1], o->nlevels_nod2D_min[en2 - 1]) - 1;
+        for (int nz = ul1; nz <= nl1; nz++) {
+            double vi, tt = T2(temporary_ttf, nz, en1) - T2(temporary_ttf, nz, en2);
+            bh_edge_coef(o, ed, nz, el1, el2, len, &vi);
+            tt = -tt * vi * dt;
+            T2(ttf, nz, en1) = T2(ttf, nz, en1) - tt / W2(o->area, nz, en1);
+            T2(ttf, nz, en2) = T2(ttf, nz, en2) + tt / W2(o->area, nz, en2);
+        }
+    }
+}
+void o_diff_part_bh(oracle_t* o, double* ttf) {          /* one partition: no exchange between the rounds */
+    o_diff_part_bh_round1(o, ttf, o->bh_tmp);
+    o_diff_part_bh_round2(o, ttf, o->bh_tmp);
+}
+
 static double surface_flux(oracle_t* o, int n, int tr_num) {      /* the `flux` of diff_ver_part_expl_ale :354-364 */
     if (tr_num == 1) return -o->heat_flux[n - 1] / vcpw;
     if (tr_num == 2) return o->virtual_salt[n - 1] + o->relax_salt[n - 1] - o->real_salt_flux[n - 1] * o->is_nonlinfs;
@@ -741,12 +848,16 @@ void o_phase5(oracle_t* o, int tr_num) {
     memcpy(told, ttf, cnt * sizeof(double));
     if (o->do_hor_diff) o_diff_part_hor_redi(o);
     if (!o->i_vert_diff) o_diff_ver_part_expl_ale(o, tr_num);
+    if (o->Redi && !o->skip_redi_expl) o_diff_ver_part_redi_expl(o);                      /* :288 (skip_redi_expl: test switch) */
     for (int n = 1; n <= o->myDim_nod2D; n++) {
         int nzmax = o->nlevels_nod2D[n - 1] - 1, nzmin = o->ulevels_nod2D[n - 1];
         for (int nz = nzmin; nz <= nzmax; nz++) T2(o->del_ttf, nz, n) = T2(o->del_ttf, nz, n) + T2(ttf, nz, n) * (T2(o->hnode, nz, n) - T2(o->hnode_new, nz, n));
         for (int nz = nzmin; nz <= nzmax; nz++) T2(ttf, nz, n) = T2(ttf, nz, n) + T2(o->del_ttf, nz, n) / T2(o->hnode_new, nz, n);
     }
     if (o->i_vert_diff) o_diff_ver_part_impl_ale(o, tr_num);
+    /* smooth_bh_tra (:321-323): one partition here; a partitioned caller sets bh_split and runs o_diff_part_bh_round1,
+     * exchange_nod(temporary_ttf), o_diff_part_bh_round2 itself */
+    if (o->smooth_bh_tra && !o->bh_split) o_diff_part_bh(o, ttf);
 }
 /* relax_to_clim, oce_tracer_mod.F90:87-119: own nodes, wet levels, tracers 1 (Tclim) and 2 (Sclim) */
 void o_relax_to_clim(oracle_t* o, int tr_num) {

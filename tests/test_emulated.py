@@ -101,3 +101,11 @@ def test_emulated_tile_edge_order_is_bit_identical(emulated, monkeypatch):
     from tests import test_gpu_tracer as t1, test_gpu_zz_ssh_assembly as t2
     t1.test_device_ale_producers_match_host_mirror("band", {"which_ale": "zstar", "water_flux": 2e-7})
     t2.test_device_ssh_assembly_matches_host_mirror("pi", {"which_ale": "zstar"})
+
+
+@pytest.mark.parametrize("name,opts", [("pi", {"Redi": True, "use_sw_pene": True}),
+                                       ("band", {"smooth_bh_tra": True, "gamma_tra": (0.0002, 0.05, 3.0), "Redi": True})])
+def test_emulated_redi_and_biharmonic_filter(emulated, name, opts):
+    """k_redi_expl (diff_ver_part_redi_expl, the term round 1 lacked) and k_bh (diff_part_bh) against the oracle, bit for bit"""
+    from tests import test_gpu_tracer as t
+    t.test_redi_and_shortwave_match_oracle(name, opts)

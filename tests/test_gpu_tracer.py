@@ -62,25 +62,19 @@ def test_tracer_step_matches_oracle(name, model_kw, opts):
         assert util.rel_err(g_tro[k], c_tro[k]) < TOL
 
 
-def _fill_redi_sw(hm, seed=7):
-    """neutral slopes (|s| <= 2e-3, smooth + noise) and a shortwave profile decaying with depth: the inputs
-    diff_part_hor_redi / diff_ver_part_impl_ale read when Redi and use_sw_pene are on"""
-    rng = np.random.default_rng(seed)
-    sl = hm["slope_tapered"]
-    n, L, _ = sl.shape
-    x = np.linspace(0.0, 6.0, n)[:, None]
-    z = np.arange(L)[None, :]
-    sl[:, :, 0] = 1e-3 * np.sin(x + 0.1 * z) + 2e-4 * rng.uniform(-1, 1, (n, L))
-    sl[:, :, 1] = 1e-3 * np.cos(2 * x - 0.2 * z) + 2e-4 * rng.uniform(-1, 1, (n, L))
-    sl[:, :, 2] = np.sqrt(sl[:, :, 0] ** 2 + sl[:, :, 1] ** 2)
-    sw = hm["sw_3d"]
-    sw[:, :] = 1e-5 * (1.0 + 0.3 * np.sin(3 * x)) * np.exp(-np.arange(sw.shape[1])[None, :] / 3.0)
+_fill_redi_sw = util.fill_redi_sw
 
 
 @pytest.mark.parametrize("name,opts", [
     ("band", {"Redi": True}),
     ("pi", {"Redi": True, "use_sw_pene": True}),
     ("soufflet", {"use_sw_pene": True, "tra_adv_lim": "NONE", "tra_adv_hor": "MUSCL"}),
+    ("cavity", {"Redi": True, "fct_cavity_neutral": True}),
+    ("pi", {"Redi": True, "i_vert_diff": False}),                   # diff_ver_part_expl_ale and diff_ver_part_redi_expl in one step
+    ("pi", {"Redi": True, "do_hor_diff": False}),                   # the tr_xy(T) the term needs is still computed
+    ("pi", {"smooth_bh_tra": True}),                                # diff_part_bh with the namelist's gamma0_tra/gamma1_tra
+    ("band", {"smooth_bh_tra": True, "gamma_tra": (0.0002, 0.05, 3.0), "Redi": True}),
+    ("cavity", {"smooth_bh_tra": True, "fct_cavity_neutral": True}),
 ])
 def test_redi_and_shortwave_match_oracle(name, opts):
     from fesom2_b200 import api
@@ -88,13 +82,14 @@ def test_redi_and_shortwave_match_oracle(name, opts):
     hm = util.build_model(name)
     _fill_redi_sw(hm)
     g_tr, g_tro = hm["tr_arr"].copy(), hm["tr_arr_old"].copy()
-    eng = api.TracerEngine(hm, **opts)
+    eng = api.TracerEngine(hm, **{k: v for k, v in opts.items() if k != "fct_cavity_neutral"})
     eng.push_step_state()
     eng.solve_tracers_ale(g_tr, g_tro)
     ob.TracerOracle(hm, **opts).step()
     wet = util.wet_mask(hm)
     for k in range(g_tr.shape[0]):
         assert util.rel_err(g_tr[k][wet], hm["tr_arr"][k][wet]) < TOL, "tracer %d" % k
+        assert np.array_equal(g_tr[k][wet], hm["tr_arr"][k][wet]), "tracer %d not bit-identical" % k
     eng.close()
 
 

@@ -43,7 +43,12 @@ def run_partitioned_oracle(hm, part, npes, opts=None, steps=1):
     opts = opts or {}
     ranks = P.build_partition(hm, part, npes)
     lms = [P.local_model(hm, r, part) for r in ranks]
-    ors = [ob.TracerOracle(lm, **opts) for lm in lms]
+    bh = bool(opts.get("smooth_bh_tra"))
+    ors = [ob.TracerOracle(lm, bh_split=bh, **opts) for lm in lms]
+    L = ob.lib()
+    for f in (L.o_diff_part_bh_round1, L.o_diff_part_bh_round2):
+        f.argtypes = [ob.C.c_void_p, ob.C.c_void_p, ob.C.c_void_p]
+        f.restype = None
     nl = hm.ipar("nl")
     ntr = hm.ipar("num_tracers")
     for _ in range(steps):
@@ -62,15 +67,28 @@ def run_partitioned_oracle(hm, part, npes, opts=None, steps=1):
                 P.exchange_host(ranks, [o.work(nm, (nl - 1, r.nod.size)) for o, r in zip(ors, ranks)], "nod")
             for o in ors:
                 o.phase(5, tr)
+            # diff_part_bh with the reference's exchange_nod(temporary_ttf) between its rounds.  NOT partition-invariant in the
+            # reference: round 1 (oce_ale_tracer.F90:1109-1119) reads ttf of halo nodes before exchange_nod(tr_arr) (:155),
+            # i.e. last step's values; a partitioned run of the restatement reproduces that, the undivided run cannot.
+            if bh:
+                tmp = [o.work("bh_tmp", (nl - 1, r.nod.size)) for o, r in zip(ors, ranks)]
+                for o, lm, t in zip(ors, lms, tmp):
+                    L.o_diff_part_bh_round1(o.o, lm["tr_arr"][tr - 1].ctypes.data, t.ctypes.data)
+                P.exchange_host(ranks, tmp, "nod")
+                for o, lm, t in zip(ors, lms, tmp):
+                    L.o_diff_part_bh_round2(o.o, lm["tr_arr"][tr - 1].ctypes.data, t.ctypes.data)
             P.exchange_host(ranks, [lm["tr_arr"][tr - 1] for lm in lms], "nod")
         for o in ors:
             o.final()
     return ranks, lms
 
 
-@pytest.mark.parametrize("name,npes,opts", [("pi", 2, {}), ("band", 3, {}), ("soufflet", 2, {"tra_adv_hor": "MUSCL"}), ("farclike", 4, {}), ("cavity", 3, {})])
+@pytest.mark.parametrize("name,npes,opts", [("pi", 2, {}), ("band", 3, {}), ("soufflet", 2, {"tra_adv_hor": "MUSCL"}), ("farclike", 4, {}), ("cavity", 3, {}),
+                                            ("pi", 3, {"Redi": True})])
 def test_partitioned_oracle_equals_undivided_oracle(name, npes, opts):
     hm = util.build_model(name)
+    if opts.get("Redi"):
+        util.fill_redi_sw(hm)
     part = P.contiguous_partition(hm, npes)
     ranks, lms = run_partitioned_oracle(hm, part, npes, opts, steps=2)
     o = ob.TracerOracle(hm, **opts)
@@ -136,3 +154,31 @@ def test_partitioned_ale_producers_need_exactly_the_four_exchanges(name, npes, k
             for nm in ("hnode", "Z_3d_n", "zbar_3d_n"):
                 assert np.array_equal(lm[nm], A[nm][nod]), (s, nm)
             assert np.array_equal(lm["helem"][:r.myDim_elem2D], A["helem"][el]), s
+
+
+def test_biharmonic_filter_on_partitions_reads_the_stale_halo_like_the_reference():
+    """diff_part_bh in a partitioned run: own nodes away from the partition boundary equal the undivided run bit for bit;
+    nodes next to a halo node differ, because the reference's first round reads tr_arr of halo nodes before the
+    exchange that follows diff_tracers_ale (oce_ale_tracer.F90:1109-1119 vs :155).  The restatement keeps that."""
+    hm = util.build_model("pi")
+    part = P.contiguous_partition(hm, 2)
+    opts = {"smooth_bh_tra": True}
+    ranks, lms = run_partitioned_oracle(hm, part, 2, opts, steps=1)
+    ob.TracerOracle(hm, **opts).step()
+    edges = hm["edges"] - 1
+    differs = 0
+    for me, (r, lm) in enumerate(zip(ranks, lms)):
+        own = r.nod[:r.myDim_nod2D] - 1
+        # distance-2 neighbourhood of the other partitions' nodes (two rounds of an edge stencil)
+        near = part != me
+        for _ in range(2):
+            grow = near.copy()
+            np.logical_or.at(grow, edges[:, 0], near[edges[:, 1]])
+            np.logical_or.at(grow, edges[:, 1], near[edges[:, 0]])
+            near = grow
+        inner = ~near[own]
+        a, b = lm["tr_arr"][0][:r.myDim_nod2D], hm["tr_arr"][0][own]
+        assert inner.sum() > 100 and np.array_equal(a[inner], b[inner])
+        differs += int((a[~inner] != b[~inner]).any())
+        assert util.rel_err(a, b) < 1e-5
+    assert differs > 0

@@ -77,6 +77,21 @@ def build_model(name="pi", dt=None, which_ale=None, w_split=False, w_max_cfl=1.0
     return hm
 
 
+def fill_redi_sw(hm, seed=7):
+    """neutral slopes (|s| <= 2e-3, smooth + noise) and a shortwave profile decaying with depth: the inputs
+    diff_part_hor_redi / diff_ver_part_impl_ale read when Redi and use_sw_pene are on"""
+    rng = np.random.default_rng(seed)
+    sl = hm["slope_tapered"]
+    n, L, _ = sl.shape
+    x = np.linspace(0.0, 6.0, n)[:, None]
+    z = np.arange(L)[None, :]
+    sl[:, :, 0] = 1e-3 * np.sin(x + 0.1 * z) + 2e-4 * rng.uniform(-1, 1, (n, L))
+    sl[:, :, 1] = 1e-3 * np.cos(2 * x - 0.2 * z) + 2e-4 * rng.uniform(-1, 1, (n, L))
+    sl[:, :, 2] = np.sqrt(sl[:, :, 0] ** 2 + sl[:, :, 1] ** 2)
+    sw = hm["sw_3d"]
+    sw[:, :] = 1e-5 * (1.0 + 0.3 * np.sin(3 * x)) * np.exp(-np.arange(sw.shape[1])[None, :] / 3.0)
+
+
 def wet_mask(hm):
     nl = hm.ipar("nl")
     lev = np.arange(1, nl)[None, :]
