@@ -20,7 +20,7 @@ LIM = {"FCT": 0, "NONE": 1}
 EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb200_psolver_set_block",
            "fb200_init_dims", "fb200_init_connectivity", "fb200_init_levels", "fb200_init_geometry",
            "fb200_set_options", "fb200_set_bh_filter", "fb200_init_commit", "fb200_push_step_state", "fb200_push_state_early", "fb200_push_state_late",
-           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_ssh_assembly_init", "fb200_update_stiff_mat", "fb200_compute_ssh_rhs", "fb200_update_vel", "fb200_push_tracers", "fb200_set_clim", "fb200_set_zonal_relax", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema", "fb200_mean_accumulate", "fb200_mean_fetch",
+           "fb200_ale_init", "fb200_ale_step_begin", "fb200_ale_step_end", "fb200_ssh_assembly_init", "fb200_update_stiff_mat", "fb200_compute_ssh_rhs", "fb200_update_vel", "fb200_push_tracers", "fb200_set_clim", "fb200_set_zonal_relax", "fb200_push_kpp_nonlocal", "fb200_tracer_extrema", "fb200_tracer_extrema_noalloc", "fb200_mean_accumulate", "fb200_mean_fetch",
            "fb200_solve_tracers", "fb200_pull_tracers", "fb200_solve_tracers_ale", "fb200_solve_tracers_ale_resident", "fb200_debug_fetch",
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
@@ -258,6 +258,13 @@ class TracerEngine:
         """(min, max) of the resident tracer tr_num (1-based) over own wet cells"""
         lo, hi = C.c_double(), C.c_double()
         self.L.fb200_tracer_extrema(_i(tr_num), C.byref(lo), C.byref(hi))
+        _check(self.L)
+        return lo.value, hi.value
+
+    def extrema_noalloc(self, tr_num, nblocks=0):
+        """the same scan through fb200_tracer_extrema_noalloc (static device scratch, no allocation); nblocks <= 0: default grid"""
+        lo, hi = C.c_double(), C.c_double()
+        self.L.fb200_tracer_extrema_noalloc(_i(tr_num), _i(nblocks), C.byref(lo), C.byref(hi))
         _check(self.L)
         return lo.value, hi.value
 

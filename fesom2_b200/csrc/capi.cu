@@ -368,6 +368,8 @@ void fb200_solve_tracers_ale_resident(double* tr_arr_out) {
 // extrema of the resident tracer *tr_num (1-based) over this partition's own wet cells (the host combines the ranks with
 // its own MPI_Allreduce, as write_step_info.F90 does)
 void fb200_tracer_extrema(int* tr_num, double* tmin, double* tmax) { tracer_extrema(tctx(), *tr_num - 1, tmin, tmax); }
+// the same scan without any allocation (static device scratch, see tracer_kernels.cu); *nblocks <= 0: the default grid
+void fb200_tracer_extrema_noalloc(int* tr_num, int* nblocks, double* tmin, double* tmax) { tracer_extrema_noalloc(tctx(), *tr_num - 1, *nblocks, tmin, tmax); }
 
 // output means of the resident tracer *tr_num (1-based): fb200_mean_accumulate = update_means for that stream
 // (io_meandata.F90:768-794; *accuracy 8 = real64, 4 = real32), fb200_mean_fetch = compute_means + clean_meanarrays (:894-900)

@@ -160,5 +160,6 @@ bool tracer_step_begin(TracerCtx& c);
 void tracer_step_tracer(TracerCtx& c, int tr);
 void tracer_step_end(TracerCtx& c);
 void tracer_extrema(TracerCtx& c, int tr, double* tmin, double* tmax);
+void tracer_extrema_noalloc(TracerCtx& c, int tr, int nblocks, double* tmin, double* tmax);
 void tracer_mean_accumulate(TracerCtx& c, int tr, int accuracy);
 void tracer_mean_fetch(TracerCtx& c, int tr, void* mean_out);

@@ -1082,6 +1082,69 @@ void tracer_extrema(TracerCtx& c, int tr, double* tmin, double* tmax) {
     *tmin = lo; *tmax = hi;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// fb200_tracer_extrema_noalloc: the extrema scan for callers that cannot call cudaMalloc (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid allocation).  No counterpart in the reference.
+// The per-block partials of k_extrema and the final (min, max) live in a file-scope device array of fixed
+// size instead of a per-call allocation: FB200_EXTREMA_MAX_BLOCKS partials (+ 1 result slot) of 16 bytes = 32 784 bytes that
+// every GPU that loads the library holds until the process exits.  In host code the array's NAME is only a host-side
+// stand-in: the device address is looked up with cudaGetSymbolAddress once per device (with that device current) and it
+// is that pointer the kernels receive.  Every call shares the array, so two calls that overlap on the GPU (different
+// streams, different host threads) race on it; calls on one stream are ordered.  Nothing in it has to start at zero: each
+// call overwrites partials [0, nblocks) and the result slot before reading them, older contents are never read.
+#define FB200_EXTREMA_MAX_BLOCKS 2048
+#define FB200_MAX_DEVICES 64
+static __device__ __align__(256) double2 g_extrema_scratch[FB200_EXTREMA_MAX_BLOCKS + 1];
+static double2* g_extrema_scratch_ptr[FB200_MAX_DEVICES];      // device address of the array on each device, filled on first use
+
+// one block: combines the nb partials of k_extrema in a fixed order (min/max are order-independent anyway) into slot[nb_max]
+__global__ void LB(256) k_extrema_final(double2* __restrict__ scratch, int nb, int result_slot) {
+    double lo = 1.0e300, hi = -1.0e300;
+    for (int i = threadIdx.x; i < nb; i += blockDim.x) { const double2 v = scratch[i]; lo = dmin(lo, v.x); hi = dmax(hi, v.y); }
+    __shared__ double slo[8], shi[8];
+    for (int o = 16; o > 0; o >>= 1) { lo = dmin(lo, __shfl_down_sync(0xffffffffu, lo, o)); hi = dmax(hi, __shfl_down_sync(0xffffffffu, hi, o)); }
+    if ((threadIdx.x & 31) == 0) { slo[threadIdx.x >> 5] = lo; shi[threadIdx.x >> 5] = hi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; w++) { lo = dmin(lo, slo[w]); hi = dmax(hi, shi[w]); }
+        scratch[result_slot] = make_double2(lo, hi);
+    }
+}
+
+void tracer_extrema_noalloc(TracerCtx& c, int tr, int nblocks, double* tmin, double* tmax) {
+    *tmin = 0.0; *tmax = 0.0;
+    if (!fb_ok()) return;
+    if (!c.committed || tr < 0 || tr >= c.ntr) { fb_set_error(27, "fb200_tracer_extrema_noalloc: not committed or no such tracer"); return; }
+    if (nblocks > FB200_EXTREMA_MAX_BLOCKS) {
+        fb_set_error(28, "fb200_tracer_extrema_noalloc: nblocks = " + std::to_string(nblocks) + " exceeds the static scratch of " +
+                             std::to_string(FB200_EXTREMA_MAX_BLOCKS) + " per-block partials");
+        return;
+    }
+    int dev = -1;
+    CUDA_CHECK(cudaGetDevice(&dev));
+    if (!fb_ok()) return;
+    if (dev < 0 || dev >= FB200_MAX_DEVICES) { fb_set_error(28, "fb200_tracer_extrema_noalloc: device ordinal beyond the per-device address table"); return; }
+    if (!g_extrema_scratch_ptr[dev]) {                          // once per device, with that device current
+        double2* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_extrema_scratch);
+        if (e != cudaSuccess || !ptr) { fb_set_error(100 + (int)e, std::string("cudaGetSymbolAddress(g_extrema_scratch): ") + cudaGetErrorString(e)); return; }
+        g_extrema_scratch_ptr[dev] = ptr;
+    }
+    double2* scratch = g_extrema_scratch_ptr[dev];
+    fb_copy_sync();
+    cudaStream_t st = c.stream = fb_stream();
+    const int want = (c.myN + 255) / 256;
+    const int nb = nblocks > 0 ? std::min(nblocks, want) : std::min(148 * 8, want);     // k_extrema strides over the nodes by its grid size
+    KP p = make_kp(c, tr);
+    { ProfScope ps_("k_extrema", st); k_extrema<<<nb, 256, 0, st>>>(p, p.T, scratch); LAUNCH_CHECK(); }
+    { ProfScope ps_("k_extrema_final", st); k_extrema_final<<<1, 256, 0, st>>>(scratch, nb, FB200_EXTREMA_MAX_BLOCKS); LAUNCH_CHECK(); }
+    double2 h = make_double2(0.0, 0.0);                          // 16 bytes on the host stack
+    CUDA_CHECK(cudaMemcpyAsync(&h, scratch + FB200_EXTREMA_MAX_BLOCKS, sizeof(double2), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    if (!fb_ok()) return;
+    *tmin = h.x; *tmax = h.y;
+}
+
 // Output means of the resident tracers: update_means (io_meandata.F90:768-794) adds the stream's field to local_values in
 // the stream's precision (real64, or real32 with the field rounded to real32 first) and counts; output (:894-900) divides
 // by real(addcounter) in that precision and clears.  The whole tiled field is accumulated (dry levels, halo and padding

@@ -185,6 +185,16 @@ void fb200_update_vel(double* d_eta, double* UV_out);
  * the extrema lines of write_step_info (src/write_step_info.F90:220-504) test; lets a host that keeps the tracers resident
  * monitor them without pulling the fields (combine the ranks with MPI_Allreduce as the reference does) */
 void fb200_tracer_extrema(int* tr_num, double* tmin, double* tmax);
+/* The same scan WITHOUT ANY ALLOCATION.  It has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid allocation).  fb200_tracer_extrema allocates and frees its per-block partials on every call; this variant keeps
+ * them in a file-scope `static __device__` array of FB200_EXTREMA_MAX_BLOCKS = 2048 partials + 1 result slot (32 784 bytes
+ * per GPU, held from library load until the process exits) and calls no cudaMalloc, cudaFree or allocating library
+ * routine.  *nblocks = number of thread blocks (= partials) of the scan, <= 0 for the default (min(1184, myDim_nod2D/256));
+ * *nblocks > 2048 is refused with error 28 and the outputs are left at 0.  Every call shares the array: calls that overlap
+ * on the GPU (two streams, two host threads) race on it; calls on the library stream are ordered.  Each call overwrites
+ * what it reads, so nothing has to be cleared between calls. */
+void fb200_tracer_extrema_noalloc(int* tr_num, int* nblocks, double* tmin, double* tmax);
 /* Output means of the device-resident tracers (src/io_meandata.F90): fb200_mean_accumulate is update_means (:768-794) for
  * the stream of tracer *tr_num (1-based) — local_values += tr_arr(:,:,tr_num) in the stream's precision, *accuracy = 8
  * (real64) or 4 (real32: the field is rounded to real32 before it is added, as the reference does), addcounter += 1;
