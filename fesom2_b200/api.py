@@ -37,7 +37,9 @@ def lib(rebuild=False):
     global _lib
     if _lib is None or rebuild:
         so = _build.CUDA_SO
-        if rebuild or not os.path.exists(so) or _build.nvcc_path() is not None:
+        if os.environ.get("FB200_SO"):                      # a variant build for A/B measurements (build.build_cuda(out=...))
+            so = os.environ["FB200_SO"]
+        elif rebuild or not os.path.exists(so) or _build.nvcc_path() is not None:
             so = _build.build_cuda()
         if not os.path.exists(so):
             raise FesomB200Error("libfesom_b200.so is missing and nvcc is unavailable: build it with __graft_entry__.build()")

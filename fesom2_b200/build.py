@@ -65,20 +65,38 @@ def nccl_flags():
     return ["-lnccl"]
 
 
-def build_cuda(force=False, verbose=False):
+def build_cuda(force=False, verbose=False, out=None, defines=(), fmad=False):
+    """every .cu -> its own object (in parallel, rebuilt only when it or a header changed), then one link.
+    out / defines: a variant library for A/B measurements (FB200_SO selects it at run time, see api.lib)"""
+    import concurrent.futures as cf
+    so = out or CUDA_SO
+    tag = "" if not out else "." + os.path.splitext(os.path.basename(out))[0]
     src = sorted(glob.glob(os.path.join(PKG, "csrc", "*.cu")))
-    dep = src + glob.glob(os.path.join(PKG, "csrc", "*.cuh")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
-    if force or _newer(CUDA_SO, dep):
-        nvcc = nvcc_path()
+    hdr = glob.glob(os.path.join(PKG, "csrc", "*.cuh")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
+    objdir = os.path.join(PKG, "csrc", "build")
+    nvcc = nvcc_path()
+    objs = [os.path.join(objdir, os.path.basename(f)[:-3] + tag + ".o") for f in src]
+    todo = [(f, o) for f, o in zip(src, objs) if force or _newer(o, [f] + hdr)]
+    if todo or force or _newer(so, objs):
         if nvcc is None:
+            if os.path.exists(so) and not force:
+                return so                  # a box without nvcc uses the library that travelled with the snapshot
             raise RuntimeError("nvcc not found: cannot build libfesom_b200.so")
-        flags = list(NVCC_FLAGS)
+        os.makedirs(objdir, exist_ok=True)
+        cflags = [x for x in NVCC_FLAGS if x != "-shared" and not (fmad and x == "--fmad=false")] + ["-c"] + ["-D" + d for d in defines]
         if verbose:
-            flags += ["-Xptxas", "-v"]
-        out = _run([nvcc] + flags + ["-I", os.path.join(ROOT, "include"), "-o", CUDA_SO] + src + nccl_flags())
+            cflags += ["-Xptxas", "-v"]
+        nf = nccl_flags()
+        inc = ["-I", os.path.join(ROOT, "include")] + (nf[nf.index("-I"):nf.index("-I") + 2] if "-I" in nf else [])
+
+        def one(fo):
+            return _run([nvcc] + cflags + inc + ["-o", fo[1], fo[0]])
+        with cf.ThreadPoolExecutor(max_workers=8) as ex:
+            outs = list(ex.map(one, todo))
         if verbose:
-            print(out)
-    return CUDA_SO
+            print("\n".join(outs))
+        _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC", "-shared", "-o", so] + objs + nccl_flags())
+    return so
 
 
 def build_oracle(force=False):

@@ -313,15 +313,19 @@ void fb200_solve_tracers_ale(double* tr_arr, double* tr_arr_old) {
     cudaStream_t comp = c.stream, copy = copy_stream();
     const int L = c.nl - 1;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
-    for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
+    for (int t0 = 0; t0 < c.ntr && fb_ok();) {             // the tracers of a pass (tracer_group_size: 1 or 2) go together
+        const int nt = tracer_group_size(c, t0);
         c.stream = copy;
-        ctx_push_node_field(c, tr_arr + rf * tr, L, c.N, c.T.p + nf * tr);
-        ctx_push_node_field(c, tr_arr_old + rf * tr, L, c.N, c.Told.p + nf * tr);
-        CUDA_CHECK(cudaEventRecord(g_ev_push[tr], copy));
+        for (int tr = t0; tr < t0 + nt; tr++) {
+            ctx_push_node_field(c, tr_arr + rf * tr, L, c.N, c.T.p + nf * tr);
+            ctx_push_node_field(c, tr_arr_old + rf * tr, L, c.N, c.Told.p + nf * tr);
+        }
+        CUDA_CHECK(cudaEventRecord(g_ev_push[t0], copy));
         c.stream = comp;
-        CUDA_CHECK(cudaStreamWaitEvent(comp, g_ev_push[tr], 0));
-        tracer_step_tracer(c, tr);
-        CUDA_CHECK(cudaEventRecord(g_ev_done[tr], comp));
+        CUDA_CHECK(cudaStreamWaitEvent(comp, g_ev_push[t0], 0));
+        tracer_step_group(c, t0, nt);
+        for (int tr = t0; tr < t0 + nt; tr++) CUDA_CHECK(cudaEventRecord(g_ev_done[tr], comp));
+        t0 += nt;
     }
     const bool late = c.opt.relax_zonal != 0;             // relax_zonal_temp touches tracer 1 on every later pass
     for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
@@ -352,13 +356,16 @@ void fb200_solve_tracers_ale_resident(double* tr_arr_out) {
     const int L = c.nl - 1;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE, rf = (size_t)L * c.N;
     const bool late = c.opt.relax_zonal != 0;             // relax_zonal_temp touches tracer 1 on every later pass: copy after the loop
-    for (int tr = 0; tr < c.ntr && fb_ok(); tr++) {
-        tracer_step_tracer(c, tr);
-        CUDA_CHECK(cudaEventRecord(g_ev_done[tr], comp));
-        if (late && tr + 1 < c.ntr) continue;
+    for (int t0 = 0; t0 < c.ntr && fb_ok();) {
+        const int nt = tracer_group_size(c, t0);
+        tracer_step_group(c, t0, nt);
+        const int last = t0 + nt - 1;
+        CUDA_CHECK(cudaEventRecord(g_ev_done[last], comp));
+        t0 += nt;
+        if (late && t0 < c.ntr) continue;
         c.stream = copy;
-        CUDA_CHECK(cudaStreamWaitEvent(copy, g_ev_done[tr], 0));
-        for (int k = late ? 0 : tr; k <= tr; k++) ctx_pull_node_field(c, c.T.p + nf * k, L, c.N, tr_arr_out + rf * k, 1, 0, false);
+        CUDA_CHECK(cudaStreamWaitEvent(copy, g_ev_done[last], 0));
+        for (int k = late ? 0 : last - nt + 1; k <= last; k++) ctx_pull_node_field(c, c.T.p + nf * k, L, c.N, tr_arr_out + rf * k, 1, 0, false);
         c.stream = comp;
     }
     tracer_step_end(c);

@@ -80,6 +80,7 @@ struct TracerCtx {
     // dimensions
     int nl = 0, nlp = 0, myN = 0, N = 0, myE = 0, E = 0, Eall = 0, myEd = 0, ntr = 0;
     int Ntiles = 0, myNtiles = 0, Etiles = 0, Edtiles = 0, maxdeg = 0, maxnie = 0;
+    int nwork = 1;                  // sets of per-tracer work fields (= tracers per pass)
     Options opt;
     bool committed = false;
     // host staging of the init_* calls
@@ -158,6 +159,8 @@ void ctx_release(TracerCtx& c);
 void tracer_step_all(TracerCtx& c);
 bool tracer_step_begin(TracerCtx& c);
 void tracer_step_tracer(TracerCtx& c, int tr);
+int tracer_group_size(const TracerCtx& c, int t0);
+void tracer_step_group(TracerCtx& c, int t0, int nt);
 void tracer_step_end(TracerCtx& c);
 void tracer_extrema(TracerCtx& c, int tr, double* tmin, double* tmax);
 void tracer_extrema_noalloc(TracerCtx& c, int tr, int nblocks, double* tmin, double* tmax);

@@ -163,7 +163,7 @@ void ctx_commit(TracerCtx& c) {
     const int nlp = c.nlp, N = c.N, myN = c.myN, Eall = c.Eall, myE = c.myE, myEd = c.myEd;
     c.Ntiles = (N + TILE - 1) / TILE; c.myNtiles = (myN + TILE - 1) / TILE;
     c.Etiles = (Eall + TILE - 1) / TILE; c.Edtiles = (myEd + TILE - 1) / TILE;
-    if ((long long)std::max(std::max(c.Ntiles, c.Etiles), c.Edtiles) * nlp * TILE >= (1LL << 31)) { fb_set_error(13, "mesh too large for 32-bit tile offsets"); return; }
+    if ((long long)std::max(std::max(c.Ntiles, c.Etiles), c.Edtiles + 1) * nlp * TILE >= (1LL << 31)) { fb_set_error(13, "mesh too large for 32-bit tile offsets"); return; }
     const double r_earth = 6367500.0;
     // elements
     std::vector<int> el_nb((size_t)3 * Eall, 0); std::vector<unsigned> el_lev(Eall);
@@ -281,9 +281,14 @@ void ctx_commit(TracerCtx& c) {
         c.ns_i.upload(ni); c.ns_m.upload(mk);
         {
             std::vector<SlotRec> sp(ns);
+            const int zero_edge = c.Edtiles * nlp * TILE;      // first entry of the never-written extra tile of the edge fields
             for (size_t k = 0; k < ns; k++) {
                 sp[k].bo = ni[k].x; sp[k].bed = ni[k].w;
                 sp[k].mk = slot[k] < 0 ? 0ull : ((mk[k].x | mk[k].y) & ~1ull) | (unsigned long long)(slot[k] & 1);
+                if (slot[k] < 0) {                              // empty slot: the node's own column and a zero edge entry (tracer_kernels2.cu, SlotBatch)
+                    const int node = (int)(k / ((size_t)c.maxdeg * TILE)) * TILE + (int)(k % TILE);
+                    sp[k].bo = tile_base(node, nlp); sp[k].bed = zero_edge;
+                }
             }
             c.ns_p.upload(sp);
         }
@@ -303,12 +308,16 @@ void ctx_commit(TracerCtx& c) {
         c.nie_slot.upload(slot);
     }
     // fields
-    const size_t nf = (size_t)c.Ntiles * nlp * TILE, ef = (size_t)c.Etiles * nlp * TILE, df = (size_t)c.Edtiles * nlp * TILE;
+    const size_t nf = (size_t)c.Ntiles * nlp * TILE, ef = (size_t)c.Etiles * nlp * TILE, df = (size_t)(c.Edtiles + 1) * nlp * TILE;   // edge fields: + 1 never-written tile (tracer_kernels2.cu)
     for (DevBuf<double>* b : {&c.area, &c.areasvol, &c.W, &c.We, &c.Wi, &c.hnode, &c.hnode_new, &c.Z3, &c.zbar3, &c.Kv, &c.Ki,
-                              &c.sl1, &c.sl2, &c.sl3, &c.sw3d, &c.trz, &c.LO, &c.adf_v, &c.tstar}) b->alloc(nf);
-    c.fpm.alloc(nf);
-    c.helem.alloc(ef); c.UV.alloc(ef); c.txy.alloc(ef);
-    c.adf_h.alloc(df); c.eflx.alloc(df);
+                              &c.sl1, &c.sl2, &c.sl3, &c.sw3d}) b->alloc(nf);
+    // work fields: one set per tracer of a pass (the column kernels take two tracers per pass)
+    c.nwork = c.ntr >= 2 ? 2 : 1;
+    const size_t nw = (size_t)c.nwork;
+    for (DevBuf<double>* b : {&c.trz, &c.LO, &c.adf_v, &c.tstar}) b->alloc(nf * nw);
+    c.fpm.alloc(nf * nw);
+    c.helem.alloc(ef); c.UV.alloc(ef); c.txy.alloc(ef * nw);
+    c.adf_h.alloc(df * nw); c.eflx.alloc(df * nw);
     c.T.alloc(nf * c.ntr); c.Told.alloc(nf * c.ntr);
     for (DevBuf<double>* b : {&c.heat_flux, &c.water_flux, &c.virtual_salt, &c.relax_salt, &c.real_salt_flux}) b->alloc(N);
     ctx_push_node_field(c, c.h_area.data(), c.nl, N, c.area.p);

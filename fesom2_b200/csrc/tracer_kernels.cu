@@ -7,68 +7,10 @@
 // (compiled with --fmad=false) — see the file:line notes at each kernel.
 #include "common.cuh"
 #include "comm.cuh"
+#include "tracer_dev.cuh"
+#include "tracer_kernels2.cuh"
 #include <algorithm>
-
-#define LB(n) __launch_bounds__(n)
-
-struct KP {                       // kernel parameter block (by value)
-    int nl, nlp, myN, N, myE, Eall, myEd, maxdeg, maxnie;
-    double dt, ph, pv, eps_ab, is_nonlinfs;
-    int hor, ver, w_split, Redi, use_sw_pene, do_hor_diff, tracer_id, tr_num;
-    const EdgeRec* edge; const EdgeHo* edgeho; const int* ne_slot; const int* nie_slot; const int* el_nb;
-    const int* tile_deg;           // per node tile: largest number of incident edges among its 32 nodes
-    const int4* ns_i;              // per (node, slot): tile bases (other node, element 1, element 2 or -1, edge)
-    const ulonglong2* ns_m;        // level masks (m1, m2)
-    const SlotRec* ns_p;           // packed record the node kernels read: one 16-byte load per (node, slot)
-    const double2 *ns_d1, *ns_d2;  // (dX1,dY1), (dX2,dY2)
-    const unsigned* el_lev; const double* el_g; const double* el_area; const unsigned* n_lev; const int* n_nbl; const double* n_znb;
-    const double2* UV;              // (u, v) per element-level
-    const double *area, *areasvol, *helem, *W, *We, *Wi, *hnode, *hnode_new, *Z3, *zbar3, *Kv, *Ki, *sl1, *sl2, *sl3, *sw3d;
-    const double *heat_flux, *water_flux, *virtual_salt, *relax_salt, *real_salt_flux;
-    const double *kgT, *kgS, *kb2, *kb3; double ref_sss; int ref_sss_local;      // KPP non-local transport (fb200_push_kpp_nonlocal)
-    double *T, *Told, *T1;        // this tracer's fields; T1 = tracer 1 (bc_surface)
-    double2 *txy, *fpm;            // (tr_xy(1), tr_xy(2)) per element-level; (fct_plus, fct_minus) per node-level
-    double *trz, *LO, *adf_h, *adf_v, *tstar;
-    const double* redi_v;          // diff_ver_part_redi_expl's contribution to del_ttf per (node, level), from k_redi_expl (Redi only)
-    double* eflx;                  // per (edge, level) scratch: upwind flux of ttf (k_ho_edge -> k_lo), then the diffusive flux (k_diff_edge -> k_update)
-};
-
-__device__ __forceinline__ int tbase(int ent, int nlp) { return (ent >> 5) * (nlp * TILE) + (ent & 31); }
-#define AT(p, base, nz) (p)[(base) + (((nz) - 1) << 5)]          // 1-based level
-__device__ __forceinline__ int node_of_base_d(int base, int nlp) { return (base / (nlp * TILE)) * TILE + base % (nlp * TILE); }   // entity id of a tile base
-
-// min/max of two non-NaN doubles as one compare + select (the values here are never NaN; fmin/fmax spend several
-// more instructions on NaN propagation)
-__device__ __forceinline__ double omin(double a, double b) { return a < b ? a : b; }     // MIN/MAX as the oracle evaluates them
-__device__ __forceinline__ double omax(double a, double b) { return a > b ? a : b; }
-__device__ __forceinline__ double dmin(double a, double b) { return (b < a) ? b : a; }
-__device__ __forceinline__ double dmax(double a, double b) { return (b > a) ? b : a; }
-// x / b, correctly rounded, given rb = 1.0 / b: quotient estimate plus one exact-residual correction (the last two
-// steps of the IEEE division sequence; the Newton iterations for 1/b are paid once per level instead of per edge).
-// tests/test_gpu_tracer.py::test_div_by_matches_ieee_division checks it against '/' on 2^24 operand pairs.
-__device__ __forceinline__ double div_by(double x, double b, double rb) {
-    const double q = x * rb;
-    const double r = fma(-b, q, x);
-    return fma(r, rb, q);
-}
-
-// Level masks of an edge: bit nz of m1 (m2) is set where the median-dual segment in element 1 (2) carries a flux at
-// level nz — the five ranges (A)-(E) of oce_adv_tra_hor.F90:129-209 evaluated once on the host (context.cu), so the
-// kernels test two bits instead of re-deriving the ranges for every (edge, level).
-__device__ __forceinline__ int mask_segs(unsigned long long m1, unsigned long long m2, int nz) {
-    return (int)((m1 >> nz) & 1ull) | ((int)((m2 >> nz) & 1ull) << 1);
-}
-// volume flux through the two median-dual segments of an edge, oce_adv_tra_hor.F90:139,157,176
-__device__ __forceinline__ double seg_vflux(const KP& p, int segs, int be1, int be2, double dX1, double dY1, double dX2, double dY2, int nz) {
-    double c1 = 0.0, c2 = 0.0;
-    if (segs & 1) { const double2 uv = AT(p.UV, be1, nz); c1 = (-uv.y * dX1 + uv.x * dY1) * AT(p.helem, be1, nz); }
-    if (segs & 2) { const double2 uv = AT(p.UV, be2, nz); c2 = (uv.y * dX2 - uv.x * dY2) * AT(p.helem, be2, nz); }
-    if (segs == 3) return c1 + c2;
-    return (segs & 1) ? c1 : c2;
-}
-__device__ __forceinline__ double upw1_flux(double t1, double t2, double vflux) {     // oce_adv_tra_hor.F90:143-146
-    return -0.5 * (t1 * (vflux + fabs(vflux)) + t2 * (vflux - fabs(vflux)));
-}
+#include <cstdlib>
 
 // ---------------------------------------------------------------------------------------------------
 // K1: Adams-Bashforth extrapolation, oce_tracer_mod.F90:64 — over every entry (halo and padding included)
@@ -107,96 +49,6 @@ __global__ void LB(128) k_grad_z(KP p, const double* __restrict__ ttf) {
     }
     AT(p.trz, b, nzmin) = 0.0;
     AT(p.trz, b, nzmax) = 0.0;
-}
-
-// ---------------------------------------------------------------------------------------------------
-// vertical fluxes at interface nz of one column (flux_in = 0 variants; the caller subtracts)
-__device__ __forceinline__ double ver_upw1(const double* __restrict__ T, const double* __restrict__ W, const double* __restrict__ area,
-                                           int b, int nz, int nzmin, int nzmax) {                 // oce_adv_tra_ver.F90:255-281
-    if (nz == nzmax) return 0.0;
-    const double w = AT(W, b, nz);
-    if (nz == nzmin) return -w * AT(T, b, nz) * AT(area, b, nz);
-    return -0.5 * (AT(T, b, nz) * (w + fabs(w)) + AT(T, b, nz - 1) * (w - fabs(w))) * AT(area, b, nz);
-}
-__device__ __forceinline__ double ver_qr4c(const KP& p, const double* __restrict__ T, const double* __restrict__ W,
-                                           int b, int nz, int nzmin, int nzmax) {                 // oce_adv_tra_ver.F90:314-356
-    if (nz == nzmax) return 0.0;
-    const double w = AT(W, b, nz), ar = AT(p.area, b, nz);
-    if (nz == nzmin) return -AT(T, b, nz) * w * ar;
-    if (nz == nzmin + 1 || nz == nzmax - 1) return -0.5 * (AT(T, b, nz - 1) + AT(T, b, nz)) * w * ar;
-    const double t0 = AT(T, b, nz), tm1 = AT(T, b, nz - 1), tm2 = AT(T, b, nz - 2), tp1 = AT(T, b, nz + 1);
-    const double z0 = AT(p.Z3, b, nz), zm1 = AT(p.Z3, b, nz - 1), zm2 = AT(p.Z3, b, nz - 2), zp1 = AT(p.Z3, b, nz + 1);
-    const double zb = AT(p.zbar3, b, nz);
-    const double qc = (tm1 - t0) / (zm1 - z0);
-    const double qu = (t0 - tp1) / (z0 - zp1);
-    const double qd = (tm2 - tm1) / (zm2 - zm1);
-    const double Tmean1 = t0 + (2 * qc + qu) * (zb - z0) / 3.0;
-    const double Tmean2 = tm1 + (2 * qc + qd) * (zb - zm1) / 3.0;
-    const double Tmean = (w + fabs(w)) * Tmean1 + (w - fabs(w)) * Tmean2;
-    return (-0.5 * (1.0 - p.pv) * Tmean - p.pv * (0.5 * (Tmean1 + Tmean2)) * w) * ar;
-}
-__device__ __forceinline__ double ver_cdiff(const KP& p, const double* __restrict__ T, const double* __restrict__ W,
-                                            int b, int nz, int nzmin) {                           // oce_adv_tra_ver.F90:566-585
-    const double w = AT(W, b, nz), ar = AT(p.area, b, nz);
-    if (nz == nzmin) return -w * AT(T, b, nz) * ar;
-    const double tv = 0.5 * (AT(T, b, nz - 1) + AT(T, b, nz));
-    return -tv * w * ar;
-}
-
-// PPM (Colella & Woodward) vertical flux, adv_tra_vert_ppm, oce_adv_tra_ver.F90:361-538.  The reference walks down the
-// column keeping the interface values tv(:) and writes tvert(nz) from the cell the flow leaves; here every interface
-// is evaluated on its own: ppm_iface() is tv(k) with the reference's assignment order deciding which rule wins on short
-// columns, ver_ppm() the flux through interface nz from its upwind cell.
-__device__ __noinline__ double ppm_iface(const double* __restrict__ T, const double* __restrict__ hn, const double* __restrict__ W,
-                                         int b, int k, int nzmin, int nzmax) {
-    if (k == nzmax) return AT(T, b, nzmax - 1);                                                        // :411
-    if (k == nzmax - 1) {                                                                              // :408-409
-        const double s = copysign(1.0, AT(W, b, nzmax - 1));
-        return -AT(T, b, max(nzmax - 2, 1)) * dmin(s, 0.0) + AT(T, b, nzmax - 1) * dmax(s, 0.0);
-    }
-    if (k == nzmin) return AT(T, b, nzmin);                                                            // :401
-    if (k == nzmin + 1) return 0.5 * (AT(T, b, nzmin) + AT(T, b, nzmin + 1));                          // :404
-    const int nz = k - 1;                                                                              // :416-456
-    const double tm1 = AT(T, b, nz - 1), t0 = AT(T, b, nz), tp1 = AT(T, b, nz + 1), tp2 = AT(T, b, nz + 2);
-    const double dzjm1 = AT(hn, b, nz - 1), dzj = AT(hn, b, nz), dzjp1 = AT(hn, b, nz + 1), dzjp2 = AT(hn, b, nz + 2);
-    double deltaj = dzj / (dzjm1 + dzj + dzjp1) *
-                    ((2.0 * dzjm1 + dzj) / (dzjp1 + dzj) * (tp1 - t0) + (dzj + 2.0 * dzjp1) / (dzjm1 + dzj) * (t0 - tm1));
-    double deltajp1 = dzjp1 / (dzj + dzjp1 + dzjp2) *
-                      ((2.0 * dzj + dzjp1) / (dzjp2 + dzjp1) * (tp2 - tp1) + (dzjp1 + 2.0 * dzjp2) / (dzj + dzjp1) * (tp1 - t0));
-    if ((tp1 - t0) * (t0 - tm1) > 0.0)
-        deltaj = copysign(dmin(dmin(fabs(deltaj), 2.0 * fabs(tp1 - t0)), 2.0 * fabs(t0 - tm1)), deltaj);
-    else deltaj = 0.0;
-    if ((tp2 - tp1) * (tp1 - t0) > 0.0)
-        deltajp1 = copysign(dmin(dmin(fabs(deltajp1), 2.0 * fabs(tp2 - tp1)), 2.0 * fabs(tp1 - t0)), deltajp1);
-    else deltajp1 = 0.0;
-    return t0 + dzj / (dzj + dzjp1) * (tp1 - t0) +
-           1.0 / (dzjm1 + dzj + dzjp1 + dzjp2) *
-               ((2.0 * dzjp1 * dzj) / (dzj + dzjp1) * ((dzjm1 + dzj) / (2.0 * dzj + dzjp1) - (dzjp2 + dzjp1) / (2.0 * dzjp1 + dzj)) * (tp1 - t0) -
-                dzj * (dzjm1 + dzj) / (2.0 * dzj + dzjp1) * deltajp1 + dzjp1 * (dzjp1 + dzjp2) / (dzj + 2.0 * dzjp1) * deltaj);
-}
-__device__ __noinline__ double ver_ppm(const KP& p, const double* __restrict__ T, const double* __restrict__ W,
-                                       int b, int nz, int nzmin, int nzmax) {
-    if (nz == nzmax) return 0.0;                                                                       // :527
-    const double w = AT(W, b, nz), ar = AT(p.area, b, nz);
-    if (nz == nzmin) return -ppm_iface(T, p.hnode_new, W, b, nzmin, nzmin, nzmax) * w * ar;            // :525
-    if (w == 0.0) return 0.0;
-    const int j = (w > 0.0) ? nz : nz - 1;                                                             // the cell the flow leaves (:461-519)
-    const double tj = AT(T, b, j);
-    double aL = ppm_iface(T, p.hnode_new, W, b, j, nzmin, nzmax), aR = ppm_iface(T, p.hnode_new, W, b, j + 1, nzmin, nzmax);
-    if ((aR - tj) * (tj - aL) <= 0.0) { aL = tj; aR = tj; }
-    if ((aR - aL) * (tj - 0.5 * (aL + aR)) > (aR - aL) * (aR - aL) / 6.0) aL = 3.0 * tj - 2.0 * aR;
-    if ((aR - aL) * (tj - 0.5 * (aR + aL)) < -((aR - aL) * (aR - aL)) / 6.0) aR = 3.0 * tj - 2.0 * aL;
-    const double dzj = AT(p.hnode, b, j);
-    const double aj = 6.0 * (tj - 0.5 * (aL + aR));
-    double f;
-    if (w > 0.0) {
-        const double x = dmin(w * p.dt / dzj, 1.0);
-        f = (-aL - 0.5 * x * (aR - aL + (1.0 - 2.0 / 3.0 * x) * aj));
-    } else {
-        const double x = dmin(-w * p.dt / dzj, 1.0);
-        f = (-aR + 0.5 * x * (aR - aL - (1.0 - 2.0 / 3.0 * x) * aj));
-    }
-    return f * ar * w;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -339,33 +191,6 @@ __global__ void LB(64) k_vert_impl(KP p, double* __restrict__ ttf, const double*
         x = tp[(nz - 1) * BS + tid] - cp[(nz - 1) * BS + tid] * x;
         AT(ttf, b, nz) = AT(ttf, b, nz) + x;
     }
-}
-
-// ---------------------------------------------------------------------------------------------------
-// area-weighted mean of the elemental gradients around a node (fill_up_dn_grad fallback, oce_muscl_adv.F90:313-328)
-__device__ __noinline__ void node_mean_grad(const int* __restrict__ nie_slot, int maxnie, const unsigned* __restrict__ el_lev,
-                                            const double* __restrict__ el_area, const double2* __restrict__ txy,
-                                            int nlp, int node, int nz, double& gx, double& gy) {
-    double tvol = 0.0, tx = 0.0, ty = 0.0;
-    const int* slot = nie_slot + (size_t)(node >> 5) * maxnie * TILE + (node & 31);
-    for (int k = 0; k < maxnie; k++) {
-        const int e = slot[k * TILE];
-        if (e < 0) break;
-        const unsigned lv = el_lev[e];
-        const int nu = lv & 255, nlm = (lv >> 8) & 255;
-        if (nlm < nz || nz < nu) continue;
-        const double ar = el_area[e];
-        const int be = tbase(e, nlp);
-        const double2 g = AT(txy, be, nz);
-        tvol = tvol + ar;
-        tx = tx + g.x * ar;
-        ty = ty + g.y * ar;
-    }
-    // tvol == 0: nz lies outside this node's own level range (above its cavity top or below its bottom).  The reference
-    // does not compute edge_up_dn_grad there (oce_muscl_adv.F90:313,337: the loops start at ulevels_nod2D(node)) and the
-    // entry only ever meets a zero volume flux (no element of the node is wet at nz); 0/0 would turn that 0 into NaN
-    if (tvol == 0.0) { gx = 0.0; gy = 0.0; return; }
-    gx = tx / tvol; gy = ty / tvol;
 }
 
 // K4: high-order horizontal flux minus low-order flux = antidiffusive flux adf_h.  Block = one tile of 32 edges
@@ -588,19 +413,6 @@ __global__ void __launch_bounds__(256, 5) k_diff_edge(KP p) {
 // K7a: b3 limiting + oce_tra_adv_flux2dtracer (oce_adv_tra_driver.F90:223-268) + del_ttf assembly
 // (oce_ale_tracer.F90:240) + diff_part_hor_redi (:934-1077) + T* update (:294-305).  Node-kernel mapping.
 // Writes tstar; tr_arr_old = tr_arr is done by the caller for all entries.
-// diffusive flux through interface z of diff_ver_part_expl_ale (oce_ale_tracer.F90:354-380): surface flux at the top,
-// Kv * dT/dz * area below, zero under the last layer
-__device__ __forceinline__ double expl_vd(const KP& p, const double* __restrict__ T, int n, int b, int z, int ul1, int nl1) {
-    if (z > nl1) return 0.0;
-    if (z == ul1) {
-        if (p.tr_num == 1) return -p.heat_flux[n] / 4.2e6;
-        if (p.tr_num == 2) return p.virtual_salt[n] + p.relax_salt[n] - p.real_salt_flux[n] * p.is_nonlinfs;
-        return 0.0;
-    }
-    const double zinv1 = 1.0 / (AT(p.Z3, b, z - 1) - AT(p.Z3, b, z));
-    return (AT(p.Kv, b, z) + 0.0) * (AT(T, b, z - 1) - AT(T, b, z)) * zinv1 * AT(p.area, b, z);
-}
-
 // FCT: limited fluxes (b3) and the LO terms of flux2dtracer, else the raw high-order fluxes; EXPL: i_vert_diff=.false.,
 // the explicit vertical diffusion joins del_ttf here and no implicit solve follows
 template <bool FCT, bool EXPL>
@@ -1042,7 +854,7 @@ __global__ void LB(128) k_clamp_salt(KP p, double* __restrict__ S) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-static KP make_kp(TracerCtx& c, int tr) {
+static KP make_kp(TracerCtx& c, int tr, int wslot = 0) {
     KP p;
     p.nl = c.nl; p.nlp = c.nlp; p.myN = c.myN; p.N = c.N; p.myE = c.myE; p.Eall = c.Eall; p.myEd = c.myEd; p.maxdeg = c.maxdeg; p.maxnie = c.maxnie;
     p.dt = c.opt.dt; p.ph = c.opt.ph; p.pv = c.opt.pv; p.eps_ab = c.opt.epsilon; p.is_nonlinfs = c.opt.is_nonlinfs;
@@ -1058,8 +870,11 @@ static KP make_kp(TracerCtx& c, int tr) {
     p.heat_flux = c.heat_flux.p; p.water_flux = c.water_flux.p; p.virtual_salt = c.virtual_salt.p; p.relax_salt = c.relax_salt.p; p.real_salt_flux = c.real_salt_flux.p;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     p.T = c.T.p + nf * tr; p.Told = c.Told.p + nf * tr; p.T1 = c.T.p;
-    p.txy = c.txy.p; p.fpm = c.fpm.p; p.trz = c.trz.p; p.LO = c.LO.p; p.adf_h = c.adf_h.p; p.adf_v = c.adf_v.p;
-    p.tstar = c.tstar.p; p.eflx = c.eflx.p; p.redi_v = c.redi_v.p;
+    // work fields: one set per tracer of a pass (work slot wslot < c.nwork)
+    const size_t ef = (size_t)c.Etiles * c.nlp * TILE, df = (size_t)(c.Edtiles + 1) * c.nlp * TILE, w = (size_t)wslot;   // edge fields: + 1 never-written tile
+    p.zero_edge = c.Edtiles * c.nlp * TILE;
+    p.txy = c.txy.p + ef * w; p.fpm = c.fpm.p + nf * w; p.trz = c.trz.p + nf * w; p.LO = c.LO.p + nf * w; p.adf_h = c.adf_h.p + df * w;
+    p.adf_v = c.adf_v.p + nf * w; p.tstar = c.tstar.p + nf * w; p.eflx = c.eflx.p + df * w; p.redi_v = c.redi_v.p ? c.redi_v.p + nf * w : nullptr;
     return p;
 }
 
@@ -1228,87 +1043,154 @@ bool tracer_step_begin(TracerCtx& c) {
     return fb_ok();
 }
 
-void tracer_step_tracer(TracerCtx& c, int tr) {
+// which phases run the first-generation kernels of this file instead of the column kernels of tracer_kernels2.cu:
+// FB200_V1 = comma-separated list of {grad, edge, lo, bounds, diff, update} or "all" (A/B measurements; results are
+// bit-identical either way).  Default: none.
+static unsigned v1_phases() {
+    static int cached = -1;
+    if (cached >= 0) return (unsigned)cached;
+    unsigned m = 0;
+    const char* e = getenv("FB200_V1");
+    if (e) {
+        std::string s(e);
+        const char* names[6] = {"grad", "edge", "lo", "bounds", "diff", "update"};
+        if (s.find("all") != std::string::npos) m = 63;
+        for (int k = 0; k < 6; k++) if (s.find(names[k]) != std::string::npos) m |= 1u << k;
+    }
+    cached = (int)m;
+    return m;
+}
+enum { PH_GRAD = 1, PH_EDGE = 2, PH_LO = 4, PH_BOUNDS = 8, PH_DIFF = 16, PH_UPDATE = 32 };
+
+// number of tracers the pass starting at tracer t0 handles together (1 or 2).  Tracers of a group must not read each
+// other inside the pass: bc_surface reads tracer 1 for every tracer with id 0 (oce_ale_tracer.F90:1170), and
+// relax_zonal_temp touches tracer 1 after every pass of the tracer loop — in both cases the tracers go one by one.
+int tracer_group_size(const TracerCtx& c, int t0) {
+    if (c.nwork < 2 || t0 + 1 >= c.ntr || c.opt.relax_zonal) return 1;
+    if (getenv("FB200_NT1")) return 1;
+    for (int t = t0; t < t0 + 2; t++) if (t > 0 && c.opt.tracer_id[t] == 0) return 1;
+    return 2;
+}
+
+// every kernel of the tracers t0 .. t0+nt-1 (nt <= MAXNT) on the library stream; work fields of tracer t0+k live in work
+// slot k
+void tracer_step_group(TracerCtx& c, int t0, int nt) {
     if (!fb_ok()) return;
     cudaStream_t st = c.stream;
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     const int gN64 = (c.myN + 63) / 64, gE = (c.myE + 127) / 128, gNall = (c.N + 127) / 128;
     const int LPB = c.nl - 1 <= 48 ? 3 : 4;                     // k_fct_bounds: one block = one tile x the whole column, <= 16 level rows
     const dim3 blk(TILE, (c.nl - 1 + LPB - 1) / LPB);
-    // kernels without block-wide exchange run on 8 level rows per block (LPT * 8 = 24 levels) and gridDim.y level chunks
+    // first-generation kernels without block-wide exchange: 8 level rows per block (LPT * 8 = 24 levels), gridDim.y level chunks
     const dim3 blk8(TILE, 8);
     const int nchunk = (c.nl - 1 + LPT * 8 - 1) / (LPT * 8);
+    const dim3 gN8(c.myNtiles, nchunk);
     const size_t smt = (size_t)c.nlp * TILE * sizeof(double);   // one [nlp][32] shared array
     const size_t sm_64 = (size_t)c.nlp * 64 * sizeof(double);
     const bool multi = comm_nranks() > 1 && c.halo_nod != nullptr;
-#define KL(name, ...) do { ProfScope ps_(name, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
-    KP p = make_kp(c, tr);
-    const double ca = -(0.5 + c.opt.epsilon), cb = 1.5 + c.opt.epsilon;
-    KL("k_ab2", k_ab2<<<148 * 8, 256, 0, st>>>(p.Told, p.T, nf, ca, cb));
-    KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told));
-    if (multi) halo_exchange_tiled(*c.halo_elem, (double*)p.txy, c.nlp, 2, st);       // exchange_elem(tr_xy), oce_tracer_mod.F90:68,72
     const bool fct = c.opt.tra_adv_lim == 0;
-    if (fct) KL("k_ho_edge", k_ho_edge<true><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-    else KL("k_ho_edge", k_ho_edge<false><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
+    // gradients: the per-tracer kernels of this file (they run at the HBM roofline; the two-tracer variant is no faster) unless FB200_V2_GRAD
+    const unsigned v1 = v2_usable(c) ? (v1_phases() | (getenv("FB200_V2_GRAD") ? 0u : (unsigned)PH_GRAD)) : 63u;
+#define KL(name, ...) do { ProfScope ps_(name, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
+#define EACH(...) for (int k_ = 0; k_ < nt; k_++) { KP& p = pk[k_]; (void)p; __VA_ARGS__; }
+    if (c.opt.Redi && !c.redi_v.p) c.redi_v.alloc(nf * c.nwork);
+    KP pk[MAXNT];
+    TrSet s;
+    for (int k = 0; k < nt; k++) {
+        pk[k] = make_kp(c, t0 + k, k);
+        s.T[k] = pk[k].T; s.Told[k] = pk[k].Told; s.LO[k] = pk[k].LO; s.adf_h[k] = pk[k].adf_h; s.adf_v[k] = pk[k].adf_v;
+        s.tstar[k] = pk[k].tstar; s.eflx[k] = pk[k].eflx; s.trz[k] = pk[k].trz; s.txy[k] = pk[k].txy; s.fpm[k] = pk[k].fpm;
+        s.redi_v[k] = pk[k].redi_v; s.tr_num[k] = t0 + k + 1;
+    }
+    for (int k = nt; k < MAXNT; k++) {
+        s.T[k] = s.T[0]; s.Told[k] = s.Told[0]; s.LO[k] = s.LO[0]; s.adf_h[k] = s.adf_h[0]; s.adf_v[k] = s.adf_v[0]; s.tstar[k] = s.tstar[0];
+        s.eflx[k] = s.eflx[0]; s.trz[k] = s.trz[0]; s.txy[k] = s.txy[0]; s.fpm[k] = s.fpm[0]; s.redi_v[k] = s.redi_v[0]; s.tr_num[k] = s.tr_num[0];
+    }
+    const KP& p0 = pk[0];                                       // the tracer-independent part is the same in every pk[k]
+    v2_ab2(c, s, nt, st);                                                              // init_tracers_AB, oce_tracer_mod.F90:64
+    if (v1 & PH_GRAD) EACH(KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.Told)))
+    else v2_grad_elem(c, p0, s, nt, 0, st);
+    if (multi) EACH(halo_exchange_tiled(*c.halo_elem, (double*)p.txy, c.nlp, 2, st))  // exchange_elem(tr_xy), oce_tracer_mod.F90:68,72
+    if (v1 & PH_EDGE) {
+        EACH(if (fct) KL("k_ho_edge", k_ho_edge<true><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
+             else KL("k_ho_edge", k_ho_edge<false><<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p)))
+    } else v2_edge_adv(c, p0, s, nt, fct, st);
     if (c.opt.tra_adv_hor != 2 && c.n_fb > 0) {
         const int gfb = (c.n_fb + 127) / 128;
-        if (fct) KL("k_ho_edge_fb", k_ho_edge_fb<true><<<gfb, 128, 0, st>>>(p, c.fb_list.p, c.n_fb));
-        else KL("k_ho_edge_fb", k_ho_edge_fb<false><<<gfb, 128, 0, st>>>(p, c.fb_list.p, c.n_fb));
+        EACH(if (fct) KL("k_ho_edge_fb", k_ho_edge_fb<true><<<gfb, 128, 0, st>>>(p, c.fb_list.p, c.n_fb));
+             else KL("k_ho_edge_fb", k_ho_edge_fb<false><<<gfb, 128, 0, st>>>(p, c.fb_list.p, c.n_fb)))
     }
-    const dim3 gN8(c.myNtiles, nchunk);                         // node kernels without block-wide exchange: 8 level rows per block, like the edge kernels
+    if (v1 & PH_LO) {
 #define LO_CASE(V) case V: if (fct) KL("k_lo", k_lo<V, true><<<gN8, blk8, 0, st>>>(p)); else KL("k_lo", k_lo<V, false><<<gN8, blk8, 0, st>>>(p)); break;
-    switch (c.opt.tra_adv_ver) { LO_CASE(0) LO_CASE(1) LO_CASE(2) default: LO_CASE(3) }
+        EACH(switch (c.opt.tra_adv_ver) { LO_CASE(0) LO_CASE(1) LO_CASE(2) default: LO_CASE(3) })
 #undef LO_CASE
+    } else v2_lo(c, p0, s, nt, fct, st);
     if (fct) {
-        if (c.opt.w_split) KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi));
-        if (multi) halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st);               // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
-        if (LPB == 3) KL("k_fct_bounds", k_fct_bounds<3><<<c.myNtiles, blk, 2 * smt, st>>>(p));
-        else KL("k_fct_bounds", k_fct_bounds<4><<<c.myNtiles, blk, 2 * smt, st>>>(p));
-        if (multi) halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st);     // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
+        if (c.opt.w_split) EACH(KL("k_vert_impl", k_vert_impl<<<gN64, 64, 2 * sm_64, st>>>(p, p.LO, p.Wi)))
+        if (multi) EACH(halo_exchange_tiled(*c.halo_nod, p.LO, c.nlp, 1, st))          // exchange_nod(fct_LO), oce_adv_tra_driver.F90:134
+        if (v1 & PH_BOUNDS) {
+            EACH(if (LPB == 3) KL("k_fct_bounds", k_fct_bounds<3><<<c.myNtiles, blk, 2 * smt, st>>>(p));
+                 else KL("k_fct_bounds", k_fct_bounds<4><<<c.myNtiles, blk, 2 * smt, st>>>(p)))
+        } else v2_fct_bounds(c, p0, s, nt, st);
+        if (multi) EACH(halo_exchange_tiled(*c.halo_nod, (double*)p.fpm, c.nlp, 2, st)) // exchange_nod(fct_plus, fct_minus), oce_adv_tra_fct.F90:279
     }
-    if (c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
-    if (c.opt.do_hor_diff && c.opt.Redi) KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T));
-    if (c.opt.do_hor_diff) KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p));
-    if (c.opt.Redi) {                                                                   // diff_ver_part_redi_expl, oce_ale_tracer.F90:288
-        if (!c.opt.do_hor_diff) KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T));
-        if (!c.redi_v.p) { c.redi_v.alloc(nf); p.redi_v = c.redi_v.p; }
-        KL("k_redi_expl", k_redi_expl<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.tstar, c.redi_v.p));
+    if (c.opt.do_hor_diff || c.opt.Redi) {                      // tracer_gradient_elements(tr_arr), oce_tracer_mod.F90:79
+        if (v1 & PH_GRAD) EACH(KL("k_grad_elem", k_grad_elem<<<gE, 128, 0, st>>>(p, p.T)))
+        else v2_grad_elem(c, p0, s, nt, 1, st);
     }
-    if (c.opt.i_vert_diff) {
-        if (fct) KL("k_update", k_update<true, false><<<gN8, blk8, 0, st>>>(p));
-        else KL("k_update", k_update<false, false><<<gN8, blk8, 0, st>>>(p));
-    } else {
-        if (fct) KL("k_update", k_update<true, true><<<gN8, blk8, 0, st>>>(p));
-        else KL("k_update", k_update<false, true><<<gN8, blk8, 0, st>>>(p));
+    if (c.opt.do_hor_diff && c.opt.Redi) {
+        if (v1 & PH_GRAD) EACH(KL("k_grad_z", k_grad_z<<<gNall, 128, 0, st>>>(p, p.T)))
+        else v2_grad_z(c, p0, s, nt, st);
     }
-    {   // tr_arr_old = tr_arr (:274)
+    if (c.opt.do_hor_diff) {
+        if (v1 & PH_DIFF) EACH(KL("k_diff_edge", k_diff_edge<<<dim3(c.Edtiles, nchunk), blk8, 0, st>>>(p)))
+        else v2_edge_diff(c, p0, s, nt, st);
+    }
+    if (c.opt.Redi)                                                                     // diff_ver_part_redi_expl, oce_ale_tracer.F90:288
+        EACH(KL("k_redi_expl", k_redi_expl<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.tstar, (double*)p.redi_v)))
+    if (v1 & PH_UPDATE) {
+        EACH(if (c.opt.i_vert_diff) {
+                 if (fct) KL("k_update", k_update<true, false><<<gN8, blk8, 0, st>>>(p));
+                 else KL("k_update", k_update<false, false><<<gN8, blk8, 0, st>>>(p));
+             } else {
+                 if (fct) KL("k_update", k_update<true, true><<<gN8, blk8, 0, st>>>(p));
+                 else KL("k_update", k_update<false, true><<<gN8, blk8, 0, st>>>(p));
+             })
+    } else v2_update(c, p0, s, nt, fct, !c.opt.i_vert_diff, st);
+    {   // tr_arr_old = tr_arr (:274); the fields of the group are contiguous
         ProfScope ps_("copy_told", st);
-        CUDA_CHECK(cudaMemcpyAsync(p.Told, p.T, nf * sizeof(double), cudaMemcpyDeviceToDevice, st));
+        CUDA_CHECK(cudaMemcpyAsync(pk[0].Told, pk[0].T, nf * nt * sizeof(double), cudaMemcpyDeviceToDevice, st));
     }
-    if (!c.opt.i_vert_diff) KL("k_copy_cols", k_copy_cols<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, p.tstar));      // T = T*, no implicit solve
-    else {
-        const bool wimpl = c.opt.w_split && !fct, kpp = c.opt.use_kpp_nonlclflx && c.kgT.p;
-        const dim3 gI((c.myNtiles + 1) / 2), bI(TILE, 2);
-        if (wimpl && kpp) KL("k_impl_diff", k_impl_diff<true, true><<<gI, bI, 0, st>>>(p));
-        else if (wimpl) KL("k_impl_diff", k_impl_diff<true, false><<<gI, bI, 0, st>>>(p));
-        else if (kpp) KL("k_impl_diff", k_impl_diff<false, true><<<gI, bI, 0, st>>>(p));
-        else KL("k_impl_diff", k_impl_diff<false, false><<<gI, bI, 0, st>>>(p));
+    for (int k = 0; k < nt; k++) {
+        KP& p = pk[k];
+        const int tr = t0 + k;
+        if (!c.opt.i_vert_diff) KL("k_copy_cols", k_copy_cols<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, p.tstar));      // T = T*, no implicit solve
+        else {
+            const bool wimpl = c.opt.w_split && !fct, kpp = c.opt.use_kpp_nonlclflx && c.kgT.p;
+            const dim3 gI((c.myNtiles + 1) / 2), bI(TILE, 2);
+            if (wimpl && kpp) KL("k_impl_diff", k_impl_diff<true, true><<<gI, bI, 0, st>>>(p));
+            else if (wimpl) KL("k_impl_diff", k_impl_diff<true, false><<<gI, bI, 0, st>>>(p));
+            else if (kpp) KL("k_impl_diff", k_impl_diff<false, true><<<gI, bI, 0, st>>>(p));
+            else KL("k_impl_diff", k_impl_diff<false, false><<<gI, bI, 0, st>>>(p));
+        }
+        if (c.opt.smooth_bh_tra) {                                                          // diff_part_bh, oce_ale_tracer.F90:321-323
+            if (!c.bh_tmp.p) c.bh_tmp.alloc(nf);
+            const int gB = (c.myN + 127) / 128;
+            KL("k_bh", k_bh<1><<<gB, 128, 0, st>>>(p, p.T, c.bh_tmp.p, c.opt.gamma0_tra, c.opt.gamma1_tra, c.opt.gamma2_tra));
+            if (multi) halo_exchange_tiled(*c.halo_nod, c.bh_tmp.p, c.nlp, 1, st);          // exchange_nod(temporary_ttf), :1121
+            KL("k_bh", k_bh<2><<<gB, 128, 0, st>>>(p, c.bh_tmp.p, p.T, c.opt.gamma0_tra, c.opt.gamma1_tra, c.opt.gamma2_tra));
+        }
+        if (c.opt.relax_zonal)                                                              // relax_zonal_temp: tracer 1 on every pass, oce_ale_tracer.F90:150-151
+            KL("k_relax_zonal", k_relax_zonal<<<gNall, 128, 0, st>>>(p, c.T.p, c.Tclim.p, c.zon_ztem.p, c.zon_nn.p, c.zon_a.p, c.opt.dt * c.zon_fac));
+        else if (c.opt.clim_relax > 1.0e-8 && tr < 2 && c.relax2clim.p)                     // relax_to_clim(tr_num), :152-154
+            KL("k_relax_clim", k_relax_clim<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, tr == 0 ? c.Tclim.p : c.Sclim.p, c.relax2clim.p));
+        if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
+        if (c.opt.clamp_salt && tr == 1) KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T));   // tr_arr(:,:,2) only, :176-198
     }
-    if (c.opt.smooth_bh_tra) {                                                          // diff_part_bh, oce_ale_tracer.F90:321-323
-        if (!c.bh_tmp.p) c.bh_tmp.alloc(nf);
-        const int gB = (c.myN + 127) / 128;
-        KL("k_bh", k_bh<1><<<gB, 128, 0, st>>>(p, p.T, c.bh_tmp.p, c.opt.gamma0_tra, c.opt.gamma1_tra, c.opt.gamma2_tra));
-        if (multi) halo_exchange_tiled(*c.halo_nod, c.bh_tmp.p, c.nlp, 1, st);          // exchange_nod(temporary_ttf), :1121
-        KL("k_bh", k_bh<2><<<gB, 128, 0, st>>>(p, c.bh_tmp.p, p.T, c.opt.gamma0_tra, c.opt.gamma1_tra, c.opt.gamma2_tra));
-    }
-    if (c.opt.relax_zonal)                                                              // relax_zonal_temp: tracer 1 on every pass, oce_ale_tracer.F90:150-151
-        KL("k_relax_zonal", k_relax_zonal<<<gNall, 128, 0, st>>>(p, c.T.p, c.Tclim.p, c.zon_ztem.p, c.zon_nn.p, c.zon_a.p, c.opt.dt * c.zon_fac));
-    else if (c.opt.clim_relax > 1.0e-8 && tr < 2 && c.relax2clim.p)                     // relax_to_clim(tr_num), :152-154
-        KL("k_relax_clim", k_relax_clim<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, tr == 0 ? c.Tclim.p : c.Sclim.p, c.relax2clim.p));
-    if (multi) halo_exchange_tiled(*c.halo_nod, p.T, c.nlp, 1, st);                    // exchange_nod(tr_arr), oce_ale_tracer.F90:155
-    if (c.opt.clamp_salt && tr == 1) KL("k_clamp_salt", k_clamp_salt<<<gNall, 128, 0, st>>>(p, p.T));   // tr_arr(:,:,2) only, :176-198
+#undef EACH
 #undef KL
 }
+void tracer_step_tracer(TracerCtx& c, int tr) { tracer_step_group(c, tr, 1); }
 
 void tracer_step_end(TracerCtx& c) {
     CUDA_CHECK(cudaEventRecord(c.ev1, c.stream));
@@ -1318,7 +1200,7 @@ void tracer_step_end(TracerCtx& c) {
 
 void tracer_step_all(TracerCtx& c) {
     if (!tracer_step_begin(c)) return;
-    for (int tr = 0; tr < c.ntr; tr++) tracer_step_tracer(c, tr);
+    for (int tr = 0; tr < c.ntr;) { const int nt = tracer_group_size(c, tr); tracer_step_group(c, tr, nt); tr += nt; }
     tracer_step_end(c);
 }
 
@@ -1326,14 +1208,18 @@ void tracer_step_all(TracerCtx& c) {
 const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind, int* ncomp, int* comp) {
     std::string s(name);
     *kind = 0; *ncomp = 1; *comp = 0;             // kind: 0 node field, 1 edge field, 2 element field
-    if (s == "fct_LO") return c.LO.p;
-    if (s == "adf_v") return c.adf_v.p;
-    if (s == "fct_plus") { *ncomp = 2; return (const double*)c.fpm.p; }
-    if (s == "fct_minus") { *ncomp = 2; *comp = 1; return (const double*)c.fpm.p; }
-    if (s == "tstar") return c.tstar.p;
-    if (s == "adf_h") { *kind = 1; return c.adf_h.p; }
-    if (s == "tr_xy_x") { *kind = 2; *ncomp = 2; return (const double*)c.txy.p; }
-    if (s == "tr_xy_y") { *kind = 2; *ncomp = 2; *comp = 1; return (const double*)c.txy.p; }
+    // work fields of the LAST tracer of the step: its work slot is its position in the last pass
+    size_t w = 0;
+    for (int t0 = 0; t0 < c.ntr;) { const int nt = tracer_group_size(c, t0); w = (size_t)(nt - 1); t0 += nt; }
+    const size_t nf = (size_t)c.Ntiles * c.nlp * TILE * w, ef = (size_t)c.Etiles * c.nlp * TILE * w, df = (size_t)(c.Edtiles + 1) * c.nlp * TILE * w;
+    if (s == "fct_LO") return c.LO.p + nf;
+    if (s == "adf_v") return c.adf_v.p + nf;
+    if (s == "fct_plus") { *ncomp = 2; return (const double*)(c.fpm.p + nf); }
+    if (s == "fct_minus") { *ncomp = 2; *comp = 1; return (const double*)(c.fpm.p + nf); }
+    if (s == "tstar") return c.tstar.p + nf;
+    if (s == "adf_h") { *kind = 1; return c.adf_h.p + df; }
+    if (s == "tr_xy_x") { *kind = 2; *ncomp = 2; return (const double*)(c.txy.p + ef); }
+    if (s == "tr_xy_y") { *kind = 2; *ncomp = 2; *comp = 1; return (const double*)(c.txy.p + ef); }
     if (s == "helem") { *kind = 2; return c.helem.p; }
     if (s == "hnode") return c.hnode.p;
     if (s == "hnode_new") return c.hnode_new.p;

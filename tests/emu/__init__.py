@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "fesom2_b200", "csrc")
 OUT = os.path.join(HERE, "_build")
 SO = os.path.join(OUT, "libfesom_b200_emu.so")
-SOURCES = ["tracer_kernels.cu", "context.cu", "capi.cu", "comm.cu", "ssh_solver.cu", "ssh_amg.cu"]
+SOURCES = ["tracer_kernels.cu", "tracer_kernels2.cu", "context.cu", "capi.cu", "comm.cu", "ssh_solver.cu", "ssh_amg.cu"]
 
 
 def _match_paren(s, i):

@@ -109,6 +109,14 @@ template <class T> static inline T __shfl_sync(unsigned, T v, int src) {
     emu_syncwarp();
     return r;
 }
+template <class T> static inline T __shfl_xor_sync(unsigned, T v, int mask) {
+    emu_shfl_put(&v, sizeof(T)); emu_syncwarp();
+    T r = v; emu_shfl_get(&r, sizeof(T), (emu_lane() ^ mask) & 31);
+    emu_syncwarp();
+    return r;
+}
+static inline int __ffsll(long long v) { return __builtin_ffsll(v); }
+static inline int __clzll(long long v) { return v ? __builtin_clzll((unsigned long long)v) : 64; }
 template <class T> static inline T atomicAdd(T* p, T v) { T o = *p; *p = o + v; return o; }
 template <class T> static inline T __ldg(const T* p) { return *p; }
 template <class T> static inline T __ldcg(const T* p) { return *p; }
