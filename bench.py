@@ -39,6 +39,10 @@ ALGO_BYTES = {
     "k_ab2": 24, "k_grad_elem": 40, "k_lo": 118, "k_ho_edge": 144, "k_ho_edge_fb": 3, "k_fct_bounds": 72, "k_update": 120, "k_diff_edge": 88,
     "copy_told": 16, "k_impl_diff": 48, "k_clamp_salt": 16, "k_vert_impl": 40, "k_grad_z": 24,
 }
+# launches of the column kernels that carry two tracers are profiled under "<name>_x2": twice the per-tracer fields, the
+# tracer-independent ones (volume flux inputs UV and helem, W, area, level depths, thicknesses, areasvol) once
+ALGO_BYTES.update({"k_ho_edge_x2": 2 * 144 - 48, "k_diff_edge_x2": 2 * 88 - 32, "k_lo_x2": 2 * 118 - 56, "k_grad_elem_x2": 80,
+                   "k_fct_bounds_x2": 2 * 72 - 8, "k_ab2_x2": 48, "copy_told_x2": 32, "k_update_x2": 2 * 120 - 24, "k_redi_expl": 64, "k_bh": 48})
 # SSH kernels: bytes per matrix row per launch (7-wide SELL rows: 7 x (8 B value + 4 B column) + vectors); the
 # block-Jacobi kernels also read their bs x bs inverse once per apply = bs x 8 B per row (added in algo_bytes_row)
 ALGO_BYTES_ROW = {
@@ -49,10 +53,12 @@ PC_KERNELS = ("k_r_update_pc", "k_p_update_pc", "k_pc")
 
 
 def ncu_traffic(name, units):
-    """DRAM bytes per launch of `name` at this run's size, from the committed ncu capture (profiles/r01_ncu_traffic.json:
+    """DRAM bytes per launch of `name` at this run's size, from the committed ncu capture (profiles/r02_ncu_traffic.json:
     dram__bytes_read.sum + dram__bytes_write.sum per unit at the captured size x this run's units); None if absent"""
+    name = {"k_ho_edge_x2": "k_edge_adv2", "k_diff_edge_x2": "k_edge_diff2", "k_lo_x2": "k_lo2", "k_update": "k_update2", "k_fct_bounds": "k_fct_bounds2",
+            "k_ab2": "k_ab2_g"}.get(name, name)
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))
+        t = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))
         return t[name]["dram_bytes_per_unit"] * units
     except (OSError, ValueError, KeyError):
         return None
@@ -99,8 +105,10 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--block", type=int, default=16, help="block-Jacobi block size of the SSH preconditioner (--pc bj)")
-    ap.add_argument("--e2e-ale", action="store_true", help="also time the end-to-end step with the device-side ALE producers "
-                    "(fb200_ale_step_begin/_end: only UV, Kv and the surface fluxes cross PCIe); single GPU")
+    ap.add_argument("--e2e-host-state", action="store_true", help="also time the end-to-end step in which the HOST produces Wvel, hnode_new, "
+                    "helem and the level depths every step (fb200_push_state_late) instead of the device-side ALE producers")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the partitioned-vs-undivided parity check before the timed region")
+    ap.add_argument("--cpu-steps", type=int, default=5, help="timed steps of the cpu_baseline leg")
     ap.add_argument("--pc", default="amg", choices=["amg", "bj"], help="SSH preconditioner: aggregation multigrid or block-Jacobi")
     return ap.parse_args()
 
@@ -224,6 +232,24 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from fesom2_b200 import api
 
+    # ---- N > 1: before anything is timed, this run's partitioned device path (NCCL halo exchanges, distributed psolve, the
+    # device-side ALE producers and SSH assembly with their exchanges) is compared with the UNDIVIDED oracle / host mirror on
+    # two small meshes (what tests/mp_check.py does; the driver's GPU test box has a single GPU and skips those tests)
+    parity = None
+    if world > 1 and not args.no_parity:
+        from tests import mp_check
+        parity = {"meshes": [], "ok": True}
+        for name in ("band", "pi"):
+            v = mp_check.run_check(name, dist, rank, world, ale=True)
+            allv = [None] * world
+            dist.all_gather_object(allv, v)
+            ok = all(mp_check.verdict_ok(x) for x in allv)
+            parity["ok"] = parity["ok"] and ok
+            parity["meshes"].append({"mesh": name, "ok": ok, "tracer_bitexact": all(x["own_bitexact"] and x["halo_bitexact"] for x in allv),
+                                     "ssh_rel": max(max(x["ssh_rel"], x["ssh_rel_mg"]) for x in allv), "ale": all(x["ale"] == "ok" for x in allv),
+                                     "iterations_bj": allv[0]["its"], "iterations_mg": allv[0]["its_mg"],
+                                     "detail": [x["ale"] for x in allv if x["ale"] != "ok"][:2]})
+
     # ---- workload (host side = what the Fortran driver owns).  N > 1: the SAME global mesh split into N partitions
     # (strong scaling, BASELINE.json config 5): rank 0 builds + partitions it and ships every rank its partition.
     target = args.nodes
@@ -316,74 +342,70 @@ def run_b200(args):
     api.profile(0)
     prof = api.profile_report()
 
-    # ---- e2e: host buffers through the C ABI, copies inside the timed region
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region.  The headline path keeps the ALE producers on the
+    # device (fb200_ale_step_begin/_end: compute_hbar_ale, vert_vel_ale, update_thickness_ale): per step the host sends UV
+    # (after update_vel), Kv, the surface fluxes and the SSH system, and receives tr_arr, hbar, ssh_rhs_old, dhe and d_eta.
     e2e = None
     if not args.no_e2e:
-        host_arrays = [hm.arr(nm) for nm in STATE] + [hm.arr("tr_arr"), hm.arr("tr_arr_old")]
+        host_arrays = [hm.arr(nm) for nm in STATE] + [hm.arr("tr_arr"), hm.arr("tr_arr_old"), hm.arr("hbar"), hm.arr("ssh_rhs_old"), hm.arr("dhe")]
         pinned = pin(host_arrays) + ssh_pinned
-        # what crosses PCIe every step: the state the host produces (all of STATE but the old thickness hnode, which is the
-        # resident hnode_new of the previous step, and Ki, static without Fer_GM/Redi), the SSH system and guess; back: the
-        # new tr_arr and the SSH solution.  The tracers are time-stepped on the device (fb200_solve_tracers_ale_resident).
-        h2d = sum(hm.arr(nm).nbytes for nm in STATE if nm not in ("hnode", "Ki")) + hm.arr("ssh_values").nbytes + 2 * 8 * n_own
-        d2h = hm.arr("tr_arr").nbytes + 8 * n_own
         tr_h = hm.arr("tr_arr").copy()
         pinned += pin([tr_h])
+        ksteps = max(1, min(args.steps, 5))
+        small = sum(hm.arr(nm).nbytes for nm in ("heat_flux", "water_flux", "virtual_salt", "relax_salt", "real_salt_flux"))
+
+        def timed(step_fn):
+            step_fn()
+            barrier()
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record(stream)
+            for _ in range(ksteps):
+                step_fn()
+            b_.record(stream)
+            barrier()
+            ms = a_.elapsed_time(b_) / ksteps
+            if dist is not None:                                    # max over ranks
+                t_ = torch.tensor([ms], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+                ms = float(t_[0])
+            return ms
+
+        host_state = None
+        if args.e2e_host_state:                                     # first: the device-side producers are not initialised yet
+            # the same step with the host producing Wvel, hnode_new, helem and the level depths: all of STATE but the old
+            # thickness (the resident hnode_new of the previous step) and Ki (static without Fer_GM / Redi) crosses PCIe
+            eng.push_step_state()
+            eng.push_tracers()
+
+            def host_step():
+                sol[:] = 0.0
+                eng.push_state_early(hnode_resident=True, ki_resident=True)
+                solver.solve(new_values=1, sol=sol)
+                eng.push_state_late()                               # H2D UV, Wvel, hnode_new, helem
+                eng.solve_tracers_ale_resident(tr_h)
+
+            hs_ms = timed(host_step)
+            host_state = {"ms_per_step": hs_ms, "steps": ksteps,
+                          "h2d": sum(hm.arr(nm).nbytes for nm in STATE if nm not in ("hnode", "Ki")) + hm.arr("ssh_values").nbytes + 2 * 8 * n_own,
+                          "d2h": hm.arr("tr_arr").nbytes + 8 * n_own}
+        eng.push_step_state()
         eng.push_tracers()                                          # once: initial condition
+        eng.ale_init()
 
         def e2e_step():
             sol[:] = 0.0
-            eng.push_state_early(hnode_resident=True, ki_resident=True)   # H2D level depths, mixing, fluxes: enqueued only,
-            solver.solve(new_values=1, sol=sol)                    #   overlaps psolve (H2D values, rhs, guess; D2H solution)
-            eng.push_state_late()                                   # H2D what the SSH solution yields: UV, Wvel, hnode_new, helem
-            eng.solve_tracers_ale_resident(tr_h)                    # step on the resident tracers, D2H tr_arr (copy of one tracer overlaps the kernels of the next)
+            eng.push_state_early(hnode_resident=True, ki_resident=True, depths_resident=True)    # H2D Kv + surface fluxes: enqueued only, overlaps psolve
+            solver.solve(new_values=1, sol=sol)                    # H2D values, rhs, guess; D2H solution
+            eng.ale_step_begin()                                    # H2D UV, water_flux; hbar / Wvel / hnode_new on the device; D2H hbar, ssh_rhs_old, dhe
+            eng.solve_tracers_ale_resident(tr_h)                    # step on the resident tracers, D2H tr_arr
+            eng.ale_step_end()                                      # hnode, zbar_3d_n, Z_3d_n, helem for the next step
 
-        e2e_step()
-        ksteps = max(1, min(args.steps, 5))
-        barrier()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(stream)
-        for _ in range(ksteps):
-            e2e_step()
-        b.record(stream)
-        barrier()
-        e2e_ms = a.elapsed_time(b) / ksteps
-        e2e_ale = None
-        if args.e2e_ale:
-            # the same step with compute_hbar_ale / vert_vel_ale / update_thickness_ale on the device: per step the host
-            # sends UV (after update_vel), Kv and the surface fluxes and receives tr_arr, hbar, ssh_rhs_old, dhe, d_eta
-            pinned += pin([hm.arr("hbar"), hm.arr("ssh_rhs_old"), hm.arr("dhe")])
-            eng.push_step_state()
-            eng.push_tracers()
-            eng.ale_init()
-
-            def e2e_ale_step():
-                sol[:] = 0.0
-                eng.push_state_early(hnode_resident=True, ki_resident=True, depths_resident=True)    # Kv + surface fluxes, overlaps psolve
-                solver.solve(new_values=1, sol=sol)
-                eng.ale_step_begin()                                # H2D UV, water_flux; hbar/Wvel/hnode_new on the device; D2H hbar, ssh_rhs_old, dhe
-                eng.solve_tracers_ale_resident(tr_h)
-                eng.ale_step_end()                                  # hnode, zbar_3d_n, Z_3d_n, helem for the next step
-
-            e2e_ale_step()
-            barrier()
-            a2, b2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a2.record(stream)
-            for _ in range(ksteps):
-                e2e_ale_step()
-            b2.record(stream)
-            barrier()
-            small = sum(hm.arr(nm).nbytes for nm in ("heat_flux", "water_flux", "virtual_salt", "relax_salt", "real_salt_flux"))
-            ale_ms = a2.elapsed_time(b2) / ksteps
-            if dist is not None:                                    # max over ranks (the byte counts are rank 0's, like e2e's)
-                t_ = torch.tensor([ale_ms], dtype=torch.float64, device="cuda")
-                dist.all_reduce(t_, op=dist.ReduceOp.MAX)
-                ale_ms = float(t_[0])
-            e2e_ale = {"ms_per_step": ale_ms, "steps": ksteps,
-                       "h2d": hm.arr("UV").nbytes + hm.arr("water_flux").nbytes + hm.arr("Kv").nbytes + small + hm.arr("ssh_values").nbytes + 2 * 8 * n_own,
-                       "d2h": hm.arr("tr_arr").nbytes + hm.arr("hbar").nbytes + hm.arr("ssh_rhs_old").nbytes + hm.arr("dhe").nbytes + 8 * n_own}
+        e2e_ms = timed(e2e_step)
+        h2d = hm.arr("UV").nbytes + hm.arr("water_flux").nbytes + hm.arr("Kv").nbytes + small + hm.arr("ssh_values").nbytes + 2 * 8 * n_own
+        d2h = hm.arr("tr_arr").nbytes + hm.arr("hbar").nbytes + hm.arr("ssh_rhs_old").nbytes + hm.arr("dhe").nbytes + 8 * n_own
         unpin(pinned)
         ssh_pinned = []
-        e2e = {"ms_per_step": e2e_ms, "steps": ksteps, "h2d": h2d, "d2h": d2h, "pinned_arrays": len(pinned), "ale": e2e_ale}
+        e2e = {"ms_per_step": e2e_ms, "steps": ksteps, "h2d": h2d, "d2h": d2h, "pinned_arrays": len(pinned), "host_state": host_state}
     unpin(ssh_pinned)
 
     # ---- max over ranks
@@ -401,7 +423,7 @@ def run_b200(args):
         units_all = float(units_per_step)
     return dict(rank=rank, world=world, hm=hm, info=info, reduced=reduced, units_all=units_all, tra_ms=tra_ms, ssh_ms=ssh_ms,
                 tot_ms=tot_ms, t_wall=t_wall, its=its, res=res, prof=prof, e2e=e2e, e2e_ms=e2e_ms, launches=launches,
-                clocks=sampler.result(), ntr=ntr, dist=dist, amg_levels=amg_levels)
+                clocks=sampler.result(), ntr=ntr, dist=dist, amg_levels=amg_levels, parity=parity)
 
 
 def _cpu_worker(idx, cpu_nodes, nl, steps, warmup, barrier, out):
@@ -410,6 +432,7 @@ def _cpu_worker(idx, cpu_nodes, nl, steps, warmup, barrier, out):
     same time so they share the memory system like the ranks of one node would."""
     try:
         from oracle import binding as ob
+        ob.use_timing_build(True)                  # copies compiled with the reference's own optimisation flags (fesom2_b200/build.py)
         hm, info = build_workload(cpu_nodes, nl)
         ntr = hm.ipar("num_tracers")
         o = ob.TracerOracle(hm)
@@ -449,7 +472,7 @@ def host_cores():
         return max(1, os.cpu_count() or 1)
 
 
-def cpu_reference(args, steps, warmup):
+def cpu_reference(args, steps, warmup, nodes_per_core=None):
     """The reference's CPU path on ALL host cores, on a bounded sample of the workload.  FESOM2 parallelises over MPI
     ranks only (one subdomain per core); neither MPI nor a Fortran compiler exists here, so every core runs one
     subdomain-sized sample (--cpu-nodes surface nodes) in its own process at the same time, with no halo exchange
@@ -458,11 +481,16 @@ def cpu_reference(args, steps, warmup):
     per-core throughputs."""
     import multiprocessing as mp
     cores = host_cores() if args.cpu_cores <= 0 else args.cpu_cores
-    per_gb = 3.5 * args.cpu_nodes / 120_000 * args.nl / 49                      # host memory of one sample
-    cores = max(1, min(cores, int(mem_available_gb() * 0.6 / per_gb)))
+    cpu_nodes = args.cpu_nodes if nodes_per_core is None else nodes_per_core
+    gb_per_node = 3.5 / 120_000 * args.nl / 49                                   # host memory of one sample, per surface node
+    # the samples of all cores together cover as much of the GPU arm's mesh as host memory and a few minutes of run time allow
+    cpu_nodes = int(max(20_000, min(cpu_nodes, mem_available_gb() * 0.6 / (cores * gb_per_node), 150.0 / ((steps + warmup) * 2.2e-5))))
+    from fesom2_b200 import build as _b0
+    _b0.build_oracle_timing()                                                    # once, before the workers load it
+    _b0.build_host()
     ctx = mp.get_context("spawn")                                                # the parent may hold a CUDA context
     barrier, out = ctx.Barrier(cores), ctx.Queue()
-    procs = [ctx.Process(target=_cpu_worker, args=(i, args.cpu_nodes, args.nl, steps, warmup, barrier, out)) for i in range(cores)]
+    procs = [ctx.Process(target=_cpu_worker, args=(i, cpu_nodes, args.nl, steps, warmup, barrier, out)) for i in range(cores)]
     for p_ in procs:
         p_.start()
     res = [out.get() for _ in procs]
@@ -481,7 +509,11 @@ def cpu_reference(args, steps, warmup):
              "tracer step = C restatement (oracle), SSH = %s; no halo exchange between the samples" % (
                  cores, info["nlon"], info["nlat"], args.nl, info["nod2D"], info["wet_node_layers"], ntr, steps,
                  "reference psolve.c+pARMS (oracle/_ref), 1 subdomain per process" if ref else "oracle BiCGStab")
-    return dict(value=value, unit=UNIT, cores=cores, kind="port", ssh_kind="reference" if ref else "port", sample=sample,
+    from fesom2_b200 import build as _b
+    flags = {"tracer_step": "gcc " + " ".join(_b.ORACLE_TIMING_FLAGS) + " (the reference's own: src/CMakeLists.txt:73; built on this host)",
+             "ssh": "gcc -O3 -finline-functions -march=x86-64-v3 (oracle/Makefile.ref, timing copy; built where /root/reference exists)"}
+    return dict(value=value, unit=UNIT, cores=cores, kind="port", ssh_kind="reference" if ref else "port", sample=sample, flags=flags,
+                sample_surface_nodes_total=info["nod2D"] * cores, steps_timed=steps,
                 tracer_ms_per_step=1e3 * t_tr / steps, ssh_ms_per_step=1e3 * t_ssh / steps, ssh_rows=n * cores,
                 ssh_us_per_row=1e6 * t_ssh / steps / (n * cores), per_core_value=value / cores), info
 
@@ -495,7 +527,7 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        cb, info = cpu_reference(args, max(1, args.steps), max(0, min(args.warmup, 1)))
+        cb, info = cpu_reference(args, max(1, args.steps), max(0, min(args.warmup, 1)), nodes_per_core=max(20_000, args.nodes // max(1, host_cores() if args.cpu_cores <= 0 else args.cpu_cores)))
         line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": cb["tracer_ms_per_step"] + cb["ssh_ms_per_step"], "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -540,7 +572,7 @@ def main():
         ach = bytes_launch / (avg_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": ncu_traffic(name, wet if per is not None else rows),
-                "traffic_source": "profiles/r01_ncu_traffic.json (ncu --set full at 1 M nodes, DRAM bytes per unit x units of this run)",
+                "traffic_source": "profiles/r02_ncu_traffic.json (ncu --set full at 1 M nodes, DRAM bytes per unit x units of this run)",
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                 "avg_launch_ms": avg_ms, "share_of_step": ms / sum(v[1] for v in prof.values())}
     kern = {k: {"launches": v[0], "ms": round(v[1], 4),
@@ -561,23 +593,30 @@ def main():
                     "ms_per_iteration": r["ssh_ms"] / K / max(1, r["its"])},
             "step_roofline": {"algorithmic_GB_per_tracer_step": step_bytes / 1e9, "achieved_GBps": step_bytes / (r["tra_ms"] / K * 1e-3) / 1e9,
                               "frac": step_bytes / (r["tra_ms"] / K * 1e-3) / 1e9 / peak},
+            "whole_step": {"value": r["units_all"] * K / (r["tot_ms"] * 1e-3), "unit": UNIT, "what": "the same units over psolve + tracer step: divide by the N = 1 figure x N for the parallel efficiency of the whole step"},
             "roofline": roof, "kernels": kern, "gpu_launches": int(r["launches"]), "clocks": r["clocks"],
             "wall_s_timed_region": r["t_wall"]}
     if r["e2e"]:
         line["e2e"] = {"value": r["units_all"] / (r["e2e_ms"] * 1e-3), "unit": UNIT, "ms_per_step": r["e2e_ms"],
                        "h2d_bytes_per_step": int(r["e2e"]["h2d"]), "d2h_bytes_per_step": int(r["e2e"]["d2h"]),
                        "steps": r["e2e"]["steps"], "pinned_arrays": r["e2e"]["pinned_arrays"]}
-        if r["e2e"].get("ale"):
-            ea = r["e2e"]["ale"]
-            line["e2e_device_producers"] = {"value": r["units_all"] / (ea["ms_per_step"] * 1e-3), "unit": UNIT, "ms_per_step": ea["ms_per_step"],
-                                            "h2d_bytes_per_step": int(ea["h2d"]), "d2h_bytes_per_step": int(ea["d2h"]), "steps": ea["steps"],
-                                            "what": "compute_hbar_ale, vert_vel_ale, update_thickness_ale on the device (fb200_ale_*): UV, Kv and the surface fluxes in; tr_arr, hbar, ssh_rhs_old, dhe, d_eta out"}
+        line["e2e"]["what"] = "psolve + fb200_ale_step_begin + fb200_solve_tracers_ale_resident + fb200_ale_step_end with pinned HOST arrays: UV, Kv, surface fluxes and the SSH system in; tr_arr, hbar, ssh_rhs_old, dhe, d_eta out (compute_hbar_ale, vert_vel_ale, update_thickness_ale on the device)"
+        if r["e2e"].get("host_state"):
+            ea = r["e2e"]["host_state"]
+            line["e2e_host_state"] = {"value": r["units_all"] / (ea["ms_per_step"] * 1e-3), "unit": UNIT, "ms_per_step": ea["ms_per_step"],
+                                      "h2d_bytes_per_step": int(ea["h2d"]), "d2h_bytes_per_step": int(ea["d2h"]), "steps": ea["steps"],
+                                      "what": "the host produces Wvel, hnode_new, helem and the level depths every step (fb200_push_state_late)"}
     if r["world"] == 1 and not args.no_cpu_baseline:
-        cb, _ = cpu_reference(args, 2, 0)
+        cb, _ = cpu_reference(args, max(1, args.cpu_steps), 1)
         line["cpu_baseline"] = cb
+    if r.get("parity") is not None:
+        line["parity"] = r["parity"]
     print(json.dumps(line))
     if r["dist"] is not None:
         r["dist"].destroy_process_group()
+    if r.get("parity") is not None and not r["parity"]["ok"]:
+        sys.stderr.write("bench.py: the partitioned run does NOT reproduce the undivided oracle: %s\n" % (r["parity"],))
+        sys.exit(3)
 
 
 if __name__ == "__main__":

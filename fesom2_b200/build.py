@@ -17,6 +17,9 @@ HOST_SO = os.path.join(PKG, "host", "libfesom_host.so")
 CUDA_SO = os.path.join(PKG, "csrc", "libfesom_b200.so")
 ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libpsolve_ref.so")
+REF_TIMING_SO = os.path.join(ROOT, "oracle", "_ref", "libpsolve_ref_timing.so")
+ORACLE_TIMING_SO = os.path.join(ROOT, "oracle", "liboracle_timing.so")
+ORACLE_TIMING_FLAGS = ["-O3", "-march=native", "-finline-functions"]      # the reference's own (src/CMakeLists.txt:73); FMA contraction allowed
 
 
 def _newer(target, sources):
@@ -103,8 +106,22 @@ def build_oracle(force=False):
     src = sorted(glob.glob(os.path.join(ROOT, "oracle", "*.c")))
     dep = src + glob.glob(os.path.join(ROOT, "oracle", "*.h"))
     if force or _newer(ORACLE_SO, dep):
-        _run(["gcc", "-O2", "-std=c99", "-fPIC", "-shared", "-ffp-contract=off", "-fopenmp", "-o", ORACLE_SO] + src + ["-lm"])
+        tmp = ORACLE_SO + ".%d.tmp" % os.getpid()
+        _run(["gcc", "-O2", "-std=c99", "-fPIC", "-shared", "-ffp-contract=off", "-fopenmp", "-o", tmp] + src + ["-lm"])
+        os.replace(tmp, ORACLE_SO)
     return ORACLE_SO
+
+
+def build_oracle_timing(force=False):
+    """A second copy of the oracle for bench.py's CPU arm only, compiled like the reference compiles its Fortran
+    (-O3 -march=native -finline-functions, contraction allowed).  Built on the machine that runs it (the sources travel)."""
+    src = sorted(glob.glob(os.path.join(ROOT, "oracle", "*.c")))
+    dep = src + glob.glob(os.path.join(ROOT, "oracle", "*.h"))
+    if force or _newer(ORACLE_TIMING_SO, dep):
+        tmp = ORACLE_TIMING_SO + ".%d.tmp" % os.getpid()
+        _run(["gcc"] + ORACLE_TIMING_FLAGS + ["-std=c99", "-fPIC", "-shared", "-fopenmp", "-o", tmp] + src + ["-lm"])
+        os.replace(tmp, ORACLE_TIMING_SO)                  # atomic: several processes may get here at the same time
+    return ORACLE_TIMING_SO
 
 
 def build_ref(force=False):
@@ -112,8 +129,8 @@ def build_ref(force=False):
     mk = os.path.join(ROOT, "oracle", "Makefile.ref")
     if not os.path.isdir("/root/reference/lib/parms") or not os.path.exists(mk):
         return REF_SO if os.path.exists(REF_SO) else None
-    if force or not os.path.exists(REF_SO):
-        _run(["make", "-s", "-f", mk, "-j8"], cwd=os.path.join(ROOT, "oracle"))
+    if force or not os.path.exists(REF_SO) or not os.path.exists(REF_TIMING_SO):
+        _run(["make", "-s", "-f", mk, "-j8", "_ref/libpsolve_ref.so", "_ref/libpsolve_ref_timing.so"], cwd=os.path.join(ROOT, "oracle"))
     return REF_SO
 
 

@@ -671,6 +671,7 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
         if (z + 2 <= nzmax) { n_kv = AT(p.Kv, b, z + 2); n_ar = AT(p.area, b, z + 2); }
         const double znp = zb2 + hp / 2.0;                                   // Z_n(z+1)
         const double h = h0;
+        const double rasv = 1.0 / asv;                                       // every division by areasvol(z) below: exact-division sequence div_by
         double a, bb, cc, zinv2 = 0.0;
         if (z == nzmin) {
             zinv2 = 1.0 / (zn0 - znp);
@@ -681,12 +682,12 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
             }
             Ty1 = Ty1 * isredi;
             a = 0.0;
-            cc = -(kv1 + Ty1) * zinv2 * zinv * ar1 / asv;
+            cc = div_by(-(kv1 + Ty1) * zinv2 * zinv * ar1, asv, rasv);
             bb = -cc + h;
             if (WIMPL) {
-                double v_adv = zinv * (AT(p.area, b, z) / asv);
+                double v_adv = zinv * div_by(AT(p.area, b, z), asv, rasv);
                 bb = bb + AT(p.Wi, b, z) * v_adv;
-                v_adv = zinv * ar1 / asv;
+                v_adv = div_by(zinv * ar1, asv, rasv);
                 const double wi1 = AT(p.Wi, b, z + 1);
                 bb = bb - omin(0.0, wi1) * v_adv;
                 cc = cc - omax(0.0, wi1) * v_adv;
@@ -700,15 +701,15 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
                 Ty1 = (zn0 - zb1) * zinv2 * (s0 * s0) * AT(p.Ki, b, z) + (zb1 - znp) * zinv2 * (s1 * s1) * AT(p.Ki, b, z + 1);
             }
             Ty = Ty * isredi; Ty1 = Ty1 * isredi;
-            a = -(kv0 + Ty) * zinv1 * zinv * (ar0 / asv);
-            cc = -(kv1 + Ty1) * zinv2 * zinv * ar1 / asv;
+            a = -(kv0 + Ty) * zinv1 * zinv * div_by(ar0, asv, rasv);
+            cc = div_by(-(kv1 + Ty1) * zinv2 * zinv * ar1, asv, rasv);
             bb = -a - cc + h;
             if (WIMPL) {
-                double v_adv = zinv * (ar0 / asv);
+                double v_adv = zinv * div_by(ar0, asv, rasv);
                 const double wi0 = AT(p.Wi, b, z), wi1 = AT(p.Wi, b, z + 1);
                 a = a + omin(0.0, wi0) * v_adv;
                 bb = bb + omax(0.0, wi0) * v_adv;
-                v_adv = zinv * ar1 / asv;
+                v_adv = div_by(zinv * ar1, asv, rasv);
                 bb = bb - omin(0.0, wi1) * v_adv;
                 cc = cc - omax(0.0, wi1) * v_adv;
             }
@@ -719,11 +720,11 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
                 Ty = (znm - zb0) * zinv1 * (sm1 * sm1) * AT(p.Ki, b, z - 1) + (zb0 - zn0) * zinv1 * (s0 * s0) * AT(p.Ki, b, z);
             }
             Ty = Ty * isredi;
-            a = -(kv0 + Ty) * zinv1 * zinv * (ar0 / asv);
+            a = -(kv0 + Ty) * zinv1 * zinv * div_by(ar0, asv, rasv);
             cc = 0.0;
             bb = -a + h;
             if (WIMPL) {
-                const double v_adv = zinv * (ar0 / asv);
+                const double v_adv = zinv * div_by(ar0, asv, rasv);
                 const double wi0 = AT(p.Wi, b, z);
                 a = a + omin(0.0, wi0) * v_adv;
                 bb = bb + omax(0.0, wi0) * v_adv;
@@ -739,9 +740,9 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
             const double m0 = z > nzmin ? omin(AT(G, b, z) * AT(B, b, z), 1.0) : 0.0;
             const double m1 = z <= nzmax - 2 ? omin(AT(G, b, z + 1) * AT(B, b, z + 1), 1.0) : 0.0;
             double x;
-            if (z == nzmin) x = -m1 * (ar1 / asv);
-            else if (z <= nzmax - 2) x = m0 * (ar0 / asv) - m1 * (ar1 / asv);
-            else x = m0 * (ar0 / asv);
+            if (z == nzmin) x = -m1 * div_by(ar1, asv, rasv);
+            else if (z <= nzmax - 2) x = m0 * div_by(ar0, asv, rasv) - m1 * div_by(ar1, asv, rasv);
+            else x = m0 * div_by(ar0, asv, rasv);
             if (p.tr_num == 1) tr = tr + x * p.heat_flux[n] / vcpw * dt;
             else {
                 const double rsss = p.ref_sss_local ? AT(TS, b, 1) : p.ref_sss;     // tr_arr(1,n,2), :691
@@ -749,7 +750,7 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
             }
         }
         if (p.use_sw_pene && p.tr_num == 1)
-            tr = tr + (AT(p.sw3d, b, z) - AT(p.sw3d, b, z + 1) * ar1 / asv) * zinv;
+            tr = tr + (AT(p.sw3d, b, z) - div_by(AT(p.sw3d, b, z + 1) * ar1, asv, rasv)) * zinv;
         if (z == nzmin) {
             double bc = 0.0;
             if (p.tracer_id == 0) {
@@ -758,10 +759,11 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
             } else if (p.tracer_id == 1)
                 bc = dt * (p.virtual_salt[n] + p.relax_salt[n] - p.real_salt_flux[n] * p.is_nonlinfs);
             tr = tr + bc;
-            cpm = cc / bb; tpm = tr / bb;                                    // Thomas :828-829
+            const double rbb = 1.0 / bb;
+            cpm = div_by(cc, bb, rbb); tpm = div_by(tr, bb, rbb);            // Thomas :828-829
         } else {
-            const double m = bb - cpm * a;                                   // :831-835
-            cpm = cc / m; tpm = (tr - tpm * a) / m;
+            const double m = bb - cpm * a, rm = 1.0 / m;                     // :831-835
+            cpm = div_by(cc, m, rm); tpm = div_by(tr - tpm * a, m, rm);
         }
         cps[(z - 1) * TILE] = cpm;
         AT(To, b, z) = tpm;
@@ -1158,7 +1160,7 @@ void tracer_step_group(TracerCtx& c, int t0, int nt) {
              })
     } else v2_update(c, p0, s, nt, fct, !c.opt.i_vert_diff, st);
     {   // tr_arr_old = tr_arr (:274); the fields of the group are contiguous
-        ProfScope ps_("copy_told", st);
+        ProfScope ps_(nt == 2 ? "copy_told_x2" : "copy_told", st);
         CUDA_CHECK(cudaMemcpyAsync(pk[0].Told, pk[0].T, nf * nt * sizeof(double), cudaMemcpyDeviceToDevice, st));
     }
     for (int k = 0; k < nt; k++) {
@@ -1233,7 +1235,9 @@ const double* tracer_debug_field(TracerCtx& c, const char* name, int* kind, int*
 
 // ---------------------------------------------------------------------------------------------------
 // self-test of div_by against IEEE division on pseudo-random operand pairs spanning the magnitudes of the tracer
-// path (fluxes 1e-30..1e12, areas 1e4..1e12) plus exact-quotient and tiny/zero numerators
+// path — even samples: fluxes 1e-30..1e12 over areas 1e4..1e12; odd samples: tracer differences / thickness sums
+// 1e-18..1e12 over layer thicknesses, level-depth differences and matrix pivots 1e-6..1e12; every 7th sample divides by the
+// constants 3 and 6 of the reconstruction formulas — plus exact-quotient and tiny/zero numerators
 __global__ void k_selftest_div(long long n, unsigned long long* mismatches) {
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -1244,8 +1248,10 @@ __global__ void k_selftest_div(long long n, unsigned long long* mismatches) {
         unsigned long long g = h * 0x94D049BB133111EBull; g ^= g >> 31;
         const double mx = 1.0 + (double)(h & 0xFFFFFFFFFFFFFull) * 2.220446049250313e-16;      // [1,2)
         const double mb = 1.0 + (double)(g & 0xFFFFFFFFFFFFFull) * 2.220446049250313e-16;
-        const int ex = (int)((h >> 52) % 140) - 100, eb = (int)((g >> 52) % 28) + 12;
+        int ex = (int)((h >> 52) % 140) - 100, eb = (int)((g >> 52) % 28) + 12;
+        if (i & 1) { ex = (int)((h >> 52) % 100) - 60; eb = (int)((g >> 52) % 61) - 20; }
         double x = ldexp(mx, ex), b = ldexp(mb, eb);
+        if (i % 7 == 3) b = (i & 8) ? 3.0 : 6.0;
         if ((i & 15) == 0) x = b * (double)(int)(h >> 58);          // exact quotients
         if ((i & 1023) == 1) x = 0.0;
         if (g >> 63) x = -x;

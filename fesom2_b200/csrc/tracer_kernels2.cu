@@ -28,6 +28,9 @@
 // compiler barrier between the load block and the arithmetic of a level: keeps the loads together at the top (without it
 // the compiler may sink each gather down to its first use to save registers, which serialises the round trips again)
 #define LOADS_DONE() asm volatile("" ::: "memory")
+// correctly rounded reciprocals of the constants the reconstruction formulas divide by (see div_by in tracer_dev.cuh)
+#define R3 (1.0 / 3.0)
+#define R6 (1.0 / 6.0)
 // minimum resident blocks per SM of the node kernels (register budget = 65536 / (128 * MB)); -D overrides for A/B builds
 #ifndef LO_MB
 #define LO_MB 3
@@ -187,12 +190,14 @@ __global__ void __launch_bounds__(128, EDGE_MB) k_edge_adv2(KP p, TrSet s) {
             if (p.hor == 2) fho = upw1_flux(a1[t], a2[t], vflux);
             else {
                 const double g1 = gu[t].x, g2 = gd[t].x, g3 = gu[t].y, g4 = gd[t].y;             // edge_up_dn_grad(1:4)
-                double Tmean2 = a2[t] - (2.0 * (a2[t] - a1[t]) + h.dxa * g2 + h.dyr * g4) / 6.0;
-                double Tmean1 = a1[t] + (2.0 * (a2[t] - a1[t]) + h.dxa * g1 + h.dyr * g3) / 6.0;
+                // x / 6.0 as the exact-division sequence with the constant's reciprocal (div_by, tracer_dev.cuh)
+                const double e2 = div_by(2.0 * (a2[t] - a1[t]) + h.dxa * g2 + h.dyr * g4, 6.0, R6), e1 = div_by(2.0 * (a2[t] - a1[t]) + h.dxa * g1 + h.dyr * g3, 6.0, R6);
+                double Tmean2 = a2[t] - e2;
+                double Tmean1 = a1[t] + e1;
                 if (p.hor == 0) {                                                                // MUSCL: c_lo, oce_adv_tra_hor.F90:352-353
                     const double c_lo1 = (nbl1 - nz) >= 0 ? 1.0 : 0.0, c_lo2 = (nbl2 - nz) >= 0 ? 1.0 : 0.0;
-                    Tmean2 = a2[t] - (2.0 * (a2[t] - a1[t]) + h.dxa * g2 + h.dyr * g4) / 6.0 * c_lo2;
-                    Tmean1 = a1[t] + (2.0 * (a2[t] - a1[t]) + h.dxa * g1 + h.dyr * g3) / 6.0 * c_lo1;
+                    Tmean2 = a2[t] - e2 * c_lo2;
+                    Tmean1 = a1[t] + e1 * c_lo1;
                 }
                 const double cHO = (vflux + fabs(vflux)) * Tmean1 + (vflux - fabs(vflux)) * Tmean2;
                 fho = -0.5 * (1.0 - p.ph) * cHO - vflux * p.ph * (0.5 * (Tmean1 + Tmean2));
@@ -305,17 +310,21 @@ __device__ __forceinline__ double ver_upw1_w(double t0, double tm1, double w, do
     if (nz == nzmin) return -w * t0 * ar;
     return -0.5 * (t0 * (w + fabs(w)) + tm1 * (w - fabs(w))) * ar;
 }
-// value form of adv_tra_ver_qr4c at interface nz (oce_adv_tra_ver.F90:314-356)
-__device__ __forceinline__ double ver_qr4c_w(double t0, double tm1, double tm2, double tp1, double z0, double zm1, double zm2, double zp1,
+// value form of adv_tra_ver_qr4c at interface nz (oce_adv_tra_ver.F90:314-356).  The three slopes divide by the level-depth
+// differences dzc = Z(nz-1) - Z(nz), dzu = Z(nz) - Z(nz+1), dzd = Z(nz-2) - Z(nz-1), which do not depend on the tracer and
+// recur from level to level: the caller keeps (difference, reciprocal) pairs in a window — one true division per level — and
+// the quotients are formed by the exact-division sequence div_by (tracer_dev.cuh), like the two divisions by 3.
+__device__ __forceinline__ double ver_qr4c_w(double t0, double tm1, double tm2, double tp1, double z0, double zm1,
+                                             double dzc, double rdzc, double dzu, double rdzu, double dzd, double rdzd,
                                              double zb, double w, double ar, double pv, int nz, int nzmin, int nzmax) {
     if (nz == nzmax) return 0.0;
     if (nz == nzmin) return -t0 * w * ar;
     if (nz == nzmin + 1 || nz == nzmax - 1) return -0.5 * (tm1 + t0) * w * ar;
-    const double qc = (tm1 - t0) / (zm1 - z0);
-    const double qu = (t0 - tp1) / (z0 - zp1);
-    const double qd = (tm2 - tm1) / (zm2 - zm1);
-    const double Tmean1 = t0 + (2 * qc + qu) * (zb - z0) / 3.0;
-    const double Tmean2 = tm1 + (2 * qc + qd) * (zb - zm1) / 3.0;
+    const double qc = div_by(tm1 - t0, dzc, rdzc);
+    const double qu = div_by(t0 - tp1, dzu, rdzu);
+    const double qd = div_by(tm2 - tm1, dzd, rdzd);
+    const double Tmean1 = t0 + div_by((2 * qc + qu) * (zb - z0), 3.0, R3);
+    const double Tmean2 = tm1 + div_by((2 * qc + qd) * (zb - zm1), 3.0, R3);
     const double Tmean = (w + fabs(w)) * Tmean1 + (w - fabs(w)) * Tmean2;
     return (-0.5 * (1.0 - pv) * Tmean - pv * (0.5 * (Tmean1 + Tmean2)) * w) * ar;
 }
@@ -351,6 +360,10 @@ __global__ void __launch_bounds__(32 * WPB, LO_MB) k_lo2(KP p, TrSet s) {
         const int zz = min(nzmin + k, nlp);
         wlo[k] = AT(Wlo, b, zz); wad[k] = AT(Wad, b, zz); who[k] = AT(Who, b, zz); ar[k] = AT(p.area, b, zz);
     }
+    // level-depth differences of the QR4C slopes and their reciprocals: index 0 = Z(z-2)-Z(z-1), 1 = Z(z-1)-Z(z), 2 = Z(z)-Z(z+1)
+    double dzw[3], rdzw[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) { dzw[k] = zw[k] - zw[k + 1]; rdzw[k] = 1.0 / dzw[k]; }
     double fv_z[NT];                                               // upwind flux (Wlo) through interface z, left by the iteration above
 #pragma unroll
     for (int t = 0; t < NT; t++) fv_z[t] = 0.0;
@@ -369,8 +382,10 @@ __global__ void __launch_bounds__(32 * WPB, LO_MB) k_lo2(KP p, TrSet s) {
         double acc[NT];
 #pragma unroll
         for (int t = 0; t < NT; t++) acc[t] = 0.0;
+        double rhnn = 1.0, rasv = 1.0;
         if (FCT) {
             hn = AT(p.hnode, b, z); hnn = AT(p.hnode_new, b, z); asv = AT(p.areasvol, b, z);
+            rhnn = 1.0 / hnn; rasv = 1.0 / asv;                    // shared by the tracers of the pass
             for (int j0 = 0; j0 < ndeg; j0 += SB) {
                 SlotBatch sb;
                 sb.setup(rec, j0, z, b);
@@ -393,12 +408,13 @@ __global__ void __launch_bounds__(32 * WPB, LO_MB) k_lo2(KP p, TrSet s) {
             if (FCT) {
                 const double fv = have_fv ? fv_z[t] : ver_upw1_w(t0, tm1, wlo[0], ar[0], z, nzmin, nzmax);
                 const double fvn = ver_upw1_w(tp1, t0, wlo[1], ar[1], z + 1, nzmin, nzmax);
-                AT(s.LO[t], b, z) = (t0 * hn + (acc[t] + (fv - fvn)) * p.dt / asv) / hnn;
+                AT(s.LO[t], b, z) = div_by(t0 * hn + div_by((acc[t] + (fv - fvn)) * p.dt, asv, rasv), hnn, rhnn);
                 fv_z[t] = fvn;
             }
             const double flo = FCT ? ver_upw1_w(t0, tm1, wad[0], ar[0], z, nzmin, nzmax) : 0.0;
             double ho;
-            if (VER == 0) ho = ver_qr4c_w(aw[t][2], aw[t][1], aw[t][0], aw[t][3], zw[2], zw[1], zw[0], zw[3], zb, who[0], ar[0], p.pv, z, nzmin, nzmax);
+            if (VER == 0) ho = ver_qr4c_w(aw[t][2], aw[t][1], aw[t][0], aw[t][3], zw[2], zw[1], dzw[1], rdzw[1], dzw[2], rdzw[2], dzw[0], rdzw[0],
+                                          zb, who[0], ar[0], p.pv, z, nzmin, nzmax);
             else if (VER == 1) ho = ver_cdiff(p, s.Told[t], Who, b, z, nzmin);
             else if (VER == 2) ho = ver_ppm(p, s.Told[t], Who, b, z, nzmin, nzmax);
             else ho = ver_upw1_w(aw[t][2], aw[t][1], who[0], ar[0], z, nzmin, nzmax);
@@ -407,6 +423,8 @@ __global__ void __launch_bounds__(32 * WPB, LO_MB) k_lo2(KP p, TrSet s) {
             aw[t][0] = aw[t][1]; aw[t][1] = aw[t][2]; aw[t][2] = aw[t][3]; aw[t][3] = n_a[t];
         }
         zw[0] = zw[1]; zw[1] = zw[2]; zw[2] = zw[3]; zw[3] = n_z3;
+        dzw[0] = dzw[1]; dzw[1] = dzw[2]; dzw[2] = zw[2] - zw[3];
+        rdzw[0] = rdzw[1]; rdzw[1] = rdzw[2]; rdzw[2] = VER == 0 ? 1.0 / dzw[2] : 0.0;
         wlo[0] = wlo[1]; wlo[1] = n_wlo; wad[0] = wad[1]; wad[1] = n_wad; who[0] = who[1]; who[1] = n_who; ar[0] = ar[1]; ar[1] = n_ar;
         have_fv = true;
     }
@@ -707,32 +725,32 @@ void v2_ab2(TracerCtx& c, const TrSet& s, int nt, cudaStream_t st) {
     const size_t nf = (size_t)c.Ntiles * c.nlp * TILE;
     const double ca = -(0.5 + c.opt.epsilon), cb = 1.5 + c.opt.epsilon;
     // the fields of a group are contiguous (tracer-major) in c.T / c.Told
-    KL("k_ab2", k_ab2_g<<<148 * 8, 256, 0, st>>>(s.Told[0], s.T[0], nf * nt, ca, cb));
+    KL(nt == 2 ? "k_ab2_x2" : "k_ab2", k_ab2_g<<<148 * 8, 256, 0, st>>>(s.Told[0], s.T[0], nf * nt, ca, cb));
 }
 void v2_grad_elem(TracerCtx& c, const KP& p, const TrSet& s, int nt, int which, cudaStream_t st) {
     static const int pnt = phase_nt("GRAD", 2);
     if (nt == 2 && pnt == 1) { v2_grad_elem(c, p, one_of(s, 0), 1, which, st); v2_grad_elem(c, p, one_of(s, 1), 1, which, st); return; }
     const int g = (c.myE + 127) / 128;
-    if (nt == 2) KL("k_grad_elem", k_grad_elem2<2><<<g, 128, 0, st>>>(p, s, which));
+    if (nt == 2) KL("k_grad_elem_x2", k_grad_elem2<2><<<g, 128, 0, st>>>(p, s, which));
     else KL("k_grad_elem", k_grad_elem2<1><<<g, 128, 0, st>>>(p, s, which));
 }
 void v2_grad_z(TracerCtx& c, const KP& p, const TrSet& s, int nt, cudaStream_t st) {
     const int g = (c.N + 127) / 128;
-    if (nt == 2) KL("k_grad_z", k_grad_z2<2><<<g, 128, 0, st>>>(p, s));
+    if (nt == 2) KL("k_grad_z_x2", k_grad_z2<2><<<g, 128, 0, st>>>(p, s));
     else KL("k_grad_z", k_grad_z2<1><<<g, 128, 0, st>>>(p, s));
 }
 void v2_edge_adv(TracerCtx& c, const KP& p, const TrSet& s, int nt, bool fct, cudaStream_t st) {
     static const int pnt = phase_nt("EDGE", 2);
     if (nt == 2 && pnt == 1) { v2_edge_adv(c, p, one_of(s, 0), 1, fct, st); v2_edge_adv(c, p, one_of(s, 1), 1, fct, st); return; }
     const int g = (c.myEd + 127) / 128;
-    if (nt == 2) { if (fct) KL("k_ho_edge", k_edge_adv2<2, true><<<g, 128, 0, st>>>(p, s)); else KL("k_ho_edge", k_edge_adv2<2, false><<<g, 128, 0, st>>>(p, s)); }
+    if (nt == 2) { if (fct) KL("k_ho_edge_x2", k_edge_adv2<2, true><<<g, 128, 0, st>>>(p, s)); else KL("k_ho_edge_x2", k_edge_adv2<2, false><<<g, 128, 0, st>>>(p, s)); }
     else { if (fct) KL("k_ho_edge", k_edge_adv2<1, true><<<g, 128, 0, st>>>(p, s)); else KL("k_ho_edge", k_edge_adv2<1, false><<<g, 128, 0, st>>>(p, s)); }
 }
 void v2_edge_diff(TracerCtx& c, const KP& p, const TrSet& s, int nt, cudaStream_t st) {
     static const int pnt = phase_nt("DIFF", 2);
     if (nt == 2 && pnt == 1) { v2_edge_diff(c, p, one_of(s, 0), 1, st); v2_edge_diff(c, p, one_of(s, 1), 1, st); return; }
     const int g = (c.myEd + 127) / 128;
-    if (nt == 2) KL("k_diff_edge", k_edge_diff2<2><<<g, 128, 0, st>>>(p, s));
+    if (nt == 2) KL("k_diff_edge_x2", k_edge_diff2<2><<<g, 128, 0, st>>>(p, s));
     else KL("k_diff_edge", k_edge_diff2<1><<<g, 128, 0, st>>>(p, s));
 }
 void v2_lo(TracerCtx& c, const KP& p, const TrSet& s, int nt, bool fct, cudaStream_t st) {
@@ -741,7 +759,7 @@ void v2_lo(TracerCtx& c, const KP& p, const TrSet& s, int nt, bool fct, cudaStre
     set_attrs2();
     const int g = col_grid(c);
     const size_t sm = fct ? slot_smem(c) : 0;
-#define LO2(NT, V) do { if (fct) KL("k_lo", k_lo2<NT, V, true><<<g, 32 * WPB, sm, st>>>(p, s)); else KL("k_lo", k_lo2<NT, V, false><<<g, 32 * WPB, sm, st>>>(p, s)); } while (0)
+#define LO2(NT, V) do { if (fct) KL(NT == 2 ? "k_lo_x2" : "k_lo", k_lo2<NT, V, true><<<g, 32 * WPB, sm, st>>>(p, s)); else KL(NT == 2 ? "k_lo_x2" : "k_lo", k_lo2<NT, V, false><<<g, 32 * WPB, sm, st>>>(p, s)); } while (0)
 #define LO2V(NT) switch (c.opt.tra_adv_ver) { case 0: LO2(NT, 0); break; case 1: LO2(NT, 1); break; case 2: LO2(NT, 2); break; default: LO2(NT, 3); }
     if (nt == 2) { LO2V(2) } else { LO2V(1) }
 #undef LO2V
@@ -751,7 +769,7 @@ void v2_fct_bounds(TracerCtx& c, const KP& p, const TrSet& s, int nt, cudaStream
     static const int pnt = phase_nt("BOUNDS", 1);
     if (nt == 2 && pnt == 1) { v2_fct_bounds(c, p, one_of(s, 0), 1, st); v2_fct_bounds(c, p, one_of(s, 1), 1, st); return; }
     set_attrs2();
-    if (nt == 2) KL("k_fct_bounds", k_fct_bounds2<2><<<col_grid(c), 32 * WPB, slot_smem(c), st>>>(p, s));
+    if (nt == 2) KL("k_fct_bounds_x2", k_fct_bounds2<2><<<col_grid(c), 32 * WPB, slot_smem(c), st>>>(p, s));
     else KL("k_fct_bounds", k_fct_bounds2<1><<<col_grid(c), 32 * WPB, slot_smem(c), st>>>(p, s));
 }
 void v2_update(TracerCtx& c, const KP& p, const TrSet& s, int nt, bool fct, bool expl, cudaStream_t st) {
@@ -761,10 +779,10 @@ void v2_update(TracerCtx& c, const KP& p, const TrSet& s, int nt, bool fct, bool
     const int g = col_grid(c);
     const size_t sm = slot_smem(c);
 #define UP2(NT) do { \
-        if (fct && !expl) KL("k_update", k_update2<NT, true, false><<<g, 32 * WPB, sm, st>>>(p, s)); \
-        else if (fct) KL("k_update", k_update2<NT, true, true><<<g, 32 * WPB, sm, st>>>(p, s)); \
-        else if (!expl) KL("k_update", k_update2<NT, false, false><<<g, 32 * WPB, sm, st>>>(p, s)); \
-        else KL("k_update", k_update2<NT, false, true><<<g, 32 * WPB, sm, st>>>(p, s)); } while (0)
+        if (fct && !expl) KL(NT == 2 ? "k_update_x2" : "k_update", k_update2<NT, true, false><<<g, 32 * WPB, sm, st>>>(p, s)); \
+        else if (fct) KL(NT == 2 ? "k_update_x2" : "k_update", k_update2<NT, true, true><<<g, 32 * WPB, sm, st>>>(p, s)); \
+        else if (!expl) KL(NT == 2 ? "k_update_x2" : "k_update", k_update2<NT, false, false><<<g, 32 * WPB, sm, st>>>(p, s)); \
+        else KL(NT == 2 ? "k_update_x2" : "k_update", k_update2<NT, false, true><<<g, 32 * WPB, sm, st>>>(p, s)); } while (0)
     if (nt == 2) UP2(2); else UP2(1);
 #undef UP2
 }

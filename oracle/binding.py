@@ -25,11 +25,23 @@ STATE_DBL = ["UV", "Wvel", "Wvel_e", "Wvel_i", "hnode", "hnode_new", "helem", "Z
 DIMS = ["nl", "myDim_nod2D", "eDim_nod2D", "myDim_elem2D", "eDim_elem2D", "eXDim_elem2D", "myDim_edge2D"]
 
 
+_timing = False
+
+
+def use_timing_build(on=True):
+    """bench.py's CPU arm only: load the copies compiled with the reference's own flags (liboracle_timing.so built on this
+    machine with -O3 -march=native -finline-functions; oracle/_ref/libpsolve_ref_timing.so) instead of the parity
+    checkers (-O2 -ffp-contract=off).  Call before the first lib() / ref_lib()."""
+    global _timing
+    assert _lib is None and _ref is None
+    _timing = bool(on)
+
+
 def lib():
     global _lib
     if _lib is None:
         from fesom2_b200 import build
-        L = C.CDLL(build.build_oracle())
+        L = C.CDLL(build.build_oracle_timing() if _timing else build.build_oracle())
         L.oracle_create.restype = C.c_void_p
         L.oracle_free.argtypes = [C.c_void_p]
         L.oracle_set_int.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
@@ -190,6 +202,8 @@ def ref_lib():
     if _ref is None:
         from fesom2_b200 import build
         so = build.build_ref()
+        if _timing and so is not None and os.path.exists(build.REF_TIMING_SO):
+            so = build.REF_TIMING_SO
         if so is None or not os.path.exists(so):
             return None
         R = C.CDLL(so)

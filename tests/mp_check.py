@@ -90,23 +90,13 @@ def check_device_ale(name, rank, world, part_in):
     return "ok" if not bad else repr(bad)
 
 
-def main():
-    import torch
-    import torch.distributed as dist
+def run_check(name, dist, rank, world, ale=False, emulate=False, steps=2):
+    """one mesh: this rank's partition through the C ABI (NCCL halo exchange / all-reduce) against the oracle on the undivided
+    mesh.  Returns this rank's verdict dict; the caller gathers them.  `dist` is an initialised torch.distributed (any backend):
+    it only carries the NCCL id."""
     from fesom2_b200 import api, partition as P
     from oracle import binding as ob
     from tests import util
-    names = [a for a in sys.argv[1:] if not a.startswith("--")]
-    name = names[0] if names else "pi"
-    steps = 2
-    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-    emulate = "--emulate" in sys.argv                         # CPU: the kernels' source through tests/emu, NCCL over files
-    if emulate:
-        from tests import emu
-        api._lib = emu.load()
-    else:
-        torch.cuda.set_device(local)
-    dist.init_process_group("gloo")                           # only used to broadcast the NCCL id and gather verdicts
     hm = util.build_model(name)
     hm.compute_ssh_rhs()
     if name == "pi" and world == 2:
@@ -127,7 +117,7 @@ def main():
         eng.solve()
     eng.pull_tracers(tr, tro)
     eng.close()
-    ale = check_device_ale(name, rank, world, part_fixed) if "--ale" in sys.argv else "ok"
+    ale_v = check_device_ale(name, rank, world, part_fixed) if ale else "ok"
     # oracle on the undivided mesh
     o = ob.TracerOracle(hm)
     for _ in range(steps):
@@ -139,7 +129,7 @@ def main():
     s = api.SSHSolver(lm, pc="bj")
     s.solve(new_values=1, sol=sol)
     its, res = s.info()
-    # the same solve with the multigrid preconditioner (each rank: V-cycle on its own diagonal block)
+    # the same solve with the multigrid preconditioner
     sol_mg = np.zeros_like(lm["d_eta"])
     s2 = api.SSHSolver(lm, ident=2, pc="amg", amg=(0.08, 0.8, 4, 50))
     s2.solve(new_values=1, sol=sol_mg)
@@ -152,18 +142,39 @@ def main():
     err_t = float(np.abs(tr[:, :r.myDim_nod2D] - hm["tr_arr"][:, own]).max())
     err_s = float(util.rel_err(sol[:r.myDim_nod2D], x_ref[own]))
     err_mg = float(util.rel_err(sol_mg[:r.myDim_nod2D], x_ref[own]))
-    verdict = dict(rank=rank, own_bitexact=ok_own, halo_bitexact=ok_halo, tracer_maxabs=err_t, ssh_rel=err_s, its=its, its_ref=its_ref,
-                   res=res, ssh_rel_mg=err_mg, its_mg=its_mg, res_mg=res_mg, ale=ale, launches=int(api.lib().fb200_kernel_launches()))
-    allv = [None] * world
-    dist.all_gather_object(allv, verdict)
+    verdict = dict(rank=rank, mesh=name, own_bitexact=ok_own, halo_bitexact=ok_halo, tracer_maxabs=err_t, ssh_rel=err_s, its=its, its_ref=its_ref,
+                   res=res, ssh_rel_mg=err_mg, its_mg=its_mg, res_mg=res_mg, ale=ale_v, launches=int(api.lib().fb200_kernel_launches()))
     api.lib().psolver_final()
     api.comm_finalize()
+    return verdict
+
+
+def verdict_ok(v):
+    return bool(v["own_bitexact"] and v["halo_bitexact"] and v["ssh_rel"] < 1e-6 and v["res"] < 1e-10
+                and v["ssh_rel_mg"] < 1e-6 and v["res_mg"] < 1e-10 and v["ale"] == "ok")
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from fesom2_b200 import api
+    names = [a for a in sys.argv[1:] if not a.startswith("--")]
+    name = names[0] if names else "pi"
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    emulate = "--emulate" in sys.argv                         # CPU: the kernels' source through tests/emu, NCCL over files
+    if emulate:
+        from tests import emu
+        api._lib = emu.load()
+    else:
+        torch.cuda.set_device(local)
+    dist.init_process_group("gloo")                           # only used to broadcast the NCCL id and gather verdicts
+    verdict = run_check(name, dist, rank, world, ale="--ale" in sys.argv, emulate=emulate)
+    allv = [None] * world
+    dist.all_gather_object(allv, verdict)
     if rank == 0:
         for v in allv:
             print("MPCHECK", v)
-        good = all(v["own_bitexact"] and v["halo_bitexact"] and v["ssh_rel"] < 1e-6 and v["res"] < 1e-10
-                   and v["ssh_rel_mg"] < 1e-6 and v["res_mg"] < 1e-10 and v["ale"] == "ok" for v in allv)
-        print("MPCHECK_RESULT", "PASS" if good else "FAIL")
+        print("MPCHECK_RESULT", "PASS" if all(verdict_ok(v) for v in allv) else "FAIL")
     dist.destroy_process_group()
 
 
