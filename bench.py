@@ -107,6 +107,8 @@ def parse():
     ap.add_argument("--block", type=int, default=16, help="block-Jacobi block size of the SSH preconditioner (--pc bj)")
     ap.add_argument("--e2e-host-state", action="store_true", help="also time the end-to-end step in which the HOST produces Wvel, hnode_new, "
                     "helem and the level depths every step (fb200_push_state_late) instead of the device-side ALE producers")
+    ap.add_argument("--partition", default="metis", choices=["metis", "strips"], help="N > 1: the reference's own partitioner (src/fort_part.c + "
+                    "METIS 5.1.0, oracle/_ref/libmetis_part.so) or contiguous strips of the node numbering")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the partitioned-vs-undivided parity check before the timed region")
     ap.add_argument("--cpu-steps", type=int, default=5, help="timed steps of the cpu_baseline leg")
     ap.add_argument("--pc", default="amg", choices=["amg", "bj"], help="SSH preconditioner: aggregation multigrid or block-Jacobi")
@@ -271,8 +273,17 @@ def run_b200(args):
         dist.broadcast_object_list(box, src=0, group=gloo)
         info = dict(box[0])
         part = None
+        part_kind = [args.partition]
         if rank == 0:
-            part = P.contiguous_partition(ghm, world)
+            if args.partition == "metis" and P.metis_lib() is not None:
+                tp = time.time()
+                part = P.metis_partition(ghm, world)
+                part_kind = ["METIS 5.1.0 through the reference's fort_part.c (weighted by 2D + 3D node counts, check_partitioning applied), %.0f s" % (time.time() - tp)]
+            else:
+                part = P.contiguous_partition(ghm, world)
+                part_kind = ["contiguous strips of the node numbering" + ("" if args.partition == "strips" else " (oracle/_ref/libmetis_part.so not built)")]
+        dist.broadcast_object_list(part_kind, src=0, group=gloo)
+        info["partition"] = part_kind[0]
         hm = P.scatter_local_models(ghm, part, dist, group=gloo)
         del ghm
         own = hm.ipar("myDim_nod2D")
@@ -584,7 +595,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload, "mesh": {k: info[k] for k in ("nlon", "nlat", "nl", "nod2D", "elem2D", "edge2D", "wet_node_layers", "nod2D_global", "halo_nodes") if k in info},
                        "mesh_is": "global mesh" if r["world"] == 1 else "partition of rank 0", "reduced_for_host_memory": r["reduced"], "l2": "inputs larger than L2 (per-field >> 126 MB)",
-                       "parallelism": "1 domain per GPU" if r["world"] == 1 else "the same global mesh in %d node partitions (contiguous split of the numbering, gen_comm.F90 halo rules), NCCL halo exchange + all-reduce" % r["world"],
+                       "parallelism": "1 domain per GPU" if r["world"] == 1 else "the same global mesh in %d node partitions (%s; gen_comm.F90 halo rules), NCCL halo exchange, peer-memory or NCCL reductions" % (r["world"], info.get("partition", "?")),
                        "ssh_initial_guess": "zero every step", "setup_s": info["setup_s"],
                        "ssh_preconditioner": ("aggregation multigrid V(1,1), levels (rows, A, P, R entries) = %s" % (r["amg_levels"],)) if args.pc == "amg"
                        else "block-Jacobi, %d rows per block" % args.block},

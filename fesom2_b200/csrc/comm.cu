@@ -2,6 +2,7 @@
 #include "comm.cuh"
 #include "fesom_b200.h"
 #include <cstring>
+#include <cstdlib>
 
 static ncclComm_t g_comm = nullptr;
 static int g_nranks = 1, g_rank = 0;
@@ -85,6 +86,79 @@ void halo_exchange_flat(HaloPlan& h, double* x, cudaStream_t st) {
 void comm_allreduce_sum(double* dev_inout, int count, cudaStream_t st) {
     if (g_nranks <= 1 || !fb_ok()) return;
     NCCL_CHECK(ncclAllReduce(dev_inout, dev_inout, count, ncclDouble, ncclSum, g_comm, st));
+}
+
+// ---- peer memory -------------------------------------------------------------------------------------
+bool peer_enabled() {
+#ifdef FB200_EMULATION
+    return false;
+#else
+    if (g_nranks <= 1) return false;
+    const char* e = getenv("FB200_SSH_COMM");
+    return !(e && !strcmp(e, "nccl"));
+#endif
+}
+void peer_release(PeerBuf& b) {
+#ifndef FB200_EMULATION
+    for (size_t r = 0; r < b.peer.size(); r++) if (b.peer[r] && (int)r != g_rank) cudaIpcCloseMemHandle(b.peer[r]);
+#endif
+    if (b.owned && b.local) cudaFree(b.local);
+    b.peer.clear(); b.d_peer.release(); b.local = nullptr; b.bytes = 0; b.owned = false;
+}
+bool peer_publish(PeerBuf& b, void* base, size_t bytes, cudaStream_t st) {
+#ifdef FB200_EMULATION
+    (void)b; (void)base; (void)bytes; (void)st;
+    return false;
+#else
+    peer_release(b);
+    if (!peer_enabled() || !g_comm || !fb_ok()) return false;
+    b.bytes = bytes;
+    if (base) { b.local = base; b.owned = false; }
+    else {
+        if (cudaMalloc(&b.local, bytes) != cudaSuccess) { cudaGetLastError(); b.local = nullptr; return false; }
+        b.owned = true;
+        CUDA_CHECK(cudaMemsetAsync(b.local, 0, bytes, st));
+    }
+    cudaIpcMemHandle_t mine;
+    int ok = cudaIpcGetMemHandle(&mine, b.local) == cudaSuccess ? 1 : 0;
+    if (!ok) cudaGetLastError();
+    // all-gather (ok flag + handle) so that every rank takes the same decision
+    const size_t rec = sizeof(cudaIpcMemHandle_t) + 8;
+    std::vector<char> hsend(rec, 0), hall(rec * g_nranks, 0);
+    memcpy(hsend.data(), &ok, sizeof(int)); memcpy(hsend.data() + 8, &mine, sizeof(mine));
+    DevBuf<char> d_s, d_a;
+    d_s.upload(hsend); d_a.alloc(rec * g_nranks);
+    NCCL_CHECK(ncclAllGather(d_s.p, d_a.p, rec, ncclChar, g_comm, st));
+    CUDA_CHECK(cudaMemcpyAsync(hall.data(), d_a.p, hall.size(), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    d_s.release(); d_a.release();
+    bool all_ok = fb_ok();
+    for (int r = 0; r < g_nranks; r++) { int f = 0; memcpy(&f, hall.data() + rec * r, sizeof(int)); all_ok = all_ok && f == 1; }
+    b.peer.assign(g_nranks, nullptr);
+    if (all_ok) {
+        for (int r = 0; r < g_nranks; r++) {
+            if (r == g_rank) { b.peer[r] = b.local; continue; }
+            cudaIpcMemHandle_t h;
+            memcpy(&h, hall.data() + rec * r + 8, sizeof(h));
+            if (cudaIpcOpenMemHandle(&b.peer[r], h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); b.peer[r] = nullptr; all_ok = false; }
+        }
+    }
+    // a second agreement round: opening can fail on one rank only
+    {
+        int mine_ok = all_ok ? 1 : 0;
+        DevBuf<int> d_f, d_g;
+        std::vector<int> f1(1, mine_ok), fall(g_nranks, 0);
+        d_f.upload(f1); d_g.alloc(g_nranks);
+        NCCL_CHECK(ncclAllGather(d_f.p, d_g.p, 1, ncclInt32, g_comm, st));
+        CUDA_CHECK(cudaMemcpyAsync(fall.data(), d_g.p, fall.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        d_f.release(); d_g.release();
+        for (int v : fall) all_ok = all_ok && v == 1;
+    }
+    if (!all_ok) { peer_release(b); return false; }
+    b.d_peer.upload(b.peer);
+    return fb_ok();
+#endif
 }
 
 extern "C" void ssh_drop_graphs();

@@ -28,4 +28,22 @@ void halo_exchange_tiled(HaloPlan& h, double* field, int nlp, int ncomp, cudaStr
 // flat vector (one value per entity): x[rlist] <- owner's x[slist]
 void halo_exchange_flat(HaloPlan& h, double* x, cudaStream_t st);
 void comm_allreduce_sum(double* dev_inout, int count, cudaStream_t st);
+
+// ---- peer memory over NVLink (one NVSwitch node is the whole machine: every GPU can load/store every other GPU's HBM).
+// A PeerBuf is one cudaMalloc'd buffer per rank whose CUDA IPC handles were all-gathered, so peer[r] is rank r's buffer
+// mapped into this process (peer[me] = local).  The SSH solver uses it for its latency-bound traffic: the 16-byte
+// all-reduces and the interface values of the SpMV are written straight into the peers' memory by the producing kernel
+// and consumed after a sequence flag arrives — no NCCL call, no extra launch (ssh_solver.cu).  NCCL remains the
+// transport of the bulk exchanges and the alternative path (FB200_SSH_COMM=nccl).
+struct PeerBuf {
+    void* local = nullptr; size_t bytes = 0; bool owned = false;
+    std::vector<void*> peer;                    // [nranks]
+    DevBuf<void*> d_peer;                       // the same table on the device
+};
+// collective over all ranks (NCCL all-gather of the handles on stream st).  base == nullptr: allocate (zeroed) `bytes`;
+// else publish an existing cudaMalloc'd allocation (base must be the allocation's base address).  false = CUDA IPC is not
+// available here (then the caller stays on NCCL).
+bool peer_publish(PeerBuf& b, void* base, size_t bytes, cudaStream_t st);
+void peer_release(PeerBuf& b);
+bool peer_enabled();                            // more than one rank, not switched off by FB200_SSH_COMM=nccl, not the CPU emulation
 #define NCCL_CHECK(x) do { ncclResult_t r_ = (x); if (r_ != ncclSuccess) fb_set_error(300 + (int)r_, std::string(#x) + ": " + ncclGetErrorString(r_)); } while (0)

@@ -1,5 +1,6 @@
 // Aggregation multigrid preconditioner of the SSH solve: host setup + device V-cycle.  See ssh_amg.cuh.
 #include "ssh_amg.cuh"
+#include <cstdlib>
 #include "fesom_b200.h"
 #include <algorithm>
 #include <cmath>
@@ -231,6 +232,7 @@ void Amg::release() {
         D.dinv.release(); D.b.release(); D.x.release(); D.x2.release(); D.r.release();
     }
     L.clear();
+    bar.release();
 }
 
 #define ABS 256
@@ -268,18 +270,97 @@ __global__ void __launch_bounds__(ABS) k_amg_post(int n, const int* __restrict__
     if (i < n) out[i] = x[i] + omega * dinv[i] * (b[i] - sell_row(sptr, scol, sval, x, i));
 }
 
+// ---- levels 1 .. K-1 of the V-cycle in ONE launch.  On a partition of a few hundred thousand rows the coarse levels hold
+// 10^5, 10^4, 10^3 rows: each of their kernels runs for a few microseconds and the cycle is bound by launch latency (8 coarse
+// launches per cycle with four levels, two cycles per BiCGStab iteration).  Here one resident grid (at most one block per SM)
+// walks down and up the coarse levels with a grid-wide barrier between the steps.  Same kernels' arithmetic, row by row.
+struct AmgLvDesc {
+    int n;
+    const int *Asp, *Asc, *Psp, *Psc, *Rsp, *Rsc;
+    const double *Asv, *Psv, *Rsv, *dinv;
+    double *b, *x, *x2, *r;
+};
+#define AMG_MAX_LEVELS 8
+struct AmgFusedArgs { AmgLvDesc lv[AMG_MAX_LEVELS]; int K; double omega; unsigned* bar; };
+// sense-reversing grid barrier: bar[0] = arrivals, bar[1] = generation.  All blocks of the launch are resident (grid <= SMs).
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned nblocks) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned g = *(volatile unsigned*)(bar + 1);
+        if (atomicAdd(bar, 1u) == nblocks - 1) { *(volatile unsigned*)bar = 0u; __threadfence(); atomicAdd(bar + 1, 1u); }
+        else while (*(volatile unsigned*)(bar + 1) == g) { }
+        __threadfence();
+    }
+    __syncthreads();
+}
+__global__ void __launch_bounds__(ABS) k_amg_coarse_fused(AmgFusedArgs a, const int* done) {
+    if (*done) return;
+    const int K = a.K, stride = gridDim.x * ABS, t0 = blockIdx.x * ABS + threadIdx.x;
+    for (int l = 1; l + 1 < K; l++) {
+        const AmgLvDesc& F = a.lv[l];
+        const AmgLvDesc& C = a.lv[l + 1];
+        for (int i = t0; i < F.n; i += stride) F.r[i] = F.b[i] - sell_row(F.Asp, F.Asc, F.Asv, F.x, i);          // k_amg_resid
+        grid_barrier(a.bar, gridDim.x);
+        for (int i = t0; i < C.n; i += stride) {                                                                  // k_amg_restrict
+            const double v = sell_row(F.Rsp, F.Rsc, F.Rsv, F.r, i);
+            C.b[i] = v; C.x[i] = a.omega * C.dinv[i] * v;
+        }
+        grid_barrier(a.bar, gridDim.x);
+    }
+    const double* cur = a.lv[K - 1].x;
+    for (int l = K - 2; l >= 1; l--) {
+        const AmgLvDesc& F = a.lv[l];
+        for (int i = t0; i < F.n; i += stride) F.x[i] += sell_row(F.Psp, F.Psc, F.Psv, cur, i);                   // k_amg_prolong
+        grid_barrier(a.bar, gridDim.x);
+        for (int i = t0; i < F.n; i += stride)                                                                    // k_amg_post
+            F.x2[i] = F.x[i] + a.omega * F.dinv[i] * (F.b[i] - sell_row(F.Asp, F.Asc, F.Asv, F.x, i));
+        if (l > 1) grid_barrier(a.bar, gridDim.x);
+        cur = F.x2;
+    }
+}
+
+static bool amg_fused_on() {
+#ifdef FB200_EMULATION
+    return false;                                   // the emulation runs the blocks of a launch one after another: no grid barrier
+#else
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("FB200_AMG_FUSED"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on == 1;
+#endif
+}
+
 void Amg::cycle(double* out, const int* done, cudaStream_t st) {
     const int K = (int)L.size();
     if (K <= 1) return;                                           // single level: the caller's Jacobi step already wrote `out`
 #define AKL(name0, namec, lev, ...) do { ProfScope ps_((lev) == 0 ? name0 : namec, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
+    const bool fused = K >= 3 && K <= AMG_MAX_LEVELS && amg_fused_on();
+    if (fused && !bar.p) bar.alloc(2);
     for (int l = 0; l + 1 < K; l++) {
+        if (fused && l >= 1) break;
         AmgDevLevel& F = L[l];
         AmgDevLevel& C = L[l + 1];
         AKL("k_amg_resid0", "k_amg_coarse", l, k_amg_resid<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.r.p, done));
         AKL("k_amg_restrict0", "k_amg_coarse", l, k_amg_restrict<<<(C.n + ABS - 1) / ABS, ABS, 0, st>>>(C.n, F.R.sptr.p, F.R.scol.p, F.R.sval.p, F.r.p, C.dinv.p, omega, C.b.p, C.x.p, done));
     }
-    const double* cur = L[K - 1].x.p;
-    for (int l = K - 2; l >= 0; l--) {
+    if (fused) {
+        AmgFusedArgs a;
+        a.K = K; a.omega = omega; a.bar = bar.p;
+        for (int l = 0; l < K; l++) {
+            AmgDevLevel& D = L[l];
+            AmgLvDesc& d = a.lv[l];
+            d.n = D.n; d.Asp = D.A.sptr.p; d.Asc = D.A.scol.p; d.Asv = D.A.sval.p; d.Psp = D.P.sptr.p; d.Psc = D.P.scol.p; d.Psv = D.P.sval.p;
+            d.Rsp = D.R.sptr.p; d.Rsc = D.R.scol.p; d.Rsv = D.R.sval.p; d.dinv = D.dinv.p; d.b = D.b.p; d.x = D.x.p; d.x2 = D.x2.p; d.r = D.r.p;
+        }
+        int sms = 148;
+        { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+        const int grid = std::max(1, std::min(sms, (L[1].n + ABS - 1) / ABS));      // every block resident: the barrier needs it
+        ProfScope ps_("k_amg_coarse_fused", st);
+        k_amg_coarse_fused<<<grid, ABS, 0, st>>>(a, done);
+        LAUNCH_CHECK();
+    }
+    const double* cur = fused ? L[1].x2.p : L[K - 1].x.p;
+    for (int l = fused ? 0 : K - 2; l >= 0; l--) {
         AmgDevLevel& F = L[l];
         double* dst = l == 0 ? out : F.x2.p;
         AKL("k_amg_prolong0", "k_amg_coarse", l, k_amg_prolong<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.P.sptr.p, F.P.scol.p, F.P.sval.p, cur, F.x.p, done));

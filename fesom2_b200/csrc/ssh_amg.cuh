@@ -47,6 +47,7 @@ struct AmgDevLevel {
 };
 struct Amg {
     std::vector<AmgDevLevel> L;
+    DevBuf<unsigned> bar;            // grid barrier of the fused coarse-level kernel
     double omega = 0.8;
     bool ready() const { return !L.empty(); }
     int levels() const { return (int)L.size(); }

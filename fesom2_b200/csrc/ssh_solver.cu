@@ -17,6 +17,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstddef>
 #include <cstring>
 #include <map>
 
@@ -25,8 +26,43 @@
 struct SolverScal {             // device-resident scalars
     double alpha, sigma, beta, rho, rho_alt, omega, tol2;
     double tmp0, tmp1;
-    int done, its, maxits, pad;
+    int done, its, maxits, comm_error;
+    unsigned long long red_seq, halo_seq[3];       // peer-memory transport: sequence numbers of the reductions / of the pushes of x, pt, st
 };
+
+// Peer-memory transport of the solver's small messages (comm.cuh: PeerBuf).  Every rank owns one control buffer
+//   RedSlot slots[4][nranks]      reduction k: rank r writes its two partial sums + k into slot [k & 3][r] of EVERY rank; a rank
+//                                 that finds all nranks sequence numbers equal to k adds the partials in rank order, so all ranks
+//                                 form bitwise the same sums and take the same decisions.  Slot k & 3 is reused by reduction
+//                                 k + 4, which a rank can only reach after every peer has contributed to k + 1 .. k + 3, i.e.
+//                                 after every peer has finished reading reduction k.
+//   u64     flags[3][nranks]      interface values: k_flat_push writes this rank's send list straight into the tails of the
+//                                 peers' vectors (x, pt or st), then its sequence number into flags[vec][me] of each peer; the
+//                                 consuming SpMV waits for the flags of its source ranks.  The reductions between two pushes
+//                                 of the same vector order the next push after the peers' reads (see psolve).
+struct RedSlot { double a, b; unsigned long long seq, pad; };
+struct PeerCtl {                // by value into the kernels.  mode 0: one rank; 1: NCCL all-reduce + k_apply_scalars; 2: peer memory
+    int mode, nranks, me, nsrc;
+    RedSlot* const* slots;      // [nranks] rank r's slot array
+    unsigned long long* const* flags;   // [nranks] rank r's flag array
+    const int* src;             // [nsrc] ranks this rank receives interface values from
+};
+#define SPIN_LIMIT_CYCLES 4000000000ll          // ~2 s: a peer that never arrives raises comm_error instead of hanging the GPU
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) { return *(const volatile unsigned long long*)p; }
+__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) { *(volatile unsigned long long*)p = v; }
+// block-level wait for the interface values of vector `vec` (0 x, 1 pt, 2 st): call at the top of the consuming kernel
+__device__ __forceinline__ void wait_halo(const PeerCtl& pc, SolverScal* sc, int vec) {
+    if (pc.mode != 2) return;
+    if (threadIdx.x == 0) {
+        const unsigned long long want = sc->halo_seq[vec];
+        const unsigned long long* f = pc.flags[pc.me] + (size_t)vec * pc.nranks;
+        const long long t0 = clock64();
+        for (int k = 0; k < pc.nsrc; k++)
+            while (ld_volatile_u64(f + pc.src[k]) < want) if (clock64() - t0 > SPIN_LIMIT_CYCLES) { sc->comm_error = 1; break; }
+        __threadfence_system();
+    }
+    __syncthreads();
+}
 
 struct Solver {
     int n = 0, nloc = 0, nnz = 0, nslice = 0, bs = 1, nblk = 0, reuse = 0, maxits = 2000;   // nloc = own rows + halo columns
@@ -49,6 +85,13 @@ struct Solver {
     cudaStream_t graph_stream = nullptr; int graph_multi = -1, graph_launches = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // transport of the reductions and interface values on several ranks: 1 = NCCL, 2 = peer memory (see PeerCtl)
+    int comm_mode = 0;
+    PeerBuf ctl, pv[3];                      // control buffer; the published vectors x, pt, st
+    DevBuf<RedSlot*> d_slots; DevBuf<unsigned long long*> d_flags;
+    DevBuf<int> s_peer, s_dst, dst_ranks, src_ranks;
+    DevBuf<unsigned> push_counter;
+    PeerCtl pctl;
 };
 static std::map<int, Solver*> g_solvers;
 #define FB200_DEFAULT_PC 1      // multigrid; block-Jacobi through fb200_psolver_set_pc(0) or FB200_SSH_PC=bj
@@ -79,8 +122,9 @@ __global__ void __launch_bounds__(SBS) k_scale_rows(int n, const int* __restrict
 
 // deterministic two-value reduction: block partials -> the last block to finish sums them in a fixed order with all
 // its threads (plain L2 loads after the fence; no floating-point atomics) and calls `fin`
-template <class Fin>
-__device__ __forceinline__ void reduce2(double a, double b, double* __restrict__ partial, unsigned* __restrict__ counter, int nblocks, Fin fin) {
+__device__ __forceinline__ void apply_scalars(SolverScal* sc, int which);
+__device__ __forceinline__ void reduce2(double a, double b, double* __restrict__ partial, unsigned* __restrict__ counter, int nblocks,
+                                        SolverScal* sc, int which, const PeerCtl& pc) {
     __shared__ double sa[SBS / 32], sb[SBS / 32];
     __shared__ bool last;
     for (int o = 16; o > 0; o >>= 1) { a += __shfl_down_sync(0xffffffffu, a, o); b += __shfl_down_sync(0xffffffffu, b, o); }
@@ -108,7 +152,34 @@ __device__ __forceinline__ void reduce2(double a, double b, double* __restrict__
         ta = 0.0; tb = 0.0;
         for (int w = 0; w < SBS / 32; w++) { ta += sa[w]; tb += sb[w]; }
         *counter = 0;
-        fin(ta, tb);
+        sa[0] = ta; sb[0] = tb;                              // this rank's sums
+    }
+    if (pc.mode != 2) {
+        if (threadIdx.x == 0) { sc->tmp0 = sa[0]; sc->tmp1 = sb[0]; if (pc.mode == 0) apply_scalars(sc, which); }
+        return;
+    }
+    // peer-memory all-reduce: thread r delivers this rank's sums to rank r, thread 0 collects
+    __shared__ unsigned long long sseq;
+    if (threadIdx.x == 0) { sseq = sc->red_seq + 1; sc->red_seq = sseq; }
+    __syncthreads();
+    const unsigned long long seq = sseq;
+    if (threadIdx.x < pc.nranks) {
+        RedSlot* dst = pc.slots[threadIdx.x] + (size_t)(seq & 3) * pc.nranks + pc.me;
+        *(volatile double*)&dst->a = sa[0]; *(volatile double*)&dst->b = sb[0];
+        __threadfence_system();
+        st_volatile_u64(&dst->seq, seq);
+    }
+    if (threadIdx.x == 0) {
+        const RedSlot* mine = pc.slots[pc.me] + (size_t)(seq & 3) * pc.nranks;
+        const long long t0 = clock64();
+        double ga = 0.0, gb = 0.0;
+        for (int r = 0; r < pc.nranks; r++) {
+            while (ld_volatile_u64(&mine[r].seq) != seq) if (clock64() - t0 > SPIN_LIMIT_CYCLES) { sc->comm_error = 1; break; }
+            __threadfence_system();
+            ga += *(const volatile double*)&mine[r].a; gb += *(const volatile double*)&mine[r].b;
+        }
+        sc->tmp0 = ga; sc->tmp1 = gb;
+        apply_scalars(sc, which);
     }
 }
 
@@ -131,7 +202,6 @@ __device__ __forceinline__ void apply_scalars(SolverScal* sc, int which) {
     }
 }
 __global__ void k_apply_scalars(SolverScal* sc, int which) { if (which == SC_INIT || !sc->done) apply_scalars(sc, which); }
-#define FIN(which) [=](double ta, double tb) { sc->tmp0 = ta; sc->tmp1 = tb; if (!multi) apply_scalars(sc, which); }
 
 // block-Jacobi apply for one row: z_i = sum_c Binv[blk][c][i_loc] * in[b0 + c]   (bs == 1: z = dinv * in)
 __device__ __forceinline__ double bj_row(const double* __restrict__ binv, const double* in, int i, int n, int bs) {
@@ -147,7 +217,8 @@ __device__ __forceinline__ double bj_row(const double* __restrict__ binv, const 
 __global__ void __launch_bounds__(SBS) k_init_res(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                   const double* __restrict__ rhs, const double* __restrict__ scale, const double* __restrict__ x,
                                                   double* __restrict__ y, double* __restrict__ r, double* __restrict__ p,
-                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
+                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc) {
+    wait_halo(pc, sc, 0);                                // interface values of the initial guess
     double a = 0.0, b = 0.0;
     for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) {
         const double yi = rhs[i] * scale[i];
@@ -155,7 +226,7 @@ __global__ void __launch_bounds__(SBS) k_init_res(int n, const int* __restrict__
         y[i] = yi; r[i] = ri; p[i] = ri;
         a += ri * ri; b += yi * ri;
     }
-    reduce2(a, b, partial, counter, nblocks, FIN(SC_INIT));
+    reduce2(a, b, partial, counter, nblocks, sc, SC_INIT, pc);
 }
 __global__ void __launch_bounds__(SBS) k_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ in, double* __restrict__ out,
                                             const SolverScal* sc) {
@@ -166,11 +237,12 @@ __global__ void __launch_bounds__(SBS) k_pc(int n, int bs, const double* __restr
 // v = A pt ; alpha = rho / (r0 . v)                                        bicgstab_ras.c:161-164
 __global__ void __launch_bounds__(SBS) k_spmv_alpha(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                     const double* __restrict__ pt, const double* __restrict__ r0, double* __restrict__ v,
-                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
+                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc) {
     if (sc->done) return;
+    wait_halo(pc, sc, 1);
     double a = 0.0;
     for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) { const double vi = sell_row(sptr, scol, sval, pt, i); v[i] = vi; a += r0[i] * vi; }
-    reduce2(a, 0.0, partial, counter, nblocks, FIN(SC_ALPHA));
+    reduce2(a, 0.0, partial, counter, nblocks, sc, SC_ALPHA, pc);
 }
 // r -= alpha v ; st = M r                                                   bicgstab_ras.c:166-175
 __global__ void __launch_bounds__(SBS) k_r_update_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ v,
@@ -186,16 +258,17 @@ __global__ void __launch_bounds__(SBS) k_r_update_pc(int n, int bs, const double
 // t = A st ; sigma = (t.r)/(t.t)                                            bicgstab_ras.c:179-197
 __global__ void __launch_bounds__(SBS) k_spmv_sigma(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                     const double* __restrict__ st, const double* __restrict__ r, double* __restrict__ t,
-                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
+                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc) {
     if (sc->done) return;
+    wait_halo(pc, sc, 2);
     double a = 0.0, b = 0.0;
     for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) { const double ti = sell_row(sptr, scol, sval, st, i); t[i] = ti; a += ti * r[i]; b += ti * ti; }
-    reduce2(a, b, partial, counter, nblocks, FIN(SC_SIGMA));
+    reduce2(a, b, partial, counter, nblocks, sc, SC_SIGMA, pc);
 }
 // r -= sigma t ; x += alpha pt + sigma st ; omega = r.r ; rho = r0.r ; convergence test ; beta     :200-225
 __global__ void __launch_bounds__(SBS) k_x_update(int n, const double* __restrict__ t, const double* __restrict__ pt, const double* __restrict__ st,
                                                   const double* __restrict__ r0, double* __restrict__ r, double* __restrict__ x,
-                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc, int multi) {
+                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc) {
     if (sc->done) return;
     const double alpha = sc->alpha, sigma = sc->sigma;
     double a = 0.0, b = 0.0;
@@ -205,7 +278,27 @@ __global__ void __launch_bounds__(SBS) k_x_update(int n, const double* __restric
         x[i] += alpha * pt[i] + sigma * st[i];
         a += ri * ri; b += r0[i] * ri;
     }
-    reduce2(a, b, partial, counter, nblocks, FIN(SC_XUPD));
+    reduce2(a, b, partial, counter, nblocks, sc, SC_XUPD, pc);
+}
+// interface values of vector `vec` (0 x, 1 pt, 2 st) written straight into the peers' copies of that vector (their tails hold
+// the off-partition columns), then the new sequence number into the peers' flag arrays.  check_done: skipped once converged.
+__global__ void __launch_bounds__(SBS) k_flat_push(int count, const int* __restrict__ slist, const int* __restrict__ s_peer, const int* __restrict__ s_dst,
+                                                   const double* __restrict__ x, double* const* __restrict__ peer_vec, int ndst, const int* __restrict__ dst_ranks,
+                                                   unsigned* counter, SolverScal* sc, PeerCtl pc, int vec, int check_done) {
+    if (check_done && sc->done) return;
+    const int i = blockIdx.x * SBS + threadIdx.x;
+    if (i < count) peer_vec[s_peer[i]][s_dst[i]] = x[slist[i]];
+    __threadfence_system();
+    __shared__ bool last;
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __shared__ unsigned long long sseq;
+    if (threadIdx.x == 0) { *counter = 0; sseq = sc->halo_seq[vec] + 1; sc->halo_seq[vec] = sseq; }
+    __syncthreads();
+    __threadfence_system();
+    if ((int)threadIdx.x < ndst) st_volatile_u64(pc.flags[dst_ranks[threadIdx.x]] + (size_t)vec * pc.nranks + pc.me, sseq);
 }
 // p = r + beta (p - sigma v) ; pt = M p                                     bicgstab_ras.c:227-230, 150-156
 __global__ void __launch_bounds__(SBS) k_p_update_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ r, const double* __restrict__ v,
@@ -377,6 +470,50 @@ static bool setup_halo(Solver& S, const int* part, const std::vector<int>& gcols
     return fb_ok();
 }
 
+// peer-memory transport: publish the control buffer and the three exchanged vectors, learn where in the peers' vectors this
+// rank's interface values go.  Collective; on any failure every rank stays on NCCL (comm_mode 1).
+static void setup_peer(Solver& S) {
+    const int np = comm_nranks(), me = comm_rank();
+    cudaStream_t st = S.stream;
+    S.pctl.mode = 1; S.pctl.nranks = np; S.pctl.me = me; S.pctl.nsrc = 0; S.pctl.slots = nullptr; S.pctl.flags = nullptr; S.pctl.src = nullptr;
+    S.comm_mode = 1;
+    if (!peer_enabled()) return;
+    const size_t slot_bytes = sizeof(RedSlot) * 4 * np, bytes = slot_bytes + sizeof(unsigned long long) * 3 * np;
+    if (!peer_publish(S.ctl, nullptr, bytes, st)) return;
+    DevBuf<double>* vecs[3] = {&S.x, &S.pt, &S.st};
+    for (int v = 0; v < 3; v++) if (!peer_publish(S.pv[v], vecs[v]->p, vecs[v]->n * sizeof(double), st)) return;
+    // the receiver tells each of its sources where its values go: index n + roff[k] of the receiver's vectors
+    const HaloPlan& H = S.halo;
+    std::vector<int> tell(H.nrp), got(H.nsp, -1);
+    for (int k = 0; k < H.nrp; k++) tell[k] = S.n + H.roff[k];
+    DevBuf<int> d_tell, d_got;
+    d_tell.upload(tell); d_got.alloc(std::max(1, H.nsp));
+    NCCL_CHECK(ncclGroupStart());
+    for (int k = 0; k < H.nsp; k++) NCCL_CHECK(ncclRecv(d_got.p + k, 1, ncclInt32, H.sPE[k], comm_handle(), st));
+    for (int k = 0; k < H.nrp; k++) NCCL_CHECK(ncclSend(d_tell.p + k, 1, ncclInt32, H.rPE[k], comm_handle(), st));
+    NCCL_CHECK(ncclGroupEnd());
+    if (H.nsp) CUDA_CHECK(cudaMemcpyAsync(got.data(), d_got.p, H.nsp * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    d_tell.release(); d_got.release();
+    if (!fb_ok()) return;
+    std::vector<int> sp(std::max(1, H.nsend()), 0), sd(std::max(1, H.nsend()), 0);
+    for (int k = 0; k < H.nsp; k++)
+        for (int i = H.soff[k]; i < H.soff[k + 1]; i++) { sp[i] = H.sPE[k]; sd[i] = got[k] + (i - H.soff[k]); }
+    S.s_peer.upload(sp); S.s_dst.upload(sd);
+    std::vector<int> dr(H.sPE), sr(H.rPE);
+    if (dr.empty()) dr.push_back(0);
+    if (sr.empty()) sr.push_back(0);
+    S.dst_ranks.upload(dr); S.src_ranks.upload(sr);
+    std::vector<RedSlot*> sl(np); std::vector<unsigned long long*> fl(np);
+    for (int r = 0; r < np; r++) { sl[r] = (RedSlot*)S.ctl.peer[r]; fl[r] = (unsigned long long*)((char*)S.ctl.peer[r] + slot_bytes); }
+    S.d_slots.upload(sl); S.d_flags.upload(fl);
+    S.push_counter.alloc(1);
+    if (H.nsp > SBS) { fb_set_error(49, "psolver: more neighbour partitions than the push kernel signals (256)"); return; }
+    if (!fb_ok()) return;
+    S.pctl.mode = 2; S.pctl.nsrc = H.nrp; S.pctl.slots = S.d_slots.p; S.pctl.flags = S.d_flags.p; S.pctl.src = S.src_ranks.p;
+    S.comm_mode = 2;
+}
+
 void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* ilulevel, int* fillin, double* droptol, int* maxits,
                   int* restart, double* soltol, int* part, int* rptr, int* cols, double* vals, int* reuse, int* fcomm) {
     (void)stype; (void)pctype; (void)pcilutype; (void)ilulevel; (void)fillin; (void)droptol; (void)restart; (void)fcomm;
@@ -430,6 +567,8 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
     upload_values(*S, vals);
     if (S->pc == 1) build_amg(*S, vals); else build_binv(*S, vals);
     CUDA_CHECK(cudaStreamSynchronize(S->stream));
+    S->pctl.mode = 0; S->pctl.nranks = 1; S->pctl.me = 0; S->pctl.nsrc = 0; S->pctl.slots = nullptr; S->pctl.flags = nullptr; S->pctl.src = nullptr;
+    if (np > 1) setup_peer(*S);
     if (!fb_ok()) { delete S; return; }
     g_solvers[*id] = S;
 }
@@ -457,13 +596,27 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     CUDA_CHECK(cudaMemcpyAsync(S.x.p, sol, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
     SolverScal h; memset(&h, 0, sizeof(h));
     h.tol2 = S.soltol * S.soltol; h.maxits = S.maxits;
-    CUDA_CHECK(cudaMemcpyAsync(S.scal.p, &h, sizeof(h), cudaMemcpyHostToDevice, st));
-    const int multi = comm_nranks() > 1 ? 1 : 0;
-    // one global reduction: all-reduce of (tmp0, tmp1) + the scalar recurrences on every rank
-#define REDUCE(which) do { if (multi) { comm_allreduce_sum(&S.scal.p->tmp0, 2, st); k_apply_scalars<<<1, 1, 0, st>>>(S.scal.p, which); LAUNCH_CHECK(); } } while (0)
-    if (multi) halo_exchange_flat(S.halo, S.x.p, st);                            // interface values of the initial guess
+    CUDA_CHECK(cudaMemcpyAsync(S.scal.p, &h, offsetof(SolverScal, red_seq), cudaMemcpyHostToDevice, st));   // the sequence numbers live on
+    const int multi = comm_nranks() > 1 ? S.comm_mode : 0;
+    const PeerCtl pc = S.pctl;
+    // one global reduction.  NCCL transport: all-reduce of (tmp0, tmp1) + the scalar recurrences on every rank; peer-memory
+    // transport: the last block of the producing kernel has already done both
+#define REDUCE(which) do { if (multi == 1) { { ProfScope ps_("nccl_allreduce", st); comm_allreduce_sum(&S.scal.p->tmp0, 2, st); } \
+                                             { ProfScope ps_("k_apply_scalars", st); k_apply_scalars<<<1, 1, 0, st>>>(S.scal.p, which); LAUNCH_CHECK(); } } } while (0)
+    // interface values of an SpMV input (parms_MatVec): vec 0 x, 1 pt, 2 st
+    auto exchange = [&](int vec, double* xv, int check_done) {
+        if (multi == 1) { ProfScope ps_("halo_exchange_flat", st); halo_exchange_flat(S.halo, xv, st); }
+        else if (multi == 2) {
+            ProfScope ps_("k_flat_push", st);
+            const int cnt = S.halo.nsend();
+            k_flat_push<<<std::max(1, (cnt + SBS - 1) / SBS), SBS, 0, st>>>(cnt, S.halo.slist.p, S.s_peer.p, S.s_dst.p, xv, (double* const*)S.pv[vec].d_peer.p,
+                                                                       S.halo.nsp, S.dst_ranks.p, S.push_counter.p, S.scal.p, pc, vec, check_done);
+            LAUNCH_CHECK();
+        }
+    };
+    exchange(0, S.x.p, 0);                                                       // interface values of the initial guess
     { ProfScope ps_("k_init_res", st); k_init_res<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
-                                   S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
+                                   S.partial.p, S.counter.p, nr, S.scal.p, pc); LAUNCH_CHECK(); }
     REDUCE(SC_INIT);
     const bool amg = S.pc == 1;
     const int* donep = &S.scal.p->done;
@@ -480,15 +633,15 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     if (!S.h_scal) CUDA_CHECK(cudaMallocHost(&S.h_scal, sizeof(SolverScal)));
     SolverScal* hs = S.h_scal;
     auto iteration = [&]() {
-        if (multi) halo_exchange_flat(S.halo, S.pt.p, st);                       // parms_MatVec: interface exchange of the SpMV input
-        { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
+        exchange(1, S.pt.p, 1);                                                  // parms_MatVec: interface exchange of the SpMV input
+        { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nr, S.scal.p, pc); LAUNCH_CHECK(); }
         REDUCE(SC_ALPHA);
         if (amg) AMG_APPLY(1, "k_amg_enter", S.st.p);
         else { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
-        if (multi) halo_exchange_flat(S.halo, S.st.p, st);
-        { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
+        exchange(2, S.st.p, 1);
+        { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nr, S.scal.p, pc); LAUNCH_CHECK(); }
         REDUCE(SC_SIGMA);
-        { ProfScope ps_("k_x_update", st); k_x_update<<<nr, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nr, S.scal.p, multi); LAUNCH_CHECK(); }
+        { ProfScope ps_("k_x_update", st); k_x_update<<<nr, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nr, S.scal.p, pc); LAUNCH_CHECK(); }
         REDUCE(SC_XUPD);
         if (amg) AMG_APPLY(2, "k_amg_enter", S.pt.p);
         else { ProfScope ps_("k_p_update_pc", st); k_p_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.r.p, S.v.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
@@ -519,6 +672,7 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
 #undef AMG_APPLY
     if (fb_ok()) {
         S.last_its = hs->its; S.last_res = sqrt(hs->omega);
+        if (hs->comm_error) fb_set_error(48, "psolve: a peer rank did not deliver its reduction / interface values within the spin limit (peer-memory transport)");
         if (hs->its >= S.maxits && hs->omega > h.tol2) printf("ERROR: no convergence\n");   // bicgstab_ras.c:237-238
     }
     CUDA_CHECK(cudaMemcpyAsync(sol, S.x.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -540,6 +694,9 @@ void psolver_final(void) {
         for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs, &S->d_vals, &S->d_sval, &S->d_scale, &S->d_binv, &S->partial}) b->release();
         S->halo.release();
         S->amg.release();
+        for (int v = 0; v < 3; v++) peer_release(S->pv[v]);
+        peer_release(S->ctl);
+        S->d_slots.release(); S->d_flags.release(); S->s_peer.release(); S->s_dst.release(); S->dst_ranks.release(); S->src_ranks.release(); S->push_counter.release();
         S->d_rp.release(); S->d_ci.release(); S->d_sptr.release(); S->d_scol.release(); S->scal.release(); S->counter.release();
         if (S->ev0) cudaEventDestroy(S->ev0);
         if (S->ev1) cudaEventDestroy(S->ev1);

@@ -626,8 +626,11 @@ __global__ void LB(128) k_bh(KP p, const double* __restrict__ src, double* __res
 // zinv1 of level nz is the same expression as zinv2 of level nz-1 and is carried over.
 // dynamic smem: cp [blockDim.y][nlp][32]
 // KPP = use_kpp_nonlclflx: the non-local transport of the boundary-layer scheme joins the right-hand side (:688-781)
-template <bool WIMPL, bool KPP>             // WIMPL = w_split without FCT: implicit upwind advection by Wvel_i enters a, b, c (:604-616, :668-682, :737-744)
-__global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
+// NT tracers per launch: the coefficients a, b, c (and with them every division and the Thomas factors c') depend on the
+// thicknesses, Kv and the areas only, so a second tracer adds its right-hand side and its d' recurrence and nothing else.
+struct ImplSet { const double* TS[2]; double* To[2]; int tr_num[2], tracer_id[2]; };
+template <bool WIMPL, bool KPP, int NT>     // WIMPL = w_split without FCT: implicit upwind advection by Wvel_i enters a, b, c (:604-616, :668-682, :737-744)
+__global__ void __launch_bounds__(64, NT == 1 ? 12 : 10) k_impl_diff(KP p, ImplSet q) {
     const int lane = threadIdx.x;
     const int tile = blockIdx.x * blockDim.y + threadIdx.y;
     const int n = tile * TILE + lane;
@@ -637,9 +640,7 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
     const unsigned lv = p.n_lev[n];
     const int nzmin = lv & 255, nzmax = (lv >> 8) & 255;
     const double* __restrict__ hn = p.hnode_new;
-    const double* __restrict__ TS = p.tstar;
-    double* To = p.T;
-    double* ZBg = To;                                     // zbar_n(z) waits in the output slot of level z until d'(z) replaces it
+    double* ZBg = q.To[0];                                // zbar_n(z) waits in the first tracer's output slot of level z until d'(z) replaces it
     const double dt = p.dt;
     const double isredi = p.Redi ? 1.0 : 0.0;
     const double vcpw = 4.2e6;
@@ -660,14 +661,22 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
     double h0 = AT(hn, b, z), hp = AT(hn, b, z + 1);
     double zn0 = zb1 + h0 / 2.0, znm = 0.0;
     double kv1 = AT(p.Kv, b, z + 1), ar1 = AT(p.area, b, z + 1), kv0 = 0.0, ar0 = 0.0;
-    double tm = 0.0, t0 = AT(TS, b, z), tp1 = AT(TS, b, z + 1);
+    double tm[NT], t0[NT], tp1[NT], tpm[NT];
+#pragma unroll
+    for (int t = 0; t < NT; t++) { tm[t] = 0.0; t0[t] = AT(q.TS[t], b, z); tp1[t] = AT(q.TS[t], b, z + 1); tpm[t] = 0.0; }
     double asv = AT(p.areasvol, b, z);
-    double zinv1 = 0.0, cpm = 0.0, tpm = 0.0;
+    double zinv1 = 0.0, cpm = 0.0;
     for (; z <= nzmax - 1; z++) {
-        double n_zb = zbot, n_asv = 0.0, n_hp = 0.0, n_tp = 0.0, n_kv = 0.0, n_ar = 0.0;
+        double n_zb = zbot, n_asv = 0.0, n_hp = 0.0, n_kv = 0.0, n_ar = 0.0, n_tp[NT];
+#pragma unroll
+        for (int t = 0; t < NT; t++) n_tp[t] = 0.0;
         if (z + 3 < nzmax) n_zb = AT(ZBg, b, z + 3);
         if (z + 1 <= nzmax - 1) n_asv = AT(p.areasvol, b, z + 1);
-        if (z + 2 <= nzmax - 1) { n_hp = AT(hn, b, z + 2); n_tp = AT(TS, b, z + 2); }
+        if (z + 2 <= nzmax - 1) {
+            n_hp = AT(hn, b, z + 2);
+#pragma unroll
+            for (int t = 0; t < NT; t++) n_tp[t] = AT(q.TS[t], b, z + 2);
+        }
         if (z + 2 <= nzmax) { n_kv = AT(p.Kv, b, z + 2); n_ar = AT(p.area, b, z + 2); }
         const double znp = zb2 + hp / 2.0;                                   // Z_n(z+1)
         const double h = h0;
@@ -730,55 +739,67 @@ __global__ void __launch_bounds__(64, 12) k_impl_diff(KP p) {
                 bb = bb + omax(0.0, wi0) * v_adv;
             }
         }
-        double tr;
-        if (z == nzmin) tr = -(bb - h) * t0 - cc * tp1;
-        else if (z <= nzmax - 2) tr = -a * tm - (bb - h) * t0 - cc * tp1;
-        else tr = -a * tm - (bb - h) * t0;
-        if (KPP && p.tr_num <= 2) {                                          // :688-781, fesom KPP and cvmix KPP share the formula
-            const double* __restrict__ G = p.tr_num == 1 ? p.kgT : p.kgS;
-            const double* __restrict__ B = p.tr_num == 1 ? p.kb2 : p.kb3;
-            const double m0 = z > nzmin ? omin(AT(G, b, z) * AT(B, b, z), 1.0) : 0.0;
-            const double m1 = z <= nzmax - 2 ? omin(AT(G, b, z + 1) * AT(B, b, z + 1), 1.0) : 0.0;
-            double x;
-            if (z == nzmin) x = -m1 * div_by(ar1, asv, rasv);
-            else if (z <= nzmax - 2) x = m0 * div_by(ar0, asv, rasv) - m1 * div_by(ar1, asv, rasv);
-            else x = m0 * div_by(ar0, asv, rasv);
-            if (p.tr_num == 1) tr = tr + x * p.heat_flux[n] / vcpw * dt;
-            else {
-                const double rsss = p.ref_sss_local ? AT(TS, b, 1) : p.ref_sss;     // tr_arr(1,n,2), :691
-                tr = tr - x * rsss * p.water_flux[n] * dt;
+        double m = bb, rm;                                                   // Thomas pivot :828-835, shared by the tracers
+        if (z > nzmin) m = bb - cpm * a;
+        rm = 1.0 / m;
+#pragma unroll
+        for (int t = 0; t < NT; t++) {
+            const int tr_num = q.tr_num[t];
+            double tr;
+            if (z == nzmin) tr = -(bb - h) * t0[t] - cc * tp1[t];
+            else if (z <= nzmax - 2) tr = -a * tm[t] - (bb - h) * t0[t] - cc * tp1[t];
+            else tr = -a * tm[t] - (bb - h) * t0[t];
+            if (KPP && tr_num <= 2) {                                        // :688-781, fesom KPP and cvmix KPP share the formula
+                const double* __restrict__ G = tr_num == 1 ? p.kgT : p.kgS;
+                const double* __restrict__ B = tr_num == 1 ? p.kb2 : p.kb3;
+                const double m0 = z > nzmin ? omin(AT(G, b, z) * AT(B, b, z), 1.0) : 0.0;
+                const double m1 = z <= nzmax - 2 ? omin(AT(G, b, z + 1) * AT(B, b, z + 1), 1.0) : 0.0;
+                double x;
+                if (z == nzmin) x = -m1 * div_by(ar1, asv, rasv);
+                else if (z <= nzmax - 2) x = m0 * div_by(ar0, asv, rasv) - m1 * div_by(ar1, asv, rasv);
+                else x = m0 * div_by(ar0, asv, rasv);
+                if (tr_num == 1) tr = tr + x * p.heat_flux[n] / vcpw * dt;
+                else {
+                    const double rsss = p.ref_sss_local ? AT(q.TS[t], b, 1) : p.ref_sss;     // tr_arr(1,n,2), :691
+                    tr = tr - x * rsss * p.water_flux[n] * dt;
+                }
             }
+            if (p.use_sw_pene && tr_num == 1)
+                tr = tr + (AT(p.sw3d, b, z) - div_by(AT(p.sw3d, b, z + 1) * ar1, asv, rasv)) * zinv;
+            if (z == nzmin) {
+                double bc = 0.0;
+                if (q.tracer_id[t] == 0) {
+                    const double tsurf = (tr_num == 1) ? t0[t] : AT(p.T1, b, nzmin);
+                    bc = -dt * (p.heat_flux[n] / vcpw + tsurf * p.water_flux[n] * p.is_nonlinfs);
+                } else if (q.tracer_id[t] == 1)
+                    bc = dt * (p.virtual_salt[n] + p.relax_salt[n] - p.real_salt_flux[n] * p.is_nonlinfs);
+                tr = tr + bc;
+                tpm[t] = div_by(tr, m, rm);                                  // :829
+            } else tpm[t] = div_by(tr - tpm[t] * a, m, rm);                  // :835
         }
-        if (p.use_sw_pene && p.tr_num == 1)
-            tr = tr + (AT(p.sw3d, b, z) - div_by(AT(p.sw3d, b, z + 1) * ar1, asv, rasv)) * zinv;
-        if (z == nzmin) {
-            double bc = 0.0;
-            if (p.tracer_id == 0) {
-                const double tsurf = (p.tr_num == 1) ? t0 : AT(p.T1, b, nzmin);
-                bc = -dt * (p.heat_flux[n] / vcpw + tsurf * p.water_flux[n] * p.is_nonlinfs);
-            } else if (p.tracer_id == 1)
-                bc = dt * (p.virtual_salt[n] + p.relax_salt[n] - p.real_salt_flux[n] * p.is_nonlinfs);
-            tr = tr + bc;
-            const double rbb = 1.0 / bb;
-            cpm = div_by(cc, bb, rbb); tpm = div_by(tr, bb, rbb);            // Thomas :828-829
-        } else {
-            const double m = bb - cpm * a, rm = 1.0 / m;                     // :831-835
-            cpm = div_by(cc, m, rm); tpm = div_by(tr - tpm * a, m, rm);
-        }
+        cpm = div_by(cc, m, rm);
         cps[(z - 1) * TILE] = cpm;
-        AT(To, b, z) = tpm;
+#pragma unroll
+        for (int t = 0; t < NT; t++) AT(q.To[t], b, z) = tpm[t];
         // shift the window to level z+1
         zb0 = zb1; zb1 = zb2; zb2 = n_zb; znm = zn0; zn0 = znp; h0 = hp; hp = n_hp; zinv1 = zinv2;
-        kv0 = kv1; kv1 = n_kv; ar0 = ar1; ar1 = n_ar; tm = t0; t0 = tp1; tp1 = n_tp; asv = n_asv;
+        kv0 = kv1; kv1 = n_kv; ar0 = ar1; ar1 = n_ar; asv = n_asv;
+#pragma unroll
+        for (int t = 0; t < NT; t++) { tm[t] = t0[t]; t0[t] = tp1[t]; tp1[t] = n_tp[t]; }
     }
 #undef ZBL
     __syncwarp();
-    double x = tpm;                                                           // :838-844
-    AT(To, b, nzmax - 1) = AT(TS, b, nzmax - 1) + x;
-#pragma unroll 4
+    double x[NT];                                                             // :838-844
+#pragma unroll
+    for (int t = 0; t < NT; t++) { x[t] = tpm[t]; AT(q.To[t], b, nzmax - 1) = AT(q.TS[t], b, nzmax - 1) + x[t]; }
+#pragma unroll 2
     for (int zz = nzmax - 2; zz >= nzmin; zz--) {
-        x = AT(To, b, zz) - cps[(zz - 1) * TILE] * x;
-        AT(To, b, zz) = AT(TS, b, zz) + x;
+        const double cp = cps[(zz - 1) * TILE];
+#pragma unroll
+        for (int t = 0; t < NT; t++) {
+            x[t] = AT(q.To[t], b, zz) - cp * x[t];
+            AT(q.To[t], b, zz) = AT(q.TS[t], b, zz) + x[t];
+        }
     }
 }
 
@@ -1163,18 +1184,27 @@ void tracer_step_group(TracerCtx& c, int t0, int nt) {
         ProfScope ps_(nt == 2 ? "copy_told_x2" : "copy_told", st);
         CUDA_CHECK(cudaMemcpyAsync(pk[0].Told, pk[0].T, nf * nt * sizeof(double), cudaMemcpyDeviceToDevice, st));
     }
+    if (c.opt.i_vert_diff) {                                    // diff_ver_part_impl_ale: the tracers of the pass share the coefficients
+        const bool wimpl = c.opt.w_split && !fct, kpp = c.opt.use_kpp_nonlclflx && c.kgT.p;
+        static const bool one_by_one = getenv("FB200_NT_IMPL") && getenv("FB200_NT_IMPL")[0] == '1';
+        const int step = (nt == 2 && !one_by_one) ? 2 : 1;
+        for (int k0 = 0; k0 < nt; k0 += step) {
+            ImplSet q;
+            for (int t = 0; t < 2; t++) {
+                const int kk = k0 + (t < step ? t : 0);
+                q.TS[t] = pk[kk].tstar; q.To[t] = pk[kk].T; q.tr_num[t] = t0 + kk + 1; q.tracer_id[t] = c.opt.tracer_id[t0 + kk];
+            }
+            const KP& p = pk[k0];                               // c' scratch: the first tracer's vertical-flux field
+            const dim3 gI((c.myNtiles + 1) / 2), bI(TILE, 2);
+#define IMPL(W, K) do { if (step == 2) KL("k_impl_diff_x2", k_impl_diff<W, K, 2><<<gI, bI, 0, st>>>(p, q)); else KL("k_impl_diff", k_impl_diff<W, K, 1><<<gI, bI, 0, st>>>(p, q)); } while (0)
+            if (wimpl && kpp) IMPL(true, true); else if (wimpl) IMPL(true, false); else if (kpp) IMPL(false, true); else IMPL(false, false);
+#undef IMPL
+        }
+    }
     for (int k = 0; k < nt; k++) {
         KP& p = pk[k];
         const int tr = t0 + k;
         if (!c.opt.i_vert_diff) KL("k_copy_cols", k_copy_cols<<<(c.myN + 127) / 128, 128, 0, st>>>(p, p.T, p.tstar));      // T = T*, no implicit solve
-        else {
-            const bool wimpl = c.opt.w_split && !fct, kpp = c.opt.use_kpp_nonlclflx && c.kgT.p;
-            const dim3 gI((c.myNtiles + 1) / 2), bI(TILE, 2);
-            if (wimpl && kpp) KL("k_impl_diff", k_impl_diff<true, true><<<gI, bI, 0, st>>>(p));
-            else if (wimpl) KL("k_impl_diff", k_impl_diff<true, false><<<gI, bI, 0, st>>>(p));
-            else if (kpp) KL("k_impl_diff", k_impl_diff<false, true><<<gI, bI, 0, st>>>(p));
-            else KL("k_impl_diff", k_impl_diff<false, false><<<gI, bI, 0, st>>>(p));
-        }
         if (c.opt.smooth_bh_tra) {                                                          // diff_part_bh, oce_ale_tracer.F90:321-323
             if (!c.bh_tmp.p) c.bh_tmp.alloc(nf);
             const int gB = (c.myN + 127) / 128;

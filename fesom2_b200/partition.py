@@ -327,3 +327,134 @@ def exchange_dist(lm, field, kind, dist, group=None):
         q.wait()
     for idx, t in rbufs:
         field[idx] = t.numpy()
+
+
+# ---------------------------------------------------------------------------------------------------
+# The reference's own partitioner: stiff_mat_ini (the node graph), partit (src/fort_part.c -> METIS 5.1.0, compiled from
+# /root/reference by oracle/Makefile.metis into oracle/_ref/libmetis_part.so) and check_partitioning.
+def node_graph(elem2D_nodes, nod2D):
+    """stiff_mat_ini (src/fvom_init.F90:1351-1412): CSR adjacency of the nodes, 1-based, no diagonal; a node's neighbours in the
+    order in which the element loop first meets them (pairs (2,1), (3,1), (3,2) of every triangle)."""
+    en = np.asarray(elem2D_nodes, dtype=np.int64)                    # (E, 3), 1-based
+    a = np.stack([en[:, 1], en[:, 2], en[:, 2]], axis=1).ravel()     # nod(i)
+    b = np.stack([en[:, 0], en[:, 0], en[:, 1]], axis=1).ravel()     # nod(j)
+    key = np.minimum(a, b) * (nod2D + 1) + np.maximum(a, b)
+    _, first = np.unique(key, return_index=True)
+    first.sort()                                                     # pairs in the order of their first occurrence
+    a, b = a[first], b[first]
+    src = np.concatenate([a, b])
+    dst = np.concatenate([b, a])
+    t = np.concatenate([np.arange(a.size), np.arange(a.size)])       # both directions enter the lists at the same time
+    order = np.lexsort((t, src))
+    src, dst = src[order], dst[order]
+    rowptr = np.ones(nod2D + 1, dtype=np.int32)
+    rowptr[1:] = 1 + np.cumsum(np.bincount(src - 1, minlength=nod2D))
+    return rowptr, dst.astype(np.int32)
+
+
+def check_partitioning(part, rowptr, colind, nlevels_nod2D, npes, verbose=False):
+    """check_partitioning (src/fvom_init.F90:1543-1690): nodes with at most one neighbour in their own partition move to an
+    adjacent partition.  part: 0-based, modified in place; returns the number of moved nodes."""
+    n = part.size
+    rp, ci = rowptr.astype(np.int64) - 1, colind.astype(np.int64) - 1
+    nl = nlevels_nod2D.astype(np.int64)
+    npp = np.zeros((2, npes), dtype=np.int64)
+    npp[0] = np.bincount(part, minlength=npes)
+    npp[1] = np.bincount(part, weights=nl, minlength=npes).astype(np.int64)
+    max1, max2 = npp[0].max(), npp[1].max()
+    # candidates: the test reads the CURRENT partition vector, so every node is re-tested in order; nodes whose own and
+    # neighbours' partitions never changed keep their initial verdict
+    same0 = np.add.reduceat((part[ci] == np.repeat(part, np.diff(rp))).astype(np.int64), rp[:-1])
+    dirty = np.zeros(n, dtype=bool)
+    moved = 0
+    for k in range(n):
+        if same0[k] > 1 and not dirty[k]:
+            continue
+        nb = part[ci[rp[k]:rp[k + 1]]]
+        if (nb == part[k]).sum() > 1:
+            continue
+        ne_part, ne_num, ne_load = [int(nb[0])], [1], [(npp[0, nb[0]] + 1, npp[1, nb[0]] + nl[k])]
+        for p_ in nb:
+            if p_ == part[k]:
+                continue
+            if p_ in ne_part:
+                ne_num[ne_part.index(int(p_))] += 1
+            else:
+                ne_part.append(int(p_)); ne_num.append(1); ne_load.append((npp[0, p_] + 1, npp[1, p_] + nl[k]))
+        kmax = int(np.argmax(ne_num))
+        if ne_num[kmax] <= 1:
+            continue
+        if ne_load[kmax][0] <= max1 and ne_load[kmax][1] <= max2:
+            kk = kmax
+        else:
+            kk = None
+            for q in range(len(ne_part)):
+                if ne_num[q] == 1 or q == kmax:
+                    continue
+                if ne_load[q][0] <= max1 and ne_load[q][1] <= max2:
+                    kk = q
+                    break
+            if kk is None:
+                kk = kmax
+        new = ne_part[kk]
+        npp[0, new] += 1; npp[1, new] += nl[k]; npp[0, part[k]] -= 1; npp[1, part[k]] -= nl[k]
+        if verbose:
+            print("node", k + 1, "moves from part", part[k], "to", new)
+        part[k] = new
+        dirty[ci[rp[k]:rp[k + 1]]] = True
+        moved += 1
+    return moved
+
+
+_metis = {}
+
+
+def metis_lib(plain=False):
+    """oracle/_ref/libmetis_part.so (built here from /root/reference by oracle/Makefile.metis; it travels with the snapshot);
+    plain: the copy compiled without -DPART_WEIGHTED / -DMETISRANDOMSEED"""
+    global _metis
+    if plain not in _metis:
+        import ctypes as C
+        root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+        so = os.path.join(root, "oracle", "_ref", "libmetis_part_plain.so" if plain else "libmetis_part.so")
+        mk = os.path.join(root, "oracle", "Makefile.metis")
+        if not os.path.exists(so) and os.path.isdir("/root/reference/lib/metis-5.1.0") and os.path.exists(mk):
+            import subprocess
+            subprocess.run(["make", "-s", "-f", mk, "-j8"], cwd=os.path.join(root, "oracle"), check=True)
+        if not os.path.exists(so):
+            return None
+        _metis[plain] = C.CDLL(so)
+    return _metis[plain]
+
+
+def metis_partition(hm, npes, check=True, plain=False):
+    """the reference's partitioning of the mesh in hm (an undivided HostModel) into npes parts: stiff_mat_ini ->
+    partit(ssh_stiff%dim, rowptr, colind, nlevels_nod2D, np, part) (src/fvom_init.F90:1528) -> check_partitioning.
+    Returns part (0-based PE per node), like the part vector behind dist_N/rpart.out."""
+    import ctypes as C
+    L = metis_lib(plain)
+    if L is None:
+        raise RuntimeError("oracle/_ref/libmetis_part.so has not been built (needs /root/reference)")
+    nod2D = hm.ipar("myDim_nod2D")
+    E = hm.ipar("myDim_elem2D")
+    rowptr, colind = node_graph(hm["elem2D_nodes"][:E], nod2D)
+    wgt = np.ascontiguousarray(hm["nlevels_nod2D"][:nod2D], dtype=np.int32)
+    npv = np.zeros(10, dtype=np.int32)
+    npv[0] = npes
+    part = np.zeros(nod2D, dtype=np.int32)
+    n = C.c_int32(nod2D)
+    # fort_part.c reports on stdout (printf); bench.py owns stdout (ONE JSON line): send the C-level stdout to stderr meanwhile
+    import sys
+    sys.stdout.flush()
+    keep = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        L.partit(C.byref(n), C.c_void_p(rowptr.ctypes.data), C.c_void_p(colind.ctypes.data), C.c_void_p(wgt.ctypes.data),
+                 C.c_void_p(npv.ctypes.data), C.c_void_p(part.ctypes.data))
+        C.CDLL(None).fflush(None)
+    finally:
+        os.dup2(keep, 1)
+        os.close(keep)
+    if check:
+        check_partitioning(part, rowptr, colind, wgt, npes)
+    return part

@@ -90,7 +90,7 @@ def _build(force, SO, optflags):
             fh.write(t)
         cpp.append(dst)
     cpp += [os.path.join(HERE, "cuda_emu.cpp"), os.path.join(HERE, "nccl_emu.cpp")]
-    cmd = ["g++", "-std=c++17"] + optflags + ["-ffp-contract=off", "-fPIC", "-shared", "-include", os.path.join(HERE, "cuda_emu.h"),
+    cmd = ["g++", "-std=c++17", "-DFB200_EMULATION"] + optflags + ["-ffp-contract=off", "-fPIC", "-shared", "-include", os.path.join(HERE, "cuda_emu.h"),
            "-I", HERE, "-I", CSRC, "-I", os.path.join(ROOT, "include"), "-o", SO + ".tmp"] + cpp
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:

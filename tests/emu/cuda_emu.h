@@ -81,6 +81,10 @@ static inline cudaError_t cudaGraphDestroy(cudaGraph_t) { return 0; }
 static inline cudaError_t cudaGraphExecDestroy(cudaGraphExec_t) { return 0; }
 static inline cudaError_t cudaGraphLaunch(cudaGraphExec_t, cudaStream_t) { return 900; }
 static inline void __threadfence() {}
+static inline void __threadfence_system() {}
+static inline long long clock64() { return 0; }
+enum { cudaDevAttrMultiProcessorCount = 16 };
+static inline cudaError_t cudaDeviceGetAttribute(int* v, int, int) { *v = 148; return 0; }
 
 // ---- execution model
 struct emu_cfg {

@@ -102,6 +102,9 @@ def run_check(name, dist, rank, world, ale=False, emulate=False, steps=2):
     if name == "pi" and world == 2:
         part = np.load(os.path.join(util.GOLD, "pi_dist2.npz"))["part"]      # the reference's own METIS partition
         part_fixed = part
+    elif P.metis_lib() is not None and "--strips" not in sys.argv:
+        part = P.metis_partition(hm, world)                                  # the reference's partitioner on this mesh
+        part_fixed = part
     else:
         part = P.contiguous_partition(hm, world)
         part_fixed = None
