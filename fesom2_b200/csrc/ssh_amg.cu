@@ -325,12 +325,16 @@ static bool amg_fused_on() {
     return false;                                   // the emulation runs the blocks of a launch one after another: no grid barrier
 #else
     static int on = -1;
-    if (on < 0) { const char* e = getenv("FB200_AMG_FUSED"); on = (e && e[0] == '0') ? 0 : 1; }
+    // measured (profiles/r02_bench_1m_2gpu_*.json): 72-84 us per fused launch against 8 x 11 us for the separate kernels — the seven
+    // grid barriers cost what the launches cost; off unless FB200_AMG_FUSED=1
+    if (on < 0) { const char* e = getenv("FB200_AMG_FUSED"); on = (e && e[0] == '1') ? 1 : 0; }
     return on == 1;
 #endif
 }
 
-void Amg::cycle(double* out, const int* done, cudaStream_t st) {
+// n_out: rows of the last (fine-level) post-smoothing step that are written to `out` — all of level 0 on one rank, the rank's own
+// rows when level 0 is an overlapping subdomain (restricted additive Schwarz: the overlap part of the result is discarded)
+void Amg::cycle(double* out, const int* done, cudaStream_t st, int n_out) {
     const int K = (int)L.size();
     if (K <= 1) return;                                           // single level: the caller's Jacobi step already wrote `out`
 #define AKL(name0, namec, lev, ...) do { ProfScope ps_((lev) == 0 ? name0 : namec, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
@@ -364,7 +368,8 @@ void Amg::cycle(double* out, const int* done, cudaStream_t st) {
         AmgDevLevel& F = L[l];
         double* dst = l == 0 ? out : F.x2.p;
         AKL("k_amg_prolong0", "k_amg_coarse", l, k_amg_prolong<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.P.sptr.p, F.P.scol.p, F.P.sval.p, cur, F.x.p, done));
-        AKL("k_amg_post0", "k_amg_coarse", l, k_amg_post<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.dinv.p, omega, dst, done));
+        const int npost = (l == 0 && n_out > 0) ? std::min(n_out, F.n) : F.n;
+        AKL("k_amg_post0", "k_amg_coarse", l, k_amg_post<<<(npost + ABS - 1) / ABS, ABS, 0, st>>>(npost, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.dinv.p, omega, dst, done));
         cur = dst;
     }
 #undef AKL

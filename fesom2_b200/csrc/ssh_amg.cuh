@@ -54,7 +54,7 @@ struct Amg {
     void upload(const std::vector<AmgHostLevel>& h, double omega_);
     // out = V-cycle(b0) where the caller has already filled L[0].b (= D * in) and L[0].x (= omega dinv0 b0), see k_amg_enter
     // in ssh_solver.cu.  `done` points at the solver's device-side convergence flag: all kernels are no-ops once it is set.
-    void cycle(double* out, const int* done, cudaStream_t st);
+    void cycle(double* out, const int* done, cudaStream_t st, int n_out = 0);
     void release();
 };
 

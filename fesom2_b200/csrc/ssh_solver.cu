@@ -27,7 +27,7 @@ struct SolverScal {             // device-resident scalars
     double alpha, sigma, beta, rho, rho_alt, omega, tol2;
     double tmp0, tmp1;
     int done, its, maxits, comm_error;
-    unsigned long long red_seq, halo_seq[3];       // peer-memory transport: sequence numbers of the reductions / of the pushes of x, pt, st
+    unsigned long long red_seq, halo_seq[4];       // peer-memory transport: sequence numbers of the reductions / of the pushes of x, pt, st and of the V-cycle's right-hand side
 };
 
 // Peer-memory transport of the solver's small messages (comm.cuh: PeerBuf).  Every rank owns one control buffer
@@ -36,7 +36,7 @@ struct SolverScal {             // device-resident scalars
 //                                 form bitwise the same sums and take the same decisions.  Slot k & 3 is reused by reduction
 //                                 k + 4, which a rank can only reach after every peer has contributed to k + 1 .. k + 3, i.e.
 //                                 after every peer has finished reading reduction k.
-//   u64     flags[3][nranks]      interface values: k_flat_push writes this rank's send list straight into the tails of the
+//   u64     flags[4][nranks]      interface values: k_flat_push writes this rank's send list straight into the tails of the
 //                                 peers' vectors (x, pt or st), then its sequence number into flags[vec][me] of each peer; the
 //                                 consuming SpMV waits for the flags of its source ranks.  The reductions between two pushes
 //                                 of the same vector order the next push after the peers' reads (see psolve).
@@ -87,11 +87,17 @@ struct Solver {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // transport of the reductions and interface values on several ranks: 1 = NCCL, 2 = peer memory (see PeerCtl)
     int comm_mode = 0;
-    PeerBuf ctl, pv[3];                      // control buffer; the published vectors x, pt, st
+    PeerBuf ctl, pv[4];                      // control buffer; the published vectors x, pt, st (interface plan) and level-0 b of the V-cycle (overlap plan)
     DevBuf<RedSlot*> d_slots; DevBuf<unsigned long long*> d_flags;
-    DevBuf<int> s_peer, s_dst, dst_ranks, src_ranks;
+    struct PushPlan { DevBuf<int> s_peer, s_dst, dst_ranks, src_ranks; int nsrc = 0; } ifc, ovp;   // where this rank's values go in the peers' vectors
     DevBuf<unsigned> push_counter;
     PeerCtl pctl;
+    // restricted additive Schwarz: the multigrid hierarchy of a rank is built on its rows PLUS `overlap` layers of its
+    // neighbours' rows (the reference's RAS extends by one layer, lib/parms/src/parms_pc_ras.c:56-120); nE = rows of that
+    // extended subdomain, ovl = whose right-hand-side values arrive per cycle, only own rows of the result are kept
+    int overlap = 0, nE = 0;
+    HaloPlan ovl;
+    std::vector<int> gcols, part;            // global column ids and the row offsets of the ranks (a rebuild with new = 2 needs them again)
 };
 static std::map<int, Solver*> g_solvers;
 #define FB200_DEFAULT_PC 1      // multigrid; block-Jacobi through fb200_psolver_set_pc(0) or FB200_SSH_PC=bj
@@ -300,6 +306,8 @@ __global__ void __launch_bounds__(SBS) k_flat_push(int count, const int* __restr
     __threadfence_system();
     if ((int)threadIdx.x < ndst) st_volatile_u64(pc.flags[dst_ranks[threadIdx.x]] + (size_t)vec * pc.nranks + pc.me, sseq);
 }
+// consumers outside this file (the fine-level kernels of the V-cycle) wait through this one-block kernel, launched right after the push
+__global__ void k_wait_halo(SolverScal* sc, PeerCtl pc, int vec) { if (!sc->done) wait_halo(pc, sc, vec); }
 // p = r + beta (p - sigma v) ; pt = M p                                     bicgstab_ras.c:227-230, 150-156
 __global__ void __launch_bounds__(SBS) k_p_update_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ r, const double* __restrict__ v,
                                                      double* __restrict__ p, double* __restrict__ pt, SolverScal* sc) {
@@ -332,6 +340,14 @@ __global__ void __launch_bounds__(SBS) k_amg_enter(int n, const double* __restri
     const double b = in / scale[i];
     b0[i] = b;
     x0[i] = omega * dinv0[i] * b;
+}
+
+// pre-smoothing step x0 = omega dinv b0 on the overlap rows (their b0 has just arrived from the owners)
+__global__ void __launch_bounds__(SBS) k_amg_tail(int n, int nE, const double* __restrict__ dinv0, double omega, const double* __restrict__ b0,
+                                                  double* __restrict__ x0, const SolverScal* sc) {
+    if (sc->done) return;
+    const int i = n + blockIdx.x * SBS + threadIdx.x;
+    if (i < nE) x0[i] = omega * dinv0[i] * b0[i];
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -383,6 +399,89 @@ static void build_amg(Solver& S, const double* vals) {
     std::vector<AmgHostLevel> h;
     amg_host_setup(A, S.amg_prm, h);
     S.amg.upload(h, S.amg_prm.omega);
+    S.nE = S.n;
+}
+
+// Several ranks: hierarchy on the overlapping subdomain.  Every rank receives the global matrix once (one NCCL broadcast per
+// rank; the preconditioner is built from the initial values and kept, psolve.c:200), grows its row set by `overlap` layers
+// of the matrix graph, and sets the multigrid up on those rows x those columns.  Extended numbering: own rows first, then
+// the overlap rows in ascending global (PE-contiguous) order, i.e. grouped by owner like the interface columns.
+// Collective.  gcols_overlap returns the global ids of the overlap rows.
+static void build_amg_overlap(Solver& S, const int* part, const int* gcols_of_entries /* cols as passed to psolver_init */, const double* vals,
+                              std::vector<int>& gcols_overlap) {
+    const int np = comm_nranks(), me = comm_rank();
+    cudaStream_t st = S.stream;
+    const int N = part[np];
+    // nnz of every rank
+    std::vector<int> nz(np, 0);
+    {
+        std::vector<int> mine(1, S.nnz);
+        DevBuf<int> d_m, d_a;
+        d_m.upload(mine); d_a.alloc(np);
+        NCCL_CHECK(ncclAllGather(d_m.p, d_a.p, 1, ncclInt32, comm_handle(), st));
+        CUDA_CHECK(cudaMemcpyAsync(nz.data(), d_a.p, np * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        d_m.release(); d_a.release();
+    }
+    if (!fb_ok()) return;
+    std::vector<long long> off(np + 1, 0);
+    for (int r = 0; r < np; r++) off[r + 1] = off[r] + nz[r];
+    if (off[np] >= (1LL << 31)) { fb_set_error(52, "psolver: global matrix too large for the 32-bit gather of the overlap setup"); return; }
+    std::vector<int> grp((size_t)N + 1, 0), gci((size_t)off[np]);
+    std::vector<double> gv((size_t)off[np]);
+    for (int r = 0; r < np && fb_ok(); r++) {
+        const int nr = part[r + 1] - part[r];
+        DevBuf<int> d_i; DevBuf<double> d_v;
+        d_i.alloc((size_t)nr + 1 + nz[r]); d_v.alloc(std::max(1, nz[r]));
+        if (r == me) {
+            CUDA_CHECK(cudaMemcpyAsync(d_i.p, S.rp.data(), ((size_t)nr + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
+            CUDA_CHECK(cudaMemcpyAsync(d_i.p + nr + 1, gcols_of_entries, (size_t)nz[r] * sizeof(int), cudaMemcpyHostToDevice, st));
+            CUDA_CHECK(cudaMemcpyAsync(d_v.p, vals, (size_t)nz[r] * sizeof(double), cudaMemcpyHostToDevice, st));
+        }
+        NCCL_CHECK(ncclBroadcast(d_i.p, d_i.p, (size_t)nr + 1 + nz[r], ncclInt32, r, comm_handle(), st));
+        NCCL_CHECK(ncclBroadcast(d_v.p, d_v.p, (size_t)std::max(1, nz[r]), ncclDouble, r, comm_handle(), st));
+        std::vector<int> hi((size_t)nr + 1 + nz[r]);
+        CUDA_CHECK(cudaMemcpyAsync(hi.data(), d_i.p, hi.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+        if (nz[r]) CUDA_CHECK(cudaMemcpyAsync(gv.data() + off[r], d_v.p, (size_t)nz[r] * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        for (int i = 0; i < nr; i++) grp[(size_t)part[r] + i + 1] = (int)off[r] + hi[i + 1];
+        std::copy(hi.begin() + nr + 1, hi.end(), gci.begin() + off[r]);
+        d_i.release(); d_v.release();
+    }
+    if (!fb_ok()) return;
+    // grow the row set by `overlap` layers
+    const int g0 = part[me], g1 = part[me + 1];
+    std::vector<char> in((size_t)N, 0);
+    std::vector<int> frontier, added;
+    for (int g = g0; g < g1; g++) in[g] = 1;
+    for (int g = g0; g < g1; g++) frontier.push_back(g);
+    for (int layer = 0; layer < S.overlap; layer++) {
+        std::vector<int> next;
+        for (int g : frontier)
+            for (int j = grp[g]; j < grp[g + 1]; j++) { const int c = gci[j]; if (c >= 0 && c < N && !in[c]) { in[c] = 1; next.push_back(c); } }
+        added.insert(added.end(), next.begin(), next.end());
+        frontier.swap(next);
+    }
+    std::sort(added.begin(), added.end());
+    gcols_overlap = added;
+    const int nE = S.n + (int)added.size();
+    auto g2e = [&](int g) -> int {                    // extended index of global row g, -1 outside the extended subdomain
+        if (g >= g0 && g < g1) return g - g0;
+        auto it = std::lower_bound(added.begin(), added.end(), g);
+        return (it != added.end() && *it == g) ? S.n + (int)(it - added.begin()) : -1;
+    };
+    HostCsr A;
+    A.nrow = A.ncol = nE;
+    A.rp.assign((size_t)nE + 1, 0);
+    for (int e = 0; e < nE; e++) {
+        const int g = e < S.n ? g0 + e : added[e - S.n];
+        for (int j = grp[g]; j < grp[g + 1]; j++) { const int c = g2e(gci[j]); if (c >= 0) { A.ci.push_back(c); A.v.push_back(gv[j]); } }
+        A.rp[e + 1] = (int)A.ci.size();
+    }
+    std::vector<AmgHostLevel> h;
+    amg_host_setup(A, S.amg_prm, h);
+    S.amg.upload(h, S.amg_prm.omega);
+    S.nE = nE;
 }
 
 static void upload_values(Solver& S, const double* vals) {
@@ -428,7 +527,7 @@ void fb200_psolve_amg_info(int* id, int* level, int* rows, long long* a_entries,
 
 // which rows of this rank the other ranks need, and which columns of theirs this rank needs: the interface-variable
 // setup of parms_MatSetup (lib/parms/src/parms_mat_dvcsr.c:93-600).  Requests travel as ints over NCCL.
-static bool setup_halo(Solver& S, const int* part, const std::vector<int>& gcols_sorted /* unique remote global columns */) {
+static bool setup_halo(Solver& S, HaloPlan& H, const int* part, const std::vector<int>& gcols_sorted /* unique remote global columns */) {
     const int np = comm_nranks(), me = comm_rank();
     cudaStream_t st = S.stream;
     std::vector<int> rPE, rptr{1}, rlist, req_cnt(np, 0);
@@ -463,31 +562,24 @@ static bool setup_halo(Solver& S, const int* part, const std::vector<int>& gcols
     if (!slist.empty()) CUDA_CHECK(cudaMemcpyAsync(slist.data(), d_snd.p, slist.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
     for (int& v : slist) { if (v < 0 || v >= S.n) { fb_set_error(45, "psolver_init: a neighbour requested a row this rank does not own"); return false; } v += 1; }
-    halo_plan_build(S.halo, (int)rPE.size(), rPE.data(), rptr.data(), rlist.data(), (int)sPE.size(), sPE.data(), sptr.data(), slist.data());
-    if (S.halo.nsend()) S.halo.sbuf.alloc(S.halo.nsend());
-    if (S.halo.nrecv()) S.halo.rbuf.alloc(S.halo.nrecv());      // sized now: no allocation may happen during graph capture
+    halo_plan_build(H, (int)rPE.size(), rPE.data(), rptr.data(), rlist.data(), (int)sPE.size(), sPE.data(), sptr.data(), slist.data());
+    if (H.nsend()) H.sbuf.alloc(H.nsend());
+    if (H.nrecv()) H.rbuf.alloc(H.nrecv());      // sized now: no allocation may happen during graph capture
     d_cnt.release(); d_all.release(); d_req.release(); d_snd.release();
     return fb_ok();
 }
 
 // peer-memory transport: publish the control buffer and the three exchanged vectors, learn where in the peers' vectors this
 // rank's interface values go.  Collective; on any failure every rank stays on NCCL (comm_mode 1).
-static void setup_peer(Solver& S) {
-    const int np = comm_nranks(), me = comm_rank();
+// destinations of one exchange plan in the peers' vectors: the receiver tells each of its sources where its values go
+// (index n + roff[k] of the receiver's vector)
+static bool setup_push_plan(Solver& S, const HaloPlan& H, Solver::PushPlan& P) {
     cudaStream_t st = S.stream;
-    S.pctl.mode = 1; S.pctl.nranks = np; S.pctl.me = me; S.pctl.nsrc = 0; S.pctl.slots = nullptr; S.pctl.flags = nullptr; S.pctl.src = nullptr;
-    S.comm_mode = 1;
-    if (!peer_enabled()) return;
-    const size_t slot_bytes = sizeof(RedSlot) * 4 * np, bytes = slot_bytes + sizeof(unsigned long long) * 3 * np;
-    if (!peer_publish(S.ctl, nullptr, bytes, st)) return;
-    DevBuf<double>* vecs[3] = {&S.x, &S.pt, &S.st};
-    for (int v = 0; v < 3; v++) if (!peer_publish(S.pv[v], vecs[v]->p, vecs[v]->n * sizeof(double), st)) return;
-    // the receiver tells each of its sources where its values go: index n + roff[k] of the receiver's vectors
-    const HaloPlan& H = S.halo;
     std::vector<int> tell(H.nrp), got(H.nsp, -1);
     for (int k = 0; k < H.nrp; k++) tell[k] = S.n + H.roff[k];
     DevBuf<int> d_tell, d_got;
-    d_tell.upload(tell); d_got.alloc(std::max(1, H.nsp));
+    d_tell.alloc(std::max(1, H.nrp)); d_got.alloc(std::max(1, H.nsp));
+    if (H.nrp) CUDA_CHECK(cudaMemcpyAsync(d_tell.p, tell.data(), H.nrp * sizeof(int), cudaMemcpyHostToDevice, st));
     NCCL_CHECK(ncclGroupStart());
     for (int k = 0; k < H.nsp; k++) NCCL_CHECK(ncclRecv(d_got.p + k, 1, ncclInt32, H.sPE[k], comm_handle(), st));
     for (int k = 0; k < H.nrp; k++) NCCL_CHECK(ncclSend(d_tell.p + k, 1, ncclInt32, H.rPE[k], comm_handle(), st));
@@ -495,22 +587,40 @@ static void setup_peer(Solver& S) {
     if (H.nsp) CUDA_CHECK(cudaMemcpyAsync(got.data(), d_got.p, H.nsp * sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
     d_tell.release(); d_got.release();
-    if (!fb_ok()) return;
+    if (!fb_ok()) return false;
     std::vector<int> sp(std::max(1, H.nsend()), 0), sd(std::max(1, H.nsend()), 0);
     for (int k = 0; k < H.nsp; k++)
         for (int i = H.soff[k]; i < H.soff[k + 1]; i++) { sp[i] = H.sPE[k]; sd[i] = got[k] + (i - H.soff[k]); }
-    S.s_peer.upload(sp); S.s_dst.upload(sd);
+    P.s_peer.upload(sp); P.s_dst.upload(sd);
     std::vector<int> dr(H.sPE), sr(H.rPE);
     if (dr.empty()) dr.push_back(0);
     if (sr.empty()) sr.push_back(0);
-    S.dst_ranks.upload(dr); S.src_ranks.upload(sr);
+    P.dst_ranks.upload(dr); P.src_ranks.upload(sr);
+    P.nsrc = H.nrp;
+    if (H.nsp > SBS) { fb_set_error(49, "psolver: more neighbour partitions than the push kernel signals (256)"); return false; }
+    return fb_ok();
+}
+// peer-memory transport: publish the control buffer and the exchanged vectors, learn where in the peers' vectors this
+// rank's values go.  Collective; on any failure every rank stays on NCCL (comm_mode 1).
+static void setup_peer(Solver& S) {
+    const int np = comm_nranks(), me = comm_rank();
+    cudaStream_t st = S.stream;
+    S.pctl.mode = 1; S.pctl.nranks = np; S.pctl.me = me; S.pctl.nsrc = 0; S.pctl.slots = nullptr; S.pctl.flags = nullptr; S.pctl.src = nullptr;
+    S.comm_mode = 1;
+    if (!peer_enabled()) return;
+    const size_t slot_bytes = sizeof(RedSlot) * 4 * np, bytes = slot_bytes + sizeof(unsigned long long) * 4 * np;
+    if (!peer_publish(S.ctl, nullptr, bytes, st)) return;
+    DevBuf<double>* vecs[4] = {&S.x, &S.pt, &S.st, nullptr};
+    if (S.overlap > 0 && S.amg.ready()) vecs[3] = &S.amg.L[0].b;
+    for (int v = 0; v < 4; v++) if (vecs[v] && !peer_publish(S.pv[v], vecs[v]->p, vecs[v]->n * sizeof(double), st)) return;
+    if (!setup_push_plan(S, S.halo, S.ifc)) return;
+    if (vecs[3] && !setup_push_plan(S, S.ovl, S.ovp)) return;
     std::vector<RedSlot*> sl(np); std::vector<unsigned long long*> fl(np);
     for (int r = 0; r < np; r++) { sl[r] = (RedSlot*)S.ctl.peer[r]; fl[r] = (unsigned long long*)((char*)S.ctl.peer[r] + slot_bytes); }
     S.d_slots.upload(sl); S.d_flags.upload(fl);
     S.push_counter.alloc(1);
-    if (H.nsp > SBS) { fb_set_error(49, "psolver: more neighbour partitions than the push kernel signals (256)"); return; }
     if (!fb_ok()) return;
-    S.pctl.mode = 2; S.pctl.nsrc = H.nrp; S.pctl.slots = S.d_slots.p; S.pctl.flags = S.d_flags.p; S.pctl.src = S.src_ranks.p;
+    S.pctl.mode = 2; S.pctl.nsrc = S.ifc.nsrc; S.pctl.slots = S.d_slots.p; S.pctl.flags = S.d_flags.p; S.pctl.src = S.ifc.src_ranks.p;
     S.comm_mode = 2;
 }
 
@@ -540,7 +650,7 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
         else S->ci[j] = S->n + int(std::lower_bound(remote.begin(), remote.end(), c) - remote.begin());
     }
     S->nloc = S->n + (int)remote.size();
-    if (np > 1 && !setup_halo(*S, part, remote)) { delete S; return; }
+    if (np > 1 && !setup_halo(*S, S->halo, part, remote)) { delete S; return; }
     const int n = S->n;
     S->nslice = (n + 31) / 32;
     S->nblocks = (n + SBS - 1) / SBS;
@@ -565,7 +675,20 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
     for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs}) b->alloc(S->nloc);
     S->partial.alloc((size_t)2 * S->nred); S->scal.alloc(1); S->counter.alloc(1);
     upload_values(*S, vals);
-    if (S->pc == 1) build_amg(*S, vals); else build_binv(*S, vals);
+    S->nE = n;
+    {   // layers of overlap of the multigrid subdomains on several ranks (restricted additive Schwarz); FB200_SSH_OVERLAP=0: none
+        const char* e = getenv("FB200_SSH_OVERLAP");
+        S->overlap = (np > 1 && S->pc == 1) ? (e ? std::max(0, atoi(e)) : 2) : 0;
+    }
+    S->gcols.assign(cols, cols + S->nnz);
+    S->part.assign(part, part + np + 1);
+    if (S->pc == 1) {
+        if (S->overlap > 0) {
+            std::vector<int> ov;
+            build_amg_overlap(*S, part, cols, vals, ov);
+            if (fb_ok() && !setup_halo(*S, S->ovl, part, ov)) { delete S; return; }
+        } else build_amg(*S, vals);
+    } else build_binv(*S, vals);
     CUDA_CHECK(cudaStreamSynchronize(S->stream));
     S->pctl.mode = 0; S->pctl.nranks = 1; S->pctl.me = 0; S->pctl.nsrc = 0; S->pctl.slots = nullptr; S->pctl.flags = nullptr; S->pctl.src = nullptr;
     if (np > 1) setup_peer(*S);
@@ -587,7 +710,13 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
             upload_values(S, vals);
             if (*newvalues == 2) {                                   // the captured graph holds the old preconditioner's buffers
                 if (S.graph) { CUDA_CHECK(cudaStreamSynchronize(st)); cudaGraphExecDestroy(S.graph); S.graph = nullptr; }
-                if (S.pc == 1) build_amg(S, vals); else build_binv(S, vals);
+                if (S.pc == 1 && S.overlap > 0) {                // collective, like the call itself
+                    std::vector<int> ov;
+                    build_amg_overlap(S, S.part.data(), S.gcols.data(), vals, ov);
+                    if (fb_ok()) setup_halo(S, S.ovl, S.part.data(), ov);
+                    if (fb_ok() && comm_nranks() > 1) setup_peer(S);  // the level-0 right-hand side is a new allocation: publish again
+                } else if (S.pc == 1) build_amg(S, vals);
+                else build_binv(S, vals);
             }
         }
         else fprintf(stderr, "ERROR: matrix data is static\n");          // psolve.c:203
@@ -603,15 +732,21 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     // transport: the last block of the producing kernel has already done both
 #define REDUCE(which) do { if (multi == 1) { { ProfScope ps_("nccl_allreduce", st); comm_allreduce_sum(&S.scal.p->tmp0, 2, st); } \
                                              { ProfScope ps_("k_apply_scalars", st); k_apply_scalars<<<1, 1, 0, st>>>(S.scal.p, which); LAUNCH_CHECK(); } } } while (0)
-    // interface values of an SpMV input (parms_MatVec): vec 0 x, 1 pt, 2 st
+    // vec 0 x, 1 pt, 2 st: interface values of an SpMV input (parms_MatVec); vec 3: the V-cycle's right-hand side on the overlap rows
     auto exchange = [&](int vec, double* xv, int check_done) {
-        if (multi == 1) { ProfScope ps_("halo_exchange_flat", st); halo_exchange_flat(S.halo, xv, st); }
+        HaloPlan& H = vec == 3 ? S.ovl : S.halo;
+        Solver::PushPlan& P = vec == 3 ? S.ovp : S.ifc;
+        if (multi == 1) { ProfScope ps_(vec == 3 ? "overlap_exchange" : "halo_exchange_flat", st); halo_exchange_flat(H, xv, st); }
         else if (multi == 2) {
             ProfScope ps_("k_flat_push", st);
-            const int cnt = S.halo.nsend();
-            k_flat_push<<<std::max(1, (cnt + SBS - 1) / SBS), SBS, 0, st>>>(cnt, S.halo.slist.p, S.s_peer.p, S.s_dst.p, xv, (double* const*)S.pv[vec].d_peer.p,
-                                                                       S.halo.nsp, S.dst_ranks.p, S.push_counter.p, S.scal.p, pc, vec, check_done);
+            const int cnt = H.nsend();
+            k_flat_push<<<std::max(1, (cnt + SBS - 1) / SBS), SBS, 0, st>>>(cnt, H.slist.p, P.s_peer.p, P.s_dst.p, xv, (double* const*)S.pv[vec].d_peer.p,
+                                                                       H.nsp, P.dst_ranks.p, S.push_counter.p, S.scal.p, pc, vec, check_done);
             LAUNCH_CHECK();
+            if (vec == 3) {                                       // the consumers are the cycle's kernels: wait in a one-block kernel
+                PeerCtl po = pc; po.nsrc = P.nsrc; po.src = P.src_ranks.p;
+                k_wait_halo<<<1, 32, 0, st>>>(S.scal.p, po, vec); LAUNCH_CHECK();
+            }
         }
     };
     exchange(0, S.x.p, 0);                                                       // interface values of the initial guess
@@ -625,7 +760,12 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
         AmgDevLevel& L0 = S.amg.L[0]; \
         { ProfScope ps_(name, st); k_amg_enter<MODE><<<nb, SBS, 0, st>>>(n, S.d_scale.p, L0.dinv.p, S.amg.omega, S.v.p, S.r.p, S.p.p, L0.b.p, \
                                                    S.amg.levels() > 1 ? L0.x.p : (out), S.scal.p); LAUNCH_CHECK(); } \
-        S.amg.cycle(out, donep, st); } while (0)
+        if (S.overlap > 0 && S.amg.levels() > 1) {              /* right-hand side of the overlap rows from their owners, their pre-smoothing step here */ \
+            exchange(3, L0.b.p, 1); \
+            const int nt_ = S.nE - n; \
+            if (nt_ > 0) { ProfScope ps_("k_amg_tail", st); k_amg_tail<<<(nt_ + SBS - 1) / SBS, SBS, 0, st>>>(n, S.nE, L0.dinv.p, S.amg.omega, L0.b.p, L0.x.p, S.scal.p); LAUNCH_CHECK(); } \
+        } \
+        S.amg.cycle(out, donep, st, n); } while (0)
     if (amg) AMG_APPLY(0, "k_amg_enter", S.pt.p);
     else { ProfScope ps_("k_pc", st); k_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.p.p, S.pt.p, S.scal.p); LAUNCH_CHECK(); }
     int done = 0, launched = 0;
@@ -694,9 +834,11 @@ void psolver_final(void) {
         for (DevBuf<double>* b : {&S->x, &S->y, &S->r, &S->p, &S->pt, &S->st, &S->v, &S->t, &S->rhs, &S->d_vals, &S->d_sval, &S->d_scale, &S->d_binv, &S->partial}) b->release();
         S->halo.release();
         S->amg.release();
-        for (int v = 0; v < 3; v++) peer_release(S->pv[v]);
+        for (int v = 0; v < 4; v++) peer_release(S->pv[v]);
+        S->ovl.release();
         peer_release(S->ctl);
-        S->d_slots.release(); S->d_flags.release(); S->s_peer.release(); S->s_dst.release(); S->dst_ranks.release(); S->src_ranks.release(); S->push_counter.release();
+        S->d_slots.release(); S->d_flags.release(); S->push_counter.release();
+        for (Solver::PushPlan* P : {&S->ifc, &S->ovp}) { P->s_peer.release(); P->s_dst.release(); P->dst_ranks.release(); P->src_ranks.release(); }
         S->d_rp.release(); S->d_ci.release(); S->d_sptr.release(); S->d_scol.release(); S->scal.release(); S->counter.release();
         if (S->ev0) cudaEventDestroy(S->ev0);
         if (S->ev1) cudaEventDestroy(S->ev1);

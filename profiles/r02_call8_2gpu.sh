@@ -1,0 +1,23 @@
+# GPU call 8 (2 GPUs): V-cycle with the fine level coupled across the partitions vs local smoothing; transports
+set -x
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_multi.py -x -q > gpurun_out/c8_pytest_multi.log 2>&1; echo "pytest multi exit $?"; tail -3 gpurun_out/c8_pytest_multi.log
+T="timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29611"
+B="bench.py --gpus 2 --nodes 1000000 --no-e2e --no-cpu-baseline --steps 5"
+$T $B > gpurun_out/c8_full_p2p.json 2> gpurun_out/c8_full_p2p.err; echo "full p2p exit $?"
+FB200_AMG_FULL=0 $T $B --no-parity > gpurun_out/c8_local_p2p.json 2> gpurun_out/c8_local_p2p.err; echo "local exit $?"
+FB200_SSH_COMM=nccl $T $B --no-parity > gpurun_out/c8_full_nccl.json 2> gpurun_out/c8_full_nccl.err; echo "nccl exit $?"
+$T $B --no-parity --partition strips > gpurun_out/c8_full_p2p_strips.json 2> gpurun_out/c8_full_p2p_strips.err; echo "strips exit $?"
+$T bench.py --gpus 2 --no-cpu-baseline --steps 5 > gpurun_out/c8_5m_2gpu.json 2> gpurun_out/c8_5m_2gpu.err; echo "5m 2gpu exit $?"
+python - <<'PY'
+import json, glob
+for f in sorted(glob.glob("gpurun_out/c8_*.json")):
+    try:
+        d = json.loads(open(f).read().strip().splitlines()[-1])
+        k = d.get("kernels", {})
+        print(f, "tracer_ms", round(d["tracer_ms_per_step"], 2), "ssh", {a: d["ssh"][a] for a in ("ms_per_step", "iterations", "ms_per_iteration")}, "e2e", d.get("e2e", {}).get("ms_per_step"), "parity", (d.get("parity") or {}).get("ok"))
+        print("   ", {n: (round(v["ms"] / v["launches"], 4), v["launches"]) for n, v in k.items() if n.startswith("k_amg") or n.startswith("k_spmv") or n.startswith("nccl") or n.startswith("k_flat") or n in ("k_x_update","k_apply_scalars","halo_exchange_flat","k_halo_pack","k_halo_unpack")})
+    except Exception as e:
+        print(f, "unreadable:", e)
+PY
+for f in gpurun_out/c8_*.err; do echo $f; tail -n 3 $f; done

@@ -20,3 +20,4 @@ ncclResult_t ncclSend(const void* buf, size_t count, ncclDataType_t, int peer, n
 ncclResult_t ncclRecv(void* buf, size_t count, ncclDataType_t, int peer, ncclComm_t comm, void* stream);
 ncclResult_t ncclAllGather(const void* send, void* recv, size_t sendcount, ncclDataType_t, ncclComm_t comm, void* stream);
 ncclResult_t ncclAllReduce(const void* send, void* recv, size_t count, ncclDataType_t, ncclRedOp_t, ncclComm_t comm, void* stream);
+ncclResult_t ncclBroadcast(const void* send, void* recv, size_t count, ncclDataType_t, int root, ncclComm_t comm, void* stream);

@@ -108,3 +108,15 @@ ncclResult_t ncclAllReduce(const void* send, void* recv, size_t count, ncclDataT
     memcpy(recv, acc.data(), count * sizeof(double));
     return 0;
 }
+ncclResult_t ncclBroadcast(const void* send, void* recv, size_t count, ncclDataType_t dt, int root, ncclComm_t comm, void*) {
+    emu_nccl_comm& c = *comm;
+    const long s = c.arseq++;
+    const size_t bytes = count * (size_t)dt;
+    const std::string path = c.dir + "/ar" + std::to_string(s) + "_r" + std::to_string(root) + ".bin";
+    if (c.rank == root) {
+        if (!write_file(path, send, bytes)) return 1;
+        if (recv != send) memcpy(recv, send, bytes);
+        return 0;
+    }
+    return read_file(path, recv, bytes, false) ? 0 : 1;
+}
