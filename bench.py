@@ -9,7 +9,8 @@ diffusion, implicit vertical diffusion, salinity clamp).  Prints ONE JSON line (
 
   value      tracer node-level updates/s = wet (node, layer) pairs x num_tracers x K / device time of the K tracer
              steps, state resident in HBM (CUDA events on the launching stream, max over ranks)
-  ssh        SSH solve ms/step (device time of psolve, incl. row scaling), iterations, final scaled residual
+  ssh        SSH solve ms/step (device time of psolve incl. row scaling; matrix values, right-hand side and solution in HBM),
+             iterations, final scaled residual
   e2e        the same two calls through the C ABI with HOST (pinned) buffers: fb200_push_state_early/_late +
              psolve + fb200_solve_tracers_ale_resident, host<->device copies inside the timed region
   roofline   dominant kernel: algorithmic bytes per launch / measured launch duration vs MEASURED_PEAKS.json
@@ -69,18 +70,21 @@ def algo_bytes_row(name, block):
     return b + 8 * block if name in PC_KERNELS else b
 
 
-def amg_bytes(levels):
+def amg_bytes(levels, folded=False):
     """Algorithmic bytes per launch of the multigrid kernels from the hierarchy's sizes [(rows, A, P, R stored SELL entries)]:
     every stored matrix entry = 8 B value + 4 B column, every vector a kernel reads or writes counted once.  The kernels
     of the coarse levels share one profile name (k_amg_coarse): its figure is the mean over the coarse launches of a cycle."""
     if not levels:
         return {}
-    out = {"k_amg_enter": 60 * levels[0][0]}
+    out = {"k_amg_enter": (52 if folded else 60) * levels[0][0]}
     coarse, ncoarse = 0, 0
     for l in range(len(levels) - 1):
         n, a, p, r = levels[l]
         nc = levels[l + 1][0]
-        per = {"resid": 12 * a + 24 * n, "restrict": 12 * r + 8 * n + 24 * nc, "prolong": 12 * p + 16 * n + 8 * nc, "post": 12 * a + 32 * n}
+        if folded:      # (a, p, r) = stored entries of T, Q, M: down b_c = M b, up x = T b + Q x_c
+            per = {"down": 12 * r + 8 * n + 8 * nc, "up": 12 * (a + p) + 16 * n + 8 * nc}
+        else:
+            per = {"resid": 12 * a + 24 * n, "restrict": 12 * r + 8 * n + 24 * nc, "prolong": 12 * p + 16 * n + 8 * nc, "post": 12 * a + 32 * n}
         for k, v in per.items():
             if l == 0:
                 out["k_amg_%s0" % k] = v
@@ -302,16 +306,23 @@ def run_b200(args):
     eng = api.TracerEngine(hm)
     solver = api.SSHSolver(hm, block=args.block, pc=args.pc)
     amg_levels = solver.amg_levels()
+    amg_folded = bool(api.lib().fb200_psolve_amg_folded(api._i(solver.ident))) if amg_levels else False
     eng.push_step_state()
     eng.push_tracers()
     L = api.lib()
     sol = np.zeros_like(hm["d_eta"])
 
+    # the kernel-only legs take the SSH system from HBM like every other input of the timed region (psolve accepts device pointers);
+    # the e2e leg below passes the host's arrays
+    d_vals = torch.from_numpy(np.ascontiguousarray(hm.arr("ssh_values"))).cuda()
+    d_rhs = torch.from_numpy(np.ascontiguousarray(hm.arr("ssh_rhs"))).cuda()
+    d_sol = torch.zeros(sol.size, dtype=torch.float64, device="cuda")
+
     def one_step(ev=None):
-        sol[:] = 0.0
+        d_sol.zero_()
         if ev:
             ev[0].record(stream)
-        solver.solve(new_values=1, sol=sol)
+        solver.solve_ptr(d_rhs.data_ptr(), d_vals.data_ptr(), d_sol.data_ptr(), new_values=1)
         if ev:
             ev[1].record(stream)
         eng.solve()
@@ -434,7 +445,7 @@ def run_b200(args):
         units_all = float(units_per_step)
     return dict(rank=rank, world=world, hm=hm, info=info, reduced=reduced, units_all=units_all, tra_ms=tra_ms, ssh_ms=ssh_ms,
                 tot_ms=tot_ms, t_wall=t_wall, its=its, res=res, prof=prof, e2e=e2e, e2e_ms=e2e_ms, launches=launches,
-                clocks=sampler.result(), ntr=ntr, dist=dist, amg_levels=amg_levels, parity=parity)
+                clocks=sampler.result(), ntr=ntr, dist=dist, amg_levels=amg_levels, amg_folded=amg_folded, parity=parity)
 
 
 def _cpu_worker(idx, cpu_nodes, nl, steps, warmup, barrier, out):
@@ -566,7 +577,7 @@ def main():
     rows = info["nod2D"]
     dom = max(prof.items(), key=lambda kv: kv[1][1]) if prof else None
     roof = None
-    amg_b = amg_bytes(r["amg_levels"])
+    amg_b = amg_bytes(r["amg_levels"], r["amg_folded"])
 
     def launch_bytes(name):
         if name in ALGO_BYTES:
@@ -597,7 +608,7 @@ def main():
                        "mesh_is": "global mesh" if r["world"] == 1 else "partition of rank 0", "reduced_for_host_memory": r["reduced"], "l2": "inputs larger than L2 (per-field >> 126 MB)",
                        "parallelism": "1 domain per GPU" if r["world"] == 1 else "the same global mesh in %d node partitions (%s; gen_comm.F90 halo rules), NCCL halo exchange, peer-memory or NCCL reductions" % (r["world"], info.get("partition", "?")),
                        "ssh_initial_guess": "zero every step", "setup_s": info["setup_s"],
-                       "ssh_preconditioner": ("aggregation multigrid V(1,1), levels (rows, A, P, R entries) = %s" % (r["amg_levels"],)) if args.pc == "amg"
+                       "ssh_preconditioner": ("aggregation multigrid V(1,1), %s = %s" % ("folded cycle, levels (rows, T, Q, M entries)" if r["amg_folded"] else "levels (rows, A, P, R entries)", r["amg_levels"])) if args.pc == "amg"
                        else "block-Jacobi, %d rows per block" % args.block},
             "tracer_ms_per_step": r["tra_ms"] / K,
             "ssh": {"ms_per_step": r["ssh_ms"] / K, "iterations": r["its"], "scaled_residual": r["res"], "rows": rows,

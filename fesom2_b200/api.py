@@ -25,7 +25,7 @@ EXPORTS = ["psolver_init", "psolve", "psolver_final", "fb200_psolve_info", "fb20
            "fb200_finalize", "fb200_status", "fb200_status_message", "fb200_clear_status",
            "fb200_kernel_launches", "fb200_last_ms", "fb200_set_stream", "fb200_profile", "fb200_profile_report",
            "fb200_selftest_div", "fb200_init_halo", "fb200_comm_unique_id", "fb200_comm_init", "fb200_comm_finalize", "fb200_psolver_use_graph",
-           "fb200_psolver_set_pc", "fb200_psolver_set_amg", "fb200_psolve_amg_info", "fb200_amg_host_build", "fb200_amg_host_levels",
+           "fb200_psolver_set_pc", "fb200_psolver_set_amg", "fb200_psolve_amg_info", "fb200_psolve_amg_folded", "fb200_amg_host_build", "fb200_amg_host_levels",
            "fb200_amg_host_dims", "fb200_amg_host_fetch", "fb200_amg_host_free"]
 
 
@@ -352,7 +352,7 @@ def amg_host_hierarchy(rp, ci, vals, theta=0.08, max_levels=4, min_rows=200):
     out = []
     for lev in range(L.fb200_amg_host_levels(_i(h))):
         d = {}
-        for which, nm in enumerate("APR"):
+        for which, nm in enumerate("APRMTQ"):
             nr, nc, nnz = C.c_int(), C.c_int(), C.c_int()
             L.fb200_amg_host_dims(_i(h), _i(lev), _i(which), C.byref(nr), C.byref(nc), C.byref(nnz))
             if nr.value == 0:
@@ -404,6 +404,14 @@ class SSHSolver:
         if hasattr(self.L, "fb200_status"):
             _check(self.L)
         return sol
+
+    def solve_ptr(self, rhs_ptr, vals_ptr, sol_ptr, new_values=1):
+        """psolve with raw addresses: the library takes host OR device pointers for rhs, vals and sol (unified addressing),
+        so a host that assembles the system on the device (fb200_update_stiff_mat / fb200_compute_ssh_rhs) solves without
+        crossing PCIe.  sol: in = initial guess, out = solution."""
+        self.L.psolve(_i(self.ident), C.c_void_p(rhs_ptr), C.c_void_p(vals_ptr), C.c_void_p(sol_ptr), _i(new_values))
+        if hasattr(self.L, "fb200_status"):
+            _check(self.L)
 
     def info(self):
         its = C.c_int()

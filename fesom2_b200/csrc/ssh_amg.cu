@@ -141,6 +141,65 @@ void amg_host_setup(const HostCsr& A0, const AmgParams& prm, std::vector<AmgHost
         A = csr_matmul(L.R, AP);
         L.P = std::move(P);
     }
+    if (amg_folded_on()) amg_fold_cycle(out, prm.omega);
+}
+
+// the cycle folded into M, T, Q per level (see ssh_amg.cuh)
+static void csr_drop_zeros(HostCsr& m) {
+    size_t w = 0;
+    for (int i = 0; i < m.nrow; i++) {
+        const int a = m.rp[i], b = m.rp[i + 1];
+        m.rp[i] = (int)w;
+        for (int j = a; j < b; j++) if (m.v[j] != 0.0) { m.ci[w] = m.ci[j]; m.v[w] = m.v[j]; w++; }
+    }
+    m.rp[m.nrow] = (int)w;
+    m.ci.resize(w); m.v.resize(w);
+}
+// I - diag(wl) A diag(wr)   (wl or wr empty = identity)
+static HostCsr csr_i_minus_scaled(const HostCsr& A, const std::vector<double>& wl, const std::vector<double>& wr) {
+    HostCsr S;
+    S.nrow = A.nrow; S.ncol = A.ncol; S.rp.assign(A.nrow + 1, 0);
+    S.ci.reserve(A.nnz() + A.nrow); S.v.reserve(A.nnz() + A.nrow);
+    for (int i = 0; i < A.nrow; i++) {
+        bool diag = false;
+        for (int j = A.rp[i]; j < A.rp[i + 1]; j++) {
+            const int c = A.ci[j];
+            if (!diag && c > i) { S.ci.push_back(i); S.v.push_back(1.0); diag = true; }      // rows are sorted: keep them so
+            double v = -A.v[j];
+            if (!wl.empty()) v *= wl[i];
+            if (!wr.empty()) v *= wr[c];
+            if (c == i) { v += 1.0; diag = true; }
+            S.ci.push_back(c); S.v.push_back(v);
+        }
+        if (!diag) { S.ci.push_back(i); S.v.push_back(1.0); }
+        S.rp[i + 1] = (int)S.ci.size();
+    }
+    return S;
+}
+void amg_fold_cycle(std::vector<AmgHostLevel>& lv, double omega) {
+    const std::vector<double> none;
+    for (size_t l = 0; l + 1 < lv.size(); l++) {
+        AmgHostLevel& L = lv[l];
+        const int n = L.A.nrow;
+        std::vector<double> w(n);
+        for (int i = 0; i < n; i++) w[i] = omega * L.dinv[i];
+        L.M = csr_matmul(L.R, csr_i_minus_scaled(L.A, none, w));
+        HostCsr S = csr_i_minus_scaled(L.A, w, none);
+        L.Q = csr_matmul(S, L.P);
+        if (l + 2 == lv.size()) {                                   // the coarsest level's x = W_c b_c
+            const std::vector<double>& dc = lv[l + 1].dinv;
+            for (size_t j = 0; j < L.Q.ci.size(); j++) L.Q.v[j] *= omega * dc[L.Q.ci[j]];
+        }
+        L.T = std::move(S);                                         // (I + S) W
+        for (int i = 0; i < n; i++)
+            for (int j = L.T.rp[i]; j < L.T.rp[i + 1]; j++) { const int c = L.T.ci[j]; L.T.v[j] = (L.T.v[j] + (c == i ? 1.0 : 0.0)) * w[c]; }
+        csr_drop_zeros(L.M); csr_drop_zeros(L.T); csr_drop_zeros(L.Q);
+    }
+}
+bool amg_folded_on() {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("FB200_AMG_FOLD"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on == 1;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -150,7 +209,7 @@ static const HostCsr* dbg_matrix(int handle, int level, int which) {
     auto it = g_dbg.find(handle);
     if (it == g_dbg.end() || level < 0 || level >= (int)it->second->size()) return nullptr;
     const AmgHostLevel& L = (*it->second)[level];
-    return which == 0 ? &L.A : which == 1 ? &L.P : &L.R;
+    return which == 0 ? &L.A : which == 1 ? &L.P : which == 2 ? &L.R : which == 3 ? &L.M : which == 4 ? &L.T : &L.Q;
 }
 extern "C" {
 int fb200_amg_host_build(int* n, int* rptr, int* cols, double* vals, double* theta, int* max_levels, int* min_rows) {
@@ -169,7 +228,7 @@ int fb200_amg_host_build(int* n, int* rptr, int* cols, double* vals, double* the
     return handle;
 }
 int fb200_amg_host_levels(int* handle) { auto it = g_dbg.find(*handle); return it == g_dbg.end() ? 0 : (int)it->second->size(); }
-// which: 0 A, 1 P, 2 R
+// which: 0 A, 1 P, 2 R, 3 M, 4 T, 5 Q (the folded cycle's matrices, amg_fold_cycle)
 void fb200_amg_host_dims(int* handle, int* level, int* which, int* nrow, int* ncol, int* nnz) {
     const HostCsr* m = dbg_matrix(*handle, *level, *which);
     *nrow = m ? m->nrow : 0; *ncol = m ? m->ncol : 0; *nnz = m ? (int)m->nnz() : 0;
@@ -215,20 +274,26 @@ void DevSell::upload(const HostCsr& m) {
 void Amg::upload(const std::vector<AmgHostLevel>& h, double omega_) {
     release();
     omega = omega_;
+    folded = h.size() > 1 && h[0].M.nrow > 0;
     L.resize(h.size());
     for (size_t l = 0; l < h.size(); l++) {
         AmgDevLevel& D = L[l];
         D.n = h[l].A.nrow;
+        D.dinv.upload(h[l].dinv);
+        D.b.alloc(D.n); D.x.alloc(D.n);
+        if (folded) {
+            if (h[l].M.nrow) { D.M.upload(h[l].M); D.T.upload(h[l].T); D.Q.upload(h[l].Q); }
+            continue;
+        }
         D.A.upload(h[l].A);
         if (h[l].P.nrow) { D.P.upload(h[l].P); D.R.upload(h[l].R); }
-        D.dinv.upload(h[l].dinv);
-        D.b.alloc(D.n); D.x.alloc(D.n); D.x2.alloc(D.n); D.r.alloc(D.n);
+        D.x2.alloc(D.n); D.r.alloc(D.n);
     }
 }
 
 void Amg::release() {
     for (AmgDevLevel& D : L) {
-        D.A.release(); D.P.release(); D.R.release();
+        D.A.release(); D.P.release(); D.R.release(); D.M.release(); D.T.release(); D.Q.release();
         D.dinv.release(); D.b.release(); D.x.release(); D.x2.release(); D.r.release();
     }
     L.clear();
@@ -270,6 +335,119 @@ __global__ void __launch_bounds__(ABS) k_amg_post(int n, const int* __restrict__
     if (i < n) out[i] = x[i] + omega * dinv[i] * (b[i] - sell_row(sptr, scol, sval, x, i));
 }
 
+// ---- NQ threads per row.  On the coarse levels (10^5 .. 10^3 rows, 15-30 entries per row) a thread per row is a chain of
+// 4-8 dependent (column -> x) load pairs and the kernel runs for ~10 us whatever its size (ncu launch list,
+// profiles/r02_ncu_ssh_500k_launches.txt).  Here a block of NQ warps owns one 32-row slice: warp q takes the entries
+// k = q, q + NQ, ... of every row (still one coalesced 32-entry line per load), the partial sums meet in shared memory and
+// warp 0 adds them in q order — deterministic, and each thread has at most a handful of independent loads in flight.
+enum { OP_RESID = 0, OP_RESTRICT = 1, OP_PROLONG = 2, OP_POST = 3 };
+template <int OP, int NQ>
+__global__ void __launch_bounds__(32 * NQ) k_amg_vec(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                                    const double* __restrict__ xin, const double* __restrict__ p1, const double* __restrict__ p2, double omega,
+                                                    double* __restrict__ o1, double* __restrict__ o2, const int* done) {
+    if (*done) return;
+    __shared__ double sh[NQ][32];
+    const int lane = threadIdx.x & 31, q = threadIdx.x >> 5;
+    const int s0 = sptr[blockIdx.x];
+    const int w = (sptr[blockIdx.x + 1] - s0) >> 5;
+    const int base = s0 + lane;
+    double s = 0.0;
+    int k = q;
+    for (; k + 3 * NQ < w; k += 4 * NQ) {
+        const int o = base + (k << 5);
+        const int c0 = scol[o], c1 = scol[o + 32 * NQ], c2 = scol[o + 64 * NQ], c3 = scol[o + 96 * NQ];
+        const double a0 = sval[o], a1 = sval[o + 32 * NQ], a2 = sval[o + 64 * NQ], a3 = sval[o + 96 * NQ];
+        const double x0 = xin[c0], x1 = xin[c1], x2 = xin[c2], x3 = xin[c3];
+        s += a0 * x0; s += a1 * x1; s += a2 * x2; s += a3 * x3;
+    }
+    for (; k < w; k += NQ) s += sval[base + (k << 5)] * xin[scol[base + (k << 5)]];
+    sh[q][lane] = s;
+    __syncthreads();
+    if (q != 0) return;
+    const int i = blockIdx.x * 32 + lane;
+    if (i >= n) return;
+    double v = sh[0][lane];
+#pragma unroll
+    for (int j = 1; j < NQ; j++) v += sh[j][lane];
+    if (OP == OP_RESID) o1[i] = p1[i] - v;
+    else if (OP == OP_RESTRICT) { o1[i] = v; o2[i] = omega * p1[i] * v; }
+    else if (OP == OP_PROLONG) o1[i] += v;
+    else o1[i] = xin[i] + omega * p2[i] * (p1[i] - v);
+}
+template <int OP>
+static void amg_vec_launch(int nq, int n, const DevSell& M, const double* xin, const double* p1, const double* p2, double omega, double* o1, double* o2,
+                           const int* done, cudaStream_t st) {
+    const int grid = (n + 31) / 32;
+    if (grid == 0) return;
+    if (nq == 2) k_amg_vec<OP, 2><<<grid, 64, 0, st>>>(n, M.sptr.p, M.scol.p, M.sval.p, xin, p1, p2, omega, o1, o2, done);
+    else if (nq == 4) k_amg_vec<OP, 4><<<grid, 128, 0, st>>>(n, M.sptr.p, M.scol.p, M.sval.p, xin, p1, p2, omega, o1, o2, done);
+    else k_amg_vec<OP, 8><<<grid, 256, 0, st>>>(n, M.sptr.p, M.scol.p, M.sval.p, xin, p1, p2, omega, o1, o2, done);
+}
+// threads per row on level l: FB200_AMG_NQ0 for the fine level (default 1 = the thread-per-row kernels), FB200_AMG_NQ for the others (default 4; 2, 4 and 8 measure the same, profiles/r02_c12_threads_per_row.log)
+static int amg_nq(int level) {
+    static int nq0 = -1, nqc = -1;
+    if (nq0 < 0) {
+        auto rd = [](const char* name, int dflt) { const char* e = getenv(name); const int v = e ? atoi(e) : dflt; return (v == 1 || v == 2 || v == 4 || v == 8) ? v : dflt; };
+        nq0 = rd("FB200_AMG_NQ0", 1); nqc = rd("FB200_AMG_NQ", 4);
+    }
+    return level == 0 ? nq0 : nqc;
+}
+
+// ---- folded cycle (amg_fold_cycle): one SpMV per level down, one two-matrix SpMV per level up.  Blocks of 8 warps; NQ warps share
+// a 32-row slice (warp q takes entries q, q + NQ, ... of every row), 8 / NQ slices per block.
+template <int NQ>
+__device__ __forceinline__ double sell_part(const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
+                                            const double* __restrict__ x, int slice, int lane, int q) {
+    const int s0 = sptr[slice];
+    const int w = (sptr[slice + 1] - s0) >> 5;
+    const int base = s0 + lane;
+    double s = 0.0;
+    int k = q;
+    for (; k + 3 * NQ < w; k += 4 * NQ) {
+        const int o = base + (k << 5);
+        const int c0 = scol[o], c1 = scol[o + 32 * NQ], c2 = scol[o + 64 * NQ], c3 = scol[o + 96 * NQ];
+        const double a0 = sval[o], a1 = sval[o + 32 * NQ], a2 = sval[o + 64 * NQ], a3 = sval[o + 96 * NQ];
+        const double x0 = x[c0], x1 = x[c1], x2 = x[c2], x3 = x[c3];
+        s += a0 * x0; s += a1 * x1; s += a2 * x2; s += a3 * x3;
+    }
+    for (; k < w; k += NQ) s += sval[base + (k << 5)] * x[scol[base + (k << 5)]];
+    return s;
+}
+// out = M1 x1 (+ M2 x2)
+template <int NQ, bool TWO>
+__global__ void __launch_bounds__(256) k_amg_fold(int n, const int* __restrict__ p1, const int* __restrict__ c1, const double* __restrict__ v1, const double* __restrict__ x1,
+                                                  const int* __restrict__ p2, const int* __restrict__ c2, const double* __restrict__ v2, const double* __restrict__ x2,
+                                                  double* __restrict__ out, const int* done) {
+    if (*done) return;
+    __shared__ double sh[8][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, q = warp % NQ;
+    const int slice = blockIdx.x * (8 / NQ) + warp / NQ;
+    const int nslice = (n + 31) >> 5;
+    double s = 0.0;
+    if (slice < nslice) {
+        s = sell_part<NQ>(p1, c1, v1, x1, slice, lane, q);
+        if (TWO) s += sell_part<NQ>(p2, c2, v2, x2, slice, lane, q);
+    }
+    if (NQ > 1) {
+        sh[warp][lane] = s;
+        __syncthreads();
+        if (q != 0) return;
+#pragma unroll
+        for (int j = 1; j < NQ; j++) s += sh[warp + j][lane];
+    }
+    const int i = slice * 32 + lane;
+    if (i < n) out[i] = s;
+}
+static void amg_fold_launch(int nq, int n, const DevSell& A1, const double* x1, const DevSell* A2, const double* x2, double* out, const int* done, cudaStream_t st) {
+    if (n <= 0) return;
+    const int nslice = (n + 31) / 32;
+#define FOLD_GO(NQ) do { const int g_ = (nslice + 8 / NQ - 1) / (8 / NQ); \
+        if (A2) k_amg_fold<NQ, true><<<g_, 256, 0, st>>>(n, A1.sptr.p, A1.scol.p, A1.sval.p, x1, A2->sptr.p, A2->scol.p, A2->sval.p, x2, out, done); \
+        else k_amg_fold<NQ, false><<<g_, 256, 0, st>>>(n, A1.sptr.p, A1.scol.p, A1.sval.p, x1, nullptr, nullptr, nullptr, nullptr, out, done); } while (0)
+    if (nq == 8) FOLD_GO(8); else if (nq == 4) FOLD_GO(4); else if (nq == 2) FOLD_GO(2); else FOLD_GO(1);
+#undef FOLD_GO
+}
+
 // ---- levels 1 .. K-1 of the V-cycle in ONE launch.  On a partition of a few hundred thousand rows the coarse levels hold
 // 10^5, 10^4, 10^3 rows: each of their kernels runs for a few microseconds and the cycle is bound by launch latency (8 coarse
 // launches per cycle with four levels, two cycles per BiCGStab iteration).  Here one resident grid (at most one block per SM)
@@ -294,9 +472,10 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned nblocks) {
     }
     __syncthreads();
 }
-__global__ void __launch_bounds__(ABS) k_amg_coarse_fused(AmgFusedArgs a, const int* done) {
+#define FBS 1024            // one block of 1024 threads per SM: 151 k threads cover level 1 of a 1 M-row partition with one row each
+__global__ void __launch_bounds__(FBS, 1) k_amg_coarse_fused(AmgFusedArgs a, const int* done) {
     if (*done) return;
-    const int K = a.K, stride = gridDim.x * ABS, t0 = blockIdx.x * ABS + threadIdx.x;
+    const int K = a.K, stride = gridDim.x * FBS, t0 = blockIdx.x * FBS + threadIdx.x;
     for (int l = 1; l + 1 < K; l++) {
         const AmgLvDesc& F = a.lv[l];
         const AmgLvDesc& C = a.lv[l + 1];
@@ -338,14 +517,30 @@ void Amg::cycle(double* out, const int* done, cudaStream_t st, int n_out) {
     const int K = (int)L.size();
     if (K <= 1) return;                                           // single level: the caller's Jacobi step already wrote `out`
 #define AKL(name0, namec, lev, ...) do { ProfScope ps_((lev) == 0 ? name0 : namec, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
+    if (folded) {
+        for (int l = 0; l + 1 < K; l++)                           // b_{l+1} = M_l b_l
+            AKL("k_amg_down0", "k_amg_coarse", l, amg_fold_launch(amg_nq(l + 1), L[l + 1].n, L[l].M, L[l].b.p, nullptr, nullptr, L[l + 1].b.p, done, st));
+        const double* cur = L[K - 1].b.p;                         // the coarsest level's W is inside Q_{K-2}
+        for (int l = K - 2; l >= 0; l--) {                        // x_l = T_l b_l + Q_l x_{l+1}
+            double* dst = l == 0 ? out : L[l].x.p;
+            const int rows = (l == 0 && n_out > 0) ? std::min(n_out, L[l].n) : L[l].n;
+            AKL("k_amg_up0", "k_amg_coarse", l, amg_fold_launch(amg_nq(l), rows, L[l].T, L[l].b.p, &L[l].Q, cur, dst, done, st));
+            cur = dst;
+        }
+        return;
+    }
     const bool fused = K >= 3 && K <= AMG_MAX_LEVELS && amg_fused_on();
     if (fused && !bar.p) bar.alloc(2);
     for (int l = 0; l + 1 < K; l++) {
         if (fused && l >= 1) break;
         AmgDevLevel& F = L[l];
         AmgDevLevel& C = L[l + 1];
-        AKL("k_amg_resid0", "k_amg_coarse", l, k_amg_resid<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.r.p, done));
-        AKL("k_amg_restrict0", "k_amg_coarse", l, k_amg_restrict<<<(C.n + ABS - 1) / ABS, ABS, 0, st>>>(C.n, F.R.sptr.p, F.R.scol.p, F.R.sval.p, F.r.p, C.dinv.p, omega, C.b.p, C.x.p, done));
+        // the restriction's rows are the coarse level's: its threads-per-row follow the level it writes
+        const int nq = amg_nq(l), nqr = amg_nq(l + 1);
+        if (nq > 1) AKL("k_amg_resid0", "k_amg_coarse", l, amg_vec_launch<OP_RESID>(nq, F.n, F.A, F.x.p, F.b.p, nullptr, omega, F.r.p, nullptr, done, st));
+        else AKL("k_amg_resid0", "k_amg_coarse", l, k_amg_resid<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.r.p, done));
+        if (nqr > 1) AKL("k_amg_restrict0", "k_amg_coarse", l, amg_vec_launch<OP_RESTRICT>(nqr, C.n, F.R, F.r.p, C.dinv.p, nullptr, omega, C.b.p, C.x.p, done, st));
+        else AKL("k_amg_restrict0", "k_amg_coarse", l, k_amg_restrict<<<(C.n + ABS - 1) / ABS, ABS, 0, st>>>(C.n, F.R.sptr.p, F.R.scol.p, F.R.sval.p, F.r.p, C.dinv.p, omega, C.b.p, C.x.p, done));
     }
     if (fused) {
         AmgFusedArgs a;
@@ -358,18 +553,21 @@ void Amg::cycle(double* out, const int* done, cudaStream_t st, int n_out) {
         }
         int sms = 148;
         { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-        const int grid = std::max(1, std::min(sms, (L[1].n + ABS - 1) / ABS));      // every block resident: the barrier needs it
+        const int grid = std::max(1, std::min(sms, (L[1].n + FBS - 1) / FBS));      // every block resident: the barrier needs it
         ProfScope ps_("k_amg_coarse_fused", st);
-        k_amg_coarse_fused<<<grid, ABS, 0, st>>>(a, done);
+        k_amg_coarse_fused<<<grid, FBS, 0, st>>>(a, done);
         LAUNCH_CHECK();
     }
     const double* cur = fused ? L[1].x2.p : L[K - 1].x.p;
     for (int l = fused ? 0 : K - 2; l >= 0; l--) {
         AmgDevLevel& F = L[l];
         double* dst = l == 0 ? out : F.x2.p;
-        AKL("k_amg_prolong0", "k_amg_coarse", l, k_amg_prolong<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.P.sptr.p, F.P.scol.p, F.P.sval.p, cur, F.x.p, done));
+        const int nq = amg_nq(l);
+        if (nq > 1) AKL("k_amg_prolong0", "k_amg_coarse", l, amg_vec_launch<OP_PROLONG>(nq, F.n, F.P, cur, nullptr, nullptr, omega, F.x.p, nullptr, done, st));
+        else AKL("k_amg_prolong0", "k_amg_coarse", l, k_amg_prolong<<<(F.n + ABS - 1) / ABS, ABS, 0, st>>>(F.n, F.P.sptr.p, F.P.scol.p, F.P.sval.p, cur, F.x.p, done));
         const int npost = (l == 0 && n_out > 0) ? std::min(n_out, F.n) : F.n;
-        AKL("k_amg_post0", "k_amg_coarse", l, k_amg_post<<<(npost + ABS - 1) / ABS, ABS, 0, st>>>(npost, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.dinv.p, omega, dst, done));
+        if (nq > 1) AKL("k_amg_post0", "k_amg_coarse", l, amg_vec_launch<OP_POST>(nq, npost, F.A, F.x.p, F.b.p, F.dinv.p, omega, dst, nullptr, done, st));
+        else AKL("k_amg_post0", "k_amg_coarse", l, k_amg_post<<<(npost + ABS - 1) / ABS, ABS, 0, st>>>(npost, F.A.sptr.p, F.A.scol.p, F.A.sval.p, F.b.p, F.x.p, F.dinv.p, omega, dst, done));
         cur = dst;
     }
 #undef AKL

@@ -22,6 +22,7 @@ struct HostCsr {
 struct AmgHostLevel {
     HostCsr A, P, R;                 // P: nrow(A) x n_coarse, R = P^T; both empty on the coarsest level
     std::vector<double> dinv;        // 1 / diag(A)
+    HostCsr M, T, Q;                 // the V(1,1) cycle's steps on this level folded into three matrices (amg_fold_cycle); empty on the coarsest level
 };
 struct AmgParams {
     double theta = 0.08;             // strength-of-connection threshold
@@ -31,6 +32,15 @@ struct AmgParams {
 };
 // pure host code (no CUDA call): usable from the CPU tests through fb200_amg_host_*
 void amg_host_setup(const HostCsr& A0, const AmgParams& prm, std::vector<AmgHostLevel>& out);
+// With damped-Jacobi smoothing from a zero guess every step of the V(1,1) cycle is linear in the level's right-hand side b, and
+// consecutive steps can be multiplied out once on the host (W = omega D^-1, S = I - W A):
+//   down   b_c = R (b - A W b)                          = M b        M = R (I - A W)
+//   up     x   = S (W b + P x_c) + W b                  = T b + Q x_c  T = (I + S) W,  Q = S P
+//   coarsest x = W b  — folded into the Q of the level above (Q <- Q W_c).
+// Same operator as the step-by-step cycle up to rounding; 2 (K-1) kernels per cycle instead of 4 (K-1), no intermediate vectors,
+// and M + T + Q hold fewer entries than 2 A + P + R.
+void amg_fold_cycle(std::vector<AmgHostLevel>& lv, double omega);
+bool amg_folded_on();               // default on; FB200_AMG_FOLD=0 keeps the step-by-step kernels
 
 struct DevSell {                     // sliced ELL, slice = 32 rows: val[sptr[s] + k*32 + lane]
     int nrow = 0, nslice = 0;
@@ -42,13 +52,15 @@ struct DevSell {                     // sliced ELL, slice = 32 rows: val[sptr[s]
 };
 struct AmgDevLevel {
     int n = 0;
-    DevSell A, P, R;
+    DevSell A, P, R;                 // step-by-step cycle
+    DevSell M, T, Q;                 // folded cycle (only one of the two sets is uploaded)
     DevBuf<double> dinv, b, x, x2, r;
 };
 struct Amg {
     std::vector<AmgDevLevel> L;
     DevBuf<unsigned> bar;            // grid barrier of the fused coarse-level kernel
     double omega = 0.8;
+    bool folded = false;
     bool ready() const { return !L.empty(); }
     int levels() const { return (int)L.size(); }
     void upload(const std::vector<AmgHostLevel>& h, double omega_);

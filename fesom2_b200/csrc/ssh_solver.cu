@@ -27,7 +27,8 @@ struct SolverScal {             // device-resident scalars
     double alpha, sigma, beta, rho, rho_alt, omega, tol2;
     double tmp0, tmp1;
     int done, its, maxits, comm_error;
-    unsigned long long red_seq, halo_seq[4];       // peer-memory transport: sequence numbers of the reductions / of the pushes of x, pt, st and of the V-cycle's right-hand side
+    unsigned long long epoch;                      // number of this psolve call (host-written, the same on every rank): high half of the interface tags
+    unsigned long long red_seq;                    // peer-memory transport: sequence number of the reductions (lives on across calls)
 };
 
 // Peer-memory transport of the solver's small messages (comm.cuh: PeerBuf).  Every rank owns one control buffer
@@ -36,9 +37,9 @@ struct SolverScal {             // device-resident scalars
 //                                 form bitwise the same sums and take the same decisions.  Slot k & 3 is reused by reduction
 //                                 k + 4, which a rank can only reach after every peer has contributed to k + 1 .. k + 3, i.e.
 //                                 after every peer has finished reading reduction k.
-//   u64     flags[4][nranks]      interface values: k_flat_push writes this rank's send list straight into the tails of the
-//                                 peers' vectors (x, pt or st), then its sequence number into flags[vec][me] of each peer; the
-//                                 consuming SpMV waits for the flags of its source ranks.  The reductions between two pushes
+//   u64     flags[4][nranks]      interface values: the head of the consuming kernel (push_and_wait) writes this rank's send list straight
+//                                 into the tails of the peers' vectors (x, pt, st, the V-cycle's b0), then the exchange's tag into
+//                                 flags[vec][me] of each peer, and waits for the flags of its own source ranks.  The reductions between two pushes
 //                                 of the same vector order the next push after the peers' reads (see psolve).
 struct RedSlot { double a, b; unsigned long long seq, pad; };
 struct PeerCtl {                // by value into the kernels.  mode 0: one rank; 1: NCCL all-reduce + k_apply_scalars; 2: peer memory
@@ -50,15 +51,46 @@ struct PeerCtl {                // by value into the kernels.  mode 0: one rank;
 #define SPIN_LIMIT_CYCLES 4000000000ll          // ~2 s: a peer that never arrives raises comm_error instead of hanging the GPU
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) { return *(const volatile unsigned long long*)p; }
 __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) { *(volatile unsigned long long*)p = v; }
-// block-level wait for the interface values of vector `vec` (0 x, 1 pt, 2 st): call at the top of the consuming kernel
-__device__ __forceinline__ void wait_halo(const PeerCtl& pc, SolverScal* sc, int vec) {
+// Interface values over peer memory, fused into the CONSUMING kernel (no launch of its own).  The first `npb` blocks of the
+// kernel write this rank's send list straight into the tails of the peers' vectors, the last of them to finish publishes the
+// tag of this exchange in flags[vec][me] of every destination rank; then every block waits until the flags of its source ranks
+// have reached the tag.  A tag is (psolve call number << 32) + a counter derived from the iteration number, which every rank
+// knows without communication and which never decreases.  Pushing comes before waiting in every block, so two ranks waiting
+// for each other always have their pushes under way; the pushing blocks are the lowest-numbered ones and are scheduled first.
+struct PushArgs {
+    int count, ndst, npb, nsrc;         // entries to send, destination ranks, pushing blocks (0: nothing to send), source ranks
+    const int *slist, *s_peer, *s_dst, *dst_ranks, *src;
+    double* const* peer_vec;            // [nranks] base of the peers' copies of the exchanged vector
+    unsigned* counter;
+};
+// vec 0 x (initial guess), 1 pt, 2 st: once per iteration.  vec 3, the V-cycle's right-hand side on the overlap rows: first apply (mode 0),
+// then per iteration mode 1 (its = k) and mode 2 (its = k + 1)  ->  1, 2, 3, 5, 6, 8, 9 ...
+__device__ __forceinline__ unsigned long long halo_tag(const SolverScal* sc, int vec, int mode) {
+    const unsigned long long its = (unsigned long long)sc->its;
+    const unsigned long long k = vec != 3 ? its + 1 : (mode == 0 ? 1ull : mode == 1 ? 3 * its + 2 : 3 * its);
+    return (sc->epoch << 32) + k;
+}
+__device__ __forceinline__ void push_and_wait(const PushArgs& pa, const double* x, const PeerCtl& pc, SolverScal* sc, int vec, int mode) {
     if (pc.mode != 2) return;
+    const unsigned long long tag = halo_tag(sc, vec, mode);
+    __shared__ bool last;
+    if ((int)blockIdx.x < pa.npb) {
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < pa.count; i += pa.npb * blockDim.x) pa.peer_vec[pa.s_peer[i]][pa.s_dst[i]] = x[pa.slist[i]];
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) last = atomicAdd(pa.counter, 1u) == (unsigned)pa.npb - 1;
+        __syncthreads();
+        if (last) {
+            if (threadIdx.x == 0) *pa.counter = 0;
+            __threadfence_system();
+            if ((int)threadIdx.x < pa.ndst) st_volatile_u64(pc.flags[pa.dst_ranks[threadIdx.x]] + (size_t)vec * pc.nranks + pc.me, tag);
+        }
+    }
     if (threadIdx.x == 0) {
-        const unsigned long long want = sc->halo_seq[vec];
         const unsigned long long* f = pc.flags[pc.me] + (size_t)vec * pc.nranks;
         const long long t0 = clock64();
-        for (int k = 0; k < pc.nsrc; k++)
-            while (ld_volatile_u64(f + pc.src[k]) < want) if (clock64() - t0 > SPIN_LIMIT_CYCLES) { sc->comm_error = 1; break; }
+        for (int k = 0; k < pa.nsrc; k++)
+            while (ld_volatile_u64(f + pa.src[k]) < tag) if (clock64() - t0 > SPIN_LIMIT_CYCLES) { sc->comm_error = 1; break; }
         __threadfence_system();
     }
     __syncthreads();
@@ -81,7 +113,7 @@ struct Solver {
     Amg amg; AmgParams amg_prm;
     int last_its = 0; double last_res = 0.0;
     SolverScal* h_scal = nullptr;            // pinned mirror of the device scalars (convergence polling)
-    cudaGraphExec_t graph = nullptr;         // `poll` BiCGStab iterations captured once (kernels + NCCL), replayed per poll
+    cudaGraphExec_t graph = nullptr; bool graph_while = false; unsigned long long epoch = 0;         // `poll` BiCGStab iterations captured once (kernels + NCCL), replayed per poll
     cudaStream_t graph_stream = nullptr; int graph_multi = -1, graph_launches = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -223,8 +255,8 @@ __device__ __forceinline__ double bj_row(const double* __restrict__ binv, const 
 __global__ void __launch_bounds__(SBS) k_init_res(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                   const double* __restrict__ rhs, const double* __restrict__ scale, const double* __restrict__ x,
                                                   double* __restrict__ y, double* __restrict__ r, double* __restrict__ p,
-                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc) {
-    wait_halo(pc, sc, 0);                                // interface values of the initial guess
+                                                  double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc, PushArgs pa) {
+    push_and_wait(pa, x, pc, sc, 0, 0);                  // interface values of the initial guess
     double a = 0.0, b = 0.0;
     for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) {
         const double yi = rhs[i] * scale[i];
@@ -243,9 +275,9 @@ __global__ void __launch_bounds__(SBS) k_pc(int n, int bs, const double* __restr
 // v = A pt ; alpha = rho / (r0 . v)                                        bicgstab_ras.c:161-164
 __global__ void __launch_bounds__(SBS) k_spmv_alpha(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                     const double* __restrict__ pt, const double* __restrict__ r0, double* __restrict__ v,
-                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc) {
+                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc, PushArgs pa) {
     if (sc->done) return;
-    wait_halo(pc, sc, 1);
+    push_and_wait(pa, pt, pc, sc, 1, 0);
     double a = 0.0;
     for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) { const double vi = sell_row(sptr, scol, sval, pt, i); v[i] = vi; a += r0[i] * vi; }
     reduce2(a, 0.0, partial, counter, nblocks, sc, SC_ALPHA, pc);
@@ -264,9 +296,9 @@ __global__ void __launch_bounds__(SBS) k_r_update_pc(int n, int bs, const double
 // t = A st ; sigma = (t.r)/(t.t)                                            bicgstab_ras.c:179-197
 __global__ void __launch_bounds__(SBS) k_spmv_sigma(int n, const int* __restrict__ sptr, const int* __restrict__ scol, const double* __restrict__ sval,
                                                     const double* __restrict__ st, const double* __restrict__ r, double* __restrict__ t,
-                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc) {
+                                                    double* partial, unsigned* counter, int nblocks, SolverScal* sc, PeerCtl pc, PushArgs pa) {
     if (sc->done) return;
-    wait_halo(pc, sc, 2);
+    push_and_wait(pa, st, pc, sc, 2, 0);
     double a = 0.0, b = 0.0;
     for (int i = blockIdx.x * SBS + threadIdx.x; i < n; i += gridDim.x * SBS) { const double ti = sell_row(sptr, scol, sval, st, i); t[i] = ti; a += ti * r[i]; b += ti * ti; }
     reduce2(a, b, partial, counter, nblocks, sc, SC_SIGMA, pc);
@@ -286,28 +318,19 @@ __global__ void __launch_bounds__(SBS) k_x_update(int n, const double* __restric
     }
     reduce2(a, b, partial, counter, nblocks, sc, SC_XUPD, pc);
 }
-// interface values of vector `vec` (0 x, 1 pt, 2 st) written straight into the peers' copies of that vector (their tails hold
-// the off-partition columns), then the new sequence number into the peers' flag arrays.  check_done: skipped once converged.
-__global__ void __launch_bounds__(SBS) k_flat_push(int count, const int* __restrict__ slist, const int* __restrict__ s_peer, const int* __restrict__ s_dst,
-                                                   const double* __restrict__ x, double* const* __restrict__ peer_vec, int ndst, const int* __restrict__ dst_ranks,
-                                                   unsigned* counter, SolverScal* sc, PeerCtl pc, int vec, int check_done) {
-    if (check_done && sc->done) return;
-    const int i = blockIdx.x * SBS + threadIdx.x;
-    if (i < count) peer_vec[s_peer[i]][s_dst[i]] = x[slist[i]];
-    __threadfence_system();
-    __shared__ bool last;
-    __syncthreads();
-    if (threadIdx.x == 0) last = atomicAdd(counter, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!last) return;
-    __shared__ unsigned long long sseq;
-    if (threadIdx.x == 0) { *counter = 0; sseq = sc->halo_seq[vec] + 1; sc->halo_seq[vec] = sseq; }
-    __syncthreads();
-    __threadfence_system();
-    if ((int)threadIdx.x < ndst) st_volatile_u64(pc.flags[dst_ranks[threadIdx.x]] + (size_t)vec * pc.nranks + pc.me, sseq);
+// restricted additive Schwarz, peer-memory transport: the V-cycle's right-hand side of this rank's rows goes to the ranks whose
+// subdomains overlap them, the overlap rows of this rank arrive from their owners, and their pre-smoothing step from a zero
+// guess x0 = omega dinv b0 follows — push, wait and the step in one launch
+__global__ void __launch_bounds__(SBS) k_overlap_rhs(PushArgs pa, PeerCtl pc, SolverScal* sc, int mode, int n, int nE, const double* __restrict__ dinv0,
+                                                     double omega, double* b0, double* __restrict__ x0) {
+    if (sc->done) return;
+    push_and_wait(pa, b0, pc, sc, 3, mode);
+    for (int i = n + blockIdx.x * SBS + threadIdx.x; i < nE; i += gridDim.x * SBS) x0[i] = omega * dinv0[i] * __ldcg(b0 + i);
 }
-// consumers outside this file (the fine-level kernels of the V-cycle) wait through this one-block kernel, launched right after the push
-__global__ void k_wait_halo(SolverScal* sc, PeerCtl pc, int vec) { if (!sc->done) wait_halo(pc, sc, vec); }
+#ifndef FB200_EMULATION
+// loop condition of the while-node that holds one BiCGStab iteration: again unless converged (or out of iterations: `done` covers both)
+__global__ void k_loop_cond(cudaGraphConditionalHandle h, const SolverScal* sc) { cudaGraphSetConditional(h, sc->done ? 0u : 1u); }
+#endif
 // p = r + beta (p - sigma v) ; pt = M p                                     bicgstab_ras.c:227-230, 150-156
 __global__ void __launch_bounds__(SBS) k_p_update_pc(int n, int bs, const double* __restrict__ binv, const double* __restrict__ r, const double* __restrict__ v,
                                                      double* __restrict__ p, double* __restrict__ pt, SolverScal* sc) {
@@ -339,7 +362,7 @@ __global__ void __launch_bounds__(SBS) k_amg_enter(int n, const double* __restri
     else { in = r[i] + sc->beta * (p[i] - sc->sigma * v[i]); p[i] = in; }
     const double b = in / scale[i];
     b0[i] = b;
-    x0[i] = omega * dinv0[i] * b;
+    if (x0) x0[i] = omega * dinv0[i] * b;                    // the folded cycle starts from b0 alone
 }
 
 // pre-smoothing step x0 = omega dinv b0 on the overlap rows (their b0 has just arrived from the owners)
@@ -485,7 +508,7 @@ static void build_amg_overlap(Solver& S, const int* part, const int* gcols_of_en
 }
 
 static void upload_values(Solver& S, const double* vals) {
-    CUDA_CHECK(cudaMemcpyAsync(S.d_vals.p, vals, (size_t)S.nnz * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+    CUDA_CHECK(cudaMemcpyAsync(S.d_vals.p, vals, (size_t)S.nnz * sizeof(double), cudaMemcpyDefault, S.stream));   // host or device pointer
     { ProfScope ps_("k_scale_rows", S.stream); k_scale_rows<<<S.nblocks, SBS, 0, S.stream>>>(S.n, S.d_rp.p, S.d_vals.p, S.d_sptr.p, S.d_sval.p, S.d_scale.p); LAUNCH_CHECK(); }
 }
 
@@ -522,8 +545,11 @@ void fb200_psolve_amg_info(int* id, int* level, int* rows, long long* a_entries,
     auto it = g_solvers.find(*id);
     if (it == g_solvers.end() || *level < 0 || *level >= it->second->amg.levels()) return;
     const AmgDevLevel& D = it->second->amg.L[*level];
-    *rows = D.n; *a_entries = (long long)D.A.entries; *p_entries = (long long)D.P.entries; *r_entries = (long long)D.R.entries;
+    const bool f = it->second->amg.folded;                   // folded cycle: the matrices it streams are T, Q, M in place of A, P, R
+    *rows = D.n; *a_entries = (long long)(f ? D.T.entries : D.A.entries); *p_entries = (long long)(f ? D.Q.entries : D.P.entries);
+    *r_entries = (long long)(f ? D.M.entries : D.R.entries);
 }
+int fb200_psolve_amg_folded(int* id) { auto it = g_solvers.find(*id); return it != g_solvers.end() && it->second->amg.folded ? 1 : 0; }
 
 // which rows of this rank the other ranks need, and which columns of theirs this rank needs: the interface-variable
 // setup of parms_MatSetup (lib/parms/src/parms_mat_dvcsr.c:93-600).  Requests travel as ints over NCCL.
@@ -721,10 +747,10 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
         }
         else fprintf(stderr, "ERROR: matrix data is static\n");          // psolve.c:203
     }
-    CUDA_CHECK(cudaMemcpyAsync(S.rhs.p, rhs, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
-    CUDA_CHECK(cudaMemcpyAsync(S.x.p, sol, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(S.rhs.p, rhs, (size_t)n * sizeof(double), cudaMemcpyDefault, st));        // rhs, vals, sol: host or device pointers (unified addressing)
+    CUDA_CHECK(cudaMemcpyAsync(S.x.p, sol, (size_t)n * sizeof(double), cudaMemcpyDefault, st));
     SolverScal h; memset(&h, 0, sizeof(h));
-    h.tol2 = S.soltol * S.soltol; h.maxits = S.maxits;
+    h.tol2 = S.soltol * S.soltol; h.maxits = S.maxits; h.epoch = ++S.epoch;
     CUDA_CHECK(cudaMemcpyAsync(S.scal.p, &h, offsetof(SolverScal, red_seq), cudaMemcpyHostToDevice, st));   // the sequence numbers live on
     const int multi = comm_nranks() > 1 ? S.comm_mode : 0;
     const PeerCtl pc = S.pctl;
@@ -732,26 +758,26 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     // transport: the last block of the producing kernel has already done both
 #define REDUCE(which) do { if (multi == 1) { { ProfScope ps_("nccl_allreduce", st); comm_allreduce_sum(&S.scal.p->tmp0, 2, st); } \
                                              { ProfScope ps_("k_apply_scalars", st); k_apply_scalars<<<1, 1, 0, st>>>(S.scal.p, which); LAUNCH_CHECK(); } } } while (0)
-    // vec 0 x, 1 pt, 2 st: interface values of an SpMV input (parms_MatVec); vec 3: the V-cycle's right-hand side on the overlap rows
-    auto exchange = [&](int vec, double* xv, int check_done) {
+    // vec 0 x, 1 pt, 2 st: interface values of an SpMV input (parms_MatVec); vec 3: the V-cycle's right-hand side on the overlap rows.
+    // NCCL transport: pack / send-recv / unpack before the consumer.  Peer-memory transport: nothing here, the consumer pushes and waits
+    // itself (push_args below).
+    auto exchange = [&](int vec, double* xv) {
+        if (multi == 1) { ProfScope ps_(vec == 3 ? "overlap_exchange" : "halo_exchange_flat", st); halo_exchange_flat(vec == 3 ? S.ovl : S.halo, xv, st); }
+    };
+    auto push_args = [&](int vec, int grid) {
+        PushArgs a; memset(&a, 0, sizeof(a));
+        if (multi != 2) return a;
         HaloPlan& H = vec == 3 ? S.ovl : S.halo;
         Solver::PushPlan& P = vec == 3 ? S.ovp : S.ifc;
-        if (multi == 1) { ProfScope ps_(vec == 3 ? "overlap_exchange" : "halo_exchange_flat", st); halo_exchange_flat(H, xv, st); }
-        else if (multi == 2) {
-            ProfScope ps_("k_flat_push", st);
-            const int cnt = H.nsend();
-            k_flat_push<<<std::max(1, (cnt + SBS - 1) / SBS), SBS, 0, st>>>(cnt, H.slist.p, P.s_peer.p, P.s_dst.p, xv, (double* const*)S.pv[vec].d_peer.p,
-                                                                       H.nsp, P.dst_ranks.p, S.push_counter.p, S.scal.p, pc, vec, check_done);
-            LAUNCH_CHECK();
-            if (vec == 3) {                                       // the consumers are the cycle's kernels: wait in a one-block kernel
-                PeerCtl po = pc; po.nsrc = P.nsrc; po.src = P.src_ranks.p;
-                k_wait_halo<<<1, 32, 0, st>>>(S.scal.p, po, vec); LAUNCH_CHECK();
-            }
-        }
+        a.count = H.nsend(); a.ndst = H.nsp; a.nsrc = P.nsrc;
+        a.npb = a.count > 0 ? std::max(1, std::min(std::min(grid, 16), (a.count + SBS - 1) / SBS)) : 0;
+        a.slist = H.slist.p; a.s_peer = P.s_peer.p; a.s_dst = P.s_dst.p; a.dst_ranks = P.dst_ranks.p; a.src = P.src_ranks.p;
+        a.peer_vec = (double* const*)S.pv[vec].d_peer.p; a.counter = S.push_counter.p;
+        return a;
     };
-    exchange(0, S.x.p, 0);                                                       // interface values of the initial guess
+    exchange(0, S.x.p);                                                       // interface values of the initial guess
     { ProfScope ps_("k_init_res", st); k_init_res<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.rhs.p, S.d_scale.p, S.x.p, S.y.p, S.r.p, S.p.p,
-                                   S.partial.p, S.counter.p, nr, S.scal.p, pc); LAUNCH_CHECK(); }
+                                   S.partial.p, S.counter.p, nr, S.scal.p, pc, push_args(0, nr)); LAUNCH_CHECK(); }
     REDUCE(SC_INIT);
     const bool amg = S.pc == 1;
     const int* donep = &S.scal.p->done;
@@ -759,11 +785,17 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
 #define AMG_APPLY(MODE, name, out) do { \
         AmgDevLevel& L0 = S.amg.L[0]; \
         { ProfScope ps_(name, st); k_amg_enter<MODE><<<nb, SBS, 0, st>>>(n, S.d_scale.p, L0.dinv.p, S.amg.omega, S.v.p, S.r.p, S.p.p, L0.b.p, \
-                                                   S.amg.levels() > 1 ? L0.x.p : (out), S.scal.p); LAUNCH_CHECK(); } \
+                                                   S.amg.levels() > 1 ? (S.amg.folded ? nullptr : L0.x.p) : (out), S.scal.p); LAUNCH_CHECK(); } \
         if (S.overlap > 0 && S.amg.levels() > 1) {              /* right-hand side of the overlap rows from their owners, their pre-smoothing step here */ \
-            exchange(3, L0.b.p, 1); \
-            const int nt_ = S.nE - n; \
-            if (nt_ > 0) { ProfScope ps_("k_amg_tail", st); k_amg_tail<<<(nt_ + SBS - 1) / SBS, SBS, 0, st>>>(n, S.nE, L0.dinv.p, S.amg.omega, L0.b.p, L0.x.p, S.scal.p); LAUNCH_CHECK(); } \
+            const int nt_ = S.amg.folded ? 0 : S.nE - n;                 /* the folded cycle needs no x0 on the overlap rows */ \
+            if (multi == 2) { \
+                const int g_ = std::max(1, std::min(64, std::max((S.ovl.nsend() + SBS - 1) / SBS, (nt_ + SBS - 1) / SBS))); \
+                ProfScope ps_("k_overlap_rhs", st); \
+                k_overlap_rhs<<<g_, SBS, 0, st>>>(push_args(3, g_), pc, S.scal.p, MODE, n, n + nt_, L0.dinv.p, S.amg.omega, L0.b.p, L0.x.p); LAUNCH_CHECK(); \
+            } else { \
+                exchange(3, L0.b.p); \
+                if (nt_ > 0) { ProfScope ps_("k_amg_tail", st); k_amg_tail<<<(nt_ + SBS - 1) / SBS, SBS, 0, st>>>(n, S.nE, L0.dinv.p, S.amg.omega, L0.b.p, L0.x.p, S.scal.p); LAUNCH_CHECK(); } \
+            } \
         } \
         S.amg.cycle(out, donep, st, n); } while (0)
     if (amg) AMG_APPLY(0, "k_amg_enter", S.pt.p);
@@ -773,13 +805,13 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     if (!S.h_scal) CUDA_CHECK(cudaMallocHost(&S.h_scal, sizeof(SolverScal)));
     SolverScal* hs = S.h_scal;
     auto iteration = [&]() {
-        exchange(1, S.pt.p, 1);                                                  // parms_MatVec: interface exchange of the SpMV input
-        { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nr, S.scal.p, pc); LAUNCH_CHECK(); }
+        exchange(1, S.pt.p);                                                     // parms_MatVec: interface exchange of the SpMV input
+        { ProfScope ps_("k_spmv_alpha", st); k_spmv_alpha<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.pt.p, S.y.p, S.v.p, S.partial.p, S.counter.p, nr, S.scal.p, pc, push_args(1, nr)); LAUNCH_CHECK(); }
         REDUCE(SC_ALPHA);
         if (amg) AMG_APPLY(1, "k_amg_enter", S.st.p);
         else { ProfScope ps_("k_r_update_pc", st); k_r_update_pc<<<nb, SBS, 0, st>>>(n, S.bs, S.d_binv.p, S.v.p, S.r.p, S.st.p, S.scal.p); LAUNCH_CHECK(); }
-        exchange(2, S.st.p, 1);
-        { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nr, S.scal.p, pc); LAUNCH_CHECK(); }
+        exchange(2, S.st.p);
+        { ProfScope ps_("k_spmv_sigma", st); k_spmv_sigma<<<nr, SBS, 0, st>>>(n, S.d_sptr.p, S.d_scol.p, S.d_sval.p, S.st.p, S.r.p, S.t.p, S.partial.p, S.counter.p, nr, S.scal.p, pc, push_args(2, nr)); LAUNCH_CHECK(); }
         REDUCE(SC_SIGMA);
         { ProfScope ps_("k_x_update", st); k_x_update<<<nr, SBS, 0, st>>>(n, S.t.p, S.pt.p, S.st.p, S.y.p, S.r.p, S.x.p, S.partial.p, S.counter.p, nr, S.scal.p, pc); LAUNCH_CHECK(); }
         REDUCE(SC_XUPD);
@@ -791,7 +823,35 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     // no-ops (every kernel returns on sc->done).  Per-kernel profiling uses plain launches.
     const bool use_graph = !prof_on() && g_use_graph;
     if (use_graph && S.graph && (S.graph_stream != st || S.graph_multi != multi)) { cudaGraphExecDestroy(S.graph); S.graph = nullptr; }
+#ifndef FB200_EMULATION
+    // Without NCCL in the loop the iterations run as the body of a conditional WHILE node: the device decides after every
+    // iteration whether another one follows, so no converged (no-op) iterations are replayed and the host synchronises once.
+    static const bool while_ok = [] { const char* e = getenv("FB200_SSH_WHILE"); return !(e && e[0] == '0'); }();
+    if (use_graph && !S.graph && multi != 1 && while_ok) {
+        cudaGraph_t g = nullptr;
+        CUDA_CHECK(cudaGraphCreate(&g, 0));
+        cudaGraphConditionalHandle hc;
+        CUDA_CHECK(cudaGraphConditionalHandleCreate(&hc, g, 1, cudaGraphCondAssignDefault));
+        cudaGraphNodeParams np_ = { cudaGraphNodeTypeConditional };
+        np_.type = cudaGraphNodeTypeConditional;
+        np_.conditional.handle = hc; np_.conditional.type = cudaGraphCondTypeWhile; np_.conditional.size = 1;
+        cudaGraphNode_t node;
+        CUDA_CHECK(cudaGraphAddNode(&node, g, nullptr, 0, &np_));
+        cudaGraph_t body = np_.conditional.phGraph_out[0];
+        CUDA_CHECK(cudaStreamBeginCaptureToGraph(st, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+        const long long l0 = g_launches;
+        iteration();
+        k_loop_cond<<<1, 1, 0, st>>>(hc, S.scal.p); LAUNCH_CHECK();
+        S.graph_launches = (int)(g_launches - l0); g_launches = l0;
+        cudaGraph_t got = nullptr;
+        CUDA_CHECK(cudaStreamEndCapture(st, &got));
+        if (fb_ok()) CUDA_CHECK(cudaGraphInstantiate(&S.graph, g, 0));
+        cudaGraphDestroy(g);
+        S.graph_stream = st; S.graph_multi = multi; S.graph_while = true;
+    }
+#endif
     if (use_graph && !S.graph) {
+        S.graph_while = false;
         cudaGraph_t g = nullptr;
         CUDA_CHECK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
         const long long l0 = g_launches;
@@ -802,11 +862,13 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
         S.graph_stream = st; S.graph_multi = multi;
     }
     while (!done && launched < S.maxits && fb_ok()) {
-        if (use_graph && S.graph) { CUDA_CHECK(cudaGraphLaunch(S.graph, st)); g_launches += S.graph_launches; launched += poll; }
+        const bool wh = use_graph && S.graph && S.graph_while;
+        if (use_graph && S.graph) { CUDA_CHECK(cudaGraphLaunch(S.graph, st)); if (!wh) { g_launches += S.graph_launches; launched += poll; } }
         else for (int k = 0; k < poll && launched < S.maxits; k++, launched++) iteration();
         CUDA_CHECK(cudaMemcpyAsync(hs, S.scal.p, sizeof(SolverScal), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
         done = hs->done;
+        if (wh) { const int ran = std::max(1, hs->its - launched); g_launches += (long long)S.graph_launches * ran; launched += ran; }
     }
 #undef REDUCE
 #undef AMG_APPLY
@@ -815,7 +877,7 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
         if (hs->comm_error) fb_set_error(48, "psolve: a peer rank did not deliver its reduction / interface values within the spin limit (peer-memory transport)");
         if (hs->its >= S.maxits && hs->omega > h.tol2) printf("ERROR: no convergence\n");   // bicgstab_ras.c:237-238
     }
-    CUDA_CHECK(cudaMemcpyAsync(sol, S.x.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(sol, S.x.p, (size_t)n * sizeof(double), cudaMemcpyDefault, st));
     CUDA_CHECK(cudaEventRecord(S.ev1, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
     if (fb_ok()) CUDA_CHECK(cudaEventElapsedTime(&g_ssh_ms, S.ev0, S.ev1));

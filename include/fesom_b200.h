@@ -52,6 +52,10 @@ void fb200_psolver_set_pc(int* kind);
 void fb200_psolver_set_amg(double* theta, double* omega, int* max_levels, int* min_rows);
 /* rows and stored sliced-ELL entries of A_l, P_l, R_l of the hierarchy of solver id (rows = 0 past the last level) */
 void fb200_psolve_amg_info(int* id, int* level, int* rows, long long* a_entries, long long* p_entries, long long* r_entries);
+/* 1 when solver *id applies the FOLDED cycle (default; FB200_AMG_FOLD=0 keeps the step-by-step kernels): per level one SpMV down
+ * (M = R (I - A W)) and one two-matrix SpMV up (T = (I + S) W, Q = S P; W = omega D^-1, S = I - W A) instead of residual /
+ * restriction / prolongation / smoothing; fb200_psolve_amg_info then reports the stored entries of T, Q, M in place of A, P, R. */
+int fb200_psolve_amg_folded(int* id);
 /* host-only access to the multigrid setup for CPU tests (no CUDA call): build a hierarchy from a 0-based CSR matrix,
  * read level `level`'s matrix `which` (0 A, 1 P, 2 R) back as CSR, free it */
 int fb200_amg_host_build(int* n, int* rptr, int* cols, double* vals, double* theta, int* max_levels, int* min_rows);

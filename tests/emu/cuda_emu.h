@@ -41,7 +41,7 @@ typedef int cudaError_t;
 typedef struct emu_stream_* cudaStream_t;
 typedef struct emu_event_* cudaEvent_t;
 enum { cudaSuccess = 0 };
-enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice, cudaMemcpyHostToHost };
+enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice, cudaMemcpyHostToHost, cudaMemcpyDefault };
 enum { cudaEventDisableTiming = 2, cudaStreamNonBlocking = 1, cudaFuncAttributeMaxDynamicSharedMemorySize = 8, cudaHostRegisterDefault = 0 };
 template <class T> static inline cudaError_t cudaMalloc(T** p, size_t n) { *p = (T*)malloc(n ? n : 1); return *p ? 0 : 2; }
 static inline cudaError_t cudaFree(void* p) { free(p); return 0; }

@@ -112,3 +112,34 @@ def test_multigrid_iterations_are_mesh_independent():
         assert res < 1e-10
         counts.append(its)
     assert max(counts) <= 20 and counts[-1] <= counts[0] + 6, counts
+
+
+def folded_cycle(H, lev, b):
+    """the cycle as the device applies it by default (ssh_amg.cuh amg_fold_cycle): b_c = M b down, x = T b + Q x_c up; the coarsest
+    level's damped-Jacobi step sits inside the Q of the level above"""
+    if "M" not in H[lev + 1]:
+        return H[lev]["T"] @ b + H[lev]["Q"] @ (H[lev]["M"] @ b)
+    return H[lev]["T"] @ b + H[lev]["Q"] @ folded_cycle(H, lev + 1, H[lev]["M"] @ b)
+
+
+@pytest.mark.parametrize("name", ["pi", "band", "farclike"])
+def test_folded_cycle_is_the_same_operator(name):
+    """M = R (I - A W), T = (I + S) W, Q = S P (W = omega D^-1, S = I - W A) multiplied out on the host reproduce the
+    step-by-step V(1,1) cycle to rounding, with fewer stored entries than 2 A + P + R"""
+    hm, rp, ci, vals, b = system(name)
+    H = api.amg_host_hierarchy(rp, ci, vals, min_rows=50)
+    assert len(H) >= 2 and "M" in H[0] and "M" not in H[-1]
+    rng = np.random.default_rng(5)
+    for _ in range(3):
+        v = rng.standard_normal(b.size)
+        ref = vcycle(H, 0, v)
+        got = folded_cycle(H, 0, v)
+        assert np.abs(got - ref).max() <= 1e-12 * np.abs(ref).max()
+    for lev in range(len(H) - 1):
+        h = H[lev]
+        for nm in "MTQ":
+            assert (h[nm].data != 0.0).all()                       # exact zeros are not stored
+        assert h["M"].shape == h["R"].shape and h["Q"].shape == h["P"].shape and h["T"].shape == h["A"].shape
+    old = 2 * H[0]["A"].nnz + H[0]["P"].nnz + H[0]["R"].nnz
+    new = H[0]["M"].nnz + H[0]["T"].nnz + H[0]["Q"].nnz
+    assert new < 1.05 * old, (new, old)

@@ -111,3 +111,24 @@ def test_psolve_multigrid_single_level_is_jacobi():
     sol = np.zeros_like(hm["d_eta"])
     s.solve(new_values=0, sol=sol)
     assert s.info()[1] < 1e-10 and scaled_residual(rp, ci, vals, sol[:b.size], b) < 2e-10
+
+
+def test_psolve_takes_device_pointers():
+    """rhs, vals and sol may live in device memory (a host that assembles the system on the device): same bits as with host arrays"""
+    import torch
+    from fesom2_b200 import api
+    hm, rp, ci, vals, b = system("band")
+    s = api.SSHSolver(hm, ident=13, pc="amg")
+    sol_h = np.zeros_like(hm["d_eta"])
+    s.solve(new_values=1, sol=sol_h)
+    its_h, res_h = s.info()
+    d_rhs = torch.from_numpy(np.ascontiguousarray(hm["ssh_rhs"])).cuda()
+    d_vals = torch.from_numpy(np.ascontiguousarray(hm["ssh_values"])).cuda()
+    d_sol = torch.zeros(sol_h.size, dtype=torch.float64, device="cuda")
+    torch.cuda.synchronize()
+    for _ in range(2):                                    # twice: the second call replays the captured iteration graph
+        d_sol.zero_()
+        torch.cuda.synchronize()
+        s.solve_ptr(d_rhs.data_ptr(), d_vals.data_ptr(), d_sol.data_ptr(), new_values=1)
+        assert s.info() == (its_h, res_h)
+        assert np.array_equal(d_sol.cpu().numpy()[:b.size], sol_h[:b.size])
