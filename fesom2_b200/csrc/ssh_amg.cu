@@ -1,6 +1,7 @@
 // Aggregation multigrid preconditioner of the SSH solve: host setup + device V-cycle.  See ssh_amg.cuh.
 #include "ssh_amg.cuh"
 #include <cstdlib>
+#include <cstring>
 #include "fesom_b200.h"
 #include <algorithm>
 #include <cmath>
@@ -176,6 +177,23 @@ static HostCsr csr_i_minus_scaled(const HostCsr& A, const std::vector<double>& w
     }
     return S;
 }
+// A + B, rows of both sorted by column
+static HostCsr csr_add(const HostCsr& A, const HostCsr& B) {
+    HostCsr C;
+    C.nrow = A.nrow; C.ncol = A.ncol; C.rp.assign(A.nrow + 1, 0);
+    C.ci.reserve(A.nnz() + B.nnz()); C.v.reserve(A.nnz() + B.nnz());
+    for (int i = 0; i < A.nrow; i++) {
+        int a = A.rp[i], b = B.rp[i];
+        const int ae = A.rp[i + 1], be = B.rp[i + 1];
+        while (a < ae || b < be) {
+            if (b >= be || (a < ae && A.ci[a] < B.ci[b])) { C.ci.push_back(A.ci[a]); C.v.push_back(A.v[a]); a++; }
+            else if (a >= ae || B.ci[b] < A.ci[a]) { C.ci.push_back(B.ci[b]); C.v.push_back(B.v[b]); b++; }
+            else { C.ci.push_back(A.ci[a]); C.v.push_back(A.v[a] + B.v[b]); a++; b++; }
+        }
+        C.rp[i + 1] = (int)C.ci.size();
+    }
+    return C;
+}
 void amg_fold_cycle(std::vector<AmgHostLevel>& lv, double omega) {
     const std::vector<double> none;
     for (size_t l = 0; l + 1 < lv.size(); l++) {
@@ -194,6 +212,11 @@ void amg_fold_cycle(std::vector<AmgHostLevel>& lv, double omega) {
         for (int i = 0; i < n; i++)
             for (int j = L.T.rp[i]; j < L.T.rp[i + 1]; j++) { const int c = L.T.ci[j]; L.T.v[j] = (L.T.v[j] + (c == i ? 1.0 : 0.0)) * w[c]; }
         csr_drop_zeros(L.M); csr_drop_zeros(L.T); csr_drop_zeros(L.Q);
+        if (l + 2 == lv.size() && n <= AMG_COLLAPSE_ROWS) {          // x = T b + Q (M b) = C b
+            L.T = csr_add(L.T, csr_matmul(L.Q, L.M));
+            csr_drop_zeros(L.T);
+            L.M = HostCsr(); L.Q = HostCsr();
+        }
     }
 }
 bool amg_folded_on() {
@@ -274,7 +297,7 @@ void DevSell::upload(const HostCsr& m) {
 void Amg::upload(const std::vector<AmgHostLevel>& h, double omega_) {
     release();
     omega = omega_;
-    folded = h.size() > 1 && h[0].M.nrow > 0;
+    folded = h.size() > 1 && h[0].T.nrow > 0;
     L.resize(h.size());
     for (size_t l = 0; l < h.size(); l++) {
         AmgDevLevel& D = L[l];
@@ -282,7 +305,8 @@ void Amg::upload(const std::vector<AmgHostLevel>& h, double omega_) {
         D.dinv.upload(h[l].dinv);
         D.b.alloc(D.n); D.x.alloc(D.n);
         if (folded) {
-            if (h[l].M.nrow) { D.M.upload(h[l].M); D.T.upload(h[l].T); D.Q.upload(h[l].Q); }
+            if (h[l].T.nrow) D.T.upload(h[l].T);
+            if (h[l].M.nrow) { D.M.upload(h[l].M); D.Q.upload(h[l].Q); }          // absent on a collapsed level
             continue;
         }
         D.A.upload(h[l].A);
@@ -414,11 +438,12 @@ __device__ __forceinline__ double sell_part(const int* __restrict__ sptr, const 
     return s;
 }
 // out = M1 x1 (+ M2 x2)
-template <int NQ, bool TWO>
-__global__ void __launch_bounds__(256) k_amg_fold(int n, const int* __restrict__ p1, const int* __restrict__ c1, const double* __restrict__ v1, const double* __restrict__ x1,
+template <int NQ, bool TWO, bool HEAD>
+__global__ void __launch_bounds__(256) k_amg_fold(int n, const int* __restrict__ p1, const int* __restrict__ c1, const double* __restrict__ v1, const double* x1,
                                                   const int* __restrict__ p2, const int* __restrict__ c2, const double* __restrict__ v2, const double* __restrict__ x2,
-                                                  double* __restrict__ out, const int* done) {
+                                                  double* __restrict__ out, const int* done, CycleHead hd) {
     if (*done) return;
+    if (HEAD) push_and_wait(hd.pa, x1, hd.pc, hd.sc, 3, hd.mode);       // x1 = b0: own rows out, overlap rows in
     __shared__ double sh[8][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, q = warp % NQ;
     const int slice = blockIdx.x * (8 / NQ) + warp / NQ;
@@ -438,12 +463,17 @@ __global__ void __launch_bounds__(256) k_amg_fold(int n, const int* __restrict__
     const int i = slice * 32 + lane;
     if (i < n) out[i] = s;
 }
-static void amg_fold_launch(int nq, int n, const DevSell& A1, const double* x1, const DevSell* A2, const double* x2, double* out, const int* done, cudaStream_t st) {
-    if (n <= 0) return;
-    const int nslice = (n + 31) / 32;
-#define FOLD_GO(NQ) do { const int g_ = (nslice + 8 / NQ - 1) / (8 / NQ); \
-        if (A2) k_amg_fold<NQ, true><<<g_, 256, 0, st>>>(n, A1.sptr.p, A1.scol.p, A1.sval.p, x1, A2->sptr.p, A2->scol.p, A2->sval.p, x2, out, done); \
-        else k_amg_fold<NQ, false><<<g_, 256, 0, st>>>(n, A1.sptr.p, A1.scol.p, A1.sval.p, x1, nullptr, nullptr, nullptr, nullptr, out, done); } while (0)
+static void amg_fold_launch(int nq, int n, const DevSell& A1, const double* x1, const DevSell* A2, const double* x2, double* out, const int* done, cudaStream_t st,
+                            const CycleHead* head = nullptr) {
+    if (n <= 0 && !head) return;
+    const int nslice = (std::max(n, 0) + 31) / 32;
+    CycleHead hd; memset(&hd, 0, sizeof(hd));
+    if (head) hd = *head;
+#define FOLD_GO(NQ) do { const int g_ = std::max(std::max(1, hd.pa.npb), (nslice + 8 / NQ - 1) / (8 / NQ)); \
+        if (A2 && head) k_amg_fold<NQ, true, true><<<g_, 256, 0, st>>>(n, A1.sptr.p, A1.scol.p, A1.sval.p, x1, A2->sptr.p, A2->scol.p, A2->sval.p, x2, out, done, hd); \
+        else if (A2) k_amg_fold<NQ, true, false><<<g_, 256, 0, st>>>(n, A1.sptr.p, A1.scol.p, A1.sval.p, x1, A2->sptr.p, A2->scol.p, A2->sval.p, x2, out, done, hd); \
+        else if (head) k_amg_fold<NQ, false, true><<<g_, 256, 0, st>>>(n, A1.sptr.p, A1.scol.p, A1.sval.p, x1, nullptr, nullptr, nullptr, nullptr, out, done, hd); \
+        else k_amg_fold<NQ, false, false><<<g_, 256, 0, st>>>(n, A1.sptr.p, A1.scol.p, A1.sval.p, x1, nullptr, nullptr, nullptr, nullptr, out, done, hd); } while (0)
     if (nq == 8) FOLD_GO(8); else if (nq == 4) FOLD_GO(4); else if (nq == 2) FOLD_GO(2); else FOLD_GO(1);
 #undef FOLD_GO
 }
@@ -513,18 +543,23 @@ static bool amg_fused_on() {
 
 // n_out: rows of the last (fine-level) post-smoothing step that are written to `out` — all of level 0 on one rank, the rank's own
 // rows when level 0 is an overlapping subdomain (restricted additive Schwarz: the overlap part of the result is discarded)
-void Amg::cycle(double* out, const int* done, cudaStream_t st, int n_out) {
+void Amg::cycle(double* out, const int* done, cudaStream_t st, int n_out, const CycleHead* head) {
     const int K = (int)L.size();
     if (K <= 1) return;                                           // single level: the caller's Jacobi step already wrote `out`
 #define AKL(name0, namec, lev, ...) do { ProfScope ps_((lev) == 0 ? name0 : namec, st); __VA_ARGS__; LAUNCH_CHECK(); } while (0)
     if (folded) {
-        for (int l = 0; l + 1 < K; l++)                           // b_{l+1} = M_l b_l
-            AKL("k_amg_down0", "k_amg_coarse", l, amg_fold_launch(amg_nq(l + 1), L[l + 1].n, L[l].M, L[l].b.p, nullptr, nullptr, L[l + 1].b.p, done, st));
+        const bool collapsed = L[K - 2].M.nrow == 0;              // level K-2: x = C b in one step (C kept in T)
+        const int ndown = collapsed ? K - 2 : K - 1;
+        for (int l = 0; l < ndown; l++) {                         // b_{l+1} = M_l b_l
+            AKL("k_amg_down0", "k_amg_coarse", l, amg_fold_launch(amg_nq(l + 1), L[l + 1].n, L[l].M, L[l].b.p, nullptr, nullptr, L[l + 1].b.p, done, st, l == 0 ? head : nullptr));
+        }
         const double* cur = L[K - 1].b.p;                         // the coarsest level's W is inside Q_{K-2}
         for (int l = K - 2; l >= 0; l--) {                        // x_l = T_l b_l + Q_l x_{l+1}
             double* dst = l == 0 ? out : L[l].x.p;
             const int rows = (l == 0 && n_out > 0) ? std::min(n_out, L[l].n) : L[l].n;
-            AKL("k_amg_up0", "k_amg_coarse", l, amg_fold_launch(amg_nq(l), rows, L[l].T, L[l].b.p, &L[l].Q, cur, dst, done, st));
+            const bool one = collapsed && l == K - 2;
+            AKL("k_amg_up0", "k_amg_coarse", l, amg_fold_launch(amg_nq(one ? 1 : l), rows, L[l].T, L[l].b.p, one ? nullptr : &L[l].Q, cur, dst, done, st,
+                                                               (one && l == 0) ? head : nullptr));
             cur = dst;
         }
         return;

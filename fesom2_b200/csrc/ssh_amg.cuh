@@ -12,6 +12,7 @@
 //                        row-gather SpMV: no atomics, bitwise reproducible.
 #pragma once
 #include "common.cuh"
+#include "ssh_peer.cuh"
 
 struct HostCsr {
     int nrow = 0, ncol = 0;
@@ -39,8 +40,14 @@ void amg_host_setup(const HostCsr& A0, const AmgParams& prm, std::vector<AmgHost
 //   coarsest x = W b  — folded into the Q of the level above (Q <- Q W_c).
 // Same operator as the step-by-step cycle up to rounding; 2 (K-1) kernels per cycle instead of 4 (K-1), no intermediate vectors,
 // and M + T + Q hold fewer entries than 2 A + P + R.
+// The last level above the coarsest is small: there down + coarsest + up collapse further into ONE matrix, x = (T + Q M) b =: C b,
+// kept in T (M and Q of that level stay empty).  Only below AMG_COLLAPSE_ROWS rows — the product is dense (100-200 entries per row): at 16 k rows
+// the one dense kernel takes as long as the three it replaces (profiles/r02_c15_*.json).
+#define AMG_COLLAPSE_ROWS 8192
 void amg_fold_cycle(std::vector<AmgHostLevel>& lv, double omega);
 bool amg_folded_on();               // default on; FB200_AMG_FOLD=0 keeps the step-by-step kernels
+
+struct CycleHead { PushArgs pa; PeerCtl pc; SolverScal* sc; int mode; };
 
 struct DevSell {                     // sliced ELL, slice = 32 rows: val[sptr[s] + k*32 + lane]
     int nrow = 0, nslice = 0;
@@ -66,7 +73,9 @@ struct Amg {
     void upload(const std::vector<AmgHostLevel>& h, double omega_);
     // out = V-cycle(b0) where the caller has already filled L[0].b (= D * in) and L[0].x (= omega dinv0 b0), see k_amg_enter
     // in ssh_solver.cu.  `done` points at the solver's device-side convergence flag: all kernels are no-ops once it is set.
-    void cycle(double* out, const int* done, cudaStream_t st, int n_out = 0);
+    // head (folded cycle, peer-memory transport, overlapping subdomains): the first kernel of the cycle pushes this rank's b0 to the
+    // ranks whose subdomains overlap its rows and waits for its own overlap rows (push_and_wait, ssh_peer.cuh)
+    void cycle(double* out, const int* done, cudaStream_t st, int n_out = 0, const CycleHead* head = nullptr);
     void release();
 };
 
