@@ -57,7 +57,8 @@ def ncu_traffic(name, units):
     """DRAM bytes per launch of `name` at this run's size, from the committed ncu capture (profiles/r02_ncu_traffic.json:
     dram__bytes_read.sum + dram__bytes_write.sum per unit at the captured size x this run's units); None if absent"""
     name = {"k_ho_edge_x2": "k_edge_adv2", "k_diff_edge_x2": "k_edge_diff2", "k_lo_x2": "k_lo2", "k_update": "k_update2", "k_fct_bounds": "k_fct_bounds2",
-            "k_ab2": "k_ab2_g"}.get(name, name)
+            "k_ab2": "k_ab2_g", "k_ab2_x2": "k_ab2_g", "k_impl_diff_x2": "k_impl_diff", "k_ho_edge": "k_edge_adv2", "k_diff_edge": "k_edge_diff2", "k_lo": "k_lo2",
+            "k_update_x2": "k_update2", "k_fct_bounds_x2": "k_fct_bounds2"}.get(name, name)
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))
         return t[name]["dram_bytes_per_unit"] * units

@@ -753,7 +753,8 @@ void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues) {
     // The iteration is launch-bound on small partitions (17 launches incl. NCCL per iteration on several ranks), so
     // `poll` iterations are captured into a CUDA graph once and replayed; converged iterations inside a replay are
     // no-ops (every kernel returns on sc->done).  Per-kernel profiling uses plain launches.
-    const bool use_graph = !prof_on() && g_use_graph;
+    static const bool graph_env = [] { const char* e = getenv("FB200_SSH_GRAPH"); return !(e && e[0] == '0'); }();   // FB200_SSH_GRAPH=0: plain launches (profilers)
+    const bool use_graph = !prof_on() && g_use_graph && graph_env;
     if (use_graph && S.graph && (S.graph_stream != st || S.graph_multi != multi)) { cudaGraphExecDestroy(S.graph); S.graph = nullptr; }
 #ifndef FB200_EMULATION
     // Without NCCL in the loop the iterations run as the body of a conditional WHILE node: the device decides after every
