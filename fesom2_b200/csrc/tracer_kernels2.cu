@@ -287,12 +287,13 @@ __global__ void __launch_bounds__(128, EDGE_MB) k_edge_diff2(KP p, TrSet s) {
 // beyond the node's degree, an entry of the extra tile — and adds +-0, which leaves every partial sum unchanged bit for bit
 // (a sum that starts at +0 never becomes -0 under round-to-nearest).  Only the max/min gathers of the limiter need the
 // activity bit: there an inactive slot reads the thread's own column instead of the other node's.
-struct SlotBatch {
-    bool on[SB], second[SB];
-    int bo[SB], bed[SB], bo_act[SB];
+template <int NS>
+struct SlotBatchT {
+    bool on[NS], second[NS];
+    int bo[NS], bed[NS], bo_act[NS];
     __device__ __forceinline__ void setup(const SlotRec* rec, int j0, int z, int own_b) {
 #pragma unroll
-        for (int j = 0; j < SB; j++) {
+        for (int j = 0; j < NS; j++) {
             const int4 v = *reinterpret_cast<const int4*>(&rec[(j0 + j) * TILE]);     // one 16-byte shared-memory load (bo, bed, mask lo, mask hi)
             const unsigned long long mk = ((unsigned long long)(unsigned)v.w << 32) | (unsigned)v.z;
             on[j] = (mk >> z) & 1ull;
@@ -303,6 +304,7 @@ struct SlotBatch {
         }
     }
 };
+typedef SlotBatchT<SB> SlotBatch;
 
 // value form of adv_tra_ver_upw1 at interface nz (oce_adv_tra_ver.F90:255-281): t0 = T(nz), tm1 = T(nz-1)
 __device__ __forceinline__ double ver_upw1_w(double t0, double tm1, double w, double ar, int nz, int nzmin, int nzmax) {
@@ -333,15 +335,8 @@ __device__ __forceinline__ double ver_qr4c_w(double t0, double tm1, double tm2, 
 //   fct_LO : oce_adv_tra_driver.F90:83-122;  adf_v : :163-179 with init_zero=.false.
 // The column values the vertical stencils need slide down the column in registers — windows over levels z-2 .. z+1 of T,
 // ttfAB and Z_3d_n, over z, z+1 of W and area; every iteration loads one new level (z+2) of each.
-template <int NT, int VER, bool FCT>
-__global__ void __launch_bounds__(32 * WPB, LO_MB) k_lo2(KP p, TrSet s) {
-    extern __shared__ SlotRec smrec[];
-    Col c;
-    if (!col_setup(p, c)) return;
-    int ndeg = 0;
-    const SlotRec* rec = FCT ? stage_slots(p, c, smrec, ndeg) : nullptr;
-    const int zlo = warp_min_i(c.valid ? c.nzmin : 255), zhi = warp_max_i(c.valid ? c.nzmax - 1 : 0);
-    if (!c.valid) return;
+template <int NT, int VER, bool FCT, int S0>
+__device__ __forceinline__ void lo_body(const KP& p, const TrSet& s, const Col& c, const SlotRec* rec, int ndeg, int zlo, int zhi) {
     const double* __restrict__ Wlo = p.We;                         // explicit part for the LO solution
     const double* __restrict__ Wad = p.w_split ? p.W : p.We;       // LO part of the antidiffusive flux: full W (:131)
     const double* __restrict__ Who = FCT ? p.W : p.We;             // high-order flux: W under FCT, Wvel_e without (:163-179)
@@ -386,17 +381,17 @@ __global__ void __launch_bounds__(32 * WPB, LO_MB) k_lo2(KP p, TrSet s) {
         if (FCT) {
             hn = AT(p.hnode, b, z); hnn = AT(p.hnode_new, b, z); asv = AT(p.areasvol, b, z);
             rhnn = 1.0 / hnn; rasv = 1.0 / asv;                    // shared by the tracers of the pass
-            for (int j0 = 0; j0 < ndeg; j0 += SB) {
-                SlotBatch sb;
+            for (int j0 = 0; j0 < (S0 < SB ? S0 : ndeg); j0 += SB) {
+                SlotBatchT<S0> sb;
                 sb.setup(rec, j0, z, b);
-                double f[NT][SB];
+                double f[NT][S0];
 #pragma unroll
-                for (int j = 0; j < SB; j++)
+                for (int j = 0; j < S0; j++)
 #pragma unroll
                     for (int t = 0; t < NT; t++) f[t][j] = AT(s.eflx[t], sb.bed[j], z);        // upwind edge flux, once per edge by k_edge_adv2
                 LOADS_DONE();
 #pragma unroll
-                for (int j = 0; j < SB; j++)
+                for (int j = 0; j < S0; j++)
 #pragma unroll
                     for (int t = 0; t < NT; t++) acc[t] = sb.second[j] ? acc[t] - f[t][j] : acc[t] + f[t][j];   // inactive slot: f = 0
             }
@@ -429,19 +424,25 @@ __global__ void __launch_bounds__(32 * WPB, LO_MB) k_lo2(KP p, TrSet s) {
         have_fv = true;
     }
 }
-
-// ---------------------------------------------------------------------------------------------------
-// Zalesak limiter, parts a1-a3 and b1-b2 of oce_tra_adv_fct (oce_adv_tra_fct.F90:93-276), per own node column.  Level z+1 is
-// gathered before level z is finished, so the 3-point vertical max/min (a3, vlimit=1) is a register window.
-template <int NT>
-__global__ void __launch_bounds__(32 * WPB, FCTB_MB) k_fct_bounds2(KP p, TrSet s) {
+template <int NT, int VER, bool FCT>
+__global__ void __launch_bounds__(32 * WPB, LO_MB) k_lo2(KP p, TrSet s) {
     extern __shared__ SlotRec smrec[];
     Col c;
     if (!col_setup(p, c)) return;
     int ndeg = 0;
-    const SlotRec* rec = stage_slots(p, c, smrec, ndeg);
+    const SlotRec* rec = FCT ? stage_slots(p, c, smrec, ndeg) : nullptr;
     const int zlo = warp_min_i(c.valid ? c.nzmin : 255), zhi = warp_max_i(c.valid ? c.nzmax - 1 : 0);
     if (!c.valid) return;
+    if (!FCT || ndeg <= 6) lo_body<NT, VER, FCT, 6>(p, s, c, rec, ndeg, zlo, zhi);
+    else if (ndeg == 7) lo_body<NT, VER, FCT, 7>(p, s, c, rec, ndeg, zlo, zhi);
+    else lo_body<NT, VER, FCT, SB>(p, s, c, rec, ndeg, zlo, zhi);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Zalesak limiter, parts a1-a3 and b1-b2 of oce_tra_adv_fct (oce_adv_tra_fct.F90:93-276), per own node column.  Level z+1 is
+// gathered before level z is finished, so the 3-point vertical max/min (a3, vlimit=1) is a register window.
+template <int NT, int S0>
+__device__ __forceinline__ void fct_bounds_body(const KP& p, const TrSet& s, const Col& c, const SlotRec* rec, int ndeg, int zlo, int zhi) {
     const double flux_eps = 1e-16, bignumber = 1e3;
     const int b = c.b;
     // window: index 0 = level z-2, 1 = level z-1 (to be finished), 2 = level z (just gathered)
@@ -475,12 +476,12 @@ __global__ void __launch_bounds__(32 * WPB, FCTB_MB) k_fct_bounds2(KP p, TrSet s
                 Mx[t][2] = M; Mn[t][2] = m;
                 avz[t] = avn[t];
             }
-            for (int j0 = 0; j0 < ndeg; j0 += SB) {
-                SlotBatch sb;
+            for (int j0 = 0; j0 < (S0 < SB ? S0 : ndeg); j0 += SB) {
+                SlotBatchT<S0> sb;
                 sb.setup(rec, j0, z, b);
-                double f[NT][SB], lo_o[NT][SB], t_o[NT][SB];
+                double f[NT][S0], lo_o[NT][S0], t_o[NT][S0];
 #pragma unroll
-                for (int j = 0; j < SB; j++)
+                for (int j = 0; j < S0; j++)
 #pragma unroll
                     for (int t = 0; t < NT; t++) {
                         f[t][j] = AT(s.adf_h[t], sb.bed[j], z);
@@ -489,7 +490,7 @@ __global__ void __launch_bounds__(32 * WPB, FCTB_MB) k_fct_bounds2(KP p, TrSet s
                     }
                 LOADS_DONE();
 #pragma unroll
-                for (int j = 0; j < SB; j++)
+                for (int j = 0; j < S0; j++)
 #pragma unroll
                     for (int t = 0; t < NT; t++) {
                         const double fs = sb.second[j] ? -f[t][j] : f[t][j];               // inactive slot: +-0, and the own column below
@@ -524,6 +525,21 @@ __global__ void __launch_bounds__(32 * WPB, FCTB_MB) k_fct_bounds2(KP p, TrSet s
         }
     }
 }
+template <int NT>
+__global__ void __launch_bounds__(32 * WPB, FCTB_MB) k_fct_bounds2(KP p, TrSet s) {
+    extern __shared__ SlotRec smrec[];
+    Col c;
+    if (!col_setup(p, c)) return;
+    int ndeg = 0;
+    const SlotRec* rec = stage_slots(p, c, smrec, ndeg);
+    const int zlo = warp_min_i(c.valid ? c.nzmin : 255), zhi = warp_max_i(c.valid ? c.nzmax - 1 : 0);
+    if (!c.valid) return;
+    // the tile's largest node degree picks the slot count of the (unrolled) batch: 6 on a regular triangulation, where 8 slots would
+    // spend a quarter of the kernel's instructions on empty slots
+    if (ndeg <= 6) fct_bounds_body<NT, 6>(p, s, c, rec, ndeg, zlo, zhi);
+    else if (ndeg == 7) fct_bounds_body<NT, 7>(p, s, c, rec, ndeg, zlo, zhi);
+    else fct_bounds_body<NT, SB>(p, s, c, rec, ndeg, zlo, zhi);
+}
 
 // ---------------------------------------------------------------------------------------------------
 // b3 limiting + oce_tra_adv_flux2dtracer (oce_adv_tra_driver.F90:223-268) + del_ttf assembly (oce_ale_tracer.F90:240) +
@@ -539,15 +555,8 @@ __device__ __forceinline__ double limited_fv2(double flux, double2 fm1, double2 
     else { ae = dmin(ae, fm1.x); ae = dmin(ae, f0.y); }
     return ae * flux;
 }
-template <int NT, bool FCT, bool EXPL>
-__global__ void __launch_bounds__(32 * WPB, UPD_MB) k_update2(KP p, TrSet s) {
-    extern __shared__ SlotRec smrec[];
-    Col c;
-    if (!col_setup(p, c)) return;
-    int ndeg = 0;
-    const SlotRec* rec = stage_slots(p, c, smrec, ndeg);
-    const int zlo = warp_min_i(c.valid ? c.nzmin : 255), zhi = warp_max_i(c.valid ? c.nzmax - 1 : 0);
-    if (!c.valid) return;
+template <int NT, bool FCT, bool EXPL, int S0>
+__device__ __forceinline__ void update_body(const KP& p, const TrSet& s, const Col& c, const SlotRec* rec, int ndeg, int zlo, int zhi) {
     const int b = c.b;
     const bool hd = p.do_hor_diff;
     // window over the own limiter factors and the vertical flux: fpm(z-1), fpm(z); adf_v(z) and the limited fv(z) of the iteration above
@@ -578,14 +587,14 @@ __global__ void __launch_bounds__(32 * WPB, UPD_MB) k_update2(KP p, TrSet s) {
 #pragma unroll
         for (int t = 0; t < NT; t++) acc[t] = 0.0;
         // first batch of slots: advective and diffusive fluxes gathered together
-        SlotBatch sb0;
-        double dfl[NT][SB];
+        SlotBatchT<S0> sb0;
+        double dfl[NT][S0];
         {
             sb0.setup(rec, 0, z, b);
-            double ah[NT][SB];
-            double2 fo[NT][SB];
+            double ah[NT][S0];
+            double2 fo[NT][S0];
 #pragma unroll
-            for (int j = 0; j < SB; j++)
+            for (int j = 0; j < S0; j++)
 #pragma unroll
                 for (int t = 0; t < NT; t++) {
                     ah[t][j] = AT(s.adf_h[t], sb0.bed[j], z);
@@ -594,7 +603,7 @@ __global__ void __launch_bounds__(32 * WPB, UPD_MB) k_update2(KP p, TrSet s) {
                 }
             LOADS_DONE();
 #pragma unroll
-            for (int j = 0; j < SB; j++)                                         // dttf_h
+            for (int j = 0; j < S0; j++)                                         // dttf_h
 #pragma unroll
                 for (int t = 0; t < NT; t++) {
                     const double flux = ah[t][j];
@@ -610,11 +619,11 @@ __global__ void __launch_bounds__(32 * WPB, UPD_MB) k_update2(KP p, TrSet s) {
                     acc[t] = sb0.second[j] ? acc[t] - d : acc[t] + d;
                 }
         }
-        for (int j0 = SB; j0 < ndeg; j0 += SB) {                                 // nodes with more than SB incident edges
+        for (int j0 = SB; S0 == SB && j0 < ndeg; j0 += SB) {                                 // nodes with more than SB incident edges
             SlotBatch sb;
             sb.setup(rec, j0, z, b);
 #pragma unroll
-            for (int j = 0; j < SB; j++)
+            for (int j = 0; j < S0; j++)
 #pragma unroll
                 for (int t = 0; t < NT; t++) {
                     const double flux = AT(s.adf_h[t], sb.bed[j], z);
@@ -645,18 +654,18 @@ __global__ void __launch_bounds__(32 * WPB, UPD_MB) k_update2(KP p, TrSet s) {
         }
         if (hd) {                                                                // diff_part_hor_redi: fluxes from k_edge_diff2
 #pragma unroll
-            for (int j = 0; j < SB; j++)
+            for (int j = 0; j < S0; j++)
 #pragma unroll
                 for (int t = 0; t < NT; t++) {
                     const double cc = dfl[t][j];
                     const double rhs = sb0.second[j] ? 0.0 - cc : 0.0 + cc;
                     acc[t] = acc[t] + div_by(rhs * p.dt, asv, rasv);
                 }
-            for (int j0 = SB; j0 < ndeg; j0 += SB) {
+            for (int j0 = SB; S0 == SB && j0 < ndeg; j0 += SB) {
                 SlotBatch sb;
                 sb.setup(rec, j0, z, b);
 #pragma unroll
-                for (int j = 0; j < SB; j++)
+                for (int j = 0; j < S0; j++)
 #pragma unroll
                     for (int t = 0; t < NT; t++) {
                         const double cc = AT(s.eflx[t], sb.bed[j], z);
@@ -684,6 +693,19 @@ __global__ void __launch_bounds__(32 * WPB, UPD_MB) k_update2(KP p, TrSet s) {
         }
         primed = true;
     }
+}
+template <int NT, bool FCT, bool EXPL>
+__global__ void __launch_bounds__(32 * WPB, UPD_MB) k_update2(KP p, TrSet s) {
+    extern __shared__ SlotRec smrec[];
+    Col c;
+    if (!col_setup(p, c)) return;
+    int ndeg = 0;
+    const SlotRec* rec = stage_slots(p, c, smrec, ndeg);
+    const int zlo = warp_min_i(c.valid ? c.nzmin : 255), zhi = warp_max_i(c.valid ? c.nzmax - 1 : 0);
+    if (!c.valid) return;
+    if (ndeg <= 6) update_body<NT, FCT, EXPL, 6>(p, s, c, rec, ndeg, zlo, zhi);
+    else if (ndeg == 7) update_body<NT, FCT, EXPL, 7>(p, s, c, rec, ndeg, zlo, zhi);
+    else update_body<NT, FCT, EXPL, SB>(p, s, c, rec, ndeg, zlo, zhi);
 }
 
 // ---------------------------------------------------------------------------------------------------
