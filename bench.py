@@ -270,7 +270,7 @@ def run_b200(args):
     if world == 1:
         hm, info = build_workload(target, args.nl, seed=12345)
     else:
-        from fesom2_b200 import partition as P
+        from harness import partition as P
         gloo = dist.new_group(backend="gloo")
         t0 = time.time()
         ghm, info = (build_workload(target, args.nl, seed=12345) if rank == 0 else (None, None))
@@ -508,7 +508,7 @@ def cpu_reference(args, steps, warmup, nodes_per_core=None):
     gb_per_node = 3.5 / 120_000 * args.nl / 49                                   # host memory of one sample, per surface node
     # the samples of all cores together cover as much of the GPU arm's mesh as host memory and a few minutes of run time allow
     cpu_nodes = int(max(20_000, min(cpu_nodes, mem_available_gb() * 0.6 / (cores * gb_per_node), 150.0 / ((steps + warmup) * 2.2e-5))))
-    from fesom2_b200 import build as _b0
+    from harness import build as _b0
     _b0.build_oracle_timing()                                                    # once, before the workers load it
     _b0.build_host()
     ctx = mp.get_context("spawn")                                                # the parent may hold a CUDA context
@@ -532,7 +532,7 @@ def cpu_reference(args, steps, warmup, nodes_per_core=None):
              "tracer step = C restatement (oracle), SSH = %s; no halo exchange between the samples" % (
                  cores, info["nlon"], info["nlat"], args.nl, info["nod2D"], info["wet_node_layers"], ntr, steps,
                  "reference psolve.c+pARMS (oracle/_ref), 1 subdomain per process" if ref else "oracle BiCGStab")
-    from fesom2_b200 import build as _b
+    from harness import build as _b
     flags = {"tracer_step": "gcc " + " ".join(_b.ORACLE_TIMING_FLAGS) + " (the reference's own: src/CMakeLists.txt:73; built on this host)",
              "ssh": "gcc -O3 -finline-functions -march=x86-64-v3 (oracle/Makefile.ref, timing copy; built where /root/reference exists)"}
     return dict(value=value, unit=UNIT, cores=cores, kind="port", ssh_kind="reference" if ref else "port", sample=sample, flags=flags,

@@ -1,9 +1,9 @@
-"""In-tree builds of the native pieces (no JIT cache: the .so files travel with the repo snapshot).
+"""In-tree build of the product (no JIT cache: the .so travels with the repo snapshot).
 
-  libfesom_host.so   fesom2_b200/host/*.cpp       g++      host-side mirror of the Fortran setup code
-  libfesom_b200.so   fesom2_b200/csrc/*.cu        nvcc     the product: CUDA kernels + C ABI (sm_100a)
-  liboracle.so       oracle/*.c                   gcc      CPU restatement of the reference (test infrastructure)
-  oracle/_ref/...    /root/reference pARMS + psolve.c  gcc (only when /root/reference exists)
+  libfesom_b200.so   fesom2_b200/csrc/*.cu        nvcc     CUDA kernels + C ABI (sm_100a)
+
+The builds of the test infrastructure (host-side mirror of the Fortran setup code, oracle, the reference's own psolve.c + pARMS
+and partitioner) live in harness/build.py.
 """
 import glob
 import os
@@ -13,13 +13,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "fesom2_b200")
-HOST_SO = os.path.join(PKG, "host", "libfesom_host.so")
 CUDA_SO = os.path.join(PKG, "csrc", "libfesom_b200.so")
-ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
-REF_SO = os.path.join(ROOT, "oracle", "_ref", "libpsolve_ref.so")
-REF_TIMING_SO = os.path.join(ROOT, "oracle", "_ref", "libpsolve_ref_timing.so")
-ORACLE_TIMING_SO = os.path.join(ROOT, "oracle", "liboracle_timing.so")
-ORACLE_TIMING_FLAGS = ["-O3", "-march=native", "-finline-functions"]      # the reference's own (src/CMakeLists.txt:73); FMA contraction allowed
 
 
 def _newer(target, sources):
@@ -35,14 +29,6 @@ def _run(cmd, cwd=None):
         sys.stderr.write(" ".join(cmd) + "\n" + r.stdout)
         raise RuntimeError("build failed: " + " ".join(cmd[:3]))
     return r.stdout
-
-
-def build_host(force=False):
-    src = sorted(glob.glob(os.path.join(PKG, "host", "*.cpp")))
-    dep = src + glob.glob(os.path.join(PKG, "host", "*.hpp"))
-    if force or _newer(HOST_SO, dep):
-        _run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-o", HOST_SO] + src)
-    return HOST_SO
 
 
 def nvcc_path():
@@ -102,40 +88,3 @@ def build_cuda(force=False, verbose=False, out=None, defines=(), fmad=False):
     return so
 
 
-def build_oracle(force=False):
-    src = sorted(glob.glob(os.path.join(ROOT, "oracle", "*.c")))
-    dep = src + glob.glob(os.path.join(ROOT, "oracle", "*.h"))
-    if force or _newer(ORACLE_SO, dep):
-        tmp = ORACLE_SO + ".%d.tmp" % os.getpid()
-        _run(["gcc", "-O2", "-std=c99", "-fPIC", "-shared", "-ffp-contract=off", "-fopenmp", "-o", tmp] + src + ["-lm"])
-        os.replace(tmp, ORACLE_SO)
-    return ORACLE_SO
-
-
-def build_oracle_timing(force=False):
-    """A second copy of the oracle for bench.py's CPU arm only, compiled like the reference compiles its Fortran
-    (-O3 -march=native -finline-functions, contraction allowed).  Built on the machine that runs it (the sources travel)."""
-    src = sorted(glob.glob(os.path.join(ROOT, "oracle", "*.c")))
-    dep = src + glob.glob(os.path.join(ROOT, "oracle", "*.h"))
-    if force or _newer(ORACLE_TIMING_SO, dep):
-        tmp = ORACLE_TIMING_SO + ".%d.tmp" % os.getpid()
-        _run(["gcc"] + ORACLE_TIMING_FLAGS + ["-std=c99", "-fPIC", "-shared", "-fopenmp", "-o", tmp] + src + ["-lm"])
-        os.replace(tmp, ORACLE_TIMING_SO)                  # atomic: several processes may get here at the same time
-    return ORACLE_TIMING_SO
-
-
-def build_ref(force=False):
-    """Compile the reference's own pARMS + psolve.c from /root/reference (read in place) into oracle/_ref."""
-    mk = os.path.join(ROOT, "oracle", "Makefile.ref")
-    if not os.path.isdir("/root/reference/lib/parms") or not os.path.exists(mk):
-        return REF_SO if os.path.exists(REF_SO) else None
-    if force or not os.path.exists(REF_SO) or not os.path.exists(REF_TIMING_SO):
-        _run(["make", "-s", "-f", mk, "-j8", "_ref/libpsolve_ref.so", "_ref/libpsolve_ref_timing.so"], cwd=os.path.join(ROOT, "oracle"))
-    return REF_SO
-
-
-def build_all(force=False):
-    build_host(force)
-    build_oracle(force)
-    build_ref(force)
-    build_cuda(force)

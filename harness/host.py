@@ -1,4 +1,4 @@
-"""ctypes front of the host-side mirror (fesom2_b200/host/*.cpp).
+"""ctypes front of the host-side mirror (harness/host/*.cpp).
 
 `HostModel` plays the part of the reference's Fortran driver state: it owns the mesh (t_mesh), the
 partition-independent derived geometry, the ALE arrays and the model state in the reference's own memory

@@ -2,7 +2,7 @@
 
 Nothing here is timed.  The fields are smooth analytic profiles plus seeded noise; the vertical velocity and
 the new layer thicknesses are NOT analytic — they come from the restated `compute_hbar_ale` / `vert_vel_ale`
-(fesom2_b200/host/ale.cpp), so that discrete continuity holds exactly as it does in the reference and a
+(harness/host/ale.cpp), so that discrete continuity holds exactly as it does in the reference and a
 constant tracer stays constant.
 """
 import numpy as np

@@ -40,7 +40,7 @@ def use_timing_build(on=True):
 def lib():
     global _lib
     if _lib is None:
-        from fesom2_b200 import build
+        from harness import build
         L = C.CDLL(build.build_oracle_timing() if _timing else build.build_oracle())
         L.oracle_create.restype = C.c_void_p
         L.oracle_free.argtypes = [C.c_void_p]
@@ -200,7 +200,7 @@ def ref_lib():
     """the reference's own psolver_init/psolve (src/psolve.c + lib/parms), or None if it was never built"""
     global _ref
     if _ref is None:
-        from fesom2_b200 import build
+        from harness import build
         so = build.build_ref()
         if _timing and so is not None and os.path.exists(build.REF_TIMING_SO):
             so = build.REF_TIMING_SO

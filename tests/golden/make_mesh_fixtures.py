@@ -8,7 +8,7 @@ import sys
 import numpy as np
 
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", ".."))
-from fesom2_b200.host import read_mesh_files  # noqa: E402
+from harness.host import read_mesh_files  # noqa: E402
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 for name in ("pi", "soufflet"):
@@ -17,7 +17,7 @@ for name in ("pi", "soufflet"):
     print(name, {k: (v.shape if hasattr(v, "shape") else v) for k, v in m.items()})
 
 # the reference's own 2-way partition of the pi mesh (test/meshes/pi/dist_2: rpart.out, my_listNNNNN.out)
-from fesom2_b200 import partition as P  # noqa: E402
+from harness import partition as P  # noqa: E402
 d = {"part": P.read_rpart("/root/reference/test/meshes/pi/dist_2", 2)}
 for me in range(2):
     for k, v in P.read_my_list("/root/reference/test/meshes/pi/dist_2", me).items():

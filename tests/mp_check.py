@@ -17,7 +17,8 @@ def check_device_ale(name, rank, world, part_in):
     """the device-side ALE producers (fb200_ale_step_begin / _end) on this rank's partition, with the reference's four
     exchanges over NCCL, against the host-side mirror on the UNDIVIDED mesh: three coupled steps, own and halo entries bit
     for bit; the tracers stepped on the device-produced state against the oracle on the undivided mesh."""
-    from fesom2_b200 import api, partition as P
+    from fesom2_b200 import api
+    from harness import partition as P
     from oracle import binding as ob
     from tests import util
     kw = dict(umax=0.05, water_flux=0.0 if name == "soufflet" else 2e-7)
@@ -94,7 +95,8 @@ def run_check(name, dist, rank, world, ale=False, emulate=False, steps=2):
     """one mesh: this rank's partition through the C ABI (NCCL halo exchange / all-reduce) against the oracle on the undivided
     mesh.  Returns this rank's verdict dict; the caller gathers them.  `dist` is an initialised torch.distributed (any backend):
     it only carries the NCCL id."""
-    from fesom2_b200 import api, partition as P
+    from fesom2_b200 import api
+    from harness import partition as P
     from oracle import binding as ob
     from tests import util
     hm = util.build_model(name)

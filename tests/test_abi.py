@@ -50,9 +50,8 @@ def test_product_never_refers_to_the_test_emulation_or_the_oracle():
                 continue
             src = open(os.path.join(dp, f)).read()
             assert "FB200_EMULATE" not in src and "libfesom_b200_emu" not in src and "tests.emu" not in src and "from tests" not in src, f
-            if f == "build.py":                            # compiles liboracle.so / oracle/_ref: building the checker is not using it
-                continue
             assert "import oracle" not in src and "from oracle" not in src and "liboracle" not in src, f
+            assert "import harness" not in src and "from harness" not in src, f          # host mirror, partitioner, synthetic meshes: harness/
     for f in ("bench.py", "__graft_entry__.py"):
         src = open(os.path.join(ROOT, f)).read()
         assert "FB200_EMULATE" not in src and "tests.emu" not in src and "libfesom_b200_emu" not in src, f

@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 
-from fesom2_b200 import partition as P
+from harness import partition as P
 from oracle import binding as ob
 from tests import util
 

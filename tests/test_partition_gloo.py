@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
-    from fesom2_b200 import partition as P
+    from harness import partition as P
     from oracle import binding as ob
     from tests import util
     os.environ["MASTER_ADDR"] = "127.0.0.1"

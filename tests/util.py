@@ -4,8 +4,8 @@ import os
 
 import numpy as np
 
-from fesom2_b200 import synth
-from fesom2_b200.host import HostModel
+from harness import synth
+from harness.host import HostModel
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
