@@ -484,23 +484,30 @@ static bool setup_halo(Solver& S, HaloPlan& H, const int* part, const std::vecto
     cudaStream_t st = S.stream;
     std::vector<int> rPE, rptr{1}, rlist, req_cnt(np, 0);
     std::vector<std::vector<int>> req(np);
-    int h = 0;
+    int h = 0, bad = 0;
     for (int g : gcols_sorted) {
         int pe = int(std::upper_bound(part, part + np + 1, g) - part) - 1;
-        if (pe < 0 || pe >= np || pe == me) { fb_set_error(44, "psolver_init: column outside the global numbering"); return false; }
+        if (pe < 0 || pe >= np || pe == me) { bad = 1; continue; }      // reported below, once every rank knows: no rank may leave the collectives alone
         req[pe].push_back(g - part[pe]);                       // row of the owner, 0-based local
         rlist.push_back(S.n + h + 1); h++;
     }
     for (int pe = 0; pe < np; pe++) if (!req[pe].empty()) { rPE.push_back(pe); rptr.push_back(rptr.back() + (int)req[pe].size()); req_cnt[pe] = (int)req[pe].size(); }
-    // all-gather the request counts: cnt[q][p] = how many rows rank q wants from rank p
+    // all-gather the request counts: cnt[q][p] = how many rows rank q wants from rank p; entry np of every rank's record = its error flag
+    const int rec = np + 1;
+    req_cnt.push_back(bad);
     DevBuf<int> d_cnt, d_all;
-    d_cnt.upload(req_cnt); d_all.alloc((size_t)np * np);
-    NCCL_CHECK(ncclAllGather(d_cnt.p, d_all.p, np, ncclInt32, comm_handle(), st));
-    std::vector<int> all((size_t)np * np);
+    d_cnt.upload(req_cnt); d_all.alloc((size_t)np * rec);
+    NCCL_CHECK(ncclAllGather(d_cnt.p, d_all.p, rec, ncclInt32, comm_handle(), st));
+    std::vector<int> all((size_t)np * rec);
     CUDA_CHECK(cudaMemcpyAsync(all.data(), d_all.p, all.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
+    if (!fb_ok()) return false;
+    for (int q = 0; q < np; q++) if (all[(size_t)q * rec + np]) {          // every rank leaves together
+        fb_set_error(44, bad ? "psolver_init: column outside the global numbering" : "psolver_init: a peer rank found a column outside the global numbering");
+        return false;
+    }
     std::vector<int> sPE, sptr{1};
-    for (int q = 0; q < np; q++) if (q != me && all[(size_t)q * np + me] > 0) { sPE.push_back(q); sptr.push_back(sptr.back() + all[(size_t)q * np + me]); }
+    for (int q = 0; q < np; q++) if (q != me && all[(size_t)q * rec + me] > 0) { sPE.push_back(q); sptr.push_back(sptr.back() + all[(size_t)q * rec + me]); }
     // exchange the requested row lists
     std::vector<int> flat;
     for (int pe : rPE) flat.insert(flat.end(), req[pe].begin(), req[pe].end());
@@ -513,7 +520,22 @@ static bool setup_halo(Solver& S, HaloPlan& H, const int* part, const std::vecto
     std::vector<int> slist(sptr.back() - 1);
     if (!slist.empty()) CUDA_CHECK(cudaMemcpyAsync(slist.data(), d_snd.p, slist.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
-    for (int& v : slist) { if (v < 0 || v >= S.n) { fb_set_error(45, "psolver_init: a neighbour requested a row this rank does not own"); return false; } v += 1; }
+    int bad2 = 0;
+    for (int& v : slist) { if (v < 0 || v >= S.n) bad2 = 1; v += 1; }
+    {   // agree on the outcome before anyone returns (the next collective would otherwise hang the healthy ranks)
+        std::vector<int> f1{bad2}, fall(np, 0);
+        DevBuf<int> d_f, d_g;
+        d_f.upload(f1); d_g.alloc(np);
+        NCCL_CHECK(ncclAllGather(d_f.p, d_g.p, 1, ncclInt32, comm_handle(), st));
+        CUDA_CHECK(cudaMemcpyAsync(fall.data(), d_g.p, np * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        d_f.release(); d_g.release();
+        if (!fb_ok()) return false;
+        for (int q = 0; q < np; q++) if (fall[q]) {
+            fb_set_error(45, bad2 ? "psolver_init: a neighbour requested a row this rank does not own" : "psolver_init: a peer rank was asked for a row it does not own");
+            return false;
+        }
+    }
     halo_plan_build(H, (int)rPE.size(), rPE.data(), rptr.data(), rlist.data(), (int)sPE.size(), sPE.data(), sptr.data(), slist.data());
     if (H.nsend()) H.sbuf.alloc(H.nsend());
     if (H.nrecv()) H.rbuf.alloc(H.nrecv());      // sized now: no allocation may happen during graph capture
@@ -580,9 +602,21 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
                   int* restart, double* soltol, int* part, int* rptr, int* cols, double* vals, int* reuse, int* fcomm) {
     (void)stype; (void)pctype; (void)pcilutype; (void)ilulevel; (void)fillin; (void)droptol; (void)restart; (void)fcomm;
     if (!fb_ok()) return;
+    const int np = comm_nranks(), me = comm_rank();
+    if (np == 1 && !getenv("FB200_SINGLE_RANK")) {
+        // the reference's psolver_init receives the MPI communicator; here the ranks are introduced by fb200_comm_init.  A process that a
+        // launcher started as one of several and that never called it would silently solve part[0..1] on every rank: refuse instead
+        for (const char* nm : {"OMPI_COMM_WORLD_SIZE", "PMI_SIZE", "MV2_COMM_WORLD_SIZE", "SLURM_NTASKS", "WORLD_SIZE"}) {
+            const char* e = getenv(nm);
+            if (e && atoi(e) > 1) {
+                fb_set_error(47, std::string("psolver_init: this process is one of ") + e + " (" + nm + ") but fb200_comm_init was not called; "
+                                 "set FB200_SINGLE_RANK=1 if every process really solves its own undivided system");
+                return;
+            }
+        }
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { fb_set_error(12, "no CUDA device: libfesom_b200 has no CPU fallback"); return; }
-    const int np = comm_nranks(), me = comm_rank();
     Solver* S = new Solver();
     S->n = part[me + 1] - part[me];                            // rows of this partition (psolve.c:38-43)
     S->nnz = rptr[S->n]; S->reuse = *reuse; S->maxits = *maxits; S->soltol = *soltol; S->bs = g_block;

@@ -1057,7 +1057,7 @@ bool tracer_step_begin(TracerCtx& c) {
     if (!fb_ok()) return false;
     if (!c.committed) { fb_set_error(20, "fb200_solve_tracers before fb200_init_commit"); return false; }
     if (c.opt.dt <= 0.0) { fb_set_error(24, "dt not set (fb200_set_options)"); return false; }
-    if (c.nl - 1 > 64) { fb_set_error(25, "nl too large for the level-row thread mapping of k_fct_bounds (nl-1 <= 64)"); return false; }
+    if (c.nlp > 63) { fb_set_error(25, "nl > 63 is not supported (64-bit level masks; fb200_init_commit applies the same limit)"); return false; }
     if (comm_nranks() > 1 && !c.halo_nod) { fb_set_error(26, "more than one rank but fb200_init_halo was not called"); return false; }
     set_smem_attrs();
     fb_copy_sync();                                             // state pushed with fb200_push_state_early must have landed

@@ -28,13 +28,22 @@ extern "C" {
  *   part  : npes+1 row offsets of the PE-contiguous numbering (0-based)
  *   rptr  : N_own+1 CSR row pointers (0-based)         cols : nnz global PE-contiguous column ids (0-based)
  *   vals  : nnz matrix values                          reuse: 1 = values will be replaced by later psolve calls
- *   fcomm : Fortran MPI communicator handle (unused by the single-process path; kept for ABI identity)
+ *   fcomm : Fortran MPI communicator handle (kept for ABI identity; the ranks are introduced by fb200_comm_init, which must come
+ *           first when there is more than one.  A process that a launcher started as one of several — OMPI_COMM_WORLD_SIZE,
+ *           PMI_SIZE, MV2_COMM_WORLD_SIZE, SLURM_NTASKS or WORLD_SIZE > 1 — and that did not call fb200_comm_init is refused with
+ *           error 47 instead of solving part[0..1] on every rank; FB200_SINGLE_RANK=1 states that this is intended.)
+ * Errors found while the ranks negotiate the interface lists (44, 45) are agreed on before any rank returns: all fail together.
  */
 void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* ilulevel, int* fillin, double* droptol,
                   int* maxits, int* restart, double* soltol, int* part, int* rptr, int* cols, double* vals,
                   int* reuse, int* fcomm);
 /* rhs: N_own (+halo) right-hand side; sol: in = initial guess (warm start, psolve.c:206), out = solution;
- * newvalues: 0 keep matrix, 1 replace values (keep preconditioner), 2 replace values and rebuild preconditioner */
+ * newvalues: 0 keep matrix, 1 replace values (keep preconditioner), 2 replace values and rebuild preconditioner.
+ * rhs, vals and sol may be HOST pointers (the reference's call) or DEVICE pointers (unified addressing decides per pointer): a
+ * host that assembles the system on the device solves without crossing PCIe.
+ * On several ranks the multigrid preconditioner works on overlapping subdomains (restricted additive Schwarz, FB200_SSH_OVERLAP
+ * layers of neighbour rows, default 2, like the reference's RAS) and the small messages of the iteration travel over peer
+ * memory (CUDA IPC over NVLink) when every rank can map its peers' buffers, else over NCCL (FB200_SSH_COMM=nccl forces it). */
 void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues);
 void psolver_final(void);
 /* iteration count and final scaled residual norm of the last psolve(id) (the reference keeps them in the

@@ -55,3 +55,17 @@ def test_product_never_refers_to_the_test_emulation_or_the_oracle():
     for f in ("bench.py", "__graft_entry__.py"):
         src = open(os.path.join(ROOT, f)).read()
         assert "FB200_EMULATE" not in src and "tests.emu" not in src and "libfesom_b200_emu" not in src, f
+
+
+def test_psolver_init_refuses_a_multi_process_launch_without_comm_init(monkeypatch):
+    """the reference's psolver_init gets the MPI communicator; here fb200_comm_init introduces the ranks.  A process started by a
+    launcher as one of several that never called it must not silently solve the first partition on every rank (error 47,
+    raised before any CUDA call)."""
+    from tests import util
+    hm = util.build_model("pi")
+    hm.compute_ssh_rhs()
+    monkeypatch.setenv("WORLD_SIZE", "4")
+    monkeypatch.delenv("FB200_SINGLE_RANK", raising=False)
+    with pytest.raises(api.FesomB200Error, match="fb200_comm_init was not called"):
+        api.SSHSolver(hm)
+    api.lib().fb200_clear_status()
