@@ -103,8 +103,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--nodes", type=int, default=5_000_000, help="target surface nodes per GPU")
-    ap.add_argument("--nl", type=int, default=49, help="number of levels (layers = nl-1)")
+    ap.add_argument("--nodes", type=int, default=0, help="target surface nodes of the global mesh (default: the --config's size)")
+    ap.add_argument("--nl", type=int, default=0, help="number of levels (layers = nl-1; default: the --config's)")
     ap.add_argument("--cpu-nodes", type=int, default=120_000, help="surface nodes of the CPU-baseline sample")
     ap.add_argument("--cpu-cores", type=int, default=0, help="processes of the CPU baseline (0 = all host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -117,7 +117,17 @@ def parse():
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the partitioned-vs-undivided parity check before the timed region")
     ap.add_argument("--cpu-steps", type=int, default=5, help="timed steps of the cpu_baseline leg")
     ap.add_argument("--pc", default="amg", choices=["amg", "bj"], help="SSH preconditioner: aggregation multigrid or block-Jacobi")
-    return ap.parse_args()
+    ap.add_argument("--config", default="sphere5m", choices=["sphere5m", "core2like", "farclike"],
+                    help="BASELINE.json configs: 5 (default, ~5 M-node band sphere x 48 layers), 3 (CORE2's size: ~127 k nodes x 47 layers, one GPU) "
+                         "or 4 (farc's size and character: ~640 k nodes x 47 layers, rows 3x denser north of 65 N; METIS partitions for N > 1); "
+                         "--nodes / --nl override the sizes")
+    ap.add_argument("--shuffle", action="store_true", help="random node and element numbering (no locality at all: the worst case for the gathers; "
+                                                           "the default numbering is row-major)")
+    a = ap.parse_args()
+    dn, dl = {"sphere5m": (5_000_000, 49), "core2like": (127_000, 48), "farclike": (640_000, 48)}[a.config]
+    a.nodes = a.nodes or dn
+    a.nl = a.nl or dl
+    return a
 
 
 def mem_available_gb():
@@ -137,11 +147,17 @@ def band_dims(target_nodes):
     return nlon, nlon // 2
 
 
+MESH_KW = {}          # set by main() from --config / --shuffle: extra arguments of the synthetic mesh (harness/synth.py lonlat_band_mesh)
+
+
 def build_workload(target_nodes, nl, seed=12345):
     from tests import util
     nlon, nlat = band_dims(target_nodes)
+    if MESH_KW.get("refine_north"):                               # rows get denser towards the north: 120 x 90 rows give 9750 nodes
+        f = (target_nodes / 9750.0) ** 0.5
+        nlon, nlat = int(round(120 * f)) // 2 * 2, int(round(90 * f))
     t0 = time.time()
-    hm = util.build_model("band", nlon=nlon, nlat=nlat, nl=nl, seed=seed, dt=600.0)
+    hm = util.build_model("band", nlon=nlon, nlat=nlat, nl=nl, seed=seed, dt=600.0, **MESH_KW)
     hm.compute_ssh_rhs()
     info = dict(nlon=nlon, nlat=nlat, nl=nl, nod2D=hm.ipar("myDim_nod2D"), elem2D=hm.ipar("myDim_elem2D"),
                 edge2D=hm.ipar("myDim_edge2D"), setup_s=round(time.time() - t0, 1))
@@ -449,13 +465,14 @@ def run_b200(args):
                 clocks=sampler.result(), ntr=ntr, dist=dist, amg_levels=amg_levels, amg_folded=amg_folded, parity=parity)
 
 
-def _cpu_worker(idx, cpu_nodes, nl, steps, warmup, barrier, out):
+def _cpu_worker(idx, cpu_nodes, nl, steps, warmup, barrier, out, mesh_kw=None):
     """One host core = one subdomain of the reference's MPI decomposition: build a sample of the workload, then time
     the oracle's tracer step and the reference's own psolve.c + pARMS (oracle/_ref) on it, all workers stepping at the
     same time so they share the memory system like the ranks of one node would."""
     try:
         from oracle import binding as ob
-        ob.use_timing_build(True)                  # copies compiled with the reference's own optimisation flags (fesom2_b200/build.py)
+        ob.use_timing_build(True)                  # copies compiled with the reference's own optimisation flags (harness/build.py)
+        MESH_KW.update(mesh_kw or {})              # spawned: the parent's globals do not travel
         hm, info = build_workload(cpu_nodes, nl)
         ntr = hm.ipar("num_tracers")
         o = ob.TracerOracle(hm)
@@ -513,7 +530,7 @@ def cpu_reference(args, steps, warmup, nodes_per_core=None):
     _b0.build_host()
     ctx = mp.get_context("spawn")                                                # the parent may hold a CUDA context
     barrier, out = ctx.Barrier(cores), ctx.Queue()
-    procs = [ctx.Process(target=_cpu_worker, args=(i, cpu_nodes, args.nl, steps, warmup, barrier, out)) for i in range(cores)]
+    procs = [ctx.Process(target=_cpu_worker, args=(i, cpu_nodes, args.nl, steps, warmup, barrier, out, dict(MESH_KW))) for i in range(cores)]
     for p_ in procs:
         p_.start()
     res = [out.get() for _ in procs]
@@ -545,8 +562,15 @@ def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    workload = "synthetic lon/lat-band sphere (|lat|<=80, ~8%% land, ragged bathymetry), ~%d surface nodes in total x %d layers, " \
-               "2 tracers, MFCT+QR4C+FCT, zstar" % (args.nodes, args.nl - 1)
+    if args.config == "farclike":
+        MESH_KW["refine_north"] = 3.0
+    if args.shuffle:
+        MESH_KW["shuffle"] = True
+    workload = "%s: synthetic lon/lat-band sphere (|lat|<=80, ~8%% land, ragged bathymetry%s), ~%d surface nodes in total x %d layers, " \
+               "2 tracers, MFCT+QR4C+FCT, zstar, %s numbering" % (
+                   {"sphere5m": "BASELINE config 5", "core2like": "BASELINE config 3 stand-in (CORE2's size)", "farclike": "BASELINE config 4 stand-in (farc's size)"}[args.config],
+                   ", rows 3x denser north of 65 N" if args.config == "farclike" else "", args.nodes, args.nl - 1,
+                   "random (shuffled)" if args.shuffle else "row-major")
     if args.impl == "reference":
         if rank != 0:
             return
