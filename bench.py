@@ -123,6 +123,8 @@ def parse():
                          "--nodes / --nl override the sizes")
     ap.add_argument("--shuffle", action="store_true", help="random node and element numbering (no locality at all: the worst case for the gathers; "
                                                            "the default numbering is row-major)")
+    ap.add_argument("--rcm", action="store_true", help="the randomly numbered mesh after an offline reverse Cuthill-McKee renumbering of its node graph "
+                                                       "(elements sorted by their smallest node): what INTEGRATION.md recommends for badly numbered meshes")
     a = ap.parse_args()
     dn, dl = {"sphere5m": (5_000_000, 49), "core2like": (127_000, 48), "farclike": (640_000, 48)}[a.config]
     a.nodes = a.nodes or dn
@@ -566,11 +568,13 @@ def main():
         MESH_KW["refine_north"] = 3.0
     if args.shuffle:
         MESH_KW["shuffle"] = True
+    if args.rcm:
+        MESH_KW["rcm"] = True
     workload = "%s: synthetic lon/lat-band sphere (|lat|<=80, ~8%% land, ragged bathymetry%s), ~%d surface nodes in total x %d layers, " \
                "2 tracers, MFCT+QR4C+FCT, zstar, %s numbering" % (
                    {"sphere5m": "BASELINE config 5", "core2like": "BASELINE config 3 stand-in (CORE2's size)", "farclike": "BASELINE config 4 stand-in (farc's size)"}[args.config],
                    ", rows 3x denser north of 65 N" if args.config == "farclike" else "", args.nodes, args.nl - 1,
-                   "random (shuffled)" if args.shuffle else "row-major")
+                   "random, then reverse Cuthill-McKee" if args.rcm else "random (shuffled)" if args.shuffle else "row-major")
     if args.impl == "reference":
         if rank != 0:
             return

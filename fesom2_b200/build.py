@@ -23,6 +23,28 @@ def _newer(target, sources):
     return any(os.path.getmtime(s) > t for s in sources)
 
 
+class _BuildLock:
+    """One builder at a time per output directory (flock on a lock file): several ranks of one job — or pytest-xdist workers — that
+    find the same library stale must not compile and link into the same files at once; the ones that waited find it fresh."""
+
+    def __init__(self, directory):
+        os.makedirs(directory, exist_ok=True)
+        self.path = os.path.join(directory, ".build.lock")
+        self.fd = None
+
+    def __enter__(self):
+        import fcntl
+        self.fd = open(self.path, "w")
+        fcntl.flock(self.fd, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *exc):
+        import fcntl
+        fcntl.flock(self.fd, fcntl.LOCK_UN)
+        self.fd.close()
+        return False
+
+
 def _run(cmd, cwd=None):
     r = subprocess.run(cmd, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
@@ -65,13 +87,19 @@ def build_cuda(force=False, verbose=False, out=None, defines=(), fmad=False):
     objdir = os.path.join(PKG, "csrc", "build")
     nvcc = nvcc_path()
     objs = [os.path.join(objdir, os.path.basename(f)[:-3] + tag + ".o") for f in src]
-    todo = [(f, o) for f, o in zip(src, objs) if force or _newer(o, [f] + hdr)]
-    if todo or force or _newer(so, objs):
-        if nvcc is None:
-            if os.path.exists(so) and not force:
-                return so                  # a box without nvcc uses the library that travelled with the snapshot
-            raise RuntimeError("nvcc not found: cannot build libfesom_b200.so")
-        os.makedirs(objdir, exist_ok=True)
+
+    def stale():
+        return [(f, o) for f, o in zip(src, objs) if force or _newer(o, [f] + hdr)]
+    if not (stale() or force or _newer(so, objs)):
+        return so
+    if nvcc is None:
+        if os.path.exists(so) and not force:
+            return so                      # a box without nvcc uses the library that travelled with the snapshot
+        raise RuntimeError("nvcc not found: cannot build libfesom_b200.so")
+    with _BuildLock(objdir):
+        todo = stale()                     # again under the lock: another process may just have built it
+        if not (todo or _newer(so, objs)):
+            return so
         cflags = [x for x in NVCC_FLAGS if x != "-shared" and not (fmad and x == "--fmad=false")] + ["-c"] + ["-D" + d for d in defines]
         if verbose:
             cflags += ["-Xptxas", "-v"]
@@ -79,12 +107,17 @@ def build_cuda(force=False, verbose=False, out=None, defines=(), fmad=False):
         inc = ["-I", os.path.join(ROOT, "include")] + (nf[nf.index("-I"):nf.index("-I") + 2] if "-I" in nf else [])
 
         def one(fo):
-            return _run([nvcc] + cflags + inc + ["-o", fo[1], fo[0]])
+            tmp = fo[1] + ".%d.tmp" % os.getpid()
+            out_ = _run([nvcc] + cflags + inc + ["-o", tmp, fo[0]])
+            os.replace(tmp, fo[1])
+            return out_
         with cf.ThreadPoolExecutor(max_workers=8) as ex:
             outs = list(ex.map(one, todo))
         if verbose:
             print("\n".join(outs))
-        _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC", "-shared", "-o", so] + objs + nccl_flags())
+        tmp_so = so + ".%d.tmp" % os.getpid()
+        _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC", "-shared", "-o", tmp_so] + objs + nccl_flags())
+        os.replace(tmp_so, so)             # a process that already maps the old file keeps it; nobody ever sees a half-written one
     return so
 
 

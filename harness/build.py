@@ -8,7 +8,7 @@
 import glob
 import os
 
-from fesom2_b200.build import ROOT, _newer, _run
+from fesom2_b200.build import ROOT, _BuildLock, _newer, _run
 
 HOST_DIR = os.path.join(ROOT, "harness", "host")
 HOST_SO = os.path.join(HOST_DIR, "libfesom_host.so")
@@ -23,7 +23,11 @@ def build_host(force=False):
     src = sorted(glob.glob(os.path.join(HOST_DIR, "*.cpp")))
     dep = src + glob.glob(os.path.join(HOST_DIR, "*.hpp"))
     if force or _newer(HOST_SO, dep):
-        _run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-o", HOST_SO] + src)
+        with _BuildLock(HOST_DIR):                         # the ranks of one job all get here at once
+            if force or _newer(HOST_SO, dep):
+                tmp = HOST_SO + ".%d.tmp" % os.getpid()
+                _run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-o", tmp] + src)
+                os.replace(tmp, HOST_SO)
     return HOST_SO
 
 
@@ -55,7 +59,9 @@ def build_ref(force=False):
     if not os.path.isdir("/root/reference/lib/parms") or not os.path.exists(mk):
         return REF_SO if os.path.exists(REF_SO) else None
     if force or not os.path.exists(REF_SO) or not os.path.exists(REF_TIMING_SO):
-        _run(["make", "-s", "-f", mk, "-j8", "_ref/libpsolve_ref.so", "_ref/libpsolve_ref_timing.so"], cwd=os.path.join(ROOT, "oracle"))
+        with _BuildLock(os.path.join(ROOT, "oracle", "_ref")):
+            if force or not os.path.exists(REF_SO) or not os.path.exists(REF_TIMING_SO):
+                _run(["make", "-s", "-f", mk, "-j8", "_ref/libpsolve_ref.so", "_ref/libpsolve_ref_timing.so"], cwd=os.path.join(ROOT, "oracle"))
     return REF_SO
 
 

@@ -81,12 +81,14 @@ def fill_state(hm, seed=12345, umax=0.5, hbar_amp=0.3, noise=0.1, water_flux=0.0
 
 # ---------------------------------------------------------------------------------------------------
 def lonlat_band_mesh(nlon, nlat, lat_max=80.0, nl=24, depth_max=5000.0, seed=20261104, land_frac=0.12,
-                     shuffle=False, refine_north=0.0):
+                     shuffle=False, refine_north=0.0, rcm=False):
     """Triangulated lon/lat band (cyclic in longitude) with elliptical land patches and ragged bathymetry.
     Returns the raw arrays `HostModel.set_global_mesh` takes.  Structured-like but stored fully unstructured.
     refine_north = r > 1: multi-resolution variant (the stand-in for the Arctic-refined farc mesh of BASELINE.json
     config 4, which is not in the repository): the meridional spacing shrinks by the factor r between 50 N and 65 N
-    and stays there up to lat_max.  shuffle: random node and element numbering (no locality at all)."""
+    and stays there up to lat_max.  shuffle: random node and element numbering (no locality at all).  rcm: the shuffled mesh
+    renumbered by reverse Cuthill-McKee on the node graph, elements sorted by their smallest node — what an offline
+    bandwidth-reducing renumbering makes of a badly numbered mesh."""
     rng = np.random.default_rng(seed)
     lons = np.linspace(0.0, 360.0, nlon, endpoint=False)
     lats = np.linspace(-lat_max, lat_max, nlat)
@@ -135,13 +137,27 @@ def lonlat_band_mesh(nlon, nlat, lat_max=80.0, nl=24, depth_max=5000.0, seed=202
     tri = newid[tri]
     lon = LON.reshape(-1)[used]
     lat = LAT.reshape(-1)[used]
-    if shuffle:                       # destroy the numbering locality (what a real mesh may look like)
+    if shuffle or rcm:                # destroy the numbering locality (what a real mesh may look like)
         perm = rng.permutation(lon.size)
         inv = np.empty_like(perm)
         inv[perm] = np.arange(perm.size)
         lon, lat = lon[perm], lat[perm]
         tri = inv[tri]
         tri = tri[rng.permutation(tri.shape[0])]
+    if rcm:
+        import scipy.sparse as sp
+        from scipy.sparse.csgraph import reverse_cuthill_mckee
+        n = lon.size
+        a = np.concatenate([tri[:, 0], tri[:, 1], tri[:, 2]])
+        b = np.concatenate([tri[:, 1], tri[:, 2], tri[:, 0]])
+        G = sp.coo_matrix((np.ones(a.size, np.int8), (a, b)), shape=(n, n)).tocsr()
+        G = ((G + G.T) > 0).astype(np.int8).tocsr()
+        perm = np.asarray(reverse_cuthill_mckee(G, symmetric_mode=True))
+        inv = np.empty_like(perm)
+        inv[perm] = np.arange(n)
+        lon, lat = lon[perm], lat[perm]
+        tri = inv[tri]
+        tri = tri[np.argsort(tri.min(axis=1), kind="stable")]
     # vertical grid: stretched, 5 m at the top
     k = np.arange(nl)
     zbar = -depth_max * (np.expm1(3.0 * k / (nl - 1)) / np.expm1(3.0))
