@@ -31,7 +31,15 @@ struct PeerCtl {                // by value into the kernels.  mode 0: one rank;
     unsigned long long* const* flags;   // [nranks] rank r's flag array
     const int* src;             // [nsrc] ranks this rank receives interface values from
 };
-#define SPIN_LIMIT_CYCLES 4000000000ll          // ~2 s: a peer that never arrives raises comm_error instead of hanging the GPU
+// A peer that never arrives raises comm_error (psolve then reports error 48) instead of hanging the GPU.  The limit is ~60 s of SM
+// clocks: the ranks of a job reach their first exchange seconds apart (host-side set-up, page-locking of large arrays), which is not a
+// failure.  Once the flag is up no wait spins any more and the iteration loop ends (done = 1): the failing solve drains in milliseconds.
+#define SPIN_LIMIT_CYCLES 120000000000ll
+__device__ __forceinline__ bool spin_expired(SolverScal* sc, long long t0) {
+    if (*(volatile int*)&sc->comm_error == 0 && clock64() - t0 <= SPIN_LIMIT_CYCLES) return false;
+    sc->comm_error = 1; sc->done = 1;
+    return true;
+}
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) { return *(const volatile unsigned long long*)p; }
 __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) { *(volatile unsigned long long*)p = v; }
 // Interface values over peer memory, fused into the CONSUMING kernel (no launch of its own).  The first `npb` blocks of the
@@ -73,7 +81,7 @@ __device__ __forceinline__ void push_and_wait(const PushArgs& pa, const double* 
         const unsigned long long* f = pc.flags[pc.me] + (size_t)vec * pc.nranks;
         const long long t0 = clock64();
         for (int k = 0; k < pa.nsrc; k++)
-            while (ld_volatile_u64(f + pa.src[k]) < tag) if (clock64() - t0 > SPIN_LIMIT_CYCLES) { sc->comm_error = 1; break; }
+            while (ld_volatile_u64(f + pa.src[k]) < tag) if (spin_expired(sc, t0)) break;
         __threadfence_system();
     }
     __syncthreads();

@@ -138,11 +138,12 @@ __device__ __forceinline__ void reduce2(double a, double b, double* __restrict__
         const long long t0 = clock64();
         double ga = 0.0, gb = 0.0;
         for (int r = 0; r < pc.nranks; r++) {
-            while (ld_volatile_u64(&mine[r].seq) != seq) if (clock64() - t0 > SPIN_LIMIT_CYCLES) { sc->comm_error = 1; break; }
+            while (ld_volatile_u64(&mine[r].seq) != seq) if (spin_expired(sc, t0)) break;
             __threadfence_system();
             ga += *(const volatile double*)&mine[r].a; gb += *(const volatile double*)&mine[r].b;
         }
         sc->tmp0 = ga; sc->tmp1 = gb;
+        if (sc->comm_error) return;                          // a peer never delivered: the sums are not sums, `done` stays up
         apply_scalars(sc, which);
     }
 }
