@@ -43,7 +43,8 @@ ALGO_BYTES = {
 # launches of the column kernels that carry two tracers are profiled under "<name>_x2": twice the per-tracer fields, the
 # tracer-independent ones (volume flux inputs UV and helem, W, area, level depths, thicknesses, areasvol) once
 ALGO_BYTES.update({"k_ho_edge_x2": 2 * 144 - 48, "k_diff_edge_x2": 2 * 88 - 32, "k_lo_x2": 2 * 118 - 56, "k_grad_elem_x2": 80,
-                   "k_fct_bounds_x2": 2 * 72 - 8, "k_ab2_x2": 48, "copy_told_x2": 32, "k_update_x2": 2 * 120 - 24, "k_redi_expl": 64, "k_bh": 48})
+                   "k_fct_bounds_x2": 2 * 72 - 8, "k_ab2_x2": 48, "copy_told_x2": 32, "k_update_x2": 2 * 120 - 24, "k_redi_expl": 64, "k_bh": 48,
+                   "k_impl_diff_x2": 2 * 48 - 16})          # Kv and the level depths once for both tracers
 # SSH kernels: bytes per matrix row per launch (7-wide SELL rows: 7 x (8 B value + 4 B column) + vectors); the
 # block-Jacobi kernels also read their bs x bs inverse once per apply = bs x 8 B per row (added in algo_bytes_row)
 ALGO_BYTES_ROW = {
