@@ -130,6 +130,7 @@ struct TracerCtx {
     // work fields, tiled
     DevBuf<double2> txy, fpm;       // (tr_xy x, y) per element-level; (fct_plus, fct_minus) per node-level
     DevBuf<double> trz, LO, adf_h, adf_v, tstar, eflx;
+    DevBuf<double2> extrema_part;                // per-block partials of fb200_tracer_extrema, kept between calls
     DevBuf<double> redi_v, bh_tmp;   // diff_ver_part_redi_expl's del_ttf term (Redi), temporary_ttf of diff_part_bh; allocated on first use
     // staging for host<->device transfers (reference layout)
     DevBuf<double> stage;

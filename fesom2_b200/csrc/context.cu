@@ -334,7 +334,7 @@ void ctx_release(TracerCtx& c) {
                               &c.helem, &c.adf_h, &c.eflx, &c.T, &c.Told, &c.heat_flux, &c.water_flux, &c.virtual_salt,
                               &c.relax_salt, &c.real_salt_flux, &c.relax2clim, &c.Tclim, &c.Sclim, &c.zon_ztem, &c.zon_a, &c.kgT, &c.kgS, &c.kb2, &c.kb3, &c.hbar, &c.hbar_old, &c.ssh_rhs_old, &c.dhe, &c.esum, &c.CFL, &c.stage, &c.el_g, &c.el_area, &c.n_znb, &c.redi_v, &c.bh_tmp}) b->release();
     c.tile_deg.release(); c.fb_list.release(); c.n_fb = 0; c.ns_p.release(); c.ns_i.release(); c.ns_m.release(); c.ns_d1.release(); c.ns_d2.release();
-    c.UV.release(); c.txy.release(); c.fpm.release(); c.zon_nn.release();
+    c.UV.release(); c.txy.release(); c.fpm.release(); c.extrema_part.release(); c.zon_nn.release();
     for (int k = 0; k < 8; k++) { c.mean8[k].release(); c.mean4[k].release(); }
     c.sa_rowptr.release(); c.sa_colind.release(); c.sa_values.release(); c.sa_rhs.release(); c.sa_eta.release(); c.UVr.release();
     c.edge.release(); c.edgeho.release(); c.ne_slot.release(); c.nie_slot.release(); c.el_nb.release(); c.el_lev.release();

@@ -908,13 +908,13 @@ void tracer_extrema(TracerCtx& c, int tr, double* tmin, double* tmax) {
     fb_copy_sync();
     cudaStream_t st = c.stream = fb_stream();
     const int nb = std::min(148 * 8, (c.myN + 255) / 256);
-    DevBuf<double2> part; part.alloc(nb);
+    if (c.extrema_part.n < (size_t)nb) c.extrema_part.alloc(nb);          // once: a monitoring call per step must not allocate and free every time
+    DevBuf<double2>& part = c.extrema_part;
     KP p = make_kp(c, tr);
     { ProfScope ps_("k_extrema", st); k_extrema<<<nb, 256, 0, st>>>(p, p.T, part.p); LAUNCH_CHECK(); }
     std::vector<double2> h(nb);
     CUDA_CHECK(cudaMemcpyAsync(h.data(), part.p, nb * sizeof(double2), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
-    part.release();
     double lo = 1.0e300, hi = -1.0e300;
     for (const double2& v : h) { lo = v.x < lo ? v.x : lo; hi = v.y > hi ? v.y : hi; }
     *tmin = lo; *tmax = hi;
