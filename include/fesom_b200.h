@@ -42,7 +42,7 @@ void psolver_init(int* id, int* stype, int* pctype, int* pcilutype, int* iluleve
  * rhs, vals and sol may be HOST pointers (the reference's call) or DEVICE pointers (unified addressing decides per pointer): a
  * host that assembles the system on the device solves without crossing PCIe.
  * On several ranks the multigrid preconditioner works on overlapping subdomains (restricted additive Schwarz, FB200_SSH_OVERLAP
- * layers of neighbour rows, default 2, like the reference's RAS) and the small messages of the iteration travel over peer
+ * layers of neighbour rows, default 4; the reference's RAS extends by one layer) and the small messages of the iteration travel over peer
  * memory (CUDA IPC over NVLink) when every rank can map its peers' buffers, else over NCCL (FB200_SSH_COMM=nccl forces it). */
 void psolve(int* id, double* rhs, double* vals, double* sol, int* newvalues);
 void psolver_final(void);
