@@ -69,3 +69,19 @@ def test_psolver_init_refuses_a_multi_process_launch_without_comm_init(monkeypat
     with pytest.raises(api.FesomB200Error, match="fb200_comm_init was not called"):
         api.SSHSolver(hm)
     api.lib().fb200_clear_status()
+
+
+def test_fortran_interface_file_covers_the_host_facing_abi():
+    """include/fesom_b200_interface.F90 (= the module text of INTEGRATION.md) declares every entry point a Fortran host calls; what
+    it leaves out are the test / diagnostic entry points listed here, and psolver_init / psolve, which FESOM declares itself"""
+    f90 = open(os.path.join(ROOT, "include", "fesom_b200_interface.F90")).read()
+    have = set(re.findall(r"name='(\w+)'", f90))
+    diagnostic = {"fb200_amg_host_build", "fb200_amg_host_dims", "fb200_amg_host_fetch", "fb200_amg_host_free", "fb200_amg_host_levels",
+                  "fb200_debug_fetch", "fb200_kernel_launches", "fb200_last_ms", "fb200_profile", "fb200_profile_report",
+                  "fb200_psolve_amg_folded", "fb200_psolve_amg_info", "fb200_psolver_use_graph", "fb200_selftest_div", "fb200_status_message"}
+    names = set(declared_symbols())
+    assert have <= names
+    assert names - have - diagnostic == {"psolver_init", "psolve", "psolver_final"}
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    for nm in have:
+        assert nm in doc, nm
